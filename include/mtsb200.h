@@ -1,0 +1,215 @@
+/*
+ * mtsb200.h -- C ABI of the B200-native rendering backend for Mitsuba 2's hot path.
+ *
+ * Drop-in boundary.  Every entry point cites the reference
+ * interface it replaces (paths relative to the Mitsuba 2 tree).  Plain pointers and
+ * sizes only: no C++ types, no torch types.  All functions return 0 on success and a
+ * negative MTSB_E_* code on failure; mtsb_last_error() gives the message of the last
+ * failure on the calling thread (the reference throws std::runtime_error via Throw(),
+ * include/mitsuba/core/logger.h; the adapter re-throws).
+ *
+ * Memory spaces: every bulk pointer argument is accompanied (per call) by a `mem`
+ * selector: MTSB_MEM_HOST (library stages through pinned memory and copies) or
+ * MTSB_MEM_DEVICE (pointer is a CUDA device pointer of the context's device).
+ */
+#ifndef MTSB200_H
+#define MTSB200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTSB_ABI_VERSION 1
+
+enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
+enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
+
+/* ---- scene description (flattened `Scene`, src/librender/scene.cpp:22-99) ---------- */
+
+/* Texture: `Texture::eval` (include/mitsuba/render/texture.h:40-143).
+ * CONSTANT = src/spectra/srgb.cpp / srgb_d65.cpp / uniform.cpp in the rgb variant,
+ * BITMAP   = src/textures/bitmap.cpp:250-293 (bilinear, repeat wrap, 3x3 uv transform). */
+enum { MTSB_TEX_CONSTANT = 0, MTSB_TEX_BITMAP = 1 };
+typedef struct mtsb_texture_desc {
+    int32_t  type;
+    float    value[3];          /* CONSTANT: rgb */
+    uint32_t width, height;     /* BITMAP */
+    uint32_t channels;          /* BITMAP: 1 or 3 */
+    const float *data;          /* BITMAP: row-major, channels interleaved (host pointer) */
+    float    to_uv[9];          /* BITMAP: row-major 3x3 affine uv transform */
+} mtsb_texture_desc;
+
+/* BSDF: `BSDF::sample/eval/pdf` (include/mitsuba/render/bsdf.h).
+ * DIFFUSE src/bsdfs/diffuse.cpp:78-135, ROUGHCONDUCTOR src/bsdfs/roughconductor.cpp:196-394,
+ * DIELECTRIC src/bsdfs/dielectric.cpp:201-326. Texture ids index mtsb_scene_desc.textures; -1 = absent. */
+enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2 };
+enum { MTSB_MF_BECKMANN = 0, MTSB_MF_GGX = 1 };
+typedef struct mtsb_bsdf_desc {
+    int32_t type;
+    int32_t reflectance_tex;        /* DIFFUSE: reflectance */
+    int32_t eta_tex, k_tex;         /* ROUGHCONDUCTOR: complex IOR (rgb) */
+    int32_t specular_reflectance_tex;   /* ROUGHCONDUCTOR / DIELECTRIC, -1 = 1.0 */
+    int32_t specular_transmittance_tex; /* DIELECTRIC, -1 = 1.0 */
+    float   alpha_u, alpha_v;       /* ROUGHCONDUCTOR */
+    int32_t distribution;           /* MTSB_MF_* */
+    int32_t sample_visible;         /* bool */
+    float   eta;                    /* DIELECTRIC: int_ior / ext_ior */
+} mtsb_bsdf_desc;
+
+/* Emitter: `Emitter::sample_direction/pdf_direction/eval`.
+ * AREA src/emitters/area.cpp:71-125 (constant radiance), ENVMAP src/emitters/envmap.cpp:132-317.
+ * The order of the array is the order of `Scene::m_emitters` (scene.cpp:23-48). */
+enum { MTSB_EMITTER_AREA = 0, MTSB_EMITTER_ENVMAP = 1 };
+typedef struct mtsb_emitter_desc {
+    int32_t  type;
+    float    radiance[3];       /* AREA */
+    int32_t  mesh_id;           /* AREA: index into meshes[] */
+    uint32_t width, height;     /* ENVMAP */
+    const float *rgba;          /* ENVMAP: width*height*4 float32 (alpha ignored), host pointer */
+    float    to_world[16];      /* ENVMAP: row-major 4x4 */
+    float    scale;             /* ENVMAP */
+} mtsb_emitter_desc;
+
+/* Mesh: `Mesh` buffers (include/mitsuba/render/mesh.h:328-332); world-space positions. */
+typedef struct mtsb_mesh_desc {
+    const uint32_t *faces;      /* 3*face_count */
+    const float *positions;     /* 3*vertex_count */
+    const float *normals;       /* 3*vertex_count or NULL */
+    const float *texcoords;     /* 2*vertex_count or NULL */
+    uint32_t face_count, vertex_count;
+    int32_t  bsdf_id;           /* index into bsdfs[] */
+    int32_t  emitter_id;        /* index into emitters[] or -1 */
+} mtsb_mesh_desc;
+
+/* Sensor + film: src/sensors/perspective.cpp:106-222, src/films/hdrfilm.cpp, rfilters. */
+enum { MTSB_RFILTER_BOX = 0, MTSB_RFILTER_TENT = 1, MTSB_RFILTER_GAUSSIAN = 2 };
+typedef struct mtsb_sensor_desc {
+    float    to_world[16];          /* row-major camera-to-world */
+    float    sample_to_camera[16];  /* row-major, perspective.cpp:125-133 */
+    float    near_clip, far_clip;
+    uint32_t film_width, film_height;   /* crop size == film size (crop windows: not yet) */
+    int32_t  rfilter;               /* MTSB_RFILTER_* */
+    float    rfilter_radius;        /* box: 0.5 (+RayEpsilon added internally), tent: 1, gaussian: 4*stddev */
+    float    rfilter_stddev;        /* gaussian */
+} mtsb_sensor_desc;
+
+/* `MonteCarloIntegrator` props (src/librender/integrator.cpp:285-298). */
+typedef struct mtsb_integrator_desc {
+    int32_t max_depth;  /* -1 = unbounded (clamped internally to 2^30) */
+    int32_t rr_depth;   /* default 5 */
+} mtsb_integrator_desc;
+
+typedef struct mtsb_scene_desc {
+    uint32_t n_meshes, n_bsdfs, n_textures, n_emitters, n_sensors;
+    const mtsb_mesh_desc    *meshes;
+    const mtsb_bsdf_desc    *bsdfs;
+    const mtsb_texture_desc *textures;
+    const mtsb_emitter_desc *emitters;
+    const mtsb_sensor_desc  *sensors;
+    mtsb_integrator_desc integrator;
+} mtsb_scene_desc;
+
+/* ---- SoA ray / hit records (128-bit loads) ------------------------------------------ */
+/* ray i = { o_mint[4i..4i+3] = (o.x,o.y,o.z,mint), d_maxt[4i..4i+3] = (d.x,d.y,d.z,maxt) }
+ * closest hit i = hits[4i..4i+3] = (t, u, v, bitcast<float>(global_prim_index)); miss: t = +inf, prim = 0xffffffff.
+ * any hit i = occluded[i] (uint32 0/1).  global prim index = prefix sum of face counts over meshes
+ * (`m_primitive_map`, include/mitsuba/render/kdtree.h:2382-2400). */
+
+typedef struct mtsb_ctx mtsb_ctx;
+typedef struct mtsb_scene mtsb_scene;
+
+/* Per-call statistics (what bench.py turns into Mrays/s, Msamples/s and roofline bytes). */
+typedef struct mtsb_stats {
+    uint64_t samples;           /* camera samples started */
+    uint64_t closest_rays;      /* closest-hit rays traced */
+    uint64_t shadow_rays;       /* any-hit rays traced */
+    uint64_t segments;          /* shade-kernel invocations (path vertices incl. misses) */
+    uint64_t kernel_launches;   /* kernels launched by this call */
+    float    ms_total;          /* device time of the call (CUDA events) */
+    float    ms_closest, ms_any, ms_shade, ms_raygen, ms_film; /* filled when profiling flag set */
+    float    ms_build;          /* BVH build (scene_create / update) */
+    uint32_t bvh_nodes;         /* wide nodes */
+    uint32_t bvh_depth;
+} mtsb_stats;
+
+const char *mtsb_last_error(void);
+int mtsb_abi_version(void);
+
+/* context = one GPU / one process rank */
+int mtsb_ctx_create(int device, mtsb_ctx **out);
+int mtsb_ctx_destroy(mtsb_ctx *ctx);
+/* `Integrator::cancel()` (include/mitsuba/render/integrator.h:51): async-signal-safe flag */
+int mtsb_cancel(mtsb_ctx *ctx);
+
+/* `Scene::Scene` + `accel_init_*` (scene.cpp:22-99, scene_native.inl:3-10): copies everything, builds the BVH on the GPU */
+int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *desc, mtsb_scene **out);
+int mtsb_scene_destroy(mtsb_scene *scene);
+int mtsb_scene_stats(mtsb_scene *scene, mtsb_stats *out);
+/* `Mesh::parameters_changed` (src/librender/mesh.cpp:794-804): new positions, normals recomputed if the
+ * mesh had computed normals, area CDF rebuilt, BVH rebuilt */
+int mtsb_scene_update_vertices(mtsb_scene *scene, uint32_t mesh_id, const float *positions, int mem);
+/* `BitmapTextureImpl::parameters_changed` (src/textures/bitmap.cpp:301-331) */
+int mtsb_scene_update_texture(mtsb_scene *scene, uint32_t tex_id, const float *data, int mem);
+
+/* `Scene::ray_intersect` (scene.cpp:108-116) / `Scene::ray_test` (scene.cpp:131-139), batched */
+int mtsb_intersect_closest(mtsb_scene *scene, uint64_t n, const float *o_mint, const float *d_maxt,
+                           float *hits, int mem, mtsb_stats *stats);
+int mtsb_intersect_any(mtsb_scene *scene, uint64_t n, const float *o_mint, const float *d_maxt,
+                       uint32_t *occluded, int mem, mtsb_stats *stats);
+/* brute-force variant of the above = `Scene::ray_intersect_naive` (scene.cpp:118-129); test hook */
+int mtsb_intersect_naive(mtsb_scene *scene, uint64_t n, const float *o_mint, const float *d_maxt,
+                         float *hits, int mem);
+
+/* `SamplingIntegrator::render` (src/librender/integrator.cpp:52-176), GPU branch semantics (:144-169):
+ * renders samples [spp_begin, spp_begin+spp_count) of every pixel of sensor `sensor_id`, sample s of pixel p
+ * uses PCG32 stream (p*spp_total + s) seeded through TEA with `seed` (independent.cpp:61-70), and ACCUMULATES
+ * into the scene's device film (XYZAW sums).  mtsb_film_* read / clear / reduce it. */
+int mtsb_render(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
+                uint32_t spp_total, uint64_t seed, mtsb_stats *stats);
+int mtsb_film_clear(mtsb_scene *scene, uint32_t sensor_id);
+/* `Film::put(ImageBlock*)`-side export: packed float32 XYZAW, width*height*5 (integrator.cpp:72-74) */
+int mtsb_film_read(mtsb_scene *scene, uint32_t sensor_id, float *xyzaw, int mem);
+/* add an external XYZAW buffer into the device film (used after the NCCL reduce and for resume) */
+int mtsb_film_accumulate(mtsb_scene *scene, uint32_t sensor_id, const float *xyzaw, int mem);
+/* `HDRFilm::bitmap()/develop()` (src/films/hdrfilm.cpp:249-320): weight-normalise + XYZ->linear sRGB, float32 RGB */
+int mtsb_film_develop(mtsb_scene *scene, uint32_t sensor_id, float *rgb, int mem);
+/* device pointer of the internal packed XYZAW staging buffer (for NCCL all-reduce by the host layer) */
+int mtsb_film_device_ptr(mtsb_scene *scene, uint32_t sensor_id, void **ptr, uint64_t *n_floats);
+
+/* Gradient pass (the adjoint of mtsb_render; replaces autodiff through path.cpp, src/python/python/autodiff.py:6-194).
+ * dL_dimage: width*height*3 float32 = dL/d(developed linear RGB).  Outputs are ACCUMULATED:
+ * grad_texture (size of texture `tex_id`), grad_vertices (3*vertex_count of mesh `mesh_id`); either may be NULL. */
+int mtsb_render_grad(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
+                     uint32_t spp_total, uint64_t seed, const float *dL_dimage,
+                     int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,
+                     int mem, mtsb_stats *stats);
+
+/* ---- batched parity hooks (device math called exactly as the kernels call it) ------- */
+/* `PCG32::seed/next_float32` (ext/enoki/include/enoki/random.h:62-101): out[i*n_draws + k] */
+int mtsb_pcg32_floats(mtsb_ctx *ctx, uint64_t n, const uint64_t *initstate, const uint64_t *initseq,
+                      uint32_t n_draws, float *out);
+/* sampler seeding of the wavefront: state/inc of stream idx (independent.cpp:67-70, core/random.h:94-113) */
+int mtsb_sampler_seed(mtsb_ctx *ctx, uint64_t n, uint64_t seed, uint64_t *state, uint64_t *inc);
+/* `Sensor::sample_ray` (perspective.cpp:151-188): pos = position_sample in [0,1]^2 */
+int mtsb_sensor_sample_ray(mtsb_scene *scene, uint32_t sensor_id, uint64_t n, const float *pos2,
+                           float *o_mint, float *d_maxt);
+/* `BSDF::sample` / `eval` / `pdf` in local frame. wi: 3n, uv: 2n, sample1: n, sample2: 2n.
+ * out_sample: 8n = (wo.xyz, pdf, eta, weight.rgb)... see DESIGN.md; eval: 3n; pdf: n */
+int mtsb_bsdf_sample(mtsb_scene *scene, uint32_t bsdf_id, uint64_t n, const float *wi, const float *uv,
+                     const float *sample1, const float *sample2, float *out9);
+int mtsb_bsdf_eval_pdf(mtsb_scene *scene, uint32_t bsdf_id, uint64_t n, const float *wi, const float *uv,
+                       const float *wo, float *eval3, float *pdf);
+/* `Scene::sample_emitter_direction` without the visibility test (scene.cpp:141-176):
+ * ref_p: 3n, sample: 2n -> out: 11n = (d.xyz, dist, pdf, value.rgb, n.xyz) */
+int mtsb_sample_emitter_direction(mtsb_scene *scene, uint64_t n, const float *ref_p, const float *sample2,
+                                  float *out11);
+/* `ImageBlock::put(pos, value)` (src/librender/imageblock.cpp:79-172) into the device film: pos 2n, value 5n */
+int mtsb_film_put(mtsb_scene *scene, uint32_t sensor_id, uint64_t n, const float *pos2, const float *value5);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTSB200_H */

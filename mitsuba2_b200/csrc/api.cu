@@ -1,0 +1,691 @@
+// api.cu -- the C ABI (include/mtsb200.h): scene snapshot upload, GPU BVH build, batched intersection,
+// wavefront render loop, film export.  No torch types, no Mitsuba headers.
+#include "../../include/mtsb200.h"
+#include "kernels.cuh"
+#include "host_tables.h"
+#include <cub/cub.cuh>
+#include <string>
+#include <vector>
+#include <memory>
+#include <cstring>
+#include <cstdio>
+
+using namespace mtsb;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(MTSB_E_CUDA, std::string(#call ": ") + cudaGetErrorString(e_)); } while (0)
+#define CHECK_ARG(c) do { if (!(c)) return fail(MTSB_E_INVALID, "invalid argument: " #c); } while (0)
+
+template <typename T> struct DevBuf {
+    T *p = nullptr; size_t n = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf &) = delete; DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    cudaError_t alloc(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc((void **) &p, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    cudaError_t upload(const T *src, size_t count, cudaStream_t s) {
+        cudaError_t e = alloc(count); if (e != cudaSuccess) return e;
+        if (count == 0) return cudaSuccess;
+        return cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, s);
+    }
+};
+
+struct mtsb_ctx {
+    int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
+};
+
+struct SensorHost { SensorDev dev; DevBuf<float4> xyza; DevBuf<float> w; DevBuf<float> packed; };
+
+struct mtsb_scene {
+    mtsb_ctx *ctx;
+    // host copies needed for updates
+    std::vector<MeshDev> meshes; std::vector<std::vector<uint32_t>> mesh_faces; std::vector<bool> computed_normals;
+    std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
+    std::vector<float> h_pos, h_nrm;
+    // device
+    DevBuf<float> pos, nrm, uv; DevBuf<uint4> faces;
+    DevBuf<MeshDev> d_meshes; DevBuf<TexDev> d_tex; DevBuf<BsdfDev> d_bsdfs; DevBuf<EmitterDev> d_emitters;
+    std::vector<std::unique_ptr<DevBuf<float>>> tables;       // texture data, cdfs, envmap levels
+    std::vector<int> tex_table;                               // texture id -> tables index (-1 constant)
+    std::vector<int> emitter_cdf_table;
+    DevBuf<float4> env_rgba;
+    DevBuf<uint4> nodes; DevBuf<float4> tris;
+    SceneDev dev;
+    std::vector<std::unique_ptr<SensorHost>> sensors;
+    // wavefront pool
+    uint32_t pool = 0;
+    DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result;
+    DevBuf<uint4> q_misc[2], q_rng[2];
+    DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
+    mtsb_stats build_stats;
+    float3 bbox_lo, bbox_hi;
+};
+
+extern "C" const char *mtsb_last_error(void) { return g_err.c_str(); }
+extern "C" int mtsb_abi_version(void) { return MTSB_ABI_VERSION; }
+
+extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
+    CHECK_ARG(out);
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(MTSB_E_INVALID, "no such CUDA device");
+    CU(cudaSetDevice(device));
+    mtsb_ctx *c = new mtsb_ctx();
+    c->device = device; c->cancel = 0;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1));
+    *out = c;
+    return MTSB_OK;
+}
+extern "C" int mtsb_ctx_destroy(mtsb_ctx *c) {
+    if (!c) return MTSB_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaStreamDestroy(c->stream);
+    delete c;
+    return MTSB_OK;
+}
+extern "C" int mtsb_cancel(mtsb_ctx *c) { if (c) c->cancel = 1; return MTSB_OK; }
+
+static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) / kBlock); }
+
+// ---------------------------------------------------------------------------------------------------
+// GPU BVH build
+// ---------------------------------------------------------------------------------------------------
+static int build_bvh(mtsb_scene *s) {
+    cudaStream_t st = s->ctx->stream;
+    uint32_t n = (uint32_t) s->faces.n;
+    s->dev.bvh.n_tris = n;
+    s->build_stats.bvh_nodes = 0; s->build_stats.bvh_depth = 0;
+    if (n == 0) { s->dev.bvh.nodes = nullptr; s->dev.bvh.tris = nullptr; return MTSB_OK; }
+    CU(cudaEventRecord(s->ctx->ev0, st));
+    DevBuf<float4> tlo, thi, nlo, nhi; DevBuf<uint64_t> keys, keys2; DevBuf<uint32_t> order, order2, rfirst, rlast, flags, counters;
+    DevBuf<int> left, right, parent, wide_bin; DevBuf<float> bounds;
+    CU(tlo.alloc(n)); CU(thi.alloc(n)); CU(nlo.alloc(2 * (size_t) n)); CU(nhi.alloc(2 * (size_t) n));
+    CU(keys.alloc(n)); CU(keys2.alloc(n)); CU(order.alloc(n)); CU(order2.alloc(n));
+    CU(rfirst.alloc(n)); CU(rlast.alloc(n)); CU(flags.alloc(n)); CU(counters.alloc(2));
+    CU(left.alloc(n)); CU(right.alloc(n)); CU(parent.alloc(2 * (size_t) n)); CU(wide_bin.alloc(n + 1));
+    CU(bounds.alloc(6));
+    CU(s->nodes.alloc(5 * ((size_t) n + 1))); CU(s->tris.alloc(3 * (size_t) n));
+    BvhBuild b;
+    b.pos = s->pos.p; b.faces = s->faces.p; b.n = n;
+    b.tlo = tlo.p; b.thi = thi.p; b.keys = keys.p; b.order = order.p; b.left = left.p; b.right = right.p; b.parent = parent.p;
+    b.rfirst = rfirst.p; b.rlast = rlast.p; b.nlo = nlo.p; b.nhi = nhi.p; b.flags = flags.p;
+    b.nodes = s->nodes.p; b.tris = s->tris.p; b.wide_bin = wide_bin.p; b.counters = counters.p;
+    float init[6] = { INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY };
+    CU(cudaMemcpyAsync(bounds.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    k_tri_bounds<<<grid_for(n), kBlock, 0, st>>>(b, bounds.p);
+    float hb[6];
+    CU(cudaMemcpyAsync(hb, bounds.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    b.scene_lo = mk3(hb[0], hb[1], hb[2]); b.scene_hi = mk3(hb[3], hb[4], hb[5]);
+    s->bbox_lo = b.scene_lo; s->bbox_hi = b.scene_hi;
+    k_morton<<<grid_for(n), kBlock, 0, st>>>(b);
+    {   // radix sort (library primitive; the build is not on the per-ray hot path)
+        size_t tmp_bytes = 0;
+        CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys2.p, order.p, order2.p, (int) n, 0, 63, st));
+        DevBuf<unsigned char> tmp; CU(tmp.alloc(tmp_bytes));
+        CU(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, keys2.p, order.p, order2.p, (int) n, 0, 63, st));
+        CU(cudaStreamSynchronize(st));
+        b.keys = keys2.p; b.order = order2.p;
+    }
+    CU(cudaMemsetAsync(flags.p, 0, n * sizeof(uint32_t), st));
+    if (n > 1) k_lbvh_nodes<<<grid_for(n - 1), kBlock, 0, st>>>(b);
+    k_lbvh_fit<<<grid_for(n), kBlock, 0, st>>>(b);
+    uint32_t c0[2] = { 1u, 0u };
+    int root = n > 1 ? 0 : 0;     // internal node 0, or leaf id (n-1)+0 = 0 when n == 1
+    CU(cudaMemcpyAsync(counters.p, c0, sizeof(c0), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(wide_bin.p, &root, sizeof(int), cudaMemcpyHostToDevice, st));
+    uint32_t begin = 0, end = 1, depth = 0;
+    while (begin < end) {
+        k_collapse<<<grid_for(end - begin), kBlock, 0, st>>>(b, begin, end);
+        uint32_t hc[2];
+        CU(cudaMemcpyAsync(hc, counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        begin = end; end = hc[0]; depth++;
+        if (depth > 4096) return fail(MTSB_E_INVALID, "BVH collapse did not terminate");
+    }
+    CU(cudaGetLastError());
+    if (depth > (uint32_t) (kStackFast + kStackSlow)) return fail(MTSB_E_INVALID, "BVH too deep for the traversal stack");
+    CU(cudaEventRecord(s->ctx->ev1, st));
+    CU(cudaEventSynchronize(s->ctx->ev1));
+    CU(cudaEventElapsedTime(&s->build_stats.ms_build, s->ctx->ev0, s->ctx->ev1));
+    s->build_stats.bvh_nodes = end; s->build_stats.bvh_depth = depth;
+    s->dev.bvh.nodes = s->nodes.p; s->dev.bvh.tris = s->tris.p;
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Scene snapshot
+// ---------------------------------------------------------------------------------------------------
+static int upload_struct_arrays(mtsb_scene *s) {
+    cudaStream_t st = s->ctx->stream;
+    CU(s->d_meshes.upload(s->meshes.data(), s->meshes.size(), st));
+    CU(s->d_tex.upload(s->tex.data(), s->tex.size(), st));
+    CU(s->d_bsdfs.upload(s->bsdfs.data(), s->bsdfs.size(), st));
+    CU(s->d_emitters.upload(s->emitters.data(), s->emitters.size(), st));
+    CU(cudaStreamSynchronize(st));
+    s->dev.pos = s->pos.p; s->dev.nrm = s->nrm.p; s->dev.uv = s->uv.p; s->dev.faces = s->faces.p;
+    s->dev.meshes = s->d_meshes.p; s->dev.tex = s->d_tex.p; s->dev.bsdfs = s->d_bsdfs.p; s->dev.emitters = s->d_emitters.p;
+    return MTSB_OK;
+}
+
+static int build_area_tables(mtsb_scene *s) {
+    cudaStream_t st = s->ctx->stream;
+    for (size_t e = 0; e < s->emitters.size(); ++e) {
+        EmitterDev &em = s->emitters[e];
+        if (em.type != MTSB_EMITTER_AREA) continue;
+        const MeshDev &m = s->meshes[em.mesh];
+        AreaTable t;
+        try { t = build_area_table(s->h_pos.data() + 3 * (size_t) m.vert_begin, s->mesh_faces[em.mesh].data(), m.face_count); }
+        catch (const std::exception &ex) { return fail(MTSB_E_INVALID, ex.what()); }
+        int ti = s->emitter_cdf_table[e];
+        if (ti < 0) { s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1; s->emitter_cdf_table[e] = ti; }
+        CU(s->tables[ti]->upload(t.cdf.data(), t.cdf.size(), st));
+        CU(cudaStreamSynchronize(st));
+        em.cdf = s->tables[ti]->p; em.cdf_sum = t.sum; em.normalization = t.normalization; em.valid_lo = t.valid_lo; em.valid_hi = t.valid_hi;
+    }
+    return MTSB_OK;
+}
+
+static void update_env_bsphere(mtsb_scene *s) {
+    // Scene bbox -> bounding sphere (envmap.cpp:126-130): radius = |max - center| * (1 + RayEpsilon)
+    float3 c = (s->bbox_lo + s->bbox_hi) * 0.5f;
+    float r = s->faces.n ? norm(s->bbox_hi - c) : 0.f;
+    r = fmaxf(kRayEpsilon, r * (1.f + kRayEpsilon));
+    for (auto &em : s->emitters) if (em.type == MTSB_EMITTER_ENVMAP) em.bsphere_radius = r;
+}
+
+extern "C" int mtsb_scene_destroy(mtsb_scene *s) {
+    if (!s) return MTSB_OK;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    delete s;
+    return MTSB_OK;
+}
+
+extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_scene **out) {
+    CHECK_ARG(ctx); CHECK_ARG(d); CHECK_ARG(out);
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    std::unique_ptr<mtsb_scene> s(new mtsb_scene());
+    s->ctx = ctx;
+    memset(&s->dev, 0, sizeof(SceneDev)); memset(&s->build_stats, 0, sizeof(mtsb_stats));
+    // ---- meshes
+    std::vector<float> h_uv; std::vector<uint4> h_faces;
+    uint32_t vbase = 0, fbase = 0;
+    for (uint32_t i = 0; i < d->n_meshes; ++i) {
+        const mtsb_mesh_desc &m = d->meshes[i];
+        CHECK_ARG(m.positions && (m.faces || m.face_count == 0));
+        CHECK_ARG(m.bsdf_id >= 0 && (uint32_t) m.bsdf_id < d->n_bsdfs);
+        CHECK_ARG(m.emitter_id < (int32_t) d->n_emitters);
+        MeshDev md; md.face_begin = fbase; md.face_count = m.face_count; md.vert_begin = vbase; md.vert_count = m.vertex_count;
+        md.bsdf = m.bsdf_id; md.emitter = m.emitter_id; md.has_normals = m.normals != nullptr; md.has_uv = m.texcoords != nullptr;
+        s->meshes.push_back(md);
+        s->h_pos.insert(s->h_pos.end(), m.positions, m.positions + 3 * (size_t) m.vertex_count);
+        if (m.normals) s->h_nrm.insert(s->h_nrm.end(), m.normals, m.normals + 3 * (size_t) m.vertex_count);
+        else s->h_nrm.insert(s->h_nrm.end(), 3 * (size_t) m.vertex_count, 0.f);
+        if (m.texcoords) h_uv.insert(h_uv.end(), m.texcoords, m.texcoords + 2 * (size_t) m.vertex_count);
+        else h_uv.insert(h_uv.end(), 2 * (size_t) m.vertex_count, 0.f);
+        s->mesh_faces.emplace_back(m.faces, m.faces + 3 * (size_t) m.face_count);
+        s->computed_normals.push_back(false);
+        for (uint32_t f = 0; f < m.face_count; ++f) {
+            uint32_t a = m.faces[3 * f], b = m.faces[3 * f + 1], c = m.faces[3 * f + 2];
+            if (a >= m.vertex_count || b >= m.vertex_count || c >= m.vertex_count) return fail(MTSB_E_INVALID, "face index out of range");
+            h_faces.push_back(make_uint4(a + vbase, b + vbase, c + vbase, i));
+        }
+        vbase += m.vertex_count; fbase += m.face_count;
+    }
+    CU(s->pos.upload(s->h_pos.data(), s->h_pos.size(), st));
+    CU(s->nrm.upload(s->h_nrm.data(), s->h_nrm.size(), st));
+    CU(s->uv.upload(h_uv.data(), h_uv.size(), st));
+    CU(s->faces.upload(h_faces.data(), h_faces.size(), st));
+    CU(cudaStreamSynchronize(st));
+    // ---- textures
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const mtsb_texture_desc &t = d->textures[i];
+        TexDev td; memset(&td, 0, sizeof(td));
+        td.type = t.type; td.value = mk3(t.value[0], t.value[1], t.value[2]);
+        int ti = -1;
+        if (t.type == MTSB_TEX_BITMAP) {
+            CHECK_ARG(t.data && t.width >= 2 && t.height >= 2 && (t.channels == 1 || t.channels == 3));
+            td.w = t.width; td.h = t.height; td.ch = t.channels; memcpy(td.to_uv, t.to_uv, sizeof(td.to_uv));
+            s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1;
+            CU(s->tables[ti]->upload(t.data, (size_t) t.width * t.height * t.channels, st));
+            CU(cudaStreamSynchronize(st));
+            td.data = s->tables[ti]->p;
+        } else CHECK_ARG(t.type == MTSB_TEX_CONSTANT);
+        s->tex.push_back(td); s->tex_table.push_back(ti);
+    }
+    // ---- bsdfs
+    auto tex_ok = [&](int32_t id, bool optional) { return (optional && id < 0) || (id >= 0 && (uint32_t) id < d->n_textures); };
+    for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
+        const mtsb_bsdf_desc &b = d->bsdfs[i];
+        BsdfDev bd; memset(&bd, 0, sizeof(bd));
+        bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex;
+        bd.spec_t = b.specular_transmittance_tex; bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution;
+        bd.sample_visible = b.sample_visible; bd.eta_f = b.eta;
+        if (b.type == MTSB_BSDF_DIFFUSE) CHECK_ARG(tex_ok(b.reflectance_tex, false));
+        else if (b.type == MTSB_BSDF_ROUGHCONDUCTOR) CHECK_ARG(tex_ok(b.eta_tex, false) && tex_ok(b.k_tex, false) && tex_ok(b.specular_reflectance_tex, true));
+        else if (b.type == MTSB_BSDF_DIELECTRIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.specular_reflectance_tex, true) && tex_ok(b.specular_transmittance_tex, true));
+        else return fail(MTSB_E_INVALID, "unknown BSDF type");
+        s->bsdfs.push_back(bd);
+    }
+    // ---- BVH (also yields the scene bbox)
+    int rc = build_bvh(s.get());
+    if (rc) return rc;
+    // ---- emitters
+    s->dev.env_emitter = -1;
+    for (uint32_t i = 0; i < d->n_emitters; ++i) {
+        const mtsb_emitter_desc &e = d->emitters[i];
+        EmitterDev ed; memset(&ed, 0, sizeof(ed));
+        ed.type = e.type;
+        s->emitter_cdf_table.push_back(-1);
+        if (e.type == MTSB_EMITTER_AREA) {
+            CHECK_ARG(e.mesh_id >= 0 && (uint32_t) e.mesh_id < d->n_meshes && d->meshes[e.mesh_id].emitter_id == (int32_t) i);
+            ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
+        } else if (e.type == MTSB_EMITTER_ENVMAP) {
+            CHECK_ARG(e.rgba && e.width >= 2 && e.height >= 2);
+            if (s->dev.env_emitter >= 0) return fail(MTSB_E_INVALID, "only one environment emitter is allowed");
+            s->dev.env_emitter = (int) i;
+            ed.w = e.width; ed.h = e.height; ed.scale = e.scale;
+            memcpy(ed.to_world, e.to_world, sizeof(ed.to_world));
+            if (!invert4x4(e.to_world, ed.to_local)) return fail(MTSB_E_INVALID, "envmap to_world is singular");
+            size_t npx = (size_t) e.width * e.height;
+            std::vector<float4> rgba(npx);
+            for (size_t k = 0; k < npx; ++k) rgba[k] = make_float4(e.rgba[4 * k], e.rgba[4 * k + 1], e.rgba[4 * k + 2], 1.f);
+            CU(s->env_rgba.upload(rgba.data(), npx, st));
+            ed.rgba = s->env_rgba.p;
+            std::vector<float> lum = env_importance(e.rgba, e.width, e.height);
+            H2DTable h = build_h2d(lum.data(), e.width, e.height);
+            if ((int) h.levels.size() > kMaxEnvLevels) return fail(MTSB_E_INVALID, "envmap too large");
+            ed.n_levels = (int) h.levels.size();
+            for (size_t l = 0; l < h.levels.size(); ++l) {
+                s->tables.emplace_back(new DevBuf<float>());
+                CU(s->tables.back()->upload(h.levels[l].data(), h.levels[l].size(), st));
+                ed.level_data[l] = s->tables.back()->p; ed.level_width[l] = h.widths[l];
+            }
+            CU(cudaStreamSynchronize(st));
+        } else return fail(MTSB_E_INVALID, "unknown emitter type");
+        s->emitters.push_back(ed);
+    }
+    s->dev.n_emitters = (int) s->emitters.size();
+    rc = build_area_tables(s.get()); if (rc) return rc;
+    update_env_bsphere(s.get());
+    // ---- sensors + films
+    for (uint32_t i = 0; i < d->n_sensors; ++i) {
+        const mtsb_sensor_desc &sd = d->sensors[i];
+        CHECK_ARG(sd.film_width > 0 && sd.film_height > 0);
+        std::unique_ptr<SensorHost> sh(new SensorHost());
+        SensorDev &sn = sh->dev; memset(&sn, 0, sizeof(sn));
+        memcpy(sn.to_world, sd.to_world, sizeof(sn.to_world)); memcpy(sn.sample_to_camera, sd.sample_to_camera, sizeof(sn.sample_to_camera));
+        sn.near_clip = sd.near_clip; sn.far_clip = sd.far_clip; sn.width = sd.film_width; sn.height = sd.film_height;
+        sn.rfilter = sd.rfilter; sn.stddev = sd.rfilter_stddev;
+        sn.radius = sd.rfilter == MTSB_RFILTER_BOX ? sd.rfilter_radius + kRayEpsilon : sd.rfilter_radius;
+        size_t npx = (size_t) sn.width * sn.height;
+        CU(sh->xyza.alloc(npx)); CU(sh->w.alloc(npx)); CU(sh->packed.alloc(5 * npx));
+        CU(cudaMemsetAsync(sh->xyza.p, 0, npx * sizeof(float4), st)); CU(cudaMemsetAsync(sh->w.p, 0, npx * sizeof(float), st));
+        sn.film_xyza = sh->xyza.p; sn.film_w = sh->w.p;
+        s->sensors.push_back(std::move(sh));
+    }
+    s->dev.max_depth = d->integrator.max_depth < 0 ? (1 << 30) : d->integrator.max_depth;
+    s->dev.rr_depth = d->integrator.rr_depth;
+    rc = upload_struct_arrays(s.get()); if (rc) return rc;
+    CU(s->counters.alloc(2048)); CU(s->dstats.alloc(4));
+    *out = s.release();
+    return MTSB_OK;
+}
+
+extern "C" int mtsb_scene_stats(mtsb_scene *s, mtsb_stats *out) {
+    CHECK_ARG(s && out);
+    *out = s->build_stats;
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Batched intersection: Scene::ray_intersect / ray_test / ray_intersect_naive
+// ---------------------------------------------------------------------------------------------------
+struct Staging {   // host<->device staging for MTSB_MEM_HOST callers
+    std::vector<std::unique_ptr<DevBuf<unsigned char>>> bufs;
+    template <typename T> int in(const T *src, size_t count, int mem, cudaStream_t st, const T **out) {
+        if (mem == MTSB_MEM_DEVICE) { *out = src; return MTSB_OK; }
+        bufs.emplace_back(new DevBuf<unsigned char>());
+        CU(bufs.back()->alloc(count * sizeof(T)));
+        CU(cudaMemcpyAsync(bufs.back()->p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+        *out = (const T *) bufs.back()->p; return MTSB_OK;
+    }
+    template <typename T> int out(T *dst, size_t count, int mem, T **dev) {
+        if (mem == MTSB_MEM_DEVICE) { *dev = dst; return MTSB_OK; }
+        bufs.emplace_back(new DevBuf<unsigned char>());
+        CU(bufs.back()->alloc(count * sizeof(T)));
+        *dev = (T *) bufs.back()->p; return MTSB_OK;
+    }
+    template <typename T> int back(T *dst, const T *dev, size_t count, int mem, cudaStream_t st) {
+        if (mem == MTSB_MEM_DEVICE) return MTSB_OK;
+        CU(cudaMemcpyAsync(dst, dev, count * sizeof(T), cudaMemcpyDeviceToHost, st));
+        return MTSB_OK;
+    }
+};
+#define RC(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
+
+static int intersect_common(mtsb_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, float *hits, uint32_t *occ,
+                            int mem, int mode, mtsb_stats *stats) {
+    CHECK_ARG(s && (n == 0 || (o_mint && d_maxt)) && n < (1ull << 32));
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n == 0) return MTSB_OK;
+    Staging sg; const float *d_o, *d_d; float *d_h = nullptr; uint32_t *d_occ = nullptr;
+    RC(sg.in(o_mint, 4 * n, mem, st, &d_o)); RC(sg.in(d_maxt, 4 * n, mem, st, &d_d));
+    if (mode == 1) RC(sg.out(occ, n, mem, &d_occ)); else RC(sg.out(hits, 4 * n, mem, &d_h));
+    CU(cudaEventRecord(s->ctx->ev0, st));
+    if (mode == 0) k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr);
+    else if (mode == 1) k_trace<true><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ);
+    else k_trace_naive<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h);
+    CU(cudaEventRecord(s->ctx->ev1, st));
+    CU(cudaGetLastError());
+    if (mode == 1) RC(sg.back(occ, d_occ, n, mem, st)); else RC(sg.back(hits, d_h, 4 * n, mem, st));
+    CU(cudaStreamSynchronize(st));
+    if (stats) {
+        CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
+        stats->kernel_launches = 1;
+        if (mode == 1) { stats->shadow_rays = n; stats->ms_any = stats->ms_total; } else { stats->closest_rays = n; stats->ms_closest = stats->ms_total; }
+    }
+    return MTSB_OK;
+}
+extern "C" int mtsb_intersect_closest(mtsb_scene *s, uint64_t n, const float *o, const float *d, float *hits, int mem, mtsb_stats *stats) {
+    CHECK_ARG(n == 0 || hits); return intersect_common(s, n, o, d, hits, nullptr, mem, 0, stats);
+}
+extern "C" int mtsb_intersect_any(mtsb_scene *s, uint64_t n, const float *o, const float *d, uint32_t *occ, int mem, mtsb_stats *stats) {
+    CHECK_ARG(n == 0 || occ); return intersect_common(s, n, o, d, nullptr, occ, mem, 1, stats);
+}
+extern "C" int mtsb_intersect_naive(mtsb_scene *s, uint64_t n, const float *o, const float *d, float *hits, int mem) {
+    CHECK_ARG(n == 0 || hits); return intersect_common(s, n, o, d, hits, nullptr, mem, 2, nullptr);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Wavefront render
+// ---------------------------------------------------------------------------------------------------
+static uint32_t pool_limit() {
+    const char *e = getenv("MTSB_POOL");
+    if (e) { long v = atol(e); if (v >= 1024) return (uint32_t) v; }
+    return 1u << 23;
+}
+static int ensure_pool(mtsb_scene *s, uint32_t n) {
+    if (n <= s->pool) return MTSB_OK;
+    for (int k = 0; k < 2; ++k) {
+        CU(s->q_o[k].alloc(n)); CU(s->q_d[k].alloc(n)); CU(s->q_hit[k].alloc(n)); CU(s->q_te[k].alloc(n));
+        CU(s->q_misc[k].alloc(n)); CU(s->q_rng[k].alloc(n));
+    }
+    CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n));
+    s->pool = n;
+    return MTSB_OK;
+}
+static PathQueue make_queue(mtsb_scene *s, int k) {
+    PathQueue q; q.o_mint = s->q_o[k].p; q.d_maxt = s->q_d[k].p; q.hit = s->q_hit[k].p; q.thr_eta = s->q_te[k].p;
+    q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; return q;
+}
+
+extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
+                           uint64_t seed, mtsb_stats *stats) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && spp_count > 0 && spp_begin + spp_count <= spp_total);
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    SensorDev sn = s->sensors[sensor_id]->dev;
+    uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
+    if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");
+    uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
+    RC(ensure_pool(s, pool));
+    ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
+    CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
+    CU(cudaEventRecord(s->ctx->ev0, st));
+    uint64_t launches = 0;
+    int max_iter = s->dev.max_depth < 1000 ? s->dev.max_depth : 1000;
+    bool poll = s->dev.max_depth > 16;
+    for (uint64_t off = 0; off < total; off += pool) {
+        if (s->ctx->cancel) { s->ctx->cancel = 0; cudaStreamSynchronize(st); return fail(MTSB_E_CANCELLED, "render cancelled"); }
+        uint32_t n = (uint32_t) ((total - off) < pool ? (total - off) : pool);
+        RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total;
+        b.seed = seed; b.result = s->result.p;
+        CU(cudaMemsetAsync(s->counters.p, 0, 2048 * sizeof(uint32_t), st));
+        int cur = 0;
+        k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); launches++;
+        for (int depth = 1; depth <= max_iter; ++depth) {
+            PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
+            k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr);
+            k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth);
+            launches += 2;
+            if (depth < s->dev.max_depth) {
+                k_shadow<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p);
+                launches++;
+            }
+            cur ^= 1;
+            if (poll) {
+                uint32_t next = 0;
+                CU(cudaMemcpyAsync(&next, s->counters.p + depth + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                if (next == 0) break;
+            }
+        }
+        k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); launches++;
+    }
+    CU(cudaEventRecord(s->ctx->ev1, st));
+    unsigned long long hs[4];
+    CU(cudaMemcpyAsync(hs, s->dstats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->samples = total; stats->closest_rays = hs[0]; stats->shadow_rays = hs[1]; stats->segments = hs[2];
+        stats->kernel_launches = launches;
+        CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
+    }
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Film
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mtsb_film_clear(mtsb_scene *s, uint32_t sensor_id) {
+    CHECK_ARG(s && sensor_id < s->sensors.size());
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    CU(cudaMemsetAsync(sh.xyza.p, 0, npx * sizeof(float4), s->ctx->stream)); CU(cudaMemsetAsync(sh.w.p, 0, npx * sizeof(float), s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+extern "C" int mtsb_film_device_ptr(mtsb_scene *s, uint32_t sensor_id, void **ptr, uint64_t *n_floats) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && ptr && n_floats);
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    k_film_pack<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, sh.packed.p);
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    *ptr = sh.packed.p; *n_floats = 5 * npx;
+    return MTSB_OK;
+}
+extern "C" int mtsb_film_read(mtsb_scene *s, uint32_t sensor_id, float *xyzaw, int mem) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && xyzaw);
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    k_film_pack<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, sh.packed.p);
+    CU(cudaMemcpyAsync(xyzaw, sh.packed.p, 5 * npx * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+static int film_write(mtsb_scene *s, uint32_t sensor_id, const float *xyzaw, int mem, int replace) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && xyzaw);
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    if ((const void *) xyzaw != (const void *) sh.packed.p)
+        CU(cudaMemcpyAsync(sh.packed.p, xyzaw, 5 * npx * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ctx->stream));
+    k_film_unpack_add<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, sh.packed.p, replace);
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+extern "C" int mtsb_film_accumulate(mtsb_scene *s, uint32_t sensor_id, const float *xyzaw, int mem) { return film_write(s, sensor_id, xyzaw, mem, 0); }
+extern "C" int mtsb_film_develop(mtsb_scene *s, uint32_t sensor_id, float *rgb, int mem) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && rgb);
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    Staging sg; float *d_rgb; RC(sg.out(rgb, 3 * npx, mem, &d_rgb));
+    k_film_develop<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, d_rgb);
+    RC(sg.back(rgb, d_rgb, 3 * npx, mem, s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+extern "C" int mtsb_film_put(mtsb_scene *s, uint32_t sensor_id, uint64_t n, const float *pos2, const float *value5) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && (n == 0 || (pos2 && value5)));
+    CU(cudaSetDevice(s->ctx->device));
+    if (n == 0) return MTSB_OK;
+    cudaStream_t st = s->ctx->stream; Staging sg; const float *dp, *dv;
+    RC(sg.in(pos2, 2 * n, MTSB_MEM_HOST, st, &dp)); RC(sg.in(value5, 5 * n, MTSB_MEM_HOST, st, &dv));
+    k_film_put<<<grid_for(n), kBlock, 0, st>>>(s->sensors[sensor_id]->dev, (uint32_t) n, dp, dv);
+    CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Parameter updates (Mesh::parameters_changed, BitmapTexture::parameters_changed)
+// ---------------------------------------------------------------------------------------------------
+// Mesh::recompute_vertex_normals (src/librender/mesh.cpp:199-276, dynamic-array branch: angle-weighted)
+static void host_recompute_normals(const float *pos, const uint32_t *faces, uint32_t nf, uint32_t nv, float *out) {
+    std::vector<double> acc(3 * (size_t) nv, 0.0);
+    for (uint32_t f = 0; f < nf; ++f) {
+        uint32_t idx[3] = { faces[3 * f], faces[3 * f + 1], faces[3 * f + 2] };
+        float3 v[3]; for (int k = 0; k < 3; ++k) v[k] = mk3(pos[3 * idx[k]], pos[3 * idx[k] + 1], pos[3 * idx[k] + 2]);
+        float3 n = cross(v[1] - v[0], v[2] - v[0]);
+        float l2 = dot(n, n);
+        if (!(l2 > 0.f)) continue;
+        n = n * (1.f / sqrtf(l2));
+        for (int k = 0; k < 3; ++k) {
+            float3 d0 = normalize(v[(k + 1) % 3] - v[k]), d1 = normalize(v[(k + 2) % 3] - v[k]);
+            // enoki unit_angle: numerically robust angle between unit vectors
+            float dp = dot(d0, d1);
+            float3 df = d1 - (dp < 0.f ? -d0 : d0);
+            float temp = 2.f * asinf(fminf(1.f, 0.5f * norm(df)));
+            float ang = dp >= 0.f ? temp : kPi - temp;
+            acc[3 * idx[k]] += n.x * ang; acc[3 * idx[k] + 1] += n.y * ang; acc[3 * idx[k] + 2] += n.z * ang;
+        }
+    }
+    for (uint32_t i = 0; i < nv; ++i) {
+        double x = acc[3 * i], y = acc[3 * i + 1], z = acc[3 * i + 2], l = sqrt(x * x + y * y + z * z);
+        if (l != 0.0) { out[3 * i] = (float) (x / l); out[3 * i + 1] = (float) (y / l); out[3 * i + 2] = (float) (z / l); }
+        else { out[3 * i] = 1.f; out[3 * i + 1] = 0.f; out[3 * i + 2] = 0.f; }
+    }
+}
+
+extern "C" int mtsb_scene_update_vertices(mtsb_scene *s, uint32_t mesh_id, const float *positions, int mem) {
+    CHECK_ARG(s && mesh_id < s->meshes.size() && positions);
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    const MeshDev &m = s->meshes[mesh_id];
+    float *hp = s->h_pos.data() + 3 * (size_t) m.vert_begin;
+    if (mem == MTSB_MEM_DEVICE) { CU(cudaMemcpyAsync(hp, positions, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+    else memcpy(hp, positions, 3 * (size_t) m.vert_count * sizeof(float));
+    CU(cudaMemcpyAsync(s->pos.p + 3 * (size_t) m.vert_begin, hp, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (m.has_normals) {
+        float *hn = s->h_nrm.data() + 3 * (size_t) m.vert_begin;
+        host_recompute_normals(hp, s->mesh_faces[mesh_id].data(), m.face_count, m.vert_count, hn);
+        CU(cudaMemcpyAsync(s->nrm.p + 3 * (size_t) m.vert_begin, hn, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    RC(build_bvh(s));
+    RC(build_area_tables(s));
+    update_env_bsphere(s);
+    return upload_struct_arrays(s);
+}
+
+extern "C" int mtsb_scene_update_texture(mtsb_scene *s, uint32_t tex_id, const float *data, int mem) {
+    CHECK_ARG(s && tex_id < s->tex.size() && data);
+    CU(cudaSetDevice(s->ctx->device));
+    TexDev &t = s->tex[tex_id];
+    if (t.type == MTSB_TEX_CONSTANT) {
+        float v[3];
+        if (mem == MTSB_MEM_DEVICE) CU(cudaMemcpy(v, data, sizeof(v), cudaMemcpyDeviceToHost)); else memcpy(v, data, sizeof(v));
+        t.value = mk3(v[0], v[1], v[2]);
+        return upload_struct_arrays(s);
+    }
+    size_t n = (size_t) t.w * t.h * t.ch;
+    CU(cudaMemcpyAsync((float *) t.data, data, n * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Parity hooks (host pointers)
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mtsb_pcg32_floats(mtsb_ctx *c, uint64_t n, const uint64_t *initstate, const uint64_t *initseq, uint32_t n_draws, float *out) {
+    CHECK_ARG(c && (n == 0 || (initstate && initseq && out)));
+    CU(cudaSetDevice(c->device));
+    if (n == 0 || n_draws == 0) return MTSB_OK;
+    Staging sg; const uint64_t *ds, *dq; float *dout;
+    RC(sg.in(initstate, n, 0, c->stream, &ds)); RC(sg.in(initseq, n, 0, c->stream, &dq)); RC(sg.out(out, n * n_draws, 0, &dout));
+    k_pcg32<<<grid_for(n), kBlock, 0, c->stream>>>((uint32_t) n, ds, dq, n_draws, dout);
+    RC(sg.back(out, dout, n * n_draws, 0, c->stream));
+    CU(cudaStreamSynchronize(c->stream)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+extern "C" int mtsb_sampler_seed(mtsb_ctx *c, uint64_t n, uint64_t seed, uint64_t *state, uint64_t *inc) {
+    CHECK_ARG(c && (n == 0 || (state && inc)));
+    CU(cudaSetDevice(c->device));
+    if (n == 0) return MTSB_OK;
+    Staging sg; uint64_t *ds, *di;
+    RC(sg.out(state, n, 0, &ds)); RC(sg.out(inc, n, 0, &di));
+    k_sampler_seed<<<grid_for(n), kBlock, 0, c->stream>>>((uint32_t) n, seed, ds, di);
+    RC(sg.back(state, ds, n, 0, c->stream)); RC(sg.back(inc, di, n, 0, c->stream));
+    CU(cudaStreamSynchronize(c->stream)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+extern "C" int mtsb_sensor_sample_ray(mtsb_scene *s, uint32_t sensor_id, uint64_t n, const float *pos2, float *o_mint, float *d_maxt) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && (n == 0 || (pos2 && o_mint && d_maxt)));
+    CU(cudaSetDevice(s->ctx->device));
+    if (n == 0) return MTSB_OK;
+    cudaStream_t st = s->ctx->stream; Staging sg; const float *dp; float *d_o, *d_d;
+    RC(sg.in(pos2, 2 * n, 0, st, &dp)); RC(sg.out(o_mint, 4 * n, 0, &d_o)); RC(sg.out(d_maxt, 4 * n, 0, &d_d));
+    k_sensor_ray<<<grid_for(n), kBlock, 0, st>>>(s->sensors[sensor_id]->dev, (uint32_t) n, dp, (float4 *) d_o, (float4 *) d_d);
+    RC(sg.back(o_mint, d_o, 4 * n, 0, st)); RC(sg.back(d_maxt, d_d, 4 * n, 0, st));
+    CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+extern "C" int mtsb_bsdf_sample(mtsb_scene *s, uint32_t bsdf_id, uint64_t n, const float *wi, const float *uv, const float *s1, const float *s2, float *out9) {
+    CHECK_ARG(s && bsdf_id < s->bsdfs.size() && (n == 0 || (wi && uv && s1 && s2 && out9)));
+    CU(cudaSetDevice(s->ctx->device));
+    if (n == 0) return MTSB_OK;
+    cudaStream_t st = s->ctx->stream; Staging sg; const float *dwi, *duv, *ds1, *ds2; float *dout;
+    RC(sg.in(wi, 3 * n, 0, st, &dwi)); RC(sg.in(uv, 2 * n, 0, st, &duv)); RC(sg.in(s1, n, 0, st, &ds1)); RC(sg.in(s2, 2 * n, 0, st, &ds2));
+    RC(sg.out(out9, 9 * n, 0, &dout));
+    k_bsdf_sample<<<grid_for(n), kBlock, 0, st>>>(s->dev, bsdf_id, (uint32_t) n, dwi, duv, ds1, ds2, dout);
+    RC(sg.back(out9, dout, 9 * n, 0, st));
+    CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+extern "C" int mtsb_bsdf_eval_pdf(mtsb_scene *s, uint32_t bsdf_id, uint64_t n, const float *wi, const float *uv, const float *wo, float *eval3, float *pdf) {
+    CHECK_ARG(s && bsdf_id < s->bsdfs.size() && (n == 0 || (wi && uv && wo && eval3 && pdf)));
+    CU(cudaSetDevice(s->ctx->device));
+    if (n == 0) return MTSB_OK;
+    cudaStream_t st = s->ctx->stream; Staging sg; const float *dwi, *duv, *dwo; float *de, *dp;
+    RC(sg.in(wi, 3 * n, 0, st, &dwi)); RC(sg.in(uv, 2 * n, 0, st, &duv)); RC(sg.in(wo, 3 * n, 0, st, &dwo));
+    RC(sg.out(eval3, 3 * n, 0, &de)); RC(sg.out(pdf, n, 0, &dp));
+    k_bsdf_eval_pdf<<<grid_for(n), kBlock, 0, st>>>(s->dev, bsdf_id, (uint32_t) n, dwi, duv, dwo, de, dp);
+    RC(sg.back(eval3, de, 3 * n, 0, st)); RC(sg.back(pdf, dp, n, 0, st));
+    CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
+    return MTSB_OK;
+}
+extern "C" int mtsb_sample_emitter_direction(mtsb_scene *s, uint64_t n, const float *ref_p, const float *s2, float *out11) {
+    CHECK_ARG(s && (n == 0 || (ref_p && s2 && out11)));
+    CU(cudaSetDevice(s->ctx->device));
+    if (n == 0) return MTSB_OK;
+    cudaStream_t st = s->ctx->stream; Staging sg; const float *dp, *ds2; float *dout;
+    RC(sg.in(ref_p, 3 * n, 0, st, &dp)); RC(sg.in(s2, 2 * n, 0, st, &ds2)); RC(sg.out(out11, 11 * n, 0, &dout));
+    k_sample_emitter<<<grid_for(n), kBlock, 0, st>>>(s->dev, (uint32_t) n, dp, ds2, dout);
+    RC(sg.back(out11, dout, 11 * n, 0, st));
+    CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
+    return MTSB_OK;
+}

@@ -1,0 +1,448 @@
+// bvh.h -- GPU-built 8-wide compressed BVH: per-thread build bodies, node encoding, and the
+// traversal core.  Replaces the SAH kd-tree of the reference (include/mitsuba/render/kdtree.h:1710
+// build, :2080-2175 traversal) -- semantics kept (closest hit in [mint,maxt] / any hit), algorithm new:
+//   Morton codes (63 bit) -> radix sort -> Karras LBVH -> bottom-up fit -> greedy surface-area collapse
+//   to 8 children -> 80-byte quantised nodes with octant-ordered child slots (after Ylitie et al. 2017)
+//   -> leaf triangles re-laid out contiguously per node (48 B, watertight test after Woop et al. 2013).
+// All bodies are HD so tests/hostsim can execute them sequentially on the CPU.
+#pragma once
+#include "vec.h"
+
+namespace mtsb {
+
+template <typename T> HD T atomic_add(T *p, T v) {
+#ifdef __CUDA_ARCH__
+    return atomicAdd(p, v);
+#else
+    T o = *p; *p = o + v; return o;
+#endif
+}
+HD void mem_fence() {
+#ifdef __CUDA_ARCH__
+    __threadfence();
+#endif
+}
+HD int clz32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __clz((int) x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+HD int clz64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    return __clzll((long long) x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+HD int popc32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
+
+constexpr int kMaxLeafTris = 3;
+
+struct BvhBuild {
+    // inputs
+    const float *pos;        // 3*V, all meshes concatenated
+    const uint4 *faces;      // (i0,i1,i2,mesh_id) with global vertex indices; index = global prim id
+    uint32_t n;              // triangles
+    // scratch
+    float4 *tlo, *thi;       // per-triangle bounds (input order)
+    uint64_t *keys; uint32_t *order;     // morton keys / sorted triangle order
+    int *left, *right;       // per internal node (n-1)
+    int *parent;             // per node id (2n-1); id < n-1 internal, else leaf (id-(n-1))
+    uint32_t *rfirst, *rlast;// per internal node: covered sorted range
+    float4 *nlo, *nhi;       // per node id bounds
+    uint32_t *flags;         // per internal node arrival counter
+    // outputs
+    uint4 *nodes;            // 5 x uint4 per wide node
+    float4 *tris;            // 3 x float4 per triangle slot
+    int *wide_bin;           // per wide node: binary node id it collapses
+    uint32_t *counters;      // [0] wide nodes allocated, [1] triangle slots allocated
+    float3 scene_lo, scene_hi;
+};
+
+HD void tri_bounds_body(const BvhBuild &b, uint32_t i, float3 &lo, float3 &hi) {
+    uint4 f = b.faces[i];
+    float3 p0 = mk3(b.pos[3 * f.x], b.pos[3 * f.x + 1], b.pos[3 * f.x + 2]);
+    float3 p1 = mk3(b.pos[3 * f.y], b.pos[3 * f.y + 1], b.pos[3 * f.y + 2]);
+    float3 p2 = mk3(b.pos[3 * f.z], b.pos[3 * f.z + 1], b.pos[3 * f.z + 2]);
+    lo = fmin3(p0, fmin3(p1, p2)); hi = fmax3(p0, fmax3(p1, p2));
+    b.tlo[i] = mk4(lo, 0.f); b.thi[i] = mk4(hi, 0.f);
+}
+
+HD uint64_t expand21(uint32_t v) {   // spread 21 bits to every third bit
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffULL;
+    x = (x | x << 16) & 0x1f0000ff0000ffULL;
+    x = (x | x << 8) & 0x100f00f00f00f00fULL;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ULL;
+    x = (x | x << 2) & 0x1249249249249249ULL;
+    return x;
+}
+HD void morton_body(const BvhBuild &b, uint32_t i) {
+    float3 c = (xyz(b.tlo[i]) + xyz(b.thi[i])) * 0.5f;
+    float3 ext = fmax3(b.scene_hi - b.scene_lo, mk3(1e-30f));
+    float3 q = (c - b.scene_lo) / ext * 2097152.f;
+    uint32_t x = (uint32_t) fminf(fmaxf(q.x, 0.f), 2097151.f);
+    uint32_t y = (uint32_t) fminf(fmaxf(q.y, 0.f), 2097151.f);
+    uint32_t z = (uint32_t) fminf(fmaxf(q.z, 0.f), 2097151.f);
+    b.keys[i] = (expand21(x) << 2) | (expand21(y) << 1) | expand21(z);
+    b.order[i] = i;
+}
+
+HD int lbvh_delta(const BvhBuild &b, int i, int j) {
+    if (j < 0 || j >= (int) b.n) return -1;
+    uint64_t a = b.keys[i], c = b.keys[j];
+    if (a == c) return 64 + clz32((uint32_t) i ^ (uint32_t) j);
+    return clz64(a ^ c);
+}
+// Karras 2012: one thread per internal node i in [0, n-2]
+HD void lbvh_node_body(const BvhBuild &b, int i) {
+    int n = (int) b.n;
+    int d = (lbvh_delta(b, i, i + 1) - lbvh_delta(b, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = lbvh_delta(b, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(b, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lbvh_delta(b, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = lbvh_delta(b, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) / 2;
+        if (lbvh_delta(b, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + (d < 0 ? -1 : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    int lc = (lo == gamma) ? (n - 1) + gamma : gamma;
+    int rc = (hi == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
+    b.left[i] = lc; b.right[i] = rc;
+    b.parent[lc] = i; b.parent[rc] = i;
+    b.rfirst[i] = (uint32_t) lo; b.rlast[i] = (uint32_t) hi;
+    if (i == 0) b.parent[0] = -1;
+}
+// bottom-up fit: one thread per sorted leaf j
+HD void lbvh_fit_body(const BvhBuild &b, int j) {
+    int n = (int) b.n;
+    uint32_t t = b.order[j];
+    int id = (n - 1) + j;
+    b.nlo[id] = b.tlo[t]; b.nhi[id] = b.thi[t];
+    if (n == 1) return;
+    int p = b.parent[id];
+    while (p >= 0) {
+        mem_fence();
+        uint32_t old = atomic_add(&b.flags[p], 1u);
+        if (old == 0) return;
+        mem_fence();
+        int l = b.left[p], r = b.right[p];
+#ifdef __CUDA_ARCH__
+        float4 llo = __ldcg(&b.nlo[l]), lhi = __ldcg(&b.nhi[l]), rlo = __ldcg(&b.nlo[r]), rhi = __ldcg(&b.nhi[r]);
+#else
+        float4 llo = b.nlo[l], lhi = b.nhi[l], rlo = b.nlo[r], rhi = b.nhi[r];
+#endif
+        b.nlo[p] = mk4(fmin3(xyz(llo), xyz(rlo)), 0.f);
+        b.nhi[p] = mk4(fmax3(xyz(lhi), xyz(rhi)), 0.f);
+        p = b.parent[p];
+    }
+}
+
+HD float half_area(float3 lo, float3 hi) {
+    float3 e = hi - lo;
+    return e.x * e.y + e.y * e.z + e.z * e.x;
+}
+HD uint32_t bin_count(const BvhBuild &b, int id) {
+    int n = (int) b.n;
+    return id >= n - 1 ? 1u : b.rlast[id] - b.rfirst[id] + 1u;
+}
+HD uint32_t bin_first(const BvhBuild &b, int id) {
+    int n = (int) b.n;
+    return id >= n - 1 ? (uint32_t) (id - (n - 1)) : b.rfirst[id];
+}
+
+// Collapse: one thread per wide node w of the current level.
+HD void collapse_body(const BvhBuild &b, uint32_t w) {
+    int n = (int) b.n;
+    int root = b.wide_bin[w];
+    int ch[8]; int nch = 0;
+    if (root >= n - 1 || bin_count(b, root) <= 1) { ch[nch++] = root; }
+    else { ch[nch++] = b.left[root]; ch[nch++] = b.right[root]; }
+    // phase 1: open children that are too big to be leaves (largest area first); phase 2: use spare
+    // slots to split multi-triangle leaves.
+    for (int phase = 0; phase < 2; ++phase) {
+        uint32_t limit = phase == 0 ? (uint32_t) kMaxLeafTris : 1u;
+        while (nch < 8) {
+            int best = -1; float best_a = -1.f;
+            for (int k = 0; k < nch; ++k) {
+                if (ch[k] >= n - 1 || bin_count(b, ch[k]) <= limit) continue;
+                float a = half_area(xyz(b.nlo[ch[k]]), xyz(b.nhi[ch[k]]));
+                if (a > best_a) { best_a = a; best = k; }
+            }
+            if (best < 0) break;
+            int id = ch[best];
+            ch[best] = b.left[id]; ch[nch++] = b.right[id];
+        }
+    }
+    // classify
+    bool internal[8]; uint32_t n_int = 0, n_tri = 0;
+    for (int k = 0; k < nch; ++k) {
+        internal[k] = ch[k] < n - 1 && bin_count(b, ch[k]) > (uint32_t) kMaxLeafTris;
+        if (internal[k]) n_int++; else n_tri += bin_count(b, ch[k]);
+    }
+    uint32_t child_base = n_int ? atomic_add(&b.counters[0], n_int) : 0u;
+    uint32_t tri_base = n_tri ? atomic_add(&b.counters[1], n_tri) : 0u;
+    float3 lo = xyz(b.nlo[root]), hi = xyz(b.nhi[root]);
+    float3 nc = (lo + hi) * 0.5f;
+    // octant slot assignment (greedy auction)
+    int slot_of[8]; bool slot_used[8]; bool done[8];
+    for (int k = 0; k < 8; ++k) { slot_used[k] = false; done[k] = false; slot_of[k] = -1; }
+    for (int it = 0; it < nch; ++it) {
+        float bc = -FLT_MAX; int bk = -1, bs = -1;
+        for (int k = 0; k < nch; ++k) {
+            if (done[k]) continue;
+            float3 c = (xyz(b.nlo[ch[k]]) + xyz(b.nhi[ch[k]])) * 0.5f - nc;
+            for (int s = 0; s < 8; ++s) {
+                if (slot_used[s]) continue;
+                float cost = ((s & 1) ? c.x : -c.x) + ((s & 2) ? c.y : -c.y) + ((s & 4) ? c.z : -c.z);
+                if (cost > bc) { bc = cost; bk = k; bs = s; }
+            }
+        }
+        done[bk] = true; slot_used[bs] = true; slot_of[bk] = bs;
+    }
+    // quantisation frame
+    int ex[3]; float sc[3]; float ext[3] = { hi.x - lo.x, hi.y - lo.y, hi.z - lo.z };
+    for (int a = 0; a < 3; ++a) {
+        int e = (int) ceilf(log2f(fmaxf(ext[a], 1e-30f) / 255.f));
+        if (e < -126) e = -126; if (e > 126) e = 126;
+        while (ceilf(ext[a] / exp2f((float) e)) > 254.f) e++;   // one unit of slack for the safety pass below
+        ex[a] = e; sc[a] = exp2f((float) e);
+    }
+    uint8_t qlo[3][8], qhi[3][8], meta[8];
+    for (int s = 0; s < 8; ++s) { meta[s] = 0; for (int a = 0; a < 3; ++a) { qlo[a][s] = 255; qhi[a][s] = 0; } }
+    uint32_t imask = 0;
+    // internal children take consecutive indices in slot order; leaves take triangle offsets in slot order
+    int kid_of_slot[8];
+    for (int s = 0; s < 8; ++s) kid_of_slot[s] = -1;
+    for (int k = 0; k < nch; ++k) kid_of_slot[slot_of[k]] = k;
+    uint32_t int_rank = 0, tri_off = 0;
+    float plo[3] = { lo.x, lo.y, lo.z };
+    for (int s = 0; s < 8; ++s) {
+        int k = kid_of_slot[s];
+        if (k < 0) continue;
+        float4 cl4 = b.nlo[ch[k]], ch4 = b.nhi[ch[k]];
+        float cl[3] = { cl4.x, cl4.y, cl4.z }, chh[3] = { ch4.x, ch4.y, ch4.z };
+        for (int a = 0; a < 3; ++a) {
+            float fl = floorf((cl[a] - plo[a]) / sc[a]), fh = ceilf((chh[a] - plo[a]) / sc[a]);
+            fl = fminf(fmaxf(fl, 0.f), 255.f); fh = fminf(fmaxf(fh, 0.f), 255.f);
+            // conservative under the exact arithmetic the traversal uses
+            while (fl > 0.f && plo[a] + fl * sc[a] > cl[a]) fl -= 1.f;
+            while (fh < 255.f && plo[a] + fh * sc[a] < chh[a]) fh += 1.f;
+            qlo[a][s] = (uint8_t) fl; qhi[a][s] = (uint8_t) fh;
+        }
+        if (internal[k]) {
+            imask |= 1u << s;
+            meta[s] = (uint8_t) ((1u << 5) | (24u + s));
+            b.wide_bin[child_base + int_rank] = ch[k];
+            int_rank++;
+        } else {
+            uint32_t cnt = bin_count(b, ch[k]), first = bin_first(b, ch[k]);
+            meta[s] = (uint8_t) ((((1u << cnt) - 1u) << 5) | tri_off);
+            for (uint32_t q = 0; q < cnt; ++q) {
+                uint32_t prim = b.order[first + q];
+                uint4 f = b.faces[prim];
+                uint32_t o = 3 * (tri_base + tri_off + q);
+                b.tris[o + 0] = make_float4(b.pos[3 * f.x], b.pos[3 * f.x + 1], b.pos[3 * f.x + 2], u2f(prim));
+                b.tris[o + 1] = make_float4(b.pos[3 * f.y], b.pos[3 * f.y + 1], b.pos[3 * f.y + 2], 0.f);
+                b.tris[o + 2] = make_float4(b.pos[3 * f.z], b.pos[3 * f.z + 1], b.pos[3 * f.z + 2], 0.f);
+            }
+            tri_off += cnt;
+        }
+    }
+    auto pack4 = [](const uint8_t *p) { return (uint32_t) p[0] | ((uint32_t) p[1] << 8) | ((uint32_t) p[2] << 16) | ((uint32_t) p[3] << 24); };
+    uint4 *o = b.nodes + 5 * (size_t) w;
+    uint32_t ew = (uint32_t) (ex[0] + 127) | ((uint32_t) (ex[1] + 127) << 8) | ((uint32_t) (ex[2] + 127) << 16) | (imask << 24);
+    o[0] = make_uint4(f2u(lo.x), f2u(lo.y), f2u(lo.z), ew);
+    o[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+    o[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
+    o[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
+    o[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Traversal
+// ------------------------------------------------------------------------------------------------
+struct Bvh {
+    const uint4 *nodes;
+    const float4 *tris;
+    uint32_t n_tris;
+};
+
+struct RayPre {     // Woop et al. 2013 per-ray precomputation (axis permutation folded into selects)
+    float3 o; float Sx, Sy, Sz; int kz;
+};
+HD float3 permute(float3 v, int kz, bool flip) {
+    // returns (v[kx], v[ky], v[kz]) with kx=(kz+1)%3, ky=(kx+1)%3, swapped if `flip`
+    float a = kz == 0 ? v.y : (kz == 1 ? v.z : v.x);
+    float b = kz == 0 ? v.z : (kz == 1 ? v.x : v.y);
+    float c = kz == 0 ? v.x : (kz == 1 ? v.y : v.z);
+    return flip ? mk3(b, a, c) : mk3(a, b, c);
+}
+struct RayWoop { float3 o; float Sx, Sy, Sz; int kz; bool flip; };
+HD RayWoop woop_setup(float3 o, float3 d) {
+    RayWoop r; r.o = o;
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    r.kz = (ax > ay) ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    float dz = r.kz == 0 ? d.x : (r.kz == 1 ? d.y : d.z);
+    r.flip = dz < 0.f;
+    float3 dp = permute(d, r.kz, r.flip);
+    r.Sx = dp.x / dp.z; r.Sy = dp.y / dp.z; r.Sz = 1.f / dp.z;
+    return r;
+}
+// returns true on hit in [mint, maxt]; (bu,bv) = barycentrics of v1, v2 (Mitsuba's si.uv convention, mesh.cpp:404-407)
+HD bool woop_intersect(const RayWoop &r, float3 v0, float3 v1, float3 v2, float mint, float maxt,
+                       float &t, float &bu, float &bv) {
+    float3 A = permute(v0 - r.o, r.kz, r.flip), B = permute(v1 - r.o, r.kz, r.flip), C = permute(v2 - r.o, r.kz, r.flip);
+    float Ax = fmaf(-r.Sx, A.z, A.x), Ay = fmaf(-r.Sy, A.z, A.y);
+    float Bx = fmaf(-r.Sx, B.z, B.x), By = fmaf(-r.Sy, B.z, B.y);
+    float Cx = fmaf(-r.Sx, C.z, C.x), Cy = fmaf(-r.Sy, C.z, C.y);
+    float U = Cx * By - Cy * Bx, V = Ax * Cy - Ay * Cx, W = Bx * Ay - By * Ax;
+    if (U == 0.f || V == 0.f || W == 0.f) {
+        double CxBy = (double) Cx * (double) By, CyBx = (double) Cy * (double) Bx;
+        U = (float) (CxBy - CyBx);
+        double AxCy = (double) Ax * (double) Cy, AyCx = (double) Ay * (double) Cx;
+        V = (float) (AxCy - AyCx);
+        double BxAy = (double) Bx * (double) Ay, ByAx = (double) By * (double) Ax;
+        W = (float) (BxAy - ByAx);
+    }
+    if ((U < 0.f || V < 0.f || W < 0.f) && (U > 0.f || V > 0.f || W > 0.f)) return false;
+    float det = U + V + W;
+    if (det == 0.f) return false;
+    float T = U * (r.Sz * A.z) + V * (r.Sz * B.z) + W * (r.Sz * C.z);
+    float inv = 1.f / det;
+    float tt = T * inv;
+    if (!(tt >= mint && tt <= maxt)) return false;
+    t = tt; bu = V * inv; bv = W * inv;
+    return true;
+}
+
+struct Hit { float t, u, v; uint32_t prim; };
+
+// Stack policy: fixed small array supplied by the caller (shared memory on the device) + local overflow.
+template <int NFast, int NSlow> struct TravStack {
+    uint2 *fast; int stride;       // fast[i*stride]
+    uint2 slow[NSlow];
+    int sp = 0;
+    HD void push(uint2 v) { if (sp < NFast) fast[sp * stride] = v; else if (sp - NFast < NSlow) slow[sp - NFast] = v; sp++; }
+    HD uint2 pop() { sp--; return sp < NFast ? fast[sp * stride] : slow[(sp - NFast) < NSlow ? (sp - NFast) : NSlow - 1]; }
+    HD bool empty() const { return sp == 0; }
+};
+
+HD uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
+
+// Intersect the 8 quantised child boxes of `node`; returns the hit mask word: bits 24..31 internal children in
+// near-to-far priority (bit = 24 + (slot ^ octinv)), bits 0..23 candidate triangles.
+HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                         float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+    float3 p = mk3(u2f(n0.x), u2f(n0.y), u2f(n0.z));
+    float sx = u2f(byte_of(n0.w, 0) << 23), sy = u2f(byte_of(n0.w, 1) << 23), sz = u2f(byte_of(n0.w, 2) << 23);
+    float3 adir = mk3(sx * idir.x, sy * idir.y, sz * idir.z);
+    float3 org = mk3((p.x - o.x) * idir.x, (p.y - o.y) * idir.y, (p.z - o.z) * idir.z);
+    uint32_t imask = n0.w >> 24;
+    uint32_t hit = 0;
+    bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        uint32_t meta4 = half ? n1.w : n1.z;
+        uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
+        uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
+        uint32_t ax = nx ? hix : lox, bx = nx ? lox : hix;
+        uint32_t ay = ny ? hiy : loy, by = ny ? loy : hiy;
+        uint32_t az = nz ? hiz : loz, bz = nz ? loz : hiz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t meta = byte_of(meta4, j);
+            float t0x = fmaf((float) byte_of(ax, j), adir.x, org.x), t1x = fmaf((float) byte_of(bx, j), adir.x, org.x);
+            float t0y = fmaf((float) byte_of(ay, j), adir.y, org.y), t1y = fmaf((float) byte_of(by, j), adir.y, org.y);
+            float t0z = fmaf((float) byte_of(az, j), adir.z, org.z), t1z = fmaf((float) byte_of(bz, j), adir.z, org.z);
+            float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            if (meta != 0 && tn <= tf * 1.0000004f) {
+                int s = half * 4 + j;
+                if (imask & (1u << s)) hit |= 1u << (24 + ((uint32_t) s ^ octinv));
+                else hit |= (meta >> 5) << (meta & 31u);
+            }
+        }
+    }
+    return hit;
+}
+
+HD uint4 ldg4(const uint4 *p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+HD float4 ldg4f(const float4 *p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+
+template <bool AnyHit, typename Stack>
+HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.prim = 0xffffffffu;
+    if (bvh.n_tris == 0) return false;
+    const float big = 1e30f;
+    float3 idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x),
+                      fabsf(d.y) > 1e-30f ? 1.f / d.y : copysignf(big, d.y),
+                      fabsf(d.z) > 1e-30f ? 1.f / d.z : copysignf(big, d.z));
+    uint32_t oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+    uint32_t octinv = 7u ^ oct;
+    RayWoop rw = woop_setup(o, d);
+    float tmax = maxt;
+    bool found = false;
+    uint2 G = make_uint2(0u, 0x80000000u);
+    while (true) {
+        if (G.y & 0xff000000u) {
+            uint32_t bit = 31u - (uint32_t) clz32(G.y);
+            G.y &= ~(1u << bit);
+            if (G.y & 0xff000000u) st.push(G);
+            uint32_t slot = (bit - 24u) ^ octinv;
+            uint32_t rel = (uint32_t) popc32(G.y & ((1u << slot) - 1u) & 0xffu);
+            const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
+            uint4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
+            uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, o, idir, octinv, mint, tmax);
+            G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+            uint32_t tb = n1.y, tm = hm & 0x00ffffffu;
+            while (tm) {
+                uint32_t b = 31u - (uint32_t) clz32(tm);
+                tm &= ~(1u << b);
+                const float4 *tp = bvh.tris + 3 * (size_t) (tb + b);
+                float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
+                float t, u, v;
+                if (woop_intersect(rw, xyz(a0), xyz(a1), xyz(a2), mint, tmax, t, u, v)) {
+                    if (AnyHit) { hit.t = t; return true; }
+                    tmax = t; found = true;
+                    hit.t = t; hit.u = u; hit.v = v; hit.prim = f2u(a0.w);
+                }
+            }
+        }
+        if ((G.y & 0xff000000u) == 0) {
+            if (st.empty()) break;
+            G = st.pop();
+        }
+    }
+    return found;
+}
+
+} // namespace mtsb

@@ -1,0 +1,164 @@
+// emit.h -- area + envmap emitters and the scene-level emitter sampling (HD bodies).
+#pragma once
+#include "shade.h"
+
+namespace mtsb {
+
+struct DirSample { float3 p, n, d; float dist, pdf; float3 value; };
+
+// enoki::binary_search (ext/enoki/include/enoki/array_utils.h:153-171)
+template <typename Pred> HD uint32_t binary_search(uint32_t start, uint32_t end, Pred pred) {
+    uint32_t iterations = (start < end) ? (uint32_t) (31 - clz32(end - start)) + 1u : 0u;
+    for (uint32_t i = 0; i < iterations; ++i) {
+        uint32_t middle = (start + end) >> 1;
+        if (pred(middle)) start = min(middle + 1, end); else end = middle;
+    }
+    return start;
+}
+
+// ---- envmap (src/emitters/envmap.cpp:132-206, 267-317) -------------------------------------------
+HD float3 env_lookup(const EmitterDev &e, float u, float v) {
+    u *= (float) (e.w - 1); v *= (float) (e.h - 1);
+    uint32_t px = min((uint32_t) u, e.w - 2), py = min((uint32_t) v, e.h - 2);
+    float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t idx = px + py * e.w;
+    float4 v00 = e.rgba[idx], v10 = e.rgba[idx + 1], v01 = e.rgba[idx + e.w], v11 = e.rgba[idx + e.w + 1];
+    float3 a = mk3(fmaf(w0x, v00.x, w1x * v10.x), fmaf(w0x, v00.y, w1x * v10.y), fmaf(w0x, v00.z, w1x * v10.z));
+    float3 b = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
+    return mk3(fmaf(w0y, a.x, w1y * b.x), fmaf(w0y, a.y, w1y * b.y), fmaf(w0y, a.z, w1y * b.z)) * e.scale;
+}
+HD void env_dir_to_uv(const EmitterDev &e, float3 dworld, float &u, float &v, float3 &dl) {
+    dl = xform_vec(e.to_local, dworld);
+    u = atan2f(dl.x, -dl.z) * kInvTwoPi; v = safe_acos(dl.y) * kInvPi;
+    u -= floorf(u); v -= floorf(v);
+}
+HD float3 env_eval(const EmitterDev &e, float3 dworld) {     // direction pointing away from the scene
+    float u, v; float3 dl; env_dir_to_uv(e, dworld, u, v, dl);
+    return env_lookup(e, u, v);
+}
+// Hierarchical2D<Float,0> (include/mitsuba/core/distr_2d.h:317-403, 495-530); level 0 = bilinear data,
+// levels 1.. = MIP pyramid in 2x2-blocked layout (Level::index, :583-586)
+HD uint32_t h2d_index(uint32_t x, uint32_t y, uint32_t width) {
+    return ((x & 1u) | (((x & ~1u) | (y & 1u)) << 1)) + ((y & ~1u) * width);
+}
+HD float interval_to_linear(float v0, float v1, float s) {
+    return fabsf(v0 - v1) > 1e-4f * (v0 + v1) ? (v0 - safe_sqrt(lerpf(sqr(v0), sqr(v1), s))) / (v0 - v1) : s;
+}
+HD void h2d_sample(const EmitterDev &e, float sx, float sy, float &u, float &v, float &pdf) {
+    sx = fminf(fmaxf(sx, 0.f), 1.f); sy = fminf(fmaxf(sy, 0.f), 1.f);
+    uint32_t ox = 0, oy = 0;
+    for (int l = e.n_levels - 2; l > 0; --l) {
+        const float *d = e.level_data[l];
+        ox <<= 1; oy <<= 1;
+        uint32_t i = h2d_index(ox, oy, e.level_width[l]);
+        float v00 = d[i], v10 = d[i + 1], v01 = d[i + 2], v11 = d[i + 3];
+        sx = fminf(fmaxf(sx, 0.f), 1.f); sy = fminf(fmaxf(sy, 0.f), 1.f);
+        float r0 = v00 + v10, r1 = v01 + v11;
+        sy *= r0 + r1;
+        bool mask = sy > r0;
+        if (mask) { oy += 1; sy -= r0; }
+        sy /= mask ? r1 : r0;
+        float c0 = mask ? v01 : v00, c1 = mask ? v11 : v10;
+        sx *= c0 + c1;
+        bool mx = sx > c0;
+        if (mx) sx -= c0;
+        sx /= mx ? c1 : c0;
+        if (mx) ox += 1;
+    }
+    const float *d0 = e.level_data[0]; uint32_t w0 = e.level_width[0];
+    uint32_t i = ox + oy * w0;
+    float v00 = d0[i], v10 = d0[i + 1], v01 = d0[i + w0], v11 = d0[i + w0 + 1];
+    // warp::square_to_bilinear (include/mitsuba/core/warp.h:398-414)
+    float r0 = v00 + v10, r1 = v01 + v11;
+    sy = interval_to_linear(r0, r1, sy);
+    float c0 = lerpf(v00, v01, sy), c1 = lerpf(v10, v11, sy);
+    sx = interval_to_linear(c0, c1, sx);
+    pdf = lerpf(c0, c1, sx);
+    u = ((float) (int) ox + sx) * (1.f / (float) (e.w - 1));
+    v = ((float) (int) oy + sy) * (1.f / (float) (e.h - 1));
+}
+HD float h2d_eval(const EmitterDev &e, float u, float v) {
+    u = fminf(fmaxf(u, 0.f), 1.f) * (float) (e.w - 1); v = fminf(fmaxf(v, 0.f), 1.f) * (float) (e.h - 1);
+    uint32_t ox = min((uint32_t) (int) u, e.w - 2), oy = min((uint32_t) (int) v, e.h - 2);
+    u -= (float) (int) ox; v -= (float) (int) oy;
+    const float *d0 = e.level_data[0]; uint32_t w0 = e.level_width[0];
+    uint32_t i = ox + oy * w0;
+    float v00 = d0[i], v10 = d0[i + 1], v01 = d0[i + w0], v11 = d0[i + w0 + 1];
+    return lerpf(lerpf(v00, v10, u), lerpf(v01, v11, u), v);
+}
+HD float env_pdf_direction(const EmitterDev &e, float3 dworld) {
+    float u, v; float3 d; env_dir_to_uv(e, dworld, u, v, d);
+    float inv_sin = 1.f / sqrtf(fmaxf(sqr(d.x) + sqr(d.z), sqr(kEpsilon)));
+    return h2d_eval(e, u, v) * inv_sin * (1.f / (2.f * sqr(kPi)));
+}
+HD DirSample env_sample_direction(const EmitterDev &e, float3 ref_p, float sx, float sy) {
+    DirSample ds;
+    float u, v, pdf; h2d_sample(e, sx, sy, u, v, pdf);
+    float theta = v * kPi, phi = u * (2.f * kPi);
+    float st, ct, sp, cp; sincosf(theta, &st, &ct); sincosf(phi, &sp, &cp);
+    float3 d = mk3(cp * st, sp * st, ct);         // math::sphdir
+    d = mk3(d.y, d.z, -d.x);
+    float dist = 2.f * e.bsphere_radius;
+    float inv_sin = 1.f / sqrtf(fmaxf(sqr(d.x) + sqr(d.z), sqr(kEpsilon)));
+    d = xform_vec(e.to_world, d);
+    ds.p = ref_p + d * dist; ds.n = -d; ds.d = d; ds.dist = dist;
+    ds.pdf = pdf > 0.f ? pdf * inv_sin * (1.f / (2.f * sqr(kPi))) : 0.f;
+    ds.value = env_lookup(e, u, v) / ds.pdf;
+    return ds;
+}
+
+// ---- area light on a mesh (src/emitters/area.cpp:103-125, src/librender/shape.cpp:252-283,
+//      src/librender/mesh.cpp:320-365, include/mitsuba/core/distr_1d.h:144-203) ---------------------
+HD DirSample area_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy) {
+    DirSample ds;
+    const MeshDev m = sc.meshes[e.mesh];
+    float value = sy * e.cdf_sum;
+    const float *cdf = e.cdf;
+    uint32_t idx = binary_search(e.valid_lo, e.valid_hi, [&](uint32_t i) { return cdf[i] < value; });
+    uint4 f = sc.faces[m.face_begin + idx];
+    float3 p0 = ld3(sc.pos, f.x), p1 = ld3(sc.pos, f.y), p2 = ld3(sc.pos, f.z);
+    float3 e0 = p1 - p0, e1 = p2 - p0;
+    float pmf = 0.5f * norm(cross(e0, e1)) * e.normalization;
+    float cdf_prev = idx > 0 ? cdf[idx - 1] * e.normalization : 0.f;
+    sy = (sy - cdf_prev) / pmf;
+    float t = safe_sqrt(1.f - sx), bx = 1.f - t, by = t * sy;
+    ds.p = p0 + e0 * bx + e1 * by;
+    if (m.has_normals) {
+        float3 n0 = ld3(sc.nrm, f.x), n1 = ld3(sc.nrm, f.y), n2 = ld3(sc.nrm, f.z);
+        ds.n = normalize(n0 * (1.f - bx - by) + n1 * bx + n2 * by);
+    } else
+        ds.n = normalize(cross(e0, e1));
+    ds.d = ds.p - ref_p;
+    float dist2 = dot(ds.d, ds.d);
+    ds.dist = sqrtf(dist2);
+    ds.d = ds.d / ds.dist;
+    float dp = fabsf(dot(ds.d, ds.n));
+    ds.pdf = e.normalization * (dp != 0.f ? dist2 / dp : 0.f);
+    bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
+    ds.value = active ? e.radiance / ds.pdf : mk3(0.f);
+    return ds;
+}
+HD float area_pdf_direction(const EmitterDev &e, float3 d, float3 n, float dist) {
+    float dp = fabsf(dot(d, n));
+    float pdf = e.normalization * (dp != 0.f ? (dist * dist) / dp : 0.f);
+    return dot(d, n) < 0.f ? pdf : 0.f;
+}
+
+// ---- Scene::sample_emitter_direction (src/librender/scene.cpp:141-176), without the shadow ray ---
+HD DirSample sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx, float sy) {
+    DirSample ds; ds.pdf = 0.f; ds.value = mk3(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
+    if (sc.n_emitters == 0) return ds;
+    uint32_t index = 0; float epdf = 1.f;
+    if (sc.n_emitters > 1) {
+        float ne = (float) sc.n_emitters;
+        epdf = 1.f / ne;
+        index = min((uint32_t) (sx * ne), (uint32_t) sc.n_emitters - 1);
+        sx = (sx - (float) index * epdf) * ne;
+    }
+    const EmitterDev &e = sc.emitters[index];
+    ds = e.type == 0 ? area_sample_direction(sc, e, ref_p, sx, sy) : env_sample_direction(e, ref_p, sx, sy);
+    if (sc.n_emitters > 1) { ds.pdf *= epdf; ds.value *= 1.f / epdf; }
+    return ds;
+}
+
+} // namespace mtsb

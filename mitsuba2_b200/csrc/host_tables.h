@@ -1,0 +1,113 @@
+// host_tables.h -- host-side construction of sampling tables uploaded once per scene.
+#pragma once
+#include <vector>
+#include <cmath>
+#include <cstdint>
+#include <stdexcept>
+
+namespace mtsb {
+
+// DiscreteDistribution::update (include/mitsuba/core/distr_1d.h:49-88) over Mesh::face_area (mesh.h:108-116)
+struct AreaTable { std::vector<float> cdf; float sum = 0, normalization = 0; uint32_t valid_lo = 0, valid_hi = 0; };
+inline AreaTable build_area_table(const float *pos, const uint32_t *faces, uint32_t n_faces) {
+    AreaTable t; t.cdf.resize(n_faces);
+    double sum = 0.0; uint32_t lo = (uint32_t) -1, hi = (uint32_t) -1;
+    for (uint32_t i = 0; i < n_faces; ++i) {
+        const float *p0 = pos + 3 * faces[3 * i], *p1 = pos + 3 * faces[3 * i + 1], *p2 = pos + 3 * faces[3 * i + 2];
+        float ax = p1[0] - p0[0], ay = p1[1] - p0[1], az = p1[2] - p0[2];
+        float bx = p2[0] - p0[0], by = p2[1] - p0[1], bz = p2[2] - p0[2];
+        float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+        float area = 0.5f * std::sqrt(cx * cx + cy * cy + cz * cz);
+        sum += (double) area;
+        t.cdf[i] = (float) sum;
+        if (area > 0.f) { if (lo == (uint32_t) -1) lo = i; hi = i; }
+    }
+    if (lo == (uint32_t) -1) throw std::runtime_error("DiscreteDistribution: no probability mass found!");
+    t.sum = (float) sum; t.normalization = (float) (1.0 / sum); t.valid_lo = lo; t.valid_hi = hi;
+    return t;
+}
+
+inline uint32_t log2i_ceil(uint32_t v) { uint32_t r = 0; while ((1u << r) < v) ++r; return r; }
+inline uint32_t h2d_index_host(uint32_t x, uint32_t y, uint32_t width) {
+    return ((x & 1u) | (((x & ~1u) | (y & 1u)) << 1)) + ((y & ~1u) * width);
+}
+// Hierarchical2D<Float,0> constructor (include/mitsuba/core/distr_2d.h:206-310), normalize = true
+struct H2DTable { std::vector<std::vector<float>> levels; std::vector<uint32_t> widths; };
+inline H2DTable build_h2d(const float *data, uint32_t w, uint32_t h) {
+    H2DTable t;
+    uint32_t npx = w - 1, npy = h - 1;
+    uint32_t max_level = log2i_ceil(npx > npy ? npx : npy);
+    t.levels.emplace_back((size_t) w * h, 0.f); t.widths.push_back(w);
+    uint32_t lx = npx, ly = npy;
+    for (int level = (int) max_level; level >= 0; --level) {
+        lx += lx & 1u; ly += ly & 1u;
+        t.levels.emplace_back((size_t) lx * ly, 0.f); t.widths.push_back(lx);
+        lx >>= 1; ly >>= 1;
+    }
+    double sum = 0.0;
+    const float *in = data;
+    for (uint32_t y = 0; y < npy; ++y) {
+        for (uint32_t x = 0; x < npx; ++x) {
+            float avg = (in[0] + in[1] + in[w] + in[w + 1]) * .25f;
+            sum += (double) avg;
+            t.levels[1][h2d_index_host(x, y, t.widths[1])] = avg;
+            ++in;
+        }
+        ++in;
+    }
+    float scale = (float) ((double) (npx * npy) / sum);
+    for (size_t i = 0; i < t.levels[0].size(); ++i) t.levels[0][i] = data[i] * scale;
+    for (size_t i = 0; i < t.levels[1].size(); ++i) t.levels[1][i] *= scale;
+    lx = npx; ly = npy;
+    for (uint32_t level = 2; level <= max_level + 1; ++level) {
+        const std::vector<float> &l0 = t.levels[level - 1]; std::vector<float> &l1 = t.levels[level];
+        lx = (lx + 1) >> 1; ly = (ly + 1) >> 1;
+        for (uint32_t y = 0; y < ly; ++y)
+            for (uint32_t x = 0; x < lx; ++x) {
+                const float *d0 = l0.data() + h2d_index_host(x * 2, y * 2, t.widths[level - 1]);
+                l1[h2d_index_host(x, y, t.widths[level])] = d0[0] + d0[1] + d0[2] + d0[3];
+            }
+    }
+    return t;
+}
+// EnvironmentMapEmitter constructor (src/emitters/envmap.cpp:87-111): luminance * sin(theta_row)
+inline std::vector<float> env_importance(const float *rgba, uint32_t w, uint32_t h) {
+    std::vector<float> lum((size_t) w * h);
+    for (uint32_t y = 0; y < h; ++y) {
+        float sin_theta = std::sin((float) y / (float) (h - 1) * 3.14159265358979323846f);
+        for (uint32_t x = 0; x < w; ++x) {
+            const float *p = rgba + 4 * ((size_t) y * w + x);
+            float l = p[0] * 0.212671f + p[1] * 0.715160f + p[2] * 0.072169f;
+            lum[(size_t) y * w + x] = l * sin_theta;
+        }
+    }
+    return lum;
+}
+
+// row-major 4x4 inverse (general, via cofactors)
+inline bool invert4x4(const float *m, float *inv) {
+    double a[16], o[16];
+    for (int i = 0; i < 16; ++i) a[i] = m[i];
+    o[0] = a[5]*a[10]*a[15] - a[5]*a[11]*a[14] - a[9]*a[6]*a[15] + a[9]*a[7]*a[14] + a[13]*a[6]*a[11] - a[13]*a[7]*a[10];
+    o[4] = -a[4]*a[10]*a[15] + a[4]*a[11]*a[14] + a[8]*a[6]*a[15] - a[8]*a[7]*a[14] - a[12]*a[6]*a[11] + a[12]*a[7]*a[10];
+    o[8] = a[4]*a[9]*a[15] - a[4]*a[11]*a[13] - a[8]*a[5]*a[15] + a[8]*a[7]*a[13] + a[12]*a[5]*a[11] - a[12]*a[7]*a[9];
+    o[12] = -a[4]*a[9]*a[14] + a[4]*a[10]*a[13] + a[8]*a[5]*a[14] - a[8]*a[6]*a[13] - a[12]*a[5]*a[10] + a[12]*a[6]*a[9];
+    o[1] = -a[1]*a[10]*a[15] + a[1]*a[11]*a[14] + a[9]*a[2]*a[15] - a[9]*a[3]*a[14] - a[13]*a[2]*a[11] + a[13]*a[3]*a[10];
+    o[5] = a[0]*a[10]*a[15] - a[0]*a[11]*a[14] - a[8]*a[2]*a[15] + a[8]*a[3]*a[14] + a[12]*a[2]*a[11] - a[12]*a[3]*a[10];
+    o[9] = -a[0]*a[9]*a[15] + a[0]*a[11]*a[13] + a[8]*a[1]*a[15] - a[8]*a[3]*a[13] - a[12]*a[1]*a[11] + a[12]*a[3]*a[9];
+    o[13] = a[0]*a[9]*a[14] - a[0]*a[10]*a[13] - a[8]*a[1]*a[14] + a[8]*a[2]*a[13] + a[12]*a[1]*a[10] - a[12]*a[2]*a[9];
+    o[2] = a[1]*a[6]*a[15] - a[1]*a[7]*a[14] - a[5]*a[2]*a[15] + a[5]*a[3]*a[14] + a[13]*a[2]*a[7] - a[13]*a[3]*a[6];
+    o[6] = -a[0]*a[6]*a[15] + a[0]*a[7]*a[14] + a[4]*a[2]*a[15] - a[4]*a[3]*a[14] - a[12]*a[2]*a[7] + a[12]*a[3]*a[6];
+    o[10] = a[0]*a[5]*a[15] - a[0]*a[7]*a[13] - a[4]*a[1]*a[15] + a[4]*a[3]*a[13] + a[12]*a[1]*a[7] - a[12]*a[3]*a[5];
+    o[14] = -a[0]*a[5]*a[14] + a[0]*a[6]*a[13] + a[4]*a[1]*a[14] - a[4]*a[2]*a[13] - a[12]*a[1]*a[6] + a[12]*a[2]*a[5];
+    o[3] = -a[1]*a[6]*a[11] + a[1]*a[7]*a[10] + a[5]*a[2]*a[11] - a[5]*a[3]*a[10] - a[9]*a[2]*a[7] + a[9]*a[3]*a[6];
+    o[7] = a[0]*a[6]*a[11] - a[0]*a[7]*a[10] - a[4]*a[2]*a[11] + a[4]*a[3]*a[10] + a[8]*a[2]*a[7] - a[8]*a[3]*a[6];
+    o[11] = -a[0]*a[5]*a[11] + a[0]*a[7]*a[9] + a[4]*a[1]*a[11] - a[4]*a[3]*a[9] - a[8]*a[1]*a[7] + a[8]*a[3]*a[5];
+    o[15] = a[0]*a[5]*a[10] - a[0]*a[6]*a[9] - a[4]*a[1]*a[10] + a[4]*a[2]*a[9] + a[8]*a[1]*a[6] - a[8]*a[2]*a[5];
+    double det = a[0]*o[0] + a[1]*o[4] + a[2]*o[8] + a[3]*o[12];
+    if (det == 0.0) return false;
+    for (int i = 0; i < 16; ++i) inv[i] = (float) (o[i] / det);
+    return true;
+}
+
+} // namespace mtsb

@@ -1,0 +1,258 @@
+// kernels.cuh -- __global__ wrappers around the HD stage bodies (device only).
+#pragma once
+#include "path.h"
+
+namespace mtsb {
+
+constexpr int kBlock = 128;
+constexpr int kStackFast = 8, kStackSlow = 56;
+
+// ---------------- BVH build ----------------------------------------------------------------------
+__device__ __forceinline__ void atomic_min_f(float *a, float v) {
+    // monotone int mapping of floats
+    int iv = __float_as_int(v);
+    if (iv >= 0) atomicMin((int *) a, iv); else atomicMax((unsigned int *) a, (unsigned int) iv);
+}
+__device__ __forceinline__ void atomic_max_f(float *a, float v) {
+    int iv = __float_as_int(v);
+    if (iv >= 0) atomicMax((int *) a, iv); else atomicMin((unsigned int *) a, (unsigned int) iv);
+}
+__global__ void k_tri_bounds(BvhBuild b, float *scene_bounds /* lo xyz, hi xyz */) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float3 lo = mk3(INFINITY), hi = mk3(-INFINITY);
+    if (i < b.n) tri_bounds_body(b, i, lo, hi);
+    for (int o = 16; o > 0; o >>= 1) {
+        lo.x = fminf(lo.x, __shfl_xor_sync(0xffffffffu, lo.x, o)); lo.y = fminf(lo.y, __shfl_xor_sync(0xffffffffu, lo.y, o));
+        lo.z = fminf(lo.z, __shfl_xor_sync(0xffffffffu, lo.z, o)); hi.x = fmaxf(hi.x, __shfl_xor_sync(0xffffffffu, hi.x, o));
+        hi.y = fmaxf(hi.y, __shfl_xor_sync(0xffffffffu, hi.y, o)); hi.z = fmaxf(hi.z, __shfl_xor_sync(0xffffffffu, hi.z, o));
+    }
+    if ((threadIdx.x & 31) == 0 && lo.x <= hi.x) {
+        atomic_min_f(scene_bounds + 0, lo.x); atomic_min_f(scene_bounds + 1, lo.y); atomic_min_f(scene_bounds + 2, lo.z);
+        atomic_max_f(scene_bounds + 3, hi.x); atomic_max_f(scene_bounds + 4, hi.y); atomic_max_f(scene_bounds + 5, hi.z);
+    }
+}
+__global__ void k_morton(BvhBuild b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) morton_body(b, i);
+}
+__global__ void k_lbvh_nodes(BvhBuild b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < b.n) lbvh_node_body(b, (int) i);
+}
+__global__ void k_lbvh_fit(BvhBuild b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) lbvh_fit_body(b, (int) i);
+}
+__global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
+    uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < end) collapse_body(b, i);
+}
+
+// ---------------- traversal ----------------------------------------------------------------------
+template <bool AnyHit>
+__global__ void __launch_bounds__(kBlock)
+k_trace(Bvh bvh, const uint32_t *count_ptr, uint32_t count_max, const float4 *__restrict__ o_mint,
+        const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded) {
+    __shared__ uint2 s_stack[kStackFast * kBlock];
+    uint32_t count = count_ptr ? min(*count_ptr, count_max) : count_max;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        float4 o = o_mint[i], d = d_maxt[i];
+        TravStack<kStackFast, kStackSlow> st; st.fast = s_stack + threadIdx.x; st.stride = kBlock;
+        Hit h;
+        bool found = bvh_trace<AnyHit>(bvh, xyz(o), xyz(d), o.w, d.w, st, h);
+        if (AnyHit) occluded[i] = found ? 1u : 0u;
+        else hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+    }
+}
+// brute force = Scene::ray_intersect_naive (kdtree.h:2304-2329) with the same triangle test
+__global__ void k_trace_naive(Bvh bvh, uint32_t count, const float4 *o_mint, const float4 *d_maxt, float4 *hits) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float4 o = o_mint[i], d = d_maxt[i];
+    RayWoop rw = woop_setup(xyz(o), xyz(d));
+    Hit h; h.t = INFINITY; h.u = h.v = 0.f; h.prim = 0xffffffffu;
+    float tmax = d.w;
+    for (uint32_t k = 0; k < bvh.n_tris; ++k) {
+        float4 a0 = bvh.tris[3 * k], a1 = bvh.tris[3 * k + 1], a2 = bvh.tris[3 * k + 2];
+        float t, u, v;
+        if (woop_intersect(rw, xyz(a0), xyz(a1), xyz(a2), o.w, tmax, t, u, v)) { tmax = t; h.t = t; h.u = u; h.v = v; h.prim = f2u(a0.w); }
+    }
+    hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+}
+
+// ---------------- wavefront stages ---------------------------------------------------------------
+// counters layout (uint32): [0..1023] live paths entering depth d (index d), [1024..2047] shadow rays of depth d
+// stats (uint64): [0] closest rays, [1] shadow rays, [2] segments
+__global__ void k_raygen(SensorDev sn, RenderBatch b, PathQueue q, uint32_t *counters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) counters[1] = b.n_paths;
+    if (i < b.n_paths) raygen_body(sn, b, q, i);
+}
+
+__device__ __forceinline__ uint32_t warp_alloc(uint32_t *counter, bool want) {
+    unsigned mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0) return 0;
+    int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t) __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t) __popc(mask & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(kBlock)
+k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
+        unsigned long long *stats, uint32_t depth) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t count = counters[depth];
+    if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
+    bool live = i < count;
+    ShadeOut out; out.extend = false; out.shadow = false;
+    if (live) out = shade_body(sc, qin, b, i);
+    uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
+    if (out.extend) {
+        qout.o_mint[slot] = out.o_mint; qout.d_maxt[slot] = out.d_maxt; qout.thr_eta[slot] = out.thr_eta;
+        qout.misc[slot] = out.misc; qout.rng[slot] = out.rng;
+    }
+    uint32_t sslot = warp_alloc(&counters[1024 + depth], out.shadow);
+    if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
+}
+
+// any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)
+__global__ void __launch_bounds__(kBlock)
+k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *stats, uint32_t depth, uint32_t count_max,
+         float4 *result) {
+    __shared__ uint2 s_stack[kStackFast * kBlock];
+    uint32_t count = min(counters[1024 + depth], count_max);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[1], (unsigned long long) count);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        float4 o = sq.o_mint[i], d = sq.d_maxt[i];
+        TravStack<kStackFast, kStackSlow> st; st.fast = s_stack + threadIdx.x; st.stride = kBlock;
+        Hit h;
+        if (!bvh_trace<true>(bvh, xyz(o), xyz(d), o.w, d.w, st, h)) {
+            float4 c = sq.contrib_id[i];
+            uint32_t pid = f2u(c.w);
+            float4 r = result[pid];
+            r.x += c.x; r.y += c.y; r.z += c.z;
+            result[pid] = r;
+        }
+    }
+}
+
+__device__ __forceinline__ void film_atomic_add(const SensorDev &sn, uint32_t pix, float4 v, float w) {
+#if __CUDA_ARCH__ >= 900
+    atomicAdd(&sn.film_xyza[pix], v);
+#else
+    atomicAdd(&sn.film_xyza[pix].x, v.x); atomicAdd(&sn.film_xyza[pix].y, v.y);
+    atomicAdd(&sn.film_xyza[pix].z, v.z); atomicAdd(&sn.film_xyza[pix].w, v.w);
+#endif
+    atomicAdd(&sn.film_w[pix], w);
+}
+
+// film splat at batch end with warp-aggregated atomics (one atomic set per warp when the warp's samples share a pixel)
+__global__ void __launch_bounds__(kBlock)
+k_splat(SensorDev sn, RenderBatch b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool live = i < b.n_paths;
+    float4 xyza = make_float4(0.f, 0.f, 0.f, 0.f); float wgt = 0.f; float fx = -10.f, fy = -10.f;
+    if (live) { xyza = radiance_to_xyza(b.result[i]); wgt = 1.f; path_film_pos(sn, b, i, fx, fy); }
+    if (sn.radius <= 1.f) {
+        int lx = (int) ceilf(fx - 1.f), ly = (int) ceilf(fy - 1.f);
+        bool ok = live && lx >= 0 && ly >= 0 && lx < (int) sn.width && ly < (int) sn.height;
+        uint32_t pix = ok ? (uint32_t) (ly * (int) sn.width + lx) : 0xffffffffu;
+        if (!ok) { xyza = make_float4(0.f, 0.f, 0.f, 0.f); wgt = 0.f; }
+        uint32_t p0 = __shfl_sync(0xffffffffu, pix, 0);
+        if (__all_sync(0xffffffffu, pix == p0)) {
+            for (int o = 16; o > 0; o >>= 1) {
+                xyza.x += __shfl_xor_sync(0xffffffffu, xyza.x, o); xyza.y += __shfl_xor_sync(0xffffffffu, xyza.y, o);
+                xyza.z += __shfl_xor_sync(0xffffffffu, xyza.z, o); xyza.w += __shfl_xor_sync(0xffffffffu, xyza.w, o);
+                wgt += __shfl_xor_sync(0xffffffffu, wgt, o);
+            }
+            if ((threadIdx.x & 31) == 0 && pix != 0xffffffffu) film_atomic_add(sn, pix, xyza, wgt);
+        } else if (ok)
+            film_atomic_add(sn, pix, xyza, wgt);
+    } else if (live) {
+        film_put(sn, fx, fy, xyza, wgt, [&](uint32_t pix, float4 v, float w) { film_atomic_add(sn, pix, v, w); });
+    }
+}
+
+// ImageBlock::put parity hook
+__global__ void k_film_put(SensorDev sn, uint32_t n, const float *pos2, const float *value5) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = make_float4(value5[5 * i], value5[5 * i + 1], value5[5 * i + 2], value5[5 * i + 3]);
+    film_put(sn, pos2[2 * i], pos2[2 * i + 1], v, value5[5 * i + 4], [&](uint32_t pix, float4 vv, float w) { film_atomic_add(sn, pix, vv, w); });
+}
+
+// film export / import / develop (src/films/hdrfilm.cpp:249-320; Bitmap::convert XYZAW -> RGB)
+__global__ void k_film_pack(SensorDev sn, float *xyzaw) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sn.width * sn.height) return;
+    float4 v = sn.film_xyza[i];
+    xyzaw[5 * i] = v.x; xyzaw[5 * i + 1] = v.y; xyzaw[5 * i + 2] = v.z; xyzaw[5 * i + 3] = v.w; xyzaw[5 * i + 4] = sn.film_w[i];
+}
+__global__ void k_film_unpack_add(SensorDev sn, const float *xyzaw, int replace) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sn.width * sn.height) return;
+    float4 v = replace ? make_float4(0.f, 0.f, 0.f, 0.f) : sn.film_xyza[i];
+    float w = replace ? 0.f : sn.film_w[i];
+    v.x += xyzaw[5 * i]; v.y += xyzaw[5 * i + 1]; v.z += xyzaw[5 * i + 2]; v.w += xyzaw[5 * i + 3]; w += xyzaw[5 * i + 4];
+    sn.film_xyza[i] = v; sn.film_w[i] = w;
+}
+__global__ void k_film_develop(SensorDev sn, float *rgb) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sn.width * sn.height) return;
+    float4 v = sn.film_xyza[i]; float w = sn.film_w[i];
+    float inv = w != 0.f ? 1.f / w : 0.f;   // Bitmap::convert: weight-normalise (0 weight -> 0)
+    float X = v.x * inv, Y = v.y * inv, Z = v.z * inv;
+    rgb[3 * i + 0] = 3.240479f * X - 1.537150f * Y - 0.498535f * Z;
+    rgb[3 * i + 1] = -0.969256f * X + 1.875991f * Y + 0.041556f * Z;
+    rgb[3 * i + 2] = 0.055648f * X - 0.204043f * Y + 1.057311f * Z;
+}
+
+// ---------------- parity hooks -------------------------------------------------------------------
+__global__ void k_pcg32(uint32_t n, const uint64_t *initstate, const uint64_t *initseq, uint32_t n_draws, float *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Pcg32 r; r.seed(initstate[i], initseq[i]);
+    for (uint32_t k = 0; k < n_draws; ++k) out[(size_t) i * n_draws + k] = r.next_f32();
+}
+__global__ void k_sampler_seed(uint32_t n, uint64_t seed, uint64_t *state, uint64_t *inc) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Pcg32 r = sampler_seed(seed, i); state[i] = r.state; inc[i] = r.inc;
+}
+__global__ void k_sensor_ray(SensorDev sn, uint32_t n, const float *pos2, float4 *o, float4 *d) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    sensor_sample_ray(sn, pos2[2 * i], pos2[2 * i + 1], o[i], d[i]);
+}
+HD SI local_si(float3 wi, float u, float v) {
+    SI si; si.p = mk3(0.f); si.n = mk3(0.f, 0.f, 1.f); si.sh.s = mk3(1.f, 0.f, 0.f); si.sh.t = mk3(0.f, 1.f, 0.f); si.sh.n = mk3(0.f, 0.f, 1.f);
+    si.u = u; si.v = v; si.wi = wi; si.t = 1.f; si.prim = 0; si.mesh = 0; si.valid = true; return si;
+}
+__global__ void k_bsdf_sample(SceneDev sc, uint32_t bsdf_id, uint32_t n, const float *wi, const float *uv, const float *s1, const float *s2, float *out9) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    SI si = local_si(ld3(wi, i), uv[2 * i], uv[2 * i + 1]);
+    BsdfSample bs = bsdf_sample(sc, sc.bsdfs[bsdf_id], si, s1[i], s2[2 * i], s2[2 * i + 1]);
+    float *o = out9 + 9 * (size_t) i;
+    o[0] = bs.wo.x; o[1] = bs.wo.y; o[2] = bs.wo.z; o[3] = bs.pdf; o[4] = bs.eta; o[5] = bs.weight.x; o[6] = bs.weight.y; o[7] = bs.weight.z; o[8] = bs.delta ? 1.f : 0.f;
+}
+__global__ void k_bsdf_eval_pdf(SceneDev sc, uint32_t bsdf_id, uint32_t n, const float *wi, const float *uv, const float *wo, float *eval3, float *pdf) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    SI si = local_si(ld3(wi, i), uv[2 * i], uv[2 * i + 1]);
+    float3 val; float p;
+    bsdf_eval_pdf(sc, sc.bsdfs[bsdf_id], si, ld3(wo, i), val, p);
+    eval3[3 * i] = val.x; eval3[3 * i + 1] = val.y; eval3[3 * i + 2] = val.z; pdf[i] = p;
+}
+__global__ void k_sample_emitter(SceneDev sc, uint32_t n, const float *ref_p, const float *s2, float *out11) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    DirSample ds = sample_emitter_direction(sc, ld3(ref_p, i), s2[2 * i], s2[2 * i + 1]);
+    float *o = out11 + 11 * (size_t) i;
+    o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.x; o[6] = ds.value.y; o[7] = ds.value.z;
+    o[8] = ds.n.x; o[9] = ds.n.y; o[10] = ds.n.z;
+}
+
+} // namespace mtsb

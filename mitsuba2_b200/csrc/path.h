@@ -1,0 +1,212 @@
+// path.h -- wavefront path-tracer stage bodies (HD): raygen, shade (emission + RR + emitter sampling with
+// MIS + BSDF sampling), shadow accumulate, film splat.  State machine = PathIntegrator::sample
+// (src/integrators/path.cpp:100-211) unrolled across kernel launches; per-sample prefix =
+// SamplingIntegrator::render_sample (src/librender/integrator.cpp:224-271).
+#pragma once
+#include "emit.h"
+
+namespace mtsb {
+
+// Compacted per-segment queue (ping-pong). 96 B per live path.
+struct PathQueue {
+    float4 *o_mint, *d_maxt;   // extension ray
+    float4 *hit;               // closest-hit result for that ray (t,u,v,prim)
+    float4 *thr_eta;           // throughput rgb, eta
+    uint4  *misc;              // path_id, depth | (prev_delta << 31), prev bsdf pdf (bits), unused
+    uint4  *rng;               // PCG32 state lo/hi, inc lo/hi
+};
+struct ShadowQueue {
+    float4 *o_mint, *d_maxt;   // shadow ray
+    float4 *contrib_id;        // mis * throughput * bsdf * Le/pdf (rgb), path_id (bits)
+};
+struct RenderBatch {
+    uint32_t n_paths;          // paths in this batch
+    uint64_t offset;           // global path index of the batch's first path (index = pixel*spp_batch + s)
+    uint32_t spp_begin, spp_batch, spp_total;
+    uint64_t seed;
+    float4 *result;            // per path: radiance rgb, alpha
+};
+
+HD void rng_store(uint4 *dst, const Pcg32 &r) {
+    *dst = make_uint4((uint32_t) r.state, (uint32_t) (r.state >> 32), (uint32_t) r.inc, (uint32_t) (r.inc >> 32));
+}
+HD Pcg32 rng_load(uint4 v) {
+    Pcg32 r; r.state = (uint64_t) v.x | ((uint64_t) v.y << 32); r.inc = (uint64_t) v.z | ((uint64_t) v.w << 32);
+    return r;
+}
+
+HD void path_ids(const RenderBatch &b, uint32_t i, uint32_t &pixel, uint32_t &stream) {
+    uint64_t g = b.offset + i;
+    pixel = (uint32_t) (g / b.spp_batch);
+    uint32_t s = b.spp_begin + (uint32_t) (g % b.spp_batch);
+    stream = pixel * b.spp_total + s;
+}
+
+// PerspectiveCamera::sample_ray (src/sensors/perspective.cpp:151-188); pos in [0,1]^2
+HD void sensor_sample_ray(const SensorDev &sn, float px, float py, float4 &o_mint, float4 &d_maxt) {
+    float3 near_p = xform_point_persp(sn.sample_to_camera, mk3(px, py, 0.f));
+    float3 d = normalize(near_p);
+    float inv_z = 1.f / d.z;
+    float3 o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
+    float3 dw = xform_vec(sn.to_world, d);
+    o_mint = mk4(o, sn.near_clip * inv_z); d_maxt = mk4(dw, sn.far_clip * inv_z);
+}
+
+HD void raygen_body(const SensorDev &sn, const RenderBatch &b, const PathQueue &q, uint32_t i) {
+    uint32_t pixel, stream; path_ids(b, i, pixel, stream);
+    Pcg32 rng = sampler_seed(b.seed, stream);
+    float jx = rng.next_f32(), jy = rng.next_f32();
+    (void) rng.next_f32();                       // wavelength sample (integrator.cpp:237), unused in rgb
+    float fx = (float) (pixel % sn.width) + jx, fy = (float) (pixel / sn.width) + jy;
+    float4 o, d;
+    sensor_sample_ray(sn, fx / (float) sn.width, fy / (float) sn.height, o, d);
+    q.o_mint[i] = o; q.d_maxt[i] = d;
+    q.thr_eta[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+    q.misc[i] = make_uint4(i, 1u, f2u(0.f), 0u);
+    rng_store(&q.rng[i], rng);
+    b.result[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+HD float mis_weight(float a, float b) { a *= a; b *= b; return a > 0.f ? a / (a + b) : 0.f; }
+
+struct ShadeOut {
+    bool extend, shadow;
+    float4 o_mint, d_maxt, thr_eta; uint4 misc, rng;          // extension record
+    float4 s_o_mint, s_d_maxt, s_contrib_id;                  // shadow record
+    // adjoint bookkeeping (filled always; cheap): first-hit info of this vertex
+    float3 emitted;                                            // radiance added at this vertex (already weighted)
+};
+
+// One iteration of the loop in path.cpp:124-208 for queue entry i.  `result` accumulates emission.
+HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i) {
+    ShadeOut out; out.extend = false; out.shadow = false; out.emitted = mk3(0.f);
+    float4 o4 = q.o_mint[i], d4 = q.d_maxt[i], h4 = q.hit[i], te = q.thr_eta[i];
+    uint4 misc = q.misc[i];
+    uint32_t path_id = misc.x, depth = misc.y & 0x7fffffffu; bool prev_delta = (misc.y >> 31) != 0;
+    float prev_pdf = u2f(misc.z);
+    float3 thr = xyz(te); float eta = te.w;
+    float3 o = xyz(o4), d = xyz(d4);
+    SI si = make_si(sc, o, d, h4);
+
+    // ---- emission (path.cpp:128-129) with the MIS weight of the previous BSDF sample (:194-205)
+    int em = si.valid ? sc.meshes[si.mesh].emitter : sc.env_emitter;
+    if (em >= 0) {
+        const EmitterDev &e = sc.emitters[em];
+        float3 Le; float emitter_pdf = 0.f;
+        if (e.type == 0) {
+            Le = si.wi.z > 0.f ? e.radiance : mk3(0.f);
+            if (depth > 1 && !prev_delta) {
+                float3 dd = si.p - o; float dist = norm(dd); dd = dd / dist;
+                emitter_pdf = area_pdf_direction(e, dd, si.sh.n, dist);
+            }
+        } else {
+            Le = env_eval(e, d);
+            if (depth > 1 && !prev_delta) emitter_pdf = env_pdf_direction(e, d);
+        }
+        if (sc.n_emitters > 1) emitter_pdf *= 1.f / (float) sc.n_emitters;
+        float w = depth > 1 ? mis_weight(prev_pdf, emitter_pdf) : 1.f;
+        float3 add = thr * Le * w;
+        out.emitted = add;
+        float4 r = b.result[path_id];
+        r.x += add.x; r.y += add.y; r.z += add.z;
+        if (depth == 1) r.w = si.valid ? 1.f : 0.f;
+        b.result[path_id] = r;
+    } else if (depth == 1) {
+        float4 r = b.result[path_id]; r.w = si.valid ? 1.f : 0.f; b.result[path_id] = r;
+    }
+    if (!si.valid) return out;
+
+    Pcg32 rng = rng_load(q.rng[i]);
+    // ---- Russian roulette (path.cpp:137-141)
+    if ((int) depth > sc.rr_depth) {
+        float qq = fminf(hmax(thr) * sqr(eta), 0.95f);
+        bool survive = rng.next_f32() < qq;
+        thr *= 1.f / qq;
+        if (!survive) return out;
+    }
+    if ((uint32_t) depth >= (uint32_t) sc.max_depth) return out;
+
+    const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
+    // ---- emitter sampling (path.cpp:155-172, scene.cpp:141-189)
+    if (bsdf_is_smooth(bsdf)) {
+        float sx = rng.next_f32(), sy = rng.next_f32();
+        if (sc.n_emitters > 0) {
+            DirSample ds = sample_emitter_direction(sc, si.p, sx, sy);
+            if (ds.pdf != 0.f) {
+                float3 wo = si.sh.to_local(ds.d);
+                float3 bval; float bpdf;
+                bsdf_eval_pdf(sc, bsdf, si, wo, bval, bpdf);
+                float mis = mis_weight(ds.pdf, bpdf);
+                float3 c = thr * bval * ds.value * mis;
+                if (c.x != 0.f || c.y != 0.f || c.z != 0.f) {
+                    out.shadow = true;
+                    out.s_o_mint = mk4(si.p, kRayEpsilon * (1.f + hmax(abs3(si.p))));
+                    out.s_d_maxt = mk4(ds.d, ds.dist * (1.f - kShadowEpsilon));
+                    out.s_contrib_id = mk4(c, u2f(path_id));
+                }
+            }
+        }
+    }
+    // ---- BSDF sampling (path.cpp:177-190)
+    float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
+    BsdfSample bs = bsdf_sample(sc, bsdf, si, s1, s2x, s2y);
+    thr *= bs.weight;
+    if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) return out;
+    eta *= bs.eta;
+    float3 wo_w = si.sh.to_world(bs.wo);
+    out.extend = true;
+    out.o_mint = mk4(si.p, (1.f + hmax(abs3(si.p))) * kRayEpsilon);
+    out.d_maxt = mk4(wo_w, INFINITY);
+    out.thr_eta = mk4(thr, eta);
+    out.misc = make_uint4(path_id, (depth + 1u) | (bs.delta ? 0x80000000u : 0u), f2u(bs.pdf), 0u);
+    rng_store(&out.rng, rng);
+    return out;
+}
+
+// ---- film: ImageBlock::put (src/librender/imageblock.cpp:79-172) on a border-less full-film block ----------
+HD float rfilter_eval(const SensorDev &sn, float x) {
+    if (sn.rfilter == 0) return fabsf(x) <= sn.radius ? 1.f : 0.f;                 // src/rfilters/box.cpp:34-36
+    if (sn.rfilter == 1) return fmaxf(0.f, 1.f - fabsf(x / sn.radius));            // src/rfilters/tent.cpp:33-35
+    float alpha = -1.f / (2.f * sn.stddev * sn.stddev);                            // src/rfilters/gaussian.cpp:34-47
+    return fmaxf(0.f, expf(alpha * x * x) - expf(alpha * sn.radius * sn.radius));
+}
+
+template <typename AddFn>
+HD void film_put(const SensorDev &sn, float px, float py, float4 xyza, float wgt, AddFn add) {
+    // full-film block: offset 0, border 0 => pos = pos_ - 0.5
+    float x = px - 0.5f, y = py - 0.5f;
+    if (sn.radius > 1.f) {
+        int lox = max((int) ceilf(x - sn.radius), 0), loy = max((int) ceilf(y - sn.radius), 0);
+        int hix = min((int) floorf(x + sn.radius), (int) sn.width - 1), hiy = min((int) floorf(y + sn.radius), (int) sn.height - 1);
+        int n = (int) ceilf((sn.radius - 2.f * kRayEpsilon) * 2.f);
+        for (int yr = 0; yr < n; ++yr) {
+            int yy = loy + yr; if (yy > hiy) break;
+            float wy = rfilter_eval(sn, (float) loy - y + (float) yr);
+            for (int xr = 0; xr < n; ++xr) {
+                int xx = lox + xr; if (xx > hix) break;
+                float w = wy * rfilter_eval(sn, (float) lox - x + (float) xr);
+                add((uint32_t) (yy * (int) sn.width + xx), make_float4(xyza.x * w, xyza.y * w, xyza.z * w, xyza.w * w), wgt * w);
+            }
+        }
+    } else {
+        int lx = (int) ceilf(x - 0.5f), ly = (int) ceilf(y - 0.5f);
+        if (lx >= 0 && ly >= 0 && lx < (int) sn.width && ly < (int) sn.height)
+            add((uint32_t) (ly * (int) sn.width + lx), xyza, wgt);
+    }
+}
+
+// src/librender/integrator.cpp:254-270: rgb -> XYZ (core/spectrum.h:220-227), aovs = {X,Y,Z,alpha,1}
+HD float4 radiance_to_xyza(float4 r) {
+    return make_float4(0.412453f * r.x + 0.357580f * r.y + 0.180423f * r.z,
+                       0.212671f * r.x + 0.715160f * r.y + 0.072169f * r.z,
+                       0.019334f * r.x + 0.119193f * r.y + 0.950227f * r.z, r.w);
+}
+// position sample of path i (re-derived from the RNG stream instead of stored)
+HD void path_film_pos(const SensorDev &sn, const RenderBatch &b, uint32_t i, float &fx, float &fy) {
+    uint32_t pixel, stream; path_ids(b, i, pixel, stream);
+    Pcg32 rng = sampler_seed(b.seed, stream);
+    float jx = rng.next_f32(), jy = rng.next_f32();
+    fx = (float) (pixel % sn.width) + jx; fy = (float) (pixel / sn.width) + jy;
+}
+
+} // namespace mtsb

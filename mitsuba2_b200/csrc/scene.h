@@ -1,0 +1,45 @@
+// scene.h -- device-side scene snapshot (POD structs of pointers) shared by all stages.
+#pragma once
+#include "bvh.h"
+
+namespace mtsb {
+
+struct TexDev {
+    int type; float3 value;
+    uint32_t w, h, ch; const float *data; float to_uv[9];
+};
+struct BsdfDev {
+    int type; int refl, eta, k, spec_r, spec_t;
+    float alpha_u, alpha_v; int distr; int sample_visible; float eta_f;
+};
+constexpr int kMaxEnvLevels = 20;
+struct EmitterDev {
+    int type;
+    // area
+    float3 radiance; int mesh; const float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
+    // envmap
+    uint32_t w, h; const float4 *rgba; float to_world[16], to_local[16]; float scale;
+    int n_levels; const float *level_data[kMaxEnvLevels]; uint32_t level_width[kMaxEnvLevels];
+    float bsphere_radius;
+};
+struct MeshDev {
+    uint32_t face_begin, face_count, vert_begin, vert_count;
+    int bsdf, emitter, has_normals, has_uv;
+};
+struct SensorDev {
+    float to_world[16], sample_to_camera[16];
+    float near_clip, far_clip;
+    uint32_t width, height;
+    int rfilter; float radius, stddev;   // radius already includes box RayEpsilon
+    float4 *film_xyza; float *film_w;    // device film accumulators
+};
+struct SceneDev {
+    Bvh bvh;
+    const float *pos, *nrm, *uv;
+    const uint4 *faces;
+    const MeshDev *meshes; const TexDev *tex; const BsdfDev *bsdfs; const EmitterDev *emitters;
+    int n_emitters, env_emitter;
+    int max_depth, rr_depth;
+};
+
+} // namespace mtsb

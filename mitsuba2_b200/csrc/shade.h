@@ -1,0 +1,310 @@
+// shade.h -- surface interaction reconstruction, textures and the three in-scope BSDFs (HD bodies).
+#pragma once
+#include "scene.h"
+
+namespace mtsb {
+
+struct SI {
+    float3 p, n; Frame sh; float u, v; float3 wi; float t; uint32_t prim; int mesh; bool valid;
+};
+
+HD float3 ld3(const float *a, uint32_t i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
+
+// ShapeKDTree::create_surface_interaction (include/mitsuba/render/kdtree.h:2334-2368) +
+// Mesh::fill_surface_interaction (src/librender/mesh.cpp:399-462); miss: scene_native.inl:29-31.
+HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
+    SI si;
+    si.t = hit.x; si.prim = f2u(hit.w); si.valid = hit.x != INFINITY;
+    if (!si.valid) { si.wi = -d; si.mesh = -1; si.p = o; si.n = mk3(0.f); si.u = si.v = 0.f; si.sh.s = si.sh.t = si.sh.n = mk3(0.f); return si; }
+    uint4 f = sc.faces[si.prim];
+    si.mesh = (int) f.w;
+    const MeshDev m = sc.meshes[f.w];
+    float b1 = hit.y, b2 = hit.z, b0 = 1.f - b1 - b2;
+    float3 p0 = ld3(sc.pos, f.x), p1 = ld3(sc.pos, f.y), p2 = ld3(sc.pos, f.z);
+    float3 dp0 = p1 - p0, dp1 = p2 - p0;
+    si.p = p0 * b0 + p1 * b1 + p2 * b2;
+    float3 n = normalize(cross(dp0, dp1));
+    si.n = n;
+    float3 dp_du, dp_dv;
+    coordinate_system(n, dp_du, dp_dv);
+    si.u = b1; si.v = b2;
+    if (m.has_uv) {
+        float u0 = sc.uv[2 * f.x], v0 = sc.uv[2 * f.x + 1], u1 = sc.uv[2 * f.y], v1 = sc.uv[2 * f.y + 1],
+              u2 = sc.uv[2 * f.z], v2 = sc.uv[2 * f.z + 1];
+        si.u = u0 * b0 + u1 * b1 + u2 * b2; si.v = v0 * b0 + v1 * b1 + v2 * b2;
+        float du0 = u1 - u0, dv0 = v1 - v0, du1 = u2 - u0, dv1 = v2 - v0;
+        float det = fmaf(du0, dv1, -(dv0 * du1));
+        if (det != 0.f) {
+            float inv = 1.f / det;
+            dp_du = (dp0 * dv1 - dp1 * dv0) * inv;
+            dp_dv = (dp1 * du0 - dp0 * du1) * inv;
+        }
+    }
+    float3 ns = n;
+    if (m.has_normals) {
+        float3 n0 = ld3(sc.nrm, f.x), n1 = ld3(sc.nrm, f.y), n2 = ld3(sc.nrm, f.z);
+        ns = normalize(n0 * b0 + n1 * b1 + n2 * b2);
+    }
+    si.sh.n = ns;
+    si.sh.s = normalize(dp_du - ns * dot(ns, dp_du));
+    si.sh.t = cross(ns, si.sh.s);
+    si.wi = si.sh.to_local(-d);
+    return si;
+}
+
+// src/textures/bitmap.cpp:250-293 (bilinear, repeat) and constant rgb (src/spectra/srgb.cpp)
+HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) {
+    const TexDev &t = sc.tex[id];
+    if (t.type == 0) return t.value;
+    float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
+    tu -= floorf(tu); tv -= floorf(tv);
+    tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
+    uint32_t px = min((uint32_t) tu, t.w - 2), py = min((uint32_t) tv, t.h - 2);
+    float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t idx = px + py * t.w;
+    if (t.ch == 1) {
+        float v00 = t.data[idx], v10 = t.data[idx + 1], v01 = t.data[idx + t.w], v11 = t.data[idx + t.w + 1];
+        float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
+        return mk3(fmaf(w0y, v0, w1y * v1));
+    }
+    float3 v00 = ld3(t.data, idx), v10 = ld3(t.data, idx + 1), v01 = ld3(t.data, idx + t.w), v11 = ld3(t.data, idx + t.w + 1);
+    float3 v0 = mk3(fmaf(w0x, v00.x, w1x * v10.x), fmaf(w0x, v00.y, w1x * v10.y), fmaf(w0x, v00.z, w1x * v10.z));
+    float3 v1 = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
+    return mk3(fmaf(w0y, v0.x, w1y * v1.x), fmaf(w0y, v0.y, w1y * v1.y), fmaf(w0y, v0.z, w1y * v1.z));
+}
+// texel footprint of a bitmap lookup (for the adjoint scatter): indices of the 4 texels + weights
+HD bool tex_footprint(const TexDev &t, float u, float v, uint32_t idx[4], float w[4]) {
+    if (t.type == 0) return false;
+    float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
+    tu -= floorf(tu); tv -= floorf(tv);
+    tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
+    uint32_t px = min((uint32_t) tu, t.w - 2), py = min((uint32_t) tv, t.h - 2);
+    float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t i = px + py * t.w;
+    idx[0] = i; idx[1] = i + 1; idx[2] = i + t.w; idx[3] = i + t.w + 1;
+    w[0] = w0x * w0y; w[1] = w1x * w0y; w[2] = w0x * w1y; w[3] = w1x * w1y;
+    return true;
+}
+
+// ---- warps (include/mitsuba/core/warp.h:54-90, 153-156, 332-356) ---------------------------------
+HD void square_to_disk_concentric(float sx, float sy, float &ox, float &oy) {
+    float x = fmaf(2.f, sx, -1.f), y = fmaf(2.f, sy, -1.f);
+    bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
+    float r = q13 ? y : x, rp = q13 ? x : y;
+    float phi = 0.25f * kPi * rp / r;
+    if (q13) phi = 0.5f * kPi - phi;
+    if (is_zero) phi = 0.f;
+    float s, c; sincosf(phi, &s, &c);
+    ox = r * c; oy = r * s;
+}
+HD float3 square_to_cosine_hemisphere(float sx, float sy) {
+    float px, py; square_to_disk_concentric(sx, sy, px, py);
+    return mk3(px, py, safe_sqrt(1.f - (px * px + py * py)));
+}
+
+struct BsdfSample { float3 wo; float pdf, eta; bool delta; float3 weight; };
+
+// ---- fresnel (include/mitsuba/render/fresnel.h:34-76, 92-116) ------------------------------------
+HD void fresnel_dielectric(float cos_i, float eta, float &r, float &cos_t, float &eta_it, float &eta_ti) {
+    bool outside = cos_i >= 0.f;
+    float rcp_eta = 1.f / eta;
+    eta_it = outside ? eta : rcp_eta; eta_ti = outside ? rcp_eta : eta;
+    float cos_t_sqr = fmaf(-fmaf(-cos_i, cos_i, 1.f), eta_ti * eta_ti, 1.f);
+    float ci = fabsf(cos_i), ct = safe_sqrt(cos_t_sqr);
+    bool index_matched = eta == 1.f, special = index_matched || ci == 0.f;
+    float r_sc = index_matched ? 0.f : 1.f;
+    float a_s = fmaf(-eta_it, ct, ci) / fmaf(eta_it, ct, ci);
+    float a_p = fmaf(-eta_it, ci, ct) / fmaf(eta_it, ci, ct);
+    r = 0.5f * (a_s * a_s + a_p * a_p);
+    if (special) r = r_sc;
+    cos_t = mulsign_neg(ct, cos_i);
+}
+HD float fresnel_conductor(float cos_i, float eta_r, float eta_i) {
+    float c2 = cos_i * cos_i, s2 = 1.f - c2, s4 = s2 * s2;
+    float temp_1 = eta_r * eta_r - eta_i * eta_i - s2;
+    float a2pb2 = safe_sqrt(temp_1 * temp_1 + 4.f * eta_i * eta_i * eta_r * eta_r);
+    float a = safe_sqrt(0.5f * (a2pb2 + temp_1));
+    float term_1 = a2pb2 + c2, term_2 = 2.f * cos_i * a;
+    float r_s = (term_1 - term_2) / (term_1 + term_2);
+    float term_3 = a2pb2 * c2 + s4, term_4 = term_2 * s2;
+    float r_p = r_s * (term_3 - term_4) / (term_3 + term_4);
+    return 0.5f * (r_s + r_p);
+}
+
+// ---- microfacet (include/mitsuba/render/microfacet.h:184-413) ------------------------------------
+HD float erfinv_giles(float x) {   // ext/enoki/include/enoki/special.h:222-247
+    float w = -logf((1.f - x) * (1.f + x));
+    float w1 = w - 2.5f, w2 = sqrtf(w) - 3.f;
+    float p1 = 2.81022636e-08f;
+    p1 = fmaf(p1, w1, 3.43273939e-07f); p1 = fmaf(p1, w1, -3.5233877e-06f); p1 = fmaf(p1, w1, -4.39150654e-06f);
+    p1 = fmaf(p1, w1, 0.00021858087f); p1 = fmaf(p1, w1, -0.00125372503f); p1 = fmaf(p1, w1, -0.00417768164f);
+    p1 = fmaf(p1, w1, 0.246640727f); p1 = fmaf(p1, w1, 1.50140941f);
+    float p2 = -0.000200214257f;
+    p2 = fmaf(p2, w2, 0.000100950558f); p2 = fmaf(p2, w2, 0.00134934322f); p2 = fmaf(p2, w2, -0.00367342844f);
+    p2 = fmaf(p2, w2, 0.00573950773f); p2 = fmaf(p2, w2, -0.0076224613f); p2 = fmaf(p2, w2, 0.00943887047f);
+    p2 = fmaf(p2, w2, 1.00167406f); p2 = fmaf(p2, w2, 2.83297682f);
+    return (w < 5.f ? p1 : p2) * x;
+}
+struct Microfacet {
+    int type; float au, av; bool visible;
+    HD Microfacet(int t, float a_u, float a_v, bool vis) : type(t), au(fmaxf(a_u, 1e-4f)), av(fmaxf(a_v, 1e-4f)), visible(vis) {}
+    HD float eval(float3 m) const {
+        float auv = au * av, ct = m.z, ct2 = ct * ct, result;
+        if (type == 0)
+            result = expf(-(sqr(m.x / au) + sqr(m.y / av)) / ct2) / (kPi * auv * sqr(ct2));
+        else
+            result = 1.f / (kPi * auv * sqr(sqr(m.x / au) + sqr(m.y / av) + sqr(m.z)));
+        return result * ct > 1e-20f ? result : 0.f;
+    }
+    HD float smith_g1(float3 v, float3 m) const {
+        float xy2 = sqr(au * v.x) + sqr(av * v.y), tan2 = xy2 / sqr(v.z), result;
+        if (type == 0) {
+            float a = 1.f / sqrtf(tan2), a2 = a * a;
+            result = a >= 1.6f ? 1.f : (3.535f * a + 2.181f * a2) / (1.f + 2.276f * a + 2.577f * a2);
+        } else
+            result = 2.f / (1.f + sqrtf(1.f + tan2));
+        if (xy2 == 0.f) result = 1.f;
+        if (dot(v, m) * v.z <= 0.f) result = 0.f;
+        return result;
+    }
+    HD float G(float3 wi, float3 wo, float3 m) const { return smith_g1(wi, m) * smith_g1(wo, m); }
+    HD float pdf(float3 wi, float3 m) const {
+        float r = eval(m);
+        if (visible) r *= smith_g1(wi, m) * fabsf(dot(wi, m)) / wi.z; else r *= m.z;
+        return r;
+    }
+    HD void sample_visible_11(float cos_i, float sx, float sy, float &ox, float &oy) const {
+        if (type == 0) {
+            float tan_i = safe_sqrt(fmaf(-cos_i, cos_i, 1.f)) / cos_i, cot_i = 1.f / tan_i;
+            float maxval = erff(cot_i);
+            sx = fmaxf(fminf(sx, 1.f - 1e-6f), 1e-6f); sy = fmaxf(fminf(sy, 1.f - 1e-6f), 1e-6f);
+            float x = maxval - (maxval + 1.f) * erff(sqrtf(-logf(sx)));
+            sx *= 1.f + maxval + kInvSqrtPi * tan_i * expf(-sqr(cot_i));
+            for (int i = 0; i < 3; ++i) {
+                float slope = erfinv_giles(x);
+                float value = 1.f + x + kInvSqrtPi * tan_i * expf(-sqr(slope)) - sx;
+                float deriv = 1.f - slope * tan_i;
+                x -= value / deriv;
+            }
+            ox = erfinv_giles(x); oy = erfinv_giles(fmaf(2.f, sy, -1.f));
+        } else {
+            float px, py; square_to_disk_concentric(sx, sy, px, py);
+            float s = 0.5f * (1.f + cos_i);
+            py = lerpf(safe_sqrt(1.f - px * px), py, s);
+            float x = px, y = py, z = safe_sqrt(1.f - (px * px + py * py));
+            float sin_i = safe_sqrt(1.f - cos_i * cos_i);
+            float nrm = 1.f / fmaf(sin_i, y, cos_i * z);
+            ox = fmaf(cos_i, y, -(sin_i * z)) * nrm; oy = x * nrm;
+        }
+    }
+    HD float3 sample(float3 wi, float sx, float sy, float &pdf_out) const {
+        if (!visible) {
+            float sin_phi, cos_phi, cos_theta, cos_theta_2, alpha_2;
+            if (au == av) { sincosf(2.f * kPi * sy, &sin_phi, &cos_phi); alpha_2 = au * au; }
+            else {
+                float ratio = av / au, tmp = ratio * tanf(2.f * kPi * sy);
+                cos_phi = 1.f / sqrtf(fmaf(tmp, tmp, 1.f));
+                cos_phi = mulsign(cos_phi, fabsf(sy - 0.5f) - 0.25f);
+                sin_phi = cos_phi * tmp;
+                alpha_2 = 1.f / (sqr(cos_phi / au) + sqr(sin_phi / av));
+            }
+            if (type == 0) {
+                cos_theta = 1.f / sqrtf(fmaf(-alpha_2, logf(1.f - sx), 1.f));
+                cos_theta_2 = cos_theta * cos_theta;
+                float c3 = fmaxf(cos_theta_2 * cos_theta, 1e-20f);
+                pdf_out = (1.f - sx) / (kPi * au * av * c3);
+            } else {
+                float t2 = alpha_2 * sx / (1.f - sx);
+                cos_theta = 1.f / sqrtf(1.f + t2); cos_theta_2 = cos_theta * cos_theta;
+                float temp = 1.f + t2 / alpha_2, c3 = fmaxf(cos_theta_2 * cos_theta, 1e-20f);
+                pdf_out = 1.f / (kPi * au * av * c3 * sqr(temp));
+            }
+            float sin_theta = sqrtf(1.f - cos_theta_2);
+            return mk3(cos_phi * sin_theta, sin_phi * sin_theta, cos_theta);
+        }
+        float3 wi_p = normalize(mk3(au * wi.x, av * wi.y, wi.z));
+        // Frame::sincos_phi (include/mitsuba/core/frame.h): degenerate -> (0, 1)
+        float sin_theta_2 = fmaf(-wi_p.z, wi_p.z, 1.f), inv = 1.f / sqrtf(sin_theta_2);
+        float sin_phi = fminf(fmaxf(wi_p.y * inv, -1.f), 1.f), cos_phi = fminf(fmaxf(wi_p.x * inv, -1.f), 1.f);
+        if (fabsf(sin_theta_2) <= 4.f * kEpsilon) { sin_phi = 0.f; cos_phi = 1.f; }
+        float slx, sly; sample_visible_11(wi_p.z, sx, sy, slx, sly);
+        float rx = fmaf(cos_phi, slx, -(sin_phi * sly)) * au, ry = fmaf(sin_phi, slx, cos_phi * sly) * av;
+        float3 m = normalize(mk3(-rx, -ry, 1.f));
+        pdf_out = eval(m) * smith_g1(wi, m) * fabsf(dot(wi, m)) / wi.z;
+        return m;
+    }
+};
+
+// ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
+HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
+    BsdfSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = mk3(0.f);
+    float cos_i = si.wi.z;
+    if (b.type == 0) {            // src/bsdfs/diffuse.cpp:78-103
+        if (!(cos_i > 0.f)) return bs;
+        bs.wo = square_to_cosine_hemisphere(sx, sy);
+        bs.pdf = kInvPi * bs.wo.z;
+        if (bs.pdf > 0.f) bs.weight = tex_eval(sc, b.refl, si.u, si.v);
+        return bs;
+    }
+    if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:196-276
+        if (!(cos_i > 0.f)) return bs;
+        Microfacet distr(b.distr, b.alpha_u, b.alpha_v, b.sample_visible != 0);
+        float3 m = distr.sample(si.wi, sx, sy, bs.pdf);
+        bs.wo = m * (2.f * dot(si.wi, m)) - si.wi;
+        bool active = bs.pdf != 0.f && bs.wo.z > 0.f;
+        float weight = b.sample_visible ? distr.smith_g1(bs.wo, m)
+                                        : distr.G(si.wi, bs.wo, m) * dot(si.wi, m) / (cos_i * m.z);
+        bs.pdf /= 4.f * dot(bs.wo, m);
+        float3 eta = tex_eval(sc, b.eta, si.u, si.v), k = tex_eval(sc, b.k, si.u, si.v);
+        float c = dot(si.wi, m);
+        float3 F = mk3(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z));
+        if (b.spec_r >= 0) F *= tex_eval(sc, b.spec_r, si.u, si.v);
+        bs.weight = active ? F * weight : mk3(0.f);
+        return bs;
+    }
+    // src/bsdfs/dielectric.cpp:201-316
+    float r_i, cos_t, eta_it, eta_ti;
+    fresnel_dielectric(cos_i, b.eta_f, r_i, cos_t, eta_it, eta_ti);
+    float t_i = 1.f - r_i;
+    bool sel_r = s1 <= r_i;
+    bs.pdf = sel_r ? r_i : t_i;
+    bs.delta = true;
+    bs.wo = sel_r ? mk3(-si.wi.x, -si.wi.y, si.wi.z) : mk3(-eta_ti * si.wi.x, -eta_ti * si.wi.y, cos_t);
+    bs.eta = sel_r ? 1.f : eta_it;
+    float3 w = mk3(1.f);
+    if (sel_r) { if (b.spec_r >= 0) w *= tex_eval(sc, b.spec_r, si.u, si.v); }
+    else { if (b.spec_t >= 0) w *= tex_eval(sc, b.spec_t, si.u, si.v); w *= sqr(eta_ti); }
+    bs.weight = w;
+    return bs;
+}
+
+HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
+    val = mk3(0.f); pdf = 0.f;
+    float ci = si.wi.z, co = wo.z;
+    if (b.type == 0) {            // src/bsdfs/diffuse.cpp:105-135
+        if (ci > 0.f && co > 0.f) { val = tex_eval(sc, b.refl, si.u, si.v) * kInvPi * co; pdf = kInvPi * co; }
+        return;
+    }
+    if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:278-394
+        if (!(ci > 0.f && co > 0.f)) return;
+        float3 H = normalize(wo + si.wi);
+        Microfacet distr(b.distr, b.alpha_u, b.alpha_v, b.sample_visible != 0);
+        float D = distr.eval(H);
+        if (D != 0.f) {
+            float G = distr.G(si.wi, wo, H);
+            float res = D * G / (4.f * ci);
+            float3 eta = tex_eval(sc, b.eta, si.u, si.v), k = tex_eval(sc, b.k, si.u, si.v);
+            float c = dot(si.wi, H);
+            float3 F = mk3(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z));
+            if (b.spec_r >= 0) F *= tex_eval(sc, b.spec_r, si.u, si.v);
+            val = F * res;
+        }
+        if (dot(si.wi, H) > 0.f && dot(wo, H) > 0.f)
+            pdf = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
+        return;
+    }
+}
+
+HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
+
+} // namespace mtsb
