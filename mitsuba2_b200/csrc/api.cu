@@ -689,3 +689,8 @@ extern "C" int mtsb_sample_emitter_direction(mtsb_scene *s, uint64_t n, const fl
     CU(cudaStreamSynchronize(st)); CU(cudaGetLastError());
     return MTSB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Gradient pass (implemented in grad.cuh)
+// ---------------------------------------------------------------------------------------------------
+#include "grad.cuh"
