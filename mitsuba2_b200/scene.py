@@ -1,0 +1,273 @@
+"""Device scene: Python mirror of the reference's ``Scene`` / ``Integrator`` / ``Film`` entry points for the
+hot path, calling the CUDA library through the C ABI (include/mtsb200.h).
+
+Reference interfaces mirrored (names and argument meaning):
+  ``Scene.ray_intersect(ray)`` / ``Scene.ray_test(ray)``  -- src/librender/scene.cpp:108-139
+  ``Integrator.render(scene, sensor)``                    -- src/librender/integrator.cpp:52-176
+  ``Film.bitmap(raw)`` / ``Film.develop()``               -- src/films/hdrfilm.cpp:249-342
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+from .scenedata import SceneData
+
+_ctx_cache = {}
+
+
+def _context(device):
+    if device not in _ctx_cache:
+        h = C.c_void_p()
+        A.check(A.lib().mtsb_ctx_create(int(device), C.byref(h)))
+        _ctx_cache[device] = h
+    return _ctx_cache[device]
+
+
+def _is_torch_cuda(x):
+    return hasattr(x, "is_cuda") and x.is_cuda
+
+
+def _arg(x, dtype, n_expected=None):
+    """-> (pointer, mem, keepalive) for a numpy array or a CUDA torch tensor."""
+    if _is_torch_cuda(x):
+        x = x.contiguous()
+        return C.c_void_p(x.data_ptr()), A.MEM_DEVICE, x
+    a = np.ascontiguousarray(x, dtype=dtype)
+    if n_expected is not None and a.size != n_expected:
+        raise ValueError(f"expected {n_expected} elements, got {a.size}")
+    return C.c_void_p(a.ctypes.data), A.MEM_HOST, a
+
+
+class Scene:
+    def __init__(self, data: SceneData, device=0):
+        self.data = data
+        self.device = device
+        self._ctx = _context(device)
+        self._h = C.c_void_p()
+        desc, keep = data.to_desc()
+        A.check(A.lib().mtsb_scene_create(self._ctx, C.byref(desc), C.byref(self._h)))
+        del keep
+        self.last_stats = None
+        prim_counts = [m.faces.shape[0] for m in data.meshes]
+        self.primitive_map = np.concatenate([[0], np.cumsum(prim_counts)]).astype(np.int64)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            A.lib().mtsb_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- statistics ---------------------------------------------------------------------------
+    def build_stats(self):
+        st = A.Stats()
+        A.check(A.lib().mtsb_scene_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
+    # ---- Scene::ray_intersect / ray_test --------------------------------------------------------
+    @staticmethod
+    def pack_rays(o, d, mint=0.0, maxt=np.inf):
+        o = np.asarray(o, dtype=np.float32).reshape(-1, 3)
+        d = np.asarray(d, dtype=np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        om = np.empty((n, 4), np.float32)
+        dm = np.empty((n, 4), np.float32)
+        om[:, :3], dm[:, :3] = o, d
+        om[:, 3], dm[:, 3] = mint, maxt
+        return om, dm
+
+    def intersect_closest_raw(self, o_mint, d_maxt, hits=None, naive=False):
+        """SoA entry: o_mint/d_maxt (n,4) float32 numpy or CUDA torch; returns hits (n,4) = t,u,v,prim bits."""
+        po, mem, k0 = _arg(o_mint, np.float32)
+        pd, mem2, k1 = _arg(d_maxt, np.float32)
+        assert mem == mem2
+        n = (k0.numel() if mem == A.MEM_DEVICE else k0.size) // 4
+        if hits is None:
+            if mem == A.MEM_DEVICE:
+                import torch
+                hits = torch.empty((n, 4), dtype=torch.float32, device=k0.device)
+            else:
+                hits = np.empty((n, 4), np.float32)
+        ph = C.c_void_p(hits.data_ptr()) if mem == A.MEM_DEVICE else C.c_void_p(hits.ctypes.data)
+        st = A.Stats()
+        if naive:
+            A.check(A.lib().mtsb_intersect_naive(self._h, n, po, pd, ph, mem))
+        else:
+            A.check(A.lib().mtsb_intersect_closest(self._h, n, po, pd, ph, mem, C.byref(st)))
+        self.last_stats = st.as_dict()
+        return hits
+
+    def intersect_any_raw(self, o_mint, d_maxt, out=None):
+        po, mem, k0 = _arg(o_mint, np.float32)
+        pd, mem2, k1 = _arg(d_maxt, np.float32)
+        assert mem == mem2
+        n = (k0.numel() if mem == A.MEM_DEVICE else k0.size) // 4
+        if out is None:
+            if mem == A.MEM_DEVICE:
+                import torch
+                out = torch.empty((n,), dtype=torch.int32, device=k0.device)
+            else:
+                out = np.empty((n,), np.uint32)
+        ph = C.c_void_p(out.data_ptr()) if mem == A.MEM_DEVICE else C.c_void_p(out.ctypes.data)
+        st = A.Stats()
+        A.check(A.lib().mtsb_intersect_any(self._h, n, po, pd, ph, mem, C.byref(st)))
+        self.last_stats = st.as_dict()
+        return out
+
+    def ray_intersect(self, o, d, mint=0.0, maxt=np.inf):
+        """Mirror of ``Scene::ray_intersect``: returns a dict with ``t`` (inf on miss), ``prim_index`` (within the
+        shape), ``shape_index``, ``prim_uv`` (barycentrics b1,b2) and ``is_valid``."""
+        om, dm = self.pack_rays(o, d, mint, maxt)
+        hits = self.intersect_closest_raw(om, dm)
+        gprim = hits[:, 3].copy().view(np.uint32).astype(np.int64)
+        valid = np.isfinite(hits[:, 0])
+        shape = np.searchsorted(self.primitive_map, np.where(valid, gprim, 0), side="right") - 1
+        return {"t": hits[:, 0].copy(), "prim_uv": hits[:, 1:3].copy(), "is_valid": valid,
+                "global_prim_index": np.where(valid, gprim, -1),
+                "shape_index": np.where(valid, shape, -1),
+                "prim_index": np.where(valid, gprim - self.primitive_map[np.clip(shape, 0, None)], -1)}
+
+    def ray_test(self, o, d, mint=0.0, maxt=np.inf):
+        om, dm = self.pack_rays(o, d, mint, maxt)
+        return self.intersect_any_raw(om, dm).astype(bool)
+
+    # ---- Integrator::render ---------------------------------------------------------------------
+    def render_accumulate(self, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None):
+        """Adds ``spp`` samples per pixel (sample indices [spp_begin, spp_begin+spp)) to the device film."""
+        spp = self.data.spp if spp is None else int(spp)
+        spp_total = spp_begin + spp if spp_total is None else int(spp_total)
+        st = A.Stats()
+        A.check(A.lib().mtsb_render(self._h, sensor, spp_begin, spp, spp_total, int(seed), C.byref(st)))
+        self.last_stats = st.as_dict()
+        return self.last_stats
+
+    def render(self, sensor=0, spp=None, seed=0):
+        """``Integrator.render`` + ``Film.bitmap()``: clears the film, renders, returns linear RGB (H,W,3) float32."""
+        self.film_clear(sensor)
+        self.render_accumulate(sensor, spp, seed)
+        return self.film_develop(sensor)
+
+    def film_clear(self, sensor=0):
+        A.check(A.lib().mtsb_film_clear(self._h, sensor))
+
+    def _film_shape(self, sensor):
+        s = self.data.sensors[sensor]
+        return s["height"], s["width"]
+
+    def film_xyzaw(self, sensor=0):
+        h, w = self._film_shape(sensor)
+        out = np.empty((h, w, 5), np.float32)
+        A.check(A.lib().mtsb_film_read(self._h, sensor, C.c_void_p(out.ctypes.data), A.MEM_HOST))
+        return out
+
+    def film_accumulate(self, xyzaw, sensor=0):
+        p, mem, keep = _arg(xyzaw, np.float32)
+        A.check(A.lib().mtsb_film_accumulate(self._h, sensor, p, mem))
+
+    def film_develop(self, sensor=0):
+        h, w = self._film_shape(sensor)
+        out = np.empty((h, w, 3), np.float32)
+        A.check(A.lib().mtsb_film_develop(self._h, sensor, C.c_void_p(out.ctypes.data), A.MEM_HOST))
+        return out
+
+    def film_device_buffer(self, sensor=0):
+        """(device pointer, n_floats) of the packed XYZAW film, for NCCL reduction by the caller."""
+        p, n = C.c_void_p(), C.c_uint64()
+        A.check(A.lib().mtsb_film_device_ptr(self._h, sensor, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def film_put(self, pos, values, sensor=0):
+        """``ImageBlock::put(pos, value)`` batched: pos (n,2), values (n,5)."""
+        pos = np.ascontiguousarray(pos, np.float32)
+        values = np.ascontiguousarray(values, np.float32)
+        A.check(A.lib().mtsb_film_put(self._h, sensor, pos.shape[0], C.c_void_p(pos.ctypes.data), C.c_void_p(values.ctypes.data)))
+
+    # ---- parameter updates (traverse()/parameters_changed) ------------------------------------------
+    def update_vertices(self, mesh_id, positions):
+        p, mem, keep = _arg(positions, np.float32)
+        A.check(A.lib().mtsb_scene_update_vertices(self._h, mesh_id, p, mem))
+        if mem == A.MEM_HOST:
+            self.data.meshes[mesh_id].positions = keep.reshape(-1, 3).copy()
+
+    def update_texture(self, tex_id, data):
+        p, mem, keep = _arg(data, np.float32)
+        A.check(A.lib().mtsb_scene_update_texture(self._h, tex_id, p, mem))
+
+    # ---- gradient pass ----------------------------------------------------------------------------
+    def render_grad(self, dL_dimage, sensor=0, spp=None, seed=0, tex_id=-1, mesh_id=-1, spp_begin=0, spp_total=None):
+        spp = self.data.spp if spp is None else int(spp)
+        spp_total = spp_begin + spp if spp_total is None else int(spp_total)
+        pd, mem, k = _arg(dL_dimage, np.float32)
+        gt = gv = None
+        if mem == A.MEM_DEVICE:
+            import torch
+            dev = k.device
+            if tex_id >= 0:
+                t = self.data.textures[tex_id]
+                n = 3 if t["type"] == A.TEX_CONSTANT else t["data"].size
+                gt = torch.zeros(n, dtype=torch.float32, device=dev)
+            if mesh_id >= 0:
+                gv = torch.zeros(self.data.meshes[mesh_id].positions.size, dtype=torch.float32, device=dev)
+            pgt = C.c_void_p(gt.data_ptr()) if gt is not None else None
+            pgv = C.c_void_p(gv.data_ptr()) if gv is not None else None
+        else:
+            if tex_id >= 0:
+                t = self.data.textures[tex_id]
+                gt = np.zeros(3 if t["type"] == A.TEX_CONSTANT else t["data"].size, np.float32)
+            if mesh_id >= 0:
+                gv = np.zeros(self.data.meshes[mesh_id].positions.size, np.float32)
+            pgt = C.c_void_p(gt.ctypes.data) if gt is not None else None
+            pgv = C.c_void_p(gv.ctypes.data) if gv is not None else None
+        st = A.Stats()
+        A.check(A.lib().mtsb_render_grad(self._h, sensor, spp_begin, spp, spp_total, int(seed), pd, tex_id, pgt, mesh_id, pgv,
+                                         mem, C.byref(st)))
+        self.last_stats = st.as_dict()
+        return gt, gv
+
+    # ---- parity hooks -----------------------------------------------------------------------------
+    def sensor_sample_ray(self, pos, sensor=0):
+        pos = np.ascontiguousarray(pos, np.float32)
+        n = pos.shape[0]
+        o, d = np.empty((n, 4), np.float32), np.empty((n, 4), np.float32)
+        A.check(A.lib().mtsb_sensor_sample_ray(self._h, sensor, n, C.c_void_p(pos.ctypes.data), C.c_void_p(o.ctypes.data), C.c_void_p(d.ctypes.data)))
+        return o, d
+
+    def bsdf_sample(self, bsdf_id, wi, uv, sample1, sample2):
+        wi, uv, s1, s2 = (np.ascontiguousarray(x, np.float32) for x in (wi, uv, sample1, sample2))
+        n = wi.shape[0]
+        out = np.empty((n, 9), np.float32)
+        A.check(A.lib().mtsb_bsdf_sample(self._h, bsdf_id, n, *(C.c_void_p(x.ctypes.data) for x in (wi, uv, s1, s2, out))))
+        return out
+
+    def bsdf_eval_pdf(self, bsdf_id, wi, uv, wo):
+        wi, uv, wo = (np.ascontiguousarray(x, np.float32) for x in (wi, uv, wo))
+        n = wi.shape[0]
+        ev, pdf = np.empty((n, 3), np.float32), np.empty((n,), np.float32)
+        A.check(A.lib().mtsb_bsdf_eval_pdf(self._h, bsdf_id, n, *(C.c_void_p(x.ctypes.data) for x in (wi, uv, wo, ev, pdf))))
+        return ev, pdf
+
+    def sample_emitter_direction(self, ref_p, sample2):
+        p, s2 = np.ascontiguousarray(ref_p, np.float32), np.ascontiguousarray(sample2, np.float32)
+        n = p.shape[0]
+        out = np.empty((n, 11), np.float32)
+        A.check(A.lib().mtsb_sample_emitter_direction(self._h, n, *(C.c_void_p(x.ctypes.data) for x in (p, s2, out))))
+        return out
+
+
+def pcg32_floats(initstate, initseq, n_draws, device=0):
+    s = np.ascontiguousarray(initstate, np.uint64)
+    q = np.ascontiguousarray(initseq, np.uint64)
+    out = np.empty((s.size, n_draws), np.float32)
+    A.check(A.lib().mtsb_pcg32_floats(_context(device), s.size, C.c_void_p(s.ctypes.data), C.c_void_p(q.ctypes.data), n_draws, C.c_void_p(out.ctypes.data)))
+    return out
+
+
+def sampler_seed(n, seed, device=0):
+    st, inc = np.empty(n, np.uint64), np.empty(n, np.uint64)
+    A.check(A.lib().mtsb_sampler_seed(_context(device), n, int(seed), C.c_void_p(st.ctypes.data), C.c_void_p(inc.ctypes.data)))
+    return st, inc

@@ -1,0 +1,265 @@
+"""Host-side flattened scene description (numpy) and its conversion to ``mtsb_scene_desc``.
+
+This is the Python mirror of what ``Scene::Scene`` collects (src/librender/scene.cpp:22-99):
+shapes (triangle meshes), their BSDFs / area emitters, environment emitter, sensors and
+the integrator properties.  The same object feeds the CUDA library (product) and, in the
+tests only, the CPU oracle.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _abi as A
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a, ty):
+    return a.ctypes.data_as(ty) if a is not None else ty()
+
+
+def perspective_sample_to_camera(x_fov_deg, near, far, aspect):
+    """``PerspectiveCamera::update_camera_transforms`` (src/sensors/perspective.cpp:106-133), no crop window:
+    inverse of scale(-.5,-.5*aspect,1) * translate(-1,-1/aspect,0) * perspective(fov,near,far)
+    (``Transform::perspective``, include/mitsuba/core/transform.h:203-220)."""
+    tan = math.tan(math.radians(x_fov_deg * 0.5))
+    inv_persp = np.array([[tan, 0, 0, 0], [0, tan, 0, 0], [0, 0, 0, 1],
+                          [0, 0, (near - far) / (far * near), 1.0 / near]], dtype=np.float64)
+    inv_trans = np.array([[1, 0, 0, 1], [0, 1, 0, 1.0 / aspect], [0, 0, 1, 0], [0, 0, 0, 1]], dtype=np.float64)
+    inv_scale = np.diag([-2.0, -2.0 / aspect, 1.0, 1.0])
+    return (inv_persp @ inv_trans @ inv_scale).astype(np.float32)
+
+
+def parse_fov(fov=None, fov_axis="x", focal_length="50mm", aspect=1.0):
+    """``parse_fov`` (src/librender/sensor.cpp:119-173) -> horizontal fov in degrees."""
+    if fov is not None:
+        fov_axis = fov_axis.lower()
+        if fov_axis == "smaller":
+            fov_axis = "y" if aspect > 1 else "x"
+        elif fov_axis == "larger":
+            fov_axis = "x" if aspect > 1 else "y"
+    else:
+        f = focal_length[:-2] if str(focal_length).endswith("mm") else focal_length
+        value = float(f)
+        fov = 2.0 * math.degrees(math.atan(math.sqrt(36 * 36 + 24 * 24) / (2.0 * value)))
+        fov_axis = "diagonal"
+    if fov_axis == "x":
+        result = fov
+    elif fov_axis == "y":
+        result = math.degrees(2.0 * math.atan(math.tan(0.5 * math.radians(fov)) * aspect))
+    elif fov_axis == "diagonal":
+        diagonal = 2.0 * math.tan(0.5 * math.radians(fov))
+        width = diagonal / math.sqrt(1.0 + 1.0 / (aspect * aspect))
+        result = math.degrees(2.0 * math.atan(width * 0.5))
+    else:
+        raise ValueError("The 'fov_axis' parameter must be set to one of 'smaller', 'larger', 'diagonal', 'x', or 'y'!")
+    if result <= 0.0 or result >= 180.0:
+        raise ValueError("The horizontal field of view must be in the range [0, 180]!")
+    return result
+
+
+def look_at(origin, target, up):
+    """``Transform::look_at`` (include/mitsuba/core/transform.h): camera-to-world, +z forward, left-handed image x."""
+    origin, target, up = (np.asarray(v, dtype=np.float64) for v in (origin, target, up))
+    d = target - origin
+    d /= np.linalg.norm(d)
+    left = np.cross(up, d)
+    left /= np.linalg.norm(left)
+    new_up = np.cross(d, left)
+    m = np.eye(4)
+    m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = left, new_up, d, origin
+    return m
+
+
+class Mesh:
+    def __init__(self, positions, faces, normals=None, texcoords=None, bsdf=0, emitter=-1, name="mesh"):
+        self.positions = _f32(positions).reshape(-1, 3)
+        self.faces = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
+        self.normals = _f32(normals).reshape(-1, 3) if normals is not None else None
+        self.texcoords = _f32(texcoords).reshape(-1, 2) if texcoords is not None else None
+        self.bsdf, self.emitter, self.name = int(bsdf), int(emitter), name
+
+
+class SceneData:
+    """Flattened scene.  Lists of plain dicts + :class:`Mesh`; ``to_desc()`` builds the C struct."""
+
+    def __init__(self):
+        self.meshes, self.bsdfs, self.textures, self.emitters, self.sensors = [], [], [], [], []
+        self.max_depth, self.rr_depth = -1, 5
+        self.spp = 4
+
+    # ---- builders -------------------------------------------------------------------------
+    def add_texture_rgb(self, rgb):
+        rgb = [float(rgb)] * 3 if np.isscalar(rgb) else [float(x) for x in rgb]
+        self.textures.append({"type": A.TEX_CONSTANT, "value": rgb})
+        return len(self.textures) - 1
+
+    def add_texture_bitmap(self, data, to_uv=None):
+        data = _f32(data)
+        if data.ndim == 2:
+            data = data[:, :, None]
+        assert data.ndim == 3 and data.shape[2] in (1, 3)
+        self.textures.append({"type": A.TEX_BITMAP, "data": np.ascontiguousarray(data),
+                              "to_uv": _f32(np.eye(3) if to_uv is None else to_uv).reshape(9)})
+        return len(self.textures) - 1
+
+    def add_diffuse(self, reflectance=0.5):
+        tex = reflectance if isinstance(reflectance, int) and not isinstance(reflectance, bool) else self.add_texture_rgb(reflectance)
+        self.bsdfs.append({"type": A.BSDF_DIFFUSE, "reflectance_tex": tex})
+        return len(self.bsdfs) - 1
+
+    def add_roughconductor(self, eta, k, alpha=0.1, alpha_v=None, distribution="beckmann", sample_visible=True,
+                           specular_reflectance=None):
+        self.bsdfs.append({"type": A.BSDF_ROUGHCONDUCTOR, "eta_tex": self.add_texture_rgb(eta),
+                           "k_tex": self.add_texture_rgb(k), "alpha_u": float(alpha),
+                           "alpha_v": float(alpha if alpha_v is None else alpha_v),
+                           "distribution": A.MF_GGX if distribution.lower() == "ggx" else A.MF_BECKMANN,
+                           "sample_visible": int(bool(sample_visible)),
+                           "specular_reflectance_tex": -1 if specular_reflectance is None else self.add_texture_rgb(specular_reflectance)})
+        return len(self.bsdfs) - 1
+
+    def add_dielectric(self, int_ior=1.5046, ext_ior=1.000277, specular_reflectance=None, specular_transmittance=None):
+        self.bsdfs.append({"type": A.BSDF_DIELECTRIC, "eta": float(int_ior) / float(ext_ior),
+                           "specular_reflectance_tex": -1 if specular_reflectance is None else self.add_texture_rgb(specular_reflectance),
+                           "specular_transmittance_tex": -1 if specular_transmittance is None else self.add_texture_rgb(specular_transmittance)})
+        return len(self.bsdfs) - 1
+
+    def add_mesh(self, mesh, area_radiance=None):
+        self.meshes.append(mesh)
+        mid = len(self.meshes) - 1
+        if area_radiance is not None:
+            self.emitters.append({"type": A.EMITTER_AREA, "radiance": [float(x) for x in area_radiance], "mesh_id": mid})
+            mesh.emitter = len(self.emitters) - 1
+        return mid
+
+    def add_envmap(self, rgba, to_world=None, scale=1.0):
+        rgba = _f32(rgba)
+        if rgba.shape[2] == 3:
+            rgba = np.concatenate([rgba, np.ones(rgba.shape[:2] + (1,), np.float32)], axis=2)
+        self.emitters.append({"type": A.EMITTER_ENVMAP, "rgba": np.ascontiguousarray(rgba),
+                              "to_world": _f32(np.eye(4) if to_world is None else to_world).reshape(16), "scale": float(scale)})
+        return len(self.emitters) - 1
+
+    def add_perspective(self, to_world, fov_x, near, far, width, height, rfilter="gaussian", stddev=0.5, radius=None):
+        kinds = {"box": A.RFILTER_BOX, "tent": A.RFILTER_TENT, "gaussian": A.RFILTER_GAUSSIAN}
+        if radius is None:
+            radius = {"box": 0.5, "tent": 1.0, "gaussian": 4.0 * stddev}[rfilter]
+        self.sensors.append({"to_world": _f32(to_world).reshape(16),
+                             "sample_to_camera": perspective_sample_to_camera(fov_x, near, far, width / height).reshape(16),
+                             "near": float(near), "far": float(far), "width": int(width), "height": int(height),
+                             "rfilter": kinds[rfilter], "radius": float(radius), "stddev": float(stddev), "fov_x": float(fov_x)})
+        return len(self.sensors) - 1
+
+    # ---- C struct -------------------------------------------------------------------------
+    def to_desc(self):
+        """Returns (SceneDesc, keepalive) -- keepalive must outlive the call that consumes the desc."""
+        keep = []
+        md = (A.MeshDesc * max(1, len(self.meshes)))()
+        for i, m in enumerate(self.meshes):
+            keep.append(m)
+            md[i].faces = _ptr(m.faces, A.c_u32_p)
+            md[i].positions = _ptr(m.positions, A.c_float_p)
+            md[i].normals = _ptr(m.normals, A.c_float_p)
+            md[i].texcoords = _ptr(m.texcoords, A.c_float_p)
+            md[i].face_count, md[i].vertex_count = m.faces.shape[0], m.positions.shape[0]
+            md[i].bsdf_id, md[i].emitter_id = m.bsdf, m.emitter
+        bd = (A.BsdfDesc * max(1, len(self.bsdfs)))()
+        for i, b in enumerate(self.bsdfs):
+            bd[i].type = b["type"]
+            for key in ("reflectance_tex", "eta_tex", "k_tex", "specular_reflectance_tex", "specular_transmittance_tex"):
+                setattr(bd[i], key, b.get(key, -1))
+            bd[i].alpha_u, bd[i].alpha_v = b.get("alpha_u", 0.1), b.get("alpha_v", 0.1)
+            bd[i].distribution, bd[i].sample_visible = b.get("distribution", 0), b.get("sample_visible", 1)
+            bd[i].eta = b.get("eta", 1.0)
+        td = (A.TextureDesc * max(1, len(self.textures)))()
+        for i, t in enumerate(self.textures):
+            td[i].type = t["type"]
+            if t["type"] == A.TEX_CONSTANT:
+                td[i].value = (C.c_float * 3)(*t["value"])
+            else:
+                d = t["data"]
+                keep.append(d)
+                td[i].height, td[i].width, td[i].channels = d.shape
+                td[i].data = _ptr(d, A.c_float_p)
+                td[i].to_uv = (C.c_float * 9)(*t["to_uv"])
+        ed = (A.EmitterDesc * max(1, len(self.emitters)))()
+        for i, e in enumerate(self.emitters):
+            ed[i].type = e["type"]
+            if e["type"] == A.EMITTER_AREA:
+                ed[i].radiance = (C.c_float * 3)(*e["radiance"])
+                ed[i].mesh_id = e["mesh_id"]
+            else:
+                keep.append(e["rgba"])
+                ed[i].height, ed[i].width = e["rgba"].shape[:2]
+                ed[i].rgba = _ptr(e["rgba"], A.c_float_p)
+                ed[i].to_world = (C.c_float * 16)(*e["to_world"])
+                ed[i].scale = e["scale"]
+        sd = (A.SensorDesc * max(1, len(self.sensors)))()
+        for i, s in enumerate(self.sensors):
+            sd[i].to_world = (C.c_float * 16)(*s["to_world"])
+            sd[i].sample_to_camera = (C.c_float * 16)(*s["sample_to_camera"])
+            sd[i].near_clip, sd[i].far_clip = s["near"], s["far"]
+            sd[i].film_width, sd[i].film_height = s["width"], s["height"]
+            sd[i].rfilter, sd[i].rfilter_radius, sd[i].rfilter_stddev = s["rfilter"], s["radius"], s["stddev"]
+        desc = A.SceneDesc()
+        desc.n_meshes, desc.n_bsdfs, desc.n_textures = len(self.meshes), len(self.bsdfs), len(self.textures)
+        desc.n_emitters, desc.n_sensors = len(self.emitters), len(self.sensors)
+        desc.meshes, desc.bsdfs, desc.textures, desc.emitters, desc.sensors = md, bd, td, ed, sd
+        desc.integrator.max_depth, desc.integrator.rr_depth = self.max_depth, self.rr_depth
+        keep += [md, bd, td, ed, sd]
+        return desc, keep
+
+    # ---- (de)serialisation for fixtures -------------------------------------------------------
+    def save_npz(self, path):
+        import json
+        arrays, meta = {}, {"max_depth": self.max_depth, "rr_depth": self.rr_depth, "spp": self.spp, "meshes": [],
+                            "bsdfs": self.bsdfs, "textures": [], "emitters": [], "sensors": []}
+        for i, m in enumerate(self.meshes):
+            arrays[f"m{i}_p"], arrays[f"m{i}_f"] = m.positions, m.faces
+            if m.normals is not None:
+                arrays[f"m{i}_n"] = m.normals
+            if m.texcoords is not None:
+                arrays[f"m{i}_t"] = m.texcoords
+            meta["meshes"].append({"bsdf": m.bsdf, "emitter": m.emitter, "name": m.name})
+        for i, t in enumerate(self.textures):
+            if t["type"] == A.TEX_BITMAP:
+                arrays[f"t{i}_d"], arrays[f"t{i}_uv"] = t["data"], t["to_uv"]
+                meta["textures"].append({"type": t["type"]})
+            else:
+                meta["textures"].append(t)
+        for i, e in enumerate(self.emitters):
+            if e["type"] == A.EMITTER_ENVMAP:
+                arrays[f"e{i}_d"], arrays[f"e{i}_w"] = e["rgba"], e["to_world"]
+                meta["emitters"].append({"type": e["type"], "scale": e["scale"]})
+            else:
+                meta["emitters"].append(e)
+        for i, s in enumerate(self.sensors):
+            arrays[f"s{i}_w"], arrays[f"s{i}_c"] = s["to_world"], s["sample_to_camera"]
+            meta["sensors"].append({k: v for k, v in s.items() if k not in ("to_world", "sample_to_camera")})
+        arrays["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+        np.savez_compressed(path, **arrays)
+
+    @staticmethod
+    def load_npz(path):
+        import json
+        z = np.load(path)
+        meta = json.loads(bytes(z["meta"]).decode())
+        sd = SceneData()
+        sd.max_depth, sd.rr_depth, sd.spp = meta["max_depth"], meta["rr_depth"], meta["spp"]
+        sd.bsdfs = meta["bsdfs"]
+        for i, m in enumerate(meta["meshes"]):
+            sd.meshes.append(Mesh(z[f"m{i}_p"], z[f"m{i}_f"], z[f"m{i}_n"] if f"m{i}_n" in z else None,
+                                  z[f"m{i}_t"] if f"m{i}_t" in z else None, m["bsdf"], m["emitter"], m["name"]))
+        for i, t in enumerate(meta["textures"]):
+            sd.textures.append({"type": t["type"], "data": _f32(z[f"t{i}_d"]), "to_uv": _f32(z[f"t{i}_uv"])} if t["type"] == A.TEX_BITMAP else t)
+        for i, e in enumerate(meta["emitters"]):
+            sd.emitters.append({"type": e["type"], "rgba": _f32(z[f"e{i}_d"]), "to_world": _f32(z[f"e{i}_w"]), "scale": e["scale"]}
+                               if e["type"] == A.EMITTER_ENVMAP else e)
+        for i, s in enumerate(meta["sensors"]):
+            s = dict(s)
+            s["to_world"], s["sample_to_camera"] = _f32(z[f"s{i}_w"]), _f32(z[f"s{i}_c"])
+            sd.sensors.append(s)
+        return sd

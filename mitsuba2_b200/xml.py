@@ -1,0 +1,322 @@
+"""Mitsuba 2 XML scene loading for the subset of the scene format the hot path covers.
+
+Mirror of ``xml::load_file`` / ``load_string`` (include/mitsuba/core/xml.h:17-29, src/libcore/xml.cpp): ``<default>``,
+``$param`` substitution (``-Dkey=value``), ``<include>``, ``<ref>``, ``<transform>`` (translate/rotate/scale/lookat/matrix),
+typed properties, and the plugins named by the north star: shapes obj/ply (+ rectangle as two triangles), BSDFs
+diffuse/roughconductor/dielectric (``twosided`` unwraps to its child: both are front-side only here), emitters
+area/envmap, sensor perspective, film hdrfilm, rfilters box/tent/gaussian, sampler independent, integrator path.
+Unknown plugins raise, like ``PluginManager`` does.
+"""
+import math
+import os
+import re
+import xml.etree.ElementTree as ET
+
+import numpy as np
+
+from . import mesh as M
+from .scenedata import SceneData, look_at, parse_fov
+
+# conductor IORs pre-integrated to linear sRGB (what complex_ior_from_file yields in rgb variants for data/ior/*.spd;
+# values from integrating the reference's .spd tables against the CIE curves -- approximate)
+CONDUCTORS_RGB = {
+    "cu": ((0.200438, 0.924033, 1.102212), (3.912949, 2.452848, 2.142188)),
+    "au": ((0.143119, 0.374957, 1.442479), (3.983160, 2.385721, 1.603215)),
+    "ag": ((0.155265, 0.116723, 0.138342), (4.828367, 3.122501, 2.147036)),
+    "al": ((1.657460, 0.880369, 0.521229), (9.223869, 6.269523, 4.837001)),
+    "none": ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0)),
+}
+IOR_NAMES = {"vacuum": 1.0, "air": 1.000277, "water": 1.3330, "bk7": 1.5046, "diamond": 2.419, "acrylic glass": 1.49,
+             "polypropylene": 1.49, "pyrex": 1.470, "sodium chloride": 1.544, "amber": 1.55, "pet": 1.5750}
+
+
+def _natural_key(s):
+    return [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", s)]
+
+
+def _floats(s):
+    return [float(x) for x in re.split(r"[\s,]+", s.strip()) if x]
+
+
+def load_image(path):
+    """float32 linear RGB (H,W,3) from EXR/HDR/PFM (linear) or PNG/JPG (sRGB -> linear)."""
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    import cv2
+    im = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+    if im is None:
+        raise IOError(f"could not read image {path}")
+    if im.ndim == 2:
+        im = im[:, :, None].repeat(3, axis=2)
+    im = im[:, :, :3][:, :, ::-1]
+    if im.dtype == np.uint8 or im.dtype == np.uint16:
+        v = im.astype(np.float32) / (255.0 if im.dtype == np.uint8 else 65535.0)
+        im = np.where(v <= 0.04045, v / 12.92, ((v + 0.055) / 1.055) ** 2.4)
+    return np.ascontiguousarray(im, dtype=np.float32)
+
+
+class _Loader:
+    def __init__(self, params, base_dir):
+        self.params = dict(params)
+        self.base_dir = base_dir
+        self.named = {}          # id -> element (bsdf / emitter / texture / shape definitions)
+        self.sd = SceneData()
+        self.bsdf_cache = {}     # id(element) -> bsdf index
+        self.children = []       # (sort key, element) of the scene's children
+        self.basedirs, self.keep = {}, []
+
+    # -- substitution / traversal ----------------------------------------------------------------
+    def subst(self, s):
+        def rep(m):
+            k = m.group(1)
+            if k not in self.params:
+                raise ValueError(f"undefined parameter ${k}")
+            return str(self.params[k])
+        return re.sub(r"\$(\w+)", rep, s) if s and "$" in s else s
+
+    def resolve(self, el, filename):
+        """FileResolver semantics: the including file's directory first, then the top-level scene directory."""
+        for d in (self.basedirs.get(id(el), self.base_dir), self.base_dir):
+            cand = os.path.join(d, filename)
+            if os.path.exists(cand):
+                return cand
+        return os.path.join(self.base_dir, filename)
+
+    def attr(self, el, name, default=None):
+        v = el.get(name)
+        return self.subst(v) if v is not None else default
+
+    def expand(self, root, base_dir, depth=0):
+        """Resolve <default> and <include> in place (include depth limit 15, xml.h:8)."""
+        if depth > 15:
+            raise ValueError("exceeded <include> recursion limit of 15")
+        out = []
+        for el in list(root):
+            if el.tag == "default":
+                self.params.setdefault(el.get("name"), self.subst(el.get("value")))
+            elif el.tag == "include":
+                path = os.path.join(base_dir, self.attr(el, "filename"))
+                sub = ET.parse(path).getroot()
+                out.extend(self.expand(sub, os.path.dirname(path), depth + 1))
+            else:
+                for d in el.iter():
+                    self.basedirs.setdefault(id(d), base_dir)
+                self.keep.append(el)
+                out.append(el)
+        return out
+
+    # -- typed properties ---------------------------------------------------------------------------
+    def props(self, el):
+        p = {}
+        for c in el:
+            n = c.get("name")
+            if c.tag in ("float",):
+                p[n] = float(self.attr(c, "value"))
+            elif c.tag == "integer":
+                p[n] = int(self.attr(c, "value"))
+            elif c.tag == "boolean":
+                p[n] = self.attr(c, "value").lower() == "true"
+            elif c.tag == "string":
+                p[n] = self.attr(c, "value")
+            elif c.tag == "rgb":
+                v = _floats(self.attr(c, "value"))
+                p[n] = ("rgb", v * 3 if len(v) == 1 else v)
+            elif c.tag == "spectrum":
+                v = self.attr(c, "value")
+                if ":" in v:
+                    raise NotImplementedError("wavelength:value <spectrum> needs the spectral variant")
+                f = _floats(v)
+                p[n] = ("rgb", f * 3 if len(f) == 1 else f)
+            elif c.tag in ("point", "vector"):
+                if c.get("value") is not None:
+                    p[n] = _floats(self.attr(c, "value"))
+                else:
+                    p[n] = [float(self.attr(c, k, "0")) for k in "xyz"]
+            elif c.tag == "transform":
+                p[n] = self.transform(c)
+            elif c.tag == "texture" and n:
+                p[n] = ("texture", c)
+        return p
+
+    def transform(self, el):
+        m = np.eye(4)
+        for c in el:
+            if c.tag == "translate":
+                v = _floats(self.attr(c, "value")) if c.get("value") else [float(self.attr(c, k, "0")) for k in "xyz"]
+                t = np.eye(4); t[:3, 3] = v
+            elif c.tag == "scale":
+                if c.get("value"):
+                    v = _floats(self.attr(c, "value")); v = v * 3 if len(v) == 1 else v
+                else:
+                    v = [float(self.attr(c, k, "1")) for k in "xyz"]
+                t = np.diag(list(v) + [1.0])
+            elif c.tag == "rotate":
+                axis = _floats(self.attr(c, "value")) if c.get("value") else [float(self.attr(c, k, "0")) for k in "xyz"]
+                a = np.asarray(axis, dtype=np.float64); a /= np.linalg.norm(a)
+                ang = math.radians(float(self.attr(c, "angle")))
+                s, co = math.sin(ang), math.cos(ang)
+                K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+                t = np.eye(4); t[:3, :3] = co * np.eye(3) + s * K + (1 - co) * np.outer(a, a)
+            elif c.tag == "lookat":
+                t = look_at(_floats(self.attr(c, "origin")), _floats(self.attr(c, "target")), _floats(self.attr(c, "up", "0,1,0")))
+            elif c.tag == "matrix":
+                v = _floats(self.attr(c, "value"))
+                t = np.asarray(v, dtype=np.float64).reshape(4, 4) if len(v) == 16 else np.block([[np.asarray(v).reshape(3, 3), np.zeros((3, 1))], [np.zeros((1, 3)), np.ones((1, 1))]])
+            else:
+                raise ValueError(f"unknown transform element <{c.tag}>")
+            m = t @ m
+        return m
+
+    # -- plugins ----------------------------------------------------------------------------------------
+    def texture_index(self, value, default):
+        if value is None:
+            return self.sd.add_texture_rgb(default)
+        kind, v = value
+        if kind == "rgb":
+            return self.sd.add_texture_rgb(v)
+        el = v
+        ty = self.attr(el, "type")
+        if ty != "bitmap":
+            raise NotImplementedError(f"texture plugin '{ty}' is outside the hot-path scope")
+        p = self.props(el)
+        img = load_image(self.resolve(el, p["filename"]))
+        return self.sd.add_texture_bitmap(img, p.get("to_uv", np.eye(4))[:3, :3] if "to_uv" in p else None)
+
+    def bsdf_index(self, el):
+        if el.tag == "ref":
+            el = self.named[self.attr(el, "id")]
+        if id(el) in self.bsdf_cache:
+            return self.bsdf_cache[id(el)]
+        ty = self.attr(el, "type")
+        p = self.props(el)
+        if ty == "twosided":
+            inner = [c for c in el if c.tag in ("bsdf", "ref")]
+            idx = self.bsdf_index(inner[0])
+        elif ty == "diffuse":
+            idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
+        elif ty == "roughconductor":
+            if "eta" in p or "k" in p:
+                eta, k = p.get("eta", ("rgb", [0.0] * 3))[1], p.get("k", ("rgb", [1.0] * 3))[1]
+            else:
+                eta, k = CONDUCTORS_RGB[p.get("material", "Cu").lower()]
+            alpha = p.get("alpha", 0.1)
+            idx = self.sd.add_roughconductor(eta, k, p.get("alpha_u", alpha), p.get("alpha_v", alpha), p.get("distribution", "beckmann"),
+                                             p.get("sample_visible", True),
+                                             p["specular_reflectance"][1] if "specular_reflectance" in p else None)
+        elif ty == "dielectric":
+            def ior(v, d):
+                v = p.get(v, d)
+                return IOR_NAMES[v.lower()] if isinstance(v, str) else float(v)
+            idx = self.sd.add_dielectric(ior("int_ior", "bk7"), ior("ext_ior", "air"),
+                                         p["specular_reflectance"][1] if "specular_reflectance" in p else None,
+                                         p["specular_transmittance"][1] if "specular_transmittance" in p else None)
+        else:
+            raise NotImplementedError(f"BSDF plugin '{ty}' is outside the hot-path scope (diffuse, roughconductor, dielectric)")
+        self.bsdf_cache[id(el)] = idx
+        return idx
+
+    def shape(self, el):
+        ty = self.attr(el, "type")
+        p = self.props(el)
+        to_world = p.get("to_world")
+        if ty == "obj":
+            m = M.load_obj(self.resolve(el, p["filename"]), to_world, p.get("face_normals", False),
+                           p.get("flip_tex_coords", True), p.get("flip_normals", False))
+        elif ty == "ply":
+            m = M.load_ply(self.resolve(el, p["filename"]), to_world, p.get("face_normals", False), p.get("flip_normals", False))
+        elif ty == "rectangle":
+            q = M.quad([-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0])
+            q.positions = M._apply(to_world, q.positions)
+            m = q
+        else:
+            raise NotImplementedError(f"shape plugin '{ty}' is outside the hot-path scope (triangle meshes)")
+        bsdf = None
+        radiance = None
+        for c in el:
+            target = self.named[self.attr(c, "id")] if c.tag == "ref" else c
+            if target.tag == "bsdf":
+                bsdf = self.bsdf_index(target)
+            elif target.tag == "emitter":
+                if self.attr(target, "type") != "area":
+                    raise ValueError("only area emitters can be attached to shapes")
+                rad = self.props(target).get("radiance", ("rgb", [1.0] * 3))
+                if rad[0] != "rgb":
+                    raise NotImplementedError("textured area-light radiance")
+                radiance = rad[1]
+        m.bsdf = bsdf if bsdf is not None else self.sd.add_diffuse(0.5)     # shape.cpp:75-76
+        self.sd.add_mesh(m, radiance)
+
+    def emitter(self, el):
+        ty = self.attr(el, "type")
+        if ty == "area":
+            return          # instantiated by the shape that references it
+        if ty != "envmap":
+            raise NotImplementedError(f"emitter plugin '{ty}' is outside the hot-path scope (area, envmap)")
+        p = self.props(el)
+        img = load_image(self.resolve(el, p["filename"]))
+        self.sd.add_envmap(img, p.get("to_world"), p.get("scale", 1.0))
+
+    def sensor(self, el):
+        if self.attr(el, "type") != "perspective":
+            raise NotImplementedError("only the perspective sensor is in scope")
+        p = self.props(el)
+        film = el.find("film")
+        fp = self.props(film) if film is not None else {}
+        w, h = fp.get("width", 768), fp.get("height", 576)            # film.cpp:11-14
+        rf = film.find("rfilter") if film is not None else None
+        rtype = self.attr(rf, "type") if rf is not None else "gaussian"    # film.cpp:46-50
+        rp = self.props(rf) if rf is not None else {}
+        if rtype not in ("box", "tent", "gaussian"):
+            raise NotImplementedError(f"rfilter '{rtype}' not yet supported")
+        sampler = el.find("sampler")
+        if sampler is not None:
+            self.sd.spp = self.props(sampler).get("sample_count", 4)
+        fov = parse_fov(p.get("fov"), p.get("fov_axis", "x"), p.get("focal_length", "50mm"), w / h)
+        self.sd.add_perspective(p.get("to_world", np.eye(4)), fov, p.get("near_clip", 1e-2), p.get("far_clip", 1e4), w, h,
+                                rtype, rp.get("stddev", 0.5), rp.get("radius"))
+
+    def load(self, root, base_dir):
+        items = self.expand(root, base_dir)
+        unnamed = 0
+        for el in items:
+            if el.get("id") is not None:
+                self.named[self.attr(el, "id")] = el
+                key = self.attr(el, "id")
+            else:
+                key = f"_unnamed_{unnamed}"
+                unnamed += 1
+            self.children.append((key, el))
+        # Properties::objects() order: std::map with numeric-suffix-aware comparison (properties.cpp:41-64)
+        self.children.sort(key=lambda kv: _natural_key(kv[0]))
+        has_integrator = False
+        for _, el in self.children:
+            if el.tag == "shape":
+                self.shape(el)
+            elif el.tag == "emitter":
+                self.emitter(el)
+            elif el.tag == "sensor":
+                self.sensor(el)
+            elif el.tag == "integrator":
+                ty = self.attr(el, "type")
+                if ty != "path":
+                    raise NotImplementedError(f"integrator '{ty}' is outside the hot-path scope (path)")
+                p = self.props(el)
+                self.sd.max_depth, self.sd.rr_depth = p.get("max_depth", -1), p.get("rr_depth", 5)
+                has_integrator = True
+            elif el.tag in ("bsdf", "texture"):
+                pass
+            else:
+                raise ValueError(f"unsupported scene element <{el.tag}>")
+        if not has_integrator:
+            self.sd.max_depth, self.sd.rr_depth = -1, 5           # scene.cpp:58-89 default `path`
+        return self.sd
+
+
+def load_file(path, **params):
+    """``mitsuba.core.xml.load_file(path, **kwargs)`` -> :class:`SceneData` (host description)."""
+    root = ET.parse(path).getroot()
+    return _Loader(params, os.path.dirname(os.path.abspath(path))).load(root, os.path.dirname(os.path.abspath(path)))
+
+
+def load_string(string, base_dir=".", **params):
+    root = ET.fromstring(string)
+    return _Loader(params, base_dir).load(root, base_dir)
