@@ -143,6 +143,9 @@ int mtsb_ctx_create(int device, mtsb_ctx **out);
 int mtsb_ctx_destroy(mtsb_ctx *ctx);
 /* `Integrator::cancel()` (include/mitsuba/render/integrator.h:51): async-signal-safe flag */
 int mtsb_cancel(mtsb_ctx *ctx);
+/* per-stage CUDA-event timing (the reference's SIGPROF phase profiler, src/libcore/profiler.cpp, re-stated as
+ * event pairs around every launch on the launching stream); fills mtsb_stats.ms_{raygen,closest,shade,any,film} */
+int mtsb_set_profiling(mtsb_ctx *ctx, int on);
 
 /* `Scene::Scene` + `accel_init_*` (scene.cpp:22-99, scene_native.inl:3-10): copies everything, builds the BVH on the GPU */
 int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *desc, mtsb_scene **out);

@@ -81,6 +81,7 @@ SYMBOLS = [
     ("mtsb_ctx_create", C.c_int, [C.c_int, C.POINTER(vp)]),
     ("mtsb_ctx_destroy", C.c_int, [vp]),
     ("mtsb_cancel", C.c_int, [vp]),
+    ("mtsb_set_profiling", C.c_int, [vp, C.c_int]),
     ("mtsb_scene_create", C.c_int, [vp, C.POINTER(SceneDesc), C.POINTER(vp)]),
     ("mtsb_scene_destroy", C.c_int, [vp]),
     ("mtsb_scene_stats", C.c_int, [vp, C.POINTER(Stats)]),

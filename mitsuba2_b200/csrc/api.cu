@@ -39,7 +39,28 @@ template <typename T> struct DevBuf {
 
 struct mtsb_ctx {
     int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
+    int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
+    std::vector<cudaEvent_t> pool;           // event pairs, grown on demand
+    std::vector<int> pool_stage; size_t pool_used = 0;
 };
+// stage ids for the profiling pool
+enum { ST_RAYGEN = 0, ST_CLOSEST = 1, ST_SHADE = 2, ST_ANY = 3, ST_FILM = 4, ST_COUNT = 5 };
+struct StageTimer {      // records an event pair around one launch when profiling is on
+    mtsb_ctx *c; bool on;
+    StageTimer(mtsb_ctx *ctx, int stage) : c(ctx), on(ctx->profiling != 0) {
+        if (!on) return;
+        if (c->pool_used + 2 > c->pool.size()) { for (int k = 0; k < 2; ++k) { cudaEvent_t e; cudaEventCreate(&e); c->pool.push_back(e); } c->pool_stage.resize(c->pool.size() / 2); }
+        c->pool_stage[c->pool_used / 2] = stage;
+        cudaEventRecord(c->pool[c->pool_used], c->stream);
+    }
+    ~StageTimer() { if (on) { cudaEventRecord(c->pool[c->pool_used + 1], c->stream); c->pool_used += 2; } }
+};
+static void collect_stage_times(mtsb_ctx *c, mtsb_stats *st) {   // call after the stream is synchronised
+    float acc[ST_COUNT] = { 0, 0, 0, 0, 0 };
+    for (size_t i = 0; i + 1 < c->pool_used; i += 2) { float ms = 0.f; cudaEventElapsedTime(&ms, c->pool[i], c->pool[i + 1]); acc[c->pool_stage[i / 2]] += ms; }
+    c->pool_used = 0;
+    if (st) { st->ms_raygen = acc[ST_RAYGEN]; st->ms_closest = acc[ST_CLOSEST]; st->ms_shade = acc[ST_SHADE]; st->ms_any = acc[ST_ANY]; st->ms_film = acc[ST_FILM]; }
+}
 
 struct SensorHost { SensorDev dev; DevBuf<float4> xyza; DevBuf<float> w; DevBuf<float> packed; };
 
@@ -93,6 +114,7 @@ extern "C" int mtsb_ctx_destroy(mtsb_ctx *c) {
     return MTSB_OK;
 }
 extern "C" int mtsb_cancel(mtsb_ctx *c) { if (c) c->cancel = 1; return MTSB_OK; }
+extern "C" int mtsb_set_profiling(mtsb_ctx *c, int on) { if (!c) return fail(MTSB_E_INVALID, "null context"); c->profiling = on; return MTSB_OK; }
 
 static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) / kBlock); }
 
@@ -456,14 +478,14 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
         b.seed = seed; b.result = s->result.p;
         CU(cudaMemsetAsync(s->counters.p, 0, 2048 * sizeof(uint32_t), st));
         int cur = 0;
-        k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); launches++;
+        { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
         for (int depth = 1; depth <= max_iter; ++depth) {
             PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
-            k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr);
-            k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth);
+            { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr); }
+            { StageTimer t(s->ctx, ST_SHADE); k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth); }
             launches += 2;
             if (depth < s->dev.max_depth) {
-                k_shadow<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p);
+                { StageTimer t(s->ctx, ST_ANY); k_shadow<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p); }
                 launches++;
             }
             cur ^= 1;
@@ -474,7 +496,7 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
                 if (next == 0) break;
             }
         }
-        k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); launches++;
+        { StageTimer t(s->ctx, ST_FILM); k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); } launches++;
     }
     CU(cudaEventRecord(s->ctx->ev1, st));
     unsigned long long hs[4];
@@ -487,6 +509,7 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
     }
+    collect_stage_times(s->ctx, stats);
     return MTSB_OK;
 }
 

@@ -257,7 +257,7 @@ def displaced_sphere(n_theta, n_phi, radius=1.0, center=(0, 0, 0), displace=True
     uv = np.stack([np.broadcast_to(phi / (2 * np.pi), (nt, nphi)), np.broadcast_to(theta / np.pi, (nt, nphi))], axis=2).reshape(-1, 2)
     i, j = np.meshgrid(np.arange(n_theta), np.arange(n_phi), indexing="ij")
     a = (i * nphi + j).ravel(); b = a + 1; c = a + nphi; d = c + 1
-    faces = np.concatenate([np.stack([a, c, b], axis=1), np.stack([b, c, d], axis=1)], axis=0).astype(np.uint32)
+    faces = np.concatenate([np.stack([a, b, c], axis=1), np.stack([b, d, c], axis=1)], axis=0).astype(np.uint32)   # outward normals
     pos = pos.astype(np.float32)
     return Mesh(pos, faces, compute_vertex_normals(pos, faces), uv.astype(np.float32), name="displaced_sphere")
 

@@ -63,6 +63,9 @@ class Scene:
         except Exception:
             pass
 
+    def set_profiling(self, on=True):
+        A.check(A.lib().mtsb_set_profiling(self._ctx, int(bool(on))))
+
     # ---- statistics ---------------------------------------------------------------------------
     def build_stats(self):
         st = A.Stats()

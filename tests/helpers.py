@@ -1,0 +1,316 @@
+"""Test helpers: ctypes bindings of the CPU oracle (oracle/) and of the host simulator (tests/hostsim), plus
+small scene builders.  The oracle is only ever loaded from tests/, __graft_entry__.smoke() and bench.py."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from mitsuba2_b200 import _abi as A                      # noqa: E402
+from mitsuba2_b200.scenedata import SceneData, Mesh, look_at   # noqa: E402
+from mitsuba2_b200 import mesh as M                       # noqa: E402
+
+ORACLE_SO = os.path.join(ROOT, "oracle", "libmts_oracle.so")
+HOSTSIM_SO = os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")
+vp = C.c_void_p
+
+
+def _newer(src_list, target):
+    return not os.path.exists(target) or any(os.path.getmtime(s) > os.path.getmtime(target) for s in src_list)
+
+
+def build_oracle():
+    src = [os.path.join(ROOT, "oracle", f) for f in ("mts_oracle.c", "mts_oracle.h")] + [os.path.join(ROOT, "include", "mtsb200.h")]
+    if _newer(src, ORACLE_SO):
+        subprocess.check_call(["gcc", "-O2", "-std=c99", "-fopenmp", "-fPIC", "-shared", "-o", ORACLE_SO, src[0], "-lm"])
+    return ORACLE_SO
+
+
+def build_hostsim():
+    csrc = os.path.join(ROOT, "mitsuba2_b200", "csrc")
+    src = [os.path.join(ROOT, "tests", "hostsim", "hostsim.cu")] + [os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith(".h")]
+    if _newer(src, HOSTSIM_SO):
+        subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-diag-suppress", "20013", "-Xcompiler", "-fPIC",
+                               "-shared", "-o", HOSTSIM_SO, src[0]])
+    return HOSTSIM_SO
+
+
+def _p(a):
+    return vp(a.ctypes.data)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class Oracle:
+    """CPU oracle scene (oracle/mts_oracle.c)."""
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            l = C.CDLL(build_oracle())
+            l.orc_scene_create.restype = vp
+            l.orc_scene_create.argtypes = [C.POINTER(A.SceneDesc)]
+            l.orc_tea32.restype = C.c_uint32
+            l.orc_tea32.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+            l.orc_tea64.restype = C.c_uint64
+            l.orc_tea64.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+            for name in ("orc_fresnel_conductor", "orc_microfacet_eval", "orc_microfacet_pdf", "orc_microfacet_smith_g1", "orc_erfinv", "orc_rfilter_eval"):
+                getattr(l, name).restype = C.c_float
+            l.orc_fresnel_conductor.argtypes = [C.c_float] * 3
+            l.orc_fresnel.argtypes = [C.c_float, C.c_float, vp]
+            l.orc_erfinv.argtypes = [C.c_float]
+            l.orc_rfilter_eval.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float]
+            l.orc_microfacet_eval.argtypes = [C.c_int, C.c_float, C.c_float, vp]
+            l.orc_microfacet_pdf.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, vp, vp]
+            l.orc_microfacet_smith_g1.argtypes = [C.c_int, C.c_float, C.c_float, vp, vp]
+            l.orc_microfacet_sample.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, vp, C.c_float, C.c_float, vp]
+            l.orc_square_to_uniform_disk_concentric.argtypes = [C.c_float, C.c_float, vp]
+            l.orc_square_to_cosine_hemisphere.argtypes = [C.c_float, C.c_float, vp]
+            l.orc_square_to_uniform_triangle.argtypes = [C.c_float, C.c_float, vp]
+            l.orc_coordinate_system.argtypes = [vp, vp, vp]
+            l.orc_perspective_sample_to_camera.argtypes = [C.c_float] * 4 + [vp]
+            l.orc_pcg32_floats.argtypes = [C.c_uint64, vp, vp, C.c_uint32, vp]
+            l.orc_sampler_seed.argtypes = [C.c_uint64, C.c_uint64, vp, vp]
+            l.orc_scene_destroy.argtypes = [vp]
+            l.orc_scene_update_vertices.argtypes = [vp, C.c_uint32, vp]
+            l.orc_scene_update_texture.argtypes = [vp, C.c_uint32, vp]
+            l.orc_intersect_closest.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
+            l.orc_intersect_any.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
+            l.orc_intersect_naive.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
+            l.orc_sensor_sample_ray.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp]
+            l.orc_bsdf_sample.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
+            l.orc_bsdf_eval_pdf.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
+            l.orc_sample_emitter_direction.argtypes = [vp, C.c_uint64, vp, vp, vp]
+            l.orc_film_put.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp]
+            l.orc_film_develop.argtypes = [vp, C.c_uint32, vp, vp]
+            l.orc_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, C.c_int, vp]
+            l.orc_trace_sample.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp]
+            cls._lib = l
+        return cls._lib
+
+    def __init__(self, data: SceneData, threads=None):
+        self.data = data
+        self.threads = threads or os.cpu_count() or 1
+        desc, keep = data.to_desc()
+        self.h = vp(self.lib().orc_scene_create(C.byref(desc)))
+        del keep
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.lib().orc_scene_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def intersect_closest(self, om, dm, naive=False):
+        om, dm = _f32(om), _f32(dm)
+        hits = np.empty((om.shape[0], 4), np.float32)
+        fn = self.lib().orc_intersect_naive if naive else self.lib().orc_intersect_closest
+        fn(self.h, om.shape[0], _p(om), _p(dm), _p(hits), self.threads)
+        return hits
+
+    def intersect_any(self, om, dm):
+        om, dm = _f32(om), _f32(dm)
+        occ = np.empty(om.shape[0], np.uint32)
+        self.lib().orc_intersect_any(self.h, om.shape[0], _p(om), _p(dm), _p(occ), self.threads)
+        return occ
+
+    def render_xyzaw(self, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None, counts=None):
+        spp = self.data.spp if spp is None else spp
+        spp_total = spp_begin + spp if spp_total is None else spp_total
+        s = self.data.sensors[sensor]
+        film = np.zeros((s["height"], s["width"], 5), np.float32)
+        cnt = np.zeros(4, np.uint64)
+        self.lib().orc_render(self.h, sensor, spp_begin, spp, spp_total, seed, _p(film), self.threads, _p(cnt))
+        if counts is not None:
+            counts[:] = cnt
+        return film
+
+    def develop(self, xyzaw, sensor=0):
+        xyzaw = _f32(xyzaw)
+        rgb = np.empty(xyzaw.shape[:2] + (3,), np.float32)
+        self.lib().orc_film_develop(self.h, sensor, _p(xyzaw), _p(rgb))
+        return rgb
+
+    def render(self, sensor=0, spp=None, seed=0):
+        return self.develop(self.render_xyzaw(sensor, spp, seed), sensor)
+
+    def film_put(self, pos, values, sensor=0):
+        pos, values = _f32(pos), _f32(values)
+        s = self.data.sensors[sensor]
+        film = np.zeros((s["height"], s["width"], 5), np.float32)
+        self.lib().orc_film_put(self.h, sensor, pos.shape[0], _p(pos), _p(values), _p(film))
+        return film
+
+    def sensor_sample_ray(self, pos, sensor=0):
+        pos = _f32(pos)
+        o, d = np.empty((pos.shape[0], 4), np.float32), np.empty((pos.shape[0], 4), np.float32)
+        self.lib().orc_sensor_sample_ray(self.h, sensor, pos.shape[0], _p(pos), _p(o), _p(d))
+        return o, d
+
+    def bsdf_sample(self, bsdf_id, wi, uv, s1, s2):
+        wi, uv, s1, s2 = map(_f32, (wi, uv, s1, s2))
+        out = np.empty((wi.shape[0], 9), np.float32)
+        self.lib().orc_bsdf_sample(self.h, bsdf_id, wi.shape[0], _p(wi), _p(uv), _p(s1), _p(s2), _p(out))
+        return out
+
+    def bsdf_eval_pdf(self, bsdf_id, wi, uv, wo):
+        wi, uv, wo = map(_f32, (wi, uv, wo))
+        ev, pdf = np.empty((wi.shape[0], 3), np.float32), np.empty(wi.shape[0], np.float32)
+        self.lib().orc_bsdf_eval_pdf(self.h, bsdf_id, wi.shape[0], _p(wi), _p(uv), _p(wo), _p(ev), _p(pdf))
+        return ev, pdf
+
+    def sample_emitter_direction(self, ref_p, s2):
+        ref_p, s2 = _f32(ref_p), _f32(s2)
+        out = np.empty((ref_p.shape[0], 11), np.float32)
+        self.lib().orc_sample_emitter_direction(self.h, ref_p.shape[0], _p(ref_p), _p(s2), _p(out))
+        return out
+
+    def update_vertices(self, mesh_id, positions):
+        positions = _f32(positions)
+        self.lib().orc_scene_update_vertices(self.h, mesh_id, _p(positions))
+
+    def update_texture(self, tex_id, data):
+        data = _f32(data)
+        self.lib().orc_scene_update_texture(self.h, tex_id, _p(data))
+
+
+class HostSim:
+    """The product's stage bodies executed sequentially on the CPU (tests/hostsim/hostsim.cu)."""
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            l = C.CDLL(build_hostsim())
+            l.hs_scene_create.restype = vp
+            l.hs_scene_create.argtypes = [C.POINTER(A.SceneDesc)]
+            l.hs_scene_destroy.argtypes = [vp]
+            l.hs_bvh_info.argtypes = [vp, vp, vp]
+            l.hs_intersect.argtypes = [vp, C.c_uint64, vp, vp, vp, vp, C.c_int]
+            l.hs_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]
+            l.hs_bsdf_sample.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
+            l.hs_sample_emitter_direction.argtypes = [vp, C.c_uint64, vp, vp, vp]
+            cls._lib = l
+        return cls._lib
+
+    def __init__(self, data: SceneData):
+        self.data = data
+        desc, keep = data.to_desc()
+        self.h = vp(self.lib().hs_scene_create(C.byref(desc)))
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.lib().hs_scene_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def bvh_info(self):
+        a, b = C.c_uint32(), C.c_uint32()
+        self.lib().hs_bvh_info(self.h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def intersect_closest(self, om, dm):
+        om, dm = _f32(om), _f32(dm)
+        hits = np.empty((om.shape[0], 4), np.float32)
+        self.lib().hs_intersect(self.h, om.shape[0], _p(om), _p(dm), _p(hits), None, 0)
+        return hits
+
+    def intersect_any(self, om, dm):
+        om, dm = _f32(om), _f32(dm)
+        occ = np.empty(om.shape[0], np.uint32)
+        self.lib().hs_intersect(self.h, om.shape[0], _p(om), _p(dm), None, _p(occ), 1)
+        return occ
+
+    def render_xyzaw(self, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None, counts=None):
+        spp = self.data.spp if spp is None else spp
+        spp_total = spp_begin + spp if spp_total is None else spp_total
+        s = self.data.sensors[sensor]
+        film = np.zeros((s["height"], s["width"], 5), np.float32)
+        cnt = np.zeros(4, np.uint64)
+        self.lib().hs_render(self.h, sensor, spp_begin, spp, spp_total, seed, _p(film), _p(cnt))
+        if counts is not None:
+            counts[:] = cnt
+        return film
+
+
+# ---- scenes ---------------------------------------------------------------------------------------
+def random_rays(n, seed, radius=1.5, maxt=np.inf):
+    rng = np.random.default_rng(seed)
+    o = rng.normal(size=(n, 3))
+    o = o / np.linalg.norm(o, axis=1, keepdims=True) * (rng.random((n, 1)) ** (1 / 3)) * radius
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    om = np.concatenate([o, np.zeros((n, 1))], axis=1).astype(np.float32)
+    dm = np.concatenate([d, np.full((n, 1), maxt)], axis=1).astype(np.float32)
+    return om, dm
+
+
+def sphere_scene(n_theta=32, n_phi=64, res=(64, 48), spp=4):
+    sd = SceneData()
+    b = sd.add_diffuse([0.5, 0.4, 0.3])
+    m = M.displaced_sphere(n_theta, n_phi)
+    m.bsdf = b
+    sd.add_mesh(m)
+    sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.spp = 6, spp
+    return sd
+
+
+def cbox_scene(res=32, spp=8, rfilter="box"):
+    """Cornell box from the committed fixture (generated by tests/golden/make_fixtures.py from the reference's XML)."""
+    sd = SceneData.load_npz(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"))
+    s = sd.sensors[0]
+    from mitsuba2_b200.scenedata import perspective_sample_to_camera
+    s["width"] = s["height"] = res
+    s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], 1.0).reshape(16)
+    kinds = {"box": (A.RFILTER_BOX, 0.5), "tent": (A.RFILTER_TENT, 1.0), "gaussian": (A.RFILTER_GAUSSIAN, 2.0)}
+    s["rfilter"], s["radius"] = kinds[rfilter]
+    s["stddev"] = 0.5
+    sd.spp = spp
+    return sd
+
+
+def synthetic_envmap(w=64, h=32, seed=7):
+    """Smooth sky gradient + a bright 'sun' blob, deterministic."""
+    v, u = np.meshgrid((np.arange(h) + 0.5) / h, (np.arange(w) + 0.5) / w, indexing="ij")
+    sky = np.stack([0.3 + 0.4 * (1 - v), 0.4 + 0.4 * (1 - v), 0.6 + 0.4 * (1 - v)], axis=2)
+    sun = 40.0 * np.exp(-(((u - 0.3) * 2) ** 2 + (v - 0.25) ** 2) / 0.004)
+    rng = np.random.default_rng(seed)
+    img = sky * (0.9 + 0.2 * rng.random((h, w, 1))) + sun[:, :, None] * np.array([1.0, 0.9, 0.7])
+    return img.astype(np.float32)
+
+
+def material_scene(res=(48, 32), spp=8, envmap=True, area=True):
+    """diffuse (textured) ground + roughconductor sphere + dielectric sphere + area light + envmap."""
+    sd = SceneData()
+    rng = np.random.default_rng(3)
+    tex = sd.add_texture_bitmap(0.2 + 0.6 * rng.random((16, 16, 3)).astype(np.float32))
+    ground = M.quad([-10, -1.2, -10], [-10, -1.2, 10], [10, -1.2, 10], [10, -1.2, -10])
+    ground.bsdf = sd.add_diffuse(tex)
+    sd.add_mesh(ground)
+    s1 = M.displaced_sphere(24, 48)
+    s1.bsdf = sd.add_roughconductor((0.200438, 0.924033, 1.102212), (3.912949, 2.452848, 2.142188), 0.1)
+    sd.add_mesh(s1)
+    s2 = M.displaced_sphere(16, 32, radius=0.4, center=(1.6, -0.8, 0), displace=False)
+    s2.bsdf = sd.add_dielectric()
+    sd.add_mesh(s2)
+    if area:
+        light = M.quad([-0.5, 3, -0.5], [0.5, 3, -0.5], [0.5, 3, 0.5], [-0.5, 3, 0.5])
+        light.bsdf = sd.add_diffuse(0.5)
+        sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
+    if envmap:
+        sd.add_envmap(synthetic_envmap())
+    sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 6, 5, spp
+    return sd

@@ -1,0 +1,202 @@
+// hostsim.cu -- TEST-ONLY host simulator: runs the product's per-thread stage bodies (mitsuba2_b200/csrc/*.h,
+// the HD functions the CUDA kernels wrap) sequentially on the CPU, so the BVH builder, the compressed-node
+// traversal and the wavefront state machine can be checked against the oracle in the `-m "not gpu"` suite.
+// It is NOT part of the product library and makes no CUDA runtime calls.
+#include "../../include/mtsb200.h"
+#include "../../mitsuba2_b200/csrc/path.h"
+#include "../../mitsuba2_b200/csrc/host_tables.h"
+#include <vector>
+#include <algorithm>
+#include <numeric>
+#include <cstring>
+#include <memory>
+
+using namespace mtsb;
+
+struct hs_scene {
+    std::vector<MeshDev> meshes; std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
+    std::vector<SensorDev> sensors;
+    std::vector<float> pos, nrm, uv; std::vector<uint4> faces;
+    std::vector<std::vector<float>> tables; std::vector<float4> env_rgba;
+    std::vector<uint4> nodes; std::vector<float4> tris;
+    std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
+    SceneDev dev; uint32_t bvh_nodes = 0, bvh_depth = 0;
+    float3 lo, hi;
+};
+
+static void hs_build_bvh(hs_scene *s) {
+    uint32_t n = (uint32_t) s->faces.size();
+    s->dev.bvh.n_tris = n; s->dev.bvh.nodes = nullptr; s->dev.bvh.tris = nullptr;
+    s->lo = mk3(INFINITY); s->hi = mk3(-INFINITY);
+    if (n == 0) return;
+    std::vector<float4> tlo(n), thi(n), nlo(2 * (size_t) n), nhi(2 * (size_t) n);
+    std::vector<uint64_t> keys(n), keys2(n); std::vector<uint32_t> order(n), order2(n), rfirst(n), rlast(n), flags(n, 0), counters(2);
+    std::vector<int> left(n), right(n), parent(2 * (size_t) n), wide_bin(n + 1);
+    s->nodes.assign(5 * ((size_t) n + 1), make_uint4(0, 0, 0, 0)); s->tris.assign(3 * (size_t) n, make_float4(0, 0, 0, 0));
+    BvhBuild b;
+    b.pos = s->pos.data(); b.faces = s->faces.data(); b.n = n;
+    b.tlo = tlo.data(); b.thi = thi.data(); b.keys = keys.data(); b.order = order.data(); b.left = left.data(); b.right = right.data();
+    b.parent = parent.data(); b.rfirst = rfirst.data(); b.rlast = rlast.data(); b.nlo = nlo.data(); b.nhi = nhi.data(); b.flags = flags.data();
+    b.nodes = s->nodes.data(); b.tris = s->tris.data(); b.wide_bin = wide_bin.data(); b.counters = counters.data();
+    for (uint32_t i = 0; i < n; ++i) { float3 lo, hi; tri_bounds_body(b, i, lo, hi); s->lo = fmin3(s->lo, lo); s->hi = fmax3(s->hi, hi); }
+    b.scene_lo = s->lo; b.scene_hi = s->hi;
+    for (uint32_t i = 0; i < n; ++i) morton_body(b, i);
+    std::vector<uint32_t> perm(n); std::iota(perm.begin(), perm.end(), 0u);
+    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t c) { return keys[a] < keys[c]; });
+    for (uint32_t i = 0; i < n; ++i) { keys2[i] = keys[perm[i]]; order2[i] = order[perm[i]]; }
+    b.keys = keys2.data(); b.order = order2.data();
+    for (uint32_t i = 0; i + 1 < n; ++i) lbvh_node_body(b, (int) i);
+    for (uint32_t i = 0; i < n; ++i) lbvh_fit_body(b, (int) i);
+    counters[0] = 1; counters[1] = 0; wide_bin[0] = 0;
+    uint32_t begin = 0, end = 1, depth = 0;
+    while (begin < end) { for (uint32_t w = begin; w < end; ++w) collapse_body(b, w); begin = end; end = counters[0]; depth++; }
+    s->bvh_nodes = end; s->bvh_depth = depth;
+    s->dev.bvh.nodes = s->nodes.data(); s->dev.bvh.tris = s->tris.data();
+}
+
+extern "C" void hs_scene_destroy(hs_scene *s) { delete s; }
+
+extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
+    hs_scene *s = new hs_scene();
+    memset(&s->dev, 0, sizeof(SceneDev));
+    uint32_t vbase = 0, fbase = 0;
+    std::vector<std::vector<uint32_t>> mesh_faces;
+    for (uint32_t i = 0; i < d->n_meshes; ++i) {
+        const mtsb_mesh_desc &m = d->meshes[i];
+        MeshDev md; md.face_begin = fbase; md.face_count = m.face_count; md.vert_begin = vbase; md.vert_count = m.vertex_count;
+        md.bsdf = m.bsdf_id; md.emitter = m.emitter_id; md.has_normals = m.normals != nullptr; md.has_uv = m.texcoords != nullptr;
+        s->meshes.push_back(md);
+        s->pos.insert(s->pos.end(), m.positions, m.positions + 3 * (size_t) m.vertex_count);
+        if (m.normals) s->nrm.insert(s->nrm.end(), m.normals, m.normals + 3 * (size_t) m.vertex_count); else s->nrm.insert(s->nrm.end(), 3 * (size_t) m.vertex_count, 0.f);
+        if (m.texcoords) s->uv.insert(s->uv.end(), m.texcoords, m.texcoords + 2 * (size_t) m.vertex_count); else s->uv.insert(s->uv.end(), 2 * (size_t) m.vertex_count, 0.f);
+        mesh_faces.emplace_back(m.faces, m.faces + 3 * (size_t) m.face_count);
+        for (uint32_t f = 0; f < m.face_count; ++f) s->faces.push_back(make_uint4(m.faces[3 * f] + vbase, m.faces[3 * f + 1] + vbase, m.faces[3 * f + 2] + vbase, i));
+        vbase += m.vertex_count; fbase += m.face_count;
+    }
+    s->tables.reserve(64 + d->n_textures + d->n_emitters);
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const mtsb_texture_desc &t = d->textures[i]; TexDev td; memset(&td, 0, sizeof(td));
+        td.type = t.type; td.value = mk3(t.value[0], t.value[1], t.value[2]);
+        if (t.type == MTSB_TEX_BITMAP) { td.w = t.width; td.h = t.height; td.ch = t.channels; memcpy(td.to_uv, t.to_uv, sizeof(td.to_uv));
+            s->tables.emplace_back(t.data, t.data + (size_t) t.width * t.height * t.channels); td.data = s->tables.back().data(); }
+        s->tex.push_back(td);
+    }
+    for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
+        const mtsb_bsdf_desc &b = d->bsdfs[i]; BsdfDev bd; memset(&bd, 0, sizeof(bd));
+        bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex; bd.spec_t = b.specular_transmittance_tex;
+        bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta;
+        s->bsdfs.push_back(bd);
+    }
+    hs_build_bvh(s);
+    s->dev.env_emitter = -1;
+    for (uint32_t i = 0; i < d->n_emitters; ++i) {
+        const mtsb_emitter_desc &e = d->emitters[i]; EmitterDev ed; memset(&ed, 0, sizeof(ed)); ed.type = e.type;
+        if (e.type == MTSB_EMITTER_AREA) {
+            ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
+            const MeshDev &m = s->meshes[e.mesh_id];
+            AreaTable t = build_area_table(s->pos.data() + 3 * (size_t) m.vert_begin, mesh_faces[e.mesh_id].data(), m.face_count);
+            s->tables.push_back(t.cdf); ed.cdf = s->tables.back().data(); ed.cdf_sum = t.sum; ed.normalization = t.normalization; ed.valid_lo = t.valid_lo; ed.valid_hi = t.valid_hi;
+        } else {
+            s->dev.env_emitter = (int) i; ed.w = e.width; ed.h = e.height; ed.scale = e.scale;
+            memcpy(ed.to_world, e.to_world, sizeof(ed.to_world)); invert4x4(e.to_world, ed.to_local);
+            size_t npx = (size_t) e.width * e.height; s->env_rgba.resize(npx);
+            for (size_t k = 0; k < npx; ++k) s->env_rgba[k] = make_float4(e.rgba[4 * k], e.rgba[4 * k + 1], e.rgba[4 * k + 2], 1.f);
+            ed.rgba = s->env_rgba.data();
+            std::vector<float> lum = env_importance(e.rgba, e.width, e.height);
+            H2DTable h = build_h2d(lum.data(), e.width, e.height);
+            ed.n_levels = (int) h.levels.size();
+            for (size_t l = 0; l < h.levels.size(); ++l) { s->tables.push_back(h.levels[l]); ed.level_data[l] = s->tables.back().data(); ed.level_width[l] = h.widths[l]; }
+            float3 c = (s->lo + s->hi) * 0.5f; float r = s->faces.size() ? norm(s->hi - c) : 0.f;
+            ed.bsphere_radius = fmaxf(kRayEpsilon, r * (1.f + kRayEpsilon));
+        }
+        s->emitters.push_back(ed);
+    }
+    s->dev.n_emitters = (int) s->emitters.size();
+    for (uint32_t i = 0; i < d->n_sensors; ++i) {
+        const mtsb_sensor_desc &sd = d->sensors[i]; SensorDev sn; memset(&sn, 0, sizeof(sn));
+        memcpy(sn.to_world, sd.to_world, sizeof(sn.to_world)); memcpy(sn.sample_to_camera, sd.sample_to_camera, sizeof(sn.sample_to_camera));
+        sn.near_clip = sd.near_clip; sn.far_clip = sd.far_clip; sn.width = sd.film_width; sn.height = sd.film_height; sn.rfilter = sd.rfilter;
+        sn.stddev = sd.rfilter_stddev; sn.radius = sd.rfilter == MTSB_RFILTER_BOX ? sd.rfilter_radius + kRayEpsilon : sd.rfilter_radius;
+        s->film_xyza.emplace_back((size_t) sn.width * sn.height, make_float4(0, 0, 0, 0)); s->film_w.emplace_back((size_t) sn.width * sn.height, 0.f);
+        s->sensors.push_back(sn);
+    }
+    for (size_t i = 0; i < s->sensors.size(); ++i) { s->sensors[i].film_xyza = s->film_xyza[i].data(); s->sensors[i].film_w = s->film_w[i].data(); }
+    s->dev.max_depth = d->integrator.max_depth < 0 ? (1 << 30) : d->integrator.max_depth; s->dev.rr_depth = d->integrator.rr_depth;
+    s->dev.pos = s->pos.data(); s->dev.nrm = s->nrm.data(); s->dev.uv = s->uv.data(); s->dev.faces = s->faces.data();
+    s->dev.meshes = s->meshes.data(); s->dev.tex = s->tex.data(); s->dev.bsdfs = s->bsdfs.data(); s->dev.emitters = s->emitters.data();
+    return s;
+}
+
+extern "C" void hs_bvh_info(hs_scene *s, uint32_t *nodes, uint32_t *depth) { *nodes = s->bvh_nodes; *depth = s->bvh_depth; }
+
+extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const float *d, float *hits, uint32_t *occ, int any) {
+    std::vector<uint2> fast(8);
+    for (uint64_t i = 0; i < n; ++i) {
+        TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1;
+        Hit h;
+        if (any) occ[i] = bvh_trace<true>(s->dev.bvh, mk3(o[4 * i], o[4 * i + 1], o[4 * i + 2]), mk3(d[4 * i], d[4 * i + 1], d[4 * i + 2]), o[4 * i + 3], d[4 * i + 3], st, h) ? 1u : 0u;
+        else { bvh_trace<false>(s->dev.bvh, mk3(o[4 * i], o[4 * i + 1], o[4 * i + 2]), mk3(d[4 * i], d[4 * i + 1], d[4 * i + 2]), o[4 * i + 3], d[4 * i + 3], st, h);
+            hits[4 * i] = h.t; hits[4 * i + 1] = h.u; hits[4 * i + 2] = h.v; hits[4 * i + 3] = u2f(h.prim); }
+    }
+}
+
+// The wavefront loop of mtsb_render, stage by stage, with sequential "threads".
+extern "C" void hs_render(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total, uint64_t seed,
+                          float *xyzaw, uint64_t *counts) {
+    SensorDev sn = s->sensors[sensor_id];
+    uint64_t total = (uint64_t) sn.width * sn.height * spp_count;
+    uint32_t pool = (uint32_t) std::min<uint64_t>(total, 1u << 20);
+    std::vector<float4> qo[2], qd[2], qh[2], qt[2], so(pool), sdv(pool), scv(pool), result(pool);
+    std::vector<uint4> qm[2], qr[2];
+    for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); }
+    auto queue = [&](int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); return q; };
+    std::vector<uint2> fast(8);
+    uint64_t c_closest = 0, c_shadow = 0, c_seg = 0;
+    for (uint64_t off = 0; off < total; off += pool) {
+        uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
+        RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = result.data();
+        int cur = 0; uint32_t count = n;
+        for (uint32_t i = 0; i < n; ++i) raygen_body(sn, b, queue(cur), i);
+        for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
+            PathQueue qin = queue(cur), qout = queue(cur ^ 1);
+            for (uint32_t i = 0; i < count; ++i) {
+                TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
+                bvh_trace<false>(s->dev.bvh, xyz(qin.o_mint[i]), xyz(qin.d_maxt[i]), qin.o_mint[i].w, qin.d_maxt[i].w, st, h);
+                qin.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+            }
+            c_closest += count; c_seg += count;
+            uint32_t next = 0, nshadow = 0;
+            for (uint32_t i = 0; i < count; ++i) {
+                ShadeOut out = shade_body(s->dev, qin, b, i);
+                if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; next++; }
+                if (out.shadow) { so[nshadow] = out.s_o_mint; sdv[nshadow] = out.s_d_maxt; scv[nshadow] = out.s_contrib_id; nshadow++; }
+            }
+            for (uint32_t i = 0; i < nshadow; ++i) {
+                TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
+                if (!bvh_trace<true>(s->dev.bvh, xyz(so[i]), xyz(sdv[i]), so[i].w, sdv[i].w, st, h)) {
+                    uint32_t pid = f2u(scv[i].w); result[pid].x += scv[i].x; result[pid].y += scv[i].y; result[pid].z += scv[i].z; }
+            }
+            c_shadow += nshadow;
+            count = next; cur ^= 1;
+        }
+        for (uint32_t i = 0; i < n; ++i) {
+            float fx, fy; path_film_pos(sn, b, i, fx, fy);
+            film_put(sn, fx, fy, radiance_to_xyza(result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
+                xyzaw[5 * (size_t) pix] += v.x; xyzaw[5 * (size_t) pix + 1] += v.y; xyzaw[5 * (size_t) pix + 2] += v.z; xyzaw[5 * (size_t) pix + 3] += v.w; xyzaw[5 * (size_t) pix + 4] += w; });
+        }
+    }
+    if (counts) { counts[0] = total; counts[1] = c_closest; counts[2] = c_shadow; counts[3] = c_seg; }
+}
+
+extern "C" void hs_bsdf_sample(hs_scene *s, uint32_t id, uint64_t n, const float *wi, const float *uv, const float *s1, const float *s2, float *out9) {
+    for (uint64_t i = 0; i < n; ++i) {
+        SI si; si.p = mk3(0.f); si.n = mk3(0, 0, 1); si.sh.s = mk3(1, 0, 0); si.sh.t = mk3(0, 1, 0); si.sh.n = mk3(0, 0, 1);
+        si.u = uv[2 * i]; si.v = uv[2 * i + 1]; si.wi = ld3(wi, (uint32_t) i); si.t = 1.f; si.prim = 0; si.mesh = 0; si.valid = true;
+        BsdfSample bs = bsdf_sample(s->dev, s->bsdfs[id], si, s1[i], s2[2 * i], s2[2 * i + 1]); float *o = out9 + 9 * i;
+        o[0] = bs.wo.x; o[1] = bs.wo.y; o[2] = bs.wo.z; o[3] = bs.pdf; o[4] = bs.eta; o[5] = bs.weight.x; o[6] = bs.weight.y; o[7] = bs.weight.z; o[8] = bs.delta ? 1.f : 0.f;
+    }
+}
+extern "C" void hs_sample_emitter_direction(hs_scene *s, uint64_t n, const float *ref_p, const float *s2, float *out11) {
+    for (uint64_t i = 0; i < n; ++i) { DirSample ds = sample_emitter_direction(s->dev, ld3(ref_p, (uint32_t) i), s2[2 * i], s2[2 * i + 1]); float *o = out11 + 11 * i;
+        o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.x; o[6] = ds.value.y; o[7] = ds.value.z; o[8] = ds.n.x; o[9] = ds.n.y; o[10] = ds.n.z; }
+}

@@ -1,0 +1,180 @@
+"""GPU parity tests proper: the CUDA path through the C ABI vs the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mi():
+    import mitsuba2_b200 as mi
+    mi.set_variant("cuda_b200_rgb")
+    return mi
+
+
+def _prims(h):
+    return np.ascontiguousarray(h[:, 3]).view(np.uint32)
+
+
+def test_pcg32_and_sampler_seed(mi):
+    st = np.array([0x853c49e6748fea9b, 1, 42, 2**63 + 5], np.uint64)
+    sq = np.array([0xda3e39cb94b95bdb, 2, 54, 7], np.uint64)
+    gpu = mi.pcg32_floats(st, sq, 16)
+    cpu = np.empty((4, 16), np.float32)
+    H.Oracle.lib().orc_pcg32_floats(4, H._p(st), H._p(sq), 16, H._p(cpu))
+    assert np.array_equal(gpu, cpu)
+    s_g, i_g = mi.sampler_seed(1000, 12345)
+    s_c, i_c = np.empty(1000, np.uint64), np.empty(1000, np.uint64)
+    H.Oracle.lib().orc_sampler_seed(1000, 12345, H._p(s_c), H._p(i_c))
+    assert np.array_equal(s_g, s_c) and np.array_equal(i_g, i_c)
+
+
+@pytest.mark.parametrize("scene_fn,n", [(lambda: H.cbox_scene(32, 4), 20000), (lambda: H.sphere_scene(128, 256), 200000)])
+def test_intersection_hit_ids(mi, scene_fn, n):
+    sd = scene_fn()
+    scene, orc = mi.Scene(sd), H.Oracle(sd)
+    rng = np.random.default_rng(0)
+    om_c, dm_c = orc.sensor_sample_ray(rng.random((n // 2, 2)))
+    lo = np.min([m.positions.min(axis=0) for m in sd.meshes], axis=0)
+    hi = np.max([m.positions.max(axis=0) for m in sd.meshes], axis=0)
+    om_i, dm_i = H.random_rays(n // 2, 1, radius=1.0)
+    om_i[:, :3] = (lo + hi) / 2 + om_i[:, :3] * (hi - lo) * 0.6
+    om, dm = np.concatenate([om_c, om_i]), np.concatenate([dm_c, dm_i])
+    h_g, h_c = scene.intersect_closest_raw(om, dm), orc.intersect_closest(om, dm)
+    mism = _prims(h_g) != _prims(h_c)
+    # classify: rays within edge epsilon (barycentric distance to an edge) or equal-t ties may legitimately differ
+    b = np.stack([h_c[:, 1], h_c[:, 2], 1 - h_c[:, 1] - h_c[:, 2]], axis=1)
+    b_g = np.stack([h_g[:, 1], h_g[:, 2], 1 - h_g[:, 1] - h_g[:, 2]], axis=1)
+    edge = (np.abs(b).min(axis=1) < 1e-4) | (np.abs(b_g).min(axis=1) < 1e-4)
+    tie = np.abs(h_g[:, 0] - h_c[:, 0]) <= 1e-5 * np.maximum(1, np.abs(h_c[:, 0]))
+    hard = mism & ~(edge | tie)
+    assert hard.sum() == 0, f"{hard.sum()} hit-id mismatches away from edges (total {mism.sum()})"
+    assert mism.mean() < 1e-3
+    ok = ~mism & np.isfinite(h_c[:, 0])
+    assert np.allclose(h_g[ok, 0], h_c[ok, 0], rtol=1e-4, atol=1e-5)
+    assert np.allclose(h_g[ok, 1:3], h_c[ok, 1:3], atol=2e-3)
+    # any-hit
+    dm2 = dm.copy()
+    dm2[:, 3] = np.random.default_rng(2).random(dm.shape[0]) * 3 * max(1.0, float((hi - lo).max()) / 2)
+    a_g, a_c = scene.intersect_any_raw(om, dm2), orc.intersect_any(om, dm2)
+    assert (a_g != a_c).mean() < 1e-3
+    # BVH vs brute force on the device (same triangle test): exact
+    sub = slice(0, 2000)
+    h_n = scene.intersect_closest_raw(om[sub], dm[sub], naive=True)
+    same = _prims(h_n) == _prims(h_g[sub])
+    assert (~same).sum() <= 2 and np.allclose(h_n[same, 0], h_g[sub][same, 0], rtol=1e-6, equal_nan=True)
+
+
+def test_empty_and_tiny_scenes(mi):
+    sd = H.SceneData()
+    sd.add_diffuse(0.5)
+    sd.add_perspective(H.look_at([0, 0, -3], [0, 0, 0], [0, 1, 0]), 45, 0.01, 100, 8, 8, "box")
+    sd.max_depth = 3
+    scene = mi.Scene(sd)
+    om, dm = H.random_rays(100, 0)
+    assert not np.isfinite(scene.intersect_closest_raw(om, dm)[:, 0]).any()
+    img = scene.render(spp=2)
+    assert np.all(img == 0)
+    assert scene.intersect_closest_raw(om[:0], dm[:0]).shape == (0, 4)
+    # single triangle
+    sd2 = H.SceneData()
+    b = sd2.add_diffuse(0.5)
+    sd2.add_mesh(H.Mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]], bsdf=b))
+    sd2.add_perspective(H.look_at([0, 0, -3], [0, 0, 0], [0, 1, 0]), 45, 0.01, 100, 8, 8, "box")
+    s2, o2 = mi.Scene(sd2), H.Oracle(sd2)
+    om = np.array([[0.2, 0.2, -1, 0], [2, 2, -1, 0]], np.float32)
+    dm = np.array([[0, 0, 1, np.inf], [0, 0, 1, np.inf]], np.float32)
+    hg, hc = s2.intersect_closest_raw(om, dm), o2.intersect_closest(om, dm)
+    assert np.array_equal(_prims(hg), _prims(hc)) and hg[0, 0] == pytest.approx(1.0)
+
+
+@pytest.mark.parametrize("scene_fn,spp,tol", [
+    (lambda: H.cbox_scene(64, 16), 16, 2e-3),
+    (lambda: H.cbox_scene(48, 8, "gaussian"), 8, 2e-3),
+    (lambda: H.cbox_scene(48, 8, "tent"), 8, 2e-3),
+    (lambda: H.material_scene((96, 64), 16), 16, 2e-2),
+])
+def test_render_matches_oracle_per_sample_streams(mi, scene_fn, spp, tol):
+    """Same per-sample PCG32 streams on both sides => images agree up to float noise / rare path divergence."""
+    sd = scene_fn()
+    scene, orc = mi.Scene(sd), H.Oracle(sd)
+    scene.film_clear()
+    st = scene.render_accumulate(spp=spp, seed=7)
+    f_g = scene.film_xyzaw()
+    cnt = np.zeros(4, np.uint64)
+    f_c = orc.render_xyzaw(spp=spp, seed=7, counts=cnt)
+    assert st["samples"] == cnt[0]
+    assert abs(int(st["closest_rays"]) - int(cnt[1])) <= 1e-3 * cnt[1] + 2
+    assert np.allclose(f_g[..., 4], f_c[..., 4], rtol=1e-4, atol=1e-4)          # weights
+    assert np.allclose(f_g[..., 3], f_c[..., 3], rtol=1e-4, atol=1e-3)          # alpha
+    num = np.abs(f_g[..., :3] - f_c[..., :3]).sum()
+    den = np.abs(f_c[..., :3]).sum()
+    assert num / den < tol, num / den
+    d = np.abs(f_g[..., :3] - f_c[..., :3]).max(axis=2) / (np.abs(f_c[..., :3]).max(axis=2) + 1e-2)
+    assert (d > 1e-2).mean() < 0.02
+    rgb_g, rgb_c = scene.film_develop(), orc.develop(f_g)
+    assert np.allclose(rgb_g, rgb_c, rtol=1e-4, atol=1e-5)
+
+
+def test_sample_sharding_is_exact_union(mi):
+    """spp sharding (8e): rendering sample indices [0,4) then [4,8) accumulates to the same film as [0,8)."""
+    sd = H.cbox_scene(32, 8)
+    scene = mi.Scene(sd)
+    scene.film_clear(); scene.render_accumulate(spp=8, seed=3, spp_begin=0, spp_total=8); full = scene.film_xyzaw()
+    scene.film_clear()
+    scene.render_accumulate(spp=4, seed=3, spp_begin=0, spp_total=8)
+    scene.render_accumulate(spp=4, seed=3, spp_begin=4, spp_total=8)
+    parts = scene.film_xyzaw()
+    assert np.allclose(full, parts, rtol=1e-5, atol=1e-5)
+
+
+def test_stage_hooks_match_oracle(mi):
+    sd = H.material_scene()
+    scene, orc = mi.Scene(sd), H.Oracle(sd)
+    rng = np.random.default_rng(5)
+    n = 4096
+    pos = rng.random((n, 2)).astype(np.float32)
+    for a, b in zip(scene.sensor_sample_ray(pos), orc.sensor_sample_ray(pos)):
+        assert np.allclose(a, b, rtol=1e-5, atol=1e-6)
+    wi = rng.normal(size=(n, 3)); wi[:, 2] = np.abs(wi[:, 2]) + 0.05; wi /= np.linalg.norm(wi, axis=1, keepdims=True)
+    wi[: n // 8, 2] *= -1                      # some back-facing
+    wo = rng.normal(size=(n, 3)); wo /= np.linalg.norm(wo, axis=1, keepdims=True)
+    uv, s1, s2 = rng.random((n, 2)), rng.random(n), rng.random((n, 2))
+    for bid in range(len(sd.bsdfs)):
+        g, c = scene.bsdf_sample(bid, wi, uv, s1, s2), orc.bsdf_sample(bid, wi, uv, s1, s2)
+        assert np.allclose(g, c, rtol=2e-3, atol=2e-4), bid
+        (eg, pg), (ec, pc) = scene.bsdf_eval_pdf(bid, wi, uv, wo), orc.bsdf_eval_pdf(bid, wi, uv, wo)
+        assert np.allclose(eg, ec, rtol=2e-3, atol=1e-5) and np.allclose(pg, pc, rtol=2e-3, atol=1e-5), bid
+    ref_p = rng.normal(size=(n, 3)).astype(np.float32)
+    g, c = scene.sample_emitter_direction(ref_p, s2), orc.sample_emitter_direction(ref_p, s2)
+    assert np.allclose(g[:, :5], c[:, :5], rtol=2e-3, atol=1e-4)
+    fin = np.isfinite(c[:, 5:8]).all(axis=1)
+    assert np.allclose(g[fin, 5:8], c[fin, 5:8], rtol=5e-3, atol=1e-3)
+
+
+def test_film_put_matches_oracle(mi):
+    for rf in ("box", "tent", "gaussian"):
+        sd = H.cbox_scene(16, 1, rf)
+        scene, orc = mi.Scene(sd), H.Oracle(sd)
+        rng = np.random.default_rng(1)
+        pos = (rng.random((500, 2)) * 18 - 1).astype(np.float32)       # includes out-of-film positions
+        val = rng.random((500, 5)).astype(np.float32)
+        scene.film_clear(); scene.film_put(pos, val)
+        assert np.allclose(scene.film_xyzaw(), orc.film_put(pos, val), rtol=1e-4, atol=1e-5), rf
+
+
+def test_update_vertices_and_texture(mi):
+    sd = H.material_scene((32, 24), 4)
+    scene, orc = mi.Scene(sd), H.Oracle(sd)
+    newp = sd.meshes[1].positions * 0.8 + np.array([0.1, 0.2, 0.0], np.float32)
+    scene.update_vertices(1, newp); orc.update_vertices(1, newp)
+    tex = (0.3 + 0.5 * np.random.default_rng(9).random((16, 16, 3))).astype(np.float32)
+    scene.update_texture(0, tex); orc.update_texture(0, tex)
+    om, dm = orc.sensor_sample_ray(np.random.default_rng(0).random((5000, 2)))
+    hg, hc = scene.intersect_closest_raw(om, dm), orc.intersect_closest(om, dm)
+    assert (_prims(hg) != _prims(hc)).mean() < 2e-3
+    scene.film_clear(); scene.render_accumulate(spp=4, seed=2)
+    f_g, f_c = scene.film_xyzaw(), orc.render_xyzaw(spp=4, seed=2)
+    assert np.abs(f_g[..., :3] - f_c[..., :3]).sum() / np.abs(f_c[..., :3]).sum() < 3e-2
