@@ -37,7 +37,9 @@ def compute_vertex_normals(positions, faces):
             d0 = d0 / np.linalg.norm(d0, axis=1, keepdims=True)
             d1 = d1 / np.linalg.norm(d1, axis=1, keepdims=True)
             ang = np.where(ok, unit_angle(d0, d1), 0.0)
-            np.add.at(acc, f[:, k], np.nan_to_num(n * ang[:, None]))
+            contrib = np.nan_to_num(n * ang[:, None])
+            for c in range(3):
+                acc[:, c] += np.bincount(f[:, k], weights=contrib[:, c], minlength=p.shape[0])
     ln = np.linalg.norm(acc, axis=1)
     out = np.where(ln[:, None] != 0, acc / np.where(ln == 0, 1.0, ln)[:, None], np.array([1.0, 0.0, 0.0]))
     return out.astype(np.float32)
