@@ -1,0 +1,273 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 path-tracing backend (contract: see the task statement).
+
+Metric (BASELINE.json): Msamples/s path tracing on the C3 workload (1920x1080, 4M-triangle scene with
+diffuse/roughconductor/dielectric BSDFs, area + envmap emitters, max_depth 6), spp-sharded over N GPUs.
+A "step" = one pass of the wavefront path tracer over 1920x1080 x --spp-per-step samples per GPU
+(weak scaling: rank r renders its own disjoint sample-index range) + one NCCL all-reduce of the film.
+
+  python bench.py --gpus 1 --steps 3 --warmup 3
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      (CPU oracle = C restatement of the reference path, all host threads)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    "c3": dict(desc="C3 path tracing 1920x1080, 4M-triangle displaced sphere (roughconductor) + textured diffuse ground + "
+                    "100k-triangle dielectric sphere + area light + envmap, max_depth 6, rr_depth 5, box filter, rgb",
+               width=1920, height=1080),
+    "c3-small": dict(desc="C3 scene at reduced size (smoke)", width=480, height=270),
+}
+
+
+def build_scene(name):
+    from mitsuba2_b200 import scenes
+    w = WORKLOADS[name]
+    if name == "c3":
+        return scenes.c3_scene(width=w["width"], height=w["height"])
+    return scenes.c3_scene(n_theta=100, n_phi=200, width=w["width"], height=w["height"], small=(32, 64), tex_res=64)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return json.load(open(path))["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def run_reference(args):
+    """Reference arm for this tier: the CPU restatement of the reference's path (oracle/), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import helpers
+    sd = build_scene(args.workload)
+    cores = os.cpu_count() or 1
+    # bounded sample of the same workload: same scene and camera, 1/4-resolution film, 1 spp per step
+    s = sd.sensors[0]
+    from mitsuba2_b200.scenedata import perspective_sample_to_camera
+    s["width"], s["height"] = max(16, s["width"] // 4), max(9, s["height"] // 4)
+    s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], s["width"] / s["height"]).reshape(16)
+    orc = helpers.Oracle(sd, threads=cores)
+    samples = s["width"] * s["height"]
+    for i in range(args.warmup):
+        orc.render_xyzaw(spp=1, seed=1, spp_begin=i, spp_total=args.warmup + args.steps)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        orc.render_xyzaw(spp=1, seed=1, spp_begin=args.warmup + i, spp_total=args.warmup + args.steps)
+    dt = time.perf_counter() - t0
+    value = samples * args.steps / dt / 1e6
+    sample = f"{s['width']}x{s['height']} x 1 spp per step of the same scene/camera ({samples} samples/step)"
+    print(json.dumps({
+        "impl": "reference", "metric": "path_tracing_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload]["desc"], "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def cpu_baseline(sd_full, budget_s=20.0):
+    """Oracle ("port" of the reference path) timed on this box's host cores on a bounded sample of the workload."""
+    import copy
+    import helpers
+    from mitsuba2_b200.scenedata import perspective_sample_to_camera
+    sd = copy.copy(sd_full)
+    sd.sensors = [dict(sd_full.sensors[0])]
+    s = sd.sensors[0]
+    s["width"], s["height"] = max(16, s["width"] // 4), max(9, s["height"] // 4)
+    s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], s["width"] / s["height"]).reshape(16)
+    cores = os.cpu_count() or 1
+    orc = helpers.Oracle(sd, threads=cores)
+    orc.render_xyzaw(spp=1, seed=1, spp_begin=0, spp_total=64)          # warm-up
+    n, t0 = 0, time.perf_counter()
+    while True:
+        orc.render_xyzaw(spp=1, seed=1, spp_begin=1 + n, spp_total=64)
+        n += 1
+        if time.perf_counter() - t0 > budget_s / 2 or n >= 32:
+            break
+    dt = time.perf_counter() - t0
+    samples = s["width"] * s["height"] * n
+    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
+            "sample": f"{s['width']}x{s['height']} film of the same scene/camera, {n} spp ({samples} samples, {dt:.1f} s)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
+    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import mitsuba2_b200 as mi
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mi.set_variant("cuda_b200_rgb")
+    t_build = time.perf_counter()
+    sd = build_scene(args.workload)
+    scene = mi.Scene(sd, device=local)
+    build = scene.build_stats()
+    t_build = time.perf_counter() - t_build
+    s = sd.sensors[0]
+    npix = s["width"] * s["height"]
+    spp, W, K = args.spp_per_step, args.warmup, args.steps
+    spp_total = (2 * (W + K) + 2) * world * spp
+    film_t = torch.empty(npix * 5, dtype=torch.float32, device=f"cuda:{local}")
+
+    def step(i, profile=False):
+        """one bench step on this rank: render this rank's sample range, then reduce the film over ranks."""
+        st = scene.render_accumulate(spp=spp, seed=1, spp_begin=(i * world + rank) * spp, spp_total=spp_total)
+        t_red = 0.0
+        if world > 1:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            mi._abi.check(mi._abi.lib().mtsb_film_read(scene._h, 0, film_t.data_ptr(), mi._abi.MEM_DEVICE))
+            e0.record()
+            dist.all_reduce(film_t)
+            e1.record()
+            e1.synchronize()
+            t_red = e0.elapsed_time(e1)
+        return st, t_red
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    scene.set_profiling(True)
+    scene.film_clear()
+    for i in range(W):
+        step(i)
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    t0 = time.perf_counter()
+    dev_ms, launches, agg = 0.0, 0, {}
+    for i in range(W, W + K):
+        st, t_red = step(i)
+        dev_ms += st["ms_total"] + t_red
+        launches += st["kernel_launches"] + (1 if world > 1 else 0)
+        for k in ("samples", "closest_rays", "shadow_rays", "segments", "ms_closest", "ms_any", "ms_shade", "ms_raygen", "ms_film"):
+            agg[k] = agg.get(k, 0) + st[k]
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clk = clocks.stop()
+    # max over ranks of the device time and wall time
+    if world > 1:
+        t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, wall_ms = t.tolist()
+    samples_all = npix * spp * K * world
+    value = samples_all / (dev_ms * 1e-3) / 1e6
+
+    # ---- e2e: the user's call with HOST buffers: upload the albedo texture (pinned), render, read the film back
+    tex_id = next(i for i, t in enumerate(sd.textures) if t["type"] == mi._abi.TEX_BITMAP)
+    tex_host = torch.from_numpy(sd.textures[tex_id]["data"].copy()).pin_memory()
+    film_host = torch.empty(npix * 5, dtype=torch.float32).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(W + K, W + 2 * K):
+        scene.update_texture(tex_id, tex_host.numpy())
+        scene.film_clear()
+        step(i)
+        mi._abi.check(mi._abi.lib().mtsb_film_read(scene._h, 0, film_host.data_ptr(), mi._abi.MEM_HOST))
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = t.item()
+    e2e = {"value": samples_all / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(tex_host.numel() * 4),
+           "d2h_bytes_per_step": int(film_host.numel() * 4)}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        # dominant kernel = closest-hit traversal; algorithmic bytes = 48 B per ray (32 B ray in + 16 B hit out)
+        ms_c = max(agg["ms_closest"], 1e-9)
+        achieved = agg["closest_rays"] * 48 / (ms_c * 1e-3) / 1e9
+        stage_ms = {k: agg[k] / K for k in ("ms_raygen", "ms_closest", "ms_shade", "ms_any", "ms_film")}
+        bytes_per_sample = (20 * agg["samples"] + 224 * agg["segments"] + 96 * agg["shadow_rays"]) / max(1, agg["samples"])
+        out = {
+            "metric": "path_tracing_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload]["desc"], "spp_per_step_per_gpu": spp,
+                       "samples_per_step": npix * spp * world, "parallelism": f"spp-sharded x{world} + film all-reduce",
+                       "l2": "queues per step (>1 GB) exceed L2; no flush needed", "timing": "CUDA events on the launching stream, max over ranks"},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes": "48 B/ray x rays per launch", "mrays_per_s": agg["closest_rays"] / (ms_c * 1e-3) / 1e6},
+            "extra": {"wall_ms_per_step": wall_ms / K, "stage_ms_per_step": stage_ms, "rays_per_sample": agg["closest_rays"] / agg["samples"],
+                      "shadow_rays_per_sample": agg["shadow_rays"] / agg["samples"], "algorithmic_bytes_per_sample": bytes_per_sample,
+                      "whole_step_gbs": bytes_per_sample * agg["samples"] / (sum(stage_ms.values()) * K * 1e-3) / 1e9,
+                      "any_hit_mrays_per_s": agg["shadow_rays"] / max(agg["ms_any"], 1e-9) / 1e3,
+                      "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"]},
+                      "scene_setup_s": t_build},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(sd)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
