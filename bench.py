@@ -65,12 +65,14 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
+        inside = [r for t, r in self.rows if (t0 is None or t >= t0) and (t1 is None or t <= t1 + 0.25)]
+        self.rows = inside if inside else [r for _, r in self.rows[-3:]]
         sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -140,7 +142,7 @@ def cpu_baseline(sd_full, budget_s=20.0):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
@@ -193,11 +195,11 @@ def main():
 
     scene.set_profiling(True)
     scene.film_clear()
+    clocks = ClockSampler(local)
+    clocks.start()
     for i in range(W):
         step(i)
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
     t0 = time.perf_counter()
     dev_ms, launches, agg = 0.0, 0, {}
     for i in range(W, W + K):
@@ -207,8 +209,9 @@ def main():
         for k in ("samples", "closest_rays", "shadow_rays", "segments", "ms_closest", "ms_any", "ms_shade", "ms_raygen", "ms_film"):
             agg[k] = agg.get(k, 0) + st[k]
     barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    clk = clocks.stop()
+    t1 = time.perf_counter()
+    wall_ms = (t1 - t0) * 1e3
+    clk = clocks.stop(t0, t1)
     # max over ranks of the device time and wall time
     if world > 1:
         t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)

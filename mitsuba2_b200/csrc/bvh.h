@@ -348,8 +348,9 @@ HD uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
 
 // Intersect the 8 quantised child boxes of `node`; returns the hit mask word: bits 24..31 internal children in
 // near-to-far priority (bit = 24 + (slot ^ octinv)), bits 0..23 candidate triangles.
-HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
-                         float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+// Reference (host / test) formulation: integer -> float conversion per plane.
+HD uint32_t node_hitmask_ref(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                             float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
     float3 p = mk3(u2f(n0.x), u2f(n0.y), u2f(n0.z));
     float sx = u2f(byte_of(n0.w, 0) << 23), sy = u2f(byte_of(n0.w, 1) << 23), sz = u2f(byte_of(n0.w, 2) << 23);
     float3 adir = mk3(sx * idir.x, sy * idir.y, sz * idir.z);
@@ -357,7 +358,6 @@ HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const u
     uint32_t imask = n0.w >> 24;
     uint32_t hit = 0;
     bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
-#pragma unroll
     for (int half = 0; half < 2; ++half) {
         uint32_t meta4 = half ? n1.w : n1.z;
         uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
@@ -365,7 +365,6 @@ HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const u
         uint32_t ax = nx ? hix : lox, bx = nx ? lox : hix;
         uint32_t ay = ny ? hiy : loy, by = ny ? loy : hiy;
         uint32_t az = nz ? hiz : loz, bz = nz ? loz : hiz;
-#pragma unroll
         for (int j = 0; j < 4; ++j) {
             uint32_t meta = byte_of(meta4, j);
             float t0x = fmaf((float) byte_of(ax, j), adir.x, org.x), t1x = fmaf((float) byte_of(bx, j), adir.x, org.x);
@@ -383,6 +382,58 @@ HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const u
     return hit;
 }
 
+#ifdef __CUDA_ARCH__
+// Device formulation: no I2F and no branches.  A quantised byte q is turned into the float 1 + q*2^-15 with one PRMT
+// (byte placed at mantissa bits 8..15 of 1.0f); the plane distance is then one FFMA: t = f*A + B with A = adir*2^15 and
+// B = org - A.  B carries a rounding error <= |adir|*2^-9 (1/512 of a grid cell); the near/far offsets are padded by
+// |adir|*2^-7 so the slab test stays conservative.  Bit positions of the hit mask are derived 4 children at a time.
+__device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                                                 float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+    float sx = __uint_as_float((n0.w & 0xffu) << 23), sy = __uint_as_float((n0.w & 0xff00u) << 15), sz = __uint_as_float((n0.w & 0xff0000u) << 7);
+    float ax_ = sx * idir.x, ay_ = sy * idir.y, az_ = sz * idir.z;
+    float Ax = ax_ * 32768.f, Ay = ay_ * 32768.f, Az = az_ * 32768.f;
+    float ox = (__uint_as_float(n0.x) - o.x) * idir.x - Ax, oy = (__uint_as_float(n0.y) - o.y) * idir.y - Ay, oz = (__uint_as_float(n0.z) - o.z) * idir.z - Az;
+    float px = fabsf(ax_) * 0.0078125f, py = fabsf(ay_) * 0.0078125f, pz = fabsf(az_) * 0.0078125f;
+    float Bnx = ox - px, Bny = oy - py, Bnz = oz - pz, Bfx = ox + px, Bfy = oy + py, Bfz = oz + pz;
+    bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
+    uint32_t octinv4 = octinv * 0x01010101u;
+    uint32_t hit = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        uint32_t meta4 = half ? n1.w : n1.z;
+        uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
+        uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
+        uint32_t ax = nx ? hix : lox, bx = nx ? lox : hix;
+        uint32_t ay = ny ? hiy : loy, by = ny ? loy : hiy;
+        uint32_t az = nz ? hiz : loz, bz = nz ? loz : hiz;
+        uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t sel = 0x7604u | ((uint32_t) j << 4);           // bytes: 0x00, q_j, 0x80, 0x3f
+            float t0x = fmaf(__uint_as_float(__byte_perm(ax, 0x3f800000u, sel)), Ax, Bnx);
+            float t0y = fmaf(__uint_as_float(__byte_perm(ay, 0x3f800000u, sel)), Ay, Bny);
+            float t0z = fmaf(__uint_as_float(__byte_perm(az, 0x3f800000u, sel)), Az, Bnz);
+            float t1x = fmaf(__uint_as_float(__byte_perm(bx, 0x3f800000u, sel)), Ax, Bfx);
+            float t1y = fmaf(__uint_as_float(__byte_perm(by, 0x3f800000u, sel)), Ay, Bfy);
+            float t1z = fmaf(__uint_as_float(__byte_perm(bz, 0x3f800000u, sel)), Az, Bfz);
+            float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            uint32_t bits = ((child_bits4 >> (8 * j)) & 0xffu) << ((bit_index4 >> (8 * j)) & 0xffu);
+            hit |= (tn <= tf) ? bits : 0u;
+        }
+    }
+    return hit;
+}
+#else
+HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                         float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+    return node_hitmask_ref(n0, n1, n2, n3, n4, o, idir, octinv, tmin, tmax);
+}
+#endif
+
 HD uint4 ldg4(const uint4 *p) {
 #ifdef __CUDA_ARCH__
     return __ldg(p);
@@ -397,6 +448,17 @@ HD float4 ldg4f(const float4 *p) {
     return *p;
 #endif
 }
+
+#ifdef MTSB_TRAV_STATS
+static unsigned long long g_trav_nodes = 0, g_trav_tris = 0;
+#endif
+#if defined(MTSB_TRAV_STATS) && !defined(__CUDA_ARCH__)
+#define TRAV_NODE() (g_trav_nodes++)
+#define TRAV_TRI() (g_trav_tris++)
+#else
+#define TRAV_NODE()
+#define TRAV_TRI()
+#endif
 
 template <bool AnyHit, typename Stack>
 HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
@@ -420,6 +482,7 @@ HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, St
             uint32_t slot = (bit - 24u) ^ octinv;
             uint32_t rel = (uint32_t) popc32(G.y & ((1u << slot) - 1u) & 0xffu);
             const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
+            TRAV_NODE();
             uint4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
             uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, o, idir, octinv, mint, tmax);
             G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
@@ -430,6 +493,7 @@ HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, St
                 const float4 *tp = bvh.tris + 3 * (size_t) (tb + b);
                 float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
                 float t, u, v;
+                TRAV_TRI();
                 if (woop_intersect(rw, xyz(a0), xyz(a1), xyz(a2), mint, tmax, t, u, v)) {
                     if (AnyHit) { hit.t = t; return true; }
                     tmax = t; found = true;

@@ -2,6 +2,7 @@
 // the HD functions the CUDA kernels wrap) sequentially on the CPU, so the BVH builder, the compressed-node
 // traversal and the wavefront state machine can be checked against the oracle in the `-m "not gpu"` suite.
 // It is NOT part of the product library and makes no CUDA runtime calls.
+#define MTSB_TRAV_STATS 1
 #include "../../include/mtsb200.h"
 #include "../../mitsuba2_b200/csrc/path.h"
 #include "../../mitsuba2_b200/csrc/host_tables.h"
@@ -127,6 +128,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     return s;
 }
 
+extern "C" void hs_trav_stats(unsigned long long *out, int reset) { out[0] = g_trav_nodes; out[1] = g_trav_tris; if (reset) g_trav_nodes = g_trav_tris = 0; }
 extern "C" void hs_bvh_info(hs_scene *s, uint32_t *nodes, uint32_t *depth) { *nodes = s->bvh_nodes; *depth = s->bvh_depth; }
 
 extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const float *d, float *hits, uint32_t *occ, int any) {
