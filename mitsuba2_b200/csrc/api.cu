@@ -40,6 +40,7 @@ template <typename T> struct DevBuf {
 struct mtsb_ctx {
     int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
     int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
+    unsigned trace_grid = 148 * 8, refill = 24; // persistent traversal launch shape (set in mtsb_ctx_create)
     std::vector<cudaEvent_t> pool;           // event pairs, grown on demand
     std::vector<int> pool_stage; size_t pool_used = 0;
 };
@@ -102,6 +103,15 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
     c->device = device; c->cancel = 0;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1));
+    {   // persistent traversal grid: resident blocks per SM x SM count (tunable for experiments)
+        int sms = 148, per_sm = 8, occ = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<false>, kBlock, 0) == cudaSuccess && occ > 0) per_sm = occ;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow, kBlock, 0) == cudaSuccess && occ > 0 && occ < per_sm) per_sm = occ;
+        if (const char *e = getenv("MTSB_TRACE_BLOCKS_PER_SM")) { int v = atoi(e); if (v > 0 && v <= 32) per_sm = v; }
+        if (const char *e = getenv("MTSB_REFILL")) { int v = atoi(e); if (v >= 0 && v <= 32) c->refill = (unsigned) v; }
+        c->trace_grid = (unsigned) (sms * per_sm);
+    }
     *out = c;
     return MTSB_OK;
 }
@@ -117,6 +127,13 @@ extern "C" int mtsb_cancel(mtsb_ctx *c) { if (c) c->cancel = 1; return MTSB_OK; 
 extern "C" int mtsb_set_profiling(mtsb_ctx *c, int on) { if (!c) return fail(MTSB_E_INVALID, "null context"); c->profiling = on; return MTSB_OK; }
 
 static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) / kBlock); }
+// counters buffer (uint32 words): [0,1024) live paths per depth, [1024,2048) shadow rays per depth,
+// [2048,3072) work-fetch cursor of the closest-hit launch of that depth, [3072,4096) same for the shadow launch
+constexpr uint32_t kCounterWords = 4096, kWorkClosest = 2048, kWorkShadow = 3072;
+static inline unsigned trace_grid_for(const mtsb_ctx *c, size_t n) {
+    unsigned g = grid_for(n);
+    return g < c->trace_grid ? (g ? g : 1u) : c->trace_grid;
+}
 
 // ---------------------------------------------------------------------------------------------------
 // GPU BVH build
@@ -360,7 +377,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
     s->dev.max_depth = d->integrator.max_depth < 0 ? (1 << 30) : d->integrator.max_depth;
     s->dev.rr_depth = d->integrator.rr_depth;
     rc = upload_struct_arrays(s.get()); if (rc) return rc;
-    CU(s->counters.alloc(2048)); CU(s->dstats.alloc(4));
+    CU(s->counters.alloc(kCounterWords)); CU(s->dstats.alloc(4));
     *out = s.release();
     return MTSB_OK;
 }
@@ -408,8 +425,11 @@ static int intersect_common(mtsb_scene *s, uint64_t n, const float *o_mint, cons
     RC(sg.in(o_mint, 4 * n, mem, st, &d_o)); RC(sg.in(d_maxt, 4 * n, mem, st, &d_d));
     if (mode == 1) RC(sg.out(occ, n, mem, &d_occ)); else RC(sg.out(hits, 4 * n, mem, &d_h));
     CU(cudaEventRecord(s->ctx->ev0, st));
-    if (mode == 0) k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr);
-    else if (mode == 1) k_trace<true><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ);
+    uint32_t *work = s->counters.p + kWorkClosest;
+    if (mode != 2) CU(cudaMemsetAsync(work, 0, sizeof(uint32_t), st));
+    unsigned tg = trace_grid_for(s->ctx, n);
+    if (mode == 0) k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill);
+    else if (mode == 1) k_trace<true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill);
     else k_trace_naive<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h);
     CU(cudaEventRecord(s->ctx->ev1, st));
     CU(cudaGetLastError());
@@ -476,16 +496,17 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
         uint32_t n = (uint32_t) ((total - off) < pool ? (total - off) : pool);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total;
         b.seed = seed; b.result = s->result.p;
-        CU(cudaMemsetAsync(s->counters.p, 0, 2048 * sizeof(uint32_t), st));
+        CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
         int cur = 0;
+        const unsigned tg = trace_grid_for(s->ctx, n);
         { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
         for (int depth = 1; depth <= max_iter; ++depth) {
             PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
-            { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr); }
+            { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill); }
             { StageTimer t(s->ctx, ST_SHADE); k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth); }
             launches += 2;
             if (depth < s->dev.max_depth) {
-                { StageTimer t(s->ctx, ST_ANY); k_shadow<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p); }
+                { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
                 launches++;
             }
             cur ^= 1;

@@ -284,34 +284,34 @@ struct Bvh {
     uint32_t n_tris;
 };
 
-struct RayPre {     // Woop et al. 2013 per-ray precomputation (axis permutation folded into selects)
-    float3 o; float Sx, Sy, Sz; int kz;
-};
-HD float3 permute(float3 v, int kz, bool flip) {
-    // returns (v[kx], v[ky], v[kz]) with kx=(kz+1)%3, ky=(kx+1)%3, swapped if `flip`
-    float a = kz == 0 ? v.y : (kz == 1 ? v.z : v.x);
-    float b = kz == 0 ? v.z : (kz == 1 ? v.x : v.y);
-    float c = kz == 0 ? v.x : (kz == 1 ? v.y : v.z);
-    return flip ? mk3(b, a, c) : mk3(a, b, c);
-}
-struct RayWoop { float3 o; float Sx, Sy, Sz; int kz; bool flip; };
+// Woop et al. 2013 watertight test.  The per-ray axis permutation + shear is folded into three row vectors so the
+// per-triangle work is branch-free FMAs: rx = e_kx - Sx e_kz, ry = e_ky - Sy e_kz, rz = Sz e_kz (kx/ky swapped when
+// d[kz] < 0 to keep the winding).  Zero coefficients multiply exactly, so shared vertices still map to identical
+// sheared coordinates and shared edges stay watertight.
+struct RayWoop { float3 rx, ry, rz; };
+HD float3 axis3(int k, float s) { return mk3(k == 0 ? s : 0.f, k == 1 ? s : 0.f, k == 2 ? s : 0.f); }
 HD RayWoop woop_setup(float3 o, float3 d) {
-    RayWoop r; r.o = o;
+    RayWoop r; (void) o;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-    r.kz = (ax > ay) ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
-    float dz = r.kz == 0 ? d.x : (r.kz == 1 ? d.y : d.z);
-    r.flip = dz < 0.f;
-    float3 dp = permute(d, r.kz, r.flip);
-    r.Sx = dp.x / dp.z; r.Sy = dp.y / dp.z; r.Sz = 1.f / dp.z;
+    int kz = (ax > ay) ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    int kx = kz == 2 ? 0 : kz + 1, ky = kx == 2 ? 0 : kx + 1;
+    float dz = kz == 0 ? d.x : (kz == 1 ? d.y : d.z);
+    if (dz < 0.f) { int tmp = kx; kx = ky; ky = tmp; }
+    float dx = kx == 0 ? d.x : (kx == 1 ? d.y : d.z), dy = ky == 0 ? d.x : (ky == 1 ? d.y : d.z);
+    float Sx = dx / dz, Sy = dy / dz, Sz = 1.f / dz;
+    r.rx = axis3(kx, 1.f) + axis3(kz, -Sx);
+    r.ry = axis3(ky, 1.f) + axis3(kz, -Sy);
+    r.rz = axis3(kz, Sz);
     return r;
 }
+HD float dot3f(float3 a, float3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
 // returns true on hit in [mint, maxt]; (bu,bv) = barycentrics of v1, v2 (Mitsuba's si.uv convention, mesh.cpp:404-407)
-HD bool woop_intersect(const RayWoop &r, float3 v0, float3 v1, float3 v2, float mint, float maxt,
+HD bool woop_intersect(const RayWoop &r, float3 o, float3 v0, float3 v1, float3 v2, float mint, float maxt,
                        float &t, float &bu, float &bv) {
-    float3 A = permute(v0 - r.o, r.kz, r.flip), B = permute(v1 - r.o, r.kz, r.flip), C = permute(v2 - r.o, r.kz, r.flip);
-    float Ax = fmaf(-r.Sx, A.z, A.x), Ay = fmaf(-r.Sy, A.z, A.y);
-    float Bx = fmaf(-r.Sx, B.z, B.x), By = fmaf(-r.Sy, B.z, B.y);
-    float Cx = fmaf(-r.Sx, C.z, C.x), Cy = fmaf(-r.Sy, C.z, C.y);
+    float3 A = v0 - o, B = v1 - o, C = v2 - o;
+    float Ax = dot3f(r.rx, A), Ay = dot3f(r.ry, A);
+    float Bx = dot3f(r.rx, B), By = dot3f(r.ry, B);
+    float Cx = dot3f(r.rx, C), Cy = dot3f(r.ry, C);
     float U = Cx * By - Cy * Bx, V = Ax * Cy - Ay * Cx, W = Bx * Ay - By * Ax;
     if (U == 0.f || V == 0.f || W == 0.f) {
         double CxBy = (double) Cx * (double) By, CyBx = (double) Cy * (double) Bx;
@@ -324,7 +324,7 @@ HD bool woop_intersect(const RayWoop &r, float3 v0, float3 v1, float3 v2, float 
     if ((U < 0.f || V < 0.f || W < 0.f) && (U > 0.f || V > 0.f || W > 0.f)) return false;
     float det = U + V + W;
     if (det == 0.f) return false;
-    float T = U * (r.Sz * A.z) + V * (r.Sz * B.z) + W * (r.Sz * C.z);
+    float T = U * dot3f(r.rz, A) + V * dot3f(r.rz, B) + W * dot3f(r.rz, C);
     float inv = 1.f / det;
     float tt = T * inv;
     if (!(tt >= mint && tt <= maxt)) return false;
@@ -338,7 +338,7 @@ struct Hit { float t, u, v; uint32_t prim; };
 template <int NFast, int NSlow> struct TravStack {
     uint2 *fast; int stride;       // fast[i*stride]
     uint2 slow[NSlow];
-    int sp = 0;
+    int sp;
     HD void push(uint2 v) { if (sp < NFast) fast[sp * stride] = v; else if (sp - NFast < NSlow) slow[sp - NFast] = v; sp++; }
     HD uint2 pop() { sp--; return sp < NFast ? fast[sp * stride] : slow[(sp - NFast) < NSlow ? (sp - NFast) : NSlow - 1]; }
     HD bool empty() const { return sp == 0; }
@@ -460,53 +460,88 @@ static unsigned long long g_trav_nodes = 0, g_trav_tris = 0;
 #define TRAV_TRI()
 #endif
 
-template <bool AnyHit, typename Stack>
-HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
-    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.prim = 0xffffffffu;
-    if (bvh.n_tris == 0) return false;
+// Traversal state of one ray.  `trav_step` advances it by one node visit (plus the triangles that visit selected), so a
+// kernel can interleave rays on a lane (persistent threads with dynamic fetch) while the host simulator just loops.
+template <typename Stack> struct Trav {
+    float3 o, idir; RayWoop rw;
+    float mint, tmax;
+    uint32_t octinv;
+    uint2 G;            // current node group: x = first child index, y = hits<<24 | imask
+    Hit hit; bool found;
+    Stack st;
+};
+
+template <typename Stack>
+HD void trav_init(Trav<Stack> &tr, float3 o, float3 d, float mint, float maxt) {
     const float big = 1e30f;
-    float3 idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x),
-                      fabsf(d.y) > 1e-30f ? 1.f / d.y : copysignf(big, d.y),
-                      fabsf(d.z) > 1e-30f ? 1.f / d.z : copysignf(big, d.z));
+    tr.o = o;
+    tr.idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x),
+                  fabsf(d.y) > 1e-30f ? 1.f / d.y : copysignf(big, d.y),
+                  fabsf(d.z) > 1e-30f ? 1.f / d.z : copysignf(big, d.z));
     uint32_t oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
-    uint32_t octinv = 7u ^ oct;
-    RayWoop rw = woop_setup(o, d);
-    float tmax = maxt;
-    bool found = false;
-    uint2 G = make_uint2(0u, 0x80000000u);
-    while (true) {
-        if (G.y & 0xff000000u) {
-            uint32_t bit = 31u - (uint32_t) clz32(G.y);
-            G.y &= ~(1u << bit);
-            if (G.y & 0xff000000u) st.push(G);
-            uint32_t slot = (bit - 24u) ^ octinv;
-            uint32_t rel = (uint32_t) popc32(G.y & ((1u << slot) - 1u) & 0xffu);
-            const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
-            TRAV_NODE();
-            uint4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
-            uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, o, idir, octinv, mint, tmax);
-            G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
-            uint32_t tb = n1.y, tm = hm & 0x00ffffffu;
-            while (tm) {
-                uint32_t b = 31u - (uint32_t) clz32(tm);
-                tm &= ~(1u << b);
-                const float4 *tp = bvh.tris + 3 * (size_t) (tb + b);
-                float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
-                float t, u, v;
-                TRAV_TRI();
-                if (woop_intersect(rw, xyz(a0), xyz(a1), xyz(a2), mint, tmax, t, u, v)) {
-                    if (AnyHit) { hit.t = t; return true; }
-                    tmax = t; found = true;
-                    hit.t = t; hit.u = u; hit.v = v; hit.prim = f2u(a0.w);
-                }
+    tr.octinv = 7u ^ oct;
+    tr.rw = woop_setup(o, d);
+    tr.mint = mint; tr.tmax = maxt;
+    tr.found = false;
+    tr.hit.t = INFINITY; tr.hit.u = 0.f; tr.hit.v = 0.f; tr.hit.prim = 0xffffffffu;
+    tr.G = make_uint2(0u, 0x80000000u);
+    tr.st.sp = 0;
+}
+
+// returns true when the ray is finished (closest: stack exhausted; any-hit: first hit or stack exhausted)
+template <bool AnyHit, typename Stack>
+HD bool trav_step(const Bvh &bvh, Trav<Stack> &tr) {
+    uint2 G = tr.G;
+    if (G.y & 0xff000000u) {
+        uint32_t bit = 31u - (uint32_t) clz32(G.y);
+        G.y &= ~(1u << bit);
+        if (G.y & 0xff000000u) tr.st.push(G);
+        uint32_t slot = (bit - 24u) ^ tr.octinv;
+        uint32_t rel = (uint32_t) popc32(G.y & ((1u << slot) - 1u) & 0xffu);
+        const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
+        TRAV_NODE();
+        uint4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
+        uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, tr.o, tr.idir, tr.octinv, tr.mint, tr.tmax);
+        G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+        uint32_t tb = n1.y, tm = hm & 0x00ffffffu;
+        while (tm) {
+            uint32_t b = 31u - (uint32_t) clz32(tm);
+            tm &= ~(1u << b);
+            const float4 *tp = bvh.tris + 3 * (size_t) (tb + b);
+            float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
+            float t, u, v;
+            TRAV_TRI();
+            if (woop_intersect(tr.rw, tr.o, xyz(a0), xyz(a1), xyz(a2), tr.mint, tr.tmax, t, u, v)) {
+                tr.found = true;
+                tr.hit.t = t;
+                if (AnyHit) return true;
+                tr.tmax = t;
+                tr.hit.u = u; tr.hit.v = v; tr.hit.prim = f2u(a0.w);
             }
         }
-        if ((G.y & 0xff000000u) == 0) {
-            if (st.empty()) break;
-            G = st.pop();
-        }
     }
-    return found;
+    if ((G.y & 0xff000000u) == 0) {
+        if (tr.st.empty()) return true;
+        G = tr.st.pop();
+    }
+    tr.G = G;
+    return false;
+}
+
+template <bool AnyHit, typename Stack>
+HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Trav<Stack> &tr, Hit &hit) {
+    trav_init(tr, o, d, mint, maxt);
+    if (bvh.n_tris != 0)
+        while (!trav_step<AnyHit>(bvh, tr)) { }
+    hit = tr.hit;
+    return tr.found;
+}
+
+// convenience form used by the host simulator: caller supplies only the stack storage
+template <bool AnyHit, typename Stack>
+HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
+    Trav<Stack> tr; tr.st.fast = st.fast; tr.st.stride = st.stride;
+    return bvh_trace<AnyHit>(bvh, o, d, mint, maxt, tr, hit);
 }
 
 } // namespace mtsb

@@ -49,20 +49,78 @@ __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
 }
 
 // ---------------- traversal ----------------------------------------------------------------------
+// Persistent-warp traversal with dynamic ray fetch (after Aila & Laine 2009): the grid is sized to fill the SMs once;
+// every warp claims chunks of kFetchChunk consecutive rays from a global work counter and hands them to lanes whose
+// previous ray has finished as soon as fewer than `refill` lanes are still traversing, so short rays do not leave
+// lanes idle until the longest ray of the warp is done.  `Sink` consumes a finished ray.
+constexpr uint32_t kFetchChunk = 64;
+#ifndef MTSB_TRACE_BLOCKS
+#define MTSB_TRACE_BLOCKS 8
+#endif
+constexpr int kTraceBlocksPerSM = MTSB_TRACE_BLOCKS;
+template <bool AnyHit, typename Sink>
+__device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count, const float4 *__restrict__ o_mint,
+                                                 const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill,
+                                                 uint2 *s_stack, Sink sink) {
+    typedef TravStack<kStackFast, kStackSlow> Stack;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    Trav<Stack> tr; tr.st.fast = s_stack + threadIdx.x; tr.st.stride = kBlock; tr.st.sp = 0;
+    bool active = false, exhausted = (count == 0 || bvh.n_tris == 0);
+    uint32_t ray = 0, w_next = 0, w_end = 0;
+    if (bvh.n_tris == 0) {      // empty scene: every ray misses
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+            Hit h; h.t = INFINITY; h.u = h.v = 0.f; h.prim = 0xffffffffu;
+            sink(i, false, h);
+        }
+        return;
+    }
+    while (true) {
+        uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && !exhausted) {
+            if (w_next == w_end) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(work, kFetchChunk);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                w_next = min(base, count); w_end = min(base + kFetchChunk, count);
+                if (w_next == w_end) exhausted = true;
+            }
+            uint32_t take = min((uint32_t) __popc(idle), w_end - w_next);
+            uint32_t r = (uint32_t) __popc(idle & lt);
+            if (!active && r < take) {
+                ray = w_next + r;
+                float4 o = o_mint[ray], d = d_maxt[ray];
+                trav_init(tr, xyz(o), xyz(d), o.w, d.w);
+                active = true;
+            }
+            w_next += take;
+        }
+        if (__ballot_sync(0xffffffffu, active) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        while (true) {
+            if (active && trav_step<AnyHit>(bvh, tr)) {
+                sink(ray, tr.found, tr.hit);
+                active = false;
+            }
+            uint32_t a = __ballot_sync(0xffffffffu, active);
+            if (a == 0u || (!exhausted && (uint32_t) __popc(a) < refill)) break;
+        }
+    }
+}
+
 template <bool AnyHit>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_trace(Bvh bvh, const uint32_t *count_ptr, uint32_t count_max, const float4 *__restrict__ o_mint,
-        const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded) {
+        const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded,
+        uint32_t *work, uint32_t refill) {
     __shared__ uint2 s_stack[kStackFast * kBlock];
     uint32_t count = count_ptr ? min(*count_ptr, count_max) : count_max;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        float4 o = o_mint[i], d = d_maxt[i];
-        TravStack<kStackFast, kStackSlow> st; st.fast = s_stack + threadIdx.x; st.stride = kBlock;
-        Hit h;
-        bool found = bvh_trace<AnyHit>(bvh, xyz(o), xyz(d), o.w, d.w, st, h);
-        if (AnyHit) occluded[i] = found ? 1u : 0u;
-        else hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
-    }
+    trace_persistent<AnyHit>(bvh, count, o_mint, d_maxt, work, refill, s_stack,
+        [=](uint32_t i, bool found, const Hit &h) {
+            if (AnyHit) occluded[i] = found ? 1u : 0u;
+            else hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+        });
 }
 // brute force = Scene::ray_intersect_naive (kdtree.h:2304-2329) with the same triangle test
 __global__ void k_trace_naive(Bvh bvh, uint32_t count, const float4 *o_mint, const float4 *d_maxt, float4 *hits) {
@@ -75,7 +133,7 @@ __global__ void k_trace_naive(Bvh bvh, uint32_t count, const float4 *o_mint, con
     for (uint32_t k = 0; k < bvh.n_tris; ++k) {
         float4 a0 = bvh.tris[3 * k], a1 = bvh.tris[3 * k + 1], a2 = bvh.tris[3 * k + 2];
         float t, u, v;
-        if (woop_intersect(rw, xyz(a0), xyz(a1), xyz(a2), o.w, tmax, t, u, v)) { tmax = t; h.t = t; h.u = u; h.v = v; h.prim = f2u(a0.w); }
+        if (woop_intersect(rw, xyz(o), xyz(a0), xyz(a1), xyz(a2), o.w, tmax, t, u, v)) { tmax = t; h.t = t; h.u = u; h.v = v; h.prim = f2u(a0.w); }
     }
     hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
 }
@@ -118,24 +176,21 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
 }
 
 // any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *stats, uint32_t depth, uint32_t count_max,
-         float4 *result) {
+         float4 *result, uint32_t *work, uint32_t refill) {
     __shared__ uint2 s_stack[kStackFast * kBlock];
     uint32_t count = min(counters[1024 + depth], count_max);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[1], (unsigned long long) count);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        float4 o = sq.o_mint[i], d = sq.d_maxt[i];
-        TravStack<kStackFast, kStackSlow> st; st.fast = s_stack + threadIdx.x; st.stride = kBlock;
-        Hit h;
-        if (!bvh_trace<true>(bvh, xyz(o), xyz(d), o.w, d.w, st, h)) {
+    trace_persistent<true>(bvh, count, sq.o_mint, sq.d_maxt, work, refill, s_stack,
+        [=](uint32_t i, bool found, const Hit &) {
+            if (found) return;
             float4 c = sq.contrib_id[i];
-            uint32_t pid = f2u(c.w);
+            uint32_t pid = f2u(c.w);            // one shadow ray per path and depth: no concurrent writer
             float4 r = result[pid];
             r.x += c.x; r.y += c.y; r.z += c.z;
             result[pid] = r;
-        }
-    }
+        });
 }
 
 __device__ __forceinline__ void film_atomic_add(const SensorDev &sn, uint32_t pix, float4 v, float w) {
