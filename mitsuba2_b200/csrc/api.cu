@@ -40,7 +40,7 @@ template <typename T> struct DevBuf {
 struct mtsb_ctx {
     int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
     int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
-    unsigned trace_grid = 148 * 8, refill = 24; // persistent traversal launch shape (set in mtsb_ctx_create)
+    unsigned trace_grid = 148 * 8, refill = 22; // persistent traversal launch shape (set in mtsb_ctx_create)
     std::vector<cudaEvent_t> pool;           // event pairs, grown on demand
     std::vector<int> pool_stage; size_t pool_used = 0;
 };
