@@ -980,3 +980,31 @@ void orc_scene_update_vertices(orc_scene *s, uint32_t mesh_id, const float *posi
     for (uint32_t i = 0; i < s->n_emitters; ++i) if (s->emitters[i].type == MTSB_EMITTER_AREA) build_area_cdf(s, &s->emitters[i]);
     update_bsphere(s);
 }
+
+/* =============================================================================================== */
+/* Distribution hooks (unit parity against the reference's Hierarchical2D / DiscreteDistribution)   */
+/* =============================================================================================== */
+static void free_h2d(oh2d *t) { for (int i = 0; i < t->n_levels; ++i) free(t->levels[i]); free(t->levels); free(t->widths); }
+void orc_h2d_sample(const float *data, uint32_t w, uint32_t h, uint64_t n, const float *s2, float *out3) {
+    oemitter e; memset(&e, 0, sizeof(e)); e.w = w; e.h = h; build_h2d(&e.warp, data, w, h);
+    for (uint64_t i = 0; i < n; ++i) h2d_sample(&e, s2[2 * i], s2[2 * i + 1], &out3[3 * i], &out3[3 * i + 1], &out3[3 * i + 2]);
+    free_h2d(&e.warp);
+}
+void orc_h2d_eval(const float *data, uint32_t w, uint32_t h, uint64_t n, const float *uv, float *out) {
+    oemitter e; memset(&e, 0, sizeof(e)); e.w = w; e.h = h; build_h2d(&e.warp, data, w, h);
+    for (uint64_t i = 0; i < n; ++i) out[i] = h2d_eval(&e, uv[2 * i], uv[2 * i + 1]);
+    free_h2d(&e.warp);
+}
+/* DiscreteDistribution::sample_reuse (distr_1d.h:49-88 update, :144-203 sample): the same arithmetic the area-light
+ * triangle pick uses (area_sample_direction above), exposed on a bare pmf */
+void orc_discrete_sample_reuse(const float *pmf, uint32_t n_pmf, uint64_t n, const float *u, uint32_t *idx, float *u_out) {
+    float *cdf = malloc(sizeof(float) * (n_pmf ? n_pmf : 1)); double sum = 0.0; uint32_t lo = (uint32_t) -1, hi = (uint32_t) -1;
+    for (uint32_t i = 0; i < n_pmf; ++i) { sum += (double) pmf[i]; cdf[i] = (float) sum; if (pmf[i] > 0.f) { if (lo == (uint32_t) -1) lo = i; hi = i; } }
+    float fsum = (float) sum, norm = (float) (1.0 / sum);
+    for (uint64_t k = 0; k < n; ++k) {
+        uint32_t j = ek_binary_search(lo, hi, cdf, u[k] * fsum);
+        float p = pmf[j] * norm, prev = j > 0 ? cdf[j - 1] * norm : 0.f;
+        idx[k] = j; u_out[k] = (u[k] - prev) / p;
+    }
+    free(cdf);
+}

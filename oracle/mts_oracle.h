@@ -45,6 +45,11 @@ float orc_erfinv(float x);
 float orc_rfilter_eval(int type, float radius, float stddev, float x);
 void orc_perspective_sample_to_camera(float x_fov_deg, float near_clip, float far_clip, float aspect, float *out16);
 
+/* distribution hooks: Hierarchical2D (distr_2d.h) over a w x h float image, DiscreteDistribution::sample_reuse (distr_1d.h) */
+void orc_h2d_sample(const float *data, uint32_t w, uint32_t h, uint64_t n, const float *s2, float *out3 /* u, v, pdf */);
+void orc_h2d_eval(const float *data, uint32_t w, uint32_t h, uint64_t n, const float *uv, float *out);
+void orc_discrete_sample_reuse(const float *pmf, uint32_t n_pmf, uint64_t n, const float *u, uint32_t *idx, float *u_out);
+
 /* scene */
 orc_scene *orc_scene_create(const mtsb_scene_desc *desc);
 void orc_scene_destroy(orc_scene *s);

@@ -314,3 +314,139 @@ def material_scene(res=(48, 32), spp=8, envmap=True, area=True):
     sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
     sd.max_depth, sd.rr_depth, sd.spp = 6, 5, spp
     return sd
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Reference header-only arithmetic (oracle/_ref/libmts_ref.so, built by `make -C oracle ref` where /root/reference
+# exists) and the matching oracle entry points, driven through one table so that the golden-vector generator
+# (tests/golden/make_ref_vectors.py) and the tests run exactly the same cases.
+# ---------------------------------------------------------------------------------------------------------------
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libmts_ref.so")
+
+
+def _bind_math(l, prefix):
+    f = C.c_float
+    sig = {
+        "pcg32_floats": (None, [C.c_uint64, vp, vp, C.c_uint32, vp]),
+        "tea32": (C.c_uint32, [C.c_uint32, C.c_uint32, C.c_int]),
+        "tea64": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_int]),
+        "square_to_uniform_disk_concentric": (None, [f, f, vp]),
+        "square_to_cosine_hemisphere": (None, [f, f, vp]),
+        "square_to_uniform_triangle": (None, [f, f, vp]),
+        "coordinate_system": (None, [vp, vp, vp]),
+        "fresnel": (None, [f, f, vp]),
+        "fresnel_conductor": (f, [f, f, f]),
+        "microfacet_eval": (f, [C.c_int, f, f, vp]),
+        "microfacet_pdf": (f, [C.c_int, f, f, C.c_int, vp, vp]),
+        "microfacet_smith_g1": (f, [C.c_int, f, f, vp, vp]),
+        "microfacet_sample": (None, [C.c_int, f, f, C.c_int, vp, f, f, vp]),
+        "erfinv": (f, [f]),
+        "perspective_sample_to_camera": (None, [f, f, f, f, vp]),
+        "h2d_sample": (None, [vp, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]),
+        "h2d_eval": (None, [vp, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]),
+        "discrete_sample_reuse": (None, [vp, C.c_uint32, C.c_uint64, vp, vp, vp]),
+    }
+    out = {}
+    for name, (res, args) in sig.items():
+        fn = getattr(l, prefix + name)
+        fn.restype = res
+        fn.argtypes = args
+        out[name] = fn
+    return out
+
+
+def oracle_math():
+    return _bind_math(Oracle.lib(), "orc_")
+
+
+def ref_math():
+    """None when the reference harness has not been built (e.g. on the GPU box)."""
+    if not os.path.exists(REF_SO):
+        return None
+    return _bind_math(C.CDLL(REF_SO), "ref_")
+
+
+def _hemi(rng, n):
+    v = rng.normal(size=(n, 3)).astype(np.float32)
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    v[:, 2] = np.abs(v[:, 2])
+    return v
+
+
+def math_cases(fn, seed=11):
+    """Run every unit case through the function table `fn` (oracle_math() or ref_math()); returns {name: ndarray}."""
+    rng = np.random.default_rng(seed)
+    R = {}
+    st = rng.integers(0, 2**63, size=8, dtype=np.uint64)
+    sq = rng.integers(0, 2**63, size=8, dtype=np.uint64)
+    st[0], sq[0] = 0x853c49e6748fea9b, 0xda3e39cb94b95bdb          # PCG32 defaults (enoki random.h)
+    out = np.zeros((8, 16), np.float32)
+    fn["pcg32_floats"](8, _p(st), _p(sq), 16, _p(out))
+    R["pcg32_floats"] = out
+    v = rng.integers(0, 2**32, size=(32, 2), dtype=np.uint64)
+    v[:8] = [[1, 1], [1, 2], [1, 3], [1, 4], [1, 5], [2, 1], [3, 1], [4, 1]]      # test_random.py:6-28
+    R["tea32"] = np.array([fn["tea32"](int(a), int(b), 4) for a, b in v], np.uint32)
+    R["tea64"] = np.array([fn["tea64"](int(a), int(b), 4) for a, b in v], np.uint64)
+    s2 = rng.random((64, 2), dtype=np.float32)
+    s2[:4] = [[0, 0], [0.5, 0.5], [1, 1], [0.25, 0.75]]
+    for name, k in (("square_to_uniform_disk_concentric", 2), ("square_to_cosine_hemisphere", 3), ("square_to_uniform_triangle", 2)):
+        o = np.zeros((64, k), np.float32)
+        for i in range(64):
+            fn[name](float(s2[i, 0]), float(s2[i, 1]), _p(o[i]))
+        R[name] = o
+    nrm = rng.normal(size=(32, 3)).astype(np.float32)
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    nrm[:3] = [[0, 0, 1], [0, 0, -1], [1, 0, 0]]
+    cs = np.zeros((32, 6), np.float32)
+    for i in range(32):
+        fn["coordinate_system"](_p(nrm[i]), _p(cs[i, :3]), _p(cs[i, 3:]))
+    R["coordinate_system"] = cs
+    fr = []
+    for eta in (1.5, 1 / 1.5, 1.0, 1.33):
+        for c in np.linspace(-1, 1, 41, dtype=np.float32):
+            o = np.zeros(4, np.float32)
+            fn["fresnel"](float(c), float(np.float32(eta)), _p(o))
+            fr.append(o)
+    R["fresnel"] = np.array(fr)
+    R["fresnel_conductor"] = np.array([fn["fresnel_conductor"](float(c), float(np.float32(e)), float(np.float32(k)))
+                                       for e, k in ((0.2, 3.9), (1.5, 0.0), (1.657, 9.22), (0.27, 3.6))
+                                       for c in np.linspace(0, 1, 21, dtype=np.float32)], np.float32)
+    wi, m = _hemi(rng, 16), _hemi(rng, 16)
+    wi[0] = [0, 0, 1]
+    ev, pd, g1, sm = [], [], [], []
+    for t in (0, 1):
+        for au, av in ((0.1, 0.1), (0.1, 0.3), (0.5, 0.5), (0.05, 0.2)):
+            au, av = float(np.float32(au)), float(np.float32(av))
+            for i in range(16):
+                ev.append(fn["microfacet_eval"](t, au, av, _p(m[i])))
+                g1.append(fn["microfacet_smith_g1"](t, au, av, _p(wi[i]), _p(m[i])))
+                for vis in (0, 1):
+                    pd.append(fn["microfacet_pdf"](t, au, av, vis, _p(wi[i]), _p(m[i])))
+                    o = np.zeros(4, np.float32)
+                    fn["microfacet_sample"](t, au, av, vis, _p(wi[i]), float(s2[i + 8, 0]), float(s2[i + 8, 1]), _p(o))
+                    sm.append(o)
+    R["microfacet_eval"], R["microfacet_pdf"] = np.array(ev, np.float32), np.array(pd, np.float32)
+    R["microfacet_smith_g1"], R["microfacet_sample"] = np.array(g1, np.float32), np.array(sm)
+    R["erfinv"] = np.array([fn["erfinv"](float(x)) for x in np.linspace(-0.999, 0.999, 101, dtype=np.float32)], np.float32)
+    ps = []
+    for fov, near, far, asp in ((45.0, 0.01, 100.0, 16 / 9), (39.3077, 0.001, 100.0, 1.0), (90.0, 1.0, 10.0, 0.5)):
+        o = np.zeros(16, np.float32)
+        fn["perspective_sample_to_camera"](float(np.float32(fov)), float(np.float32(near)), float(np.float32(far)), float(np.float32(asp)), _p(o))
+        ps.append(o)
+    R["perspective_sample_to_camera"] = np.array(ps)
+    for tag, (w, h) in (("a", (17, 9)), ("b", (64, 32)), ("c", (33, 47))):
+        img = (rng.random((h, w), dtype=np.float32) ** 4 * 10 + 0.01).astype(np.float32)
+        s = rng.random((256, 2), dtype=np.float32)
+        o3 = np.zeros((256, 3), np.float32)
+        fn["h2d_sample"](_p(img), w, h, 256, _p(s), _p(o3))
+        R["h2d_sample_" + tag] = o3
+        o1 = np.zeros(256, np.float32)
+        fn["h2d_eval"](_p(img), w, h, 256, _p(s), _p(o1))
+        R["h2d_eval_" + tag] = o1
+    pmf = rng.random(37, dtype=np.float32)
+    pmf[[0, 5, 6, 36]] = 0
+    u = rng.random(256, dtype=np.float32)
+    idx, uo = np.zeros(256, np.uint32), np.zeros(256, np.float32)
+    fn["discrete_sample_reuse"](_p(pmf), 37, 256, _p(u), _p(idx), _p(uo))
+    R["discrete_idx"], R["discrete_u"] = idx, uo
+    return R
