@@ -184,6 +184,30 @@ class Scene:
         A.check(A.lib().mtsb_film_device_ptr(self._h, sensor, C.byref(p), C.byref(n)))
         return p.value, n.value
 
+    def render_xyzaw_tensor(self, spp_begin, spp_count, spp_total, seed=0, sensor=0):
+        """Clear the film, render sample indices [spp_begin, spp_begin+spp_count) and return the packed XYZAW sums as
+        a flat torch CUDA tensor (device-to-device copy; the form `distributed.render_sharded` reduces over NCCL)."""
+        import torch
+        h, w = self._film_shape(sensor)
+        film = torch.empty(h * w * 5, dtype=torch.float32, device=f"cuda:{self.device}")
+        self.film_clear(sensor)
+        if spp_count > 0:
+            self.render_accumulate(sensor, spp_count, seed, spp_begin, spp_total)
+        A.check(A.lib().mtsb_film_read(self._h, sensor, C.c_void_p(film.data_ptr()), A.MEM_DEVICE))
+        return film
+
+    def render_distributed(self, sensor=0, spp=None, seed=0, group=None):
+        """`Integrator.render` over all ranks of the process group: every rank renders its share of the sample
+        indices, the film sums are all-reduced (NCCL) and installed as this rank's film; returns linear RGB."""
+        import torch
+        from . import distributed as D
+        spp = int(self.data.spp if spp is None else spp)
+        film = D.render_sharded(lambda b, c, t, sd: self.render_xyzaw_tensor(b, c, t, sd, sensor), spp, seed, group)
+        torch.cuda.synchronize(self.device)
+        self.film_clear(sensor)
+        A.check(A.lib().mtsb_film_accumulate(self._h, sensor, C.c_void_p(film.data_ptr()), A.MEM_DEVICE))
+        return self.film_develop(sensor)
+
     def film_put(self, pos, values, sensor=0):
         """``ImageBlock::put(pos, value)`` batched: pos (n,2), values (n,5)."""
         pos = np.ascontiguousarray(pos, np.float32)

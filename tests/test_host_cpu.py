@@ -1,0 +1,202 @@
+"""CPU tests (no GPU): the C-ABI library loads and exports everything include/mtsb200.h declares, the product's
+stage bodies (compiled for the host by tests/hostsim) agree with the oracle, the host-side mirror (loaders, scene
+description) behaves like the reference's, and the multi-rank sharding logic reduces to the single-rank film (gloo)."""
+import ctypes as C
+import os
+import re
+import socket
+import tempfile
+
+import numpy as np
+import pytest
+
+import helpers as H
+from helpers import HostSim, Oracle
+from mitsuba2_b200 import _abi as A
+from mitsuba2_b200 import distributed as D
+from mitsuba2_b200 import mesh as M
+from mitsuba2_b200 import xml as X
+from mitsuba2_b200.scenedata import SceneData, look_at, perspective_sample_to_camera
+
+
+# ---- C ABI ---------------------------------------------------------------------------------------------------------
+def _declared_functions():
+    txt = open(os.path.join(H.ROOT, "include", "mtsb200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(mtsb_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_abi_exports_every_declared_symbol():
+    lib = A.lib()
+    names = _declared_functions()
+    assert len(names) >= 25
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    bound = {n for n, _, _ in A.SYMBOLS}
+    assert set(names) == bound, set(names) ^ bound       # the ctypes mirror binds exactly the header
+    ver = int(re.search(r"#define\s+MTSB_ABI_VERSION\s+(\d+)", open(os.path.join(H.ROOT, "include", "mtsb200.h")).read()).group(1))
+    assert lib.mtsb_abi_version() == ver
+
+
+def test_abi_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    ctx = C.c_void_p()
+    rc = A.lib().mtsb_ctx_create(0, C.byref(ctx))
+    assert rc != 0
+    assert A.lib().mtsb_last_error()
+    with pytest.raises(RuntimeError):
+        import mitsuba2_b200 as mi
+        mi.Scene(H.sphere_scene())
+
+
+# ---- product stage bodies on the host vs the oracle ---------------------------------------------------------------
+@pytest.mark.parametrize("which", ["sphere", "cbox", "material"])
+def test_hostsim_hit_ids_match_oracle(which):
+    sd = {"sphere": H.sphere_scene, "cbox": H.cbox_scene, "material": H.material_scene}[which]()
+    o, h = Oracle(sd), HostSim(sd)
+    om, dm = H.random_rays(20000, 5, radius={"sphere": 1.5, "cbox": 0.9, "material": 3.0}[which])
+    if which == "cbox":
+        om[:, :3] = om[:, :3] * np.float32(250) + np.float32([278, 273, 280])
+    a, b = o.intersect_closest(om, dm), h.intersect_closest(om, dm)
+    pa, pb = a.view(np.uint32)[:, 3], b.view(np.uint32)[:, 3]
+    assert np.mean(pa != pb) < 5e-3                       # Moeller-Trumbore vs watertight: only edge/tie rays differ
+    same = (pa == pb) & (pa != 0xffffffff)
+    np.testing.assert_allclose(a[same, 0], b[same, 0], rtol=3e-4, atol=1e-5)   # grazing hits are ill-conditioned in t
+    assert np.mean(o.intersect_any(om, dm) != h.intersect_any(om, dm)) < 5e-3
+    hn = o.intersect_closest(om[:2000], dm[:2000], naive=True)      # Scene::ray_intersect_naive (kdtree.h:2304-2329)
+    assert np.mean(hn.view(np.uint32)[:, 3] != pa[:2000]) < 5e-3
+
+
+def test_hostsim_bvh_shape():
+    n, depth = HostSim(H.sphere_scene()).bvh_info()
+    assert n >= 1 and 1 <= depth <= 64
+
+
+@pytest.mark.parametrize("rfilter", ["box", "gaussian", "tent"])
+def test_hostsim_cbox_film_matches_oracle(rfilter):
+    sd = H.cbox_scene(res=16, spp=4, rfilter=rfilter)
+    a, b = Oracle(sd).render_xyzaw(seed=3), HostSim(sd).render_xyzaw(seed=3)
+    assert np.abs(a - b).max() < 2e-3 * max(1.0, np.abs(a).max())
+
+
+def test_hostsim_material_film_close_to_oracle():
+    sd = H.material_scene(res=(24, 16), spp=4)
+    a, b = Oracle(sd).render_xyzaw(seed=1), HostSim(sd).render_xyzaw(seed=1)
+    bad = np.abs(a - b).max(axis=2) > 1e-3 * (1 + np.abs(a).max(axis=2))
+    assert bad.mean() < 0.02                               # a path through a specular chain may flip at an edge
+
+
+def test_sample_range_union_equals_full_render():
+    sd = H.cbox_scene(res=12, spp=6)
+    h = HostSim(sd)
+    full = h.render_xyzaw(seed=9)
+    parts = sum(h.render_xyzaw(seed=9, spp=c, spp_begin=b, spp_total=6) for b, c in ((0, 2), (2, 3), (5, 1)))
+    np.testing.assert_allclose(parts, full, rtol=1e-5, atol=1e-6)
+
+
+# ---- host mirror -----------------------------------------------------------------------------------------------------
+def test_obj_ply_roundtrip_and_normals():
+    m = M.displaced_sphere(6, 12)
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "m.ply")
+        M.write_ply(p, m)
+        m2 = M.load_ply(p)
+        np.testing.assert_array_equal(m.faces, m2.faces)
+        np.testing.assert_allclose(m.positions, m2.positions)
+        obj = os.path.join(d, "q.obj")
+        open(obj, "w").write("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\nf 1/1 2/2 3/3 4/4\n")
+        q = M.load_obj(obj)
+        assert q.faces.shape == (2, 3) and q.positions.shape[0] == 4 and q.texcoords is not None
+    n = M.compute_vertex_normals(m.positions, m.faces)
+    r = m.positions / np.linalg.norm(m.positions, axis=1, keepdims=True)
+    inner = np.abs(r[:, 1]) < 0.99                         # pole rows only touch degenerate triangles -> (1,0,0) fallback (mesh.cpp:262-270)
+    assert np.all(np.sum(n * r, axis=1)[inner] > 0.8)      # outward
+
+
+def test_perspective_matrix_matches_oracle():
+    o = np.zeros(16, np.float32)
+    Oracle.lib().orc_perspective_sample_to_camera(45.0, 0.01, 100.0, 16 / 9, H._p(o))
+    np.testing.assert_allclose(perspective_sample_to_camera(45.0, 0.01, 100.0, 16 / 9).ravel(), o, rtol=1e-6, atol=1e-7)
+
+
+def test_xml_subset_loader():
+    xml = """<scene version="2.0.0">
+      <default name="spp" value="4"/>
+      <integrator type="path"><integer name="max_depth" value="5"/></integrator>
+      <sensor type="perspective"><float name="fov" value="40"/>
+        <transform name="to_world"><lookat origin="0,0,4" target="0,0,0" up="0,1,0"/></transform>
+        <sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>
+        <film type="hdrfilm"><integer name="width" value="20"/><integer name="height" value="10"/><rfilter type="box"/></film>
+      </sensor>
+      <bsdf type="diffuse" id="red"><rgb name="reflectance" value="0.8,0.1,0.1"/></bsdf>
+      <shape type="rectangle"><ref id="red"/></shape>
+      <shape type="rectangle"><transform name="to_world"><translate y="2"/><rotate x="1" angle="90"/></transform>
+        <emitter type="area"><rgb name="radiance" value="5"/></emitter></shape>
+    </scene>"""
+    sd = X.load_string(xml)
+    assert sd.spp == 4 and sd.max_depth == 5
+    assert sd.sensors[0]["width"] == 20 and sd.sensors[0]["height"] == 10
+    assert len(sd.meshes) == 2 and len(sd.emitters) == 1
+    assert Oracle(sd).render_xyzaw(seed=0).shape == (10, 20, 5)
+    with pytest.raises(Exception):
+        X.load_string("<scene version='2.0.0'><shape type='nosuchshape'/></scene>")
+
+
+def test_scenedata_npz_roundtrip(tmp_path):
+    sd = H.material_scene(res=(8, 8), spp=1)
+    p = str(tmp_path / "s.npz")
+    sd.save_npz(p)
+    sd2 = SceneData.load_npz(p)
+    np.testing.assert_array_equal(Oracle(sd).render_xyzaw(seed=2), Oracle(sd2).render_xyzaw(seed=2))
+
+
+# ---- multi-rank logic over gloo -----------------------------------------------------------------------------------------
+def test_sample_share_partition():
+    for total in (0, 1, 7, 16, 1024):
+        for world in (1, 2, 3, 8):
+            shares = [D.sample_share(total, r, world) for r in range(world)]
+            assert shares[0][0] == 0 and sum(c for _, c in shares) == total
+            assert all(shares[i][0] + shares[i][1] == shares[i + 1][0] for i in range(world - 1))
+            assert max(c for _, c in shares) - min(c for _, c in shares) <= 1
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _gloo_worker(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sd = H.cbox_scene(res=12, spp=5)
+        h = HostSim(sd)
+
+        def render(b, c, t, seed):
+            return torch.from_numpy(h.render_xyzaw(seed=seed, spp=c, spp_begin=b, spp_total=t).ravel().copy())
+
+        film = D.render_sharded(render, 5, seed=4)
+        g = [torch.full((3,), float(rank + 1))]
+        D.allreduce_gradients(g)
+        np.save(os.path.join(out_dir, f"film{rank}.npy"), film.numpy())
+        np.save(os.path.join(out_dir, f"grad{rank}.npy"), g[0].numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_sharded_render_equals_single(tmp_path):
+    import torch.multiprocessing as mp
+    H.build_hostsim()
+    mp.spawn(_gloo_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    full = HostSim(H.cbox_scene(res=12, spp=5)).render_xyzaw(seed=4).ravel()
+    f0, f1 = np.load(tmp_path / "film0.npy"), np.load(tmp_path / "film1.npy")
+    np.testing.assert_array_equal(f0, f1)
+    np.testing.assert_allclose(f0, full, rtol=1e-5, atol=1e-6)
+    np.testing.assert_array_equal(np.load(tmp_path / "grad0.npy"), np.full(3, 3.0, np.float32))
