@@ -83,7 +83,7 @@ struct mtsb_scene {
     std::vector<std::unique_ptr<SensorHost>> sensors;
     // wavefront pool
     uint32_t pool = 0;
-    DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result;
+    DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result, final_radiance;
     DevBuf<uint4> q_misc[2], q_rng[2];
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;
@@ -466,13 +466,48 @@ static int ensure_pool(mtsb_scene *s, uint32_t n) {
         CU(s->q_o[k].alloc(n)); CU(s->q_d[k].alloc(n)); CU(s->q_hit[k].alloc(n)); CU(s->q_te[k].alloc(n));
         CU(s->q_misc[k].alloc(n)); CU(s->q_rng[k].alloc(n));
     }
-    CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n));
+    CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n)); 
     s->pool = n;
     return MTSB_OK;
 }
 static PathQueue make_queue(mtsb_scene *s, int k) {
     PathQueue q; q.o_mint = s->q_o[k].p; q.d_maxt = s->q_d[k].p; q.hit = s->q_hit[k].p; q.thr_eta = s->q_te[k].p;
     q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; return q;
+}
+
+// One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
+// (k_shade_grad scatters texel gradients); `splat` adds the finished paths to the film.
+static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches) {
+    cudaStream_t st = s->ctx->stream;
+    const uint32_t n = b.n_paths;
+    ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
+    int max_iter = s->dev.max_depth < 1000 ? s->dev.max_depth : 1000;
+    bool poll = s->dev.max_depth > 16;
+    CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
+    int cur = 0;
+    const unsigned tg = trace_grid_for(s->ctx, n);
+    { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
+    for (int depth = 1; depth <= max_iter; ++depth) {
+        PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
+        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill); }
+        { StageTimer t(s->ctx, ST_SHADE);
+          if (grad) k_shade_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+          else k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth); }
+        launches += 2;
+        if (depth < s->dev.max_depth) {
+            { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
+            launches++;
+        }
+        cur ^= 1;
+        if (poll) {
+            uint32_t next = 0;
+            CU(cudaMemcpyAsync(&next, s->counters.p + depth + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            if (next == 0) break;
+        }
+    }
+    if (splat) { StageTimer t(s->ctx, ST_FILM); k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); launches++; }
+    return MTSB_OK;
 }
 
 extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
@@ -485,39 +520,15 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
     if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");
     uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
     RC(ensure_pool(s, pool));
-    ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaEventRecord(s->ctx->ev0, st));
     uint64_t launches = 0;
-    int max_iter = s->dev.max_depth < 1000 ? s->dev.max_depth : 1000;
-    bool poll = s->dev.max_depth > 16;
     for (uint64_t off = 0; off < total; off += pool) {
         if (s->ctx->cancel) { s->ctx->cancel = 0; cudaStreamSynchronize(st); return fail(MTSB_E_CANCELLED, "render cancelled"); }
         uint32_t n = (uint32_t) ((total - off) < pool ? (total - off) : pool);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total;
         b.seed = seed; b.result = s->result.p;
-        CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
-        int cur = 0;
-        const unsigned tg = trace_grid_for(s->ctx, n);
-        { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
-        for (int depth = 1; depth <= max_iter; ++depth) {
-            PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
-            { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill); }
-            { StageTimer t(s->ctx, ST_SHADE); k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth); }
-            launches += 2;
-            if (depth < s->dev.max_depth) {
-                { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
-                launches++;
-            }
-            cur ^= 1;
-            if (poll) {
-                uint32_t next = 0;
-                CU(cudaMemcpyAsync(&next, s->counters.p + depth + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-                CU(cudaStreamSynchronize(st));
-                if (next == 0) break;
-            }
-        }
-        { StageTimer t(s->ctx, ST_FILM); k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); } launches++;
+        RC(run_batch(s, sn, b, nullptr, true, launches));
     }
     CU(cudaEventRecord(s->ctx->ev1, st));
     unsigned long long hs[4];

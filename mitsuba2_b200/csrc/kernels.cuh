@@ -175,6 +175,28 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
     if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
 }
 
+// adjoint replay of k_shade: identical control flow, plus the texel-gradient scatter of texture_adjoint()
+__global__ void __launch_bounds__(kBlock)
+k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
+             unsigned long long *stats, uint32_t depth, GradCtx g) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t count = counters[depth];
+    if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
+    bool live = i < count;
+    ShadeOut out; out.extend = false; out.shadow = false;
+    if (live)
+        out = shade_body(sc, qin, b, i, [&](const SceneDev &sc_, const RenderBatch &b_, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
+            texture_adjoint(sc_, b_, g, pid, si, bsdf, [](float *dst, float v) { if (v != 0.f) atomicAdd(dst, v); });
+        });
+    uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
+    if (out.extend) {
+        qout.o_mint[slot] = out.o_mint; qout.d_maxt[slot] = out.d_maxt; qout.thr_eta[slot] = out.thr_eta;
+        qout.misc[slot] = out.misc; qout.rng[slot] = out.rng;
+    }
+    uint32_t sslot = warp_alloc(&counters[1024 + depth], out.shadow);
+    if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
+}
+
 // any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *stats, uint32_t depth, uint32_t count_max,

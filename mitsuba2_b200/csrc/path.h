@@ -77,8 +77,48 @@ struct ShadeOut {
     float3 emitted;                                            // radiance added at this vertex (already weighted)
 };
 
-// One iteration of the loop in path.cpp:124-208 for queue entry i.  `result` accumulates emission.
-HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i) {
+// ---- adjoint of the path w.r.t. a bitmap texture that enters a BSDF multiplicatively ------------------------------
+// (diffuse `reflectance`, src/bsdfs/diffuse.cpp:78-135; roughconductor `specular_reflectance`, roughconductor.cpp:270)
+// L = P_k + a_k * R_k at every vertex k that looks the texture up (a_k = bilinear texel mix, P_k = radiance gathered
+// before the vertex's own BSDF is used, a_k R_k = everything after).  The replay pass knows the final radiance of the
+// path (from the primal pass) and the running prefix, so  dL/da_k = (L - P_k) / a_k  and the texel gradient is that
+// times the bilinear weights.  Sampling decisions and Russian roulette are treated as constants (detached), which
+// keeps the estimator unbiased.  Replaces the Enoki tape of src/python/python/autodiff.py:6-194 for this parameter.
+struct GradCtx {
+    const float4 *final_radiance;   // per path, from the primal pass
+    const float *dL_dimage;         // width*height*3, dL/d(developed RGB)
+    float *grad_tex;                // texture-sized accumulator
+    int tex_id;
+    float scale;                    // d(developed pixel)/d(sample radiance) = 1/spp_total (box filter)
+};
+struct NoGrad { HD void operator()(const SceneDev &, const RenderBatch &, uint32_t, const SI &, const BsdfDev &) const { } };
+
+template <typename AddFn>
+HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx &g, uint32_t path_id, const SI &si,
+                        const BsdfDev &bsdf, AddFn add) {
+    int tid = bsdf.type == 0 ? bsdf.refl : (bsdf.type == 1 ? bsdf.spec_r : -1);
+    if (tid != g.tex_id || tid < 0) return;
+    if (!(si.wi.z > 0.f)) return;                      // both BSDFs are one-sided: nothing after this vertex
+    const TexDev &t = sc.tex[tid];
+    uint32_t idx[4]; float w[4];
+    if (!tex_footprint(t, si.u, si.v, idx, w)) return;
+    float3 a = tex_eval(sc, tid, si.u, si.v);
+    float4 fin = g.final_radiance[path_id], run = b.result[path_id];
+    uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
+    float3 dI = ld3(g.dL_dimage, pixel) * g.scale;
+    const float tiny = 1e-8f;
+    float3 ga = mk3(a.x > tiny ? dI.x * (fin.x - run.x) / a.x : 0.f, a.y > tiny ? dI.y * (fin.y - run.y) / a.y : 0.f,
+                    a.z > tiny ? dI.z * (fin.z - run.z) / a.z : 0.f);
+    for (int k = 0; k < 4; ++k) {
+        if (t.ch == 1) add(g.grad_tex + idx[k], (ga.x + ga.y + ga.z) * w[k]);
+        else { add(g.grad_tex + 3 * (size_t) idx[k], ga.x * w[k]); add(g.grad_tex + 3 * (size_t) idx[k] + 1, ga.y * w[k]); add(g.grad_tex + 3 * (size_t) idx[k] + 2, ga.z * w[k]); }
+    }
+}
+
+// One iteration of the loop in path.cpp:124-208 for queue entry i.  `result` accumulates emission.  `grad` is called
+// once the vertex's BSDF is known to be used (after emission, Russian roulette and the depth cut).
+template <typename GradFn = NoGrad>
+HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, GradFn grad = GradFn()) {
     ShadeOut out; out.extend = false; out.shadow = false; out.emitted = mk3(0.f);
     float4 o4 = q.o_mint[i], d4 = q.d_maxt[i], h4 = q.hit[i], te = q.thr_eta[i];
     uint4 misc = q.misc[i];
@@ -127,6 +167,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     if ((uint32_t) depth >= (uint32_t) sc.max_depth) return out;
 
     const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
+    grad(sc, b, path_id, si, bsdf);
     // ---- emitter sampling (path.cpp:155-172, scene.cpp:141-189)
     if (bsdf_is_smooth(bsdf)) {
         float sx = rng.next_f32(), sy = rng.next_f32();

@@ -197,6 +197,7 @@ class HostSim:
             l.hs_bvh_info.argtypes = [vp, vp, vp]
             l.hs_intersect.argtypes = [vp, C.c_uint64, vp, vp, vp, vp, C.c_int]
             l.hs_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]
+            l.hs_render_grad.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, C.c_int32, vp]
             l.hs_bsdf_sample.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
             l.hs_sample_emitter_direction.argtypes = [vp, C.c_uint64, vp, vp, vp]
             cls._lib = l
@@ -242,6 +243,15 @@ class HostSim:
         if counts is not None:
             counts[:] = cnt
         return film
+
+    def render_grad(self, dL_dimage, tex_id, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None):
+        spp = self.data.spp if spp is None else spp
+        spp_total = spp_begin + spp if spp_total is None else spp_total
+        t = self.data.textures[tex_id]
+        g = np.zeros_like(np.ascontiguousarray(t["data"], np.float32))
+        dl = _f32(dL_dimage)
+        self.lib().hs_render_grad(self.h, sensor, spp_begin, spp, spp_total, seed, _p(dl), tex_id, _p(g))
+        return g
 
 
 # ---- scenes ---------------------------------------------------------------------------------------
@@ -450,3 +460,20 @@ def math_cases(fn, seed=11):
     fn["discrete_sample_reuse"](_p(pmf), 37, 256, _p(u), _p(idx), _p(uo))
     R["discrete_idx"], R["discrete_u"] = idx, uo
     return R
+
+
+def textured_cbox(res=16, spp=16, tex_res=6, seed=4, rr_off=True):
+    """C4-style scene: Cornell box whose floor reflectance is a small RGB bitmap (the differentiated parameter).
+    Returns (scene, texture id).  With `rr_off` Russian roulette never triggers, so the render is a polynomial in the
+    texel values and central finite differences are exact up to rounding."""
+    sd = cbox_scene(res=res, spp=spp, rfilter="box")
+    rng = np.random.default_rng(seed)
+    tex = sd.add_texture_bitmap((0.2 + 0.6 * rng.random((tex_res, tex_res, 3))).astype(np.float32))
+    floor = next(m for m in sd.meshes if "floor" in m.name)
+    p = floor.positions
+    lo, hi = p.min(axis=0), p.max(axis=0)
+    floor.texcoords = np.ascontiguousarray(((p - lo) / np.maximum(hi - lo, 1e-6))[:, [0, 2]], np.float32)
+    floor.bsdf = sd.add_diffuse(tex)
+    if rr_off:
+        sd.rr_depth = sd.max_depth + 1
+    return sd, tex

@@ -142,52 +142,83 @@ extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const floa
     }
 }
 
-// The wavefront loop of mtsb_render, stage by stage, with sequential "threads".
+// The wavefront loop of mtsb_render (run_batch in api.cu), stage by stage, with sequential "threads".
+struct HsPool {
+    std::vector<float4> qo[2], qd[2], qh[2], qt[2], so, sdv, scv, result;
+    std::vector<uint4> qm[2], qr[2];
+    explicit HsPool(uint32_t pool) : so(pool), sdv(pool), scv(pool), result(pool) {
+        for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); }
+    }
+    PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); return q; }
+};
+template <typename GradFn>
+static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad) {
+    std::vector<uint2> fast(8);
+    uint32_t n = b.n_paths; int cur = 0; uint32_t count = n;
+    for (uint32_t i = 0; i < n; ++i) raygen_body(sn, b, P.queue(cur), i);
+    for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
+        PathQueue qin = P.queue(cur), qout = P.queue(cur ^ 1);
+        for (uint32_t i = 0; i < count; ++i) {
+            TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
+            bvh_trace<false>(s->dev.bvh, xyz(qin.o_mint[i]), xyz(qin.d_maxt[i]), qin.o_mint[i].w, qin.d_maxt[i].w, st, h);
+            qin.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+        }
+        cnt[0] += count; cnt[2] += count;
+        uint32_t next = 0, nshadow = 0;
+        for (uint32_t i = 0; i < count; ++i) {
+            ShadeOut out = shade_body(s->dev, qin, b, i, grad);
+            if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; next++; }
+            if (out.shadow) { P.so[nshadow] = out.s_o_mint; P.sdv[nshadow] = out.s_d_maxt; P.scv[nshadow] = out.s_contrib_id; nshadow++; }
+        }
+        for (uint32_t i = 0; i < nshadow; ++i) {
+            TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
+            if (!bvh_trace<true>(s->dev.bvh, xyz(P.so[i]), xyz(P.sdv[i]), P.so[i].w, P.sdv[i].w, st, h)) {
+                uint32_t pid = f2u(P.scv[i].w); P.result[pid].x += P.scv[i].x; P.result[pid].y += P.scv[i].y; P.result[pid].z += P.scv[i].z; }
+        }
+        cnt[1] += nshadow;
+        count = next; cur ^= 1;
+    }
+}
+
 extern "C" void hs_render(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total, uint64_t seed,
                           float *xyzaw, uint64_t *counts) {
     SensorDev sn = s->sensors[sensor_id];
     uint64_t total = (uint64_t) sn.width * sn.height * spp_count;
     uint32_t pool = (uint32_t) std::min<uint64_t>(total, 1u << 20);
-    std::vector<float4> qo[2], qd[2], qh[2], qt[2], so(pool), sdv(pool), scv(pool), result(pool);
-    std::vector<uint4> qm[2], qr[2];
-    for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); }
-    auto queue = [&](int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); return q; };
-    std::vector<uint2> fast(8);
-    uint64_t c_closest = 0, c_shadow = 0, c_seg = 0;
+    HsPool P(pool);
+    uint64_t cnt[3] = { 0, 0, 0 };
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
-        RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = result.data();
-        int cur = 0; uint32_t count = n;
-        for (uint32_t i = 0; i < n; ++i) raygen_body(sn, b, queue(cur), i);
-        for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
-            PathQueue qin = queue(cur), qout = queue(cur ^ 1);
-            for (uint32_t i = 0; i < count; ++i) {
-                TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
-                bvh_trace<false>(s->dev.bvh, xyz(qin.o_mint[i]), xyz(qin.d_maxt[i]), qin.o_mint[i].w, qin.d_maxt[i].w, st, h);
-                qin.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
-            }
-            c_closest += count; c_seg += count;
-            uint32_t next = 0, nshadow = 0;
-            for (uint32_t i = 0; i < count; ++i) {
-                ShadeOut out = shade_body(s->dev, qin, b, i);
-                if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; next++; }
-                if (out.shadow) { so[nshadow] = out.s_o_mint; sdv[nshadow] = out.s_d_maxt; scv[nshadow] = out.s_contrib_id; nshadow++; }
-            }
-            for (uint32_t i = 0; i < nshadow; ++i) {
-                TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
-                if (!bvh_trace<true>(s->dev.bvh, xyz(so[i]), xyz(sdv[i]), so[i].w, sdv[i].w, st, h)) {
-                    uint32_t pid = f2u(scv[i].w); result[pid].x += scv[i].x; result[pid].y += scv[i].y; result[pid].z += scv[i].z; }
-            }
-            c_shadow += nshadow;
-            count = next; cur ^= 1;
-        }
+        RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
+        hs_run_batch(s, sn, b, P, cnt, NoGrad());
         for (uint32_t i = 0; i < n; ++i) {
             float fx, fy; path_film_pos(sn, b, i, fx, fy);
-            film_put(sn, fx, fy, radiance_to_xyza(result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
+            film_put(sn, fx, fy, radiance_to_xyza(P.result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
                 xyzaw[5 * (size_t) pix] += v.x; xyzaw[5 * (size_t) pix + 1] += v.y; xyzaw[5 * (size_t) pix + 2] += v.z; xyzaw[5 * (size_t) pix + 3] += v.w; xyzaw[5 * (size_t) pix + 4] += w; });
         }
     }
-    if (counts) { counts[0] = total; counts[1] = c_closest; counts[2] = c_shadow; counts[3] = c_seg; }
+    if (counts) { counts[0] = total; counts[1] = cnt[0]; counts[2] = cnt[1]; counts[3] = cnt[2]; }
+}
+
+// mtsb_render_grad (grad.cuh) on the host: primal pass -> final radiance, replay with the texel scatter
+extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total, uint64_t seed,
+                               const float *dL_dimage, int32_t tex_id, float *grad_texture) {
+    SensorDev sn = s->sensors[sensor_id];
+    uint64_t total = (uint64_t) sn.width * sn.height * spp_count;
+    uint32_t pool = (uint32_t) std::min<uint64_t>(total, 1u << 20);
+    HsPool P(pool);
+    std::vector<float4> fin(pool);
+    uint64_t cnt[3] = { 0, 0, 0 };
+    GradCtx g; g.final_radiance = fin.data(); g.dL_dimage = dL_dimage; g.grad_tex = grad_texture; g.tex_id = tex_id; g.scale = 1.f / (float) spp_total;
+    for (uint64_t off = 0; off < total; off += pool) {
+        uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
+        RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
+        hs_run_batch(s, sn, b, P, cnt, NoGrad());
+        std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
+        hs_run_batch(s, sn, b, P, cnt, [&](const SceneDev &sc, const RenderBatch &bb, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
+            texture_adjoint(sc, bb, g, pid, si, bsdf, [](float *dst, float v) { *dst += v; });
+        });
+    }
 }
 
 extern "C" void hs_bsdf_sample(hs_scene *s, uint32_t id, uint64_t n, const float *wi, const float *uv, const float *s1, const float *s2, float *out9) {
