@@ -23,7 +23,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;
-    if (sn.rfilter != 0 || sn.radius > 0.5f)
+    if (sn.rfilter != 0 || sn.radius > 1.f)      // single-pixel splat of weight 1 (imageblock.cpp:162-169)
         return fail(MTSB_E_INVALID, "mtsb_render_grad: only the box reconstruction filter is supported");
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
     if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");

@@ -210,24 +210,26 @@ def test_texture_gradient_matches_host_replay_and_fd(mi):
 
 
 def test_inverse_rendering_recovers_texture_with_adam(mi):
-    """autodiff.render_torch + torch.optim.Adam (reference: autodiff.py:240-482): the L2 image loss must drop."""
+    """autodiff.render_torch + torch.optim.Adam (reference: autodiff.py:240-482).  Target and iterates share the seed
+    (and Russian roulette is off), so the paths are identical and the L2 loss is a deterministic function of the
+    texels: it must drop by a large factor and the texels must move towards the target."""
     import torch
     from mitsuba2_b200 import autodiff
-    sd, tex = H.textured_cbox(res=32, spp=16, tex_res=4, rr_off=False)
+    sd, tex = H.textured_cbox(res=32, spp=16, tex_res=4, rr_off=True)
     target_tex = sd.textures[tex]["data"].copy()
     sc = mi.Scene(sd)
-    target = torch.from_numpy(sc.render(spp=64, seed=99).copy())
+    target = torch.from_numpy(sc.render(spp=16, seed=7).copy())
     param = torch.full(target_tex.shape, 0.5, dtype=torch.float32, requires_grad=True)
-    opt = torch.optim.Adam([param], lr=0.05)
+    opt = torch.optim.Adam([param], lr=0.03)
     losses = []
-    for it in range(30):
+    for it in range(60):
         opt.zero_grad()
-        img = autodiff.render_torch(sc, param, tex, spp=16, seed=it)
-        loss = ((img - target) ** 2).mean()
+        img = autodiff.render_torch(sc, param, tex, spp=16, seed=7)
+        loss = ((img - target) ** 2).sum()
         loss.backward()
         opt.step()
         with torch.no_grad():
             param.clamp_(0.01, 0.99)
-        losses.append(float(loss))
-    assert losses[-1] < 0.35 * losses[0]
-    assert np.abs(param.detach().numpy() - target_tex).mean() < np.abs(0.5 - target_tex).mean()
+        losses.append(loss.item())
+    assert losses[-1] < 0.05 * losses[0], (losses[0], losses[-1])
+    assert np.abs(param.detach().numpy() - target_tex).mean() < 0.5 * np.abs(0.5 - target_tex).mean()
