@@ -40,6 +40,42 @@ def build_scene(name):
     return scenes.c3_scene(n_theta=100, n_phi=200, width=w["width"], height=w["height"], small=(32, 64), tex_res=64)
 
 
+def side_metrics(mi, local):
+    """BASELINE.json's other two metrics, measured briefly on rank 0 at N=1 and reported under `extra`:
+    C2 intersection throughput (1M-triangle displaced sphere, 2.07M coherent / incoherent rays, closest and any hit) and
+    the C4 gradient pass (512^2 x 64 spp, 512^2 x 3 albedo texels)."""
+    import torch
+    from mitsuba2_b200 import scenes
+    out = {}
+    sd = scenes.c2_scene()
+    sc = mi.Scene(sd, device=local)
+    for kind in ("coherent", "incoherent"):
+        om, dm = scenes.c2_rays(sd, kind)
+        o_t, d_t = torch.from_numpy(om).cuda(local), torch.from_numpy(dm).cuda(local)
+        _, dms = scenes.c2_rays(sd, kind + "_shadow")
+        ds_t = torch.from_numpy(dms).cuda(local)
+        for mode, dd in (("closest", d_t), ("any", ds_t)):
+            fn = sc.intersect_closest_raw if mode == "closest" else sc.intersect_any_raw
+            ms = []
+            for i in range(3 + 10):
+                fn(o_t, dd)
+                if i >= 3:
+                    ms.append(sc.last_stats["ms_total"])
+            out[f"c2_{kind}_{mode}_mrays_per_s"] = om.shape[0] / (float(np.median(ms)) * 1e-3) / 1e6
+    del sc
+    sd4, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"))
+    sc4 = mi.Scene(sd4, device=local)
+    dl = torch.randn(512 * 512 * 3, device=f"cuda:{local}")
+    ms = []
+    for i in range(2 + 3):
+        sc4.render_grad(dl, spp=64, seed=i, tex_id=tex)
+        if i >= 2:
+            ms.append(sc4.last_stats["ms_total"])
+    out["c4_gradient_pass_ms"] = float(np.median(ms))
+    out["c4_gradient_pass_msamples_per_s"] = 512 * 512 * 64 / (out["c4_gradient_pass_ms"] * 1e-3) / 1e6
+    return out
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -148,6 +184,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
     ap.add_argument("--spp-per-step", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-side-metrics", action="store_true", help="skip the C2 intersect / C4 gradient side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -265,6 +302,12 @@ def main():
                       "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"]},
                       "scene_setup_s": t_build},
         }
+        if world == 1 and not args.no_side_metrics:
+            del scene
+            try:
+                out["extra"]["side_metrics"] = side_metrics(mi, local)
+            except Exception as e:      # the headline line must still be printed
+                out["extra"]["side_metrics"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(sd)
         print(json.dumps(out), flush=True)

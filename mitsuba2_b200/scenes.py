@@ -81,3 +81,28 @@ def c3_scene(n_theta=1000, n_phi=2000, width=1920, height=1080, small=(158, 316)
     sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, width, height, "box")
     sd.max_depth, sd.rr_depth, sd.spp = 6, 5, 1024
     return sd
+
+
+def c4_scene(cbox_npz, res=512, spp=64, tex_res=512, sphere=(100, 100), seed=4):
+    """C4 (gradient pass): Cornell-box geometry (fixture `cbox_npz`) whose floor reflectance is a tex_res^2 RGB bitmap
+    (values U[0.2,0.8)) and whose small box is replaced by a ~20k-triangle displaced sphere.  Returns (scene, tex id)."""
+    sd = SceneData.load_npz(cbox_npz)
+    s = sd.sensors[0]
+    sd.sensors = []
+    sd.add_perspective(s["to_world"].reshape(4, 4), s["fov_x"], s["near"], s["far"], res, res, "box")
+    rng = np.random.default_rng(seed)
+    tex = sd.add_texture_bitmap((0.2 + 0.6 * rng.random((tex_res, tex_res, 3))).astype(np.float32))
+    floor = next(m for m in sd.meshes if "floor" in m.name)
+    p = floor.positions
+    lo, hi = p.min(axis=0), p.max(axis=0)
+    floor.texcoords = np.ascontiguousarray(((p - lo) / np.maximum(hi - lo, 1e-6))[:, [0, 2]], np.float32)
+    floor.bsdf = sd.add_diffuse(tex)
+    for i, m in enumerate(sd.meshes):
+        if "smallbox" in m.name:
+            c = 0.5 * (m.positions.min(axis=0) + m.positions.max(axis=0))
+            r = 0.5 * float((m.positions.max(axis=0) - m.positions.min(axis=0)).min())
+            sph = M.displaced_sphere(sphere[0], sphere[1], radius=r, center=tuple(c))
+            sph.bsdf, sph.name = m.bsdf, "c4_sphere"
+            sd.meshes[i] = sph
+    sd.spp = spp
+    return sd, tex
