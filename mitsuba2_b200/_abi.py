@@ -114,11 +114,12 @@ def lib():
     """Load libmtsb200.so (built by ``__graft_entry__.build()``); raises if it is missing."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("MTSB_LIB", LIB_PATH)       # MTSB_LIB: alternative build of the same library (kernel experiments)
+        if not os.path.exists(path):
             raise RuntimeError(
-                f"mitsuba2_b200: CUDA library {LIB_PATH} not found -- run `python -c 'import __graft_entry__ as g; "
+                f"mitsuba2_b200: CUDA library {path} not found -- run `python -c 'import __graft_entry__ as g; "
                 "g.build()'` (nvcc, sm_100a). There is no CPU fallback.")
-        l = C.CDLL(LIB_PATH)
+        l = C.CDLL(path)
         for name, res, args in SYMBOLS:
             fn = getattr(l, name)
             fn.restype = res

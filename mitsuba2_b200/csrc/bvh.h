@@ -398,6 +398,7 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1,
     bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
     uint32_t octinv4 = octinv * 0x01010101u;
     uint32_t hit = 0;
+    const uint32_t one = 0x3f800000u;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         uint32_t meta4 = half ? n1.w : n1.z;
@@ -412,13 +413,16 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1,
         uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t sel = 0x7604u | ((uint32_t) j << 4);           // bytes: 0x00, q_j, 0x80, 0x3f
-            float t0x = fmaf(__uint_as_float(__byte_perm(ax, 0x3f800000u, sel)), Ax, Bnx);
-            float t0y = fmaf(__uint_as_float(__byte_perm(ay, 0x3f800000u, sel)), Ay, Bny);
-            float t0z = fmaf(__uint_as_float(__byte_perm(az, 0x3f800000u, sel)), Az, Bnz);
-            float t1x = fmaf(__uint_as_float(__byte_perm(bx, 0x3f800000u, sel)), Ax, Bfx);
-            float t1y = fmaf(__uint_as_float(__byte_perm(by, 0x3f800000u, sel)), Ay, Bfy);
-            float t1z = fmaf(__uint_as_float(__byte_perm(bz, 0x3f800000u, sel)), Az, Bfz);
+            // result bytes: 0x00, q_j, 0x80, 0x3f.  The constant is the FIRST source (a register that stays live), the
+            // selector an immediate: with the constant as the third source the selector had to be re-materialised
+            // from a uniform register before every PRMT (41 extra moves per node in the SASS).
+            const uint32_t sel = 0x3240u + ((uint32_t) j << 4);
+            float t0x = fmaf(__uint_as_float(__byte_perm(one, ax, sel)), Ax, Bnx);
+            float t0y = fmaf(__uint_as_float(__byte_perm(one, ay, sel)), Ay, Bny);
+            float t0z = fmaf(__uint_as_float(__byte_perm(one, az, sel)), Az, Bnz);
+            float t1x = fmaf(__uint_as_float(__byte_perm(one, bx, sel)), Ax, Bfx);
+            float t1y = fmaf(__uint_as_float(__byte_perm(one, by, sel)), Ay, Bfy);
+            float t1z = fmaf(__uint_as_float(__byte_perm(one, bz, sel)), Az, Bfz);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             uint32_t bits = ((child_bits4 >> (8 * j)) & 0xffu) << ((bit_index4 >> (8 * j)) & 0xffu);
@@ -460,19 +464,20 @@ static unsigned long long g_trav_nodes = 0, g_trav_tris = 0;
 #define TRAV_TRI()
 #endif
 
-// Traversal state of one ray.  `trav_step` advances it by one node visit (plus the triangles that visit selected), so a
-// kernel can interleave rays on a lane (persistent threads with dynamic fetch) while the host simulator just loops.
-template <typename Stack> struct Trav {
+// Traversal state of one ray (scalars only, so it lives in registers; the stack is a separate object because its
+// overflow array is dynamically indexed and would drag the whole struct into local memory).  `trav_step` advances the
+// ray by one node visit (plus the triangles that visit selected), so a kernel can interleave rays on a lane
+// (persistent threads with dynamic fetch) while the host simulator just loops.
+struct Trav {
     float3 o, idir; RayWoop rw;
     float mint, tmax;
     uint32_t octinv;
     uint2 G;            // current node group: x = first child index, y = hits<<24 | imask
     Hit hit; bool found;
-    Stack st;
 };
 
 template <typename Stack>
-HD void trav_init(Trav<Stack> &tr, float3 o, float3 d, float mint, float maxt) {
+HD void trav_init(Trav &tr, Stack &st, float3 o, float3 d, float mint, float maxt) {
     const float big = 1e30f;
     tr.o = o;
     tr.idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x),
@@ -485,17 +490,17 @@ HD void trav_init(Trav<Stack> &tr, float3 o, float3 d, float mint, float maxt) {
     tr.found = false;
     tr.hit.t = INFINITY; tr.hit.u = 0.f; tr.hit.v = 0.f; tr.hit.prim = 0xffffffffu;
     tr.G = make_uint2(0u, 0x80000000u);
-    tr.st.sp = 0;
+    st.sp = 0;
 }
 
 // returns true when the ray is finished (closest: stack exhausted; any-hit: first hit or stack exhausted)
 template <bool AnyHit, typename Stack>
-HD bool trav_step(const Bvh &bvh, Trav<Stack> &tr) {
+HD bool trav_step(const Bvh &bvh, Trav &tr, Stack &st) {
     uint2 G = tr.G;
     if (G.y & 0xff000000u) {
         uint32_t bit = 31u - (uint32_t) clz32(G.y);
         G.y &= ~(1u << bit);
-        if (G.y & 0xff000000u) tr.st.push(G);
+        if (G.y & 0xff000000u) st.push(G);
         uint32_t slot = (bit - 24u) ^ tr.octinv;
         uint32_t rel = (uint32_t) popc32(G.y & ((1u << slot) - 1u) & 0xffu);
         const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
@@ -521,27 +526,21 @@ HD bool trav_step(const Bvh &bvh, Trav<Stack> &tr) {
         }
     }
     if ((G.y & 0xff000000u) == 0) {
-        if (tr.st.empty()) return true;
-        G = tr.st.pop();
+        if (st.empty()) return true;
+        G = st.pop();
     }
     tr.G = G;
     return false;
 }
 
 template <bool AnyHit, typename Stack>
-HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Trav<Stack> &tr, Hit &hit) {
-    trav_init(tr, o, d, mint, maxt);
+HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
+    Trav tr;
+    trav_init(tr, st, o, d, mint, maxt);
     if (bvh.n_tris != 0)
-        while (!trav_step<AnyHit>(bvh, tr)) { }
+        while (!trav_step<AnyHit>(bvh, tr, st)) { }
     hit = tr.hit;
     return tr.found;
-}
-
-// convenience form used by the host simulator: caller supplies only the stack storage
-template <bool AnyHit, typename Stack>
-HD bool bvh_trace(const Bvh &bvh, float3 o, float3 d, float mint, float maxt, Stack &st, Hit &hit) {
-    Trav<Stack> tr; tr.st.fast = st.fast; tr.st.stride = st.stride;
-    return bvh_trace<AnyHit>(bvh, o, d, mint, maxt, tr, hit);
 }
 
 } // namespace mtsb

@@ -55,16 +55,20 @@ __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
 // lanes idle until the longest ray of the warp is done.  `Sink` consumes a finished ray.
 constexpr uint32_t kFetchChunk = 64;
 #ifndef MTSB_TRACE_BLOCKS
-#define MTSB_TRACE_BLOCKS 8
+#define MTSB_TRACE_BLOCKS 7
 #endif
 constexpr int kTraceBlocksPerSM = MTSB_TRACE_BLOCKS;
+#ifndef MTSB_SHADE_BLOCKS
+#define MTSB_SHADE_BLOCKS 10
+#endif
+constexpr int kShadeBlocksPerSM = MTSB_SHADE_BLOCKS;      // resident 128-thread blocks the shade kernel is compiled for
 template <bool AnyHit, typename Sink>
 __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count, const float4 *__restrict__ o_mint,
                                                  const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill,
                                                  uint2 *s_stack, Sink sink) {
     typedef TravStack<kStackFast, kStackSlow> Stack;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    Trav<Stack> tr; tr.st.fast = s_stack + threadIdx.x; tr.st.stride = kBlock; tr.st.sp = 0;
+    Trav tr; Stack st; st.fast = s_stack + threadIdx.x; st.stride = kBlock; st.sp = 0;
     bool active = false, exhausted = (count == 0 || bvh.n_tris == 0);
     uint32_t ray = 0, w_next = 0, w_end = 0;
     if (bvh.n_tris == 0) {      // empty scene: every ray misses
@@ -89,7 +93,7 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
             if (!active && r < take) {
                 ray = w_next + r;
                 float4 o = o_mint[ray], d = d_maxt[ray];
-                trav_init(tr, xyz(o), xyz(d), o.w, d.w);
+                trav_init(tr, st, xyz(o), xyz(d), o.w, d.w);
                 active = true;
             }
             w_next += take;
@@ -99,7 +103,7 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
             continue;
         }
         while (true) {
-            if (active && trav_step<AnyHit>(bvh, tr)) {
+            if (active && trav_step<AnyHit>(bvh, tr, st)) {
                 sink(ray, tr.found, tr.hit);
                 active = false;
             }
@@ -157,7 +161,7 @@ __device__ __forceinline__ uint32_t warp_alloc(uint32_t *counter, bool want) {
     return base + (uint32_t) __popc(mask & ((1u << lane) - 1u));
 }
 
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, kShadeBlocksPerSM)
 k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
         unsigned long long *stats, uint32_t depth) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
