@@ -477,3 +477,15 @@ def textured_cbox(res=16, spp=16, tex_res=6, seed=4, rr_off=True):
     if rr_off:
         sd.rr_depth = sd.max_depth + 1
     return sd, tex
+
+
+def z_test_pass_fraction(mean, reference, var_per_sample, n_mean, n_ref, significance=0.01):
+    """Per-pixel two-sided z-test of src/librender/tests/test_renders.py:60-126 (variance floor 1e-4, Sidak-corrected
+    significance); returns the fraction of pixel-channel values for which the null hypothesis is accepted."""
+    from math import erf, sqrt
+    var = np.maximum(var_per_sample, 1e-4)
+    z = np.abs(mean - reference) / np.sqrt(var * (1.0 / n_mean + 1.0 / n_ref))
+    cdf = 0.5 * (1.0 + np.vectorize(erf)(z / sqrt(2.0)))
+    p = 2.0 * (1.0 - cdf)
+    alpha = 1.0 - (1.0 - significance) ** (1.0 / (mean.size // mean.shape[-1]))
+    return float(np.mean(p > alpha))

@@ -181,6 +181,27 @@ def test_update_vertices_and_texture(mi):
     assert np.abs(f_g[..., :3] - f_c[..., :3]).sum() / np.abs(f_c[..., :3]).sum() < 3e-2
 
 
+# ---- statistical parity with independent random streams (the reference's own acceptance method) -------------------------
+@pytest.mark.parametrize("which", ["cbox", "material"])
+def test_z_test_against_oracle_with_independent_seeds(mi, which):
+    """test_renders.py:60-126: z-test per pixel, >= 99.75 % of the values must accept the null hypothesis.  GPU and
+    oracle use DIFFERENT seeds, so this checks the estimator (means), not the sample streams."""
+    sd = H.cbox_scene(res=32, spp=16) if which == "cbox" else H.material_scene(res=(32, 24), spp=16)
+    sc = mi.Scene(sd)
+    batches = np.stack([sc.render(spp=16, seed=100 + k) for k in range(32)])      # 32 x 16 spp
+    mean = batches.mean(axis=0)
+    o = H.Oracle(sd)
+    ref_batches = np.stack([o.develop(o.render_xyzaw(spp=16, seed=1000 + k)) for k in range(32)])
+    ref = ref_batches.mean(axis=0)
+    # per-sample variance: the larger of the two batch estimates (32 batches each; a firefly seen by only one side
+    # would otherwise make the test reject on an underestimated variance)
+    var_per_sample = np.maximum(batches.var(axis=0, ddof=1), ref_batches.var(axis=0, ddof=1)) * 16
+    frac = H.z_test_pass_fraction(mean, ref, var_per_sample, 32 * 16, 32 * 16)
+    assert frac >= 0.9975, frac
+    rel_mse = float(np.mean((mean - ref) ** 2 / (ref ** 2 + 1e-2)))
+    assert rel_mse < 2e-2, rel_mse
+
+
 # ---- gradient pass -------------------------------------------------------------------------------------------------
 def test_texture_gradient_matches_host_replay_and_fd(mi):
     """mtsb_render_grad through the C ABI vs (a) the same adjoint run by the host simulator, (b) central finite
