@@ -57,7 +57,7 @@ def side_metrics(mi, local):
         for mode, dd in (("closest", d_t), ("any", ds_t)):
             fn = sc.intersect_closest_raw if mode == "closest" else sc.intersect_any_raw
             ms = []
-            for i in range(3 + 10):
+            for i in range(3 + 20):
                 fn(o_t, dd)
                 if i >= 3:
                     ms.append(sc.last_stats["ms_total"])
@@ -73,7 +73,51 @@ def side_metrics(mi, local):
             ms.append(sc4.last_stats["ms_total"])
     out["c4_gradient_pass_ms"] = float(np.median(ms))
     out["c4_gradient_pass_msamples_per_s"] = 512 * 512 * 64 / (out["c4_gradient_pass_ms"] * 1e-3) / 1e6
+    del sc4
+    out["parity_gates"] = parity_gates(mi, local)
     return out
+
+
+def parity_gates(mi, local):
+    """the parity numbers reported next to every perf number, against the CPU oracle (checker only):
+    hit-id mismatch rate, image agreement at identical sample streams, gradient cosine vs finite differences."""
+    import helpers as H
+    g = {}
+    sd = H.sphere_scene(n_theta=128, n_phi=256)
+    sc, orc = mi.Scene(sd, device=local), H.Oracle(sd)
+    om, dm = H.random_rays(200000, 5, radius=1.5)
+    a = np.ascontiguousarray(sc.intersect_closest_raw(om, dm)[:, 3]).view(np.uint32)
+    b = np.ascontiguousarray(orc.intersect_closest(om, dm)[:, 3]).view(np.uint32)
+    g["hit_id_mismatch_rate"] = float(np.mean(a != b))
+    sdc = H.cbox_scene(res=64, spp=16, rfilter="box")
+    scc, orcc = mi.Scene(sdc, device=local), H.Oracle(sdc)
+    ia, ib = scc.render(spp=16, seed=3), orcc.develop(orcc.render_xyzaw(spp=16, seed=3))
+    g["cbox_same_streams_rel_mse"] = float(np.mean((ia - ib) ** 2) / np.mean(ib ** 2))
+    g["cbox_same_streams_max_abs"] = float(np.abs(ia - ib).max())
+    sdt, tex = H.textured_cbox(res=16, spp=32, tex_res=5)
+    sct, orct = mi.Scene(sdt, device=local), H.Oracle(sdt)
+    rng = np.random.default_rng(0)
+    wgt = rng.normal(size=(16, 16, 3)).astype(np.float32)
+    gt, _ = sct.render_grad(wgt, spp=32, seed=5, tex_id=tex)
+    gt = gt.reshape(sdt.textures[tex]["data"].shape)
+    base = sdt.textures[tex]["data"].copy()
+
+    def loss(data):
+        orct.update_texture(tex, data)
+        return float(np.sum(np.float64(wgt) * orct.develop(orct.render_xyzaw(seed=5))))
+
+    fd, an = [], []
+    for y, x, c in zip(rng.integers(0, 5, 16), rng.integers(0, 5, 16), rng.integers(0, 3, 16)):
+        d = base.copy()
+        d[y, x, c] += 0.02
+        lp = loss(d)
+        d[y, x, c] -= 0.04
+        fd.append((lp - loss(d)) / 0.04)
+        an.append(gt[y, x, c])
+    fd, an = np.array(fd), np.array(an)
+    g["texture_grad_cosine_vs_fd"] = float(np.dot(fd, an) / (np.linalg.norm(fd) * np.linalg.norm(an)))
+    g["texture_grad_rel_l2_vs_fd"] = float(np.linalg.norm(fd - an) / np.linalg.norm(fd))
+    return g
 
 
 def peaks():

@@ -11,12 +11,13 @@ from __future__ import annotations
 import numpy as np
 
 
-def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None):
+def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None, shard=True):
     """Render `scene` with bitmap texture `tex_id` set to the torch tensor `texture` (H,W,C); returns the developed
     linear-RGB image (H,W,3) as a tensor on the texture's device, differentiable w.r.t. `texture`.
 
-    With an initialised process group every rank renders its share of the samples and both the image and the
-    texture gradient are all-reduced (distributed.py), so all ranks see identical values."""
+    With an initialised process group and `shard=True` every rank renders its share of the samples of the SAME view and
+    both the image and the texture gradient are all-reduced (distributed.py), so all ranks see identical values.
+    `shard=False` renders locally (multi-view optimisation: one view per rank, the caller reduces the gradients)."""
     import torch
     from . import distributed as D
 
@@ -25,7 +26,7 @@ def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None)
         def forward(ctx, tex):
             t = tex.detach().contiguous().float()
             scene.update_texture(tex_id, t if t.is_cuda else t.cpu().numpy())
-            rank, world = D.world_info(group)
+            rank, world = D.world_info(group) if shard else (0, 1)
             total = int(scene.data.spp if spp is None else spp)
             begin, count = D.sample_share(total, rank, world)
             ctx.share = (begin, count, total)
@@ -46,7 +47,8 @@ def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None)
                 gt = np.zeros(int(np.prod(texture.shape)), np.float32)
             gt = gt if isinstance(gt, torch.Tensor) else torch.from_numpy(gt)
             gt = gt.to(grad_img.device).reshape(texture.shape)
-            D.allreduce_gradients([gt], group)
+            if shard:
+                D.allreduce_gradients([gt], group)
             return gt
 
     return _Render.apply(texture)
