@@ -120,6 +120,16 @@ def parity_gates(mi, local):
     return g
 
 
+def ncu_traffic(kernel="k_trace<0>"):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu capture of this same
+    command (profiles/r1_kernel_traffic.json, made by profiles/README.md's recipe); None if absent."""
+    path = os.path.join(ROOT, "profiles", "r1_kernel_traffic.json")
+    try:
+        return float(json.load(open(path))[kernel]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -325,6 +335,8 @@ def main():
         peak, peak_src = peaks()
         # dominant kernel = closest-hit traversal; algorithmic bytes = 48 B per ray (32 B ray in + 16 B hit out)
         ms_c = max(agg["ms_closest"], 1e-9)
+        pool = int(os.environ.get("MTSB_POOL", 1 << 23))
+        n_trace_launches = K * (-(-npix * spp // pool)) * sd.max_depth      # one closest-hit launch per batch and depth
         achieved = agg["closest_rays"] * 48 / (ms_c * 1e-3) / 1e9
         stage_ms = {k: agg[k] / K for k in ("ms_raygen", "ms_closest", "ms_shade", "ms_any", "ms_film")}
         bytes_per_sample = (20 * agg["samples"] + 224 * agg["segments"] + 96 * agg["shadow_rays"]) / max(1, agg["samples"])
@@ -337,8 +349,11 @@ def main():
                        "l2": "queues per step (>1 GB) exceed L2; no flush needed", "timing": "CUDA events on the launching stream, max over ranks"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes": "48 B/ray x rays per launch", "mrays_per_s": agg["closest_rays"] / (ms_c * 1e-3) / 1e6},
+                         "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "algorithmic_bytes": "48 B/ray x rays per launch",
+                         "algorithmic_bytes_per_launch": agg["closest_rays"] * 48 / max(1, n_trace_launches),
+                         "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per k_trace<closest> launch, profiles/r1_kernel_traffic.json",
+                         "limiter": "SM instruction issue / ALU pipe (ncu: issue slots 78% busy, ALU pipe 58%, DRAM 2% of peak), see profiles/", "mrays_per_s": agg["closest_rays"] / (ms_c * 1e-3) / 1e6},
             "extra": {"wall_ms_per_step": wall_ms / K, "stage_ms_per_step": stage_ms, "rays_per_sample": agg["closest_rays"] / agg["samples"],
                       "shadow_rays_per_sample": agg["shadow_rays"] / agg["samples"], "algorithmic_bytes_per_sample": bytes_per_sample,
                       "whole_step_gbs": bytes_per_sample * agg["samples"] / (sum(stage_ms.values()) * K * 1e-3) / 1e9,
