@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 1
+#define MTSB_ABI_VERSION 2
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -57,20 +57,25 @@ typedef struct mtsb_bsdf_desc {
     int32_t distribution;           /* MTSB_MF_* */
     int32_t sample_visible;         /* bool */
     float   eta;                    /* DIELECTRIC: int_ior / ext_ior */
+    int32_t two_sided;              /* bool: wrapped in `twosided` with the same BRDF on both sides
+                                       (src/bsdfs/twosided.cpp:66-200); not allowed for DIELECTRIC */
 } mtsb_bsdf_desc;
 
 /* Emitter: `Emitter::sample_direction/pdf_direction/eval`.
  * AREA src/emitters/area.cpp:71-125 (constant radiance), ENVMAP src/emitters/envmap.cpp:132-317.
  * The order of the array is the order of `Scene::m_emitters` (scene.cpp:23-48). */
-enum { MTSB_EMITTER_AREA = 0, MTSB_EMITTER_ENVMAP = 1 };
+enum { MTSB_EMITTER_AREA = 0, MTSB_EMITTER_ENVMAP = 1,
+       MTSB_EMITTER_CONSTANT = 2,  /* src/emitters/constant.cpp:77-108: uniform background, `radiance` */
+       MTSB_EMITTER_POINT = 3 };   /* src/emitters/point.cpp:80-105: isotropic point light, `radiance` = intensity */
 typedef struct mtsb_emitter_desc {
     int32_t  type;
-    float    radiance[3];       /* AREA */
+    float    radiance[3];       /* AREA / CONSTANT: radiance; POINT: intensity */
     int32_t  mesh_id;           /* AREA: index into meshes[] */
     uint32_t width, height;     /* ENVMAP */
     const float *rgba;          /* ENVMAP: width*height*4 float32 (alpha ignored), host pointer */
     float    to_world[16];      /* ENVMAP: row-major 4x4 */
     float    scale;             /* ENVMAP */
+    float    position[3];       /* POINT: world-space position */
 } mtsb_emitter_desc;
 
 /* Mesh: `Mesh` buffers (include/mitsuba/render/mesh.h:328-332); world-space positions. */

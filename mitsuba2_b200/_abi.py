@@ -14,7 +14,7 @@ MEM_HOST, MEM_DEVICE = 0, 1
 TEX_CONSTANT, TEX_BITMAP = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC = 0, 1, 2
 MF_BECKMANN, MF_GGX = 0, 1
-EMITTER_AREA, EMITTER_ENVMAP = 0, 1
+EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = 0, 1, 2
 
 c_float_p = C.POINTER(C.c_float)
@@ -31,12 +31,13 @@ class BsdfDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("reflectance_tex", C.c_int32), ("eta_tex", C.c_int32), ("k_tex", C.c_int32),
                 ("specular_reflectance_tex", C.c_int32), ("specular_transmittance_tex", C.c_int32),
                 ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("distribution", C.c_int32),
-                ("sample_visible", C.c_int32), ("eta", C.c_float)]
+                ("sample_visible", C.c_int32), ("eta", C.c_float), ("two_sided", C.c_int32)]
 
 
 class EmitterDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("radiance", C.c_float * 3), ("mesh_id", C.c_int32), ("width", C.c_uint32),
-                ("height", C.c_uint32), ("rgba", c_float_p), ("to_world", C.c_float * 16), ("scale", C.c_float)]
+                ("height", C.c_uint32), ("rgba", c_float_p), ("to_world", C.c_float * 16), ("scale", C.c_float),
+                ("position", C.c_float * 3)]
 
 
 class MeshDesc(C.Structure):

@@ -239,7 +239,7 @@ static void update_env_bsphere(mtsb_scene *s) {
     float3 c = (s->bbox_lo + s->bbox_hi) * 0.5f;
     float r = s->faces.n ? norm(s->bbox_hi - c) : 0.f;
     r = fmaxf(kRayEpsilon, r * (1.f + kRayEpsilon));
-    for (auto &em : s->emitters) if (em.type == MTSB_EMITTER_ENVMAP) em.bsphere_radius = r;
+    for (auto &em : s->emitters) if (em.type == MTSB_EMITTER_ENVMAP || em.type == MTSB_EMITTER_CONSTANT) em.bsphere_radius = r;   // constant.cpp:45-49
 }
 
 extern "C" int mtsb_scene_destroy(mtsb_scene *s) {
@@ -310,7 +310,8 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         BsdfDev bd; memset(&bd, 0, sizeof(bd));
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex;
         bd.spec_t = b.specular_transmittance_tex; bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution;
-        bd.sample_visible = b.sample_visible; bd.eta_f = b.eta;
+        bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
+        if (b.two_sided && b.type == MTSB_BSDF_DIELECTRIC) return fail(MTSB_E_INVALID, "twosided: only materials without a transmission component can be nested");
         if (b.type == MTSB_BSDF_DIFFUSE) CHECK_ARG(tex_ok(b.reflectance_tex, false));
         else if (b.type == MTSB_BSDF_ROUGHCONDUCTOR) CHECK_ARG(tex_ok(b.eta_tex, false) && tex_ok(b.k_tex, false) && tex_ok(b.specular_reflectance_tex, true));
         else if (b.type == MTSB_BSDF_DIELECTRIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.specular_reflectance_tex, true) && tex_ok(b.specular_transmittance_tex, true));
@@ -330,6 +331,13 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         if (e.type == MTSB_EMITTER_AREA) {
             CHECK_ARG(e.mesh_id >= 0 && (uint32_t) e.mesh_id < d->n_meshes && d->meshes[e.mesh_id].emitter_id == (int32_t) i);
             ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
+        } else if (e.type == MTSB_EMITTER_CONSTANT) {
+            if (s->dev.env_emitter >= 0) return fail(MTSB_E_INVALID, "only one environment emitter is allowed");
+            s->dev.env_emitter = (int) i;
+            ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = -1;
+        } else if (e.type == MTSB_EMITTER_POINT) {
+            ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = -1;
+            ed.position = mk3(e.position[0], e.position[1], e.position[2]);
         } else if (e.type == MTSB_EMITTER_ENVMAP) {
             CHECK_ARG(e.rgba && e.width >= 2 && e.height >= 2);
             if (s->dev.env_emitter >= 0) return fail(MTSB_E_INVALID, "only one environment emitter is allowed");

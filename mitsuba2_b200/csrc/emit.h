@@ -4,7 +4,7 @@
 
 namespace mtsb {
 
-struct DirSample { float3 p, n, d; float dist, pdf; float3 value; };
+struct DirSample { float3 p, n, d; float dist, pdf; float3 value; bool delta; };
 
 // enoki::binary_search (ext/enoki/include/enoki/array_utils.h:153-171)
 template <typename Pred> HD uint32_t binary_search(uint32_t start, uint32_t end, Pred pred) {
@@ -145,8 +145,30 @@ HD float area_pdf_direction(const EmitterDev &e, float3 d, float3 n, float dist)
 }
 
 // ---- Scene::sample_emitter_direction (src/librender/scene.cpp:141-176), without the shadow ray ---
+// warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:262-267)
+HD float3 square_to_uniform_sphere(float sx, float sy) {
+    float z = fmaf(-2.f, sy, 1.f), r = safe_sqrt(fmaf(-z, z, 1.f));
+    float sn, cs; sincosf(2.f * kPi * sx, &sn, &cs);
+    return mk3(r * cs, r * sn, z);
+}
+// ConstantBackgroundEmitter::sample_direction (src/emitters/constant.cpp:77-103); pdf_direction = 1/(4 pi)
+HD DirSample constant_sample_direction(const EmitterDev &e, float3 ref_p, float sx, float sy) {
+    DirSample ds; float3 d = square_to_uniform_sphere(sx, sy);
+    ds.dist = 2.f * e.bsphere_radius; ds.p = ref_p + d * ds.dist; ds.n = -d; ds.d = d;
+    ds.pdf = 0.25f * kInvPi; ds.value = e.radiance * (1.f / ds.pdf); ds.delta = false;
+    return ds;
+}
+// PointLight::sample_direction (src/emitters/point.cpp:74-98): delta position, pdf 1, intensity / dist^2
+HD DirSample point_sample_direction(const EmitterDev &e, float3 ref_p) {
+    DirSample ds; ds.p = e.position; ds.n = mk3(0.f); ds.pdf = 1.f; ds.delta = true;
+    ds.d = ds.p - ref_p; ds.dist = norm(ds.d);
+    float inv = 1.f / ds.dist; ds.d = ds.d * inv;
+    ds.value = e.radiance * (inv * inv);
+    return ds;
+}
+
 HD DirSample sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx, float sy) {
-    DirSample ds; ds.pdf = 0.f; ds.value = mk3(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
+    DirSample ds; ds.delta = false; ds.pdf = 0.f; ds.value = mk3(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
     if (sc.n_emitters == 0) return ds;
     uint32_t index = 0; float epdf = 1.f;
     if (sc.n_emitters > 1) {
@@ -156,7 +178,11 @@ HD DirSample sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx
         sx = (sx - (float) index * epdf) * ne;
     }
     const EmitterDev &e = sc.emitters[index];
-    ds = e.type == 0 ? area_sample_direction(sc, e, ref_p, sx, sy) : env_sample_direction(e, ref_p, sx, sy);
+    if (e.type == 0) ds = area_sample_direction(sc, e, ref_p, sx, sy);
+    else if (e.type == 1) ds = env_sample_direction(e, ref_p, sx, sy);
+    else if (e.type == 2) ds = constant_sample_direction(e, ref_p, sx, sy);
+    else ds = point_sample_direction(e, ref_p);
+    ds.delta = e.type == 3;
     if (sc.n_emitters > 1) { ds.pdf *= epdf; ds.value *= 1.f / epdf; }
     return ds;
 }

@@ -98,7 +98,7 @@ HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx 
                         const BsdfDev &bsdf, AddFn add) {
     int tid = bsdf.type == 0 ? bsdf.refl : (bsdf.type == 1 ? bsdf.spec_r : -1);
     if (tid != g.tex_id || tid < 0) return;
-    if (!(si.wi.z > 0.f)) return;                      // both BSDFs are one-sided: nothing after this vertex
+    if (bsdf.two_sided ? si.wi.z == 0.f : !(si.wi.z > 0.f)) return;   // no light is carried past this vertex
     const TexDev &t = sc.tex[tid];
     uint32_t idx[4]; float w[4];
     if (!tex_footprint(t, si.u, si.v, idx, w)) return;
@@ -139,9 +139,12 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
                 float3 dd = si.p - o; float dist = norm(dd); dd = dd / dist;
                 emitter_pdf = area_pdf_direction(e, dd, si.sh.n, dist);
             }
-        } else {
+        } else if (e.type == 1) {
             Le = env_eval(e, d);
             if (depth > 1 && !prev_delta) emitter_pdf = env_pdf_direction(e, d);
+        } else {                                                  // constant background (constant.cpp:105-108)
+            Le = e.radiance;
+            if (depth > 1 && !prev_delta) emitter_pdf = 0.25f * kInvPi;
         }
         if (sc.n_emitters > 1) emitter_pdf *= 1.f / (float) sc.n_emitters;
         float w = depth > 1 ? mis_weight(prev_pdf, emitter_pdf) : 1.f;
@@ -177,7 +180,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
                 float3 wo = si.sh.to_local(ds.d);
                 float3 bval; float bpdf;
                 bsdf_eval_pdf(sc, bsdf, si, wo, bval, bpdf);
-                float mis = mis_weight(ds.pdf, bpdf);
+                float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
                 float3 c = thr * bval * ds.value * mis;
                 if (c.x != 0.f || c.y != 0.f || c.z != 0.f) {
                     out.shadow = true;

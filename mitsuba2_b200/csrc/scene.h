@@ -11,11 +11,13 @@ struct TexDev {
 struct BsdfDev {
     int type; int refl, eta, k, spec_r, spec_t;
     float alpha_u, alpha_v; int distr; int sample_visible; float eta_f;
+    int two_sided;          // `twosided` adapter, same BRDF on both sides (src/bsdfs/twosided.cpp)
 };
 constexpr int kMaxEnvLevels = 20;
 struct EmitterDev {
-    int type;
-    // area
+    int type;               // 0 area, 1 envmap, 2 constant background, 3 point
+    float3 position;        // point
+    // area (radiance doubles as the constant emitter's radiance and the point light's intensity)
     float3 radiance; int mesh; const float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
     // envmap
     uint32_t w, h; const float4 *rgba; float to_world[16], to_local[16]; float scale;

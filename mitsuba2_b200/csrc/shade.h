@@ -236,7 +236,7 @@ struct Microfacet {
 };
 
 // ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
-HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
+HD BsdfSample bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
     BsdfSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = mk3(0.f);
     float cos_i = si.wi.z;
     if (b.type == 0) {            // src/bsdfs/diffuse.cpp:78-103
@@ -278,7 +278,7 @@ HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, fl
     return bs;
 }
 
-HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
+HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
     val = mk3(0.f); pdf = 0.f;
     float ci = si.wi.z, co = wo.z;
     if (b.type == 0) {            // src/bsdfs/diffuse.cpp:105-135
@@ -305,6 +305,24 @@ HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3
     }
 }
 
+// `twosided` (src/bsdfs/twosided.cpp:98-200): on the back side mirror wi (and wo) about the surface and use the
+// nested BRDF; cos(wi) == 0 belongs to neither side.
+HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
+    if (!b.two_sided || si.wi.z > 0.f) return bsdf_sample_one_sided(sc, b, si, s1, sx, sy);
+    BsdfSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = mk3(0.f);
+    if (!(si.wi.z < 0.f)) return bs;
+    SI s2 = si; s2.wi.z = -s2.wi.z;
+    bs = bsdf_sample_one_sided(sc, b, s2, s1, sx, sy);
+    bs.wo.z = -bs.wo.z;
+    return bs;
+}
+HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
+    if (!b.two_sided || si.wi.z > 0.f) { bsdf_eval_pdf_one_sided(sc, b, si, wo, val, pdf); return; }
+    val = mk3(0.f); pdf = 0.f;
+    if (!(si.wi.z < 0.f)) return;
+    SI s2 = si; s2.wi.z = -s2.wi.z; wo.z = -wo.z;
+    bsdf_eval_pdf_one_sided(sc, b, s2, wo, val, pdf);
+}
 HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
 
 } // namespace mtsb

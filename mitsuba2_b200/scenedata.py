@@ -135,6 +135,25 @@ class SceneData:
             mesh.emitter = len(self.emitters) - 1
         return mid
 
+    def make_two_sided(self, bsdf_id):
+        """``twosided`` adapter with the same BRDF on both sides (src/bsdfs/twosided.cpp); returns the id."""
+        if self.bsdfs[bsdf_id]["type"] == A.BSDF_DIELECTRIC:
+            raise ValueError("Only materials without a transmission component can be nested!")
+        self.bsdfs[bsdf_id]["two_sided"] = 1
+        return bsdf_id
+
+    def add_constant(self, radiance):
+        """``constant`` environment emitter (src/emitters/constant.cpp)."""
+        rad = [float(radiance)] * 3 if np.isscalar(radiance) else [float(x) for x in radiance]
+        self.emitters.append({"type": A.EMITTER_CONSTANT, "radiance": rad})
+        return len(self.emitters) - 1
+
+    def add_point(self, position, intensity):
+        """``point`` light (src/emitters/point.cpp)."""
+        it = [float(intensity)] * 3 if np.isscalar(intensity) else [float(x) for x in intensity]
+        self.emitters.append({"type": A.EMITTER_POINT, "radiance": it, "position": [float(x) for x in position]})
+        return len(self.emitters) - 1
+
     def add_envmap(self, rgba, to_world=None, scale=1.0):
         rgba = _f32(rgba)
         if rgba.shape[2] == 3:
@@ -174,6 +193,7 @@ class SceneData:
             bd[i].alpha_u, bd[i].alpha_v = b.get("alpha_u", 0.1), b.get("alpha_v", 0.1)
             bd[i].distribution, bd[i].sample_visible = b.get("distribution", 0), b.get("sample_visible", 1)
             bd[i].eta = b.get("eta", 1.0)
+            bd[i].two_sided = int(b.get("two_sided", 0))
         td = (A.TextureDesc * max(1, len(self.textures)))()
         for i, t in enumerate(self.textures):
             td[i].type = t["type"]
@@ -191,6 +211,13 @@ class SceneData:
             if e["type"] == A.EMITTER_AREA:
                 ed[i].radiance = (C.c_float * 3)(*e["radiance"])
                 ed[i].mesh_id = e["mesh_id"]
+            elif e["type"] == A.EMITTER_CONSTANT:
+                ed[i].radiance = (C.c_float * 3)(*e["radiance"])
+                ed[i].mesh_id = -1
+            elif e["type"] == A.EMITTER_POINT:
+                ed[i].radiance = (C.c_float * 3)(*e["radiance"])
+                ed[i].position = (C.c_float * 3)(*e["position"])
+                ed[i].mesh_id = -1
             else:
                 keep.append(e["rgba"])
                 ed[i].height, ed[i].width = e["rgba"].shape[:2]

@@ -3,8 +3,8 @@
 Mirror of ``xml::load_file`` / ``load_string`` (include/mitsuba/core/xml.h:17-29, src/libcore/xml.cpp): ``<default>``,
 ``$param`` substitution (``-Dkey=value``), ``<include>``, ``<ref>``, ``<transform>`` (translate/rotate/scale/lookat/matrix),
 typed properties, and the plugins named by the north star: shapes obj/ply (+ rectangle as two triangles), BSDFs
-diffuse/roughconductor/dielectric (``twosided`` unwraps to its child: both are front-side only here), emitters
-area/envmap, sensor perspective, film hdrfilm, rfilters box/tent/gaussian, sampler independent, integrator path.
+diffuse/roughconductor/dielectric (+ ``twosided`` around the first two), emitters
+area/envmap/constant/point, sensor perspective, film hdrfilm, rfilters box/tent/gaussian, sampler independent, integrator path.
 Unknown plugins raise, like ``PluginManager`` does.
 """
 import math
@@ -14,6 +14,7 @@ import xml.etree.ElementTree as ET
 
 import numpy as np
 
+from . import _abi as A
 from . import mesh as M
 from .scenedata import SceneData, look_at, parse_fov
 
@@ -190,7 +191,14 @@ class _Loader:
         p = self.props(el)
         if ty == "twosided":
             inner = [c for c in el if c.tag in ("bsdf", "ref")]
-            idx = self.bsdf_index(inner[0])
+            if len(inner) != 1:
+                raise NotImplementedError("twosided: exactly one nested BRDF (used on both sides) is supported")
+            b = dict(self.sd.bsdfs[self.bsdf_index(inner[0])])       # twosided.cpp:66-96
+            if b["type"] == A.BSDF_DIELECTRIC:
+                raise RuntimeError("Only materials without a transmission component can be nested!")
+            b["two_sided"] = 1
+            self.sd.bsdfs.append(b)
+            idx = len(self.sd.bsdfs) - 1
         elif ty == "diffuse":
             idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
         elif ty == "roughconductor":
@@ -249,9 +257,21 @@ class _Loader:
         ty = self.attr(el, "type")
         if ty == "area":
             return          # instantiated by the shape that references it
-        if ty != "envmap":
-            raise NotImplementedError(f"emitter plugin '{ty}' is outside the hot-path scope (area, envmap)")
         p = self.props(el)
+        if ty == "constant":
+            rad = p.get("radiance", ("rgb", [1.0] * 3))
+            self.sd.add_constant(rad[1] if isinstance(rad, tuple) else rad)
+            return
+        if ty == "point":
+            it = p.get("intensity", ("rgb", [1.0] * 3))
+            pos = p.get("position")
+            if pos is None:
+                tw = p.get("to_world")
+                pos = [0.0, 0.0, 0.0] if tw is None else list(np.asarray(tw, np.float64).reshape(4, 4)[:3, 3])
+            self.sd.add_point(pos, it[1] if isinstance(it, tuple) else it)
+            return
+        if ty != "envmap":
+            raise NotImplementedError(f"emitter plugin '{ty}' is outside the hot-path scope (area, envmap, constant, point)")
         img = load_image(self.resolve(el, p["filename"]))
         self.sd.add_envmap(img, p.get("to_world"), p.get("scale", 1.0))
 

@@ -277,7 +277,7 @@ typedef struct { uint32_t face_begin, face_count, vert_begin, vert_count; int bs
 typedef struct { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf [left, left+count) in order[] ; else children left,left+1 */ } onode;
 typedef struct { int n_levels; float **levels; uint32_t *widths; } oh2d;
 typedef struct {
-    int type; v3 radiance; int mesh; float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
+    int type; v3 radiance, position; int mesh; float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
     uint32_t w, h; float *rgba; float to_world[16], to_local[16]; float scale; oh2d warp; float bsphere_radius;
 } oemitter;
 typedef struct { int type; v3 value; uint32_t w, h, ch; float *data; float to_uv[9]; } otex;
@@ -462,7 +462,7 @@ static void update_bsphere(orc_scene *s) {   /* envmap.cpp:126-130 */
     v3 c = vscale(vadd(s->bbox_lo, s->bbox_hi), .5f);
     float r = s->n_faces ? vnorm(vsub(s->bbox_hi, c)) : 0.f;
     r = fmaxf(RAY_EPS, r * (1.f + RAY_EPS));
-    for (uint32_t i = 0; i < s->n_emitters; ++i) if (s->emitters[i].type == MTSB_EMITTER_ENVMAP) s->emitters[i].bsphere_radius = r;
+    for (uint32_t i = 0; i < s->n_emitters; ++i) if (s->emitters[i].type == MTSB_EMITTER_ENVMAP || s->emitters[i].type == MTSB_EMITTER_CONSTANT) s->emitters[i].bsphere_radius = r;
 }
 
 orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
@@ -498,6 +498,9 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
         const mtsb_emitter_desc *e = &d->emitters[i]; oemitter *oe = &s->emitters[i];
         oe->type = e->type;
         if (e->type == MTSB_EMITTER_AREA) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = e->mesh_id; build_area_cdf(s, oe); }
+        else if (e->type == MTSB_EMITTER_CONSTANT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1; s->env_emitter = (int) i; }  /* constant.cpp:33-49 */
+        else if (e->type == MTSB_EMITTER_POINT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1;
+            oe->position = V(e->position[0], e->position[1], e->position[2]); }                                    /* point.cpp:38-58 */
         else {
             s->env_emitter = (int) i; oe->w = e->width; oe->h = e->height; oe->scale = e->scale;
             memcpy(oe->to_world, e->to_world, sizeof(oe->to_world)); invert4(e->to_world, oe->to_local);
@@ -585,7 +588,7 @@ static v3 tex_eval(const orc_scene *s, int id, float u, float v) {
     return V(out[0], out[1], out[2]);
 }
 typedef struct { v3 wo, weight; float pdf, eta; int delta; } obs;
-static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy) {
+static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy) {
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
     float cos_theta_i = si->wi.z;
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:78-103 */
@@ -621,7 +624,7 @@ static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *s
     else { if (b->specular_transmittance_tex >= 0) w = vmul(w, tex_eval(s, b->specular_transmittance_tex, si->u, si->v)); w = vscale(w, sqrf(eta_ti)); }
     bs.weight = w; return bs;
 }
-static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, v3 *val, float *pdf) {
+static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, v3 *val, float *pdf) {
     *val = V(0, 0, 0); *pdf = 0.f;
     float cos_theta_i = si->wi.z, cos_theta_o = wo.z;
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:105-135 */
@@ -644,6 +647,24 @@ static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi
         if (vdot(si->wi, H) > 0.f && vdot(wo, H) > 0.f)
             *pdf = b->sample_visible ? D * mf_g1(&distr, si->wi, H) / (4.f * cos_theta_i) : mf_pdf(&distr, si->wi, H) / (4.f * vdot(wo, H));
     }
+}
+/* TwoSidedBRDF::sample / eval / pdf (twosided.cpp:98-200) with the same nested BRDF on both sides: on the back side flip
+ * wi (and wo) about the surface; cos(wi) == 0 is neither front nor back */
+static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy) {
+    if (!b->two_sided || si->wi.z > 0.f) return bsdf_sample_nested(s, b, si, s1, sx, sy);
+    obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
+    if (!(si->wi.z < 0.f)) return bs;
+    osi flipped = *si; flipped.wi.z *= -1.f;
+    bs = bsdf_sample_nested(s, b, &flipped, s1, sx, sy);
+    bs.wo.z *= -1.f;
+    return bs;
+}
+static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, v3 *val, float *pdf) {
+    if (!b->two_sided || si->wi.z > 0.f) { bsdf_eval_pdf_nested(s, b, si, wo, val, pdf); return; }
+    *val = V(0, 0, 0); *pdf = 0.f;
+    if (!(si->wi.z < 0.f)) return;
+    osi flipped = *si; flipped.wi.z *= -1.f; wo.z *= -1.f;
+    bsdf_eval_pdf_nested(s, b, &flipped, wo, val, pdf);
 }
 /* ---- emitters ---- */
 static v3 xf_vec(const float *m, v3 v) { return V(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z, m[8] * v.x + m[9] * v.y + m[10] * v.z); }
@@ -704,7 +725,7 @@ static float env_pdf_direction(const oemitter *e, v3 dw) {        /* envmap.cpp:
     float inv_sin_theta = 1.f / sqrtf(fmaxf(sqrf(d.x) + sqrf(d.z), sqrf(EPS_F)));
     return h2d_eval(e, u, v) * inv_sin_theta * (1.f / (2.f * sqrf(PI_F)));
 }
-typedef struct { v3 p, n, d, value; float dist, pdf; } ods;
+typedef struct { v3 p, n, d, value; float dist, pdf; int delta; } ods;
 static ods env_sample_direction(const oemitter *e, v3 ref_p, float sx, float sy) {   /* envmap.cpp:154-187 */
     ods ds; float u, v, pdf; h2d_sample(e, sx, sy, &u, &v, &pdf);
     float theta = v * PI_F, phi = u * (2.f * PI_F);
@@ -751,6 +772,25 @@ static float area_pdf_direction(const oemitter *e, v3 d, v3 n, float dist) {   /
     float dp = fabsf(vdot(d, n)), pdf = e->normalization * (dp != 0.f ? (dist * dist) / dp : 0.f);
     return vdot(d, n) < 0.f ? pdf : 0.f;
 }
+static v3 square_to_uniform_sphere(float sx, float sy) {    /* warp.h:262-267 */
+    float z = 1.f - 2.f * sy, r = safe_sqrtf(1.f - z * z), phi = 2.f * PI_F * sx;
+    return V(r * cosf(phi), r * sinf(phi), z);
+}
+static ods constant_sample_direction(const oemitter *e, v3 ref_p, float sx, float sy) {   /* constant.cpp:77-103 */
+    ods ds; memset(&ds, 0, sizeof(ds));
+    v3 d = square_to_uniform_sphere(sx, sy);
+    ds.dist = 2.f * e->bsphere_radius; ds.p = vadd(ref_p, vscale(d, ds.dist)); ds.n = vneg(d); ds.d = d;
+    ds.pdf = .25f * INV_PI_F; ds.value = vscale(e->radiance, 1.f / ds.pdf);
+    return ds;
+}
+static ods point_sample_direction(const oemitter *e, v3 ref_p) {    /* point.cpp:74-98 */
+    ods ds; memset(&ds, 0, sizeof(ds));
+    ds.p = e->position; ds.pdf = 1.f; ds.delta = 1;
+    ds.d = vsub(ds.p, ref_p); ds.dist = vnorm(ds.d);
+    float inv_dist = 1.f / ds.dist; ds.d = vscale(ds.d, inv_dist);
+    ds.value = vscale(e->radiance, inv_dist * inv_dist);
+    return ds;
+}
 static ods sample_emitter_direction(const orc_scene *s, v3 ref_p, float sx, float sy) {   /* scene.cpp:141-176 */
     ods ds; memset(&ds, 0, sizeof(ds));
     if (s->n_emitters == 0) return ds;
@@ -761,7 +801,11 @@ static ods sample_emitter_direction(const orc_scene *s, v3 ref_p, float sx, floa
         sx = (sx - (float) index * emitter_pdf) * (float) s->n_emitters;
     }
     const oemitter *e = &s->emitters[index];
-    ds = e->type == MTSB_EMITTER_AREA ? area_sample_direction(s, e, ref_p, sx, sy) : env_sample_direction(e, ref_p, sx, sy);
+    if (e->type == MTSB_EMITTER_AREA) ds = area_sample_direction(s, e, ref_p, sx, sy);
+    else if (e->type == MTSB_EMITTER_ENVMAP) ds = env_sample_direction(e, ref_p, sx, sy);
+    else if (e->type == MTSB_EMITTER_CONSTANT) ds = constant_sample_direction(e, ref_p, sx, sy);
+    else ds = point_sample_direction(e, ref_p);
+    ds.delta = e->type == MTSB_EMITTER_POINT;
     if (s->n_emitters > 1) { ds.pdf *= emitter_pdf; ds.value = vscale(ds.value, 1.f / emitter_pdf); }
     return ds;
 }
@@ -799,7 +843,8 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
         cnt[3]++;
         if (emitter >= 0) {
             const oemitter *e = &s->emitters[emitter];
-            v3 Le = e->type == MTSB_EMITTER_AREA ? (si.wi.z > 0.f ? e->radiance : V(0, 0, 0)) : env_eval(e, ray_d);   /* area.cpp:71-79, envmap.cpp:132-145 */
+            v3 Le = e->type == MTSB_EMITTER_AREA ? (si.wi.z > 0.f ? e->radiance : V(0, 0, 0))       /* area.cpp:71-79 */
+                  : e->type == MTSB_EMITTER_ENVMAP ? env_eval(e, ray_d) : e->radiance;              /* envmap.cpp:132-145, constant.cpp:105-108 */
             result = vadd(result, vscale(vmul(throughput, Le), emission_weight));
         }
         if (!si.valid) break;
@@ -824,7 +869,7 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
                     }
                     v3 wo = to_local(&si, ds.d), bsdf_val; float bsdf_pdf;
                     bsdf_eval_pdf(s, bsdf, &si, wo, &bsdf_val, &bsdf_pdf);
-                    float mis = mis_weight(ds.pdf, bsdf_pdf);
+                    float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bsdf_pdf);      /* path.cpp:169 */
                     result = vadd(result, vscale(vmul(vmul(throughput, bsdf_val), emitter_val), mis));
                 }
             }
@@ -845,7 +890,8 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
                 if (e->type == MTSB_EMITTER_AREA) {
                     v3 dd = vsub(si_bsdf.p, si.p); float dist = vnorm(dd); dd = vscale(dd, 1.f / dist);
                     emitter_pdf = area_pdf_direction(e, dd, si_bsdf.sh_n, dist);
-                } else emitter_pdf = env_pdf_direction(e, nd);       /* ds.d = -si_bsdf.wi = ray.d on a miss (records.h:173) */
+                } else if (e->type == MTSB_EMITTER_ENVMAP) emitter_pdf = env_pdf_direction(e, nd);   /* ds.d = -si_bsdf.wi = ray.d on a miss (records.h:173) */
+                else emitter_pdf = .25f * INV_PI_F;                                                  /* constant.cpp:98-103 */
                 if (s->n_emitters > 1) emitter_pdf *= 1.f / (float) s->n_emitters;
             }
             emission_weight = mis_weight(bs.pdf, emitter_pdf);

@@ -244,6 +244,12 @@ class HostSim:
             counts[:] = cnt
         return film
 
+    def sample_emitter_direction(self, ref_p, s2):
+        ref_p, s2 = _f32(ref_p), _f32(s2)
+        out = np.empty((ref_p.shape[0], 11), np.float32)
+        self.lib().hs_sample_emitter_direction(self.h, ref_p.shape[0], _p(ref_p), _p(s2), _p(out))
+        return out
+
     def render_grad(self, dL_dimage, tex_id, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None):
         spp = self.data.spp if spp is None else spp
         spp_total = spp_begin + spp if spp_total is None else spp_total
@@ -489,3 +495,23 @@ def z_test_pass_fraction(mean, reference, var_per_sample, n_mean, n_ref, signifi
     p = 2.0 * (1.0 - cdf)
     alpha = 1.0 - (1.0 - significance) ** (1.0 / (mean.size // mean.shape[-1]))
     return float(np.mean(p > alpha))
+
+
+def n1_scene(res=(32, 24), spp=8):
+    """SURVEY 8(f) N1 plugins: `twosided` BRDFs (an open quad seen from both sides, a rough-metal sphere), a `point`
+    light and a `constant` background."""
+    sd = SceneData()
+    wall = M.quad([-2, -1, 1.5], [2, -1, 1.5], [2, 2, 1.5], [-2, 2, 1.5])
+    wall.bsdf = sd.make_two_sided(sd.add_diffuse((0.7, 0.5, 0.3)))
+    sd.add_mesh(wall)
+    flip = M.quad([-2, -1.0, -3], [-2, -1.0, 1.5], [2, -1.0, 1.5], [2, -1.0, -3])      # normal points down: back side faces the camera
+    flip.bsdf = sd.make_two_sided(sd.add_diffuse(0.6))
+    sd.add_mesh(flip)
+    s1 = M.displaced_sphere(16, 32, radius=0.6, center=(0.3, -0.3, 0.2))
+    s1.bsdf = sd.make_two_sided(sd.add_roughconductor((0.2, 0.92, 1.1), (3.9, 2.45, 2.14), 0.2))
+    sd.add_mesh(s1)
+    sd.add_point([-1.0, 1.5, -1.0], (8.0, 7.0, 6.0))
+    sd.add_constant((0.3, 0.4, 0.6))
+    sd.add_perspective(look_at([0, 0.3, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 5, 3, spp
+    return sd

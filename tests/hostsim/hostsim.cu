@@ -85,7 +85,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
         const mtsb_bsdf_desc &b = d->bsdfs[i]; BsdfDev bd; memset(&bd, 0, sizeof(bd));
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex; bd.spec_t = b.specular_transmittance_tex;
-        bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta;
+        bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
         s->bsdfs.push_back(bd);
     }
     hs_build_bvh(s);
@@ -97,6 +97,14 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
             const MeshDev &m = s->meshes[e.mesh_id];
             AreaTable t = build_area_table(s->pos.data() + 3 * (size_t) m.vert_begin, mesh_faces[e.mesh_id].data(), m.face_count);
             s->tables.push_back(t.cdf); ed.cdf = s->tables.back().data(); ed.cdf_sum = t.sum; ed.normalization = t.normalization; ed.valid_lo = t.valid_lo; ed.valid_hi = t.valid_hi;
+        } else if (e.type == MTSB_EMITTER_CONSTANT || e.type == MTSB_EMITTER_POINT) {
+            ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = -1;
+            ed.position = mk3(e.position[0], e.position[1], e.position[2]);
+            if (e.type == MTSB_EMITTER_CONSTANT) {
+                s->dev.env_emitter = (int) i;
+                float3 c = (s->lo + s->hi) * 0.5f; float r = s->faces.size() ? norm(s->hi - c) : 0.f;
+                ed.bsphere_radius = fmaxf(kRayEpsilon, r * (1.f + kRayEpsilon));
+            }
         } else {
             s->dev.env_emitter = (int) i; ed.w = e.width; ed.h = e.height; ed.scale = e.scale;
             memcpy(ed.to_world, e.to_world, sizeof(ed.to_world)); invert4x4(e.to_world, ed.to_local);

@@ -181,6 +181,36 @@ def test_update_vertices_and_texture(mi):
     assert np.abs(f_g[..., :3] - f_c[..., :3]).sum() / np.abs(f_c[..., :3]).sum() < 3e-2
 
 
+# ---- 8(f) N1 plugins ---------------------------------------------------------------------------------------------------
+def test_n1_twosided_constant_point_match_oracle(mi):
+    sd = H.n1_scene(res=(48, 32), spp=8)
+    sc, o = mi.Scene(sd), H.Oracle(sd)
+    a, b = sc.render(spp=8, seed=2), o.develop(o.render_xyzaw(spp=8, seed=2))
+    bad = np.abs(a - b).max(axis=2) > 1e-3 * (1 + np.abs(b).max(axis=2))
+    assert bad.mean() < 0.02
+    ref = np.zeros((256, 3), np.float32)
+    s2 = np.random.default_rng(0).random((256, 2)).astype(np.float32)
+    np.testing.assert_allclose(sc.sample_emitter_direction(ref, s2), o.sample_emitter_direction(ref, s2), rtol=1e-5, atol=1e-6)
+    xml = """<scene version="2.0.0">
+      <integrator type="path"><integer name="max_depth" value="4"/></integrator>
+      <sensor type="perspective"><float name="fov" value="40"/>
+        <transform name="to_world"><lookat origin="0,0,4" target="0,0,0" up="0,1,0"/></transform>
+        <sampler type="independent"><integer name="sample_count" value="8"/></sampler>
+        <film type="hdrfilm"><integer name="width" value="24"/><integer name="height" value="16"/><rfilter type="box"/></film>
+      </sensor>
+      <shape type="rectangle"><bsdf type="twosided"><bsdf type="diffuse"/></bsdf>
+        <transform name="to_world"><rotate y="1" angle="180"/></transform></shape>
+      <emitter type="point"><point name="position" value="0,1,3"/><rgb name="intensity" value="10"/></emitter>
+      <emitter type="constant"><rgb name="radiance" value="0.2"/></emitter>
+    </scene>"""
+    s2 = mi.load_string(xml)
+    img = s2.render(seed=1)
+    o2 = H.Oracle(s2.data)
+    ref_img = o2.develop(o2.render_xyzaw(spp=8, seed=1))
+    assert img[8, 12].min() > 0.25                      # the back side of the rectangle is lit by the point light
+    np.testing.assert_allclose(img, ref_img, rtol=2e-3, atol=2e-4)
+
+
 # ---- statistical parity with independent random streams (the reference's own acceptance method) -------------------------
 @pytest.mark.parametrize("which", ["cbox", "material"])
 def test_z_test_against_oracle_with_independent_seeds(mi, which):

@@ -200,3 +200,49 @@ def test_world_size_2_sharded_render_equals_single(tmp_path):
     np.testing.assert_array_equal(f0, f1)
     np.testing.assert_allclose(f0, full, rtol=1e-5, atol=1e-6)
     np.testing.assert_array_equal(np.load(tmp_path / "grad0.npy"), np.full(3, 3.0, np.float32))
+
+
+# ---- 8(f) N1: twosided / constant / point -------------------------------------------------------------------------
+def test_n1_plugins_hostsim_matches_oracle():
+    sd = H.n1_scene()
+    a, b = Oracle(sd).render_xyzaw(seed=2), HostSim(sd).render_xyzaw(seed=2)
+    assert a[..., :3].max() > 0
+    bad = np.abs(a - b).max(axis=2) > 1e-3 * (1 + np.abs(a).max(axis=2))
+    assert bad.mean() < 0.02
+
+
+def test_twosided_mirrors_the_nested_brdf():
+    """twosided.cpp:98-200: f(wi, wo) on the back side equals the nested f(-wi.z, -wo.z)."""
+    sd = SceneData()
+    q = M.quad([-1, 0, -1], [-1, 0, 1], [1, 0, 1], [1, 0, -1])
+    q.bsdf = sd.make_two_sided(sd.add_diffuse(0.5))
+    sd.add_mesh(q)
+    sd.add_perspective(look_at([0, 3, 0], [0, 0, 0], [0, 0, 1]), 45.0, 0.01, 100.0, 4, 4, "box")
+    o = Oracle(sd)
+    wi = np.array([[0.3, 0.1, 0.9], [0.3, 0.1, -0.9]], np.float32)
+    wo = np.array([[-0.2, 0.4, 0.8], [-0.2, 0.4, -0.8]], np.float32)
+    ev, pdf = o.bsdf_eval_pdf(0, wi, np.zeros((2, 2), np.float32), wo)
+    assert pdf[0] > 0 and pdf[0] == pdf[1] and np.array_equal(ev[0], ev[1])
+    ev, pdf = o.bsdf_eval_pdf(0, wi, np.zeros((2, 2), np.float32), wo[::-1].copy())     # opposite sides: no transmission
+    assert np.all(pdf == 0) and np.all(ev == 0)
+    bs = o.bsdf_sample(0, wi, np.zeros((2, 2), np.float32), np.array([0.3, 0.3], np.float32), np.array([[0.2, 0.7]] * 2, np.float32))
+    assert bs[0, 2] > 0 and bs[1, 2] == -bs[0, 2] and np.array_equal(bs[0, :2], bs[1, :2])
+    with pytest.raises(ValueError):
+        sd.make_two_sided(sd.add_dielectric())
+
+
+def test_constant_and_point_emitter_sampling():
+    sd = H.n1_scene()
+    o = Oracle(sd)
+    ref = np.zeros((64, 3), np.float32)
+    s2 = np.random.default_rng(0).random((64, 2)).astype(np.float32)
+    out = o.sample_emitter_direction(ref, s2)        # d[3], dist, pdf, value[3], n[3]
+    point = s2[:, 0] < 0.5                           # two emitters: sample reuse picks index floor(2 * s.x)
+    np.testing.assert_allclose(out[point, 4], 0.5)                                  # delta light: pdf 1 x emitter pdf
+    np.testing.assert_allclose(out[~point, 4], 0.5 / (4 * np.pi), rtol=1e-6)        # constant.cpp:98-103
+    d = np.array([-1.0, 1.5, -1.0]); dist = np.linalg.norm(d)
+    np.testing.assert_allclose(out[point, :3], np.tile(d / dist, (point.sum(), 1)), atol=1e-6)
+    np.testing.assert_allclose(out[point, 5:8], np.tile(np.array([8.0, 7.0, 6.0]) / dist**2 / 0.5, (point.sum(), 1)), rtol=1e-5)
+    np.testing.assert_allclose(out[~point, 5:8], np.tile(np.array([0.3, 0.4, 0.6]) * 4 * np.pi / 0.5, ((~point).sum(), 1)), rtol=1e-5)
+    h = HostSim(sd)
+    np.testing.assert_allclose(h.sample_emitter_direction(ref, s2), out, rtol=1e-5, atol=1e-6)
