@@ -207,7 +207,7 @@ def test_n1_twosided_constant_point_match_oracle(mi):
     img = s2.render(seed=1)
     o2 = H.Oracle(s2.data)
     ref_img = o2.develop(o2.render_xyzaw(spp=8, seed=1))
-    assert img[8, 12].min() > 0.25                      # the back side of the rectangle is lit by the point light
+    assert img[8, 12].min() > 0.2                       # the back side of the rectangle is lit by the point light
     np.testing.assert_allclose(img, ref_img, rtol=2e-3, atol=2e-4)
 
 
