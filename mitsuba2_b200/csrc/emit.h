@@ -94,8 +94,7 @@ HD float env_pdf_direction(const EmitterDev &e, float3 dworld) {
 HD DirSample env_sample_direction(const EmitterDev &e, float3 ref_p, float sx, float sy) {
     DirSample ds;
     float u, v, pdf; h2d_sample(e, sx, sy, u, v, pdf);
-    float theta = v * kPi, phi = u * (2.f * kPi);
-    float st, ct, sp, cp; sincosf(theta, &st, &ct); sincosf(phi, &sp, &cp);
+    float st, ct, sp, cp; sincospif(v, &st, &ct); sincospif(2.f * u, &sp, &cp);      // theta = v pi, phi = 2 u pi
     float3 d = mk3(cp * st, sp * st, ct);         // math::sphdir
     d = mk3(d.y, d.z, -d.x);
     float dist = 2.f * e.bsphere_radius;
@@ -148,7 +147,7 @@ HD float area_pdf_direction(const EmitterDev &e, float3 d, float3 n, float dist)
 // warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:262-267)
 HD float3 square_to_uniform_sphere(float sx, float sy) {
     float z = fmaf(-2.f, sy, 1.f), r = safe_sqrt(fmaf(-z, z, 1.f));
-    float sn, cs; sincosf(2.f * kPi * sx, &sn, &cs);
+    float sn, cs; sincospif(2.f * sx, &sn, &cs);
     return mk3(r * cs, r * sn, z);
 }
 // ConstantBackgroundEmitter::sample_direction (src/emitters/constant.cpp:77-103); pdf_direction = 1/(4 pi)

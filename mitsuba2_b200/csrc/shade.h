@@ -91,10 +91,11 @@ HD void square_to_disk_concentric(float sx, float sy, float &ox, float &oy) {
     float x = fmaf(2.f, sx, -1.f), y = fmaf(2.f, sy, -1.f);
     bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
     float r = q13 ? y : x, rp = q13 ? x : y;
-    float phi = 0.25f * kPi * rp / r;
-    if (q13) phi = 0.5f * kPi - phi;
+    // angle in units of pi: sincospif needs no large-argument reduction path (smaller kernel, no local-memory table)
+    float phi = 0.25f * rp / r;
+    if (q13) phi = 0.5f - phi;
     if (is_zero) phi = 0.f;
-    float s, c; sincosf(phi, &s, &c);
+    float s, c; sincospif(phi, &s, &c);
     ox = r * c; oy = r * s;
 }
 HD float3 square_to_cosine_hemisphere(float sx, float sy) {
@@ -200,9 +201,9 @@ struct Microfacet {
     HD float3 sample(float3 wi, float sx, float sy, float &pdf_out) const {
         if (!visible) {
             float sin_phi, cos_phi, cos_theta, cos_theta_2, alpha_2;
-            if (au == av) { sincosf(2.f * kPi * sy, &sin_phi, &cos_phi); alpha_2 = au * au; }
+            if (au == av) { sincospif(2.f * sy, &sin_phi, &cos_phi); alpha_2 = au * au; }
             else {
-                float ratio = av / au, tmp = ratio * tanf(2.f * kPi * sy);
+                float ratio = av / au, ts, tc; sincospif(2.f * sy, &ts, &tc); float tmp = ratio * (ts / tc);
                 cos_phi = 1.f / sqrtf(fmaf(tmp, tmp, 1.f));
                 cos_phi = mulsign(cos_phi, fabsf(sy - 0.5f) - 0.25f);
                 sin_phi = cos_phi * tmp;
@@ -306,21 +307,19 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
 }
 
 // `twosided` (src/bsdfs/twosided.cpp:98-200): on the back side mirror wi (and wo) about the surface and use the
-// nested BRDF; cos(wi) == 0 belongs to neither side.
+// nested BRDF; cos(wi) == 0 belongs to neither side.  One call site each, so the nested code is not duplicated.
 HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
-    if (!b.two_sided || si.wi.z > 0.f) return bsdf_sample_one_sided(sc, b, si, s1, sx, sy);
-    BsdfSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = mk3(0.f);
-    if (!(si.wi.z < 0.f)) return bs;
-    SI s2 = si; s2.wi.z = -s2.wi.z;
-    bs = bsdf_sample_one_sided(sc, b, s2, s1, sx, sy);
-    bs.wo.z = -bs.wo.z;
+    bool back = b.two_sided && si.wi.z < 0.f;
+    SI s2 = si;
+    if (back) s2.wi.z = -s2.wi.z;
+    BsdfSample bs = bsdf_sample_one_sided(sc, b, s2, s1, sx, sy);
+    if (back) bs.wo.z = -bs.wo.z;
     return bs;
 }
 HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
-    if (!b.two_sided || si.wi.z > 0.f) { bsdf_eval_pdf_one_sided(sc, b, si, wo, val, pdf); return; }
-    val = mk3(0.f); pdf = 0.f;
-    if (!(si.wi.z < 0.f)) return;
-    SI s2 = si; s2.wi.z = -s2.wi.z; wo.z = -wo.z;
+    bool back = b.two_sided && si.wi.z < 0.f;
+    SI s2 = si;
+    if (back) { s2.wi.z = -s2.wi.z; wo.z = -wo.z; }
     bsdf_eval_pdf_one_sided(sc, b, s2, wo, val, pdf);
 }
 HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
