@@ -176,8 +176,40 @@ static int build_bvh(mtsb_scene *s) {
         b.keys = keys2.p; b.order = order2.p;
     }
     CU(cudaMemsetAsync(flags.p, 0, n * sizeof(uint32_t), st));
-    if (n > 1) k_lbvh_nodes<<<grid_for(n - 1), kBlock, 0, st>>>(b);
-    k_lbvh_fit<<<grid_for(n), kBlock, 0, st>>>(b);
+    const char *bvh_mode = getenv("MTSB_BVH");
+    if (n > 1 && !(bvh_mode && !strcmp(bvh_mode, "lbvh"))) {
+        // PLOC agglomeration over the Morton order (default).  The Morton keys are dead after the sort, so their two
+        // buffers serve as scratch: cluster arrays (ping/pong), nearest-neighbour indices, new leaf ids.
+        int *cur = (int *) keys.p, *nxt = cur + n, *nn = (int *) keys2.p, *leaf_new = nn + n;
+        uint32_t *order_out = order.p;            // the buffer the sort did not leave the result in
+        uint32_t zero = 0;
+        CU(cudaMemcpyAsync(counters.p, &zero, sizeof(zero), cudaMemcpyHostToDevice, st));
+        k_ploc_init<<<grid_for(n), kBlock, 0, st>>>(b, cur);
+        DevBuf<unsigned char> tmp; DevBuf<int> d_count; CU(d_count.alloc(1));
+        size_t tmp_bytes = 0;
+        CU(cub::DeviceSelect::If(nullptr, tmp_bytes, nxt, cur, d_count.p, (int) n, PlocAlive(), st));
+        CU(tmp.alloc(tmp_bytes));
+        uint32_t m = n; int rounds = 0;
+        while (m > 1) {
+            k_ploc_nearest<<<grid_for(m), kBlock, 0, st>>>(b, cur, m, nn);
+            k_ploc_merge<<<grid_for(m), kBlock, 0, st>>>(b, cur, nn, m, nxt);
+            CU(cub::DeviceSelect::If(tmp.p, tmp_bytes, nxt, cur, d_count.p, (int) m, PlocAlive(), st));
+            int hm = 0;
+            CU(cudaMemcpyAsync(&hm, d_count.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            if (hm <= 0 || (uint32_t) hm >= m) return fail(MTSB_E_INVALID, "PLOC made no progress");
+            m = (uint32_t) hm;
+            if (++rounds > 4096) return fail(MTSB_E_INVALID, "PLOC did not terminate");
+        }
+        k_ploc_finalize_internal<<<grid_for(n), kBlock, 0, st>>>(b);
+        k_ploc_finalize_leaf<<<grid_for(n), kBlock, 0, st>>>(b, order_out, leaf_new);
+        k_ploc_patch_leaf<<<grid_for(n), kBlock, 0, st>>>(b, leaf_new);
+        k_ploc_leaf_bounds<<<grid_for(n), kBlock, 0, st>>>(b, order_out);
+        b.order = order_out;
+    } else {
+        if (n > 1) k_lbvh_nodes<<<grid_for(n - 1), kBlock, 0, st>>>(b);
+        k_lbvh_fit<<<grid_for(n), kBlock, 0, st>>>(b);
+    }
     uint32_t c0[2] = { 1u, 0u };
     int root = n > 1 ? 0 : 0;     // internal node 0, or leaf id (n-1)+0 = 0 when n == 1
     CU(cudaMemcpyAsync(counters.p, c0, sizeof(c0), cudaMemcpyHostToDevice, st));

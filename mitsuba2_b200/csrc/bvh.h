@@ -158,6 +158,86 @@ HD float half_area(float3 lo, float3 hi) {
     float3 e = hi - lo;
     return e.x * e.y + e.y * e.z + e.z * e.x;
 }
+
+// ------------------------------------------------------------------------------------------------
+// PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) over the Morton-sorted triangles.  Bottom-up
+// agglomeration: every cluster looks at its 2R neighbours in the current (Morton-ordered) cluster array and picks the
+// one whose union box has the smallest area; mutual nearest neighbours merge.  Gives a markedly better tree than the
+// plain Morton-split LBVH (fewer node visits per ray) at a build cost of a few passes over a shrinking array.
+// Node numbering is the one the collapse expects: internal nodes [0, n-1) with the ROOT = 0 (ids are handed out
+// downwards from n-2, the last merge creates the root), leaves n-1+position.  After the last merge the leaves are
+// renumbered in depth-first order so that every subtree again covers a contiguous range [rfirst, rlast] of `order`.
+// Scratch use in PLOC mode: flags[id] = triangles below internal node id; parent[c] = 2*parent + (c is right child).
+// ------------------------------------------------------------------------------------------------
+constexpr int kPlocRadius = 6;
+
+HD void ploc_init_body(const BvhBuild &b, int *cid, uint32_t i) {       // cluster i = leaf i (sorted position)
+    int leaf = (int) b.n - 1 + (int) i;
+    uint32_t prim = b.order[i];
+    b.nlo[leaf] = b.tlo[prim]; b.nhi[leaf] = b.thi[prim];
+    cid[i] = leaf;
+}
+HD void ploc_nearest_body(const BvhBuild &b, const int *cid, uint32_t m, int *nn, uint32_t i) {
+    float3 lo = xyz(b.nlo[cid[i]]), hi = xyz(b.nhi[cid[i]]);
+    int j0 = (int) i - kPlocRadius, j1 = (int) i + kPlocRadius;
+    if (j0 < 0) j0 = 0;
+    if (j1 > (int) m - 1) j1 = (int) m - 1;
+    float best = INFINITY; int bj = -1;
+    for (int j = j0; j <= j1; ++j) {
+        if (j == (int) i) continue;
+        float a = half_area(fmin3(lo, xyz(b.nlo[cid[j]])), fmax3(hi, xyz(b.nhi[cid[j]])));
+        if (a < best) { best = a; bj = j; }          // ties: lowest index (deterministic)
+    }
+    nn[i] = bj;
+}
+// returns 1 if cluster i survives this round (as itself or as the merged node), 0 if it was absorbed by its partner
+HD uint32_t ploc_merge_body(const BvhBuild &b, const int *cid, const int *nn, int *cid_out, uint32_t i) {
+    int j = nn[i];
+    if (j < 0 || nn[j] != (int) i) { cid_out[i] = cid[i]; return 1u; }
+    if ((int) i > j) { cid_out[i] = -1; return 0u; }
+    int l = cid[i], r = cid[j], n = (int) b.n;
+    int id = n - 2 - (int) atomic_add(&b.counters[0], 1u);
+    b.left[id] = l; b.right[id] = r;
+    b.parent[l] = 2 * id; b.parent[r] = 2 * id + 1;
+    b.nlo[id] = mk4(fmin3(xyz(b.nlo[l]), xyz(b.nlo[r])), 0.f);
+    b.nhi[id] = mk4(fmax3(xyz(b.nhi[l]), xyz(b.nhi[r])), 0.f);
+    b.flags[id] = (l >= n - 1 ? 1u : b.flags[l]) + (r >= n - 1 ? 1u : b.flags[r]);
+    cid_out[i] = id;
+    return 1u;
+}
+// depth-first position of the leftmost leaf below `node`: sum of the left siblings' sizes on the way up (root = 0)
+HD uint32_t ploc_first_leaf(const BvhBuild &b, int node) {
+    int n = (int) b.n; uint32_t pos = 0;
+    while (node != 0) {
+        int pc = b.parent[node], p = pc >> 1;
+        if (pc & 1) { int l = b.left[p]; pos += l >= n - 1 ? 1u : b.flags[l]; }
+        node = p;
+    }
+    return pos;
+}
+HD void ploc_finalize_internal_body(const BvhBuild &b, int id) {
+    uint32_t first = ploc_first_leaf(b, id);
+    b.rfirst[id] = first; b.rlast[id] = first + b.flags[id] - 1u;
+}
+// leaf at sorted position i moves to depth-first position pos; `leaf_new[i]` = its new id (children are patched afterwards)
+HD void ploc_finalize_leaf_body(const BvhBuild &b, uint32_t *order_out, int *leaf_new, uint32_t i) {
+    int n = (int) b.n;
+    uint32_t pos = ploc_first_leaf(b, n - 1 + (int) i);
+    order_out[pos] = b.order[i];
+    leaf_new[i] = n - 1 + (int) pos;
+}
+// second half: patch the parent's child pointer and write the leaf bounds at the new id (nothing reads the old ones now)
+HD void ploc_patch_leaf_body(const BvhBuild &b, const int *leaf_new, uint32_t i) {
+    int n = (int) b.n, old_id = n - 1 + (int) i, new_id = leaf_new[i];
+    int pc = b.parent[old_id], p = pc >> 1;
+    if (pc & 1) b.right[p] = new_id; else b.left[p] = new_id;
+    (void) old_id;
+}
+HD void ploc_leaf_bounds_body(const BvhBuild &b, const uint32_t *order_out, uint32_t pos) {
+    int leaf = (int) b.n - 1 + (int) pos;
+    uint32_t prim = order_out[pos];
+    b.nlo[leaf] = b.tlo[prim]; b.nhi[leaf] = b.thi[prim];
+}
 HD uint32_t bin_count(const BvhBuild &b, int id) {
     int n = (int) b.n;
     return id >= n - 1 ? 1u : b.rlast[id] - b.rfirst[id] + 1u;

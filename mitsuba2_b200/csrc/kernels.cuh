@@ -43,6 +43,37 @@ __global__ void k_lbvh_fit(BvhBuild b) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < b.n) lbvh_fit_body(b, (int) i);
 }
+// PLOC passes (bodies in bvh.h)
+__global__ void k_ploc_init(BvhBuild b, int *cid) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) ploc_init_body(b, cid, i);
+}
+__global__ void k_ploc_nearest(BvhBuild b, const int *cid, uint32_t m, int *nn) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) ploc_nearest_body(b, cid, m, nn, i);
+}
+__global__ void k_ploc_merge(BvhBuild b, const int *cid, const int *nn, uint32_t m, int *cid_out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) ploc_merge_body(b, cid, nn, cid_out, i);
+}
+__global__ void k_ploc_finalize_internal(BvhBuild b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < b.n) ploc_finalize_internal_body(b, (int) i);
+}
+__global__ void k_ploc_finalize_leaf(BvhBuild b, uint32_t *order_out, int *leaf_new) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) ploc_finalize_leaf_body(b, order_out, leaf_new, i);
+}
+__global__ void k_ploc_patch_leaf(BvhBuild b, const int *leaf_new) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) ploc_patch_leaf_body(b, leaf_new, i);
+}
+__global__ void k_ploc_leaf_bounds(BvhBuild b, const uint32_t *order_out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b.n) ploc_leaf_bounds_body(b, order_out, i);
+}
+struct PlocAlive { __host__ __device__ bool operator()(int v) const { return v >= 0; } };
+
 __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
     uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i < end) collapse_body(b, i);

@@ -25,6 +25,48 @@ struct hs_scene {
     float3 lo, hi;
 };
 
+// EXPERIMENT (HS_SAH=1): top-down binned-SAH binary tree in the node numbering the collapse expects, to measure how much
+// a higher-quality tree would save over the Morton-order LBVH.
+struct SahCtx { BvhBuild *b; std::vector<float3> clo, chi, cen; int next_internal; };
+static int sah_build(SahCtx &c, uint32_t a, uint32_t e) {      // range [a, e) of b.order
+    BvhBuild &b = *c.b; int n = (int) b.n;
+    if (e - a == 1) { int id = n - 1 + (int) a; uint32_t t = b.order[a]; b.nlo[id] = mk4(c.clo[t], 0.f); b.nhi[id] = mk4(c.chi[t], 0.f); return id; }
+    int id = c.next_internal++;
+    float3 lo = mk3(INFINITY), hi = mk3(-INFINITY), klo = mk3(INFINITY), khi = mk3(-INFINITY);
+    for (uint32_t i = a; i < e; ++i) { uint32_t t = b.order[i]; lo = fmin3(lo, c.clo[t]); hi = fmax3(hi, c.chi[t]); klo = fmin3(klo, c.cen[t]); khi = fmax3(khi, c.cen[t]); }
+    const int NB = 16; float best = INFINITY; int best_axis = -1, best_bin = -1;
+    for (int ax = 0; ax < 3; ++ax) {
+        float k0 = ax == 0 ? klo.x : ax == 1 ? klo.y : klo.z, k1 = ax == 0 ? khi.x : ax == 1 ? khi.y : khi.z;
+        if (!(k1 > k0)) continue;
+        float3 blo[NB], bhi[NB]; uint32_t cnt[NB];
+        for (int k = 0; k < NB; ++k) { blo[k] = mk3(INFINITY); bhi[k] = mk3(-INFINITY); cnt[k] = 0; }
+        float scale = (float) NB / (k1 - k0);
+        for (uint32_t i = a; i < e; ++i) { uint32_t t = b.order[i]; float cv = ax == 0 ? c.cen[t].x : ax == 1 ? c.cen[t].y : c.cen[t].z;
+            int k = std::min(NB - 1, std::max(0, (int) ((cv - k0) * scale))); cnt[k]++; blo[k] = fmin3(blo[k], c.clo[t]); bhi[k] = fmax3(bhi[k], c.chi[t]); }
+        float ra[NB]; uint32_t rc[NB]; float3 l2 = mk3(INFINITY), h2 = mk3(-INFINITY); uint32_t cc = 0;
+        for (int k = NB - 1; k > 0; --k) { l2 = fmin3(l2, blo[k]); h2 = fmax3(h2, bhi[k]); cc += cnt[k]; ra[k] = cc ? half_area(l2, h2) : 0.f; rc[k] = cc; }
+        l2 = mk3(INFINITY); h2 = mk3(-INFINITY); cc = 0;
+        for (int k = 0; k + 1 < NB; ++k) { l2 = fmin3(l2, blo[k]); h2 = fmax3(h2, bhi[k]); cc += cnt[k];
+            if (cc == 0 || rc[k + 1] == 0) continue;
+            float cost = half_area(l2, h2) * (float) cc + ra[k + 1] * (float) rc[k + 1];
+            if (cost < best) { best = cost; best_axis = ax; best_bin = k; } }
+    }
+    uint32_t mid;
+    if (best_axis < 0) mid = (a + e) / 2;
+    else {
+        float k0 = best_axis == 0 ? klo.x : best_axis == 1 ? klo.y : klo.z, k1 = best_axis == 0 ? khi.x : best_axis == 1 ? khi.y : khi.z;
+        float scale = (float) NB / (k1 - k0);
+        auto it = std::partition(b.order + a, b.order + e, [&](uint32_t t) { float cv = best_axis == 0 ? c.cen[t].x : best_axis == 1 ? c.cen[t].y : c.cen[t].z;
+            return std::min(NB - 1, std::max(0, (int) ((cv - k0) * scale))) <= best_bin; });
+        mid = (uint32_t) (it - b.order);
+        if (mid == a || mid == e) mid = (a + e) / 2;
+    }
+    b.rfirst[id] = a; b.rlast[id] = e - 1; b.nlo[id] = mk4(lo, 0.f); b.nhi[id] = mk4(hi, 0.f);
+    int l = sah_build(c, a, mid), r = sah_build(c, mid, e);
+    b.left[id] = l; b.right[id] = r; b.parent[l] = id; b.parent[r] = id;
+    return id;
+}
+
 static void hs_build_bvh(hs_scene *s) {
     uint32_t n = (uint32_t) s->faces.size();
     s->dev.bvh.n_tris = n; s->dev.bvh.nodes = nullptr; s->dev.bvh.tris = nullptr;
@@ -46,8 +88,33 @@ static void hs_build_bvh(hs_scene *s) {
     std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t c) { return keys[a] < keys[c]; });
     for (uint32_t i = 0; i < n; ++i) { keys2[i] = keys[perm[i]]; order2[i] = order[perm[i]]; }
     b.keys = keys2.data(); b.order = order2.data();
+    const char *mode = getenv("HS_BVH");           // default: PLOC (the product default); "lbvh" = Morton-split tree
+    if (!getenv("HS_SAH") && n > 1 && !(mode && !strcmp(mode, "lbvh"))) {
+        // same sequence as build_bvh() in api.cu
+        std::vector<int> cidA(n), cidB(n), nn(n), leaf_new(n); std::vector<uint32_t> order3(n);
+        counters[0] = 0;
+        for (uint32_t i = 0; i < n; ++i) ploc_init_body(b, cidA.data(), i);
+        uint32_t m = n; int *cur = cidA.data(), *nxt = cidB.data();
+        while (m > 1) {
+            for (uint32_t i = 0; i < m; ++i) ploc_nearest_body(b, cur, m, nn.data(), i);
+            for (uint32_t i = 0; i < m; ++i) ploc_merge_body(b, cur, nn.data(), nxt, i);
+            uint32_t k = 0;
+            for (uint32_t i = 0; i < m; ++i) if (nxt[i] >= 0) cur[k++] = nxt[i];
+            m = k;
+        }
+        for (uint32_t i = 0; i + 1 < n; ++i) ploc_finalize_internal_body(b, (int) i);
+        for (uint32_t i = 0; i < n; ++i) ploc_finalize_leaf_body(b, order3.data(), leaf_new.data(), i);
+        for (uint32_t i = 0; i < n; ++i) ploc_patch_leaf_body(b, leaf_new.data(), i);
+        for (uint32_t i = 0; i < n; ++i) ploc_leaf_bounds_body(b, order3.data(), i);
+        order2 = order3; b.order = order2.data();
+    } else if (getenv("HS_SAH") && n > 1) {
+        SahCtx c; c.b = &b; c.next_internal = 0; c.clo.resize(n); c.chi.resize(n); c.cen.resize(n);
+        for (uint32_t i = 0; i < n; ++i) { float3 lo, hi; tri_bounds_body(b, i, lo, hi); c.clo[i] = lo; c.chi[i] = hi; c.cen[i] = (lo + hi) * 0.5f; }
+        sah_build(c, 0, n);
+    } else {
     for (uint32_t i = 0; i + 1 < n; ++i) lbvh_node_body(b, (int) i);
     for (uint32_t i = 0; i < n; ++i) lbvh_fit_body(b, (int) i);
+    }
     counters[0] = 1; counters[1] = 0; wide_bin[0] = 0;
     uint32_t begin = 0, end = 1, depth = 0;
     while (begin < end) { for (uint32_t w = begin; w < end; ++w) collapse_body(b, w); begin = end; end = counters[0]; depth++; }
