@@ -40,6 +40,7 @@ template <typename T> struct DevBuf {
 struct mtsb_ctx {
     int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
     int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
+    int bin_materials = 1;                   // sort queue entries by material class before shading (MTSB_BIN=0 disables)
     unsigned trace_grid = 148 * 8, refill = 22; // persistent traversal launch shape (set in mtsb_ctx_create)
     std::vector<cudaEvent_t> pool;           // event pairs, grown on demand
     std::vector<int> pool_stage; size_t pool_used = 0;
@@ -84,6 +85,7 @@ struct mtsb_scene {
     // wavefront pool
     uint32_t pool = 0;
     DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result, final_radiance;
+    DevBuf<uint32_t> class_lists;            // material bins of the shade stage: kShadeClasses x pool queue indices
     DevBuf<uint4> q_misc[2], q_rng[2];
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;
@@ -111,6 +113,7 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
         if (const char *e = getenv("MTSB_TRACE_BLOCKS_PER_SM")) { int v = atoi(e); if (v > 0 && v <= 32) per_sm = v; }
         if (const char *e = getenv("MTSB_REFILL")) { int v = atoi(e); if (v >= 0 && v <= 32) c->refill = (unsigned) v; }
         c->trace_grid = (unsigned) (sms * per_sm);
+        if (const char *e = getenv("MTSB_BIN")) c->bin_materials = atoi(e) != 0;
     }
     *out = c;
     return MTSB_OK;
@@ -129,7 +132,8 @@ extern "C" int mtsb_set_profiling(mtsb_ctx *c, int on) { if (!c) return fail(MTS
 static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) / kBlock); }
 // counters buffer (uint32 words): [0,1024) live paths per depth, [1024,2048) shadow rays per depth,
 // [2048,3072) work-fetch cursor of the closest-hit launch of that depth, [3072,4096) same for the shadow launch
-constexpr uint32_t kCounterWords = 4096, kWorkClosest = 2048, kWorkShadow = 3072;
+// [4096, 8192) shade-class counters, 4 per depth
+constexpr uint32_t kCounterWords = 8192, kWorkClosest = 2048, kWorkShadow = 3072, kClassCounts = 4096;
 static inline unsigned trace_grid_for(const mtsb_ctx *c, size_t n) {
     unsigned g = grid_for(n);
     return g < c->trace_grid ? (g ? g : 1u) : c->trace_grid;
@@ -506,7 +510,7 @@ static int ensure_pool(mtsb_scene *s, uint32_t n) {
         CU(s->q_o[k].alloc(n)); CU(s->q_d[k].alloc(n)); CU(s->q_hit[k].alloc(n)); CU(s->q_te[k].alloc(n));
         CU(s->q_misc[k].alloc(n)); CU(s->q_rng[k].alloc(n));
     }
-    CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n)); 
+    CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n)); CU(s->class_lists.alloc((size_t) kShadeClasses * n)); 
     s->pool = n;
     return MTSB_OK;
 }
@@ -532,7 +536,15 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
         { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill); }
         { StageTimer t(s->ctx, ST_SHADE);
           if (grad) k_shade_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
-          else k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth); }
+          else if (depth == 1 || !s->ctx->bin_materials) {      // primary hits are already coherent: identity lists
+              ShadeBins bins; bins.lists = nullptr; bins.counts = s->counters.p + depth; bins.pool = 0;
+              k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+          } else {
+              ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + 4 * depth; bins.pool = s->pool;
+              k_classify<<<grid_for(n), kBlock, 0, st>>>(s->dev, s->counters.p + depth, qin.hit, bins);
+              k_shade<<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              launches++;
+          } }
         launches += 2;
         if (depth < s->dev.max_depth) {
             { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }

@@ -169,7 +169,10 @@ HD float half_area(float3 lo, float3 hi) {
 // renumbered in depth-first order so that every subtree again covers a contiguous range [rfirst, rlast] of `order`.
 // Scratch use in PLOC mode: flags[id] = triangles below internal node id; parent[c] = 2*parent + (c is right child).
 // ------------------------------------------------------------------------------------------------
-constexpr int kPlocRadius = 6;
+#ifndef MTSB_PLOC_RADIUS
+#define MTSB_PLOC_RADIUS 6
+#endif
+constexpr int kPlocRadius = MTSB_PLOC_RADIUS;      // neighbours examined on each side
 
 HD void ploc_init_body(const BvhBuild &b, int *cid, uint32_t i) {       // cluster i = leaf i (sorted position)
     int leaf = (int) b.n - 1 + (int) i;

@@ -192,13 +192,57 @@ __device__ __forceinline__ uint32_t warp_alloc(uint32_t *counter, bool want) {
     return base + (uint32_t) __popc(mask & ((1u << lane) - 1u));
 }
 
+// ---- material binning -------------------------------------------------------------------------------------------------
+// After a bounce the queue is incoherent: neighbouring entries hit different materials, so a warp of the shade kernel
+// would run the diffuse, rough-conductor, dielectric and environment branches one after the other.  k_classify appends
+// every queue index to the list of its class (warp-aggregated atomics); the shade kernel then walks the four lists
+// back to back, each padded to a warp boundary, so that a warp sees one class only.
+constexpr int kShadeClasses = 4;          // 0 = miss (environment), 1 + BSDF type otherwise
+struct ShadeBins {
+    uint32_t *lists;                      // kShadeClasses x pool queue indices
+    uint32_t *counts;                     // kShadeClasses counters of the current depth
+    uint32_t pool;
+};
+__global__ void k_classify(SceneDev sc, const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins bins) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t count = *count_ptr;
+    int cls = -1;
+    if (i < count) {
+        float4 h = hit[i];
+        cls = 0;
+        if (h.x != INFINITY) cls = 1 + sc.bsdfs[sc.meshes[sc.faces[f2u(h.w)].w].bsdf].type;
+    }
+#pragma unroll
+    for (int c = 0; c < kShadeClasses; ++c) {
+        uint32_t slot = warp_alloc(&bins.counts[c], cls == c);
+        if (cls == c) bins.lists[(size_t) c * bins.pool + slot] = i;
+    }
+}
+// thread -> queue index through the bins; returns false for padding threads
+__device__ __forceinline__ bool shade_index(const ShadeBins &bins, uint32_t t, uint32_t &i) {
+    if (bins.lists == nullptr) { i = t; return t < bins.counts[0]; }      // identity: counts[0] = live paths
+    uint32_t start = 0;
+#pragma unroll
+    for (int c = 0; c < kShadeClasses; ++c) {
+        uint32_t n = bins.counts[c], padded = (n + 31u) & ~31u;
+        if (t < start + padded) {
+            uint32_t k = t - start;
+            if (k >= n) return false;
+            i = bins.lists[(size_t) c * bins.pool + k];
+            return true;
+        }
+        start += padded;
+    }
+    return false;
+}
+
 __global__ void __launch_bounds__(kBlock, kShadeBlocksPerSM)
 k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
-        unsigned long long *stats, uint32_t depth) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+        unsigned long long *stats, uint32_t depth, ShadeBins bins) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x, i = 0;
     uint32_t count = counters[depth];
-    if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
-    bool live = i < count;
+    if (t == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
+    bool live = shade_index(bins, t, i);
     ShadeOut out; out.extend = false; out.shadow = false;
     if (live) out = shade_body(sc, qin, b, i);
     uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
