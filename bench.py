@@ -337,7 +337,7 @@ def main():
         peak, peak_src = peaks()
         # dominant kernel = closest-hit traversal; algorithmic bytes = 48 B per ray (32 B ray in + 16 B hit out)
         ms_c = max(agg["ms_closest"], 1e-9)
-        pool = int(os.environ.get("MTSB_POOL", 1 << 23))
+        pool = int(os.environ.get("MTSB_POOL", 1 << 25))
         n_trace_launches = K * (-(-npix * spp // pool)) * sd.max_depth      # one closest-hit launch per batch and depth
         achieved = agg["closest_rays"] * 48 / (ms_c * 1e-3) / 1e9
         stage_ms = {k: agg[k] / K for k in ("ms_raygen", "ms_closest", "ms_shade", "ms_any", "ms_film")}
