@@ -284,3 +284,19 @@ def test_inverse_rendering_recovers_texture_with_adam(mi):
         losses.append(loss.item())
     assert losses[-1] < 0.05 * losses[0], (losses[0], losses[-1])
     assert np.abs(param.detach().numpy() - target_tex).mean() < 0.5 * np.abs(0.5 - target_tex).mean()
+
+
+def test_cpp_host_renders_through_the_c_abi(mi, tmp_path):
+    """examples/host_render.cpp: a C++ program linked against libmtsb200.so (no Python in the loop)."""
+    import os
+    import subprocess
+    from mitsuba2_b200 import imageio
+    inc, libdir = os.path.join(H.ROOT, "include"), os.path.join(H.ROOT, "mitsuba2_b200")
+    exe, out = str(tmp_path / "host_render"), str(tmp_path / "o.pfm")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + inc, os.path.join(H.ROOT, "examples", "host_render.cpp"),
+                           "-L" + libdir, "-lmtsb200", "-Wl,-rpath," + libdir, "-o", exe])
+    r = subprocess.run([exe, out, "16"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    img = imageio.read_pfm(out)
+    assert img.shape == (128, 128, 3) and np.isfinite(img).all()
+    assert img[64, 20, 0] > 2 * img[64, 20, 1] and img[64, 108, 1] > 2 * img[64, 108, 0]      # red wall left, green wall right

@@ -246,3 +246,21 @@ def test_constant_and_point_emitter_sampling():
     np.testing.assert_allclose(out[~point, 5:8], np.tile(np.array([0.3, 0.4, 0.6]) * 4 * np.pi / 0.5, ((~point).sum(), 1)), rtol=1e-5)
     h = HostSim(sd)
     np.testing.assert_allclose(h.sample_emitter_direction(ref, s2), out, rtol=1e-5, atol=1e-6)
+
+
+# ---- the ABI from C and C++ ---------------------------------------------------------------------------------------------
+def test_header_is_valid_c99_and_cpp_host_links(tmp_path):
+    import subprocess
+    c = tmp_path / "abi.c"
+    c.write_text('#include "mtsb200.h"\nint main(void) { return mtsb_abi_version() == MTSB_ABI_VERSION ? 0 : 1; }\n')
+    inc = os.path.join(H.ROOT, "include")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + inc, "-c", str(c), "-o", str(tmp_path / "abi.o")])
+    A.lib()                                      # library must exist
+    libdir = os.path.join(H.ROOT, "mitsuba2_b200")
+    exe = str(tmp_path / "host_render")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + inc, os.path.join(H.ROOT, "examples", "host_render.cpp"),
+                           "-L" + libdir, "-lmtsb200", "-Wl,-rpath," + libdir, "-o", exe])
+    import torch
+    if not torch.cuda.is_available():            # without a GPU the host must fail loudly, not fall back
+        r = subprocess.run([exe, str(tmp_path / "o.pfm"), "2"], capture_output=True, text=True)
+        assert r.returncode != 0 and "failed" in r.stderr
