@@ -35,7 +35,7 @@ int main(int argc, char **argv) {
         { { 1, -1, -1,  1, 1, -1,  1, 1, 1,  1, -1, 1 }, 2, -1 },          // right  (normal -x)
         { { -.3f, .98f, -.3f,  -.3f, .98f, .3f,  .3f, .98f, .3f,  .3f, .98f, -.3f }, 0, 0 },   // light (normal -y)
     };
-    static const uint32_t faces[6] = { 0, 1, 2, 0, 2, 3 };
+    static const uint32_t faces[6] = { 0, 2, 1, 0, 3, 2 };      // winding chosen so the normals listed above point into the box
     std::vector<mtsb_mesh_desc> meshes(quads.size());
     for (size_t i = 0; i < quads.size(); ++i) {
         memset(&meshes[i], 0, sizeof(mtsb_mesh_desc));
@@ -46,7 +46,7 @@ int main(int argc, char **argv) {
     em.type = MTSB_EMITTER_AREA; em.radiance[0] = 18.f; em.radiance[1] = 14.f; em.radiance[2] = 8.f; em.mesh_id = 5;
     // perspective camera at (0,0,-3.4) looking down +z, 40 degrees: sample_to_camera as in perspective.cpp:125-133
     mtsb_sensor_desc sn; memset(&sn, 0, sizeof(sn));
-    const float to_world[16] = { -1, 0, 0, 0,  0, 1, 0, 0,  0, 0, 1, -3.4f,  0, 0, 0, 1 };      // left-handed look_at(+z), x flipped
+    const float to_world[16] = { 1, 0, 0, 0,  0, 1, 0, 0,  0, 0, 1, -3.4f,  0, 0, 0, 1 };       // look_at((0,0,-3.4) -> origin, up +y)
     memcpy(sn.to_world, to_world, sizeof(to_world));
     float tanv = tanf(40.f * 0.5f * 3.14159265f / 180.f), nearc = 0.01f, farc = 100.f, aspect = (float) W / H;
     // inverse of scale(-.5,-.5*aspect,1) * translate(-1,-1/aspect,0) * perspective(fov,near,far)

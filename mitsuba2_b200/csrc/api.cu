@@ -85,6 +85,7 @@ struct mtsb_scene {
     // wavefront pool
     uint32_t pool = 0;
     DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result, final_radiance;
+    DevBuf<uint8_t> prim_class;              // per primitive: 1 + BSDF type (shade class), see k_classify
     DevBuf<uint32_t> class_lists;            // material bins of the shade stage: kShadeClasses x pool queue indices
     DevBuf<uint4> q_misc[2], q_rng[2];
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
@@ -246,6 +247,13 @@ static int upload_struct_arrays(mtsb_scene *s) {
     CU(s->d_tex.upload(s->tex.data(), s->tex.size(), st));
     CU(s->d_bsdfs.upload(s->bsdfs.data(), s->bsdfs.size(), st));
     CU(s->d_emitters.upload(s->emitters.data(), s->emitters.size(), st));
+    {   // shade class of every primitive (1 + BSDF type), looked up by the traversal kernel when a ray finishes
+        size_t np = 0; for (const MeshDev &m : s->meshes) np += m.face_count;
+        std::vector<uint8_t> cls(np ? np : 1, 0);
+        for (const MeshDev &m : s->meshes)
+            for (uint32_t f = 0; f < m.face_count; ++f) cls[m.face_begin + f] = (uint8_t) (1 + s->bsdfs[m.bsdf].type);
+        CU(s->prim_class.upload(cls.data(), cls.size(), st));
+    }
     CU(cudaStreamSynchronize(st));
     s->dev.pos = s->pos.p; s->dev.nrm = s->nrm.p; s->dev.uv = s->uv.p; s->dev.faces = s->faces.p;
     s->dev.meshes = s->d_meshes.p; s->dev.tex = s->d_tex.p; s->dev.bsdfs = s->d_bsdfs.p; s->dev.emitters = s->d_emitters.p;
@@ -311,6 +319,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         else h_uv.insert(h_uv.end(), 2 * (size_t) m.vertex_count, 0.f);
         s->mesh_faces.emplace_back(m.faces, m.faces + 3 * (size_t) m.face_count);
         s->computed_normals.push_back(false);
+        if ((size_t) h_faces.size() + m.face_count > (size_t) kPrimMask) return fail(MTSB_E_INVALID, "more than 2^30 - 1 triangles");
         for (uint32_t f = 0; f < m.face_count; ++f) {
             uint32_t a = m.faces[3 * f], b = m.faces[3 * f + 1], c = m.faces[3 * f + 2];
             if (a >= m.vertex_count || b >= m.vertex_count || c >= m.vertex_count) return fail(MTSB_E_INVALID, "face index out of range");
@@ -472,8 +481,8 @@ static int intersect_common(mtsb_scene *s, uint64_t n, const float *o_mint, cons
     uint32_t *work = s->counters.p + kWorkClosest;
     if (mode != 2) CU(cudaMemsetAsync(work, 0, sizeof(uint32_t), st));
     unsigned tg = trace_grid_for(s->ctx, n);
-    if (mode == 0) k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill);
-    else if (mode == 1) k_trace<true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill);
+    if (mode == 0) k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill, nullptr);
+    else if (mode == 1) k_trace<true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill, nullptr);
     else k_trace_naive<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h);
     CU(cudaEventRecord(s->ctx->ev1, st));
     CU(cudaGetLastError());
@@ -535,7 +544,7 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
     for (int depth = 1; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
-        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill); }
+        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE);
           if (grad) k_shade_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
           else if (depth == 1 || !s->ctx->bin_materials) {      // primary hits are already coherent: identity lists
@@ -543,7 +552,7 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
               k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
           } else {
               ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + 4 * depth; bins.pool = s->pool;
-              k_classify<<<grid_for(n), kBlock, 0, st>>>(s->dev, s->counters.p + depth, qin.hit, bins);
+              k_classify<<<grid_for(n), kBlock, 0, st>>>(s->counters.p + depth, qin.hit, bins);
               k_shade<<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
               launches++;
           } }

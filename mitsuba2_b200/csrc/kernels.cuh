@@ -148,13 +148,19 @@ template <bool AnyHit>
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_trace(Bvh bvh, const uint32_t *count_ptr, uint32_t count_max, const float4 *__restrict__ o_mint,
         const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded,
-        uint32_t *work, uint32_t refill) {
+        uint32_t *work, uint32_t refill, const uint8_t *__restrict__ prim_class) {
     __shared__ uint2 s_stack[kStackFast * kBlock];
     uint32_t count = count_ptr ? min(*count_ptr, count_max) : count_max;
     trace_persistent<AnyHit>(bvh, count, o_mint, d_maxt, work, refill, s_stack,
         [=](uint32_t i, bool found, const Hit &h) {
             if (AnyHit) occluded[i] = found ? 1u : 0u;
-            else hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+            else {
+                // wavefront launches tag the hit with its shade class in the two top bits of the primitive id
+                // (kPrimMask strips them again in make_si); the public intersect entry points pass no table
+                uint32_t p = h.prim;
+                if (prim_class != nullptr && found) p |= (uint32_t) prim_class[p] << 30;
+                hits[i] = make_float4(h.t, h.u, h.v, u2f(p));
+            }
         });
 }
 // brute force = Scene::ray_intersect_naive (kdtree.h:2304-2329) with the same triangle test
@@ -203,14 +209,13 @@ struct ShadeBins {
     uint32_t *counts;                     // kShadeClasses counters of the current depth
     uint32_t pool;
 };
-__global__ void k_classify(SceneDev sc, const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins bins) {
+__global__ void k_classify(const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins bins) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t count = *count_ptr;
     int cls = -1;
     if (i < count) {
         float4 h = hit[i];
-        cls = 0;
-        if (h.x != INFINITY) cls = 1 + sc.bsdfs[sc.meshes[sc.faces[f2u(h.w)].w].bsdf].type;
+        cls = h.x != INFINITY ? (int) (f2u(h.w) >> 30) : 0;       // class tag written by k_trace
     }
 #pragma unroll
     for (int c = 0; c < kShadeClasses; ++c) {

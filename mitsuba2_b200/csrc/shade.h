@@ -12,9 +12,10 @@ HD float3 ld3(const float *a, uint32_t i) { return mk3(a[3 * i], a[3 * i + 1], a
 
 // ShapeKDTree::create_surface_interaction (include/mitsuba/render/kdtree.h:2334-2368) +
 // Mesh::fill_surface_interaction (src/librender/mesh.cpp:399-462); miss: scene_native.inl:29-31.
+constexpr uint32_t kPrimMask = 0x3fffffffu;     // primitive ids use 30 bits; the top two carry the shade class in the queues
 HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     SI si;
-    si.t = hit.x; si.prim = f2u(hit.w); si.valid = hit.x != INFINITY;
+    si.t = hit.x; si.prim = f2u(hit.w) & kPrimMask; si.valid = hit.x != INFINITY;
     if (!si.valid) { si.wi = -d; si.mesh = -1; si.p = o; si.n = mk3(0.f); si.u = si.v = 0.f; si.sh.s = si.sh.t = si.sh.n = mk3(0.f); return si; }
     uint4 f = sc.faces[si.prim];
     si.mesh = (int) f.w;

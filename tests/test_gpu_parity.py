@@ -299,4 +299,5 @@ def test_cpp_host_renders_through_the_c_abi(mi, tmp_path):
     assert r.returncode == 0, r.stderr + r.stdout
     img = imageio.read_pfm(out)
     assert img.shape == (128, 128, 3) and np.isfinite(img).all()
-    assert img[64, 20, 0] > 2 * img[64, 20, 1] and img[64, 108, 1] > 2 * img[64, 108, 0]      # red wall left, green wall right
+    # Mitsuba's look_at is left-handed: +x (the green wall) appears on the left of the image
+    assert img[64, 20, 1] > 2 * img[64, 20, 0] and img[64, 108, 0] > 2 * img[64, 108, 1]
