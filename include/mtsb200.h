@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 2
+#define MTSB_ABI_VERSION 3
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -32,14 +32,24 @@ enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
 /* Texture: `Texture::eval` (include/mitsuba/render/texture.h:40-143).
  * CONSTANT = src/spectra/srgb.cpp / srgb_d65.cpp / uniform.cpp in the rgb variant,
  * BITMAP   = src/textures/bitmap.cpp:250-293 (bilinear, repeat wrap, 3x3 uv transform). */
-enum { MTSB_TEX_CONSTANT = 0, MTSB_TEX_BITMAP = 1 };
+enum { MTSB_TEX_CONSTANT = 0, MTSB_TEX_BITMAP = 1,
+       /* spectral mode only (MTSB_MODE_SPECTRAL): tabulated spectra, wavelengths in nm */
+       MTSB_TEX_REGULAR = 2,    /* src/spectra/regular.cpp: `width` samples evenly spaced over [lambda_min, lambda_max] */
+       MTSB_TEX_IRREGULAR = 3,  /* src/spectra/irregular.cpp: data = `width` wavelengths followed by `width` values */
+       MTSB_TEX_UNIFORM = 4 };  /* src/spectra/uniform.cpp: value[0] at every wavelength */
+/* In spectral mode the host hands over what the reference's texture plugins store in that mode: CONSTANT `value` and
+   3-channel BITMAP texels are sRGB-model coefficients (srgb_model_fetch, src/librender/srgb.cpp:15-42; srgb.cpp:44-48,
+   bitmap.cpp:262-275), not colours.  d65_scale != 0 multiplies the value by the D65 whitepoint spectrum times d65_scale:
+   that is `srgb_d65` (src/spectra/srgb_d65.cpp:36-62), the spectrum of an emitter given as an rgb colour. */
 typedef struct mtsb_texture_desc {
     int32_t  type;
-    float    value[3];          /* CONSTANT: rgb */
-    uint32_t width, height;     /* BITMAP */
+    float    value[3];          /* CONSTANT: rgb (spectral mode: model coefficients); UNIFORM: value[0] */
+    uint32_t width, height;     /* BITMAP; REGULAR / IRREGULAR: width = number of samples */
     uint32_t channels;          /* BITMAP: 1 or 3 */
-    const float *data;          /* BITMAP: row-major, channels interleaved (host pointer) */
+    const float *data;          /* BITMAP: row-major, channels interleaved (host pointer); REGULAR / IRREGULAR: samples */
     float    to_uv[9];          /* BITMAP: row-major 3x3 affine uv transform */
+    float    lambda_min, lambda_max;   /* REGULAR */
+    float    d65_scale;         /* spectral mode: 0 = plain; else value *= D65(lambda) * d65_scale */
 } mtsb_texture_desc;
 
 /* BSDF: `BSDF::sample/eval/pdf` (include/mitsuba/render/bsdf.h).
@@ -76,6 +86,10 @@ typedef struct mtsb_emitter_desc {
     float    to_world[16];      /* ENVMAP: row-major 4x4 */
     float    scale;             /* ENVMAP */
     float    position[3];       /* POINT: world-space position */
+    const float *coeff_scale;   /* ENVMAP, spectral mode: width*height*4, per texel srgb_model_fetch(rgb / max(1e-8, 2 hmax(rgb)))
+                                   and the scale 2 hmax(rgb) (src/emitters/envmap.cpp:98-110); `rgba` still drives the importance map */
+    int32_t  radiance_tex;      /* spectral mode: texture holding the radiance / intensity spectrum (AREA, CONSTANT, POINT);
+                                   ENVMAP texels are then model coefficients + scale (src/emitters/envmap.cpp:98-110) */
 } mtsb_emitter_desc;
 
 /* Mesh: `Mesh` buffers (include/mitsuba/render/mesh.h:328-332); world-space positions. */
@@ -107,6 +121,7 @@ typedef struct mtsb_integrator_desc {
     int32_t rr_depth;   /* default 5 */
 } mtsb_integrator_desc;
 
+enum { MTSB_MODE_RGB = 0, MTSB_MODE_SPECTRAL = 1 };
 typedef struct mtsb_scene_desc {
     uint32_t n_meshes, n_bsdfs, n_textures, n_emitters, n_sensors;
     const mtsb_mesh_desc    *meshes;
@@ -115,6 +130,8 @@ typedef struct mtsb_scene_desc {
     const mtsb_emitter_desc *emitters;
     const mtsb_sensor_desc  *sensors;
     mtsb_integrator_desc integrator;
+    int32_t mode;               /* MTSB_MODE_RGB (scalar_rgb semantics) or MTSB_MODE_SPECTRAL (scalar_spectral: 4 wavelengths
+                                   per path, include/mitsuba/core/spectrum.h:304-316, film in XYZ via cie1931_xyz :147-217) */
 } mtsb_scene_desc;
 
 /* ---- SoA ray / hit records (128-bit loads) ------------------------------------------ */

@@ -11,7 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
 
 MEM_HOST, MEM_DEVICE = 0, 1
-TEX_CONSTANT, TEX_BITMAP = 0, 1
+TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM = 0, 1, 2, 3, 4
+MODE_RGB, MODE_SPECTRAL = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC = 0, 1, 2
 MF_BECKMANN, MF_GGX = 0, 1
 EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
@@ -24,7 +25,8 @@ c_u64_p = C.POINTER(C.c_uint64)
 
 class TextureDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("value", C.c_float * 3), ("width", C.c_uint32), ("height", C.c_uint32),
-                ("channels", C.c_uint32), ("data", c_float_p), ("to_uv", C.c_float * 9)]
+                ("channels", C.c_uint32), ("data", c_float_p), ("to_uv", C.c_float * 9),
+                ("lambda_min", C.c_float), ("lambda_max", C.c_float), ("d65_scale", C.c_float)]
 
 
 class BsdfDesc(C.Structure):
@@ -37,7 +39,7 @@ class BsdfDesc(C.Structure):
 class EmitterDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("radiance", C.c_float * 3), ("mesh_id", C.c_int32), ("width", C.c_uint32),
                 ("height", C.c_uint32), ("rgba", c_float_p), ("to_world", C.c_float * 16), ("scale", C.c_float),
-                ("position", C.c_float * 3)]
+                ("position", C.c_float * 3), ("coeff_scale", c_float_p), ("radiance_tex", C.c_int32)]
 
 
 class MeshDesc(C.Structure):
@@ -61,7 +63,7 @@ class SceneDesc(C.Structure):
                 ("n_emitters", C.c_uint32), ("n_sensors", C.c_uint32),
                 ("meshes", C.POINTER(MeshDesc)), ("bsdfs", C.POINTER(BsdfDesc)), ("textures", C.POINTER(TextureDesc)),
                 ("emitters", C.POINTER(EmitterDesc)), ("sensors", C.POINTER(SensorDesc)),
-                ("integrator", IntegratorDesc)]
+                ("integrator", IntegratorDesc), ("mode", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -3,6 +3,7 @@
 #include "../../include/mtsb200.h"
 #include "kernels.cuh"
 #include "host_tables.h"
+#include "cie_tables.h"
 #include <cub/cub.cuh>
 #include <string>
 #include <vector>
@@ -79,6 +80,9 @@ struct mtsb_scene {
     std::vector<int> tex_table;                               // texture id -> tables index (-1 constant)
     std::vector<int> emitter_cdf_table;
     DevBuf<float4> env_rgba;
+    bool spectral = false;                   // MTSB_MODE_SPECTRAL: 4 wavelengths per path
+    DevBuf<float> cie;                       // spectral mode: CIE 1931 x/y/z + D65/10568 (cie_tables.h)
+    DevBuf<float2> q_we[2];                  // spectral mode: wavelength sample + eta per queue entry
     DevBuf<uint4> nodes; DevBuf<float4> tris;
     SceneDev dev;
     std::vector<std::unique_ptr<SensorHost>> sensors;
@@ -332,6 +336,17 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
     CU(s->uv.upload(h_uv.data(), h_uv.size(), st));
     CU(s->faces.upload(h_faces.data(), h_faces.size(), st));
     CU(cudaStreamSynchronize(st));
+    // ---- colour mode
+    CHECK_ARG(d->mode == MTSB_MODE_RGB || d->mode == MTSB_MODE_SPECTRAL);
+    s->spectral = d->mode == MTSB_MODE_SPECTRAL;
+    if (s->spectral) {
+        std::vector<float> tbl(4 * 95);
+        for (int k = 0; k < 3 * 95; ++k) tbl[k] = kCie1931[k];
+        for (int k = 0; k < 95; ++k) tbl[3 * 95 + k] = kCieD65[k] * (1.f / 10568.f);      // D65Spectrum: scale / 10568 (d65.cpp:63)
+        CU(s->cie.upload(tbl.data(), tbl.size(), st));
+        CU(cudaStreamSynchronize(st));
+        s->dev.cie = s->cie.p;
+    }
     // ---- textures
     for (uint32_t i = 0; i < d->n_textures; ++i) {
         const mtsb_texture_desc &t = d->textures[i];
@@ -345,7 +360,20 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             CU(s->tables[ti]->upload(t.data, (size_t) t.width * t.height * t.channels, st));
             CU(cudaStreamSynchronize(st));
             td.data = s->tables[ti]->p;
+        } else if (t.type == MTSB_TEX_REGULAR || t.type == MTSB_TEX_IRREGULAR) {
+            if (!s->spectral) return fail(MTSB_E_INVALID, "tabulated spectra need MTSB_MODE_SPECTRAL (rgb variants pre-integrate them to a colour on the host)");
+            CHECK_ARG(t.data && t.width >= 2);
+            if (t.type == MTSB_TEX_REGULAR) CHECK_ARG(t.lambda_max > t.lambda_min);
+            else for (uint32_t k = 1; k < t.width; ++k) CHECK_ARG(t.data[k] > t.data[k - 1]);     // IrregularContinuousDistribution: nodes strictly increasing
+            td.w = t.width; td.lambda_min = t.lambda_min; td.lambda_max = t.lambda_max;
+            s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1;
+            CU(s->tables[ti]->upload(t.data, (size_t) t.width * (t.type == MTSB_TEX_IRREGULAR ? 2 : 1), st));
+            CU(cudaStreamSynchronize(st));
+            td.data = s->tables[ti]->p;
+        } else if (t.type == MTSB_TEX_UNIFORM) {
+            if (!s->spectral) return fail(MTSB_E_INVALID, "uniform spectra need MTSB_MODE_SPECTRAL");
         } else CHECK_ARG(t.type == MTSB_TEX_CONSTANT);
+        if (s->spectral) td.d65_scale = t.d65_scale; else CHECK_ARG(t.d65_scale == 0.f);
         s->tex.push_back(td); s->tex_table.push_back(ti);
     }
     // ---- bsdfs
@@ -371,8 +399,12 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
         const mtsb_emitter_desc &e = d->emitters[i];
         EmitterDev ed; memset(&ed, 0, sizeof(ed));
-        ed.type = e.type;
+        ed.type = e.type; ed.radiance_tex = -1;
         s->emitter_cdf_table.push_back(-1);
+        if (s->spectral && e.type != MTSB_EMITTER_ENVMAP) {
+            CHECK_ARG(e.radiance_tex >= 0 && (uint32_t) e.radiance_tex < d->n_textures && d->textures[e.radiance_tex].type != MTSB_TEX_BITMAP);
+            ed.radiance_tex = e.radiance_tex;
+        }
         if (e.type == MTSB_EMITTER_AREA) {
             CHECK_ARG(e.mesh_id >= 0 && (uint32_t) e.mesh_id < d->n_meshes && d->meshes[e.mesh_id].emitter_id == (int32_t) i);
             ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
@@ -392,6 +424,10 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             if (!invert4x4(e.to_world, ed.to_local)) return fail(MTSB_E_INVALID, "envmap to_world is singular");
             size_t npx = (size_t) e.width * e.height;
             std::vector<float4> rgba(npx);
+            if (s->spectral) {       // texels = sRGB-model coefficients + scale (envmap.cpp:98-110); importance still from the rgb image
+                CHECK_ARG(e.coeff_scale != nullptr);
+                for (size_t k = 0; k < npx; ++k) rgba[k] = make_float4(e.coeff_scale[4 * k], e.coeff_scale[4 * k + 1], e.coeff_scale[4 * k + 2], e.coeff_scale[4 * k + 3]);
+            } else
             for (size_t k = 0; k < npx; ++k) rgba[k] = make_float4(e.rgba[4 * k], e.rgba[4 * k + 1], e.rgba[4 * k + 2], 1.f);
             CU(s->env_rgba.upload(rgba.data(), npx, st));
             ed.rgba = s->env_rgba.p;
@@ -520,6 +556,7 @@ static int ensure_pool(mtsb_scene *s, uint32_t n) {
     for (int k = 0; k < 2; ++k) {
         CU(s->q_o[k].alloc(n)); CU(s->q_d[k].alloc(n)); CU(s->q_hit[k].alloc(n)); CU(s->q_te[k].alloc(n));
         CU(s->q_misc[k].alloc(n)); CU(s->q_rng[k].alloc(n));
+        if (s->spectral) CU(s->q_we[k].alloc(n));
     }
     CU(s->s_o.alloc(n)); CU(s->s_d.alloc(n)); CU(s->s_c.alloc(n)); CU(s->result.alloc(n)); CU(s->class_lists.alloc((size_t) kShadeClasses * n)); 
     s->pool = n;
@@ -527,7 +564,7 @@ static int ensure_pool(mtsb_scene *s, uint32_t n) {
 }
 static PathQueue make_queue(mtsb_scene *s, int k) {
     PathQueue q; q.o_mint = s->q_o[k].p; q.d_maxt = s->q_d[k].p; q.hit = s->q_hit[k].p; q.thr_eta = s->q_te[k].p;
-    q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; return q;
+    q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; q.wav_eta = s->q_we[k].p; return q;
 }
 
 // One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
@@ -541,7 +578,8 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
     int cur = 0;
     const unsigned tg = trace_grid_for(s->ctx, n);
-    { StageTimer t(s->ctx, ST_RAYGEN); k_raygen<<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
+    { StageTimer t(s->ctx, ST_RAYGEN); if (s->spectral) k_raygen<Spectral><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p);
+      else k_raygen<Rgb><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
     for (int depth = 1; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
         { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
@@ -549,11 +587,13 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
           if (grad) k_shade_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
           else if (depth == 1 || !s->ctx->bin_materials) {      // primary hits are already coherent: identity lists
               ShadeBins bins; bins.lists = nullptr; bins.counts = s->counters.p + depth; bins.pool = 0;
-              k_shade<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              if (s->spectral) k_shade<Spectral><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              else k_shade<Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
           } else {
               ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + 4 * depth; bins.pool = s->pool;
               k_classify<<<grid_for(n), kBlock, 0, st>>>(s->counters.p + depth, qin.hit, bins);
-              k_shade<<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              if (s->spectral) k_shade<Spectral><<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              else k_shade<Rgb><<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
               launches++;
           } }
         launches += 2;
@@ -569,7 +609,7 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
             if (next == 0) break;
         }
     }
-    if (splat) { StageTimer t(s->ctx, ST_FILM); k_splat<<<grid_for(n), kBlock, 0, st>>>(sn, b); launches++; }
+    if (splat) { StageTimer t(s->ctx, ST_FILM); if (s->spectral) k_splat<Spectral><<<grid_for(n), kBlock, 0, st>>>(sn, b); else k_splat<Rgb><<<grid_for(n), kBlock, 0, st>>>(sn, b); launches++; }
     return MTSB_OK;
 }
 

@@ -4,7 +4,14 @@
 
 namespace mtsb {
 
-struct DirSample { float3 p, n, d; float dist, pdf; float3 value; bool delta; };
+template <typename M> struct DirSampleT { float3 p, n, d; float dist, pdf; typename M::Spec value; bool delta; };
+typedef DirSampleT<Rgb> DirSample;
+
+// radiance (area, constant) / intensity (point) of an emitter: an rgb triple, or in spectral mode a texture
+// (srgb_d65 for rgb input, or any tabulated spectrum)
+template <typename M> HD typename M::Spec emitter_radiance(const SceneDev &sc, const EmitterDev &e, float4 wav);
+template <> HD float3 emitter_radiance<Rgb>(const SceneDev &, const EmitterDev &e, float4) { return e.radiance; }
+template <> HD float4 emitter_radiance<Spectral>(const SceneDev &sc, const EmitterDev &e, float4 wav) { return tex_eval_spectral(sc, e.radiance_tex, 0.f, 0.f, wav); }
 
 // enoki::binary_search (ext/enoki/include/enoki/array_utils.h:153-171)
 template <typename Pred> HD uint32_t binary_search(uint32_t start, uint32_t end, Pred pred) {
@@ -27,14 +34,32 @@ HD float3 env_lookup(const EmitterDev &e, float u, float v) {
     float3 b = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
     return mk3(fmaf(w0y, a.x, w1y * b.x), fmaf(w0y, a.y, w1y * b.y), fmaf(w0y, a.z, w1y * b.z)) * e.scale;
 }
+// spectral branch of EnvironmentMapEmitter::eval_spectrum (envmap.cpp:285-306): texels = model coefficients + scale
+HD float4 env_lookup_spectral(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav) {
+    u *= (float) (e.w - 1); v *= (float) (e.h - 1);
+    uint32_t px = min((uint32_t) u, e.w - 2), py = min((uint32_t) v, e.h - 2);
+    float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t idx = px + py * e.w;
+    float4 v00 = e.rgba[idx], v10 = e.rgba[idx + 1], v01 = e.rgba[idx + e.w], v11 = e.rgba[idx + e.w + 1];
+    auto bx = [&](float a, float b) { return fmaf(w0x, a, w1x * b); };
+    auto by = [&](float a, float b) { return fmaf(w0y, a, w1y * b); };
+    float4 s0 = map_spec(srgb_model_eval(xyz(v00), wav), srgb_model_eval(xyz(v10), wav), bx),
+           s1 = map_spec(srgb_model_eval(xyz(v01), wav), srgb_model_eval(xyz(v11), wav), bx);
+    float f = by(bx(v00.w, v10.w), bx(v01.w, v11.w));
+    return map_spec(s0, s1, by) * d65_eval(sc, wav) * f * e.scale;
+}
+template <typename M> HD typename M::Spec env_lookup_m(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav);
+template <> HD float3 env_lookup_m<Rgb>(const SceneDev &, const EmitterDev &e, float u, float v, float4) { return env_lookup(e, u, v); }
+template <> HD float4 env_lookup_m<Spectral>(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav) { return env_lookup_spectral(sc, e, u, v, wav); }
 HD void env_dir_to_uv(const EmitterDev &e, float3 dworld, float &u, float &v, float3 &dl) {
     dl = xform_vec(e.to_local, dworld);
     u = atan2f(dl.x, -dl.z) * kInvTwoPi; v = safe_acos(dl.y) * kInvPi;
     u -= floorf(u); v -= floorf(v);
 }
-HD float3 env_eval(const EmitterDev &e, float3 dworld) {     // direction pointing away from the scene
+template <typename M = Rgb>
+HD typename M::Spec env_eval(const SceneDev &sc, const EmitterDev &e, float3 dworld, float4 wav = float4()) {     // direction pointing away from the scene
     float u, v; float3 dl; env_dir_to_uv(e, dworld, u, v, dl);
-    return env_lookup(e, u, v);
+    return env_lookup_m<M>(sc, e, u, v, wav);
 }
 // Hierarchical2D<Float,0> (include/mitsuba/core/distr_2d.h:317-403, 495-530); level 0 = bilinear data,
 // levels 1.. = MIP pyramid in 2x2-blocked layout (Level::index, :583-586)
@@ -91,8 +116,9 @@ HD float env_pdf_direction(const EmitterDev &e, float3 dworld) {
     float inv_sin = 1.f / sqrtf(fmaxf(sqr(d.x) + sqr(d.z), sqr(kEpsilon)));
     return h2d_eval(e, u, v) * inv_sin * (1.f / (2.f * sqr(kPi)));
 }
-HD DirSample env_sample_direction(const EmitterDev &e, float3 ref_p, float sx, float sy) {
-    DirSample ds;
+template <typename M>
+HD DirSampleT<M> env_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {
+    DirSampleT<M> ds;
     float u, v, pdf; h2d_sample(e, sx, sy, u, v, pdf);
     float st, ct, sp, cp; sincospif(v, &st, &ct); sincospif(2.f * u, &sp, &cp);      // theta = v pi, phi = 2 u pi
     float3 d = mk3(cp * st, sp * st, ct);         // math::sphdir
@@ -102,14 +128,15 @@ HD DirSample env_sample_direction(const EmitterDev &e, float3 ref_p, float sx, f
     d = xform_vec(e.to_world, d);
     ds.p = ref_p + d * dist; ds.n = -d; ds.d = d; ds.dist = dist;
     ds.pdf = pdf > 0.f ? pdf * inv_sin * (1.f / (2.f * sqr(kPi))) : 0.f;
-    ds.value = env_lookup(e, u, v) / ds.pdf;
+    ds.value = env_lookup_m<M>(sc, e, u, v, wav) / ds.pdf;
     return ds;
 }
 
 // ---- area light on a mesh (src/emitters/area.cpp:103-125, src/librender/shape.cpp:252-283,
 //      src/librender/mesh.cpp:320-365, include/mitsuba/core/distr_1d.h:144-203) ---------------------
-HD DirSample area_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy) {
-    DirSample ds;
+template <typename M>
+HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {
+    DirSampleT<M> ds;
     const MeshDev m = sc.meshes[e.mesh];
     float value = sy * e.cdf_sum;
     const float *cdf = e.cdf;
@@ -134,7 +161,7 @@ HD DirSample area_sample_direction(const SceneDev &sc, const EmitterDev &e, floa
     float dp = fabsf(dot(ds.d, ds.n));
     ds.pdf = e.normalization * (dp != 0.f ? dist2 / dp : 0.f);
     bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
-    ds.value = active ? e.radiance / ds.pdf : mk3(0.f);
+    ds.value = active ? emitter_radiance<M>(sc, e, wav) / ds.pdf : M::splat(0.f);
     return ds;
 }
 HD float area_pdf_direction(const EmitterDev &e, float3 d, float3 n, float dist) {
@@ -151,23 +178,26 @@ HD float3 square_to_uniform_sphere(float sx, float sy) {
     return mk3(r * cs, r * sn, z);
 }
 // ConstantBackgroundEmitter::sample_direction (src/emitters/constant.cpp:77-103); pdf_direction = 1/(4 pi)
-HD DirSample constant_sample_direction(const EmitterDev &e, float3 ref_p, float sx, float sy) {
-    DirSample ds; float3 d = square_to_uniform_sphere(sx, sy);
+template <typename M>
+HD DirSampleT<M> constant_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {
+    DirSampleT<M> ds; float3 d = square_to_uniform_sphere(sx, sy);
     ds.dist = 2.f * e.bsphere_radius; ds.p = ref_p + d * ds.dist; ds.n = -d; ds.d = d;
-    ds.pdf = 0.25f * kInvPi; ds.value = e.radiance * (1.f / ds.pdf); ds.delta = false;
+    ds.pdf = 0.25f * kInvPi; ds.value = emitter_radiance<M>(sc, e, wav) * (1.f / ds.pdf); ds.delta = false;
     return ds;
 }
 // PointLight::sample_direction (src/emitters/point.cpp:74-98): delta position, pdf 1, intensity / dist^2
-HD DirSample point_sample_direction(const EmitterDev &e, float3 ref_p) {
-    DirSample ds; ds.p = e.position; ds.n = mk3(0.f); ds.pdf = 1.f; ds.delta = true;
+template <typename M>
+HD DirSampleT<M> point_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float4 wav) {
+    DirSampleT<M> ds; ds.p = e.position; ds.n = mk3(0.f); ds.pdf = 1.f; ds.delta = true;
     ds.d = ds.p - ref_p; ds.dist = norm(ds.d);
     float inv = 1.f / ds.dist; ds.d = ds.d * inv;
-    ds.value = e.radiance * (inv * inv);
+    ds.value = emitter_radiance<M>(sc, e, wav) * (inv * inv);
     return ds;
 }
 
-HD DirSample sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx, float sy) {
-    DirSample ds; ds.delta = false; ds.pdf = 0.f; ds.value = mk3(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
+template <typename M = Rgb>
+HD DirSampleT<M> sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx, float sy, float4 wav = float4()) {
+    DirSampleT<M> ds; ds.delta = false; ds.pdf = 0.f; ds.value = M::splat(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
     if (sc.n_emitters == 0) return ds;
     uint32_t index = 0; float epdf = 1.f;
     if (sc.n_emitters > 1) {
@@ -177,10 +207,10 @@ HD DirSample sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx
         sx = (sx - (float) index * epdf) * ne;
     }
     const EmitterDev &e = sc.emitters[index];
-    if (e.type == 0) ds = area_sample_direction(sc, e, ref_p, sx, sy);
-    else if (e.type == 1) ds = env_sample_direction(e, ref_p, sx, sy);
-    else if (e.type == 2) ds = constant_sample_direction(e, ref_p, sx, sy);
-    else ds = point_sample_direction(e, ref_p);
+    if (e.type == 0) ds = area_sample_direction<M>(sc, e, ref_p, sx, sy, wav);
+    else if (e.type == 1) ds = env_sample_direction<M>(sc, e, ref_p, sx, sy, wav);
+    else if (e.type == 2) ds = constant_sample_direction<M>(sc, e, ref_p, sx, sy, wav);
+    else ds = point_sample_direction<M>(sc, e, ref_p, wav);
     ds.delta = e.type == 3;
     if (sc.n_emitters > 1) { ds.pdf *= epdf; ds.value *= 1.f / epdf; }
     return ds;

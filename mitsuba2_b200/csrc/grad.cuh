@@ -19,7 +19,8 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex-position gradients are not implemented (texture gradients only)");
     CHECK_ARG(grad_texture && tex_id >= 0 && (size_t) tex_id < s->tex.size());
     const TexDev td = s->tex[tex_id];
-    if (td.type == 0) return fail(MTSB_E_INVALID, "mtsb_render_grad: texture is not a bitmap");
+    if (td.type != 1) return fail(MTSB_E_INVALID, "mtsb_render_grad: texture is not a bitmap");
+    if (s->spectral) return fail(MTSB_E_INVALID, "mtsb_render_grad: the adjoint pass is implemented for MTSB_MODE_RGB only");
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;

@@ -182,10 +182,11 @@ __global__ void k_trace_naive(Bvh bvh, uint32_t count, const float4 *o_mint, con
 // ---------------- wavefront stages ---------------------------------------------------------------
 // counters layout (uint32): [0..1023] live paths entering depth d (index d), [1024..2047] shadow rays of depth d
 // stats (uint64): [0] closest rays, [1] shadow rays, [2] segments
+template <typename M>
 __global__ void k_raygen(SensorDev sn, RenderBatch b, PathQueue q, uint32_t *counters) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) counters[1] = b.n_paths;
-    if (i < b.n_paths) raygen_body(sn, b, q, i);
+    if (i < b.n_paths) raygen_body<M>(sn, b, q, i);
 }
 
 __device__ __forceinline__ uint32_t warp_alloc(uint32_t *counter, bool want) {
@@ -241,7 +242,10 @@ __device__ __forceinline__ bool shade_index(const ShadeBins &bins, uint32_t t, u
     return false;
 }
 
-__global__ void __launch_bounds__(kBlock, kShadeBlocksPerSM)
+// M = Rgb (3 channels) or Spectral (4 wavelengths; the spectral instance needs more registers, so it is not held to
+// the rgb kernel's occupancy target)
+template <typename M>
+__global__ void __launch_bounds__(kBlock, M::spectral ? 4 : kShadeBlocksPerSM)
 k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
         unsigned long long *stats, uint32_t depth, ShadeBins bins) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x, i = 0;
@@ -249,11 +253,12 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
     if (t == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
     bool live = shade_index(bins, t, i);
     ShadeOut out; out.extend = false; out.shadow = false;
-    if (live) out = shade_body(sc, qin, b, i);
+    if (live) out = shade_body<M>(sc, qin, b, i);
     uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
     if (out.extend) {
         qout.o_mint[slot] = out.o_mint; qout.d_maxt[slot] = out.d_maxt; qout.thr_eta[slot] = out.thr_eta;
         qout.misc[slot] = out.misc; qout.rng[slot] = out.rng;
+        if (M::spectral) qout.wav_eta[slot] = out.wav_eta;
     }
     uint32_t sslot = warp_alloc(&counters[1024 + depth], out.shadow);
     if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
@@ -310,12 +315,13 @@ __device__ __forceinline__ void film_atomic_add(const SensorDev &sn, uint32_t pi
 }
 
 // film splat at batch end with warp-aggregated atomics (one atomic set per warp when the warp's samples share a pixel)
+template <typename M>
 __global__ void __launch_bounds__(kBlock)
 k_splat(SensorDev sn, RenderBatch b) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     bool live = i < b.n_paths;
     float4 xyza = make_float4(0.f, 0.f, 0.f, 0.f); float wgt = 0.f; float fx = -10.f, fy = -10.f;
-    if (live) { xyza = radiance_to_xyza(b.result[i]); wgt = 1.f; path_film_pos(sn, b, i, fx, fy); }
+    if (live) { xyza = result_to_xyza<M>(b.result[i]); wgt = 1.f; path_film_pos(sn, b, i, fx, fy); }
     if (sn.radius <= 1.f) {
         int lx = (int) ceilf(fx - 1.f), ly = (int) ceilf(fy - 1.f);
         bool ok = live && lx >= 0 && ly >= 0 && lx < (int) sn.width && ly < (int) sn.height;

@@ -14,17 +14,18 @@ struct PathQueue {
     float4 *thr_eta;           // throughput rgb, eta
     uint4  *misc;              // path_id, depth | (prev_delta << 31), prev bsdf pdf (bits), unused
     uint4  *rng;               // PCG32 state lo/hi, inc lo/hi
+    float2 *wav_eta;           // spectral mode only (+8 B): wavelength sample of the path, eta; thr_eta then holds 4 channels
 };
 struct ShadowQueue {
     float4 *o_mint, *d_maxt;   // shadow ray
-    float4 *contrib_id;        // mis * throughput * bsdf * Le/pdf (rgb), path_id (bits)
+    float4 *contrib_id;        // mis * throughput * bsdf * Le/pdf (rgb; spectral mode: already converted to XYZ), path_id (bits)
 };
 struct RenderBatch {
     uint32_t n_paths;          // paths in this batch
     uint64_t offset;           // global path index of the batch's first path (index = pixel*spp_batch + s)
     uint32_t spp_begin, spp_batch, spp_total;
     uint64_t seed;
-    float4 *result;            // per path: radiance rgb, alpha
+    float4 *result;            // per path: radiance rgb (spectral mode: XYZ), alpha
 };
 
 HD void rng_store(uint4 *dst, const Pcg32 &r) {
@@ -52,11 +53,13 @@ HD void sensor_sample_ray(const SensorDev &sn, float px, float py, float4 &o_min
     o_mint = mk4(o, sn.near_clip * inv_z); d_maxt = mk4(dw, sn.far_clip * inv_z);
 }
 
+template <typename M = Rgb>
 HD void raygen_body(const SensorDev &sn, const RenderBatch &b, const PathQueue &q, uint32_t i) {
     uint32_t pixel, stream; path_ids(b, i, pixel, stream);
     Pcg32 rng = sampler_seed(b.seed, stream);
     float jx = rng.next_f32(), jy = rng.next_f32();
-    (void) rng.next_f32();                       // wavelength sample (integrator.cpp:237), unused in rgb
+    float wavelength_sample = rng.next_f32();    // integrator.cpp:237; drawn in every mode, used by the spectral one
+    if (M::spectral) q.wav_eta[i] = make_float2(wavelength_sample, 1.f);
     float fx = (float) (pixel % sn.width) + jx, fy = (float) (pixel / sn.width) + jy;
     float4 o, d;
     sensor_sample_ray(sn, fx / (float) sn.width, fy / (float) sn.height, o, d);
@@ -71,11 +74,21 @@ HD float mis_weight(float a, float b) { a *= a; b *= b; return a > 0.f ? a / (a 
 
 struct ShadeOut {
     bool extend, shadow;
-    float4 o_mint, d_maxt, thr_eta; uint4 misc, rng;          // extension record
+    float4 o_mint, d_maxt, thr_eta; uint4 misc, rng; float2 wav_eta;   // extension record
     float4 s_o_mint, s_d_maxt, s_contrib_id;                  // shadow record
     // adjoint bookkeeping (filled always; cheap): first-hit info of this vertex
     float3 emitted;                                            // radiance added at this vertex (already weighted)
 };
+
+// per-mode packing of (throughput, eta): rgb -> one float4; spectral -> 4 channels + (wavelength sample, eta) in wav_eta
+HD void load_throughput(const PathQueue &, uint32_t, float4 te, float3 &thr, float &eta, float2 &) { thr = xyz(te); eta = te.w; }
+HD void load_throughput(const PathQueue &q, uint32_t i, float4 te, float4 &thr, float &eta, float2 &we) { thr = te; we = q.wav_eta[i]; eta = we.y; }
+HD void store_throughput(ShadeOut &out, float3 thr, float eta, float2) { out.thr_eta = mk4(thr, eta); }
+HD void store_throughput(ShadeOut &out, float4 thr, float eta, float2 we) { out.thr_eta = thr; out.wav_eta = make_float2(we.x, eta); }
+// what a contribution adds to the per-path result: rgb radiance as is; spectral mode applies the sensor's wavelength
+// weight and converts to XYZ right away (integrator.cpp:249-262 does both once per sample; the conversion is linear)
+HD float3 to_result(const SceneDev &, float3 c, float4, float4) { return c; }
+HD float3 to_result(const SceneDev &sc, float4 c, float4 wav, float4 ray_weight) { return spectrum_to_xyz(sc, ray_weight * c, wav); }
 
 // ---- adjoint of the path w.r.t. a bitmap texture that enters a BSDF multiplicatively ------------------------------
 // (diffuse `reflectance`, src/bsdfs/diffuse.cpp:78-135; roughconductor `specular_reflectance`, roughconductor.cpp:270)
@@ -117,14 +130,17 @@ HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx 
 
 // One iteration of the loop in path.cpp:124-208 for queue entry i.  `result` accumulates emission.  `grad` is called
 // once the vertex's BSDF is known to be used (after emission, Russian roulette and the depth cut).
-template <typename GradFn = NoGrad>
+template <typename M = Rgb, typename GradFn = NoGrad>
 HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, GradFn grad = GradFn()) {
+    typedef typename M::Spec Spec;
     ShadeOut out; out.extend = false; out.shadow = false; out.emitted = mk3(0.f);
     float4 o4 = q.o_mint[i], d4 = q.d_maxt[i], h4 = q.hit[i], te = q.thr_eta[i];
     uint4 misc = q.misc[i];
     uint32_t path_id = misc.x, depth = misc.y & 0x7fffffffu; bool prev_delta = (misc.y >> 31) != 0;
     float prev_pdf = u2f(misc.z);
-    float3 thr = xyz(te); float eta = te.w;
+    Spec thr; float eta; float4 wav = float4(), ray_weight = float4(); float2 we = float2();
+    load_throughput(q, i, te, thr, eta, we);
+    if (M::spectral) sample_wavelengths(we.x, wav, ray_weight);
     float3 o = xyz(o4), d = xyz(d4);
     SI si = make_si(sc, o, d, h4);
 
@@ -132,23 +148,23 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     int em = si.valid ? sc.meshes[si.mesh].emitter : sc.env_emitter;
     if (em >= 0) {
         const EmitterDev &e = sc.emitters[em];
-        float3 Le; float emitter_pdf = 0.f;
+        Spec Le; float emitter_pdf = 0.f;
         if (e.type == 0) {
-            Le = si.wi.z > 0.f ? e.radiance : mk3(0.f);
+            Le = si.wi.z > 0.f ? emitter_radiance<M>(sc, e, wav) : M::splat(0.f);
             if (depth > 1 && !prev_delta) {
                 float3 dd = si.p - o; float dist = norm(dd); dd = dd / dist;
                 emitter_pdf = area_pdf_direction(e, dd, si.sh.n, dist);
             }
         } else if (e.type == 1) {
-            Le = env_eval(e, d);
+            Le = env_eval<M>(sc, e, d, wav);
             if (depth > 1 && !prev_delta) emitter_pdf = env_pdf_direction(e, d);
         } else {                                                  // constant background (constant.cpp:105-108)
-            Le = e.radiance;
+            Le = emitter_radiance<M>(sc, e, wav);
             if (depth > 1 && !prev_delta) emitter_pdf = 0.25f * kInvPi;
         }
         if (sc.n_emitters > 1) emitter_pdf *= 1.f / (float) sc.n_emitters;
         float w = depth > 1 ? mis_weight(prev_pdf, emitter_pdf) : 1.f;
-        float3 add = thr * Le * w;
+        float3 add = to_result(sc, thr * Le * w, wav, ray_weight);
         out.emitted = add;
         float4 r = b.result[path_id];
         r.x += add.x; r.y += add.y; r.z += add.z;
@@ -175,33 +191,33 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     if (bsdf_is_smooth(bsdf)) {
         float sx = rng.next_f32(), sy = rng.next_f32();
         if (sc.n_emitters > 0) {
-            DirSample ds = sample_emitter_direction(sc, si.p, sx, sy);
+            DirSampleT<M> ds = sample_emitter_direction<M>(sc, si.p, sx, sy, wav);
             if (ds.pdf != 0.f) {
                 float3 wo = si.sh.to_local(ds.d);
-                float3 bval; float bpdf;
-                bsdf_eval_pdf(sc, bsdf, si, wo, bval, bpdf);
+                Spec bval; float bpdf;
+                bsdf_eval_pdf<M>(sc, bsdf, si, wo, bval, bpdf, wav);
                 float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
-                float3 c = thr * bval * ds.value * mis;
-                if (c.x != 0.f || c.y != 0.f || c.z != 0.f) {
+                Spec c = thr * bval * ds.value * mis;
+                if (!is_black(c)) {
                     out.shadow = true;
                     out.s_o_mint = mk4(si.p, kRayEpsilon * (1.f + hmax(abs3(si.p))));
                     out.s_d_maxt = mk4(ds.d, ds.dist * (1.f - kShadowEpsilon));
-                    out.s_contrib_id = mk4(c, u2f(path_id));
+                    out.s_contrib_id = mk4(to_result(sc, c, wav, ray_weight), u2f(path_id));
                 }
             }
         }
     }
     // ---- BSDF sampling (path.cpp:177-190)
     float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
-    BsdfSample bs = bsdf_sample(sc, bsdf, si, s1, s2x, s2y);
+    BsdfSampleT<M> bs = bsdf_sample<M>(sc, bsdf, si, s1, s2x, s2y, wav);
     thr *= bs.weight;
-    if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) return out;
+    if (is_black(thr)) return out;
     eta *= bs.eta;
     float3 wo_w = si.sh.to_world(bs.wo);
     out.extend = true;
     out.o_mint = mk4(si.p, (1.f + hmax(abs3(si.p))) * kRayEpsilon);
     out.d_maxt = mk4(wo_w, INFINITY);
-    out.thr_eta = mk4(thr, eta);
+    store_throughput(out, thr, eta, we);
     out.misc = make_uint4(path_id, (depth + 1u) | (bs.delta ? 0x80000000u : 0u), f2u(bs.pdf), 0u);
     rng_store(&out.rng, rng);
     return out;
@@ -240,6 +256,10 @@ HD void film_put(const SensorDev &sn, float px, float py, float4 xyza, float wgt
 }
 
 // src/librender/integrator.cpp:254-270: rgb -> XYZ (core/spectrum.h:220-227), aovs = {X,Y,Z,alpha,1}
+template <typename M> HD float4 result_to_xyza(float4 r);
+HD float4 radiance_to_xyza(float4 r);
+template <> HD float4 result_to_xyza<Spectral>(float4 r) { return r; }
+template <> HD float4 result_to_xyza<Rgb>(float4 r) { return radiance_to_xyza(r); }
 HD float4 radiance_to_xyza(float4 r) {
     return make_float4(0.412453f * r.x + 0.357580f * r.y + 0.180423f * r.z,
                        0.212671f * r.x + 0.715160f * r.y + 0.072169f * r.z,

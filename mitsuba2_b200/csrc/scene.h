@@ -4,9 +4,14 @@
 
 namespace mtsb {
 
+// type 0: constant (rgb colour; spectral mode: sRGB-model coefficients, src/spectra/srgb.cpp), 1: bitmap (spectral mode,
+// 3 channels: coefficient texels, src/textures/bitmap.cpp:262-275), 2: `regular` tabulated spectrum (w samples over
+// [lambda_min, lambda_max]), 3: `irregular` (w nodes then w values in data), 4: `uniform` spectrum (value.x).
+// d65_scale != 0: the value is multiplied by the D65 whitepoint spectrum times d65_scale (src/spectra/srgb_d65.cpp).
 struct TexDev {
     int type; float3 value;
     uint32_t w, h, ch; const float *data; float to_uv[9];
+    float lambda_min, lambda_max, d65_scale;
 };
 struct BsdfDev {
     int type; int refl, eta, k, spec_r, spec_t;
@@ -18,9 +23,11 @@ struct EmitterDev {
     int type;               // 0 area, 1 envmap, 2 constant background, 3 point
     float3 position;        // point
     // area (radiance doubles as the constant emitter's radiance and the point light's intensity)
-    float3 radiance; int mesh; const float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
+    float3 radiance; int radiance_tex;   // spectral mode: radiance / intensity spectrum = texture radiance_tex
+    int mesh; const float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
     // envmap
-    uint32_t w, h; const float4 *rgba; float to_world[16], to_local[16]; float scale;
+    uint32_t w, h; const float4 *rgba;   // rgb + 1; spectral mode: sRGB-model coefficients + scale (envmap.cpp:98-110)
+    float to_world[16], to_local[16]; float scale;
     int n_levels; const float *level_data[kMaxEnvLevels]; uint32_t level_width[kMaxEnvLevels];
     float bsphere_radius;
 };
@@ -42,6 +49,7 @@ struct SceneDev {
     const MeshDev *meshes; const TexDev *tex; const BsdfDev *bsdfs; const EmitterDev *emitters;
     int n_emitters, env_emitter;
     int max_depth, rr_depth;
+    const float *cie;       // spectral mode: x-bar, y-bar, z-bar (3 x 95) then D65 / 10568 (95), 360..830 nm
 };
 
 } // namespace mtsb

@@ -1,6 +1,6 @@
 // shade.h -- surface interaction reconstruction, textures and the three in-scope BSDFs (HD bodies).
 #pragma once
-#include "scene.h"
+#include "spectrum.h"
 
 namespace mtsb {
 
@@ -54,9 +54,9 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
 }
 
 // src/textures/bitmap.cpp:250-293 (bilinear, repeat) and constant rgb (src/spectra/srgb.cpp)
-HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) {
+HD float3 tex_eval_rgb(const SceneDev &sc, int id, float u, float v) {
     const TexDev &t = sc.tex[id];
-    if (t.type == 0) return t.value;
+    if (t.type != 1) return t.value;
     float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
     tu -= floorf(tu); tv -= floorf(tv);
     tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
@@ -73,9 +73,44 @@ HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) {
     float3 v1 = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
     return mk3(fmaf(w0y, v0.x, w1y * v1.x), fmaf(w0y, v0.y, w1y * v1.y), fmaf(w0y, v0.z, w1y * v1.z));
 }
+// Spectral mode: the same textures hold sRGB-model coefficients (srgb.cpp:44-48; bitmap.cpp:262-275 evaluates the model at
+// the four texels and blends the spectra), or a tabulated / uniform spectrum; emitters multiply by D65 (srgb_d65.cpp:60-62).
+HD float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wav) {
+    const TexDev &t = sc.tex[id];
+    float4 r;
+    if (t.type == 0) r = srgb_model_eval(t.value, wav);
+    else if (t.type == 2) { float inv = (float) (t.w - 1) / (t.lambda_max - t.lambda_min);
+        r = map_spec(wav, [&](float l) { return regular_eval1(t.data, t.w, t.lambda_min, t.lambda_max, inv, l); }); }
+    else if (t.type == 3) r = map_spec(wav, [&](float l) { return irregular_eval1(t.data, t.data + t.w, t.w, l); });
+    else if (t.type == 4) r = mk4(t.value.x);
+    else {
+        float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
+        tu -= floorf(tu); tv -= floorf(tv);
+        tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
+        uint32_t px = min((uint32_t) tu, t.w - 2), py = min((uint32_t) tv, t.h - 2);
+        float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+        uint32_t idx = px + py * t.w;
+        auto blend = [&](float a, float b) { return fmaf(w0x, a, w1x * b); };
+        if (t.ch == 1) {
+            float v0 = blend(t.data[idx], t.data[idx + 1]), v1 = blend(t.data[idx + t.w], t.data[idx + t.w + 1]);
+            r = mk4(fmaf(w0y, v0, w1y * v1));
+        } else {
+            float4 c00 = srgb_model_eval(ld3(t.data, idx), wav), c10 = srgb_model_eval(ld3(t.data, idx + 1), wav),
+                   c01 = srgb_model_eval(ld3(t.data, idx + t.w), wav), c11 = srgb_model_eval(ld3(t.data, idx + t.w + 1), wav);
+            float4 c0 = map_spec(c00, c10, blend), c1 = map_spec(c01, c11, blend);
+            r = map_spec(c0, c1, [&](float a, float b) { return fmaf(w0y, a, w1y * b); });
+        }
+    }
+    if (t.d65_scale != 0.f) r = d65_eval(sc, wav) * t.d65_scale * r;
+    return r;
+}
+template <typename M> HD typename M::Spec tex_eval_m(const SceneDev &sc, int id, float u, float v, float4 wav);
+template <> HD float3 tex_eval_m<Rgb>(const SceneDev &sc, int id, float u, float v, float4) { return tex_eval_rgb(sc, id, u, v); }
+template <> HD float4 tex_eval_m<Spectral>(const SceneDev &sc, int id, float u, float v, float4 wav) { return tex_eval_spectral(sc, id, u, v, wav); }
+HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) { return tex_eval_rgb(sc, id, u, v); }
 // texel footprint of a bitmap lookup (for the adjoint scatter): indices of the 4 texels + weights
 HD bool tex_footprint(const TexDev &t, float u, float v, uint32_t idx[4], float w[4]) {
-    if (t.type == 0) return false;
+    if (t.type != 1) return false;
     float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
     tu -= floorf(tu); tv -= floorf(tv);
     tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
@@ -104,7 +139,8 @@ HD float3 square_to_cosine_hemisphere(float sx, float sy) {
     return mk3(px, py, safe_sqrt(1.f - (px * px + py * py)));
 }
 
-struct BsdfSample { float3 wo; float pdf, eta; bool delta; float3 weight; };
+template <typename M> struct BsdfSampleT { float3 wo; float pdf, eta; bool delta; typename M::Spec weight; };
+typedef BsdfSampleT<Rgb> BsdfSample;
 
 // ---- fresnel (include/mitsuba/render/fresnel.h:34-76, 92-116) ------------------------------------
 HD void fresnel_dielectric(float cos_i, float eta, float &r, float &cos_t, float &eta_it, float &eta_ti) {
@@ -132,6 +168,9 @@ HD float fresnel_conductor(float cos_i, float eta_r, float eta_i) {
     float r_p = r_s * (term_3 - term_4) / (term_3 + term_4);
     return 0.5f * (r_s + r_p);
 }
+
+HD float3 fresnel_conductor(float c, float3 eta, float3 k) { return mk3(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z)); }
+HD float4 fresnel_conductor(float c, float4 eta, float4 k) { return make_float4(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z), fresnel_conductor(c, eta.w, k.w)); }
 
 // ---- microfacet (include/mitsuba/render/microfacet.h:184-413) ------------------------------------
 HD float erfinv_giles(float x) {   // ext/enoki/include/enoki/special.h:222-247
@@ -238,14 +277,16 @@ struct Microfacet {
 };
 
 // ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
-HD BsdfSample bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
-    BsdfSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = mk3(0.f);
+template <typename M>
+HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav) {
+    typedef typename M::Spec Spec;
+    BsdfSampleT<M> bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = M::splat(0.f);
     float cos_i = si.wi.z;
     if (b.type == 0) {            // src/bsdfs/diffuse.cpp:78-103
         if (!(cos_i > 0.f)) return bs;
         bs.wo = square_to_cosine_hemisphere(sx, sy);
         bs.pdf = kInvPi * bs.wo.z;
-        if (bs.pdf > 0.f) bs.weight = tex_eval(sc, b.refl, si.u, si.v);
+        if (bs.pdf > 0.f) bs.weight = tex_eval_m<M>(sc, b.refl, si.u, si.v, wav);
         return bs;
     }
     if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:196-276
@@ -257,11 +298,10 @@ HD BsdfSample bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const 
         float weight = b.sample_visible ? distr.smith_g1(bs.wo, m)
                                         : distr.G(si.wi, bs.wo, m) * dot(si.wi, m) / (cos_i * m.z);
         bs.pdf /= 4.f * dot(bs.wo, m);
-        float3 eta = tex_eval(sc, b.eta, si.u, si.v), k = tex_eval(sc, b.k, si.u, si.v);
-        float c = dot(si.wi, m);
-        float3 F = mk3(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z));
-        if (b.spec_r >= 0) F *= tex_eval(sc, b.spec_r, si.u, si.v);
-        bs.weight = active ? F * weight : mk3(0.f);
+        Spec eta = tex_eval_m<M>(sc, b.eta, si.u, si.v, wav), k = tex_eval_m<M>(sc, b.k, si.u, si.v, wav);
+        Spec F = fresnel_conductor(dot(si.wi, m), eta, k);
+        if (b.spec_r >= 0) F *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav);
+        bs.weight = active ? F * weight : M::splat(0.f);
         return bs;
     }
     // src/bsdfs/dielectric.cpp:201-316
@@ -273,18 +313,20 @@ HD BsdfSample bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const 
     bs.delta = true;
     bs.wo = sel_r ? mk3(-si.wi.x, -si.wi.y, si.wi.z) : mk3(-eta_ti * si.wi.x, -eta_ti * si.wi.y, cos_t);
     bs.eta = sel_r ? 1.f : eta_it;
-    float3 w = mk3(1.f);
-    if (sel_r) { if (b.spec_r >= 0) w *= tex_eval(sc, b.spec_r, si.u, si.v); }
-    else { if (b.spec_t >= 0) w *= tex_eval(sc, b.spec_t, si.u, si.v); w *= sqr(eta_ti); }
+    Spec w = M::splat(1.f);
+    if (sel_r) { if (b.spec_r >= 0) w *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav); }
+    else { if (b.spec_t >= 0) w *= tex_eval_m<M>(sc, b.spec_t, si.u, si.v, wav); w *= sqr(eta_ti); }
     bs.weight = w;
     return bs;
 }
 
-HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
-    val = mk3(0.f); pdf = 0.f;
+template <typename M>
+HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav) {
+    typedef typename M::Spec Spec;
+    val = M::splat(0.f); pdf = 0.f;
     float ci = si.wi.z, co = wo.z;
     if (b.type == 0) {            // src/bsdfs/diffuse.cpp:105-135
-        if (ci > 0.f && co > 0.f) { val = tex_eval(sc, b.refl, si.u, si.v) * kInvPi * co; pdf = kInvPi * co; }
+        if (ci > 0.f && co > 0.f) { val = tex_eval_m<M>(sc, b.refl, si.u, si.v, wav) * kInvPi * co; pdf = kInvPi * co; }
         return;
     }
     if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:278-394
@@ -295,10 +337,9 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
         if (D != 0.f) {
             float G = distr.G(si.wi, wo, H);
             float res = D * G / (4.f * ci);
-            float3 eta = tex_eval(sc, b.eta, si.u, si.v), k = tex_eval(sc, b.k, si.u, si.v);
-            float c = dot(si.wi, H);
-            float3 F = mk3(fresnel_conductor(c, eta.x, k.x), fresnel_conductor(c, eta.y, k.y), fresnel_conductor(c, eta.z, k.z));
-            if (b.spec_r >= 0) F *= tex_eval(sc, b.spec_r, si.u, si.v);
+            Spec eta = tex_eval_m<M>(sc, b.eta, si.u, si.v, wav), k = tex_eval_m<M>(sc, b.k, si.u, si.v, wav);
+            Spec F = fresnel_conductor(dot(si.wi, H), eta, k);
+            if (b.spec_r >= 0) F *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav);
             val = F * res;
         }
         if (dot(si.wi, H) > 0.f && dot(wo, H) > 0.f)
@@ -309,19 +350,21 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
 
 // `twosided` (src/bsdfs/twosided.cpp:98-200): on the back side mirror wi (and wo) about the surface and use the
 // nested BRDF; cos(wi) == 0 belongs to neither side.  One call site each, so the nested code is not duplicated.
-HD BsdfSample bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy) {
+template <typename M = Rgb>
+HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav = float4()) {
     bool back = b.two_sided && si.wi.z < 0.f;
     SI s2 = si;
     if (back) s2.wi.z = -s2.wi.z;
-    BsdfSample bs = bsdf_sample_one_sided(sc, b, s2, s1, sx, sy);
+    BsdfSampleT<M> bs = bsdf_sample_one_sided<M>(sc, b, s2, s1, sx, sy, wav);
     if (back) bs.wo.z = -bs.wo.z;
     return bs;
 }
-HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, float3 &val, float &pdf) {
+template <typename M = Rgb>
+HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
     bool back = b.two_sided && si.wi.z < 0.f;
     SI s2 = si;
     if (back) { s2.wi.z = -s2.wi.z; wo.z = -wo.z; }
-    bsdf_eval_pdf_one_sided(sc, b, s2, wo, val, pdf);
+    bsdf_eval_pdf_one_sided<M>(sc, b, s2, wo, val, pdf, wav);
 }
 HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
 

@@ -5,6 +5,7 @@
 #include <string.h>
 #include <stdio.h>
 #include <float.h>
+#include "../mitsuba2_b200/csrc/cie_tables.h"   /* published CIE 1931 / D65 data tables (data only) */
 
 typedef struct { float x, y, z; } v3;
 static inline v3 V(float x, float y, float z) { v3 r = { x, y, z }; return r; }
@@ -28,6 +29,16 @@ static inline uint32_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u;
 static inline float bitsf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 static inline float mulsign(float a, float b) { return bitsf(fbits(a) ^ (fbits(b) & 0x80000000u)); }
 static inline float mulsign_neg(float a, float b) { return bitsf(fbits(a) ^ ((~fbits(b)) & 0x80000000u)); }
+/* Spectrum: Color<float,3> in rgb mode, 4 wavelengths in spectral mode (include/mitsuba/core/spectrum.h); the 4th
+ * channel is carried along unused in rgb mode, reductions take the channel count */
+typedef struct { float c[4]; } col;
+static inline col C1(float v) { col r = { { v, v, v, v } }; return r; }
+static inline col C3(v3 a) { col r = { { a.x, a.y, a.z, 0.f } }; return r; }
+static inline col cmul(col a, col b) { col r; for (int i = 0; i < 4; ++i) r.c[i] = a.c[i] * b.c[i]; return r; }
+static inline col cadd(col a, col b) { col r; for (int i = 0; i < 4; ++i) r.c[i] = a.c[i] + b.c[i]; return r; }
+static inline col cscale(col a, float s) { col r; for (int i = 0; i < 4; ++i) r.c[i] = a.c[i] * s; return r; }
+static inline float chmax(col a, int n) { float m = a.c[0]; for (int i = 1; i < n; ++i) m = fmaxf(m, a.c[i]); return m; }
+static inline int cblack(col a, int n) { for (int i = 0; i < n; ++i) if (a.c[i] != 0.f) return 0; return 1; }
 
 /* include/mitsuba/core/math.h:36-38 */
 #define EPS_F (FLT_EPSILON / 2.f)
@@ -277,16 +288,17 @@ typedef struct { uint32_t face_begin, face_count, vert_begin, vert_count; int bs
 typedef struct { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf [left, left+count) in order[] ; else children left,left+1 */ } onode;
 typedef struct { int n_levels; float **levels; uint32_t *widths; } oh2d;
 typedef struct {
-    int type; v3 radiance, position; int mesh; float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
+    int type; v3 radiance, position; int radiance_tex; int mesh; float *cdf; float cdf_sum, normalization; uint32_t valid_lo, valid_hi;
     uint32_t w, h; float *rgba; float to_world[16], to_local[16]; float scale; oh2d warp; float bsphere_radius;
 } oemitter;
-typedef struct { int type; v3 value; uint32_t w, h, ch; float *data; float to_uv[9]; } otex;
+typedef struct { int type; v3 value; uint32_t w, h, ch; float *data; float to_uv[9]; float lambda_min, lambda_max, d65_scale; } otex;
 struct orc_scene {
     uint32_t n_meshes, n_bsdfs, n_tex, n_emitters, n_sensors, n_faces, n_verts;
     omesh *meshes; mtsb_bsdf_desc *bsdfs; otex *tex; oemitter *emitters; mtsb_sensor_desc *sensors;
     float *pos, *nrm, *uv; uint32_t *faces /* 3 per face, global vertex ids */; uint32_t *face_mesh;
     onode *nodes; uint32_t n_nodes; uint32_t *order;
     int env_emitter; int max_depth, rr_depth;
+    int spectral, nch;        /* MTSB_MODE_SPECTRAL: 4 wavelengths per path */
     v3 bbox_lo, bbox_hi;
 };
 
@@ -485,10 +497,14 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
     }
     s->bsdfs = calloc(d->n_bsdfs ? d->n_bsdfs : 1, sizeof(mtsb_bsdf_desc)); memcpy(s->bsdfs, d->bsdfs, sizeof(mtsb_bsdf_desc) * d->n_bsdfs);
     s->sensors = calloc(d->n_sensors ? d->n_sensors : 1, sizeof(mtsb_sensor_desc)); memcpy(s->sensors, d->sensors, sizeof(mtsb_sensor_desc) * d->n_sensors);
+    s->spectral = d->mode == MTSB_MODE_SPECTRAL; s->nch = s->spectral ? 4 : 3;
     s->tex = calloc(d->n_textures ? d->n_textures : 1, sizeof(otex));
     for (uint32_t i = 0; i < d->n_textures; ++i) {
         const mtsb_texture_desc *t = &d->textures[i]; otex *ot = &s->tex[i];
         ot->type = t->type; ot->value = V(t->value[0], t->value[1], t->value[2]);
+        ot->lambda_min = t->lambda_min; ot->lambda_max = t->lambda_max; ot->d65_scale = t->d65_scale; ot->w = t->width;
+        if (t->type == MTSB_TEX_REGULAR || t->type == MTSB_TEX_IRREGULAR) { size_t n = (size_t) t->width * (t->type == MTSB_TEX_IRREGULAR ? 2 : 1);
+            ot->data = malloc(sizeof(float) * n); memcpy(ot->data, t->data, sizeof(float) * n); }
         if (t->type == MTSB_TEX_BITMAP) { ot->w = t->width; ot->h = t->height; ot->ch = t->channels; memcpy(ot->to_uv, t->to_uv, sizeof(ot->to_uv));
             size_t n = (size_t) t->width * t->height * t->channels; ot->data = malloc(sizeof(float) * n); memcpy(ot->data, t->data, sizeof(float) * n); }
     }
@@ -496,7 +512,7 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
     s->emitters = calloc(d->n_emitters ? d->n_emitters : 1, sizeof(oemitter)); s->env_emitter = -1;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
         const mtsb_emitter_desc *e = &d->emitters[i]; oemitter *oe = &s->emitters[i];
-        oe->type = e->type;
+        oe->type = e->type; oe->radiance_tex = e->radiance_tex;
         if (e->type == MTSB_EMITTER_AREA) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = e->mesh_id; build_area_cdf(s, oe); }
         else if (e->type == MTSB_EMITTER_CONSTANT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1; s->env_emitter = (int) i; }  /* constant.cpp:33-49 */
         else if (e->type == MTSB_EMITTER_POINT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1;
@@ -504,7 +520,7 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
         else {
             s->env_emitter = (int) i; oe->w = e->width; oe->h = e->height; oe->scale = e->scale;
             memcpy(oe->to_world, e->to_world, sizeof(oe->to_world)); invert4(e->to_world, oe->to_local);
-            size_t n = (size_t) e->width * e->height; oe->rgba = malloc(sizeof(float) * 4 * n); memcpy(oe->rgba, e->rgba, sizeof(float) * 4 * n);
+            size_t n = (size_t) e->width * e->height; oe->rgba = malloc(sizeof(float) * 4 * n); memcpy(oe->rgba, s->spectral ? e->coeff_scale : e->rgba, sizeof(float) * 4 * n);
             float *lum = malloc(sizeof(float) * n);
             for (uint32_t y = 0; y < e->height; ++y) {     /* envmap.cpp:87-111 */
                 float sin_theta = sinf((float) y / (float) (e->height - 1) * PI_F);
@@ -570,31 +586,124 @@ static void make_si(const orc_scene *s, v3 o, v3 d, const ohit *h, osi *si) {
     si->wi = to_local(si, vneg(d));
 }
 /* src/textures/bitmap.cpp:250-293, src/spectra/srgb.cpp */
-static v3 tex_eval(const orc_scene *s, int id, float u, float v) {
-    const otex *t = &s->tex[id];
-    if (t->type == MTSB_TEX_CONSTANT) return t->value;
-    float tu = t->to_uv[0] * u + t->to_uv[1] * v + t->to_uv[2], tv = t->to_uv[3] * u + t->to_uv[4] * v + t->to_uv[5];
-    tu -= floorf(tu); tv -= floorf(tv);
-    tu *= (float) (t->w - 1); tv *= (float) (t->h - 1);
-    uint32_t px = (uint32_t) tu, py = (uint32_t) tv; if (px > t->w - 2) px = t->w - 2; if (py > t->h - 2) py = t->h - 2;
-    float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
-    size_t idx = px + (size_t) py * t->w; float out[3];
-    for (uint32_t c = 0; c < 3; ++c) {
-        uint32_t cc = t->ch == 1 ? 0 : c;
-        float v00 = t->data[idx * t->ch + cc], v10 = t->data[(idx + 1) * t->ch + cc], v01 = t->data[(idx + t->w) * t->ch + cc], v11 = t->data[(idx + t->w + 1) * t->ch + cc];
-        float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
-        out[c] = fmaf(w0y, v0, w1y * v1);
+/* ---- spectral mode arithmetic -------------------------------------------------------------------------------- */
+/* sample_wavelength (core/spectrum.h:304-316) = sample_rgb_spectrum (:270-285) of math::sample_shifted (core/math.h:418-442) */
+static void sample_wavelengths(float u, float *wav, float *weight) {
+    for (int i = 0; i < 4; ++i) {
+        float v = u + (float) i / 4.f; if (v > 1.f) v -= 1.f;
+        wav[i] = 538.f - atanhf(0.8569106254698279f - 1.8275019724092267f * v) * 138.88888888888889f;
+        float t = coshf(0.0072f * (wav[i] - 538.f));
+        weight[i] = 253.82f * t * t;
     }
-    return V(out[0], out[1], out[2]);
 }
-typedef struct { v3 wo, weight; float pdf, eta; int delta; } obs;
-static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy) {
+void orc_sample_wavelength(float u, float *wav4, float *weight4) { sample_wavelengths(u, wav4, weight4); }
+/* srgb_model_eval, include/mitsuba/render/srgb.h:8-24 */
+static float srgb_model_eval(const float *c, float l) {
+    float v = fmaf(fmaf(c[0], l, c[1]), l, c[2]);
+    if (isinf(c[2])) return fmaf(copysignf(1.f, c[2]), .5f, .5f);
+    return fmaxf(0.f, fmaf(.5f * v, 1.f / sqrtf(fmaf(v, v, 1.f)), .5f));
+}
+float orc_srgb_model_eval(const float *coeff3, float lambda) { return srgb_model_eval(coeff3, lambda); }
+/* ContinuousDistribution::eval_pdf, core/distr_1d.h:378-393 (`regular` spectrum, src/spectra/regular.cpp:77-84) */
+static float regular_eval(const float *values, uint32_t n, float lo, float hi, float x) {
+    if (!(x >= lo && x <= hi)) return 0.f;
+    float inv_interval = (float) (n - 1) / (hi - lo);       /* m_inv_interval_size, distr_1d.h:316-318 */
+    x = (x - lo) * inv_interval;
+    int32_t idx = (int32_t) x; if (idx < 0) idx = 0; if (idx > (int32_t) n - 2) idx = (int32_t) n - 2;
+    float w1 = x - (float) idx, w0 = 1.f - w1;
+    return fmaf(w0, values[idx], w1 * values[idx + 1]);
+}
+float orc_regular_eval(const float *values, uint32_t n, float lo, float hi, float x) { return regular_eval(values, n, lo, hi, x); }
+/* IrregularContinuousDistribution::eval_pdf, core/distr_1d.h:655-677 (`irregular` spectrum) */
+static float irregular_eval(const float *nodes, const float *values, uint32_t n, float x) {
+    if (!(x >= nodes[0] && x <= nodes[n - 1])) return 0.f;
+    uint32_t start = 0, end = n, iterations = 0; { uint32_t v = n; while (v) { ++iterations; v >>= 1; } }   /* log2i(n) + 1 */
+    for (uint32_t i = 0; i < iterations; ++i) {             /* enoki::binary_search, array_utils.h:153-171 */
+        uint32_t middle = (start + end) >> 1;
+        int pred = middle < n && nodes[middle] < x;
+        if (pred) start = middle + 1 < end ? middle + 1 : end; else end = middle;
+    }
+    uint32_t idx = start < n - 1 ? start : n - 1; if (idx < 1) idx = 1; idx -= 1;
+    float x0 = nodes[idx], x1 = nodes[idx + 1], y0 = values[idx], y1 = values[idx + 1];
+    x = (x - x0) / (x1 - x0);
+    return fmaf(x, y1 - y0, y0);
+}
+float orc_irregular_eval(const float *nodes, const float *values, uint32_t n, float x) { return irregular_eval(nodes, values, n, x); }
+/* D65 whitepoint: `d65` expands to `regular` over data * scale / 10568 (src/spectra/d65.cpp:56-73) */
+static float d65_eval(float l) {
+    static float tbl[95]; static int init = 0;
+    if (!init) {
+        #pragma omp critical
+        { for (int i = 0; i < 95; ++i) tbl[i] = kCieD65[i] * (1.f / 10568.f); init = 1; }
+    }
+    return regular_eval(tbl, 95, 360.f, 830.f, l);
+}
+float orc_d65_eval(float lambda) { return d65_eval(lambda); }
+/* cie1931_xyz, core/spectrum.h:147-176 */
+static v3 cie1931_xyz(float l) {
+    float t = (l - 360.f) * (94.f / (830.f - 360.f));
+    if (!(l >= 360.f && l <= 830.f)) return V(0, 0, 0);
+    int32_t i0 = (int32_t) t; if (i0 < 0) i0 = 0; if (i0 > 93) i0 = 93;
+    float w1 = t - (float) i0, w0 = 1.f - w1;
+    return V(fmaf(w0, kCie1931[i0], w1 * kCie1931[i0 + 1]), fmaf(w0, kCie1931[95 + i0], w1 * kCie1931[95 + i0 + 1]),
+             fmaf(w0, kCie1931[190 + i0], w1 * kCie1931[190 + i0 + 1]));
+}
+/* spectrum_to_xyz, core/spectrum.h:209-217: hmean over the 4 wavelengths (pairwise horizontal sum) */
+static v3 spectrum_to_xyz(const float *value, const float *wav) {
+    v3 m[4]; for (int i = 0; i < 4; ++i) m[i] = cie1931_xyz(wav[i]);
+    return V(((m[0].x * value[0] + m[1].x * value[1]) + (m[2].x * value[2] + m[3].x * value[3])) * .25f,
+             ((m[0].y * value[0] + m[1].y * value[1]) + (m[2].y * value[2] + m[3].y * value[3])) * .25f,
+             ((m[0].z * value[0] + m[1].z * value[1]) + (m[2].z * value[2] + m[3].z * value[3])) * .25f);
+}
+void orc_spectrum_to_xyz(const float *value4, const float *wav4, float *xyz) { v3 r = spectrum_to_xyz(value4, wav4); xyz[0] = r.x; xyz[1] = r.y; xyz[2] = r.z; }
+
+/* Texture::eval.  rgb mode: src/spectra/srgb.cpp:44-50 (constant), src/textures/bitmap.cpp:250-293.  Spectral mode (wav != NULL):
+ * constants and 3-channel texels are sRGB-model coefficients (srgb.cpp:44-48, bitmap.cpp:262-275), tabulated spectra
+ * (regular.cpp, irregular.cpp), uniform.cpp; srgb_d65.cpp:60-62 multiplies by the D65 spectrum. */
+static col tex_eval(const orc_scene *s, int id, float u, float v, const float *wav) {
+    const otex *t = &s->tex[id]; col r = C1(0.f);
+    if (t->type != MTSB_TEX_BITMAP) {
+        if (!s->spectral) return C3(t->value);
+        float cf[3] = { t->value.x, t->value.y, t->value.z };
+        for (int i = 0; i < 4; ++i)
+            r.c[i] = t->type == MTSB_TEX_CONSTANT ? srgb_model_eval(cf, wav[i])
+                   : t->type == MTSB_TEX_REGULAR ? regular_eval(t->data, t->w, t->lambda_min, t->lambda_max, wav[i])
+                   : t->type == MTSB_TEX_IRREGULAR ? irregular_eval(t->data, t->data + t->w, t->w, wav[i]) : t->value.x;
+    } else {
+        float tu = t->to_uv[0] * u + t->to_uv[1] * v + t->to_uv[2], tv = t->to_uv[3] * u + t->to_uv[4] * v + t->to_uv[5];
+        tu -= floorf(tu); tv -= floorf(tv);
+        tu *= (float) (t->w - 1); tv *= (float) (t->h - 1);
+        uint32_t px = (uint32_t) tu, py = (uint32_t) tv; if (px > t->w - 2) px = t->w - 2; if (py > t->h - 2) py = t->h - 2;
+        float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+        size_t idx = px + (size_t) py * t->w;
+        if (s->spectral && t->ch == 3) {
+            const float *c00 = t->data + 3 * idx, *c10 = c00 + 3, *c01 = c00 + 3 * (size_t) t->w, *c11 = c01 + 3;
+            for (int i = 0; i < 4; ++i) {
+                float v0 = fmaf(w0x, srgb_model_eval(c00, wav[i]), w1x * srgb_model_eval(c10, wav[i])),
+                      v1 = fmaf(w0x, srgb_model_eval(c01, wav[i]), w1x * srgb_model_eval(c11, wav[i]));
+                r.c[i] = fmaf(w0y, v0, w1y * v1);
+            }
+        } else {
+            for (uint32_t c = 0; c < (uint32_t) s->nch; ++c) {
+                uint32_t cc = t->ch == 1 ? 0 : c;
+                float v00 = t->data[idx * t->ch + cc], v10 = t->data[(idx + 1) * t->ch + cc], v01 = t->data[(idx + t->w) * t->ch + cc], v11 = t->data[(idx + t->w + 1) * t->ch + cc];
+                float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
+                r.c[c] = fmaf(w0y, v0, w1y * v1);
+            }
+        }
+    }
+    if (s->spectral && t->d65_scale != 0.f) for (int i = 0; i < 4; ++i) r.c[i] = d65_eval(wav[i]) * t->d65_scale * r.c[i];
+    return r;
+}
+typedef struct { v3 wo; col weight; float pdf, eta; int delta; } obs;
+static col fresnel_conductor_col(float c, col eta, col k) { col r; for (int i = 0; i < 4; ++i) r.c[i] = orc_fresnel_conductor(c, eta.c[i], k.c[i]); return r; }
+static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
     float cos_theta_i = si->wi.z;
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:78-103 */
         if (!(cos_theta_i > 0.f)) return bs;
         bs.wo = cosine_hemisphere(sx, sy); bs.pdf = INV_PI_F * bs.wo.z;
-        if (bs.pdf > 0.f) bs.weight = tex_eval(s, b->reflectance_tex, si->u, si->v);
+        if (bs.pdf > 0.f) bs.weight = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
         return bs;
     }
     if (b->type == MTSB_BSDF_ROUGHCONDUCTOR) {         /* roughconductor.cpp:196-276 */
@@ -606,11 +715,10 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         float weight = b->sample_visible ? mf_g1(&distr, bs.wo, m)
                                          : mf_g1(&distr, si->wi, m) * mf_g1(&distr, bs.wo, m) * vdot(si->wi, m) / (cos_theta_i * m.z);
         bs.pdf /= 4.f * vdot(bs.wo, m);
-        v3 eta = tex_eval(s, b->eta_tex, si->u, si->v), k = tex_eval(s, b->k_tex, si->u, si->v);
-        float c = vdot(si->wi, m);
-        v3 F = V(orc_fresnel_conductor(c, eta.x, k.x), orc_fresnel_conductor(c, eta.y, k.y), orc_fresnel_conductor(c, eta.z, k.z));
-        if (b->specular_reflectance_tex >= 0) F = vmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v));
-        bs.weight = active ? vscale(F, weight) : V(0, 0, 0);
+        col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+        col F = fresnel_conductor_col(vdot(si->wi, m), eta, k);
+        if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+        bs.weight = active ? cscale(F, weight) : C1(0.f);
         return bs;
     }
     /* dielectric.cpp:201-316 */
@@ -619,16 +727,16 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
     bs.pdf = selected_r ? r_i : t_i; bs.delta = 1;
     bs.wo = selected_r ? V(-si->wi.x, -si->wi.y, si->wi.z) : V(-eta_ti * si->wi.x, -eta_ti * si->wi.y, cos_theta_t);
     bs.eta = selected_r ? 1.f : eta_it;
-    v3 w = V(1, 1, 1);
-    if (selected_r) { if (b->specular_reflectance_tex >= 0) w = vmul(w, tex_eval(s, b->specular_reflectance_tex, si->u, si->v)); }
-    else { if (b->specular_transmittance_tex >= 0) w = vmul(w, tex_eval(s, b->specular_transmittance_tex, si->u, si->v)); w = vscale(w, sqrf(eta_ti)); }
+    col w = C1(1.f);
+    if (selected_r) { if (b->specular_reflectance_tex >= 0) w = cmul(w, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav)); }
+    else { if (b->specular_transmittance_tex >= 0) w = cmul(w, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav)); w = cscale(w, sqrf(eta_ti)); }
     bs.weight = w; return bs;
 }
-static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, v3 *val, float *pdf) {
-    *val = V(0, 0, 0); *pdf = 0.f;
+static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav) {
+    *val = C1(0.f); *pdf = 0.f;
     float cos_theta_i = si->wi.z, cos_theta_o = wo.z;
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:105-135 */
-        if (cos_theta_i > 0.f && cos_theta_o > 0.f) { *val = vscale(tex_eval(s, b->reflectance_tex, si->u, si->v), INV_PI_F * cos_theta_o); *pdf = INV_PI_F * cos_theta_o; }
+        if (cos_theta_i > 0.f && cos_theta_o > 0.f) { *val = cscale(cscale(tex_eval(s, b->reflectance_tex, si->u, si->v, wav), INV_PI_F), cos_theta_o); *pdf = INV_PI_F * cos_theta_o; }
         return;
     }
     if (b->type == MTSB_BSDF_ROUGHCONDUCTOR) {         /* roughconductor.cpp:278-394 */
@@ -638,11 +746,10 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         float D = mf_eval(&distr, H);
         if (D != 0.f) {
             float G = mf_g1(&distr, si->wi, H) * mf_g1(&distr, wo, H), result = D * G / (4.f * cos_theta_i);
-            v3 eta = tex_eval(s, b->eta_tex, si->u, si->v), k = tex_eval(s, b->k_tex, si->u, si->v);
-            float c = vdot(si->wi, H);
-            v3 F = V(orc_fresnel_conductor(c, eta.x, k.x), orc_fresnel_conductor(c, eta.y, k.y), orc_fresnel_conductor(c, eta.z, k.z));
-            if (b->specular_reflectance_tex >= 0) F = vmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v));
-            *val = vscale(F, result);
+            col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+            col F = fresnel_conductor_col(vdot(si->wi, H), eta, k);
+            if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            *val = cscale(F, result);
         }
         if (vdot(si->wi, H) > 0.f && vdot(wo, H) > 0.f)
             *pdf = b->sample_visible ? D * mf_g1(&distr, si->wi, H) / (4.f * cos_theta_i) : mf_pdf(&distr, si->wi, H) / (4.f * vdot(wo, H));
@@ -650,42 +757,55 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
 }
 /* TwoSidedBRDF::sample / eval / pdf (twosided.cpp:98-200) with the same nested BRDF on both sides: on the back side flip
  * wi (and wo) about the surface; cos(wi) == 0 is neither front nor back */
-static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy) {
-    if (!b->two_sided || si->wi.z > 0.f) return bsdf_sample_nested(s, b, si, s1, sx, sy);
+static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
+    if (!b->two_sided || si->wi.z > 0.f) return bsdf_sample_nested(s, b, si, s1, sx, sy, wav);
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
     if (!(si->wi.z < 0.f)) return bs;
     osi flipped = *si; flipped.wi.z *= -1.f;
-    bs = bsdf_sample_nested(s, b, &flipped, s1, sx, sy);
+    bs = bsdf_sample_nested(s, b, &flipped, s1, sx, sy, wav);
     bs.wo.z *= -1.f;
     return bs;
 }
-static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, v3 *val, float *pdf) {
-    if (!b->two_sided || si->wi.z > 0.f) { bsdf_eval_pdf_nested(s, b, si, wo, val, pdf); return; }
-    *val = V(0, 0, 0); *pdf = 0.f;
+static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav) {
+    if (!b->two_sided || si->wi.z > 0.f) { bsdf_eval_pdf_nested(s, b, si, wo, val, pdf, wav); return; }
+    *val = C1(0.f); *pdf = 0.f;
     if (!(si->wi.z < 0.f)) return;
     osi flipped = *si; flipped.wi.z *= -1.f; wo.z *= -1.f;
-    bsdf_eval_pdf_nested(s, b, &flipped, wo, val, pdf);
+    bsdf_eval_pdf_nested(s, b, &flipped, wo, val, pdf, wav);
 }
 /* ---- emitters ---- */
 static v3 xf_vec(const float *m, v3 v) { return V(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z, m[8] * v.x + m[9] * v.y + m[10] * v.z); }
-static v3 env_lookup(const oemitter *e, float u, float v) {     /* envmap.cpp:267-317 */
+static col env_lookup(const orc_scene *s, const oemitter *e, float u, float v, const float *wav) {     /* envmap.cpp:267-317 */
     u *= (float) (e->w - 1); v *= (float) (e->h - 1);
     uint32_t px = (uint32_t) u, py = (uint32_t) v; if (px > e->w - 2) px = e->w - 2; if (py > e->h - 2) py = e->h - 2;
     float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
-    size_t idx = px + (size_t) py * e->w; float out[3];
-    for (int c = 0; c < 3; ++c) {
-        float v00 = e->rgba[4 * idx + c], v10 = e->rgba[4 * (idx + 1) + c], v01 = e->rgba[4 * (idx + e->w) + c], v11 = e->rgba[4 * (idx + e->w + 1) + c];
-        float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
-        out[c] = fmaf(w0y, v0, w1y * v1) * e->scale;
+    size_t idx = px + (size_t) py * e->w; col out = C1(0.f);
+    const float *t00 = e->rgba + 4 * idx, *t10 = t00 + 4, *t01 = t00 + 4 * (size_t) e->w, *t11 = t01 + 4;
+    if (s->spectral) {       /* texels = model coefficients + scale; result = s * wp * f * m_scale (envmap.cpp:285-306) */
+        float f = fmaf(w0y, fmaf(w0x, t00[3], w1x * t10[3]), w1y * fmaf(w0x, t01[3], w1x * t11[3]));
+        for (int i = 0; i < 4; ++i) {
+            float s0 = fmaf(w0x, srgb_model_eval(t00, wav[i]), w1x * srgb_model_eval(t10, wav[i])),
+                  s1 = fmaf(w0x, srgb_model_eval(t01, wav[i]), w1x * srgb_model_eval(t11, wav[i]));
+            out.c[i] = fmaf(w0y, s0, w1y * s1) * d65_eval(wav[i]) * f * e->scale;
+        }
+        return out;
     }
-    return V(out[0], out[1], out[2]);
+    for (int c = 0; c < 3; ++c) {
+        float v0 = fmaf(w0x, t00[c], w1x * t10[c]), v1 = fmaf(w0x, t01[c], w1x * t11[c]);
+        out.c[c] = fmaf(w0y, v0, w1y * v1) * e->scale;
+    }
+    return out;
+}
+/* radiance of area / constant emitters, intensity of point lights: rgb triple, or (spectral) a spectrum texture */
+static col emitter_radiance(const orc_scene *s, const oemitter *e, const float *wav) {
+    return s->spectral ? tex_eval(s, e->radiance_tex, 0.f, 0.f, wav) : C3(e->radiance);
 }
 static void env_uv(const oemitter *e, v3 dw, float *u, float *v, v3 *dl) {   /* envmap.cpp:132-145 */
     *dl = xf_vec(e->to_local, dw);
     *u = atan2f(dl->x, -dl->z) * INV_TWOPI_F; *v = safe_acosf(dl->y) * INV_PI_F;
     *u -= floorf(*u); *v -= floorf(*v);
 }
-static v3 env_eval(const oemitter *e, v3 dw) { float u, v; v3 dl; env_uv(e, dw, &u, &v, &dl); return env_lookup(e, u, v); }
+static col env_eval(const orc_scene *s, const oemitter *e, v3 dw, const float *wav) { float u, v; v3 dl; env_uv(e, dw, &u, &v, &dl); return env_lookup(s, e, u, v, wav); }
 static float h2d_eval(const oemitter *e, float u, float v) {      /* distr_2d.h:495-530 */
     u = fminf(fmaxf(u, 0.f), 1.f) * (float) (e->w - 1); v = fminf(fmaxf(v, 0.f), 1.f) * (float) (e->h - 1);
     uint32_t ox = (uint32_t) (int) u, oy = (uint32_t) (int) v; if (ox > e->w - 2) ox = e->w - 2; if (oy > e->h - 2) oy = e->h - 2;
@@ -725,8 +845,8 @@ static float env_pdf_direction(const oemitter *e, v3 dw) {        /* envmap.cpp:
     float inv_sin_theta = 1.f / sqrtf(fmaxf(sqrf(d.x) + sqrf(d.z), sqrf(EPS_F)));
     return h2d_eval(e, u, v) * inv_sin_theta * (1.f / (2.f * sqrf(PI_F)));
 }
-typedef struct { v3 p, n, d, value; float dist, pdf; int delta; } ods;
-static ods env_sample_direction(const oemitter *e, v3 ref_p, float sx, float sy) {   /* envmap.cpp:154-187 */
+typedef struct { v3 p, n, d; col value; float dist, pdf; int delta; } ods;
+static ods env_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy, const float *wav) {   /* envmap.cpp:154-187 */
     ods ds; float u, v, pdf; h2d_sample(e, sx, sy, &u, &v, &pdf);
     float theta = v * PI_F, phi = u * (2.f * PI_F);
     v3 d = V(cosf(phi) * sinf(theta), sinf(phi) * sinf(theta), cosf(theta));
@@ -736,7 +856,7 @@ static ods env_sample_direction(const oemitter *e, v3 ref_p, float sx, float sy)
     d = xf_vec(e->to_world, d);
     ds.p = vadd(ref_p, vscale(d, dist)); ds.n = vneg(d); ds.d = d; ds.dist = dist;
     ds.pdf = pdf > 0.f ? pdf * inv_sin_theta * (1.f / (2.f * sqrf(PI_F))) : 0.f;
-    ds.value = vscale(env_lookup(e, u, v), 1.f / ds.pdf);
+    ds.value = cscale(env_lookup(s, e, u, v, wav), 1.f / ds.pdf);
     return ds;
 }
 static uint32_t ek_binary_search(uint32_t start, uint32_t end, const float *cdf, float value) {   /* array_utils.h:153-171 */
@@ -748,7 +868,7 @@ static uint32_t ek_binary_search(uint32_t start, uint32_t end, const float *cdf,
     }
     return start;
 }
-static ods area_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy) {
+static ods area_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy, const float *wav) {
     /* area.cpp:103-117 -> shape.cpp:252-270 -> mesh.cpp:320-365 -> distr_1d.h:144-203 */
     ods ds; const omesh *m = &s->meshes[e->mesh];
     uint32_t idx = ek_binary_search(e->valid_lo, e->valid_hi, e->cdf, sy * e->cdf_sum);
@@ -765,7 +885,7 @@ static ods area_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p
     float dp = fabsf(vdot(ds.d, ds.n));
     ds.pdf = e->normalization * (dp != 0.f ? dist_squared / dp : 0.f);
     int active = vdot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
-    ds.value = active ? vscale(e->radiance, 1.f / ds.pdf) : V(0, 0, 0);
+    ds.value = active ? cscale(emitter_radiance(s, e, wav), 1.f / ds.pdf) : C1(0.f);
     return ds;
 }
 static float area_pdf_direction(const oemitter *e, v3 d, v3 n, float dist) {   /* area.cpp:119-125, shape.cpp:272-283 */
@@ -776,22 +896,22 @@ static v3 square_to_uniform_sphere(float sx, float sy) {    /* warp.h:262-267 */
     float z = 1.f - 2.f * sy, r = safe_sqrtf(1.f - z * z), phi = 2.f * PI_F * sx;
     return V(r * cosf(phi), r * sinf(phi), z);
 }
-static ods constant_sample_direction(const oemitter *e, v3 ref_p, float sx, float sy) {   /* constant.cpp:77-103 */
+static ods constant_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy, const float *wav) {   /* constant.cpp:77-103 */
     ods ds; memset(&ds, 0, sizeof(ds));
     v3 d = square_to_uniform_sphere(sx, sy);
     ds.dist = 2.f * e->bsphere_radius; ds.p = vadd(ref_p, vscale(d, ds.dist)); ds.n = vneg(d); ds.d = d;
-    ds.pdf = .25f * INV_PI_F; ds.value = vscale(e->radiance, 1.f / ds.pdf);
+    ds.pdf = .25f * INV_PI_F; ds.value = cscale(emitter_radiance(s, e, wav), 1.f / ds.pdf);
     return ds;
 }
-static ods point_sample_direction(const oemitter *e, v3 ref_p) {    /* point.cpp:74-98 */
+static ods point_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, const float *wav) {    /* point.cpp:74-98 */
     ods ds; memset(&ds, 0, sizeof(ds));
     ds.p = e->position; ds.pdf = 1.f; ds.delta = 1;
     ds.d = vsub(ds.p, ref_p); ds.dist = vnorm(ds.d);
     float inv_dist = 1.f / ds.dist; ds.d = vscale(ds.d, inv_dist);
-    ds.value = vscale(e->radiance, inv_dist * inv_dist);
+    ds.value = cscale(emitter_radiance(s, e, wav), inv_dist * inv_dist);
     return ds;
 }
-static ods sample_emitter_direction(const orc_scene *s, v3 ref_p, float sx, float sy) {   /* scene.cpp:141-176 */
+static ods sample_emitter_direction(const orc_scene *s, v3 ref_p, float sx, float sy, const float *wav) {   /* scene.cpp:141-176 */
     ods ds; memset(&ds, 0, sizeof(ds));
     if (s->n_emitters == 0) return ds;
     uint32_t index = 0; float emitter_pdf = 1.f;
@@ -801,12 +921,12 @@ static ods sample_emitter_direction(const orc_scene *s, v3 ref_p, float sx, floa
         sx = (sx - (float) index * emitter_pdf) * (float) s->n_emitters;
     }
     const oemitter *e = &s->emitters[index];
-    if (e->type == MTSB_EMITTER_AREA) ds = area_sample_direction(s, e, ref_p, sx, sy);
-    else if (e->type == MTSB_EMITTER_ENVMAP) ds = env_sample_direction(e, ref_p, sx, sy);
-    else if (e->type == MTSB_EMITTER_CONSTANT) ds = constant_sample_direction(e, ref_p, sx, sy);
-    else ds = point_sample_direction(e, ref_p);
+    if (e->type == MTSB_EMITTER_AREA) ds = area_sample_direction(s, e, ref_p, sx, sy, wav);
+    else if (e->type == MTSB_EMITTER_ENVMAP) ds = env_sample_direction(s, e, ref_p, sx, sy, wav);
+    else if (e->type == MTSB_EMITTER_CONSTANT) ds = constant_sample_direction(s, e, ref_p, sx, sy, wav);
+    else ds = point_sample_direction(s, e, ref_p, wav);
     ds.delta = e->type == MTSB_EMITTER_POINT;
-    if (s->n_emitters > 1) { ds.pdf *= emitter_pdf; ds.value = vscale(ds.value, 1.f / emitter_pdf); }
+    if (s->n_emitters > 1) { ds.pdf *= emitter_pdf; ds.value = cscale(ds.value, 1.f / emitter_pdf); }
     return ds;
 }
 
@@ -831,9 +951,9 @@ void orc_sensor_sample_ray(const orc_scene *s, uint32_t id, uint64_t n, const fl
 static float mis_weight(float a, float b) { a *= a; b *= b; return a > 0.f ? a / (a + b) : 0.f; }   /* path.cpp:223-227 */
 
 /* PathIntegrator::sample, src/integrators/path.cpp:100-211 */
-static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, float maxt, float *out4, uint64_t *cnt) {
-    float eta = 1.f, emission_weight = 1.f;
-    v3 throughput = V(1, 1, 1), result = V(0, 0, 0);
+static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, float maxt, const float *wav, float *out5, uint64_t *cnt) {
+    float eta = 1.f, emission_weight = 1.f; const int nch = s->nch;
+    col throughput = C1(1.f), result = C1(0.f);
     ohit h; trace(s, o, d, mint, maxt, 0, &h); cnt[1]++;
     osi si; make_si(s, o, d, &h, &si);
     int valid_ray = si.valid;
@@ -843,15 +963,15 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
         cnt[3]++;
         if (emitter >= 0) {
             const oemitter *e = &s->emitters[emitter];
-            v3 Le = e->type == MTSB_EMITTER_AREA ? (si.wi.z > 0.f ? e->radiance : V(0, 0, 0))       /* area.cpp:71-79 */
-                  : e->type == MTSB_EMITTER_ENVMAP ? env_eval(e, ray_d) : e->radiance;              /* envmap.cpp:132-145, constant.cpp:105-108 */
-            result = vadd(result, vscale(vmul(throughput, Le), emission_weight));
+            col Le = e->type == MTSB_EMITTER_AREA ? (si.wi.z > 0.f ? emitter_radiance(s, e, wav) : C1(0.f))       /* area.cpp:71-79 */
+                   : e->type == MTSB_EMITTER_ENVMAP ? env_eval(s, e, ray_d, wav) : emitter_radiance(s, e, wav);   /* envmap.cpp:132-145, constant.cpp:105-108 */
+            result = cadd(result, cscale(cmul(throughput, Le), emission_weight));
         }
         if (!si.valid) break;
         if (depth > s->rr_depth) {
-            float q = fminf(vhmax(throughput) * sqrf(eta), .95f);
+            float q = fminf(chmax(throughput, nch) * sqrf(eta), .95f);
             int survive = pcg_float(rng) < q;
-            throughput = vscale(throughput, 1.f / q);
+            throughput = cscale(throughput, 1.f / q);
             if (!survive) break;
         }
         if ((uint32_t) depth >= (uint32_t) s->max_depth) break;
@@ -859,25 +979,25 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
         if (bsdf->type != MTSB_BSDF_DIELECTRIC) {     /* has a Smooth lobe */
             float sx = pcg_float(rng), sy = pcg_float(rng);
             if (s->n_emitters > 0) {
-                ods ds = sample_emitter_direction(s, si.p, sx, sy);
+                ods ds = sample_emitter_direction(s, si.p, sx, sy, wav);
                 if (ds.pdf != 0.f) {
-                    v3 emitter_val = ds.value;
-                    if (emitter_val.x != 0.f || emitter_val.y != 0.f || emitter_val.z != 0.f) {
+                    col emitter_val = ds.value;
+                    if (!cblack(emitter_val, nch)) {
                         /* visibility: scene.cpp:178-182 */
                         ohit sh; cnt[2]++;
-                        if (trace(s, si.p, ds.d, RAY_EPS * (1.f + vhmax(vabs(si.p))), ds.dist * (1.f - SHADOW_EPS), 1, &sh)) emitter_val = V(0, 0, 0);
+                        if (trace(s, si.p, ds.d, RAY_EPS * (1.f + vhmax(vabs(si.p))), ds.dist * (1.f - SHADOW_EPS), 1, &sh)) emitter_val = C1(0.f);
                     }
-                    v3 wo = to_local(&si, ds.d), bsdf_val; float bsdf_pdf;
-                    bsdf_eval_pdf(s, bsdf, &si, wo, &bsdf_val, &bsdf_pdf);
+                    v3 wo = to_local(&si, ds.d); col bsdf_val; float bsdf_pdf;
+                    bsdf_eval_pdf(s, bsdf, &si, wo, &bsdf_val, &bsdf_pdf, wav);
                     float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bsdf_pdf);      /* path.cpp:169 */
-                    result = vadd(result, vscale(vmul(vmul(throughput, bsdf_val), emitter_val), mis));
+                    result = cadd(result, cscale(cmul(cmul(throughput, bsdf_val), emitter_val), mis));
                 }
             }
         }
         float s1 = pcg_float(rng), s2x = pcg_float(rng), s2y = pcg_float(rng);
-        obs bs = bsdf_sample(s, bsdf, &si, s1, s2x, s2y);
-        throughput = vmul(throughput, bs.weight);
-        if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+        obs bs = bsdf_sample(s, bsdf, &si, s1, s2x, s2y, wav);
+        throughput = cmul(throughput, bs.weight);
+        if (cblack(throughput, nch)) break;
         eta *= bs.eta;
         v3 no = si.p, nd = to_world(&si, bs.wo);
         ohit h2; trace(s, no, nd, (1.f + vhmax(vabs(si.p))) * RAY_EPS, INFINITY, 0, &h2); cnt[1]++;
@@ -898,7 +1018,8 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
         }
         si = si_bsdf; ray_d = nd;
     }
-    out4[0] = result.x; out4[1] = result.y; out4[2] = result.z; out4[3] = valid_ray ? 1.f : 0.f;
+    for (int i = 0; i < 4; ++i) out5[i] = result.c[i];
+    out5[4] = valid_ray ? 1.f : 0.f;
 }
 
 /* ImageBlock::put, src/librender/imageblock.cpp:79-172, block = full film, border 0, analytic filter eval */
@@ -940,15 +1061,24 @@ void orc_film_develop(const orc_scene *s, uint32_t id, const float *xyzaw, float
     }
 }
 /* SamplingIntegrator::render_sample (integrator.cpp:224-271) for stream `stream` of pixel `pixel` */
+/* rad4: rgb mode = radiance rgb + alpha; spectral mode = XYZ + alpha (integrator.cpp:249-262: ray_weight * result -> spectrum_to_xyz) */
 static void render_one(const orc_scene *s, const mtsb_sensor_desc *sn, uint32_t pixel, uint32_t stream, uint64_t seed, float *pos2, float *rad4, uint64_t *cnt) {
     pcg32 rng; sampler_seed(&rng, seed, stream);
     float jx = pcg_float(&rng), jy = pcg_float(&rng);
-    (void) pcg_float(&rng);                          /* wavelength sample */
+    float wavelength_sample = pcg_float(&rng);       /* integrator.cpp:237 */
+    float wav[4] = { 0, 0, 0, 0 }, wav_weight[4] = { 1, 1, 1, 1 };
+    if (s->spectral) sample_wavelengths(wavelength_sample, wav, wav_weight);     /* perspective.cpp:196 */
     float fx = (float) (pixel % sn->film_width) + jx, fy = (float) (pixel / sn->film_width) + jy;
     v3 o, d; float mint, maxt;
     sensor_ray(sn, fx / (float) sn->film_width, fy / (float) sn->film_height, &o, &d, &mint, &maxt);
     cnt[0]++;
-    path_sample(s, &rng, o, d, mint, maxt, rad4, cnt);
+    float r5[5];
+    path_sample(s, &rng, o, d, mint, maxt, wav, r5, cnt);
+    if (s->spectral) {
+        for (int i = 0; i < 4; ++i) r5[i] = wav_weight[i] * r5[i];
+        v3 xyz = spectrum_to_xyz(r5, wav); rad4[0] = xyz.x; rad4[1] = xyz.y; rad4[2] = xyz.z;
+    } else { rad4[0] = r5[0]; rad4[1] = r5[1]; rad4[2] = r5[2]; }
+    rad4[3] = r5[4];
     pos2[0] = fx; pos2[1] = fy;
 }
 void orc_trace_sample(const orc_scene *s, uint32_t id, uint32_t pixel, uint32_t stream, uint64_t seed, float *out4) {
@@ -966,6 +1096,7 @@ void orc_render(const orc_scene *s, uint32_t id, uint32_t spp_begin, uint32_t sp
             render_one(s, sn, (uint32_t) p, (uint32_t) p * spp_total + spp_begin + k, seed, pos, r, cnt);
             float v5[5] = { 0.412453f * r[0] + 0.357580f * r[1] + 0.180423f * r[2], 0.212671f * r[0] + 0.715160f * r[1] + 0.072169f * r[2],
                             0.019334f * r[0] + 0.119193f * r[1] + 0.950227f * r[2], r[3], 1.f };     /* spectrum.h:220-227 */
+            if (s->spectral) { v5[0] = r[0]; v5[1] = r[1]; v5[2] = r[2]; }
             film_put(sn, pos[0], pos[1], v5, xyzaw);
             c0 += cnt[0]; c1 += cnt[1]; c2 += cnt[2]; c3 += cnt[3];
         }
@@ -980,17 +1111,17 @@ static void local_si(osi *si, const float *wi, const float *uv) {
 }
 void orc_bsdf_sample(const orc_scene *s, uint32_t id, uint64_t n, const float *wi, const float *uv, const float *s1, const float *s2, float *out9) {
     for (uint64_t i = 0; i < n; ++i) { osi si; local_si(&si, wi + 3 * i, uv + 2 * i);
-        obs bs = bsdf_sample(s, &s->bsdfs[id], &si, s1[i], s2[2 * i], s2[2 * i + 1]); float *o = out9 + 9 * i;
-        o[0] = bs.wo.x; o[1] = bs.wo.y; o[2] = bs.wo.z; o[3] = bs.pdf; o[4] = bs.eta; o[5] = bs.weight.x; o[6] = bs.weight.y; o[7] = bs.weight.z; o[8] = bs.delta ? 1.f : 0.f; }
+        obs bs = bsdf_sample(s, &s->bsdfs[id], &si, s1[i], s2[2 * i], s2[2 * i + 1], NULL); float *o = out9 + 9 * i;
+        o[0] = bs.wo.x; o[1] = bs.wo.y; o[2] = bs.wo.z; o[3] = bs.pdf; o[4] = bs.eta; o[5] = bs.weight.c[0]; o[6] = bs.weight.c[1]; o[7] = bs.weight.c[2]; o[8] = bs.delta ? 1.f : 0.f; }
 }
 void orc_bsdf_eval_pdf(const orc_scene *s, uint32_t id, uint64_t n, const float *wi, const float *uv, const float *wo, float *eval3, float *pdf) {
-    for (uint64_t i = 0; i < n; ++i) { osi si; local_si(&si, wi + 3 * i, uv + 2 * i); v3 val;
-        bsdf_eval_pdf(s, &s->bsdfs[id], &si, V(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), &val, &pdf[i]);
-        eval3[3 * i] = val.x; eval3[3 * i + 1] = val.y; eval3[3 * i + 2] = val.z; }
+    for (uint64_t i = 0; i < n; ++i) { osi si; local_si(&si, wi + 3 * i, uv + 2 * i); col val;
+        bsdf_eval_pdf(s, &s->bsdfs[id], &si, V(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), &val, &pdf[i], NULL);
+        eval3[3 * i] = val.c[0]; eval3[3 * i + 1] = val.c[1]; eval3[3 * i + 2] = val.c[2]; }
 }
 void orc_sample_emitter_direction(const orc_scene *s, uint64_t n, const float *ref_p, const float *s2, float *out11) {
-    for (uint64_t i = 0; i < n; ++i) { ods ds = sample_emitter_direction(s, V(ref_p[3 * i], ref_p[3 * i + 1], ref_p[3 * i + 2]), s2[2 * i], s2[2 * i + 1]);
-        float *o = out11 + 11 * i; o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.x; o[6] = ds.value.y; o[7] = ds.value.z;
+    for (uint64_t i = 0; i < n; ++i) { ods ds = sample_emitter_direction(s, V(ref_p[3 * i], ref_p[3 * i + 1], ref_p[3 * i + 2]), s2[2 * i], s2[2 * i + 1], NULL);
+        float *o = out11 + 11 * i; o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.c[0]; o[6] = ds.value.c[1]; o[7] = ds.value.c[2];
         o[8] = ds.n.x; o[9] = ds.n.y; o[10] = ds.n.z; }
 }
 

@@ -76,6 +76,15 @@ void orc_render(const orc_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint
 /* one path, for debugging parity: returns radiance rgb + alpha of stream `stream` at pixel `pixel` */
 void orc_trace_sample(const orc_scene *s, uint32_t sensor_id, uint32_t pixel, uint32_t stream, uint64_t seed, float *out4);
 
+/* spectral mode arithmetic (scalar_spectral): core/spectrum.h:147-217, 270-316; render/srgb.h:8-24; core/distr_1d.h:378-393, 655-677;
+ * src/spectra/d65.cpp */
+void orc_sample_wavelength(float u, float *wav4, float *weight4);
+float orc_srgb_model_eval(const float *coeff3, float lambda);
+float orc_regular_eval(const float *values, uint32_t n, float lo, float hi, float x);
+float orc_irregular_eval(const float *nodes, const float *values, uint32_t n, float x);
+float orc_d65_eval(float lambda);
+void orc_spectrum_to_xyz(const float *value4, const float *wav4, float *xyz);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,6 +6,7 @@
 #include "../../include/mtsb200.h"
 #include "../../mitsuba2_b200/csrc/path.h"
 #include "../../mitsuba2_b200/csrc/host_tables.h"
+#include "../../mitsuba2_b200/csrc/cie_tables.h"
 #include <vector>
 #include <algorithm>
 #include <numeric>
@@ -18,7 +19,7 @@ struct hs_scene {
     std::vector<MeshDev> meshes; std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
     std::vector<SensorDev> sensors;
     std::vector<float> pos, nrm, uv; std::vector<uint4> faces;
-    std::vector<std::vector<float>> tables; std::vector<float4> env_rgba;
+    std::vector<std::vector<float>> tables; std::vector<float4> env_rgba; std::vector<float> cie; bool spectral = false;
     std::vector<uint4> nodes; std::vector<float4> tris;
     std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
     SceneDev dev; uint32_t bvh_nodes = 0, bvh_depth = 0;
@@ -142,11 +143,21 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         vbase += m.vertex_count; fbase += m.face_count;
     }
     s->tables.reserve(64 + d->n_textures + d->n_emitters);
+    s->spectral = d->mode == MTSB_MODE_SPECTRAL;
+    if (s->spectral) {
+        s->cie.resize(4 * 95);
+        for (int k = 0; k < 3 * 95; ++k) s->cie[k] = kCie1931[k];
+        for (int k = 0; k < 95; ++k) s->cie[3 * 95 + k] = kCieD65[k] * (1.f / 10568.f);
+        s->dev.cie = s->cie.data();
+    }
     for (uint32_t i = 0; i < d->n_textures; ++i) {
         const mtsb_texture_desc &t = d->textures[i]; TexDev td; memset(&td, 0, sizeof(td));
         td.type = t.type; td.value = mk3(t.value[0], t.value[1], t.value[2]);
         if (t.type == MTSB_TEX_BITMAP) { td.w = t.width; td.h = t.height; td.ch = t.channels; memcpy(td.to_uv, t.to_uv, sizeof(td.to_uv));
             s->tables.emplace_back(t.data, t.data + (size_t) t.width * t.height * t.channels); td.data = s->tables.back().data(); }
+        if (t.type == MTSB_TEX_REGULAR || t.type == MTSB_TEX_IRREGULAR) { td.w = t.width; td.lambda_min = t.lambda_min; td.lambda_max = t.lambda_max;
+            s->tables.emplace_back(t.data, t.data + (size_t) t.width * (t.type == MTSB_TEX_IRREGULAR ? 2 : 1)); td.data = s->tables.back().data(); }
+        td.d65_scale = t.d65_scale;
         s->tex.push_back(td);
     }
     for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
@@ -158,7 +169,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     hs_build_bvh(s);
     s->dev.env_emitter = -1;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
-        const mtsb_emitter_desc &e = d->emitters[i]; EmitterDev ed; memset(&ed, 0, sizeof(ed)); ed.type = e.type;
+        const mtsb_emitter_desc &e = d->emitters[i]; EmitterDev ed; memset(&ed, 0, sizeof(ed)); ed.type = e.type; ed.radiance_tex = e.radiance_tex;
         if (e.type == MTSB_EMITTER_AREA) {
             ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
             const MeshDev &m = s->meshes[e.mesh_id];
@@ -176,7 +187,8 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
             s->dev.env_emitter = (int) i; ed.w = e.width; ed.h = e.height; ed.scale = e.scale;
             memcpy(ed.to_world, e.to_world, sizeof(ed.to_world)); invert4x4(e.to_world, ed.to_local);
             size_t npx = (size_t) e.width * e.height; s->env_rgba.resize(npx);
-            for (size_t k = 0; k < npx; ++k) s->env_rgba[k] = make_float4(e.rgba[4 * k], e.rgba[4 * k + 1], e.rgba[4 * k + 2], 1.f);
+            for (size_t k = 0; k < npx; ++k) s->env_rgba[k] = s->spectral ? make_float4(e.coeff_scale[4 * k], e.coeff_scale[4 * k + 1], e.coeff_scale[4 * k + 2], e.coeff_scale[4 * k + 3])
+                                                             : make_float4(e.rgba[4 * k], e.rgba[4 * k + 1], e.rgba[4 * k + 2], 1.f);
             ed.rgba = s->env_rgba.data();
             std::vector<float> lum = env_importance(e.rgba, e.width, e.height);
             H2DTable h = build_h2d(lum.data(), e.width, e.height);
@@ -220,17 +232,17 @@ extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const floa
 // The wavefront loop of mtsb_render (run_batch in api.cu), stage by stage, with sequential "threads".
 struct HsPool {
     std::vector<float4> qo[2], qd[2], qh[2], qt[2], so, sdv, scv, result;
-    std::vector<uint4> qm[2], qr[2];
+    std::vector<uint4> qm[2], qr[2]; std::vector<float2> qw[2];
     explicit HsPool(uint32_t pool) : so(pool), sdv(pool), scv(pool), result(pool) {
-        for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); }
+        for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); qw[k].resize(pool); }
     }
-    PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); return q; }
+    PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); q.wav_eta = qw[k].data(); return q; }
 };
-template <typename GradFn>
+template <typename M, typename GradFn>
 static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad) {
     std::vector<uint2> fast(8);
     uint32_t n = b.n_paths; int cur = 0; uint32_t count = n;
-    for (uint32_t i = 0; i < n; ++i) raygen_body(sn, b, P.queue(cur), i);
+    for (uint32_t i = 0; i < n; ++i) raygen_body<M>(sn, b, P.queue(cur), i);
     for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
         PathQueue qin = P.queue(cur), qout = P.queue(cur ^ 1);
         for (uint32_t i = 0; i < count; ++i) {
@@ -241,8 +253,8 @@ static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b,
         cnt[0] += count; cnt[2] += count;
         uint32_t next = 0, nshadow = 0;
         for (uint32_t i = 0; i < count; ++i) {
-            ShadeOut out = shade_body(s->dev, qin, b, i, grad);
-            if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; next++; }
+            ShadeOut out = shade_body<M>(s->dev, qin, b, i, grad);
+            if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; if (M::spectral) qout.wav_eta[next] = out.wav_eta; next++; }
             if (out.shadow) { P.so[nshadow] = out.s_o_mint; P.sdv[nshadow] = out.s_d_maxt; P.scv[nshadow] = out.s_contrib_id; nshadow++; }
         }
         for (uint32_t i = 0; i < nshadow; ++i) {
@@ -265,10 +277,10 @@ extern "C" void hs_render(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, u
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
-        hs_run_batch(s, sn, b, P, cnt, NoGrad());
+        if (s->spectral) hs_run_batch<Spectral>(s, sn, b, P, cnt, NoGrad()); else hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad());
         for (uint32_t i = 0; i < n; ++i) {
             float fx, fy; path_film_pos(sn, b, i, fx, fy);
-            film_put(sn, fx, fy, radiance_to_xyza(P.result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
+            film_put(sn, fx, fy, s->spectral ? result_to_xyza<Spectral>(P.result[i]) : result_to_xyza<Rgb>(P.result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
                 xyzaw[5 * (size_t) pix] += v.x; xyzaw[5 * (size_t) pix + 1] += v.y; xyzaw[5 * (size_t) pix + 2] += v.z; xyzaw[5 * (size_t) pix + 3] += v.w; xyzaw[5 * (size_t) pix + 4] += w; });
         }
     }
@@ -288,9 +300,9 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
-        hs_run_batch(s, sn, b, P, cnt, NoGrad());
+        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad());
         std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
-        hs_run_batch(s, sn, b, P, cnt, [&](const SceneDev &sc, const RenderBatch &bb, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
+        hs_run_batch<Rgb>(s, sn, b, P, cnt, [&](const SceneDev &sc, const RenderBatch &bb, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
             texture_adjoint(sc, bb, g, pid, si, bsdf, [](float *dst, float v) { *dst += v; });
         });
     }
