@@ -74,7 +74,33 @@ def side_metrics(mi, local):
     out["c4_gradient_pass_ms"] = float(np.median(ms))
     out["c4_gradient_pass_msamples_per_s"] = 512 * 512 * 64 / (out["c4_gradient_pass_ms"] * 1e-3) / 1e6
     del sc4
+    out.update(spectral_metric(mi, local))
     out["parity_gates"] = parity_gates(mi, local)
+    return out
+
+
+def spectral_metric(mi, local, spp=16, steps=3, warmup=2):
+    """C3 in the spectral mode (`cuda_b200_spectral`: 4 wavelengths per path, same scene authored in RGB + Cu optical
+    constants): Msamples/s on one GPU, inputs resident, same timing as the headline."""
+    import time
+    from mitsuba2_b200 import scenes
+    sd = scenes.c3_scene()
+    sd.mode = "spectral"
+    t0 = time.time()
+    sc = mi.Scene(sd, device=local)
+    out = {"c3_spectral_scene_setup_s": time.time() - t0}
+    ms, stages = [], {}
+    for i in range(warmup + steps):
+        sc.film_clear()
+        st = sc.render_accumulate(spp=spp, seed=i, spp_begin=0, spp_total=spp)
+        if i >= warmup:
+            ms.append(st["ms_total"])
+            for k in ("ms_closest", "ms_shade", "ms_any"):
+                stages[k] = stages.get(k, 0.0) + st[k] / steps
+    n = sd.sensors[0]["width"] * sd.sensors[0]["height"] * spp
+    out["c3_spectral_msamples_per_s"] = n / (float(np.median(ms)) * 1e-3) / 1e6
+    out["c3_spectral_stage_ms_per_step"] = stages
+    out["c3_spectral_samples_per_step"] = n
     return out
 
 

@@ -90,12 +90,47 @@ class SceneData:
         self.meshes, self.bsdfs, self.textures, self.emitters, self.sensors = [], [], [], [], []
         self.max_depth, self.rr_depth = -1, 5
         self.spp = 4
+        # "rgb" (scalar_rgb semantics) or "spectral" (scalar_spectral): the same authored scene serves both; to_desc()
+        # performs the conversions the reference's plugins do at load time in a spectral variant (RGB -> model
+        # coefficients, emitters -> coefficients x D65, named conductors -> tabulated eta/k)
+        self.mode = "rgb"
+        self.rgb2spec_model = None      # optional (scale, data) table for rgb2spec.fetch (tests use a small one)
 
     # ---- builders -------------------------------------------------------------------------
     def add_texture_rgb(self, rgb):
         rgb = [float(rgb)] * 3 if np.isscalar(rgb) else [float(x) for x in rgb]
         self.textures.append({"type": A.TEX_CONSTANT, "value": rgb})
         return len(self.textures) - 1
+
+    def add_texture_spectrum(self, wavelengths, values):
+        """``irregular`` spectrum (src/spectra/irregular.cpp); spectral mode only."""
+        w, v = _f32(wavelengths).reshape(-1), _f32(values).reshape(-1)
+        assert w.shape == v.shape and w.size >= 2 and np.all(np.diff(w) > 0)
+        self.textures.append({"type": A.TEX_IRREGULAR, "data": np.ascontiguousarray(np.concatenate([w, v]))})
+        return len(self.textures) - 1
+
+    def add_texture_regular(self, lambda_min, lambda_max, values):
+        """``regular`` spectrum (src/spectra/regular.cpp); spectral mode only."""
+        self.textures.append({"type": A.TEX_REGULAR, "data": _f32(values).reshape(-1), "lambda_min": float(lambda_min), "lambda_max": float(lambda_max)})
+        return len(self.textures) - 1
+
+    def add_texture_uniform(self, value):
+        """``uniform`` spectrum (src/spectra/uniform.cpp); spectral mode only."""
+        self.textures.append({"type": A.TEX_UNIFORM, "value": [float(value)] * 3})
+        return len(self.textures) - 1
+
+    def add_texture_coeff(self, coeff, d65_scale=0.0):
+        """Constant texture given directly as sRGB-model coefficients (spectral mode; what ``srgb`` stores, srgb.cpp:44-48)."""
+        self.textures.append({"type": A.TEX_CONSTANT, "value": [float(x) for x in coeff], "coeff": True, "d65_scale": float(d65_scale)})
+        return len(self.textures) - 1
+
+    def _tex(self, x):
+        """texture id | rgb triple / scalar | {"wavelengths", "values"} -> texture id"""
+        if isinstance(x, (int, np.integer)) and not isinstance(x, bool):
+            return int(x)
+        if isinstance(x, dict):
+            return self.add_texture_spectrum(x["wavelengths"], x["values"])
+        return self.add_texture_rgb(x)
 
     def add_texture_bitmap(self, data, to_uv=None):
         data = _f32(data)
@@ -111,10 +146,24 @@ class SceneData:
         self.bsdfs.append({"type": A.BSDF_DIFFUSE, "reflectance_tex": tex})
         return len(self.bsdfs) - 1
 
-    def add_roughconductor(self, eta, k, alpha=0.1, alpha_v=None, distribution="beckmann", sample_visible=True,
-                           specular_reflectance=None):
-        self.bsdfs.append({"type": A.BSDF_ROUGHCONDUCTOR, "eta_tex": self.add_texture_rgb(eta),
-                           "k_tex": self.add_texture_rgb(k), "alpha_u": float(alpha),
+    def add_roughconductor(self, eta=None, k=None, alpha=0.1, alpha_v=None, distribution="beckmann", sample_visible=True,
+                           specular_reflectance=None, material=None):
+        """``eta``/``k``: rgb triples, spectra ({"wavelengths", "values"}) or texture ids; or ``material`` = a named
+        conductor (roughconductor.cpp:155 -> complex_ior_from_file): rgb mode uses the pre-integrated colour, spectral
+        mode the tabulated optical constants."""
+        if material is not None:
+            from ._ior_data import CONDUCTORS_SPD
+            from .xml import CONDUCTORS_RGB
+            name = material.lower()
+            spd = CONDUCTORS_SPD.get(name)
+            eta_id = self.add_texture_rgb(CONDUCTORS_RGB[name][0])
+            k_id = self.add_texture_rgb(CONDUCTORS_RGB[name][1])
+            if spd is not None:      # spectral alternative of the same two textures
+                self.textures[eta_id]["spectrum"] = (spd["wavelengths"], spd["eta"])
+                self.textures[k_id]["spectrum"] = (spd["wavelengths"], spd["k"])
+            eta, k = eta_id, k_id
+        self.bsdfs.append({"type": A.BSDF_ROUGHCONDUCTOR, "eta_tex": self._tex(eta),
+                           "k_tex": self._tex(k), "alpha_u": float(alpha),
                            "alpha_v": float(alpha if alpha_v is None else alpha_v),
                            "distribution": A.MF_GGX if distribution.lower() == "ggx" else A.MF_BECKMANN,
                            "sample_visible": int(bool(sample_visible)),
@@ -131,9 +180,15 @@ class SceneData:
         self.meshes.append(mesh)
         mid = len(self.meshes) - 1
         if area_radiance is not None:
-            self.emitters.append({"type": A.EMITTER_AREA, "radiance": [float(x) for x in area_radiance], "mesh_id": mid})
+            self.emitters.append(dict(self._radiance(area_radiance), type=A.EMITTER_AREA, mesh_id=mid))
             mesh.emitter = len(self.emitters) - 1
         return mid
+
+    def _radiance(self, value):
+        """rgb triple / scalar -> {"radiance"}; a spectrum ({"wavelengths", "values"}, spectral mode) -> + {"radiance_tex"}"""
+        if isinstance(value, dict):
+            return {"radiance": [0.0, 0.0, 0.0], "radiance_tex": self.add_texture_spectrum(value["wavelengths"], value["values"])}
+        return {"radiance": [float(value)] * 3 if np.isscalar(value) else [float(x) for x in value]}
 
     def make_two_sided(self, bsdf_id):
         """``twosided`` adapter with the same BRDF on both sides (src/bsdfs/twosided.cpp); returns the id."""
@@ -144,14 +199,12 @@ class SceneData:
 
     def add_constant(self, radiance):
         """``constant`` environment emitter (src/emitters/constant.cpp)."""
-        rad = [float(radiance)] * 3 if np.isscalar(radiance) else [float(x) for x in radiance]
-        self.emitters.append({"type": A.EMITTER_CONSTANT, "radiance": rad})
+        self.emitters.append(dict(self._radiance(radiance), type=A.EMITTER_CONSTANT))
         return len(self.emitters) - 1
 
     def add_point(self, position, intensity):
         """``point`` light (src/emitters/point.cpp)."""
-        it = [float(intensity)] * 3 if np.isscalar(intensity) else [float(x) for x in intensity]
-        self.emitters.append({"type": A.EMITTER_POINT, "radiance": it, "position": [float(x) for x in position]})
+        self.emitters.append(dict(self._radiance(intensity), type=A.EMITTER_POINT, position=[float(x) for x in position]))
         return len(self.emitters) - 1
 
     def add_envmap(self, rgba, to_world=None, scale=1.0):
@@ -194,20 +247,63 @@ class SceneData:
             bd[i].distribution, bd[i].sample_visible = b.get("distribution", 0), b.get("sample_visible", 1)
             bd[i].eta = b.get("eta", 1.0)
             bd[i].two_sided = int(b.get("two_sided", 0))
-        td = (A.TextureDesc * max(1, len(self.textures)))()
-        for i, t in enumerate(self.textures):
+        spectral = self.mode == "spectral"
+        if self.mode not in ("rgb", "spectral"):
+            raise ValueError("SceneData.mode must be 'rgb' or 'spectral'")
+        if spectral:
+            from . import rgb2spec
+
+            def fetch(rgb):
+                return rgb2spec.fetch(rgb, model=self.rgb2spec_model)
+        texs = [dict(t) for t in self.textures]
+        emit_tex = {}
+        if spectral:
+            # what the texture plugins do when they are instantiated in a spectral variant
+            for t in texs:
+                if t["type"] == A.TEX_CONSTANT and "spectrum" in t:          # ior.h:100-115 -> `irregular`
+                    w, v = t["spectrum"]
+                    t["type"], t["data"] = A.TEX_IRREGULAR, np.ascontiguousarray(np.concatenate([_f32(w), _f32(v)]))
+                elif t["type"] == A.TEX_CONSTANT and not t.get("coeff"):     # srgb.cpp:28-48
+                    c = np.asarray(t["value"], dtype=np.float32)
+                    if np.any(c < 0) or np.any(c > 1):
+                        raise ValueError(f"Invalid RGB reflectance value {c}, must be in the range [0, 1]!")
+                    t["value"] = [float(x) for x in fetch(c)]
+                elif t["type"] == A.TEX_BITMAP and t["data"].shape[2] == 3:  # bitmap.cpp:120-135 (texels -> coefficients)
+                    t["data"] = np.ascontiguousarray(fetch(np.clip(t["data"], 0.0, 1.0)))
+            for i, e in enumerate(self.emitters):                            # srgb_d65.cpp:36-52
+                if e["type"] != A.EMITTER_ENVMAP:
+                    if "radiance_tex" in e:
+                        emit_tex[i] = e["radiance_tex"]
+                    else:
+                        coeff, scale = rgb2spec.emitter_coeff_scale(np.asarray(e["radiance"], dtype=np.float32), self.rgb2spec_model)
+                        texs.append({"type": A.TEX_CONSTANT, "value": [float(x) for x in coeff], "d65_scale": float(scale)})
+                        emit_tex[i] = len(texs) - 1
+        else:
+            for t in texs:
+                if t["type"] not in (A.TEX_CONSTANT, A.TEX_BITMAP) or t.get("coeff"):
+                    raise ValueError("spectrum textures need mode='spectral' (rgb variants take pre-integrated colours)")
+        td = (A.TextureDesc * max(1, len(texs)))()
+        for i, t in enumerate(texs):
             td[i].type = t["type"]
-            if t["type"] == A.TEX_CONSTANT:
+            td[i].d65_scale = t.get("d65_scale", 0.0)
+            if t["type"] in (A.TEX_CONSTANT, A.TEX_UNIFORM):
                 td[i].value = (C.c_float * 3)(*t["value"])
-            else:
+            elif t["type"] == A.TEX_BITMAP:
                 d = t["data"]
                 keep.append(d)
                 td[i].height, td[i].width, td[i].channels = d.shape
                 td[i].data = _ptr(d, A.c_float_p)
                 td[i].to_uv = (C.c_float * 9)(*t["to_uv"])
+            else:
+                d = t["data"]
+                keep.append(d)
+                td[i].width = d.size // (2 if t["type"] == A.TEX_IRREGULAR else 1)
+                td[i].data = _ptr(d, A.c_float_p)
+                td[i].lambda_min, td[i].lambda_max = t.get("lambda_min", 0.0), t.get("lambda_max", 0.0)
         ed = (A.EmitterDesc * max(1, len(self.emitters)))()
         for i, e in enumerate(self.emitters):
             ed[i].type = e["type"]
+            ed[i].radiance_tex = emit_tex.get(i, -1)
             if e["type"] == A.EMITTER_AREA:
                 ed[i].radiance = (C.c_float * 3)(*e["radiance"])
                 ed[i].mesh_id = e["mesh_id"]
@@ -224,6 +320,11 @@ class SceneData:
                 ed[i].rgba = _ptr(e["rgba"], A.c_float_p)
                 ed[i].to_world = (C.c_float * 16)(*e["to_world"])
                 ed[i].scale = e["scale"]
+                if spectral:                                                 # envmap.cpp:98-110
+                    coeff, scale = rgb2spec.emitter_coeff_scale(e["rgba"][:, :, :3], self.rgb2spec_model)
+                    cs = np.ascontiguousarray(np.concatenate([coeff, scale[:, :, None]], axis=2).astype(np.float32))
+                    keep.append(cs)
+                    ed[i].coeff_scale = _ptr(cs, A.c_float_p)
         sd = (A.SensorDesc * max(1, len(self.sensors)))()
         for i, s in enumerate(self.sensors):
             sd[i].to_world = (C.c_float * 16)(*s["to_world"])
@@ -232,7 +333,8 @@ class SceneData:
             sd[i].film_width, sd[i].film_height = s["width"], s["height"]
             sd[i].rfilter, sd[i].rfilter_radius, sd[i].rfilter_stddev = s["rfilter"], s["radius"], s["stddev"]
         desc = A.SceneDesc()
-        desc.n_meshes, desc.n_bsdfs, desc.n_textures = len(self.meshes), len(self.bsdfs), len(self.textures)
+        desc.n_meshes, desc.n_bsdfs, desc.n_textures = len(self.meshes), len(self.bsdfs), len(texs)
+        desc.mode = A.MODE_SPECTRAL if spectral else A.MODE_RGB
         desc.n_emitters, desc.n_sensors = len(self.emitters), len(self.sensors)
         desc.meshes, desc.bsdfs, desc.textures, desc.emitters, desc.sensors = md, bd, td, ed, sd
         desc.integrator.max_depth, desc.integrator.rr_depth = self.max_depth, self.rr_depth

@@ -65,7 +65,7 @@ def c3_scene(n_theta=1000, n_phi=2000, width=1920, height=1080, small=(158, 316)
     512^2 bitmap), ~100k-triangle dielectric sphere r=0.4 at (1.6,-0.8,0), 1x1 area light at y=3, envmap."""
     sd = SceneData()
     big = M.displaced_sphere(n_theta, n_phi)
-    big.bsdf = sd.add_roughconductor(CU_ETA, CU_K, 0.1)
+    big.bsdf = sd.add_roughconductor(material="Cu", alpha=0.1)     # rgb mode: CU_ETA / CU_K; spectral mode: Cu.{eta,k}.spd
     sd.add_mesh(big)
     tex = 0.2 + 0.6 * M._pcg32_stream(tex_res * tex_res * 3, 3, 1).reshape(tex_res, tex_res, 3)
     ground = M.quad([-10, -1.2, -10], [-10, -1.2, 10], [10, -1.2, 10], [10, -1.2, -10])

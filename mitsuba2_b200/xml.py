@@ -123,10 +123,12 @@ class _Loader:
                 p[n] = ("rgb", v * 3 if len(v) == 1 else v)
             elif c.tag == "spectrum":
                 v = self.attr(c, "value")
-                if ":" in v:
-                    raise NotImplementedError("wavelength:value <spectrum> needs the spectral variant")
-                f = _floats(v)
-                p[n] = ("rgb", f * 3 if len(f) == 1 else f)
+                if ":" in v:         # xml.cpp: "wavelength:value, ..." pairs -> `irregular` spectrum (spectral variants)
+                    pairs = [t.split(":") for t in re.split(r"[\s,]+", v.strip()) if t]
+                    p[n] = ("spectrum", {"wavelengths": [float(a) for a, _ in pairs], "values": [float(b) for _, b in pairs]})
+                else:
+                    f = _floats(v)
+                    p[n] = ("rgb", f * 3 if len(f) == 1 else f)
             elif c.tag in ("point", "vector"):
                 if c.get("value") is not None:
                     p[n] = _floats(self.attr(c, "value"))
@@ -174,6 +176,8 @@ class _Loader:
         kind, v = value
         if kind == "rgb":
             return self.sd.add_texture_rgb(v)
+        if kind == "spectrum":
+            return self.sd.add_texture_spectrum(v["wavelengths"], v["values"])
         el = v
         ty = self.attr(el, "type")
         if ty != "bitmap":
@@ -202,14 +206,17 @@ class _Loader:
         elif ty == "diffuse":
             idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
         elif ty == "roughconductor":
+            material = None
             if "eta" in p or "k" in p:
                 eta, k = p.get("eta", ("rgb", [0.0] * 3))[1], p.get("k", ("rgb", [1.0] * 3))[1]
             else:
-                eta, k = CONDUCTORS_RGB[p.get("material", "Cu").lower()]
+                eta, k, material = None, None, p.get("material", "Cu")
+                if material.lower() not in CONDUCTORS_RGB:
+                    raise NotImplementedError(f"conductor material '{material}' is not in the built-in table")
             alpha = p.get("alpha", 0.1)
             idx = self.sd.add_roughconductor(eta, k, p.get("alpha_u", alpha), p.get("alpha_v", alpha), p.get("distribution", "beckmann"),
                                              p.get("sample_visible", True),
-                                             p["specular_reflectance"][1] if "specular_reflectance" in p else None)
+                                             p["specular_reflectance"][1] if "specular_reflectance" in p else None, material=material)
         elif ty == "dielectric":
             def ior(v, d):
                 v = p.get(v, d)
@@ -247,7 +254,7 @@ class _Loader:
                 if self.attr(target, "type") != "area":
                     raise ValueError("only area emitters can be attached to shapes")
                 rad = self.props(target).get("radiance", ("rgb", [1.0] * 3))
-                if rad[0] != "rgb":
+                if rad[0] not in ("rgb", "spectrum"):
                     raise NotImplementedError("textured area-light radiance")
                 radiance = rad[1]
         m.bsdf = bsdf if bsdf is not None else self.sd.add_diffuse(0.5)     # shape.cpp:75-76

@@ -16,6 +16,7 @@
 #include <mitsuba/core/spectrum.h>
 #include <mitsuba/render/fresnel.h>
 #include <mitsuba/render/microfacet.h>
+#include <mitsuba/render/srgb.h>
 #include <enoki/random.h>
 #include <enoki/special.h>
 #include <cstdint>
@@ -31,6 +32,13 @@ namespace detail {
     throw std::runtime_error(std::string(file) + ":" + std::to_string(line) + ": " + msg);
 }
 }  // namespace detail
+}  // namespace mitsuba
+
+// The CIE 1931 table pointers live in libmitsuba-core (src/libcore/spectrum.cpp:187-189); the harness points them at the
+// same published data (mitsuba2_b200/csrc/cie_tables.h is generated from that file, tools/gen_cie_tables.py).
+#include "../mitsuba2_b200/csrc/cie_tables.h"
+namespace mitsuba {
+const float *cie1931_x_data = kCie1931, *cie1931_y_data = kCie1931 + 95, *cie1931_z_data = kCie1931 + 190;
 }  // namespace mitsuba
 
 using namespace mitsuba;
@@ -127,5 +135,32 @@ void ref_bbox_ray_intersect(const float *lo, const float *hi, const float *o, co
 // srgb_to_xyz / xyz_to_srgb (include/mitsuba/core/spectrum.h:220-245)
 void ref_srgb_to_xyz(const float *rgb, float *xyz) { auto r = srgb_to_xyz(Color<float, 3>(rgb[0], rgb[1], rgb[2])); xyz[0] = r.x(); xyz[1] = r.y(); xyz[2] = r.z(); }
 void ref_xyz_to_srgb(const float *xyz, float *rgb) { auto r = xyz_to_srgb(Color<float, 3>(xyz[0], xyz[1], xyz[2])); rgb[0] = r.x(); rgb[1] = r.y(); rgb[2] = r.z(); }
+
+// ---- spectral variants (Spectrum = mitsuba::Spectrum<float, 4>) ----
+using Spec4 = mitsuba::Spectrum<float, 4>;
+// sample_wavelength (include/mitsuba/core/spectrum.h:304-316)
+void ref_sample_wavelength(float u, float *wav4, float *weight4) {
+    auto [w, wt] = sample_wavelength<float, Spec4>(u);
+    for (int i = 0; i < 4; ++i) { wav4[i] = w[i]; weight4[i] = wt[i]; }
+}
+// srgb_model_eval (include/mitsuba/render/srgb.h:8-24), one wavelength replicated over the 4 lanes
+float ref_srgb_model_eval(const float *c, float lambda) {
+    return srgb_model_eval<Spec4>(Array<float, 3>(c[0], c[1], c[2]), Spec4(lambda))[0];
+}
+// ContinuousDistribution / IrregularContinuousDistribution::eval_pdf (include/mitsuba/core/distr_1d.h:378-393, 655-677)
+float ref_regular_eval(const float *values, uint32_t n, float lo, float hi, float x) {
+    ContinuousDistribution<float> d(Vector<float, 2>(lo, hi), values, n);
+    return d.eval_pdf(x);
+}
+float ref_irregular_eval(const float *nodes, const float *values, uint32_t n, float x) {
+    IrregularContinuousDistribution<float> d(nodes, values, n);
+    return d.eval_pdf(x);
+}
+// spectrum_to_xyz (include/mitsuba/core/spectrum.h:209-217)
+void ref_spectrum_to_xyz(const float *value4, const float *wav4, float *xyz) {
+    Spec4 v(value4[0], value4[1], value4[2], value4[3]), w(wav4[0], wav4[1], wav4[2], wav4[3]);
+    auto r = spectrum_to_xyz(v, w);
+    xyz[0] = r.x(); xyz[1] = r.y(); xyz[2] = r.z();
+}
 
 }  // extern "C"

@@ -307,7 +307,15 @@ def synthetic_envmap(w=64, h=32, seed=7):
     return img.astype(np.float32)
 
 
-def material_scene(res=(48, 32), spp=8, envmap=True, area=True):
+def spectral(sd):
+    """Switch a scene to the spectral mode (scalar_spectral semantics), using a small resolution-16 sRGB model table so
+    that the CPU suite does not have to build the 64^3 one."""
+    from mitsuba2_b200 import rgb2spec
+    sd.mode, sd.rgb2spec_model = "spectral", rgb2spec.table(16)
+    return sd
+
+
+def material_scene(res=(48, 32), spp=8, envmap=True, area=True, named_conductor=False):
     """diffuse (textured) ground + roughconductor sphere + dielectric sphere + area light + envmap."""
     sd = SceneData()
     rng = np.random.default_rng(3)
@@ -316,7 +324,8 @@ def material_scene(res=(48, 32), spp=8, envmap=True, area=True):
     ground.bsdf = sd.add_diffuse(tex)
     sd.add_mesh(ground)
     s1 = M.displaced_sphere(24, 48)
-    s1.bsdf = sd.add_roughconductor((0.200438, 0.924033, 1.102212), (3.912949, 2.452848, 2.142188), 0.1)
+    s1.bsdf = sd.add_roughconductor(material="Cu", alpha=0.1) if named_conductor else \
+        sd.add_roughconductor((0.200438, 0.924033, 1.102212), (3.912949, 2.452848, 2.142188), 0.1)
     sd.add_mesh(s1)
     s2 = M.displaced_sphere(16, 32, radius=0.4, center=(1.6, -0.8, 0), displace=False)
     s2.bsdf = sd.add_dielectric()
@@ -361,6 +370,12 @@ def _bind_math(l, prefix):
         "h2d_sample": (None, [vp, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]),
         "h2d_eval": (None, [vp, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]),
         "discrete_sample_reuse": (None, [vp, C.c_uint32, C.c_uint64, vp, vp, vp]),
+        # spectral variants
+        "sample_wavelength": (None, [f, vp, vp]),
+        "srgb_model_eval": (f, [vp, f]),
+        "regular_eval": (f, [vp, C.c_uint32, f, f, f]),
+        "irregular_eval": (f, [vp, vp, C.c_uint32, f]),
+        "spectrum_to_xyz": (None, [vp, vp, vp]),
     }
     out = {}
     for name, (res, args) in sig.items():
@@ -465,6 +480,26 @@ def math_cases(fn, seed=11):
     idx, uo = np.zeros(256, np.uint32), np.zeros(256, np.float32)
     fn["discrete_sample_reuse"](_p(pmf), 37, 256, _p(u), _p(idx), _p(uo))
     R["discrete_idx"], R["discrete_u"] = idx, uo
+    # ---- spectral variants (core/spectrum.h:147-217, 270-316; render/srgb.h:8-24; core/distr_1d.h:378-393, 655-677)
+    us = np.concatenate([np.array([0.0, 0.25, 0.5, 0.75, 0.999999], np.float32), rng.random(123, dtype=np.float32)])
+    sw = np.zeros((us.size, 8), np.float32)
+    for i, u in enumerate(us):
+        fn["sample_wavelength"](float(u), _p(sw[i, :4]), _p(sw[i, 4:]))
+    R["sample_wavelength"] = sw
+    coeffs = (rng.standard_normal((64, 3)) * np.array([1e-4, 0.05, 10.0])).astype(np.float32)
+    coeffs[0], coeffs[1], coeffs[2] = (0, 0, np.inf), (0, 0, -np.inf), (0, 0, 0)
+    lam = np.concatenate([np.array([360.0, 830.0, 538.0], np.float32), rng.uniform(360, 830, 13).astype(np.float32)])
+    R["srgb_model_eval"] = np.array([[fn["srgb_model_eval"](_p(c), float(l)) for l in lam] for c in coeffs], np.float32)
+    vals = rng.random(40, dtype=np.float32)
+    nodes = np.sort(rng.uniform(300, 900, 40)).astype(np.float32)
+    xs = np.concatenate([np.array([360.0, 830.0, 359.9, 830.1], np.float32), nodes[[0, 7, 39]], rng.uniform(280, 920, 200).astype(np.float32)])
+    R["regular_eval"] = np.array([fn["regular_eval"](_p(vals), 40, 360.0, 830.0, float(x)) for x in xs], np.float32)
+    R["irregular_eval"] = np.array([fn["irregular_eval"](_p(nodes), _p(vals), 40, float(x)) for x in xs], np.float32)
+    sx = np.zeros((128, 3), np.float32)
+    for i in range(128):
+        v4, w4 = rng.random(4, dtype=np.float32), rng.uniform(350, 840, 4).astype(np.float32)
+        fn["spectrum_to_xyz"](_p(v4), _p(w4), _p(sx[i]))
+    R["spectrum_to_xyz"] = sx
     return R
 
 
@@ -497,7 +532,7 @@ def z_test_pass_fraction(mean, reference, var_per_sample, n_mean, n_ref, signifi
     return float(np.mean(p > alpha))
 
 
-def n1_scene(res=(32, 24), spp=8):
+def n1_scene(res=(32, 24), spp=8, named_conductor=False):
     """SURVEY 8(f) N1 plugins: `twosided` BRDFs (an open quad seen from both sides, a rough-metal sphere), a `point`
     light and a `constant` background."""
     sd = SceneData()
@@ -508,7 +543,8 @@ def n1_scene(res=(32, 24), spp=8):
     flip.bsdf = sd.make_two_sided(sd.add_diffuse(0.6))
     sd.add_mesh(flip)
     s1 = M.displaced_sphere(16, 32, radius=0.6, center=(0.3, -0.3, 0.2))
-    s1.bsdf = sd.make_two_sided(sd.add_roughconductor((0.2, 0.92, 1.1), (3.9, 2.45, 2.14), 0.2))
+    s1.bsdf = sd.make_two_sided(sd.add_roughconductor(material="Au", alpha=0.2) if named_conductor else
+                                sd.add_roughconductor((0.2, 0.92, 1.1), (3.9, 2.45, 2.14), 0.2))
     sd.add_mesh(s1)
     sd.add_point([-1.0, 1.5, -1.0], (8.0, 7.0, 6.0))
     sd.add_constant((0.3, 0.4, 0.6))

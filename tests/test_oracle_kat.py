@@ -20,6 +20,9 @@ TOL = {
     # hierarchical warp: a few ulps in a level's interval_to_linear are amplified near patch borders
     "h2d_sample_a": (1e-4, 1e-4), "h2d_sample_b": (1e-4, 1e-4), "h2d_sample_c": (1e-4, 1e-4),
     "h2d_eval_a": (3e-6, 1e-6), "h2d_eval_b": (3e-6, 1e-6), "h2d_eval_c": (3e-6, 1e-6),
+    # spectral variants: libm atanh/cosh/rsqrt vs enoki's vectorised approximations
+    "sample_wavelength": (3e-6, 1e-5), "srgb_model_eval": (0, 3e-6), "regular_eval": (0, 2e-7), "irregular_eval": (0, 2e-7),
+    "spectrum_to_xyz": (1e-6, 3e-7),
 }
 
 
