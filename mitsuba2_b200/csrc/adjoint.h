@@ -1,0 +1,347 @@
+// adjoint.h -- vertex-position adjoint of the path tracer (HD bodies).
+//
+// What the reference does: src/python/python/autodiff.py:6-194 records the whole render on the Enoki tape
+// (ext/enoki/src/autodiff/autodiff.cpp:838-988) and back-propagates through it; vertex positions are exposed by
+// Mesh::traverse / parameters_changed (src/librender/mesh.cpp:781-804).  `pathreparam` is not in the tree.
+// What this file does instead (no tape, O(pool) memory), in the wavefront replay of grad.cuh:
+//
+//   dI/dv = interior term + primary-visibility boundary term.
+//
+// * Interior term.  The pixel sample keeps its film position (x1 = camera ray ∩ moving triangle slides along the ray);
+//   every later vertex keeps its barycentric coordinates on the triangle it hit ("material" parameterisation), so the
+//   path integral is taken over triangle areas.  With sampling densities, MIS weights and Russian roulette detached
+//   (they are functions of the material coordinates only), a path's radiance is a sum of products of LOCAL factors
+//       S_k = f_s(x_{k-1}, x_k, x_{k+1}) * |N_{k+1} . D| / (2 |D|^3),     D = x_{k+1} - x_k,  N = e1 x e2 (unnormalised),
+//   (BSDF value incl. the shading cosine, times the geometry term incl. the triangle-area Jacobian), and
+//       dL/dv = sum_k (L - P_k) * dlog S_k/dv,
+//   where P_k is the radiance gathered before S_k is used -- the same bookkeeping as texture_adjoint() in path.h, so
+//   the replay only needs the two previous vertices of a path (PathQueue::prev1/prev2).  dlog f_s is evaluated with
+//   forward-mode dual numbers over (wi, wo); everything else is closed form.
+// * Boundary term (edge_* bodies): Reynolds transport over the film plane.  Mesh edges are sampled proportionally to
+//   their projected length, the radiance on both sides of the edge is path-traced with common random numbers, and
+//   (L+ - L-) * dL/dI(pixel) * d(alpha)/dv is scattered to the two edge vertices (Li et al. 2018, primary visibility).
+//   Every edge is a candidate, so shading discontinuities of flat-shaded meshes are covered as well as silhouettes.
+// Not covered (documented in DESIGN.md): visibility changes seen from secondary vertices (moving shadow boundaries and
+// indirect occlusion), paths beyond a delta (dielectric) vertex, texture-coordinate sliding at x1, emitter meshes.
+#pragma once
+#include "path.h"
+
+namespace mtsb {
+
+// ---- forward-mode dual numbers over N inputs ------------------------------------------------------------------------
+template <int N> struct Dual { float v; float d[N]; };
+template <int N> HD Dual<N> dconst(float v) { Dual<N> r; r.v = v; for (int i = 0; i < N; ++i) r.d[i] = 0.f; return r; }
+template <int N> HD Dual<N> dvar(float v, int k) { Dual<N> r = dconst<N>(v); r.d[k] = 1.f; return r; }
+template <int N> HD Dual<N> operator+(Dual<N> a, Dual<N> b) { a.v += b.v; for (int i = 0; i < N; ++i) a.d[i] += b.d[i]; return a; }
+template <int N> HD Dual<N> operator-(Dual<N> a, Dual<N> b) { a.v -= b.v; for (int i = 0; i < N; ++i) a.d[i] -= b.d[i]; return a; }
+template <int N> HD Dual<N> operator-(Dual<N> a) { a.v = -a.v; for (int i = 0; i < N; ++i) a.d[i] = -a.d[i]; return a; }
+template <int N> HD Dual<N> operator*(Dual<N> a, Dual<N> b) { Dual<N> r; r.v = a.v * b.v; for (int i = 0; i < N; ++i) r.d[i] = a.d[i] * b.v + a.v * b.d[i]; return r; }
+template <int N> HD Dual<N> operator/(Dual<N> a, Dual<N> b) {
+    Dual<N> r; float inv = 1.f / b.v; r.v = a.v * inv;
+    for (int i = 0; i < N; ++i) r.d[i] = (a.d[i] - r.v * b.d[i]) * inv;
+    return r;
+}
+template <int N> HD Dual<N> operator+(Dual<N> a, float b) { a.v += b; return a; }
+template <int N> HD Dual<N> operator+(float b, Dual<N> a) { a.v += b; return a; }
+template <int N> HD Dual<N> operator-(Dual<N> a, float b) { a.v -= b; return a; }
+template <int N> HD Dual<N> operator-(float b, Dual<N> a) { return -a + b; }
+template <int N> HD Dual<N> operator*(Dual<N> a, float b) { a.v *= b; for (int i = 0; i < N; ++i) a.d[i] *= b; return a; }
+template <int N> HD Dual<N> operator*(float b, Dual<N> a) { return a * b; }
+template <int N> HD Dual<N> operator/(Dual<N> a, float b) { return a * (1.f / b); }
+template <int N> HD Dual<N> operator/(float b, Dual<N> a) { return dconst<N>(b) / a; }
+template <int N> HD Dual<N> dsqr(Dual<N> a) { return a * a; }
+template <int N> HD Dual<N> dsqrt(Dual<N> a) {          // safe_sqrt: clamps at 0 with a zero derivative
+    if (!(a.v > 0.f)) return dconst<N>(0.f);
+    Dual<N> r; r.v = sqrtf(a.v); float h = 0.5f / r.v; for (int i = 0; i < N; ++i) r.d[i] = a.d[i] * h; return r;
+}
+template <int N> HD Dual<N> dexp(Dual<N> a) { Dual<N> r; r.v = expf(a.v); for (int i = 0; i < N; ++i) r.d[i] = a.d[i] * r.v; return r; }
+
+typedef Dual<6> D6;      // inputs: wi.xyz (0..2), wo.xyz (3..5), both in the local shading frame
+
+// MicrofacetDistribution::smith_g1 (include/mitsuba/render/microfacet.h:289-321), same branches as Microfacet::smith_g1
+HD D6 rc_smith_g1(const D6 v[3], D6 dot_vm, float au, float av, int type) {
+    D6 xy2 = dsqr(v[0] * au) + dsqr(v[1] * av);
+    if (xy2.v == 0.f) return dconst<6>(1.f);
+    if (dot_vm.v * v[2].v <= 0.f) return dconst<6>(0.f);
+    D6 tan2 = xy2 / dsqr(v[2]);
+    if (type == 0) {
+        D6 a = 1.f / dsqrt(tan2);
+        if (a.v >= 1.6f) return dconst<6>(1.f);
+        D6 a2 = a * a;
+        return (3.535f * a + 2.181f * a2) / (1.f + 2.276f * a + 2.577f * a2);
+    }
+    return 2.f / (1.f + dsqrt(1.f + tan2));
+}
+// fresnel_conductor (include/mitsuba/render/fresnel.h:92-116) on dual numbers
+HD D6 rc_fresnel_conductor(D6 cos_i, float eta_r, float eta_i) {
+    D6 c2 = cos_i * cos_i, s2 = 1.f - c2, s4 = s2 * s2;
+    D6 temp_1 = (eta_r * eta_r - eta_i * eta_i) - s2;
+    D6 a2pb2 = dsqrt(temp_1 * temp_1 + 4.f * eta_i * eta_i * eta_r * eta_r);
+    D6 a = dsqrt(0.5f * (a2pb2 + temp_1));
+    D6 term_1 = a2pb2 + c2, term_2 = 2.f * cos_i * a;
+    D6 r_s = (term_1 - term_2) / (term_1 + term_2);
+    D6 term_3 = a2pb2 * c2 + s4, term_4 = term_2 * s2;
+    D6 r_p = r_s * (term_3 - term_4) / (term_3 + term_4);
+    return 0.5f * (r_s + r_p);
+}
+
+// sum_c w_c * dlog f_c / d(wi, wo) for the smooth BSDFs, f = BSDF value * cos(wo) as BSDF::eval returns it
+// (src/bsdfs/diffuse.cpp:105-121, src/bsdfs/roughconductor.cpp:278-340, twosided.cpp:144-170).  false: f = 0.
+HD bool bsdf_log_grad(const SceneDev &sc, const BsdfDev &b, float u, float v, float3 wi, float3 wo, float3 w,
+                      float3 &g_wi, float3 &g_wo) {
+    g_wi = mk3(0.f); g_wo = mk3(0.f);
+    bool back = b.two_sided && wi.z < 0.f;
+    if (back) { wi.z = -wi.z; wo.z = -wo.z; }
+    if (!(wi.z > 0.f && wo.z > 0.f)) return false;
+    float q = w.x + w.y + w.z;
+    if (b.type == 0) {
+        g_wo.z = q / wo.z;
+    } else if (b.type == 1) {
+        D6 i[3] = { dvar<6>(wi.x, 0), dvar<6>(wi.y, 1), dvar<6>(wi.z, 2) }, o[3] = { dvar<6>(wo.x, 3), dvar<6>(wo.y, 4), dvar<6>(wo.z, 5) };
+        D6 h[3] = { i[0] + o[0], i[1] + o[1], i[2] + o[2] };
+        D6 inv = 1.f / dsqrt(dsqr(h[0]) + dsqr(h[1]) + dsqr(h[2]));
+        for (int k = 0; k < 3; ++k) h[k] = h[k] * inv;
+        float au = fmaxf(b.alpha_u, 1e-4f), av = fmaxf(b.alpha_v, 1e-4f);
+        D6 ct2 = dsqr(h[2]), D;
+        if (b.distr == 0) D = dexp(-(dsqr(h[0] / au) + dsqr(h[1] / av)) / ct2) / (kPi * au * av * dsqr(ct2));
+        else D = 1.f / (kPi * au * av * dsqr(dsqr(h[0] / au) + dsqr(h[1] / av) + ct2));
+        if (!(D.v * h[2].v > 1e-20f)) return false;
+        D6 cih = i[0] * h[0] + i[1] * h[1] + i[2] * h[2], coh = o[0] * h[0] + o[1] * h[1] + o[2] * h[2];
+        D6 res = D * rc_smith_g1(i, cih, au, av, b.distr) * rc_smith_g1(o, coh, au, av, b.distr) / (4.f * i[2]);
+        if (!(res.v > 0.f)) return false;
+        float3 eta = tex_eval(sc, b.eta, u, v), k = tex_eval(sc, b.k, u, v);
+        float etas[3] = { eta.x, eta.y, eta.z }, ks[3] = { k.x, k.y, k.z }, ws[3] = { w.x, w.y, w.z };
+        float acc[6]; float rinv = 1.f / res.v;
+        for (int j = 0; j < 6; ++j) acc[j] = q * res.d[j] * rinv;
+        for (int c = 0; c < 3; ++c) {
+            if (ws[c] == 0.f) continue;
+            D6 F = rc_fresnel_conductor(cih, etas[c], ks[c]);
+            if (!(F.v > 0.f)) continue;
+            float s = ws[c] / F.v;
+            for (int j = 0; j < 6; ++j) acc[j] += s * F.d[j];
+        }
+        g_wi = mk3(acc[0], acc[1], acc[2]); g_wo = mk3(acc[3], acc[4], acc[5]);
+    } else
+        return false;
+    if (back) { g_wi.z = -g_wi.z; g_wo.z = -g_wo.z; }
+    return true;
+}
+
+// ---- geometry helpers -------------------------------------------------------------------------------------------------
+struct VtxRec { uint32_t prim; float b1, b2; };           // a path vertex: triangle + barycentrics; prim ~0 = the camera
+HD VtxRec vtx_rec(float4 r) { VtxRec v; v.prim = f2u(r.x) & kPrimMask; if (f2u(r.x) == 0xffffffffu) v.prim = 0xffffffffu; v.b1 = r.y; v.b2 = r.z; return v; }
+struct TriGeo { uint32_t i0, i1, i2; int mesh; float3 p0, e1, e2, N; };
+HD TriGeo tri_geo(const SceneDev &sc, uint32_t prim) {
+    TriGeo t; uint4 f = sc.faces[prim];
+    t.i0 = f.x; t.i1 = f.y; t.i2 = f.z; t.mesh = (int) f.w;
+    t.p0 = ld3(sc.pos, f.x); t.e1 = ld3(sc.pos, f.y) - t.p0; t.e2 = ld3(sc.pos, f.z) - t.p0;
+    t.N = cross(t.e1, t.e2);
+    return t;
+}
+HD float3 tri_point(const TriGeo &t, const VtxRec &r) { return t.p0 + t.e1 * r.b1 + t.e2 * r.b2; }
+
+template <typename Add> HD void add_vertex(const GradCtx &g, uint32_t vi, float3 v, Add add) {
+    uint32_t k = vi - g.vert_begin;
+    if (k < g.vert_count) { add(g.grad_pos + 3 * (size_t) k, v.x); add(g.grad_pos + 3 * (size_t) k + 1, v.y); add(g.grad_pos + 3 * (size_t) k + 2, v.z); }
+}
+// adjoint of a path-vertex position.  Attached vertex: x = sum b_i v_i.  Primary vertex: x = o + t d slides along the camera
+// ray, dx = d (N . sum b_i dv_i) / (N . d).
+template <typename Add>
+HD void scatter_point(const GradCtx &g, const TriGeo &t, const VtxRec &r, bool primary, float3 x, float3 gx, Add add) {
+    if (t.mesh != g.mesh_id) return;
+    if (primary) {
+        float3 d = x - g.cam_o; float dn = dot(d, t.N);
+        if (!(fabsf(dn) > 1e-20f)) return;
+        gx = t.N * (dot(d, gx) / dn);
+    }
+    add_vertex(g, t.i0, gx * (1.f - r.b1 - r.b2), add); add_vertex(g, t.i1, gx * r.b1, add); add_vertex(g, t.i2, gx * r.b2, add);
+}
+// adjoint of the unnormalised normal N = e1 x e2
+template <typename Add> HD void scatter_normal(const GradCtx &g, const TriGeo &t, float3 gN, Add add) {
+    if (t.mesh != g.mesh_id) return;
+    float3 ge1 = cross(t.e2, gN), ge2 = cross(gN, t.e1);
+    add_vertex(g, t.i1, ge1, add); add_vertex(g, t.i2, ge2, add); add_vertex(g, t.i0, -(ge1 + ge2), add);
+}
+
+// ---- one local factor S = f_s(A, B, C) * G~(B, C) --------------------------------------------------------------------
+enum { kEndSurface = 0, kEndDirection = 1, kEndFixedArea = 2, kEndFixedPoint = 3 };
+// A = previous vertex (position xA; recA.prim ~0: camera), B = the vertex whose BSDF is used (siB reconstructed by
+// make_si), C = what the outgoing direction ends on: an attached surface point (xC, recC), a fixed direction (xC holds
+// it; environment), a fixed point with normal nC on an emitter that is not differentiated, or a fixed point light.
+// w = per-channel weight dL/dI * (radiance carried through this factor).
+template <typename Add>
+HD void vertex_triple(const SceneDev &sc, const GradCtx &g, float3 xA, VtxRec recA, bool A_primary, const SI &siB, VtxRec recB,
+                      bool B_primary, int kindC, float3 xC, VtxRec recC, float3 nC, float3 w, Add add) {
+    if (w.x == 0.f && w.y == 0.f && w.z == 0.f) return;
+    const BsdfDev bsdf = sc.bsdfs[sc.meshes[siB.mesh].bsdf];
+    float3 din = xA - siB.p; float rin = norm(din);
+    if (!(rin > 0.f)) return;
+    float3 win = din / rin, dout = mk3(0.f), wout = xC; float rout = 1.f;
+    if (kindC != kEndDirection) { dout = xC - siB.p; rout = norm(dout); if (!(rout > 0.f)) return; wout = dout / rout; }
+    float3 wi = siB.sh.to_local(win), wo = siB.sh.to_local(wout), g_wi, g_wo;
+    if (!bsdf_log_grad(sc, bsdf, siB.u, siB.v, wi, wo, w, g_wi, g_wo)) return;
+    float q = w.x + w.y + w.z;
+    float3 n = siB.sh.n;
+    float3 g_win = siB.sh.to_world(g_wi), g_wout = siB.sh.to_world(g_wo);
+    // shading normal; the tangents follow it rigidly (exact for isotropic BSDFs): ds = -n (s . dn), dt = -n (t . dn)
+    float3 g_n = win * g_wi.z + wout * g_wo.z - (siB.sh.s * g_wi.x + siB.sh.t * g_wi.y) * dot(n, win)
+                                              - (siB.sh.s * g_wo.x + siB.sh.t * g_wo.y) * dot(n, wout);
+    float3 g_din = (g_win - win * dot(win, g_win)) / rin, g_dout = mk3(0.f);
+    if (kindC != kEndDirection) g_dout = (g_wout - wout * dot(wout, g_wout)) / rout;
+    TriGeo tC; float3 g_NC = mk3(0.f);
+    if (kindC == kEndSurface) {
+        tC = tri_geo(sc, recC.prim);
+        float nd = dot(tC.N, dout);
+        if (fabsf(nd) > 1e-20f) { g_dout += (tC.N * (1.f / nd) - dout * (3.f / (rout * rout))) * q; g_NC = dout * (q / nd); }
+    } else if (kindC == kEndFixedArea) {
+        float nd = dot(nC, dout);
+        if (fabsf(nd) > 1e-20f) g_dout += (nC * (1.f / nd) - dout * (3.f / (rout * rout))) * q;
+    } else if (kindC == kEndFixedPoint)
+        g_dout += dout * (-2.f * q / (rout * rout));
+    // scatter
+    if (recA.prim != 0xffffffffu) { TriGeo tA = tri_geo(sc, recA.prim); scatter_point(g, tA, recA, A_primary, xA, g_din, add); }
+    TriGeo tB = tri_geo(sc, recB.prim);
+    scatter_point(g, tB, recB, B_primary, siB.p, -(g_din + g_dout), add);
+    float lN = norm(tB.N);
+    if (lN > 0.f) {
+        // dn_g = P dN / |N|; the shading normal turns with the face: dn_s = (n_g x dn_g) x n_s (= dn_g for flat shading)
+        float3 ng = tB.N / lN;
+        float3 g_ng = g_n * dot(ng, n) - n * dot(g_n, ng);
+        scatter_normal(g, tB, (g_ng - ng * dot(ng, g_ng)) / lN, add);
+    }
+    if (kindC == kEndSurface) { scatter_point(g, tC, recC, false, xC, g_dout, add); scatter_normal(g, tC, g_NC, add); }
+}
+
+// ---- replay hooks (plugged into shade_body, path.h) ----------------------------------------------------------------
+// Add = functor (float *dst, float v) accumulating into a gradient buffer (atomicAdd on the device).
+template <typename Add, bool Vtx = true> struct ReplayGrad {
+    static constexpr bool kVertex = Vtx;
+    GradCtx g; Add add;
+    HD float3 weight(const RenderBatch &b, uint32_t path_id, float3 radiance) const {
+        uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
+        return ld3(g.dL_dimage, pixel) * radiance * g.scale;
+    }
+    // factor S_{k-1} = f_s(x_{k-2}, x_{k-1}, x_k) G~(x_{k-1}, x_k), complete now that x_k (or a miss) is known
+    HD void on_vertex(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, uint32_t path_id, uint32_t depth,
+                      float3 o, float3 d, const SI &si) const {
+        if (g.grad_pos == nullptr || depth < 2) return;
+        float4 fin = g.final_radiance[path_id], run = b.result[path_id];
+        float3 w = weight(b, path_id, mk3(fin.x - run.x, fin.y - run.y, fin.z - run.z));
+        VtxRec recB = vtx_rec(q.prev1[i]), recA = vtx_rec(q.prev2[i]), recC; recC.prim = si.prim; recC.b1 = si.u; recC.b2 = si.v;
+        float3 xA = g.cam_o;
+        if (recA.prim != 0xffffffffu) xA = tri_point(tri_geo(sc, recA.prim), recA);
+        SI siB = make_si(sc, xA, mk3(0.f, 0.f, 1.f), make_float4(1.f, recB.b1, recB.b2, u2f(recB.prim)));
+        if (si.valid) {
+            float4 h = q.hit[i]; recC.b1 = h.y; recC.b2 = h.z;
+            vertex_triple(sc, g, xA, recA, depth == 3, siB, recB, depth == 2, kEndSurface, si.p, recC, mk3(0.f), w, add);
+        } else
+            vertex_triple(sc, g, xA, recA, depth == 3, siB, recB, depth == 2, kEndDirection, d, recC, mk3(0.f), w, add);
+        (void) o;
+    }
+    HD void on_bsdf(const SceneDev &sc, const RenderBatch &b, uint32_t path_id, const SI &si, const BsdfDev &bsdf) const {
+        if (g.grad_tex != nullptr) texture_adjoint(sc, b, g, path_id, si, bsdf, add);
+    }
+    // emitter sample at x_k: factor f_s(x_{k-1}, x_k, y) G~(x_k, y), weighted by the sample's own contribution when
+    // the shadow ray is free (tested here; the primal k_shadow pass adds the contribution itself)
+    template <typename DS>
+    HD void on_nee(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, uint32_t path_id, uint32_t depth,
+                   const SI &si, const DS &ds, float3 c) const {
+        if (g.grad_pos == nullptr) return;
+        uint2 fast[8]; TravStack<8, 56> st; st.fast = fast; st.stride = 1; Hit h;
+        if (bvh_trace<true>(sc.bvh, si.p, ds.d, kRayEpsilon * (1.f + hmax(abs3(si.p))), ds.dist * (1.f - kShadowEpsilon), st, h)) return;
+        VtxRec recA; recA.prim = 0xffffffffu; recA.b1 = recA.b2 = 0.f;
+        float3 xA = g.cam_o;
+        if (depth > 1) { recA = vtx_rec(q.prev1[i]); xA = tri_point(tri_geo(sc, recA.prim), recA); }
+        float4 hc = q.hit[i];
+        VtxRec recB; recB.prim = si.prim; recB.b1 = hc.y; recB.b2 = hc.z;
+        // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point
+        int kind = ds.etype == 0 ? kEndFixedArea : (ds.etype == 3 ? kEndFixedPoint : kEndDirection);
+        float3 xC = kind == kEndDirection ? ds.d : ds.p;
+        vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recB, ds.n, weight(b, path_id, c), add);
+    }
+};
+
+// ---- boundary term: edge sampling on the film plane ---------------------------------------------------------------
+struct EdgeCtx {
+    const uint2 *edges; uint32_t n_edges;   // unique edges of the differentiated mesh (scene-global vertex indices)
+    const float *cdf;                       // inclusive prefix sum of the projected edge lengths (pixels)
+    float total_len;
+    float w2s[16];                          // world -> sample space (x, y in [0,1]^2 after the divide by w), row-major
+    uint32_t width, height;
+    uint64_t seed; uint64_t first;          // global index of this call's first boundary sample
+    float weight;                           // 1 / (boundary samples of the whole job)
+    float eps;                              // half distance (pixels) between the two radiance samples
+};
+HD bool edge_project(const EdgeCtx &e, float3 v, float &x, float &y, float &hw) {
+    const float *m = e.w2s;
+    float hx = m[0] * v.x + m[1] * v.y + m[2] * v.z + m[3], hy = m[4] * v.x + m[5] * v.y + m[6] * v.z + m[7];
+    hw = m[12] * v.x + m[13] * v.y + m[14] * v.z + m[15];
+    if (!(hw > 1e-6f)) return false;
+    x = hx / hw * (float) e.width; y = hy / hw * (float) e.height;
+    return true;
+}
+HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, uint32_t k) {
+    uint2 ed = e.edges[k]; float ax, ay, aw, bx, by, bw;
+    if (!edge_project(e, ld3(sc.pos, ed.x), ax, ay, aw) || !edge_project(e, ld3(sc.pos, ed.y), bx, by, bw)) return 0.f;
+    float l = sqrtf(sqr(ax - bx) + sqr(ay - by));
+    return l < 1e30f ? l : 0.f;
+}
+struct EdgeSample { uint32_t edge; float t, px, py, nx, ny, len; float3 va, vb; bool valid; Pcg32 rng; };
+HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j) {
+    EdgeSample s; s.valid = false; s.edge = 0; s.t = 0.f; s.px = s.py = s.nx = s.ny = s.len = 0.f; s.va = s.vb = mk3(0.f);
+    s.rng = sampler_seed(e.seed ^ 0x9e3779b97f4a7c15ull, (uint32_t) (e.first + j));
+    float u1 = s.rng.next_f32(), u2 = s.rng.next_f32(); (void) s.rng.next_f32();
+    if (!(e.total_len > 0.f) || e.n_edges == 0) return s;
+    float value = u1 * e.total_len; const float *cdf = e.cdf;
+    s.edge = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
+    uint2 ed = e.edges[s.edge];
+    s.va = ld3(sc.pos, ed.x); s.vb = ld3(sc.pos, ed.y);
+    float ax, ay, aw, bx, by, bw;
+    if (!edge_project(e, s.va, ax, ay, aw) || !edge_project(e, s.vb, bx, by, bw)) return s;
+    s.len = sqrtf(sqr(ax - bx) + sqr(ay - by));
+    if (!(s.len > 0.f)) return s;
+    s.t = u2; s.px = ax + u2 * (bx - ax); s.py = ay + u2 * (by - ay);
+    s.nx = (ay - by) / s.len; s.ny = (bx - ax) / s.len;            // grad_xy(alpha) / |grad_xy(alpha)|
+    s.valid = s.px >= 0.f && s.py >= 0.f && s.px < (float) e.width && s.py < (float) e.height;
+    return s;
+}
+// two primary rays per boundary sample: 2j on the alpha > 0 side, 2j+1 on the other, same random-number stream
+HD void edge_raygen_body(const SceneDev &sc, const SensorDev &sn, const EdgeCtx &e, const RenderBatch &b, const PathQueue &q, uint32_t j) {
+    EdgeSample s = edge_sample(sc, e, j);
+    if (!s.valid) { s.px = 0.5f * (float) e.width; s.py = 0.5f * (float) e.height; s.nx = 1.f; s.ny = 0.f; }
+    for (uint32_t side = 0; side < 2; ++side) {
+        uint32_t i = 2 * j + side; float sg = side == 0 ? e.eps : -e.eps;
+        float4 o, d;
+        sensor_sample_ray(sn, (s.px + sg * s.nx) / (float) sn.width, (s.py + sg * s.ny) / (float) sn.height, o, d);
+        q.o_mint[i] = o; q.d_maxt[i] = d; q.thr_eta[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+        q.misc[i] = make_uint4(i, 1u, f2u(0.f), 0u);
+        rng_store(&q.rng[i], s.rng);
+        b.result[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+// dPhi = (1/N) sum  dL/dI(pixel) . (L+ - L-) * grad_v(alpha) * total_len / len,  alpha = edge function through a, b
+template <typename Add>
+HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g, const float4 *result, uint32_t j, Add add) {
+    EdgeSample s = edge_sample(sc, e, j);
+    if (!s.valid) return;
+    float4 lp = result[2 * j], lm = result[2 * j + 1];
+    uint32_t pixel = (uint32_t) s.py * e.width + (uint32_t) s.px;
+    float3 dI = ld3(g.dL_dimage, pixel);
+    float sc_ = (dI.x * (lp.x - lm.x) + dI.y * (lp.y - lm.y) + dI.z * (lp.z - lm.z)) * e.weight * e.total_len;
+    if (sc_ == 0.f || !(fabsf(sc_) < 1e30f)) return;
+    // grad_a(alpha) = -(1 - t) len n, grad_b(alpha) = -t len n; the 1/len of the edge pick cancels len
+    uint2 ed = e.edges[s.edge];
+    const float *m = e.w2s;
+    for (int k = 0; k < 2; ++k) {
+        float3 v = k == 0 ? s.va : s.vb; float wgt = -(k == 0 ? 1.f - s.t : s.t) * sc_;
+        float gx = wgt * s.nx, gy = wgt * s.ny, x, y, hw;
+        edge_project(e, v, x, y, hw);
+        float sx = x / (float) e.width, sy = y / (float) e.height, W = (float) e.width / hw, H = (float) e.height / hw;
+        float3 gv = mk3(gx * W * (m[0] - sx * m[12]) + gy * H * (m[4] - sy * m[12]),
+                        gx * W * (m[1] - sx * m[13]) + gy * H * (m[5] - sy * m[13]),
+                        gx * W * (m[2] - sx * m[14]) + gy * H * (m[6] - sy * m[14]));
+        add_vertex(g, k == 0 ? ed.x : ed.y, gv, add);
+    }
+}
+
+} // namespace mtsb

@@ -7,6 +7,9 @@
 #include <cub/cub.cuh>
 #include <string>
 #include <vector>
+#include <map>
+#include <algorithm>
+#include <cmath>
 #include <memory>
 #include <cstring>
 #include <cstdio>
@@ -92,6 +95,9 @@ struct mtsb_scene {
     DevBuf<uint8_t> prim_class;              // per primitive: 1 + BSDF type (shade class), see k_classify
     DevBuf<uint32_t> class_lists;            // material bins of the shade stage: kShadeClasses x pool queue indices
     DevBuf<uint4> q_misc[2], q_rng[2];
+    DevBuf<float4> q_p1[2], q_p2[2];         // vertex-gradient replay: previous two path vertices per queue entry
+    std::map<int, std::unique_ptr<DevBuf<uint2>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
+    int grad_boundary = 1; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;
     float3 bbox_lo, bbox_hi;
@@ -564,12 +570,14 @@ static int ensure_pool(mtsb_scene *s, uint32_t n) {
 }
 static PathQueue make_queue(mtsb_scene *s, int k) {
     PathQueue q; q.o_mint = s->q_o[k].p; q.d_maxt = s->q_d[k].p; q.hit = s->q_hit[k].p; q.thr_eta = s->q_te[k].p;
-    q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; q.wav_eta = s->q_we[k].p; return q;
+    q.misc = s->q_misc[k].p; q.rng = s->q_rng[k].p; q.wav_eta = s->q_we[k].p; q.prev1 = s->q_p1[k].p; q.prev2 = s->q_p2[k].p; return q;
 }
 
 // One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
 // (k_shade_grad scatters texel gradients); `splat` adds the finished paths to the film.
-static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches) {
+struct EdgeLaunch { EdgeCtx e; const float *total_len; };     // primary rays come from edge samples instead of the film
+static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches,
+                     const EdgeLaunch *edge = nullptr) {
     cudaStream_t st = s->ctx->stream;
     const uint32_t n = b.n_paths;
     ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
@@ -578,13 +586,16 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
     int cur = 0;
     const unsigned tg = trace_grid_for(s->ctx, n);
+    if (edge) { StageTimer t(s->ctx, ST_RAYGEN); k_edge_raygen<<<grid_for(n / 2), kBlock, 0, st>>>(s->dev, sn, edge->e, edge->total_len, b, make_queue(s, cur), s->counters.p); launches++; }
+    else
     { StageTimer t(s->ctx, ST_RAYGEN); if (s->spectral) k_raygen<Spectral><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p);
       else k_raygen<Rgb><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
     for (int depth = 1; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
         { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE);
-          if (grad) k_shade_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+          if (grad && grad->grad_pos) k_shade_grad<true><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+          else if (grad) k_shade_grad<false><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
           else if (depth == 1 || !s->ctx->bin_materials) {      // primary hits are already coherent: identity lists
               ShadeBins bins; bins.lists = nullptr; bins.counts = s->counters.p + depth; bins.pool = 0;
               if (s->spectral) k_shade<Spectral><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);

@@ -4,7 +4,7 @@
 
 namespace mtsb {
 
-template <typename M> struct DirSampleT { float3 p, n, d; float dist, pdf; typename M::Spec value; bool delta; };
+template <typename M> struct DirSampleT { float3 p, n, d; float dist, pdf; typename M::Spec value; bool delta; int etype; /* EmitterDev::type */ };
 typedef DirSampleT<Rgb> DirSample;
 
 // radiance (area, constant) / intensity (point) of an emitter: an rgb triple, or in spectral mode a texture
@@ -197,7 +197,7 @@ HD DirSampleT<M> point_sample_direction(const SceneDev &sc, const EmitterDev &e,
 
 template <typename M = Rgb>
 HD DirSampleT<M> sample_emitter_direction(const SceneDev &sc, float3 ref_p, float sx, float sy, float4 wav = float4()) {
-    DirSampleT<M> ds; ds.delta = false; ds.pdf = 0.f; ds.value = M::splat(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
+    DirSampleT<M> ds; ds.delta = false; ds.etype = 0; ds.pdf = 0.f; ds.value = M::splat(0.f); ds.d = mk3(0.f); ds.dist = 0.f; ds.p = ds.n = mk3(0.f);
     if (sc.n_emitters == 0) return ds;
     uint32_t index = 0; float epdf = 1.f;
     if (sc.n_emitters > 1) {
@@ -211,7 +211,7 @@ HD DirSampleT<M> sample_emitter_direction(const SceneDev &sc, float3 ref_p, floa
     else if (e.type == 1) ds = env_sample_direction<M>(sc, e, ref_p, sx, sy, wav);
     else if (e.type == 2) ds = constant_sample_direction<M>(sc, e, ref_p, sx, sy, wav);
     else ds = point_sample_direction<M>(sc, e, ref_p, wav);
-    ds.delta = e.type == 3;
+    ds.delta = e.type == 3; ds.etype = e.type;
     if (sc.n_emitters > 1) { ds.pdf *= epdf; ds.value *= 1.f / epdf; }
     return ds;
 }

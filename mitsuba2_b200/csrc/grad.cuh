@@ -1,8 +1,10 @@
 // grad.cuh -- adjoint pass entry point (included at the end of api.cu).
 //
-// mtsb_render_grad = the backward pass of mtsb_render for one bitmap texture (see texture_adjoint() in path.h).
+// mtsb_render_grad = the backward pass of mtsb_render for one bitmap texture (texture_adjoint() in path.h) and / or the
+// vertex positions of one mesh (adjoint.h).
 // Per batch: (1) primal wavefront without the splat -> per-path final radiance; (2) replay with identical RNG streams,
-// k_shade_grad scatters dL/dtexel with float atomics.  Memory is O(pool), independent of spp and path length, unlike the
+// k_shade_grad scatters dL/dtexel and the interior term of dL/dvertex with float atomics.  Vertex gradients then add the
+// primary-visibility boundary term: edges sampled by projected length, two paths per edge sample (k_edge_*).  Memory is O(pool), independent of spp and path length, unlike the
 // reference's tape (src/python/python/autodiff.py:6-194, ext/enoki/src/autodiff/autodiff.cpp:838-988).
 #pragma once
 
@@ -11,16 +13,69 @@ __global__ void k_axpy(size_t n, const float *__restrict__ x, float *__restrict_
     if (i < n) y[i] += x[i];
 }
 
+
+// row-major 4x4 inverse (double), for world -> sample space of a sensor
+static void invert4(const float *m, double *out) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = m[4 * r + c]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int c = 0; c < 4; ++c) {
+        int piv = c; for (int r = c + 1; r < 4; ++r) if (fabs(a[r][c]) > fabs(a[piv][c])) piv = r;
+        for (int k = 0; k < 8; ++k) std::swap(a[c][k], a[piv][k]);
+        double inv = 1.0 / a[c][c]; for (int k = 0; k < 8; ++k) a[c][k] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != c) { double f = a[r][c]; for (int k = 0; k < 8; ++k) a[r][k] -= f * a[c][k]; }
+    }
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out[4 * r + c] = a[r][4 + c];
+}
+// unique edges of a mesh in scene-global vertex indices (host sort once per mesh; the list is topology, not positions)
+static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint2 **edges, uint32_t *n_edges) {
+    auto it = s->mesh_edges.find(mesh_id);
+    if (it == s->mesh_edges.end()) {
+        const MeshDev &m = s->meshes[mesh_id];
+        const std::vector<uint32_t> &f = s->mesh_faces[mesh_id];
+        std::vector<uint64_t> keys; keys.reserve(f.size());
+        for (size_t t = 0; t + 2 < f.size(); t += 3)
+            for (int k = 0; k < 3; ++k) {
+                uint32_t a = f[t + k] + m.vert_begin, c = f[t + (k + 1) % 3] + m.vert_begin;
+                if (a > c) std::swap(a, c);
+                keys.push_back(((uint64_t) a << 32) | c);
+            }
+        std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+        std::vector<uint2> e(keys.size());
+        for (size_t k = 0; k < keys.size(); ++k) e[k] = make_uint2((uint32_t) (keys[k] >> 32), (uint32_t) keys[k]);
+        std::unique_ptr<DevBuf<uint2>> buf(new DevBuf<uint2>());
+        CU(buf->upload(e.data(), e.size(), s->ctx->stream));
+        CU(cudaStreamSynchronize(s->ctx->stream));
+        it = s->mesh_edges.emplace(mesh_id, std::move(buf)).first;
+    }
+    *edges = it->second->p; *n_edges = (uint32_t) it->second->n;
+    return MTSB_OK;
+}
+
+/* boundary: 0 = interior term only, 1 = + primary-visibility edge sampling; edge_fraction = edge samples per path sample */
+extern "C" int mtsb_grad_config(mtsb_scene *s, int boundary, float edge_fraction) {
+    CHECK_ARG(s && edge_fraction >= 0.f && edge_fraction <= 64.f);
+    s->grad_boundary = boundary; s->grad_edge_fraction = edge_fraction;
+    return MTSB_OK;
+}
+
 extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
                                 uint64_t seed, const float *dL_dimage, int32_t tex_id, float *grad_texture, int32_t mesh_id,
                                 float *grad_vertices, int mem, mtsb_stats *stats) {
     CHECK_ARG(s && sensor_id < s->sensors.size() && spp_count > 0 && spp_begin + spp_count <= spp_total && dL_dimage);
-    if (grad_vertices || mesh_id >= 0)
-        return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex-position gradients are not implemented (texture gradients only)");
-    CHECK_ARG(grad_texture && tex_id >= 0 && (size_t) tex_id < s->tex.size());
-    const TexDev td = s->tex[tex_id];
-    if (td.type != 1) return fail(MTSB_E_INVALID, "mtsb_render_grad: texture is not a bitmap");
+    CHECK_ARG(grad_texture || grad_vertices);
     if (s->spectral) return fail(MTSB_E_INVALID, "mtsb_render_grad: the adjoint pass is implemented for MTSB_MODE_RGB only");
+    size_t ntex = 0, nvert = 0;
+    if (grad_texture) {
+        CHECK_ARG(tex_id >= 0 && (size_t) tex_id < s->tex.size());
+        const TexDev td = s->tex[tex_id];
+        if (td.type != 1) return fail(MTSB_E_INVALID, "mtsb_render_grad: texture is not a bitmap");
+        ntex = (size_t) td.w * td.h * td.ch;
+    }
+    if (grad_vertices) {
+        CHECK_ARG(mesh_id >= 0 && (size_t) mesh_id < s->meshes.size());
+        if (s->meshes[mesh_id].emitter >= 0) return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex gradients of an emitter mesh are not supported");
+        nvert = 3 * (size_t) s->meshes[mesh_id].vert_count;
+    }
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;
@@ -29,16 +84,27 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
     if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");
     uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
+    if (grad_vertices && pool < 2) pool = 2;
     RC(ensure_pool(s, pool));
     CU(s->final_radiance.alloc(s->pool));
-    size_t ntex = (size_t) td.w * td.h * td.ch;
-    Staging sg; const float *d_dl; float *d_g = nullptr;
+    if (grad_vertices) for (int k = 0; k < 2; ++k) { CU(s->q_p1[k].alloc(s->pool)); CU(s->q_p2[k].alloc(s->pool)); }
+    Staging sg; const float *d_dl;
     RC(sg.in(dL_dimage, 3 * npix, mem, st, &d_dl));
-    DevBuf<float> gbuf;
-    if (mem == MTSB_MEM_DEVICE) d_g = grad_texture;
-    else { CU(gbuf.alloc(ntex)); d_g = gbuf.p; CU(cudaMemsetAsync(d_g, 0, ntex * sizeof(float), st)); }
-    GradCtx g; g.final_radiance = s->final_radiance.p; g.dL_dimage = d_dl; g.grad_tex = d_g; g.tex_id = tex_id;
+    DevBuf<float> gbuf, vbuf;
+    float *d_g = nullptr, *d_v = nullptr;
+    if (grad_texture) {
+        if (mem == MTSB_MEM_DEVICE) d_g = grad_texture;
+        else { CU(gbuf.alloc(ntex)); d_g = gbuf.p; CU(cudaMemsetAsync(d_g, 0, ntex * sizeof(float), st)); }
+    }
+    if (grad_vertices) {
+        if (mem == MTSB_MEM_DEVICE) d_v = grad_vertices;
+        else { CU(vbuf.alloc(nvert)); d_v = vbuf.p; CU(cudaMemsetAsync(d_v, 0, nvert * sizeof(float), st)); }
+    }
+    GradCtx g; g.final_radiance = s->final_radiance.p; g.dL_dimage = d_dl; g.grad_tex = d_g; g.tex_id = grad_texture ? tex_id : -1;
     g.scale = 1.f / (float) spp_total;
+    g.grad_pos = d_v; g.mesh_id = grad_vertices ? mesh_id : -1; g.vert_begin = g.vert_count = 0;
+    if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
+    g.cam_o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaEventRecord(s->ctx->ev0, st));
     uint64_t launches = 0;
@@ -51,20 +117,61 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         CU(cudaMemcpyAsync(s->final_radiance.p, s->result.p, (size_t) n * sizeof(float4), cudaMemcpyDeviceToDevice, st));
         RC(run_batch(s, sn, b, &g, false, launches));
     }
+    uint64_t edge_samples = 0;
+    if (grad_vertices && s->grad_boundary && s->grad_edge_fraction > 0.f) {
+        // ---- boundary term: sum over edge samples of dL/dI (L+ - L-) d(alpha)/dv (adjoint.h)
+        EdgeLaunch el; EdgeCtx &e = el.e;
+        RC(mesh_edge_list(s, mesh_id, &e.edges, &e.n_edges));
+        if (e.n_edges > 0) {
+            e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.02f; e.total_len = 0.f;
+            double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
+            DevBuf<float> len, cdf; DevBuf<uint8_t> tmp; size_t tmp_bytes = 0;
+            CU(len.alloc(e.n_edges)); CU(cdf.alloc(e.n_edges));
+            k_edge_len<<<grid_for(e.n_edges), kBlock, 0, st>>>(s->dev, e, len.p); launches++;
+            CU(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, len.p, cdf.p, (int) e.n_edges, st));
+            CU(tmp.alloc(tmp_bytes));
+            CU(cub::DeviceScan::InclusiveSum(tmp.p, tmp_bytes, len.p, cdf.p, (int) e.n_edges, st)); launches++;
+            e.cdf = cdf.p; el.total_len = cdf.p + (e.n_edges - 1);
+            double frac = s->grad_edge_fraction;
+            uint64_t nb_total = (uint64_t) ((double) npix * spp_total * frac); if (nb_total < 1) nb_total = 1;
+            uint64_t nb_first = (uint64_t) ((double) npix * spp_begin * frac), nb_end = (uint64_t) ((double) npix * (spp_begin + spp_count) * frac);
+            if (spp_begin + spp_count == spp_total) nb_end = nb_total;
+            e.weight = 1.f / (float) nb_total;
+            uint32_t half = s->pool / 2;
+            for (uint64_t off = nb_first; off < nb_end; off += half) {
+                if (s->ctx->cancel) { s->ctx->cancel = 0; cudaStreamSynchronize(st); return fail(MTSB_E_CANCELLED, "render cancelled"); }
+                uint32_t nb = (uint32_t) ((nb_end - off) < half ? (nb_end - off) : half);
+                e.first = off;
+                RenderBatch b; b.n_paths = 2 * nb; b.offset = 0; b.spp_begin = 0; b.spp_batch = 1; b.spp_total = 1; b.seed = seed; b.result = s->result.p;
+                RC(run_batch(s, sn, b, nullptr, false, launches, &el));
+                k_edge_scatter<<<grid_for(nb), kBlock, 0, st>>>(s->dev, e, el.total_len, g, s->result.p, nb); launches++;
+                edge_samples += nb;
+            }
+            CU(cudaStreamSynchronize(st));       // len / cdf / tmp are released at scope exit
+        }
+    }
     CU(cudaEventRecord(s->ctx->ev1, st));
     unsigned long long hs[4];
     CU(cudaMemcpyAsync(hs, s->dstats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
     if (mem != MTSB_MEM_DEVICE) {
-        std::vector<float> h(ntex);
-        CU(cudaMemcpyAsync(h.data(), d_g, ntex * sizeof(float), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-        for (size_t i = 0; i < ntex; ++i) grad_texture[i] += h[i];
+        std::vector<float> h(ntex > nvert ? ntex : nvert);
+        if (grad_texture) {
+            CU(cudaMemcpyAsync(h.data(), d_g, ntex * sizeof(float), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            for (size_t i = 0; i < ntex; ++i) grad_texture[i] += h[i];
+        }
+        if (grad_vertices) {
+            CU(cudaMemcpyAsync(h.data(), d_v, nvert * sizeof(float), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            for (size_t i = 0; i < nvert; ++i) grad_vertices[i] += h[i];
+        }
     }
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());
     if (stats) {
         memset(stats, 0, sizeof(*stats));
-        stats->samples = total; stats->closest_rays = hs[0]; stats->shadow_rays = hs[1]; stats->segments = hs[2];
+        stats->samples = total + 2 * edge_samples; stats->closest_rays = hs[0]; stats->shadow_rays = hs[1]; stats->segments = hs[2];
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
     }

@@ -1,6 +1,6 @@
 // kernels.cuh -- __global__ wrappers around the HD stage bodies (device only).
 #pragma once
-#include "path.h"
+#include "adjoint.h"
 
 namespace mtsb {
 
@@ -264,7 +264,10 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
     if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
 }
 
-// adjoint replay of k_shade: identical control flow, plus the texel-gradient scatter of texture_adjoint()
+// adjoint replay of k_shade: identical control flow, plus the texel-gradient scatter of texture_adjoint() and, with
+// Vtx, the vertex-position adjoint of adjoint.h (which carries the two previous path vertices through the queue)
+struct DevAdd { __device__ __forceinline__ void operator()(float *dst, float v) const { if (v != 0.f) atomicAdd(dst, v); } };
+template <bool Vtx>
 __global__ void __launch_bounds__(kBlock)
 k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
              unsigned long long *stats, uint32_t depth, GradCtx g) {
@@ -273,17 +276,31 @@ k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQu
     if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
     bool live = i < count;
     ShadeOut out; out.extend = false; out.shadow = false;
-    if (live)
-        out = shade_body(sc, qin, b, i, [&](const SceneDev &sc_, const RenderBatch &b_, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
-            texture_adjoint(sc_, b_, g, pid, si, bsdf, [](float *dst, float v) { if (v != 0.f) atomicAdd(dst, v); });
-        });
+    if (live) { ReplayGrad<DevAdd, Vtx> rg; rg.g = g; out = shade_body<Rgb>(sc, qin, b, i, rg); }
     uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
     if (out.extend) {
         qout.o_mint[slot] = out.o_mint; qout.d_maxt[slot] = out.d_maxt; qout.thr_eta[slot] = out.thr_eta;
         qout.misc[slot] = out.misc; qout.rng[slot] = out.rng;
+        if (Vtx) { qout.prev1[slot] = out.prev1; qout.prev2[slot] = out.prev2; }
     }
     uint32_t sslot = warp_alloc(&counters[1024 + depth], out.shadow);
     if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
+}
+// boundary term of the vertex adjoint (adjoint.h): projected edge lengths, two primary rays per edge sample, scatter
+__global__ void k_edge_len(SceneDev sc, EdgeCtx e, float *len) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < e.n_edges) len[k] = edge_len_body(sc, e, k);
+}
+__global__ void k_edge_raygen(SceneDev sc, SensorDev sn, EdgeCtx e, const float *total_len, RenderBatch b, PathQueue q, uint32_t *counters) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0) counters[1] = b.n_paths;
+    e.total_len = *total_len;
+    if (2 * j < b.n_paths) edge_raygen_body(sc, sn, e, b, q, j);
+}
+__global__ void k_edge_scatter(SceneDev sc, EdgeCtx e, const float *total_len, GradCtx g, const float4 *result, uint32_t n_samples) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    e.total_len = *total_len;
+    if (j < n_samples) edge_scatter_body(sc, e, g, result, j, DevAdd());
 }
 
 // any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)

@@ -15,6 +15,8 @@ struct PathQueue {
     uint4  *misc;              // path_id, depth | (prev_delta << 31), prev bsdf pdf (bits), unused
     uint4  *rng;               // PCG32 state lo/hi, inc lo/hi
     float2 *wav_eta;           // spectral mode only (+8 B): wavelength sample of the path, eta; thr_eta then holds 4 channels
+    float4 *prev1, *prev2;     // vertex-gradient replay only (else null): the two previous path vertices
+                               // (prim bits, b1, b2, chain flag); prim 0xffffffff = the camera
 };
 struct ShadowQueue {
     float4 *o_mint, *d_maxt;   // shadow ray
@@ -76,6 +78,7 @@ struct ShadeOut {
     bool extend, shadow;
     float4 o_mint, d_maxt, thr_eta; uint4 misc, rng; float2 wav_eta;   // extension record
     float4 s_o_mint, s_d_maxt, s_contrib_id;                  // shadow record
+    float4 prev1, prev2;                                       // vertex-gradient replay: records carried to the next vertex
     // adjoint bookkeeping (filled always; cheap): first-hit info of this vertex
     float3 emitted;                                            // radiance added at this vertex (already weighted)
 };
@@ -103,8 +106,23 @@ struct GradCtx {
     float *grad_tex;                // texture-sized accumulator
     int tex_id;
     float scale;                    // d(developed pixel)/d(sample radiance) = 1/spp_total (box filter)
+    // vertex-position adjoint (adjoint.h); grad_pos == nullptr: texture gradient only
+    float *grad_pos;                // 3 floats per vertex of mesh `mesh_id`
+    int mesh_id; uint32_t vert_begin, vert_count;
+    float3 cam_o;                   // sensor origin (x0 of every path)
 };
-struct NoGrad { HD void operator()(const SceneDev &, const RenderBatch &, uint32_t, const SI &, const BsdfDev &) const { } };
+// Hooks the adjoint replays plug into shade_body (all empty for the primal render):
+//   on_vertex: a path vertex was reconstructed (before its emission is added to the result);
+//   on_bsdf:   the vertex's BSDF is going to be used (after emission, Russian roulette and the depth cut);
+//   on_nee:    an emitter sample with non-zero contribution `c` was generated at the vertex.
+template <typename M> struct DirSampleT;
+struct NoGrad {
+    static constexpr bool kVertex = false;
+    HD void on_vertex(const SceneDev &, const PathQueue &, const RenderBatch &, uint32_t, uint32_t, uint32_t, float3, float3, const SI &) const { }
+    HD void on_bsdf(const SceneDev &, const RenderBatch &, uint32_t, const SI &, const BsdfDev &) const { }
+    template <typename DS> HD void on_nee(const SceneDev &, const PathQueue &, const RenderBatch &, uint32_t, uint32_t, uint32_t, const SI &,
+                                          const DS &, float3) const { }
+};
 
 template <typename AddFn>
 HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx &g, uint32_t path_id, const SI &si,
@@ -131,7 +149,7 @@ HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx 
 // One iteration of the loop in path.cpp:124-208 for queue entry i.  `result` accumulates emission.  `grad` is called
 // once the vertex's BSDF is known to be used (after emission, Russian roulette and the depth cut).
 template <typename M = Rgb, typename GradFn = NoGrad>
-HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, GradFn grad = GradFn()) {
+HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, const GradFn &grad = GradFn()) {
     typedef typename M::Spec Spec;
     ShadeOut out; out.extend = false; out.shadow = false; out.emitted = mk3(0.f);
     float4 o4 = q.o_mint[i], d4 = q.d_maxt[i], h4 = q.hit[i], te = q.thr_eta[i];
@@ -143,6 +161,13 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     if (M::spectral) sample_wavelengths(we.x, wav, ray_weight);
     float3 o = xyz(o4), d = xyz(d4);
     SI si = make_si(sc, o, d, h4);
+    bool chain_ok = true;                     // vertex-gradient replay: no delta vertex on the path so far
+    if (GradFn::kVertex) {
+        float4 p1 = depth > 1 ? q.prev1[i] : make_float4(u2f(0xffffffffu), 0.f, 0.f, u2f(1u));
+        chain_ok = f2u(p1.w) != 0u;
+        out.prev2 = p1;
+        if (chain_ok) grad.on_vertex(sc, q, b, i, path_id, depth, o, d, si);
+    }
 
     // ---- emission (path.cpp:128-129) with the MIS weight of the previous BSDF sample (:194-205)
     int em = si.valid ? sc.meshes[si.mesh].emitter : sc.env_emitter;
@@ -186,7 +211,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     if ((uint32_t) depth >= (uint32_t) sc.max_depth) return out;
 
     const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
-    grad(sc, b, path_id, si, bsdf);
+    grad.on_bsdf(sc, b, path_id, si, bsdf);
     // ---- emitter sampling (path.cpp:155-172, scene.cpp:141-189)
     if (bsdf_is_smooth(bsdf)) {
         float sx = rng.next_f32(), sy = rng.next_f32();
@@ -199,6 +224,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
                 float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
                 Spec c = thr * bval * ds.value * mis;
                 if (!is_black(c)) {
+                    if (GradFn::kVertex && !M::spectral && chain_ok) grad.on_nee(sc, q, b, i, path_id, depth, si, ds, to_result(sc, c, wav, ray_weight));
                     out.shadow = true;
                     out.s_o_mint = mk4(si.p, kRayEpsilon * (1.f + hmax(abs3(si.p))));
                     out.s_d_maxt = mk4(ds.d, ds.dist * (1.f - kShadowEpsilon));
@@ -220,6 +246,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     store_throughput(out, thr, eta, we);
     out.misc = make_uint4(path_id, (depth + 1u) | (bs.delta ? 0x80000000u : 0u), f2u(bs.pdf), 0u);
     rng_store(&out.rng, rng);
+    if (GradFn::kVertex) out.prev1 = make_float4(u2f(si.prim), h4.y, h4.z, u2f(chain_ok && !bs.delta ? 1u : 0u));
     return out;
 }
 

@@ -226,7 +226,14 @@ class Scene:
         A.check(A.lib().mtsb_scene_update_texture(self._h, tex_id, p, mem))
 
     # ---- gradient pass ----------------------------------------------------------------------------
+    def grad_config(self, boundary=True, edge_fraction=0.25):
+        """Options of the vertex-gradient pass: `boundary` = add the primary-visibility edge-sampling term,
+        `edge_fraction` = edge samples per path sample."""
+        A.check(A.lib().mtsb_grad_config(self._h, int(bool(boundary)), float(edge_fraction)))
+
     def render_grad(self, dL_dimage, sensor=0, spp=None, seed=0, tex_id=-1, mesh_id=-1, spp_begin=0, spp_total=None):
+        """Adjoint of `render`: returns (d/d texture `tex_id`, d/d vertex positions of mesh `mesh_id`) of
+        sum(dL_dimage * developed image); either is None when its id is negative."""
         spp = self.data.spp if spp is None else int(spp)
         spp_total = spp_begin + spp if spp_total is None else int(spp_total)
         pd, mem, k = _arg(dL_dimage, np.float32)

@@ -197,7 +197,8 @@ class HostSim:
             l.hs_bvh_info.argtypes = [vp, vp, vp]
             l.hs_intersect.argtypes = [vp, C.c_uint64, vp, vp, vp, vp, C.c_int]
             l.hs_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]
-            l.hs_render_grad.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, C.c_int32, vp]
+            l.hs_render_grad.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, C.c_int32, vp, C.c_int32, vp,
+                                         C.c_int, C.c_float]
             l.hs_bsdf_sample.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
             l.hs_sample_emitter_direction.argtypes = [vp, C.c_uint64, vp, vp, vp]
             cls._lib = l
@@ -256,7 +257,18 @@ class HostSim:
         t = self.data.textures[tex_id]
         g = np.zeros_like(np.ascontiguousarray(t["data"], np.float32))
         dl = _f32(dL_dimage)
-        self.lib().hs_render_grad(self.h, sensor, spp_begin, spp, spp_total, seed, _p(dl), tex_id, _p(g))
+        self.lib().hs_render_grad(self.h, sensor, spp_begin, spp, spp_total, seed, _p(dl), tex_id, _p(g), -1, None, 0, 0.0)
+        return g
+
+    def render_grad_vertices(self, dL_dimage, mesh_id, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None, boundary=True,
+                             edge_fraction=0.25):
+        """d(sum(dL_dimage * image))/d(vertex positions of mesh_id): the same adjoint as mtsb_render_grad, run on the host."""
+        spp = self.data.spp if spp is None else spp
+        spp_total = spp_begin + spp if spp_total is None else spp_total
+        g = np.zeros_like(_f32(self.data.meshes[mesh_id].positions))
+        dl = _f32(dL_dimage)
+        self.lib().hs_render_grad(self.h, sensor, spp_begin, spp, spp_total, seed, _p(dl), -1, None, mesh_id, _p(g), int(boundary),
+                                  float(edge_fraction))
         return g
 
 
@@ -551,3 +563,65 @@ def n1_scene(res=(32, 24), spp=8, named_conductor=False):
     sd.add_perspective(look_at([0, 0.3, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
     sd.max_depth, sd.rr_depth, sd.spp = 5, 3, spp
     return sd
+
+
+# ---- vertex-gradient test scenes (tests/test_grad_cpu.py, tests/test_gpu_parity.py) -------------------------------------
+def grid_mesh(nx, ny, size, origin, ax_u, ax_v):
+    u, v = np.linspace(-0.5, 0.5, nx + 1), np.linspace(-0.5, 0.5, ny + 1)
+    P = np.array([np.array(origin) + size * (a * np.array(ax_u) + b * np.array(ax_v)) for b in v for a in u], np.float32)
+    F = []
+    for j in range(ny):
+        for i in range(nx):
+            a = j * (nx + 1) + i
+            F += [[a, a + 1, a + nx + 2], [a, a + nx + 2, a + nx + 1]]
+    return P, np.array(F, np.uint32)
+
+
+def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
+    """Scenes whose vertex gradients have no secondary-visibility component (see mitsuba2_b200/csrc/adjoint.h), mesh 0
+    is the differentiated one.  plane*: one big plane filling the view (interior term only); quadenv: a small quad in
+    front of a constant background (boundary term only); corner: plane + wall + area light outside the view."""
+    sd = SceneData()
+    if bsdf == "diffuse":
+        b = sd.add_diffuse([0.6, 0.5, 0.4])
+    elif bsdf == "beckmann":
+        b = sd.add_roughconductor(material="Cu", alpha=0.3)
+    else:
+        b = sd.add_roughconductor(material="Au", alpha=0.25, distribution="ggx")
+    bw = sd.add_diffuse([0.3, 0.5, 0.7])
+    if kind.startswith("plane") or kind == "corner":
+        P, F = grid_mesh(4, 4, 8.0, [0, 0, 1.0], [1, 0, 0], [0, -1, 0])
+        sd.add_mesh(Mesh(P, F, bsdf=b))
+    if kind == "plane":
+        sd.add_point([0.5, 1.0, -1.0], [8, 8, 8])
+    if kind in ("planearea", "corner"):
+        P3, F3 = grid_mesh(1, 1, 0.8, [-0.5, 1.5, -0.5], [1, 0, 0], [0, 0, 1])
+        sd.add_mesh(Mesh(P3, F3, bsdf=bw), area_radiance=[20, 20, 20])
+    if kind == "corner":
+        P2, F2 = grid_mesh(2, 2, 3.0, [2.2, 0, -0.6], [0, 0, 1], [0, -1, 0])
+        sd.add_mesh(Mesh(P2, F2, bsdf=bw))
+    if kind == "quadenv":
+        P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
+        sd.add_mesh(Mesh(P, F, bsdf=b))
+        sd.add_constant([1.0, 1.0, 1.0])
+    sd.add_perspective(look_at([0, 0, -3.0], [0, 0, 0], [0, 1, 0]), 40.0, 0.01, 100.0, res, res, "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 4, 100, spp
+    return sd
+
+
+def displacement_fields(P):
+    """Global deformations used to compare per-vertex gradients with finite differences: d(loss)/d(tau) = sum_v g_v . D_v."""
+    c, z = P.mean(0), np.zeros(len(P))
+    return {"tx": np.tile([1.0, 0, 0], (len(P), 1)), "ty": np.tile([0, 1.0, 0], (len(P), 1)), "tz": np.tile([0, 0, 1.0], (len(P), 1)),
+            "scale": P - c, "tilt": np.stack([z, z, P[:, 0] - c[0]], 1)}
+
+
+def oracle_fd_vertices(sd, mesh_id, wgt, D, eps, spp, seed):
+    """Central finite difference of sum(wgt * image) along the vertex displacement field D, rendered by the oracle."""
+    orc = Oracle(sd)
+    P0 = _f32(sd.meshes[mesh_id].positions).reshape(-1, 3)
+    vals = []
+    for sgn in (+1.0, -1.0):
+        orc.update_vertices(mesh_id, (P0 + sgn * eps * D).astype(np.float32))
+        vals.append(float((orc.render(spp=spp, seed=seed).astype(np.float64) * wgt).sum()))
+    return (vals[0] - vals[1]) / (2 * eps)

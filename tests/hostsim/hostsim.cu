@@ -4,7 +4,7 @@
 // It is NOT part of the product library and makes no CUDA runtime calls.
 #define MTSB_TRAV_STATS 1
 #include "../../include/mtsb200.h"
-#include "../../mitsuba2_b200/csrc/path.h"
+#include "../../mitsuba2_b200/csrc/adjoint.h"
 #include "../../mitsuba2_b200/csrc/host_tables.h"
 #include "../../mitsuba2_b200/csrc/cie_tables.h"
 #include <vector>
@@ -232,17 +232,19 @@ extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const floa
 // The wavefront loop of mtsb_render (run_batch in api.cu), stage by stage, with sequential "threads".
 struct HsPool {
     std::vector<float4> qo[2], qd[2], qh[2], qt[2], so, sdv, scv, result;
-    std::vector<uint4> qm[2], qr[2]; std::vector<float2> qw[2];
+    std::vector<uint4> qm[2], qr[2]; std::vector<float2> qw[2]; std::vector<float4> p1[2], p2[2];
     explicit HsPool(uint32_t pool) : so(pool), sdv(pool), scv(pool), result(pool) {
-        for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); qw[k].resize(pool); }
+        for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); qw[k].resize(pool);
+                                      p1[k].resize(pool); p2[k].resize(pool); }
     }
-    PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); q.wav_eta = qw[k].data(); return q; }
+    PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); q.wav_eta = qw[k].data();
+                             q.prev1 = p1[k].data(); q.prev2 = p2[k].data(); return q; }
 };
 template <typename M, typename GradFn>
-static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad) {
+static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad, bool raygen = true) {
     std::vector<uint2> fast(8);
     uint32_t n = b.n_paths; int cur = 0; uint32_t count = n;
-    for (uint32_t i = 0; i < n; ++i) raygen_body<M>(sn, b, P.queue(cur), i);
+    if (raygen) for (uint32_t i = 0; i < n; ++i) raygen_body<M>(sn, b, P.queue(cur), i);
     for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
         PathQueue qin = P.queue(cur), qout = P.queue(cur ^ 1);
         for (uint32_t i = 0; i < count; ++i) {
@@ -254,7 +256,8 @@ static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b,
         uint32_t next = 0, nshadow = 0;
         for (uint32_t i = 0; i < count; ++i) {
             ShadeOut out = shade_body<M>(s->dev, qin, b, i, grad);
-            if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; if (M::spectral) qout.wav_eta[next] = out.wav_eta; next++; }
+            if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; if (M::spectral) qout.wav_eta[next] = out.wav_eta;
+                              if (GradFn::kVertex) { qout.prev1[next] = out.prev1; qout.prev2[next] = out.prev2; } next++; }
             if (out.shadow) { P.so[nshadow] = out.s_o_mint; P.sdv[nshadow] = out.s_d_maxt; P.scv[nshadow] = out.s_contrib_id; nshadow++; }
         }
         for (uint32_t i = 0; i < nshadow; ++i) {
@@ -287,24 +290,68 @@ extern "C" void hs_render(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, u
     if (counts) { counts[0] = total; counts[1] = cnt[0]; counts[2] = cnt[1]; counts[3] = cnt[2]; }
 }
 
-// mtsb_render_grad (grad.cuh) on the host: primal pass -> final radiance, replay with the texel scatter
+// mtsb_render_grad (grad.cuh) on the host: primal pass -> final radiance, replay with the texel / vertex scatter, then
+// the boundary (edge-sampling) pass for vertex gradients
+struct HostAdd { HD void operator()(float *dst, float v) const { *dst += v; } };
+static void invert4(const float *m, double *out) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = m[4 * r + c]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int c = 0; c < 4; ++c) {
+        int piv = c; for (int r = c + 1; r < 4; ++r) if (fabs(a[r][c]) > fabs(a[piv][c])) piv = r;
+        for (int k = 0; k < 8; ++k) std::swap(a[c][k], a[piv][k]);
+        double inv = 1.0 / a[c][c]; for (int k = 0; k < 8; ++k) a[c][k] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != c) { double f = a[r][c]; for (int k = 0; k < 8; ++k) a[r][k] -= f * a[c][k]; }
+    }
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out[4 * r + c] = a[r][4 + c];
+}
 extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total, uint64_t seed,
-                               const float *dL_dimage, int32_t tex_id, float *grad_texture) {
+                               const float *dL_dimage, int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,
+                               int boundary, float edge_fraction) {
     SensorDev sn = s->sensors[sensor_id];
-    uint64_t total = (uint64_t) sn.width * sn.height * spp_count;
+    uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
     uint32_t pool = (uint32_t) std::min<uint64_t>(total, 1u << 20);
     HsPool P(pool);
     std::vector<float4> fin(pool);
     uint64_t cnt[3] = { 0, 0, 0 };
-    GradCtx g; g.final_radiance = fin.data(); g.dL_dimage = dL_dimage; g.grad_tex = grad_texture; g.tex_id = tex_id; g.scale = 1.f / (float) spp_total;
+    GradCtx g; g.final_radiance = fin.data(); g.dL_dimage = dL_dimage; g.grad_tex = grad_texture; g.tex_id = grad_texture ? tex_id : -1; g.scale = 1.f / (float) spp_total;
+    g.grad_pos = grad_vertices; g.mesh_id = mesh_id; g.vert_begin = g.vert_count = 0;
+    g.cam_o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
+    if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
         hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad());
         std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
-        hs_run_batch<Rgb>(s, sn, b, P, cnt, [&](const SceneDev &sc, const RenderBatch &bb, uint32_t pid, const SI &si, const BsdfDev &bsdf) {
-            texture_adjoint(sc, bb, g, pid, si, bsdf, [](float *dst, float v) { *dst += v; });
-        });
+        ReplayGrad<HostAdd> rg; rg.g = g;
+        hs_run_batch<Rgb>(s, sn, b, P, cnt, rg);
+    }
+    if (!grad_vertices || !boundary) return;
+    // ---- boundary term: unique edges of the mesh, projected-length cdf, two paths per edge sample
+    const MeshDev &m = s->meshes[mesh_id];
+    std::vector<uint64_t> keys;
+    for (uint32_t f = 0; f < m.face_count; ++f) { uint4 fc = s->faces[m.face_begin + f]; uint32_t v[3] = { fc.x, fc.y, fc.z };
+        for (int k = 0; k < 3; ++k) { uint32_t a = v[k], c = v[(k + 1) % 3]; if (a > c) std::swap(a, c); keys.push_back(((uint64_t) a << 32) | c); } }
+    std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    std::vector<uint2> edges(keys.size());
+    for (size_t k = 0; k < keys.size(); ++k) edges[k] = make_uint2((uint32_t) (keys[k] >> 32), (uint32_t) keys[k]);
+    EdgeCtx e; e.edges = edges.data(); e.n_edges = (uint32_t) edges.size(); e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.02f;
+    double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
+    std::vector<float> cdf(edges.size()); double acc = 0;
+    for (uint32_t k = 0; k < e.n_edges; ++k) { acc += edge_len_body(s->dev, e, k); cdf[k] = (float) acc; }
+    e.cdf = cdf.data(); e.total_len = (float) acc;
+    uint64_t nb_total = std::max<uint64_t>(1, (uint64_t) ((double) npix * spp_total * edge_fraction));
+    uint64_t nb_first = (uint64_t) ((double) npix * spp_begin * edge_fraction), nb_end = (uint64_t) ((double) npix * (spp_begin + spp_count) * edge_fraction);
+    if (spp_begin + spp_count == spp_total) nb_end = nb_total;
+    e.weight = 1.f / (float) nb_total;
+    uint32_t half = pool / 2;
+    for (uint64_t off = nb_first; off < nb_end; off += half) {
+        uint32_t nb = (uint32_t) std::min<uint64_t>(half, nb_end - off);
+        e.first = off;
+        RenderBatch b; b.n_paths = 2 * nb; b.offset = 0; b.spp_begin = 0; b.spp_batch = 1; b.spp_total = 1; b.seed = seed; b.result = P.result.data();
+        for (uint32_t j = 0; j < nb; ++j) edge_raygen_body(s->dev, sn, e, b, P.queue(0), j);
+        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad(), false);
+        for (uint32_t j = 0; j < nb; ++j) edge_scatter_body(s->dev, e, g, P.result.data(), j, HostAdd());
     }
 }
 
