@@ -73,6 +73,20 @@ def side_metrics(mi, local):
             ms.append(sc4.last_stats["ms_total"])
     out["c4_gradient_pass_ms"] = float(np.median(ms))
     out["c4_gradient_pass_msamples_per_s"] = 512 * 512 * 64 / (out["c4_gradient_pass_ms"] * 1e-3) / 1e6
+    # the full C4 parameter set: albedo texture + the vertex positions of the 20k-triangle sphere in one pass
+    # (interior term + edge-sampling boundary term at 0.25 edge samples per path sample)
+    mid = next(i for i, m in enumerate(sd4.meshes) if m.name == "c4_sphere")
+    ms, stages = [], None
+    sc4.set_profiling(True)
+    for i in range(2 + 3):
+        sc4.render_grad(dl, spp=64, seed=i, tex_id=tex, mesh_id=mid)
+        if i >= 2:
+            ms.append(sc4.last_stats["ms_total"])
+            stages = {k: sc4.last_stats[k] for k in ("ms_closest", "ms_shade", "ms_any", "ms_raygen")}
+    sc4.set_profiling(False)
+    out["c4_gradient_pass_texture_and_vertices_ms"] = float(np.median(ms))
+    out["c4_gradient_pass_texture_and_vertices_stage_ms"] = stages
+    out["c4_sphere_triangles"] = int(len(sd4.meshes[mid].faces))
     del sc4
     out.update(spectral_metric(mi, local))
     out["parity_gates"] = parity_gates(mi, local)
@@ -143,6 +157,20 @@ def parity_gates(mi, local):
     fd, an = np.array(fd), np.array(an)
     g["texture_grad_cosine_vs_fd"] = float(np.dot(fd, an) / (np.linalg.norm(fd) * np.linalg.norm(an)))
     g["texture_grad_rel_l2_vs_fd"] = float(np.linalg.norm(fd - an) / np.linalg.norm(fd))
+    # vertex-position adjoint vs central finite differences of the oracle along global displacement fields:
+    # interior term (plane under a point light: same estimator sample by sample) and boundary term (quad on a background)
+    for kind, fields, eps, fd_spp, name in (("plane", ("tz", "tilt"), 2e-3, 32, "interior"), ("quadenv", ("tx", "ty", "scale"), 0.02, 1024, "boundary")):
+        sdv = H.vgrad_scene(kind, "ggx" if kind == "plane" else "diffuse", res=16, spp=32 if kind == "plane" else 128)
+        yy, xx = np.mgrid[0:16, 0:16]
+        w = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
+        scv = mi.Scene(sdv, device=local)
+        scv.grad_config(boundary=(kind != "plane"), edge_fraction=1.0)
+        _, gv = scv.render_grad(w, seed=3, mesh_id=0)
+        P0 = np.asarray(sdv.meshes[0].positions, np.float32).reshape(-1, 3)
+        F = H.displacement_fields(P0)
+        fd = np.array([H.oracle_fd_vertices(sdv, 0, w, F[n].astype(np.float32), eps, fd_spp, 3) for n in fields])
+        an = np.array([float((gv * F[n]).sum()) for n in fields])
+        g[f"vertex_grad_{name}_rel_l2_vs_fd"] = float(np.linalg.norm(fd - an) / np.linalg.norm(fd))
     return g
 
 

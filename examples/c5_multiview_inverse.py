@@ -4,8 +4,11 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 examples/c5_multiview_inverse.py
 
 Every rank holds the whole scene, renders ITS view with all samples, computes the L2 image loss against its target
-view, and back-propagates through `mtsb_render_grad`; the texture gradients are summed over the ranks with one NCCL
+view, and back-propagates through `mtsb_render_grad`; the parameter gradients are summed over the ranks with one NCCL
 all-reduce and every rank applies the identical Adam update (parameters never need a broadcast).
+
+--param vertices (default, BASELINE config C5): Adam on the vertex positions of the sphere, started from a shrunk and
+shifted copy of the target shape.  --param texture: Adam on the floor's albedo texture.
 """
 import argparse
 import os
@@ -28,13 +31,18 @@ def main():
     ap.add_argument("--res", type=int, default=256)
     ap.add_argument("--spp", type=int, default=16)
     ap.add_argument("--tex", type=int, default=64)
+    ap.add_argument("--param", choices=("vertices", "texture"), default="vertices")
+    ap.add_argument("--sphere", type=int, default=40, help="latitude bands of the sphere (longitude = 2x)")
+    ap.add_argument("--lr", type=float, default=None)
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mi.set_variant("cuda_b200_rgb")
-    sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=args.res, spp=args.spp, tex_res=args.tex)
+    sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=args.res, spp=args.spp, tex_res=args.tex,
+                              sphere=(args.sphere, 2 * args.sphere))
+    mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
     # view `rank`: orbit the camera around the box centre
     s0 = sd.sensors[0]
     ang = (rank - (world - 1) / 2) * 0.12
@@ -43,24 +51,37 @@ def main():
     sd.sensors = []
     sd.add_perspective(look_at(eye, c, [0, 1, 0]), s0["fov_x"], s0["near"], s0["far"], args.res, args.res, "box")
     scene = mi.Scene(sd, device=local)
-    target_tex = torch.from_numpy(sd.textures[tex]["data"].copy()).cuda(local)
-    target = torch.from_numpy(scene.render(spp=4 * args.spp, seed=12345).copy()).cuda(local)
-    param = torch.full_like(target_tex, 0.5, requires_grad=True)
-    opt = torch.optim.Adam([param], lr=0.02)
     from mitsuba2_b200 import autodiff
+    target = torch.from_numpy(scene.render(spp=4 * args.spp, seed=12345).copy()).cuda(local)
+    if args.param == "texture":
+        truth = torch.from_numpy(sd.textures[tex]["data"].copy()).cuda(local)
+        param = torch.full_like(truth, 0.5, requires_grad=True)
+        lr = args.lr or 0.02
+    else:
+        truth = torch.from_numpy(np.asarray(sd.meshes[mid].positions, np.float32).reshape(-1, 3).copy()).cuda(local)
+        c0 = truth.mean(0, keepdim=True)
+        size = float((truth.max(0).values - truth.min(0).values).max())
+        start = c0 + 0.8 * (truth - c0) + torch.tensor([[0.06 * size, 0.04 * size, 0.0]], device=truth.device)
+        param = start.clone().requires_grad_(True)
+        lr = args.lr or 0.004 * size
+    opt = torch.optim.Adam([param], lr=lr)
     for it in range(args.iters):
         opt.zero_grad()
-        img = autodiff.render_torch(scene, param, tex, spp=args.spp, seed=it, shard=False)
+        if args.param == "texture":
+            img = autodiff.render_torch(scene, param, tex, spp=args.spp, seed=it, shard=False)
+        else:
+            img = autodiff.render_torch(scene, spp=args.spp, seed=it, shard=False, vertices=param, mesh_id=mid)
         loss = ((img - target) ** 2).mean()
         loss.backward()
         if world > 1:                              # sum the per-view gradients; identical update everywhere
             distributed.allreduce_gradients([param.grad])
         opt.step()
-        with torch.no_grad():
-            param.clamp_(0.01, 0.99)
+        if args.param == "texture":
+            with torch.no_grad():
+                param.clamp_(0.01, 0.99)
         if rank == 0 and (it % 10 == 0 or it == args.iters - 1):
-            err = (param.detach() - target_tex).abs().mean().item()
-            print(f"iter {it:4d}  loss(view 0) {loss.item():.6f}  mean |texel error| {err:.4f}", flush=True)
+            err = (param.detach() - truth).abs().mean().item()
+            print(f"iter {it:4d}  loss(view 0) {loss.item():.6f}  mean |{args.param} error| {err:.4f}", flush=True)
     if world > 1:
         dist.destroy_process_group()
 

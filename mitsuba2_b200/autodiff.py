@@ -3,29 +3,45 @@
 reference's own ``Adam``/``SGD`` classes, :240-377, are thin re-implementations of the same updates) can drive inverse
 rendering.  The backward pass is ``mtsb_render_grad`` (replay adjoint), not a tape.
 
-Only bitmap textures that enter a BSDF multiplicatively (diffuse ``reflectance``, roughconductor
-``specular_reflectance``) are differentiable in this round; vertex positions raise.
+Differentiable parameters (the reference exposes them through ``traverse``, src/python/python/util.py:14-179):
+* a bitmap texture that enters a BSDF multiplicatively -- ``<bsdf>.reflectance.data`` of ``diffuse``,
+  ``specular_reflectance`` of ``roughconductor`` (src/textures/bitmap.cpp:295-331);
+* the vertex positions of a mesh -- ``<mesh>.vertex_positions_buf`` (src/librender/mesh.cpp:781-804): interior term +
+  primary-visibility boundary term (csrc/adjoint.h lists what is not covered).
 """
 from __future__ import annotations
 
 import numpy as np
 
 
-def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None, shard=True):
-    """Render `scene` with bitmap texture `tex_id` set to the torch tensor `texture` (H,W,C); returns the developed
-    linear-RGB image (H,W,3) as a tensor on the texture's device, differentiable w.r.t. `texture`.
+def render_torch(scene, texture=None, tex_id=-1, spp=None, seed=0, sensor=0, group=None, shard=True, vertices=None, mesh_id=-1):
+    """Render `scene` with bitmap texture `tex_id` set to the torch tensor `texture` (H,W,C) and / or the vertex
+    positions of mesh `mesh_id` set to `vertices` (V,3); returns the developed linear-RGB image (H,W,3) as a tensor on
+    the parameters' device, differentiable w.r.t. both.
 
     With an initialised process group and `shard=True` every rank renders its share of the samples of the SAME view and
-    both the image and the texture gradient are all-reduced (distributed.py), so all ranks see identical values.
+    the image and the gradients are all-reduced (distributed.py), so all ranks see identical values.
     `shard=False` renders locally (multi-view optimisation: one view per rank, the caller reduces the gradients)."""
     import torch
     from . import distributed as D
 
+    if texture is None and vertices is None:
+        raise ValueError("render_torch: pass a texture and / or vertices to differentiate")
+    use_tex, use_vtx = texture is not None, vertices is not None
+    if use_tex and tex_id < 0 or use_vtx and mesh_id < 0:
+        raise ValueError("render_torch: tex_id / mesh_id missing")
+    dev = (texture if use_tex else vertices).device
+
+    def _host(t):
+        return t if t.is_cuda else t.cpu().numpy()
+
     class _Render(torch.autograd.Function):
         @staticmethod
-        def forward(ctx, tex):
-            t = tex.detach().contiguous().float()
-            scene.update_texture(tex_id, t if t.is_cuda else t.cpu().numpy())
+        def forward(ctx, tex, vtx):
+            if use_tex:
+                scene.update_texture(tex_id, _host(tex.detach().contiguous().float()))
+            if use_vtx:
+                scene.update_vertices(mesh_id, _host(vtx.detach().contiguous().float()))
             rank, world = D.world_info(group) if shard else (0, 1)
             total = int(scene.data.spp if spp is None else spp)
             begin, count = D.sample_share(total, rank, world)
@@ -34,21 +50,28 @@ def render_torch(scene, texture, tex_id, spp=None, seed=0, sensor=0, group=None,
                 img = scene.render_distributed(sensor, total, seed, group)
             else:
                 img = scene.render(sensor, total, seed)
-            return torch.from_numpy(np.ascontiguousarray(img)).to(tex.device)
+            return torch.from_numpy(np.ascontiguousarray(img)).to(dev)
 
         @staticmethod
         def backward(ctx, grad_img):
             begin, count, total = ctx.share
             g = grad_img.detach().contiguous().float()
-            gt = None
+            gt = gv = None
             if count > 0:
-                gt, _ = scene.render_grad(g if g.is_cuda else g.cpu().numpy(), sensor, count, seed, tex_id, -1, begin, total)
-            if gt is None:
-                gt = np.zeros(int(np.prod(texture.shape)), np.float32)
-            gt = gt if isinstance(gt, torch.Tensor) else torch.from_numpy(gt)
-            gt = gt.to(grad_img.device).reshape(texture.shape)
+                gt, gv = scene.render_grad(_host(g), sensor, count, seed, tex_id if use_tex else -1,
+                                           mesh_id if use_vtx else -1, begin, total)
+            out = []
+            for want, val, like in ((use_tex, gt, texture), (use_vtx, gv, vertices)):
+                if not want:
+                    out.append(None)
+                    continue
+                if val is None:
+                    val = np.zeros(int(np.prod(like.shape)), np.float32)
+                val = val if isinstance(val, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(val))
+                out.append(val.to(grad_img.device).reshape(like.shape))
             if shard:
-                D.allreduce_gradients([gt], group)
-            return gt
+                D.allreduce_gradients([o for o in out if o is not None], group)
+            return out[0], out[1]
 
-    return _Render.apply(texture)
+    dummy = torch.zeros(1, device=dev)
+    return _Render.apply(texture if use_tex else dummy, vertices if use_vtx else dummy)

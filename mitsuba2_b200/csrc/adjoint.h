@@ -209,6 +209,21 @@ HD void vertex_triple(const SceneDev &sc, const GradCtx &g, float3 xA, VtxRec re
         float3 g_ng = g_n * dot(ng, n) - n * dot(g_n, ng);
         scatter_normal(g, tB, (g_ng - ng * dot(ng, g_ng)) / lN, add);
     }
+    if (B_primary && tB.mesh == g.mesh_id && sc.meshes[tB.mesh].has_normals && lN > 0.f) {
+        // x1 slides over the triangle when the vertices move under a fixed camera ray, so the INTERPOLATED normal
+        // changes through the barycentrics: r = dt d - u (in-plane), db1 = r . (e2 x N)/|N|^2, db2 = r . (N x e1)/|N|^2
+        float3 n0 = ld3(sc.nrm, tB.i0), n1 = ld3(sc.nrm, tB.i1), n2 = ld3(sc.nrm, tB.i2);
+        float b0 = 1.f - recB.b1 - recB.b2;
+        float L = norm(n0 * b0 + n1 * recB.b1 + n2 * recB.b2);
+        float3 d = siB.p - g.cam_o; float nd = dot(tB.N, d);
+        if (L > 0.f && fabsf(nd) > 1e-20f) {
+            float3 gm = (g_n - n * dot(n, g_n)) / L;
+            float gb1 = dot(gm, n1 - n0), gb2 = dot(gm, n2 - n0);
+            float3 gr = (cross(tB.e2, tB.N) * gb1 + cross(tB.N, tB.e1) * gb2) / (lN * lN);
+            float3 gu = tB.N * (dot(d, gr) / nd) - gr;
+            add_vertex(g, tB.i0, gu * b0, add); add_vertex(g, tB.i1, gu * recB.b1, add); add_vertex(g, tB.i2, gu * recB.b2, add);
+        }
+    }
     if (kindC == kEndSurface) { scatter_point(g, tC, recC, false, xC, g_dout, add); scatter_normal(g, tC, g_NC, add); }
 }
 
@@ -263,7 +278,8 @@ template <typename Add, bool Vtx = true> struct ReplayGrad {
 
 // ---- boundary term: edge sampling on the film plane ---------------------------------------------------------------
 struct EdgeCtx {
-    const uint2 *edges; uint32_t n_edges;   // unique edges of the differentiated mesh (scene-global vertex indices)
+    const uint4 *edges; uint32_t n_edges;   // unique edges of the differentiated mesh: scene-global vertex indices a, b and
+                                            // the primitive ids of the two adjacent faces (second = ~0 on a border)
     const float *cdf;                       // inclusive prefix sum of the projected edge lengths (pixels)
     float total_len;
     float w2s[16];                          // world -> sample space (x, y in [0,1]^2 after the divide by w), row-major
@@ -280,9 +296,18 @@ HD bool edge_project(const EdgeCtx &e, float3 v, float &x, float &y, float &hw) 
     x = hx / hw * (float) e.width; y = hy / hw * (float) e.height;
     return true;
 }
-HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, uint32_t k) {
-    uint2 ed = e.edges[k]; float ax, ay, aw, bx, by, bw;
-    if (!edge_project(e, ld3(sc.pos, ed.x), ax, ay, aw) || !edge_project(e, ld3(sc.pos, ed.y), bx, by, bw)) return 0.f;
+// sampling weight of an edge = projected length.  A smooth-shaded mesh (vertex normals) is discontinuous on the film only
+// along its silhouette -- edges whose two faces look opposite ways from the camera, and border edges -- so the others get
+// weight 0; a flat-shaded mesh also jumps across every edge that has a front-facing side.
+HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, float3 cam_o, uint32_t k) {
+    uint4 ed = e.edges[k]; float ax, ay, aw, bx, by, bw;
+    float3 va = ld3(sc.pos, ed.x);
+    if (!edge_project(e, va, ax, ay, aw) || !edge_project(e, ld3(sc.pos, ed.y), bx, by, bw)) return 0.f;
+    if (ed.w != 0xffffffffu) {
+        float s0 = dot(tri_geo(sc, ed.z).N, va - cam_o), s1 = dot(tri_geo(sc, ed.w).N, va - cam_o);
+        bool smooth = sc.meshes[sc.faces[ed.z].w].has_normals != 0;
+        if (smooth ? (s0 < 0.f) == (s1 < 0.f) : (s0 >= 0.f && s1 >= 0.f)) return 0.f;
+    }
     float l = sqrtf(sqr(ax - bx) + sqr(ay - by));
     return l < 1e30f ? l : 0.f;
 }
@@ -294,7 +319,7 @@ HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j) {
     if (!(e.total_len > 0.f) || e.n_edges == 0) return s;
     float value = u1 * e.total_len; const float *cdf = e.cdf;
     s.edge = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
-    uint2 ed = e.edges[s.edge];
+    uint4 ed = e.edges[s.edge];
     s.va = ld3(sc.pos, ed.x); s.vb = ld3(sc.pos, ed.y);
     float ax, ay, aw, bx, by, bw;
     if (!edge_project(e, s.va, ax, ay, aw) || !edge_project(e, s.vb, bx, by, bw)) return s;
@@ -330,7 +355,7 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
     float sc_ = (dI.x * (lp.x - lm.x) + dI.y * (lp.y - lm.y) + dI.z * (lp.z - lm.z)) * e.weight * e.total_len;
     if (sc_ == 0.f || !(fabsf(sc_) < 1e30f)) return;
     // grad_a(alpha) = -(1 - t) len n, grad_b(alpha) = -t len n; the 1/len of the edge pick cancels len
-    uint2 ed = e.edges[s.edge];
+    uint4 ed = e.edges[s.edge];
     const float *m = e.w2s;
     for (int k = 0; k < 2; ++k) {
         float3 v = k == 0 ? s.va : s.vb; float wgt = -(k == 0 ? 1.f - s.t : s.t) * sc_;

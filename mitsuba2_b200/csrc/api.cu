@@ -96,7 +96,7 @@ struct mtsb_scene {
     DevBuf<uint32_t> class_lists;            // material bins of the shade stage: kShadeClasses x pool queue indices
     DevBuf<uint4> q_misc[2], q_rng[2];
     DevBuf<float4> q_p1[2], q_p2[2];         // vertex-gradient replay: previous two path vertices per queue entry
-    std::map<int, std::unique_ptr<DevBuf<uint2>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
+    std::map<int, std::unique_ptr<DevBuf<uint4>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
     int grad_boundary = 1; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;

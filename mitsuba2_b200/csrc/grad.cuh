@@ -26,23 +26,31 @@ static void invert4(const float *m, double *out) {
     }
     for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out[4 * r + c] = a[r][4 + c];
 }
-// unique edges of a mesh in scene-global vertex indices (host sort once per mesh; the list is topology, not positions)
-static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint2 **edges, uint32_t *n_edges) {
+// unique edges of a mesh (scene-global vertex indices + the primitive ids of the two adjacent faces); host sort once per
+// mesh: the list is topology, not positions
+static void build_edge_list(const uint32_t *faces, size_t n_faces, uint32_t vert_begin, uint32_t face_begin, std::vector<uint4> &out) {
+    std::vector<std::pair<uint64_t, uint32_t>> keys; keys.reserve(3 * n_faces);
+    for (size_t t = 0; t < n_faces; ++t)
+        for (int k = 0; k < 3; ++k) {
+            uint32_t a = faces[3 * t + k] + vert_begin, c = faces[3 * t + (k + 1) % 3] + vert_begin;
+            if (a > c) std::swap(a, c);
+            keys.emplace_back(((uint64_t) a << 32) | c, face_begin + (uint32_t) t);
+        }
+    std::sort(keys.begin(), keys.end());
+    out.clear();
+    for (size_t i = 0; i < keys.size();) {
+        size_t j = i + 1; while (j < keys.size() && keys[j].first == keys[i].first) ++j;
+        out.push_back(make_uint4((uint32_t) (keys[i].first >> 32), (uint32_t) keys[i].first, keys[i].second, j - i > 1 ? keys[i + 1].second : 0xffffffffu));
+        i = j;
+    }
+}
+static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint4 **edges, uint32_t *n_edges) {
     auto it = s->mesh_edges.find(mesh_id);
     if (it == s->mesh_edges.end()) {
         const MeshDev &m = s->meshes[mesh_id];
-        const std::vector<uint32_t> &f = s->mesh_faces[mesh_id];
-        std::vector<uint64_t> keys; keys.reserve(f.size());
-        for (size_t t = 0; t + 2 < f.size(); t += 3)
-            for (int k = 0; k < 3; ++k) {
-                uint32_t a = f[t + k] + m.vert_begin, c = f[t + (k + 1) % 3] + m.vert_begin;
-                if (a > c) std::swap(a, c);
-                keys.push_back(((uint64_t) a << 32) | c);
-            }
-        std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
-        std::vector<uint2> e(keys.size());
-        for (size_t k = 0; k < keys.size(); ++k) e[k] = make_uint2((uint32_t) (keys[k] >> 32), (uint32_t) keys[k]);
-        std::unique_ptr<DevBuf<uint2>> buf(new DevBuf<uint2>());
+        std::vector<uint4> e;
+        build_edge_list(s->mesh_faces[mesh_id].data(), m.face_count, m.vert_begin, m.face_begin, e);
+        std::unique_ptr<DevBuf<uint4>> buf(new DevBuf<uint4>());
         CU(buf->upload(e.data(), e.size(), s->ctx->stream));
         CU(cudaStreamSynchronize(s->ctx->stream));
         it = s->mesh_edges.emplace(mesh_id, std::move(buf)).first;
@@ -123,12 +131,12 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         EdgeLaunch el; EdgeCtx &e = el.e;
         RC(mesh_edge_list(s, mesh_id, &e.edges, &e.n_edges));
         if (e.n_edges > 0) {
-            e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.02f; e.total_len = 0.f;
+            e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f; e.total_len = 0.f;
             double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
             for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
             DevBuf<float> len, cdf; DevBuf<uint8_t> tmp; size_t tmp_bytes = 0;
             CU(len.alloc(e.n_edges)); CU(cdf.alloc(e.n_edges));
-            k_edge_len<<<grid_for(e.n_edges), kBlock, 0, st>>>(s->dev, e, len.p); launches++;
+            k_edge_len<<<grid_for(e.n_edges), kBlock, 0, st>>>(s->dev, e, g.cam_o, len.p); launches++;
             CU(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, len.p, cdf.p, (int) e.n_edges, st));
             CU(tmp.alloc(tmp_bytes));
             CU(cub::DeviceScan::InclusiveSum(tmp.p, tmp_bytes, len.p, cdf.p, (int) e.n_edges, st)); launches++;

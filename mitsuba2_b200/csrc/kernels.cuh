@@ -287,9 +287,9 @@ k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQu
     if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
 }
 // boundary term of the vertex adjoint (adjoint.h): projected edge lengths, two primary rays per edge sample, scatter
-__global__ void k_edge_len(SceneDev sc, EdgeCtx e, float *len) {
+__global__ void k_edge_len(SceneDev sc, EdgeCtx e, float3 cam_o, float *len) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k < e.n_edges) len[k] = edge_len_body(sc, e, k);
+    if (k < e.n_edges) len[k] = edge_len_body(sc, e, cam_o, k);
 }
 __global__ void k_edge_raygen(SceneDev sc, SensorDev sn, EdgeCtx e, const float *total_len, RenderBatch b, PathQueue q, uint32_t *counters) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;

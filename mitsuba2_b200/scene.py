@@ -261,6 +261,8 @@ class Scene:
         A.check(A.lib().mtsb_render_grad(self._h, sensor, spp_begin, spp, spp_total, int(seed), pd, tex_id, pgt, mesh_id, pgv,
                                          mem, C.byref(st)))
         self.last_stats = st.as_dict()
+        if gv is not None:
+            gv = gv.reshape(-1, 3)
         return gt, gv
 
     # ---- parity hooks -----------------------------------------------------------------------------

@@ -600,12 +600,17 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
     if kind == "corner":
         P2, F2 = grid_mesh(2, 2, 3.0, [2.2, 0, -0.6], [0, 0, 1], [0, -1, 0])
         sd.add_mesh(Mesh(P2, F2, bsdf=bw))
+    if kind == "wavy":      # smooth-shaded height field filling the view, distant point light: shading follows the normals only
+        P, F = grid_mesh(12, 12, 8.0, [0, 0, 1.0], [1, 0, 0], [0, -1, 0])
+        P[:, 2] += 0.15 * np.sin(2.0 * P[:, 0]) * np.cos(1.5 * P[:, 1])
+        sd.add_mesh(Mesh(P, F, normals=M.compute_vertex_normals(P, F).astype(np.float32), bsdf=b))
+        sd.add_point([500.0, 1000.0, -1000.0], [8e6, 8e6, 8e6])
     if kind == "quadenv":
         P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P, F, bsdf=b))
         sd.add_constant([1.0, 1.0, 1.0])
     sd.add_perspective(look_at([0, 0, -3.0], [0, 0, 0], [0, 1, 0]), 40.0, 0.01, 100.0, res, res, "box")
-    sd.max_depth, sd.rr_depth, sd.spp = 4, 100, spp
+    sd.max_depth, sd.rr_depth, sd.spp = (2 if kind == "wavy" else 4), 100, spp
     return sd
 
 

@@ -328,17 +328,22 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     if (!grad_vertices || !boundary) return;
     // ---- boundary term: unique edges of the mesh, projected-length cdf, two paths per edge sample
     const MeshDev &m = s->meshes[mesh_id];
-    std::vector<uint64_t> keys;
+    // same construction as build_edge_list() in grad.cuh
+    std::vector<std::pair<uint64_t, uint32_t>> keys;
     for (uint32_t f = 0; f < m.face_count; ++f) { uint4 fc = s->faces[m.face_begin + f]; uint32_t v[3] = { fc.x, fc.y, fc.z };
-        for (int k = 0; k < 3; ++k) { uint32_t a = v[k], c = v[(k + 1) % 3]; if (a > c) std::swap(a, c); keys.push_back(((uint64_t) a << 32) | c); } }
-    std::sort(keys.begin(), keys.end()); keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
-    std::vector<uint2> edges(keys.size());
-    for (size_t k = 0; k < keys.size(); ++k) edges[k] = make_uint2((uint32_t) (keys[k] >> 32), (uint32_t) keys[k]);
-    EdgeCtx e; e.edges = edges.data(); e.n_edges = (uint32_t) edges.size(); e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.02f;
+        for (int k = 0; k < 3; ++k) { uint32_t a = v[k], c = v[(k + 1) % 3]; if (a > c) std::swap(a, c); keys.emplace_back(((uint64_t) a << 32) | c, m.face_begin + f); } }
+    std::sort(keys.begin(), keys.end());
+    std::vector<uint4> edges;
+    for (size_t i = 0; i < keys.size();) {
+        size_t j = i + 1; while (j < keys.size() && keys[j].first == keys[i].first) ++j;
+        edges.push_back(make_uint4((uint32_t) (keys[i].first >> 32), (uint32_t) keys[i].first, keys[i].second, j - i > 1 ? keys[i + 1].second : 0xffffffffu));
+        i = j;
+    }
+    EdgeCtx e; e.edges = edges.data(); e.n_edges = (uint32_t) edges.size(); e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f;
     double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
     for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
     std::vector<float> cdf(edges.size()); double acc = 0;
-    for (uint32_t k = 0; k < e.n_edges; ++k) { acc += edge_len_body(s->dev, e, k); cdf[k] = (float) acc; }
+    for (uint32_t k = 0; k < e.n_edges; ++k) { acc += edge_len_body(s->dev, e, g.cam_o, k); cdf[k] = (float) acc; }
     e.cdf = cdf.data(); e.total_len = (float) acc;
     uint64_t nb_total = std::max<uint64_t>(1, (uint64_t) ((double) npix * spp_total * edge_fraction));
     uint64_t nb_first = (uint64_t) ((double) npix * spp_begin * edge_fraction), nb_end = (uint64_t) ((double) npix * (spp_begin + spp_count) * edge_fraction);

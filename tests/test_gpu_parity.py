@@ -268,7 +268,7 @@ def test_vertex_gradient_interior_matches_host_replay(mi, kind, bsdf):
     sc = mi.Scene(sd)
     sc.grad_config(boundary=False)
     _, g = sc.render_grad(wgt, spp=32, seed=3, mesh_id=0)
-    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=False)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=False).reshape(-1, 3)
     assert np.isfinite(g).all() and np.abs(g).max() > 0
     np.testing.assert_allclose(g, gh, rtol=2e-2, atol=2e-3 * np.abs(gh).max())
     P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
@@ -289,7 +289,7 @@ def test_vertex_gradient_boundary_matches_host_replay_and_fd(mi):
     sc = mi.Scene(sd)
     sc.grad_config(boundary=True, edge_fraction=1.0)
     _, g = sc.render_grad(wgt, spp=128, seed=3, mesh_id=0)
-    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=True, edge_fraction=1.0)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=True, edge_fraction=1.0).reshape(-1, 3)
     np.testing.assert_allclose(g, gh, rtol=2e-2, atol=5e-3 * np.abs(gh).max())
     P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
     F = H.displacement_fields(P0)

@@ -80,6 +80,23 @@ def test_vertex_gradient_interior_point_light_matches_fd(bsdf):
         assert abs(float((g * F[name]).sum())) < 1e-3
 
 
+def test_vertex_gradient_smooth_normals_matches_fd():
+    """Smooth-shaded mesh, direct light only: at a fixed pixel the hit point slides over the triangle, so the interpolated
+    normal changes through the barycentrics (exact), and vertex normals are re-derived from the moved positions by
+    `parameters_changed` (mesh.cpp:794-804) -- modelled as turning rigidly with the face (approximation; exact for rigid
+    motions).  FD = oracle with recomputed normals.  5 % of the largest derivative."""
+    sd = H.vgrad_scene("wavy", "diffuse", res=16, spp=8)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    g = HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=True).reshape(-1, 3)     # no silhouette in view: boundary = 0
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 1e-3, 8, 3) for n in F}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < 0.05 * ref, (n, fd)
+    assert abs(float((g * F["tilt"]).sum()) - fds["tilt"]) < 0.02 * abs(fds["tilt"])
+
+
 def test_vertex_gradient_area_light_and_indirect_matches_fd_statistically():
     """Area light + a wall (MIS, emitter hits, one indirect bounce): the detached adjoint and the same-seed finite
     difference are different estimators of the same derivative; they must agree within 4 standard errors over seeds."""
