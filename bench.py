@@ -83,7 +83,6 @@ def side_metrics(mi, local):
         if i >= 2:
             ms.append(sc4.last_stats["ms_total"])
             stages = {k: sc4.last_stats[k] for k in ("ms_closest", "ms_shade", "ms_any", "ms_raygen")}
-    sc4.set_profiling(False)
     out["c4_gradient_pass_texture_and_vertices_ms"] = float(np.median(ms))
     out["c4_gradient_pass_texture_and_vertices_stage_ms"] = stages
     out["c4_sphere_triangles"] = int(len(sd4.meshes[mid].faces))
@@ -103,6 +102,7 @@ def spectral_metric(mi, local, spp=16, steps=3, warmup=2):
     t0 = time.time()
     sc = mi.Scene(sd, device=local)
     out = {"c3_spectral_scene_setup_s": time.time() - t0}
+    sc.set_profiling(True)
     ms, stages = [], {}
     for i in range(warmup + steps):
         sc.film_clear()

@@ -32,8 +32,9 @@ def main():
     ap.add_argument("--spp", type=int, default=16)
     ap.add_argument("--tex", type=int, default=64)
     ap.add_argument("--param", choices=("vertices", "texture"), default="vertices")
-    ap.add_argument("--sphere", type=int, default=40, help="latitude bands of the sphere (longitude = 2x)")
+    ap.add_argument("--sphere", type=int, default=16, help="latitude bands of the sphere (longitude = 2x)")
     ap.add_argument("--lr", type=float, default=None)
+    ap.add_argument("--smooth", type=int, default=8, help="Jacobi sweeps of gradient smoothing over the mesh (vertices mode)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -64,6 +65,21 @@ def main():
         start = c0 + 0.8 * (truth - c0) + torch.tensor([[0.06 * size, 0.04 * size, 0.0]], device=truth.device)
         param = start.clone().requires_grad_(True)
         lr = args.lr or 0.004 * size
+        # per-vertex Monte Carlo gradients are noisy (a vertex sees a handful of pixels): low-pass them over the mesh
+        # before Adam (a few Jacobi sweeps of g_i <- mean of g over the closed 1-ring), as mesh-based inverse rendering
+        # commonly does; the gradient itself is what mtsb_render_grad returns
+        fc = torch.from_numpy(np.asarray(sd.meshes[mid].faces, np.int64).reshape(-1, 3)).cuda(local)
+        ii = torch.cat([fc[:, 0], fc[:, 1], fc[:, 2], fc[:, 1], fc[:, 2], fc[:, 0]])
+        jj = torch.cat([fc[:, 1], fc[:, 2], fc[:, 0], fc[:, 0], fc[:, 1], fc[:, 2]])
+        nv = truth.shape[0]
+        adj = torch.sparse_coo_tensor(torch.stack([ii, jj]), torch.ones(ii.numel(), device=ii.device), (nv, nv)).coalesce()
+        adj = torch.sparse_coo_tensor(adj.indices(), torch.ones_like(adj.values()), (nv, nv))
+        deg = torch.sparse.sum(adj, 1).to_dense().unsqueeze(1)
+
+        def smooth(gv, sweeps=args.smooth):
+            for _ in range(sweeps):
+                gv = (gv + torch.sparse.mm(adj, gv)) / (1.0 + deg)
+            return gv
     opt = torch.optim.Adam([param], lr=lr)
     for it in range(args.iters):
         opt.zero_grad()
@@ -75,6 +91,8 @@ def main():
         loss.backward()
         if world > 1:                              # sum the per-view gradients; identical update everywhere
             distributed.allreduce_gradients([param.grad])
+        if args.param == "vertices":
+            param.grad.copy_(smooth(param.grad))
         opt.step()
         if args.param == "texture":
             with torch.no_grad():
