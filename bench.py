@@ -159,12 +159,13 @@ def parity_gates(mi, local):
     g["texture_grad_rel_l2_vs_fd"] = float(np.linalg.norm(fd - an) / np.linalg.norm(fd))
     # vertex-position adjoint vs central finite differences of the oracle along global displacement fields:
     # interior term (plane under a point light: same estimator sample by sample) and boundary term (quad on a background)
-    for kind, fields, eps, fd_spp, name in (("plane", ("tz", "tilt"), 2e-3, 32, "interior"), ("quadenv", ("tx", "ty", "scale"), 0.02, 1024, "boundary")):
+    for kind, fields, eps, fd_spp, name in (("plane", ("tz", "tilt"), 2e-3, 32, "interior"), ("quadenv", ("tx", "ty", "scale"), 0.02, 1024, "boundary"),
+                                        ("quadshadow", ("tx", "tz", "scale"), 0.02, 1024, "shadow_boundary")):
         sdv = H.vgrad_scene(kind, "ggx" if kind == "plane" else "diffuse", res=16, spp=32 if kind == "plane" else 128)
         yy, xx = np.mgrid[0:16, 0:16]
         w = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
         scv = mi.Scene(sdv, device=local)
-        scv.grad_config(boundary=(kind != "plane"), edge_fraction=1.0)
+        scv.grad_config(boundary=(0 if kind == "plane" else 2), edge_fraction=1.0)
         _, gv = scv.render_grad(w, seed=3, mesh_id=0)
         P0 = np.asarray(sdv.meshes[0].positions, np.float32).reshape(-1, 3)
         F = H.displacement_fields(P0)

@@ -208,14 +208,15 @@ int mtsb_film_device_ptr(mtsb_scene *scene, uint32_t sensor_id, void **ptr, uint
  * dL_dimage: width*height*3 float32 = dL/d(developed linear RGB).  Outputs are ACCUMULATED:
  * grad_texture (size of texture `tex_id`), grad_vertices (3*vertex_count of mesh `mesh_id`, the parameter the reference
  * exposes as `<mesh>.vertex_positions_buf`, src/librender/mesh.cpp:781-804); either may be NULL.
- * Vertex gradients = interior term (path-space adjoint) + primary-visibility boundary term (edge sampling), see
+ * Vertex gradients = interior term (path-space adjoint) + boundary terms (edge sampling on the film and from x1), see
  * mitsuba2_b200/csrc/adjoint.h; the box reconstruction filter and MTSB_MODE_RGB are required. */
 int mtsb_render_grad(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
                      uint32_t spp_total, uint64_t seed, const float *dL_dimage,
                      int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,
                      int mem, mtsb_stats *stats);
-/* Options of the vertex-gradient pass: boundary = 0 drops the edge-sampling term (interior term only, for tests);
- * edge_fraction = edge samples per path sample (default 0.25; each edge sample traces two paths). */
+/* Options of the vertex-gradient pass: boundary = 0 interior term only, 1 = + edge sampling on the film (primary
+ * visibility), 2 (default) = + edge sampling seen from the first path vertex (shadow / occlusion boundaries);
+ * edge_fraction = edge samples of each kind per path sample (default 0.25). */
 int mtsb_grad_config(mtsb_scene *scene, int boundary, float edge_fraction);
 
 /* ---- batched parity hooks (device math called exactly as the kernels call it) ------- */

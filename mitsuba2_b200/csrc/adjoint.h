@@ -369,4 +369,125 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
     }
 }
 
+// ---- boundary term seen from the first path vertex: edge sampling in the direction domain of x1 ---------------------------
+// The interior term integrates x2.. over triangle areas with fixed barycentrics, so what is left at a visibility boundary is
+// the far side only:  at a silhouette edge (as seen from x1) of the differentiated mesh the region of directions that see
+// the surface BEHIND the edge shrinks or grows, with the edge's angular velocity measured relative to the material point
+// x2 seen behind it (the occluder's own side moves with its material -- no term):
+//     dPhi += - dL/dI . f_s(x1, wi, w) cos . L_far(w) * n_out . [ (dp - dx1)/r - (dx2 - dx1)/r2 ] * |dw/dt| / P(edge, t)
+// w = direction to the edge point p = a + t (b - a), r = |p - x1|, n_out = unit normal of the plane (x1, a, b) pointing away
+// from the occluding face, x2 = first hit of the ray just outside the edge (r2 = its distance; infinite for a miss),
+// L_far = full incident radiance along that ray (path-traced by the normal wavefront from depth 2, emitter hits unweighted).
+// Edges are drawn by resampling: `candidates` edges proportional to their 3D length, one of those that are silhouettes from
+// x1 kept uniformly, P = (len / total) * candidates / (silhouette candidates).  Covers moving shadow boundaries and occlusion
+// of indirect light as seen directly by the camera; deeper vertices are not sampled.
+struct Edge2Ctx {
+    const uint4 *edges; uint32_t n_edges; const float *cdf; float total_len;   // cdf over 3D edge lengths
+    int candidates; float eps;                                                 // eps: angular offset of the far ray
+    float4 *aux;                     // 4 x float4 per sample: (edge, t, |dw/dt| / P, valid) | x2 (prim, b1, b2, r2) | d | hit of x1
+};
+HD float edge_len3_body(const SceneDev &sc, const Edge2Ctx &e, uint32_t k) {
+    uint4 ed = e.edges[k];
+    float l = norm(ld3(sc.pos, ed.y) - ld3(sc.pos, ed.x));
+    return l < 1e30f ? l : 0.f;
+}
+struct Edge2Geo { float3 a, b, p, w, n_out; float r, dwdt; bool silhouette; };
+// geometry of edge `ed` at parameter t seen from x; silhouette = its faces look opposite ways from x (or it is a border)
+HD Edge2Geo edge2_geo(const SceneDev &sc, uint4 ed, float t, float3 x) {
+    Edge2Geo g; g.a = ld3(sc.pos, ed.x); g.b = ld3(sc.pos, ed.y);
+    TriGeo f0 = tri_geo(sc, ed.z);
+    float s0 = dot(f0.N, g.a - x);
+    g.silhouette = true;
+    uint32_t front = ed.z;                  // the face that looks at x occludes; the far region is on the other side of the edge
+    if (ed.w != 0xffffffffu) {
+        float s1 = dot(tri_geo(sc, ed.w).N, g.a - x);
+        g.silhouette = (s0 < 0.f) != (s1 < 0.f);
+        if (!(s0 < 0.f)) front = ed.w;
+    }
+    g.p = g.a + (g.b - g.a) * t;
+    float3 dp = g.p - x; g.r = norm(dp); g.w = dp / g.r;
+    float3 ne = cross(g.a - x, g.b - x); float ln = norm(ne);
+    if (!(ln > 0.f) || !(g.r > 0.f)) { g.silhouette = false; g.n_out = mk3(0.f); g.dwdt = 0.f; return g; }
+    ne = ne / ln;
+    uint4 ff = sc.faces[front];             // third vertex of the occluding face tells its side
+    uint32_t third = (ff.x != ed.x && ff.x != ed.y) ? ff.x : ((ff.y != ed.x && ff.y != ed.y) ? ff.y : ff.z);
+    g.n_out = dot(ne, ld3(sc.pos, third) - g.a) > 0.f ? -ne : ne;
+    float3 e = g.b - g.a; float3 pe = e - g.w * dot(g.w, e);
+    g.dwdt = norm(pe) / g.r;
+    return g;
+}
+// stage B: queue entry j holds the camera ray, its hit and the sampler state; writes the far ray as a depth-2 path
+HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBatch &b, const PathQueue &qin, const PathQueue &qout, uint32_t j) {
+    float4 o4 = qin.o_mint[j], d4 = qin.d_maxt[j], h4 = qin.hit[j];
+    Pcg32 rng = rng_load(qin.rng[j]);
+    float4 rec0 = make_float4(0.f, 0.f, 0.f, 0.f), rec1 = make_float4(u2f(0xffffffffu), 0.f, 0.f, INFINITY);
+    float4 ro = make_float4(0.f, 0.f, 0.f, INFINITY), rd = make_float4(0.f, 0.f, 1.f, 0.f);
+    SI si = make_si(sc, xyz(o4), xyz(d4), h4);
+    bool ok = si.valid && e.n_edges > 0 && e.total_len > 0.f;
+    BsdfDev bsdf;
+    if (ok) { bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf]; ok = bsdf.type != 2 && (bsdf.two_sided ? si.wi.z != 0.f : si.wi.z > 0.f); }
+    uint32_t chosen = 0, n_sil = 0;
+    for (int c = 0; c < e.candidates; ++c) {          // same number of draws whatever happens: the stream stays aligned
+        float u = rng.next_f32(), pick = rng.next_f32();
+        if (!ok) continue;
+        float value = u * e.total_len; const float *cdf = e.cdf;
+        uint32_t k = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
+        if (!edge2_geo(sc, e.edges[k], 0.5f, si.p).silhouette) continue;
+        n_sil++;
+        if (pick * (float) n_sil < 1.f) chosen = k;      // reservoir: keeps each silhouette candidate with equal probability
+    }
+    float t = rng.next_f32();
+    if (ok && n_sil > 0) {
+        uint4 ed = e.edges[chosen];
+        Edge2Geo g = edge2_geo(sc, ed, t, si.p);
+        float len = norm(g.b - g.a);
+        float mint = kRayEpsilon * (1.f + hmax(abs3(si.p)));
+        uint2 fast[8]; TravStack<8, 56> st; st.fast = fast; st.stride = 1; Hit h;
+        bool vis = g.silhouette && len > 0.f && dot(g.w, si.sh.n) * si.wi.z > 0.f &&
+                   !bvh_trace<true>(sc.bvh, si.p, g.w, mint, g.r * (1.f - 1e-3f), st, h);
+        if (vis) {
+            float3 wf = normalize(g.w + g.n_out * e.eps);
+            bool hit2 = bvh_trace<false>(sc.bvh, si.p, wf, mint, INFINITY, st, h);
+            if (!hit2 || h.t > g.r * (1.f - 1e-3f)) {     // the ray really passes the edge
+                float inv_p = (e.total_len / len) * ((float) n_sil / (float) e.candidates);
+                rec0 = make_float4(u2f(chosen), t, g.dwdt * inv_p, 1.f);
+                if (hit2) rec1 = make_float4(u2f(h.prim), h.u, h.v, h.t);
+                ro = mk4(si.p, mint); rd = mk4(wf, INFINITY);
+            }
+        }
+    }
+    e.aux[4 * (size_t) j] = rec0; e.aux[4 * (size_t) j + 1] = rec1; e.aux[4 * (size_t) j + 2] = d4; e.aux[4 * (size_t) j + 3] = h4;
+    qout.o_mint[j] = ro; qout.d_maxt[j] = rd; qout.thr_eta[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+    qout.misc[j] = make_uint4(j, 2u | 0x80000000u, f2u(1.f), 0u);      // depth 2 after a "delta" bounce: emitter hits count fully
+    rng_store(&qout.rng[j], rng);
+    b.result[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+template <typename Add>
+HD void edge2_scatter_body(const SceneDev &sc, const Edge2Ctx &e, const GradCtx &g, const RenderBatch &b, uint32_t j, Add add) {
+    float4 rec0 = e.aux[4 * (size_t) j];
+    if (rec0.w == 0.f) return;
+    float4 rec1 = e.aux[4 * (size_t) j + 1], d4 = e.aux[4 * (size_t) j + 2], h4 = e.aux[4 * (size_t) j + 3];
+    SI si = make_si(sc, g.cam_o, xyz(d4), h4);
+    uint4 ed = e.edges[f2u(rec0.x)];
+    Edge2Geo eg = edge2_geo(sc, ed, rec0.y, si.p);
+    const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
+    float3 val; float pdf;
+    bsdf_eval_pdf(sc, bsdf, si, si.sh.to_local(eg.w), val, pdf);
+    float4 L = b.result[j];
+    uint32_t pixel = (uint32_t) ((b.offset + j) / b.spp_batch);
+    float3 dI = ld3(g.dL_dimage, pixel);
+    float c = -(dI.x * val.x * L.x + dI.y * val.y * L.y + dI.z * val.z * L.z) * g.scale * rec0.z;
+    if (c == 0.f || !(fabsf(c) < 1e30f)) return;
+    float inv_r = 1.f / eg.r, inv_r2 = rec1.w < INFINITY ? 1.f / rec1.w : 0.f;
+    float3 gp = eg.n_out * (c * inv_r);
+    add_vertex(g, ed.x, gp * (1.f - rec0.y), add); add_vertex(g, ed.y, gp * rec0.y, add);
+    VtxRec r1; r1.prim = si.prim; r1.b1 = h4.y; r1.b2 = h4.z;
+    scatter_point(g, tri_geo(sc, r1.prim), r1, true, si.p, eg.n_out * (c * (inv_r2 - inv_r)), add);
+    if (inv_r2 > 0.f) {
+        VtxRec r2; r2.prim = f2u(rec1.x); r2.b1 = rec1.y; r2.b2 = rec1.z;
+        TriGeo t2 = tri_geo(sc, r2.prim);
+        scatter_point(g, t2, r2, false, tri_point(t2, r2), eg.n_out * (-c * inv_r2), add);
+    }
+}
+
 } // namespace mtsb

@@ -97,7 +97,8 @@ struct mtsb_scene {
     DevBuf<uint4> q_misc[2], q_rng[2];
     DevBuf<float4> q_p1[2], q_p2[2];         // vertex-gradient replay: previous two path vertices per queue entry
     std::map<int, std::unique_ptr<DevBuf<uint4>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
-    int grad_boundary = 1; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
+    int grad_boundary = 2; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
+    DevBuf<float4> edge_aux;                 // boundary term seen from x1: 4 float4 per sample
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;
     float3 bbox_lo, bbox_hi;
@@ -576,8 +577,9 @@ static PathQueue make_queue(mtsb_scene *s, int k) {
 // One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
 // (k_shade_grad scatters texel gradients); `splat` adds the finished paths to the film.
 struct EdgeLaunch { EdgeCtx e; const float *total_len; };     // primary rays come from edge samples instead of the film
+struct Edge2Launch { Edge2Ctx e; const float *total_len; };   // depth-2 rays come from edge samples seen from the primary hits
 static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches,
-                     const EdgeLaunch *edge = nullptr) {
+                     const EdgeLaunch *edge = nullptr, const Edge2Launch *edge2 = nullptr) {
     cudaStream_t st = s->ctx->stream;
     const uint32_t n = b.n_paths;
     ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
@@ -590,7 +592,14 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     else
     { StageTimer t(s->ctx, ST_RAYGEN); if (s->spectral) k_raygen<Spectral><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p);
       else k_raygen<Rgb><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
-    for (int depth = 1; depth <= max_iter; ++depth) {
+    int depth0 = 1;
+    if (edge2) {      // primary hits, then one far ray per sample as the depth-2 entry of the other queue
+        PathQueue q0 = make_queue(s, 0), q1 = make_queue(s, 1);
+        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p); }
+        { StageTimer t(s->ctx, ST_SHADE); k_edge2_raygen<<<grid_for(n), kBlock, 0, st>>>(s->dev, edge2->e, edge2->total_len, b, q0, q1, s->counters.p); }
+        launches += 2; cur = 1; depth0 = 2;
+    }
+    for (int depth = depth0; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
         { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE);

@@ -59,10 +59,11 @@ static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint4 **edges, uint3
     return MTSB_OK;
 }
 
-/* boundary: 0 = interior term only, 1 = + primary-visibility edge sampling; edge_fraction = edge samples per path sample */
+/* boundary: 0 = interior term only, 1 = + primary-visibility edge sampling, 2 = + edge sampling seen from the first path
+ * vertex (shadow / occlusion boundaries); edge_fraction = edge samples per path sample */
 extern "C" int mtsb_grad_config(mtsb_scene *s, int boundary, float edge_fraction) {
     CHECK_ARG(s && edge_fraction >= 0.f && edge_fraction <= 64.f);
-    s->grad_boundary = boundary; s->grad_edge_fraction = edge_fraction;
+    s->grad_boundary = boundary < 0 ? 0 : boundary; s->grad_edge_fraction = edge_fraction;
     return MTSB_OK;
 }
 
@@ -155,6 +156,31 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
                 RC(run_batch(s, sn, b, nullptr, false, launches, &el));
                 k_edge_scatter<<<grid_for(nb), kBlock, 0, st>>>(s->dev, e, el.total_len, g, s->result.p, nb); launches++;
                 edge_samples += nb;
+            }
+            // ---- boundary term seen from the first path vertex (moving shadow / occlusion boundaries)
+            if (s->grad_boundary >= 2) {
+                Edge2Launch l2; Edge2Ctx &e2 = l2.e;
+                e2.edges = e.edges; e2.n_edges = e.n_edges; e2.candidates = 16; e2.eps = 1e-3f; e2.total_len = 0.f;
+                DevBuf<float> len3, cdf3;
+                CU(len3.alloc(e.n_edges)); CU(cdf3.alloc(e.n_edges));
+                k_edge_len3<<<grid_for(e.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;
+                CU(cub::DeviceScan::InclusiveSum(tmp.p, tmp_bytes, len3.p, cdf3.p, (int) e.n_edges, st)); launches++;
+                e2.cdf = cdf3.p; l2.total_len = cdf3.p + (e.n_edges - 1);
+                CU(s->edge_aux.alloc(4 * (size_t) s->pool)); e2.aux = s->edge_aux.p;
+                // sample counts per pixel follow the path samples: the same (begin, count, total) split, scaled
+                uint32_t s2_total = (uint32_t) ceil((double) spp_total * frac); if (s2_total < 1) s2_total = 1;
+                uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
+                GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
+                uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
+                for (uint64_t off = 0; off < total2; off += s->pool) {
+                    uint32_t n2 = (uint32_t) ((total2 - off) < s->pool ? (total2 - off) : s->pool);
+                    RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
+                    b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = s->result.p;
+                    RC(run_batch(s, sn, b, nullptr, false, launches, nullptr, &l2));
+                    k_edge2_scatter<<<grid_for(n2), kBlock, 0, st>>>(s->dev, e2, g2, b); launches++;
+                    edge_samples += n2 / 2;
+                }
+                CU(cudaStreamSynchronize(st));
             }
             CU(cudaStreamSynchronize(st));       // len / cdf / tmp are released at scope exit
         }

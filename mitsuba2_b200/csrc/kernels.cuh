@@ -393,6 +393,22 @@ __global__ void k_film_develop(SensorDev sn, float *rgb) {
     rgb[3 * i + 2] = 0.055648f * X - 0.204043f * Y + 1.057311f * Z;
 }
 
+// boundary term seen from x1 (adjoint.h): 3D edge lengths, far-ray generation from the primary hits, scatter
+__global__ void k_edge_len3(SceneDev sc, Edge2Ctx e, float *len) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < e.n_edges) len[k] = edge_len3_body(sc, e, k);
+}
+__global__ void k_edge2_raygen(SceneDev sc, Edge2Ctx e, const float *total_len, RenderBatch b, PathQueue qin, PathQueue qout, uint32_t *counters) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0) counters[2] = b.n_paths;
+    e.total_len = *total_len;
+    if (j < b.n_paths) edge2_raygen_body(sc, e, b, qin, qout, j);
+}
+__global__ void k_edge2_scatter(SceneDev sc, Edge2Ctx e, GradCtx g, RenderBatch b) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < b.n_paths) edge2_scatter_body(sc, e, g, b, j, DevAdd());
+}
+
 // ---------------- parity hooks -------------------------------------------------------------------
 __global__ void k_pcg32(uint32_t n, const uint64_t *initstate, const uint64_t *initseq, uint32_t n_draws, float *out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

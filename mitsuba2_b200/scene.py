@@ -226,10 +226,12 @@ class Scene:
         A.check(A.lib().mtsb_scene_update_texture(self._h, tex_id, p, mem))
 
     # ---- gradient pass ----------------------------------------------------------------------------
-    def grad_config(self, boundary=True, edge_fraction=0.25):
-        """Options of the vertex-gradient pass: `boundary` = add the primary-visibility edge-sampling term,
-        `edge_fraction` = edge samples per path sample."""
-        A.check(A.lib().mtsb_grad_config(self._h, int(bool(boundary)), float(edge_fraction)))
+    def grad_config(self, boundary=2, edge_fraction=0.25):
+        """Options of the vertex-gradient pass: `boundary` 0 / False = interior term only, 1 = + edge sampling on the film
+        (primary visibility), 2 / True = + edge sampling seen from the first path vertex (shadows, occlusion);
+        `edge_fraction` = edge samples of each kind per path sample."""
+        boundary = 2 if boundary is True else int(boundary)
+        A.check(A.lib().mtsb_grad_config(self._h, boundary, float(edge_fraction)))
 
     def render_grad(self, dL_dimage, sensor=0, spp=None, seed=0, tex_id=-1, mesh_id=-1, spp_begin=0, spp_total=None):
         """Adjoint of `render`: returns (d/d texture `tex_id`, d/d vertex positions of mesh `mesh_id`) of

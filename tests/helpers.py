@@ -605,6 +605,12 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         P[:, 2] += 0.15 * np.sin(2.0 * P[:, 0]) * np.cos(1.5 * P[:, 1])
         sd.add_mesh(Mesh(P, F, normals=M.compute_vertex_normals(P, F).astype(np.float32), bsdf=b))
         sd.add_point([500.0, 1000.0, -1000.0], [8e6, 8e6, 8e6])
+    if kind == "quadshadow":      # quad above a lit plane under a constant sky: its shadow on the plane moves with it
+        P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
+        sd.add_mesh(Mesh(P, F, bsdf=b))
+        P2, F2 = grid_mesh(1, 1, 12.0, [0, 0, 2.0], [1, 0, 0], [0, -1, 0])
+        sd.add_mesh(Mesh(P2, F2, bsdf=bw))
+        sd.add_constant([1.0, 1.0, 1.0])
     if kind == "quadenv":
         P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P, F, bsdf=b))

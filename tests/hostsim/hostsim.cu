@@ -241,11 +241,22 @@ struct HsPool {
                              q.prev1 = p1[k].data(); q.prev2 = p2[k].data(); return q; }
 };
 template <typename M, typename GradFn>
-static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad, bool raygen = true) {
+static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad, bool raygen = true,
+                         const Edge2Ctx *edge2 = nullptr) {
     std::vector<uint2> fast(8);
-    uint32_t n = b.n_paths; int cur = 0; uint32_t count = n;
+    uint32_t n = b.n_paths; int cur = 0, depth0 = 1; uint32_t count = n;
     if (raygen) for (uint32_t i = 0; i < n; ++i) raygen_body<M>(sn, b, P.queue(cur), i);
-    for (int depth = 1; count > 0 && depth <= s->dev.max_depth; ++depth) {
+    if (edge2) {       // run_batch(edge2) in api.cu: primary hits, then the far rays as depth-2 entries of the other queue
+        PathQueue q0 = P.queue(0), q1 = P.queue(1);
+        for (uint32_t i = 0; i < n; ++i) {
+            TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
+            bvh_trace<false>(s->dev.bvh, xyz(q0.o_mint[i]), xyz(q0.d_maxt[i]), q0.o_mint[i].w, q0.d_maxt[i].w, st, h);
+            q0.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
+        }
+        for (uint32_t i = 0; i < n; ++i) edge2_raygen_body(s->dev, *edge2, b, q0, q1, i);
+        cur = 1; depth0 = 2;
+    }
+    for (int depth = depth0; count > 0 && depth <= s->dev.max_depth; ++depth) {
         PathQueue qin = P.queue(cur), qout = P.queue(cur ^ 1);
         for (uint32_t i = 0; i < count; ++i) {
             TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
@@ -357,6 +368,24 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         for (uint32_t j = 0; j < nb; ++j) edge_raygen_body(s->dev, sn, e, b, P.queue(0), j);
         hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad(), false);
         for (uint32_t j = 0; j < nb; ++j) edge_scatter_body(s->dev, e, g, P.result.data(), j, HostAdd());
+    }
+    if (boundary < 2) return;
+    // ---- boundary term seen from the first path vertex (same sequence as mtsb_render_grad)
+    Edge2Ctx e2; e2.edges = edges.data(); e2.n_edges = (uint32_t) edges.size(); e2.candidates = 16; e2.eps = 1e-3f;
+    std::vector<float> cdf3(edges.size()); acc = 0;
+    for (uint32_t k = 0; k < e2.n_edges; ++k) { acc += edge_len3_body(s->dev, e2, k); cdf3[k] = (float) acc; }
+    e2.cdf = cdf3.data(); e2.total_len = (float) acc;
+    std::vector<float4> aux(4 * (size_t) pool); e2.aux = aux.data();
+    uint32_t s2_total = (uint32_t) ceil((double) spp_total * edge_fraction); if (s2_total < 1) s2_total = 1;
+    uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
+    GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
+    uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
+    for (uint64_t off = 0; off < total2; off += pool) {
+        uint32_t n2 = (uint32_t) std::min<uint64_t>(pool, total2 - off);
+        RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
+        b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = P.result.data();
+        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad(), true, &e2);
+        for (uint32_t j = 0; j < n2; ++j) edge2_scatter_body(s->dev, e2, g2, b, j, HostAdd());
     }
 }
 

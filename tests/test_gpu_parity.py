@@ -287,9 +287,9 @@ def test_vertex_gradient_boundary_matches_host_replay_and_fd(mi):
     yy, xx = np.mgrid[0:16, 0:16]
     wgt = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
     sc = mi.Scene(sd)
-    sc.grad_config(boundary=True, edge_fraction=1.0)
+    sc.grad_config(boundary=1, edge_fraction=1.0)
     _, g = sc.render_grad(wgt, spp=128, seed=3, mesh_id=0)
-    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=True, edge_fraction=1.0).reshape(-1, 3)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=1, edge_fraction=1.0).reshape(-1, 3)
     np.testing.assert_allclose(g, gh, rtol=2e-2, atol=5e-3 * np.abs(gh).max())
     P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
     F = H.displacement_fields(P0)
@@ -298,11 +298,30 @@ def test_vertex_gradient_boundary_matches_host_replay_and_fd(mi):
     for n, fd in fds.items():
         assert abs(float((g.reshape(-1, 3) * F[n]).sum()) - fd) < 0.06 * ref, (n, fd)
     # sample ranges of two calls add up to the single call
-    sc.grad_config(boundary=True, edge_fraction=0.5)
+    sc.grad_config(boundary=2, edge_fraction=0.5)
     _, full = sc.render_grad(wgt, spp=8, seed=2, mesh_id=0)
     _, p1 = sc.render_grad(wgt, spp=3, seed=2, mesh_id=0, spp_begin=0, spp_total=8)
     _, p2 = sc.render_grad(wgt, spp=5, seed=2, mesh_id=0, spp_begin=3, spp_total=8)
     np.testing.assert_allclose(p1 + p2, full, rtol=1e-3, atol=1e-4 * np.abs(full).max())
+
+
+def test_vertex_gradient_shadow_boundary_matches_host_replay_and_fd(mi):
+    """Boundary term seen from the first path vertex (moving shadow of a quad on a plane): GPU vs host simulator on the
+    same samples, and vs finite differences of the oracle (12 % of the largest derivative)."""
+    sd = H.vgrad_scene("quadshadow", "diffuse", res=16, spp=128)
+    yy, xx = np.mgrid[0:16, 0:16]
+    wgt = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
+    sc = mi.Scene(sd)
+    sc.grad_config(boundary=2, edge_fraction=1.0)
+    _, g = sc.render_grad(wgt, spp=128, seed=3, mesh_id=0)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=2, edge_fraction=1.0).reshape(-1, 3)
+    np.testing.assert_allclose(g, gh, rtol=2e-2, atol=1e-2 * np.abs(gh).max())
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "tz", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < 0.12 * ref, (n, fd)
 
 
 def test_vertex_gradient_rejects_unsupported(mi):

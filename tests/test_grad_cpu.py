@@ -130,13 +130,31 @@ def test_vertex_gradient_boundary_term_matches_fd():
         assert abs(float((gi * F[n]).sum())) < 0.01 * ref          # the interior term alone sees nothing
 
 
+def test_vertex_gradient_shadow_boundary_matches_fd():
+    """A quad floating above a lit plane: most of the derivative is the quad's moving shadow / sky occlusion on the plane,
+    i.e. the boundary term seen from the first path vertex (boundary=2).  Without it the scale derivative even has the
+    wrong sign.  FD of the oracle, wide step; tolerance 12 % of the largest derivative (Monte Carlo on both sides)."""
+    sd = H.vgrad_scene("quadshadow", "diffuse", res=16, spp=128)
+    wgt = _ramp(16)
+    h = HostSim(sd)
+    g2 = h.render_grad_vertices(wgt, 0, seed=3, boundary=2, edge_fraction=1.0).reshape(-1, 3)
+    g1 = h.render_grad_vertices(wgt, 0, seed=3, boundary=1, edge_fraction=1.0).reshape(-1, 3)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "tz", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((g2 * F[n]).sum()) - fd) < 0.12 * ref, (n, float((g2 * F[n]).sum()), fd)
+    assert abs(float((g1 * F["scale"]).sum()) - fds["scale"]) > 0.5 * ref      # the term matters here
+
+
 def test_vertex_gradient_sample_ranges_add_up():
     """Splitting the samples over two calls (ranks) gives the same gradient as one call: interior term exactly (float
     association), boundary term because edge-sample indices are derived from the sample range."""
-    sd = H.vgrad_scene("quadenv", "diffuse", res=8, spp=6)
+    sd = H.vgrad_scene("quadshadow", "diffuse", res=8, spp=6)
     wgt = _ramp(8)
     h = HostSim(sd)
-    full = h.render_grad_vertices(wgt, 0, seed=2, spp=6)
-    parts = h.render_grad_vertices(wgt, 0, seed=2, spp=2, spp_begin=0, spp_total=6) + \
-        h.render_grad_vertices(wgt, 0, seed=2, spp=4, spp_begin=2, spp_total=6)
+    full = h.render_grad_vertices(wgt, 0, seed=2, spp=6, boundary=2, edge_fraction=0.5)
+    parts = h.render_grad_vertices(wgt, 0, seed=2, spp=2, spp_begin=0, spp_total=6, boundary=2, edge_fraction=0.5) + \
+        h.render_grad_vertices(wgt, 0, seed=2, spp=4, spp_begin=2, spp_total=6, boundary=2, edge_fraction=0.5)
     assert np.allclose(full, parts, rtol=1e-4, atol=1e-5 * np.abs(full).max())
