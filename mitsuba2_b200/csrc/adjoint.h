@@ -5,7 +5,7 @@
 // Mesh::traverse / parameters_changed (src/librender/mesh.cpp:781-804).  `pathreparam` is not in the tree.
 // What this file does instead (no tape, O(pool) memory), in the wavefront replay of grad.cuh:
 //
-//   dI/dv = interior term + primary-visibility boundary term.
+//   dI/dv = interior term + boundary term on the film (primary visibility) + boundary term seen from x1 (shadows).
 //
 // * Interior term.  The pixel sample keeps its film position (x1 = camera ray ∩ moving triangle slides along the ray);
 //   every later vertex keeps its barycentric coordinates on the triangle it hit ("material" parameterisation), so the
@@ -21,8 +21,9 @@
 //   their projected length, the radiance on both sides of the edge is path-traced with common random numbers, and
 //   (L+ - L-) * dL/dI(pixel) * d(alpha)/dv is scattered to the two edge vertices (Li et al. 2018, primary visibility).
 //   Every edge is a candidate, so shading discontinuities of flat-shaded meshes are covered as well as silhouettes.
-// Not covered (documented in DESIGN.md): visibility changes seen from secondary vertices (moving shadow boundaries and
-// indirect occlusion), paths beyond a delta (dielectric) vertex, texture-coordinate sliding at x1, emitter meshes.
+// * Boundary term seen from the first path vertex (edge2_* bodies, end of this file): silhouette edges as seen from x1.
+// Not covered (documented in DESIGN.md): visibility changes seen from the second and later vertices, paths beyond a delta
+// (dielectric) vertex, texture-coordinate sliding at x1, mesh-mesh intersections, emitter meshes.
 #pragma once
 #include "path.h"
 
