@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 3
+#define MTSB_ABI_VERSION 4
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -104,15 +104,20 @@ typedef struct mtsb_mesh_desc {
 } mtsb_mesh_desc;
 
 /* Sensor + film: src/sensors/perspective.cpp:106-222, src/films/hdrfilm.cpp, rfilters. */
-enum { MTSB_RFILTER_BOX = 0, MTSB_RFILTER_TENT = 1, MTSB_RFILTER_GAUSSIAN = 2 };
+/* src/rfilters/{box,tent,gaussian,mitchell,catmullrom,lanczos}.cpp */
+enum { MTSB_RFILTER_BOX = 0, MTSB_RFILTER_TENT = 1, MTSB_RFILTER_GAUSSIAN = 2, MTSB_RFILTER_MITCHELL = 3, MTSB_RFILTER_CATMULLROM = 4,
+       MTSB_RFILTER_LANCZOS = 5 };
 typedef struct mtsb_sensor_desc {
     float    to_world[16];          /* row-major camera-to-world */
     float    sample_to_camera[16];  /* row-major, perspective.cpp:125-133 */
     float    near_clip, far_clip;
-    uint32_t film_width, film_height;   /* crop size == film size (crop windows: not yet) */
+    uint32_t film_width, film_height;   /* size of the rendered block = the film's crop window; the window's placement in the
+                                         * full film is folded into sample_to_camera (perspective.cpp:106-133) by the host */
     int32_t  rfilter;               /* MTSB_RFILTER_* */
-    float    rfilter_radius;        /* box: 0.5 (+RayEpsilon added internally), tent: 1, gaussian: 4*stddev */
-    float    rfilter_stddev;        /* gaussian */
+    float    rfilter_radius;        /* box: 0.5 (+RayEpsilon added internally), tent: 1, gaussian: 4*stddev, mitchell and
+                                     * catmullrom: 2, lanczos: number of lobes (default 3) */
+    float    rfilter_stddev;        /* gaussian: stddev; mitchell: B (default 1/3) */
+    float    rfilter_c;             /* mitchell: C (default 1/3)                      (since ABI 4) */
 } mtsb_sensor_desc;
 
 /* `MonteCarloIntegrator` props (src/librender/integrator.cpp:285-298). */

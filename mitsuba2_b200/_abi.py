@@ -16,7 +16,7 @@ MODE_RGB, MODE_SPECTRAL = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC = 0, 1, 2
 MF_BECKMANN, MF_GGX = 0, 1
 EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
-RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = 0, 1, 2
+RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN, RFILTER_MITCHELL, RFILTER_CATMULLROM, RFILTER_LANCZOS = 0, 1, 2, 3, 4, 5
 
 c_float_p = C.POINTER(C.c_float)
 c_u32_p = C.POINTER(C.c_uint32)
@@ -51,7 +51,7 @@ class MeshDesc(C.Structure):
 class SensorDesc(C.Structure):
     _fields_ = [("to_world", C.c_float * 16), ("sample_to_camera", C.c_float * 16), ("near_clip", C.c_float),
                 ("far_clip", C.c_float), ("film_width", C.c_uint32), ("film_height", C.c_uint32),
-                ("rfilter", C.c_int32), ("rfilter_radius", C.c_float), ("rfilter_stddev", C.c_float)]
+                ("rfilter", C.c_int32), ("rfilter_radius", C.c_float), ("rfilter_stddev", C.c_float), ("rfilter_c", C.c_float)]
 
 
 class IntegratorDesc(C.Structure):

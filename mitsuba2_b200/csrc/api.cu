@@ -462,7 +462,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         SensorDev &sn = sh->dev; memset(&sn, 0, sizeof(sn));
         memcpy(sn.to_world, sd.to_world, sizeof(sn.to_world)); memcpy(sn.sample_to_camera, sd.sample_to_camera, sizeof(sn.sample_to_camera));
         sn.near_clip = sd.near_clip; sn.far_clip = sd.far_clip; sn.width = sd.film_width; sn.height = sd.film_height;
-        sn.rfilter = sd.rfilter; sn.stddev = sd.rfilter_stddev;
+        sn.rfilter = sd.rfilter; sn.stddev = sd.rfilter_stddev; sn.filter_c = sd.rfilter_c;
         sn.radius = sd.rfilter == MTSB_RFILTER_BOX ? sd.rfilter_radius + kRayEpsilon : sd.rfilter_radius;
         size_t npx = (size_t) sn.width * sn.height;
         CU(sh->xyza.alloc(npx)); CU(sh->w.alloc(npx)); CU(sh->packed.alloc(5 * npx));

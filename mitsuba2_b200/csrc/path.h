@@ -254,6 +254,17 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
 HD float rfilter_eval(const SensorDev &sn, float x) {
     if (sn.rfilter == 0) return fabsf(x) <= sn.radius ? 1.f : 0.f;                 // src/rfilters/box.cpp:34-36
     if (sn.rfilter == 1) return fmaxf(0.f, 1.f - fabsf(x / sn.radius));            // src/rfilters/tent.cpp:33-35
+    if (sn.rfilter == 3 || sn.rfilter == 4) {                                      // mitchell.cpp:40-53, catmullrom.cpp:29-43
+        float B = sn.rfilter == 3 ? sn.stddev : 0.f, C = sn.rfilter == 3 ? sn.filter_c : 0.5f;
+        x = fabsf(x); float x2 = x * x, x3 = x2 * x;
+        float r = (1.f / 6.f) * (x < 1.f ? (12.f - 9.f * B - 6.f * C) * x3 + (-18.f + 12.f * B + 6.f * C) * x2 + (6.f - 2.f * B)
+                                         : (-B - 6.f * C) * x3 + (6.f * B + 30.f * C) * x2 + (-12.f * B - 48.f * C) * x + (8.f * B + 24.f * C));
+        return x < 2.f ? r : 0.f;
+    }
+    if (sn.rfilter == 5) {                                                         // lanczos.cpp:44-54
+        x = fabsf(x); float x1 = kPi * x, x2 = x1 / sn.radius;
+        return x < kEpsilon ? 1.f : (x > sn.radius ? 0.f : (sinf(x1) * sinf(x2)) / (x1 * x2));
+    }
     float alpha = -1.f / (2.f * sn.stddev * sn.stddev);                            // src/rfilters/gaussian.cpp:34-47
     return fmaxf(0.f, expf(alpha * x * x) - expf(alpha * sn.radius * sn.radius));
 }

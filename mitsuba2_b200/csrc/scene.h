@@ -39,7 +39,8 @@ struct SensorDev {
     float to_world[16], sample_to_camera[16];
     float near_clip, far_clip;
     uint32_t width, height;
-    int rfilter; float radius, stddev;   // radius already includes box RayEpsilon
+    int rfilter; float radius, stddev;   // radius already includes box RayEpsilon; stddev doubles as Mitchell's B
+    float filter_c;                      // Mitchell's C
     float4 *film_xyza; float *film_w;    // device film accumulators
 };
 struct SceneDev {

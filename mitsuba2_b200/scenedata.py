@@ -21,16 +21,18 @@ def _ptr(a, ty):
     return a.ctypes.data_as(ty) if a is not None else ty()
 
 
-def perspective_sample_to_camera(x_fov_deg, near, far, aspect):
-    """``PerspectiveCamera::update_camera_transforms`` (src/sensors/perspective.cpp:106-133), no crop window:
-    inverse of scale(-.5,-.5*aspect,1) * translate(-1,-1/aspect,0) * perspective(fov,near,far)
-    (``Transform::perspective``, include/mitsuba/core/transform.h:203-220)."""
+def perspective_sample_to_camera(x_fov_deg, near, far, aspect, rel_offset=(0.0, 0.0), rel_size=(1.0, 1.0)):
+    """``PerspectiveCamera::update_camera_transforms`` (src/sensors/perspective.cpp:106-133): inverse of
+    scale(1/rel_size) * translate(-rel_offset) * scale(-.5,-.5*aspect,1) * translate(-1,-1/aspect,0) *
+    perspective(fov,near,far) (``Transform::perspective``, include/mitsuba/core/transform.h:203-220); rel_offset /
+    rel_size = the film's crop window relative to the full film (aspect = full film width / height)."""
     tan = math.tan(math.radians(x_fov_deg * 0.5))
     inv_persp = np.array([[tan, 0, 0, 0], [0, tan, 0, 0], [0, 0, 0, 1],
                           [0, 0, (near - far) / (far * near), 1.0 / near]], dtype=np.float64)
     inv_trans = np.array([[1, 0, 0, 1], [0, 1, 0, 1.0 / aspect], [0, 0, 1, 0], [0, 0, 0, 1]], dtype=np.float64)
     inv_scale = np.diag([-2.0, -2.0 / aspect, 1.0, 1.0])
-    return (inv_persp @ inv_trans @ inv_scale).astype(np.float32)
+    inv_crop = np.array([[rel_size[0], 0, 0, rel_offset[0]], [0, rel_size[1], 0, rel_offset[1]], [0, 0, 1, 0], [0, 0, 0, 1]], dtype=np.float64)
+    return (inv_persp @ inv_trans @ inv_scale @ inv_crop).astype(np.float32)
 
 
 def parse_fov(fov=None, fov_axis="x", focal_length="50mm", aspect=1.0):
@@ -215,14 +217,25 @@ class SceneData:
                               "to_world": _f32(np.eye(4) if to_world is None else to_world).reshape(16), "scale": float(scale)})
         return len(self.emitters) - 1
 
-    def add_perspective(self, to_world, fov_x, near, far, width, height, rfilter="gaussian", stddev=0.5, radius=None):
-        kinds = {"box": A.RFILTER_BOX, "tent": A.RFILTER_TENT, "gaussian": A.RFILTER_GAUSSIAN}
+    def add_perspective(self, to_world, fov_x, near, far, width, height, rfilter="gaussian", stddev=0.5, radius=None,
+                        B=1.0 / 3.0, C=1.0 / 3.0, lobes=3, crop=None):
+        """`width` x `height` = the full film; `crop` = (offset_x, offset_y, crop_width, crop_height) renders only that
+        window (src/librender/film.cpp:16-44): the device film then has the crop's size."""
+        kinds = {"box": A.RFILTER_BOX, "tent": A.RFILTER_TENT, "gaussian": A.RFILTER_GAUSSIAN, "mitchell": A.RFILTER_MITCHELL,
+                 "catmullrom": A.RFILTER_CATMULLROM, "lanczos": A.RFILTER_LANCZOS}
         if radius is None:
-            radius = {"box": 0.5, "tent": 1.0, "gaussian": 4.0 * stddev}[rfilter]
+            radius = {"box": 0.5, "tent": 1.0, "gaussian": 4.0 * stddev, "mitchell": 2.0, "catmullrom": 2.0, "lanczos": float(lobes)}[rfilter]
+        cw, ch, rel_off, rel_size = int(width), int(height), (0.0, 0.0), (1.0, 1.0)
+        if crop is not None:
+            ox, oy, cw, ch = (int(v) for v in crop)
+            if ox < 0 or oy < 0 or cw <= 0 or ch <= 0 or ox + cw > width or oy + ch > height:
+                raise ValueError("invalid crop window")
+            rel_off, rel_size = (ox / width, oy / height), (cw / width, ch / height)
         self.sensors.append({"to_world": _f32(to_world).reshape(16),
-                             "sample_to_camera": perspective_sample_to_camera(fov_x, near, far, width / height).reshape(16),
-                             "near": float(near), "far": float(far), "width": int(width), "height": int(height),
-                             "rfilter": kinds[rfilter], "radius": float(radius), "stddev": float(stddev), "fov_x": float(fov_x)})
+                             "sample_to_camera": perspective_sample_to_camera(fov_x, near, far, width / height, rel_off, rel_size).reshape(16),
+                             "near": float(near), "far": float(far), "width": cw, "height": ch,
+                             "rfilter": kinds[rfilter], "radius": float(radius),
+                             "stddev": float(B if rfilter == "mitchell" else stddev), "filter_c": float(C), "fov_x": float(fov_x)})
         return len(self.sensors) - 1
 
     # ---- C struct -------------------------------------------------------------------------
@@ -332,6 +345,7 @@ class SceneData:
             sd[i].near_clip, sd[i].far_clip = s["near"], s["far"]
             sd[i].film_width, sd[i].film_height = s["width"], s["height"]
             sd[i].rfilter, sd[i].rfilter_radius, sd[i].rfilter_stddev = s["rfilter"], s["radius"], s["stddev"]
+            sd[i].rfilter_c = s.get("filter_c", 1.0 / 3.0)
         desc = A.SceneDesc()
         desc.n_meshes, desc.n_bsdfs, desc.n_textures = len(self.meshes), len(self.bsdfs), len(texs)
         desc.mode = A.MODE_SPECTRAL if spectral else A.MODE_RGB

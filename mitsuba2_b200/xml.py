@@ -4,7 +4,7 @@ Mirror of ``xml::load_file`` / ``load_string`` (include/mitsuba/core/xml.h:17-29
 ``$param`` substitution (``-Dkey=value``), ``<include>``, ``<ref>``, ``<transform>`` (translate/rotate/scale/lookat/matrix),
 typed properties, and the plugins named by the north star: shapes obj/ply (+ rectangle as two triangles), BSDFs
 diffuse/roughconductor/dielectric (+ ``twosided`` around the first two), emitters
-area/envmap/constant/point, sensor perspective, film hdrfilm, rfilters box/tent/gaussian, sampler independent, integrator path.
+area/envmap/constant/point, sensor perspective, film hdrfilm, rfilters box/tent/gaussian/mitchell/catmullrom/lanczos, film crop window, sampler independent, integrator path.
 Unknown plugins raise, like ``PluginManager`` does.
 """
 import math
@@ -292,14 +292,18 @@ class _Loader:
         rf = film.find("rfilter") if film is not None else None
         rtype = self.attr(rf, "type") if rf is not None else "gaussian"    # film.cpp:46-50
         rp = self.props(rf) if rf is not None else {}
-        if rtype not in ("box", "tent", "gaussian"):
-            raise NotImplementedError(f"rfilter '{rtype}' not yet supported")
+        if rtype not in ("box", "tent", "gaussian", "mitchell", "catmullrom", "lanczos"):
+            raise NotImplementedError(f"rfilter '{rtype}' is not a Mitsuba 2 reconstruction filter")
+        crop = None
+        if any(k in fp for k in ("crop_offset_x", "crop_offset_y", "crop_width", "crop_height")):   # film.cpp:16-44
+            crop = (fp.get("crop_offset_x", 0), fp.get("crop_offset_y", 0), fp.get("crop_width", w), fp.get("crop_height", h))
         sampler = el.find("sampler")
         if sampler is not None:
             self.sd.spp = self.props(sampler).get("sample_count", 4)
         fov = parse_fov(p.get("fov"), p.get("fov_axis", "x"), p.get("focal_length", "50mm"), w / h)
         self.sd.add_perspective(p.get("to_world", np.eye(4)), fov, p.get("near_clip", 1e-2), p.get("far_clip", 1e4), w, h,
-                                rtype, rp.get("stddev", 0.5), rp.get("radius"))
+                                rtype, rp.get("stddev", 0.5), rp.get("radius"), rp.get("B", 1.0 / 3.0), rp.get("C", 1.0 / 3.0),
+                                rp.get("lobes", 3), crop)
 
     def load(self, root, base_dir):
         items = self.expand(root, base_dir)

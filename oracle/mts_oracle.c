@@ -256,7 +256,22 @@ void orc_microfacet_sample(int type, float au, float av, int vis, const float *w
     o[0] = m.x; o[1] = m.y; o[2] = m.z; o[3] = pdf;
 }
 
-/* ---------------- reconstruction filters: src/rfilters/{box,tent,gaussian}.cpp ------------------ */
+/* ---------------- reconstruction filters: src/rfilters/{box,tent,gaussian,mitchell,catmullrom,lanczos}.cpp ---- */
+static float cubic_bc(float x, float B, float C) {                                 /* mitchell.cpp:40-53 = catmullrom.cpp:29-43 */
+    x = fabsf(x); float x2 = x * x, x3 = x2 * x;
+    float r = (1.f / 6.f) * (x < 1.f ? (12.f - 9.f * B - 6.f * C) * x3 + (-18.f + 12.f * B + 6.f * C) * x2 + (6.f - 2.f * B)
+                                     : (-B - 6.f * C) * x3 + (6.f * B + 30.f * C) * x2 + (-12.f * B - 48.f * C) * x + (8.f * B + 24.f * C));
+    return x < 2.f ? r : 0.f;
+}
+float orc_rfilter_eval2(int type, float radius, float stddev, float c, float x) {
+    if (type == MTSB_RFILTER_MITCHELL) return cubic_bc(x, stddev, c);
+    if (type == MTSB_RFILTER_CATMULLROM) return cubic_bc(x, 0.f, 0.5f);
+    if (type == MTSB_RFILTER_LANCZOS) {                                            /* lanczos.cpp:44-54 */
+        x = fabsf(x); float x1 = PI_F * x, x2 = x1 / radius;
+        return x < EPS_F ? 1.f : (x > radius ? 0.f : (sinf(x1) * sinf(x2)) / (x1 * x2));
+    }
+    return orc_rfilter_eval(type, radius, stddev, x);
+}
 float orc_rfilter_eval(int type, float radius, float stddev, float x) {
     if (type == MTSB_RFILTER_BOX) return fabsf(x) <= radius ? 1.f : 0.f;           /* radius includes +RayEpsilon, box.cpp:30 */
     if (type == MTSB_RFILTER_TENT) return fmaxf(0.f, 1.f - fabsf(x / radius));
@@ -1031,9 +1046,9 @@ static void film_put(const mtsb_sensor_desc *sn, float px, float py, const float
         int hix = (int) floorf(x + radius), hiy = (int) floorf(y + radius); if (hix > W - 1) hix = W - 1; if (hiy > H - 1) hiy = H - 1;
         int n = (int) ceilf((radius - 2.f * RAY_EPS) * 2.f);
         for (int yr = 0; yr < n; ++yr) { int yy = loy + yr; if (yy > hiy) break;
-            float wy = orc_rfilter_eval(sn->rfilter, radius, sn->rfilter_stddev, (float) loy - y + (float) yr);
+            float wy = orc_rfilter_eval2(sn->rfilter, radius, sn->rfilter_stddev, sn->rfilter_c, (float) loy - y + (float) yr);
             for (int xr = 0; xr < n; ++xr) { int xx = lox + xr; if (xx > hix) break;
-                float w = wy * orc_rfilter_eval(sn->rfilter, radius, sn->rfilter_stddev, (float) lox - x + (float) xr);
+                float w = wy * orc_rfilter_eval2(sn->rfilter, radius, sn->rfilter_stddev, sn->rfilter_c, (float) lox - x + (float) xr);
                 float *p = xyzaw + 5 * ((size_t) yy * W + xx);
                 for (int k = 0; k < 5; ++k) {
                     #pragma omp atomic

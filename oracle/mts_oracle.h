@@ -43,6 +43,7 @@ float orc_microfacet_smith_g1(int type, float au, float av, const float *v, cons
 void orc_microfacet_sample(int type, float au, float av, int visible, const float *wi, float sx, float sy, float *out4 /* m, pdf */);
 float orc_erfinv(float x);
 float orc_rfilter_eval(int type, float radius, float stddev, float x);
+float orc_rfilter_eval2(int type, float radius, float stddev, float c, float x);   /* + mitchell (B = stddev, C = c), catmullrom, lanczos */
 void orc_perspective_sample_to_camera(float x_fov_deg, float near_clip, float far_clip, float aspect, float *out16);
 
 /* distribution hooks: Hierarchical2D (distr_2d.h) over a w x h float image, DiscreteDistribution::sample_reuse (distr_1d.h) */

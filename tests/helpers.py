@@ -67,6 +67,8 @@ class Oracle:
             l.orc_fresnel.argtypes = [C.c_float, C.c_float, vp]
             l.orc_erfinv.argtypes = [C.c_float]
             l.orc_rfilter_eval.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float]
+            l.orc_rfilter_eval2.restype = C.c_float
+            l.orc_rfilter_eval2.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
             l.orc_microfacet_eval.argtypes = [C.c_int, C.c_float, C.c_float, vp]
             l.orc_microfacet_pdf.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, vp, vp]
             l.orc_microfacet_smith_g1.argtypes = [C.c_int, C.c_float, C.c_float, vp, vp]
@@ -302,9 +304,10 @@ def cbox_scene(res=32, spp=8, rfilter="box"):
     from mitsuba2_b200.scenedata import perspective_sample_to_camera
     s["width"] = s["height"] = res
     s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], 1.0).reshape(16)
-    kinds = {"box": (A.RFILTER_BOX, 0.5), "tent": (A.RFILTER_TENT, 1.0), "gaussian": (A.RFILTER_GAUSSIAN, 2.0)}
+    kinds = {"box": (A.RFILTER_BOX, 0.5), "tent": (A.RFILTER_TENT, 1.0), "gaussian": (A.RFILTER_GAUSSIAN, 2.0),
+             "mitchell": (A.RFILTER_MITCHELL, 2.0), "catmullrom": (A.RFILTER_CATMULLROM, 2.0), "lanczos": (A.RFILTER_LANCZOS, 3.0)}
     s["rfilter"], s["radius"] = kinds[rfilter]
-    s["stddev"] = 0.5
+    s["stddev"], s["filter_c"] = (1.0 / 3.0, 1.0 / 3.0) if rfilter == "mitchell" else (0.5, 0.0)
     sd.spp = spp
     return sd
 

@@ -204,7 +204,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         const mtsb_sensor_desc &sd = d->sensors[i]; SensorDev sn; memset(&sn, 0, sizeof(sn));
         memcpy(sn.to_world, sd.to_world, sizeof(sn.to_world)); memcpy(sn.sample_to_camera, sd.sample_to_camera, sizeof(sn.sample_to_camera));
         sn.near_clip = sd.near_clip; sn.far_clip = sd.far_clip; sn.width = sd.film_width; sn.height = sd.film_height; sn.rfilter = sd.rfilter;
-        sn.stddev = sd.rfilter_stddev; sn.radius = sd.rfilter == MTSB_RFILTER_BOX ? sd.rfilter_radius + kRayEpsilon : sd.rfilter_radius;
+        sn.stddev = sd.rfilter_stddev; sn.filter_c = sd.rfilter_c; sn.radius = sd.rfilter == MTSB_RFILTER_BOX ? sd.rfilter_radius + kRayEpsilon : sd.rfilter_radius;
         s->film_xyza.emplace_back((size_t) sn.width * sn.height, make_float4(0, 0, 0, 0)); s->film_w.emplace_back((size_t) sn.width * sn.height, 0.f);
         s->sensors.push_back(sn);
     }

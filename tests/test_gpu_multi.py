@@ -1,5 +1,5 @@
 """Multi-GPU (needs >= 2 devices; skipped otherwise): spp-sharded render + NCCL film all-reduce equals the one-GPU render
-of the union of the sample indices; the texture gradient all-reduce equals the one-GPU gradient."""
+of the union of the sample indices; the texture and vertex gradient all-reduces equal the one-GPU gradients."""
 import os
 import socket
 
@@ -38,6 +38,15 @@ def _worker(rank, world, port, out_dir):
         wgt = torch.from_numpy(np.random.default_rng(0).normal(size=(24, 24, 3)).astype(np.float32)).cuda(rank)
         (out * wgt).sum().backward()
         np.save(os.path.join(out_dir, f"grad{rank}.npy"), p.grad.cpu().numpy())
+        # vertex positions: samples sharded over the ranks, gradient all-reduced
+        sdv = H.vgrad_scene("quadshadow", "diffuse", res=16, spp=8)
+        scv = mi.Scene(sdv, device=rank)
+        scv.grad_config(boundary=2, edge_fraction=0.5)
+        v = torch.from_numpy(np.asarray(sdv.meshes[0].positions, np.float32).reshape(-1, 3).copy()).cuda(rank).requires_grad_(True)
+        outv = autodiff.render_torch(scv, spp=8, seed=4, vertices=v, mesh_id=0)
+        wv = torch.from_numpy(np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)).cuda(rank)
+        (outv * wv).sum().backward()
+        np.save(os.path.join(out_dir, f"vgrad{rank}.npy"), v.grad.cpu().numpy())
     finally:
         dist.destroy_process_group()
 
@@ -61,3 +70,11 @@ def test_two_gpu_render_and_gradient_equal_single_gpu(tmp_path):
     g0, g1 = np.load(tmp_path / "grad0.npy"), np.load(tmp_path / "grad1.npy")
     np.testing.assert_array_equal(g0, g1)
     np.testing.assert_allclose(g0.ravel(), g, rtol=1e-3, atol=1e-4 * np.abs(g).max())
+    sdv = H.vgrad_scene("quadshadow", "diffuse", res=16, spp=8)
+    scv = mi.Scene(sdv, device=0)
+    scv.grad_config(boundary=2, edge_fraction=0.5)
+    wv = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    _, gv = scv.render_grad(wv, spp=8, seed=4, mesh_id=0)
+    v0, v1 = np.load(tmp_path / "vgrad0.npy"), np.load(tmp_path / "vgrad1.npy")
+    np.testing.assert_array_equal(v0, v1)
+    np.testing.assert_allclose(v0, gv, rtol=1e-3, atol=1e-4 * np.abs(gv).max())

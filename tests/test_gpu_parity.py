@@ -95,6 +95,8 @@ def test_empty_and_tiny_scenes(mi):
     (lambda: H.cbox_scene(64, 16), 16, 2e-3),
     (lambda: H.cbox_scene(48, 8, "gaussian"), 8, 2e-3),
     (lambda: H.cbox_scene(48, 8, "tent"), 8, 2e-3),
+    (lambda: H.cbox_scene(48, 8, "mitchell"), 8, 2e-3),
+    (lambda: H.cbox_scene(48, 8, "lanczos"), 8, 2e-3),
     (lambda: H.material_scene((96, 64), 16), 16, 2e-2),
 ])
 def test_render_matches_oracle_per_sample_streams(mi, scene_fn, spp, tol):
@@ -156,7 +158,7 @@ def test_stage_hooks_match_oracle(mi):
 
 
 def test_film_put_matches_oracle(mi):
-    for rf in ("box", "tent", "gaussian"):
+    for rf in ("box", "tent", "gaussian", "mitchell", "catmullrom", "lanczos"):
         sd = H.cbox_scene(16, 1, rf)
         scene, orc = mi.Scene(sd), H.Oracle(sd)
         rng = np.random.default_rng(1)

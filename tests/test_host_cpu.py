@@ -74,7 +74,7 @@ def test_hostsim_bvh_shape():
     assert n >= 1 and 1 <= depth <= 64
 
 
-@pytest.mark.parametrize("rfilter", ["box", "gaussian", "tent"])
+@pytest.mark.parametrize("rfilter", ["box", "gaussian", "tent", "mitchell", "catmullrom", "lanczos"])
 def test_hostsim_cbox_film_matches_oracle(rfilter):
     sd = H.cbox_scene(res=16, spp=4, rfilter=rfilter)
     a, b = Oracle(sd).render_xyzaw(seed=3), HostSim(sd).render_xyzaw(seed=3)
@@ -264,3 +264,28 @@ def test_header_is_valid_c99_and_cpp_host_links(tmp_path):
     if not torch.cuda.is_available():            # without a GPU the host must fail loudly, not fall back
         r = subprocess.run([exe, str(tmp_path / "o.pfm"), "2"], capture_output=True, text=True)
         assert r.returncode != 0 and "failed" in r.stderr
+
+
+def test_crop_window_equals_the_window_of_the_full_film():
+    """`hdrfilm` crop (src/librender/film.cpp:16-44; perspective.cpp:106-133 folds it into camera_to_sample): the camera
+    rays of a crop-window sensor are those of the same pixels of the full film."""
+    from mitsuba2_b200.scenedata import SceneData, look_at
+    full, crop = SceneData(), SceneData()
+    tw = look_at([0, 0, -3], [0, 0.2, 0], [0, 1, 0])
+    full.add_perspective(tw, 50.0, 0.1, 100.0, 40, 30, "box")
+    crop.add_perspective(tw, 50.0, 0.1, 100.0, 40, 30, "box", crop=(8, 5, 16, 12))
+    assert crop.sensors[0]["width"] == 16 and crop.sensors[0]["height"] == 12
+    for sd in (full, crop):
+        sd.add_mesh(H.Mesh(*H.grid_mesh(1, 1, 1.0, [0, 0, 0], [1, 0, 0], [0, 1, 0]), bsdf=sd.add_diffuse(0.5)))
+    px = np.random.default_rng(0).random((64, 2))
+    of, df = Oracle(full).sensor_sample_ray((px * [16, 12] + [8, 5]) / [40, 30])
+    oc, dc = Oracle(crop).sensor_sample_ray(px)
+    assert np.allclose(of, oc, atol=1e-5) and np.allclose(df[:, :3], dc[:, :3], atol=1e-5)
+    from mitsuba2_b200 import xml
+    sd = xml.load_string("""<scene version="2.0.0"><sensor type="perspective"><film type="hdrfilm">
+        <integer name="width" value="40"/><integer name="height" value="30"/><integer name="crop_offset_x" value="8"/>
+        <integer name="crop_offset_y" value="5"/><integer name="crop_width" value="16"/><integer name="crop_height" value="12"/>
+        <rfilter type="mitchell"><float name="B" value="0.2"/></rfilter></film></sensor>
+        <shape type="rectangle"/></scene>""")
+    s = sd.sensors[0]
+    assert (s["width"], s["height"]) == (16, 12) and abs(s["stddev"] - 0.2) < 1e-6 and abs(s["filter_c"] - 1 / 3) < 1e-6

@@ -182,6 +182,13 @@ def test_rfilter_spot_values():
     assert l.orc_rfilter_eval(A.RFILTER_GAUSSIAN, 2.0, 0.5, 2.1) == 0
     assert abs(l.orc_rfilter_eval(A.RFILTER_TENT, 1.0, 0.0, 0.1) - 0.903) < 5e-2
     assert l.orc_rfilter_eval(A.RFILTER_TENT, 1.0, 0.0, 1.1) == 0
+    # test_rfilter.py:24-45 (lanczos 3 lobes, mitchell B = C = 1/3, catmullrom)
+    e2 = l.orc_rfilter_eval2
+    assert abs(e2(A.RFILTER_LANCZOS, 3.0, 0.0, 0.0, 1.4) - (-0.14668)) < 1e-2 and e2(A.RFILTER_LANCZOS, 3.0, 0.0, 0.0, 3.1) == 0
+    assert e2(A.RFILTER_LANCZOS, 3.0, 0.0, 0.0, 0.0) == 1
+    assert abs(e2(A.RFILTER_MITCHELL, 2.0, 1 / 3, 1 / 3, 0.0) - 0.8888) < 1e-3 and e2(A.RFILTER_MITCHELL, 2.0, 1 / 3, 1 / 3, 2.1) == 0
+    assert abs(e2(A.RFILTER_CATMULLROM, 2.0, 0.0, 0.0, 0.0) - 0.9765) < 5e-2 and e2(A.RFILTER_CATMULLROM, 2.0, 0.0, 0.0, 2.1) == 0
+    assert e2(A.RFILTER_CATMULLROM, 2.0, 0.0, 0.0, 1.5) < 0                      # negative lobe
 
 
 # ---- BSDF spot checks through the oracle scene hooks -----------------------------------------------------------------
