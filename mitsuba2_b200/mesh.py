@@ -190,6 +190,62 @@ def load_ply(path, to_world=None, face_normals=False, flip_normals=False):
     return Mesh(pos, faces, nrm, tex, name=str(path))
 
 
+def load_serialized(path, to_world=None, shape_index=0, face_normals=False, flip_normals=False):
+    """``SerializedMesh`` (src/shapes/serialized.cpp:177-330): header 0x041C + version 3/4, optional offset dictionary
+    at the end of the file (``shape_index``), then a zlib stream with flags, [name (v4)], uint64 vertex / face counts,
+    positions, [normals], [texcoords], [colors (skipped)] in single or double precision, uint32 face indices."""
+    import struct
+    import zlib
+    raw = open(path, "rb").read()
+    fmt, version = struct.unpack_from("<hh", raw, 0)
+    if fmt != 0x041C:
+        raise ValueError(f'Error while loading serialized file "{path}": encountered an invalid file format!')
+    if version not in (3, 4):
+        raise ValueError(f'Error while loading serialized file "{path}": encountered an incompatible file version!')
+    start = 4
+    if shape_index != 0:
+        count = struct.unpack_from("<I", raw, len(raw) - 4)[0]
+        if shape_index < 0 or shape_index >= count:
+            raise ValueError(f"Unable to unserialize mesh, shape index is out of range! (requested {shape_index} out of 0..{count - 1})")
+        if version == 4:
+            start = struct.unpack_from("<Q", raw, len(raw) - 8 * (count - shape_index) - 4)[0] + 4
+        else:
+            start = struct.unpack_from("<I", raw, len(raw) - 4 * (count - shape_index + 1))[0] + 4
+    data = zlib.decompressobj().decompress(raw[start:])
+    off = 0
+    flags = struct.unpack_from("<I", data, off)[0]; off += 4
+    name = str(path)
+    if version == 4:
+        end = data.index(b"\0", off)
+        name = data[off:end].decode("utf-8", "replace") or name
+        off = end + 1
+    nv, nf = struct.unpack_from("<QQ", data, off); off += 16
+    dt = np.dtype("<f8") if flags & 0x2000 else np.dtype("<f4")
+
+    def take(dim):
+        nonlocal off
+        a = np.frombuffer(data, dt, nv * dim, off).reshape(nv, dim).astype(np.float32)
+        off += nv * dim * dt.itemsize
+        return a
+
+    pos = take(3)
+    nrm = take(3) if flags & 0x0001 else None
+    tex = take(2) if flags & 0x0002 else None
+    if flags & 0x0008:
+        take(3)
+    faces = np.frombuffer(data, "<u4", nf * 3, off).reshape(nf, 3).astype(np.uint32)
+    pos = _apply(to_world, pos)
+    if face_normals:
+        nrm = None
+    elif nrm is not None:
+        nrm = _apply(to_world, nrm, normal=True)
+        if flip_normals:
+            nrm = -nrm
+    else:
+        nrm = compute_vertex_normals(pos, faces)
+    return Mesh(pos, faces, nrm, tex, name=name)
+
+
 def write_ply(path, mesh):
     """Binary little-endian PLY (so the reference could load the identical mesh)."""
     p, f = mesh.positions, mesh.faces

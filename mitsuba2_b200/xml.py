@@ -2,7 +2,7 @@
 
 Mirror of ``xml::load_file`` / ``load_string`` (include/mitsuba/core/xml.h:17-29, src/libcore/xml.cpp): ``<default>``,
 ``$param`` substitution (``-Dkey=value``), ``<include>``, ``<ref>``, ``<transform>`` (translate/rotate/scale/lookat/matrix),
-typed properties, and the plugins named by the north star: shapes obj/ply (+ rectangle as two triangles), BSDFs
+typed properties, and the plugins named by the north star: shapes obj/ply/serialized (+ rectangle as two triangles), BSDFs
 diffuse/roughconductor/dielectric (+ ``twosided`` around the first two), emitters
 area/envmap/constant/point, sensor perspective, film hdrfilm, rfilters box/tent/gaussian/mitchell/catmullrom/lanczos, film crop window, sampler independent, integrator path.
 Unknown plugins raise, like ``PluginManager`` does.
@@ -238,6 +238,9 @@ class _Loader:
                            p.get("flip_tex_coords", True), p.get("flip_normals", False))
         elif ty == "ply":
             m = M.load_ply(self.resolve(el, p["filename"]), to_world, p.get("face_normals", False), p.get("flip_normals", False))
+        elif ty == "serialized":
+            m = M.load_serialized(self.resolve(el, p["filename"]), to_world, p.get("shape_index", 0), p.get("face_normals", False),
+                                  p.get("flip_normals", False))
         elif ty == "rectangle":
             q = M.quad([-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0])
             q.positions = M._apply(to_world, q.positions)

@@ -289,3 +289,53 @@ def test_crop_window_equals_the_window_of_the_full_film():
         <shape type="rectangle"/></scene>""")
     s = sd.sensors[0]
     assert (s["width"], s["height"]) == (16, 12) and abs(s["stddev"] - 0.2) < 1e-6 and abs(s["filter_c"] - 1 / 3) < 1e-6
+
+
+def _write_serialized(path, meshes, version=4, double=False):
+    """Writer for the format of src/shapes/serialized.cpp:56-135 (test helper): zlib streams + offset dictionary."""
+    import struct
+    import zlib
+    blob, offsets = b"", []
+    for name, pos, nrm, tex, faces in meshes:
+        flags = (0x2000 if double else 0x1000) | (0x0001 if nrm is not None else 0) | (0x0002 if tex is not None else 0)
+        dt = "<f8" if double else "<f4"
+        body = struct.pack("<I", flags) + (name.encode() + b"\0" if version == 4 else b"") + struct.pack("<QQ", len(pos), len(faces))
+        body += np.asarray(pos, dt).tobytes()
+        if nrm is not None:
+            body += np.asarray(nrm, dt).tobytes()
+        if tex is not None:
+            body += np.asarray(tex, dt).tobytes()
+        body += np.asarray(faces, "<u4").tobytes()
+        offsets.append(len(blob))
+        blob += struct.pack("<hh", 0x041C, version) + zlib.compress(body)
+    tail = b"".join(struct.pack("<Q" if version == 4 else "<I", o) for o in offsets) + struct.pack("<I", len(offsets))
+    open(path, "wb").write(blob + tail)
+
+
+@pytest.mark.parametrize("version,double", [(4, False), (3, False), (4, True)])
+def test_serialized_loader(tmp_path, version, double):
+    """`serialized` shape plugin (src/shapes/serialized.cpp:177-330): versions 3 / 4, shape_index, precision flags, normals
+    computed when the file has none; plus the reference's own fixtures and expected values (test_mesh.py:131-170) when
+    the reference tree is present."""
+    from mitsuba2_b200 import mesh as M
+    rng = np.random.default_rng(version)
+    a = ("first", rng.random((5, 3)), None, rng.random((5, 2)), [[0, 1, 2], [2, 3, 4]])
+    nb = rng.normal(size=(4, 3)); nb /= np.linalg.norm(nb, axis=1, keepdims=True)
+    b = ("second", rng.random((4, 3)), nb, None, [[0, 1, 2], [0, 2, 3]])
+    path = str(tmp_path / "two.serialized")
+    _write_serialized(path, [a, b], version, double)
+    m0, m1 = M.load_serialized(path), M.load_serialized(path, shape_index=1)
+    assert np.allclose(m0.positions, a[1], atol=1e-6) and np.allclose(m0.texcoords, a[3], atol=1e-6) and m0.faces.tolist() == a[4]
+    assert np.allclose(m0.normals, M.compute_vertex_normals(m0.positions, m0.faces))
+    assert np.allclose(m1.positions, b[1], atol=1e-6) and np.allclose(m1.normals, nb, atol=1e-6) and m1.texcoords is None
+    if version == 4:
+        assert m1.name == "second"
+    assert M.load_serialized(path, face_normals=True).normals is None
+    with pytest.raises(ValueError):
+        M.load_serialized(path, shape_index=2)
+    ref = "/root/reference/resources/data/tests/serialized/rectangle_normals_uv.serialized"
+    if os.path.exists(ref):
+        m = M.load_serialized(ref)
+        assert np.allclose(m.positions[[0, 2, 3]], [[-2.85, 0, -7.6], [2.85, 0, 0.6], [2.85, 0, -7.6]], atol=1e-3)
+        assert np.allclose(m.texcoords[[0, 2, 3]], [[0.950589, 1 - 0.988416], [0.025105, 1 - 0.689127], [0.950589, 1 - 0.689127]], atol=1e-3)
+        assert np.allclose(m.normals, [[0, 1, 0]] * 4)

@@ -1,0 +1,37 @@
+#!/usr/bin/env python
+"""Small driver for ncu captures (profiles/README.md): one short invocation of a hot path, nothing timed.
+
+    python tools/prof_run.py spectral   # C3 in the spectral mode, 2 x 2 spp
+    python tools/prof_run.py grad       # C4 gradient pass (texture + vertex positions), 8 spp
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np                      # noqa: E402
+import mitsuba2_b200 as mi              # noqa: E402
+from mitsuba2_b200 import scenes        # noqa: E402
+
+
+def main():
+    what = sys.argv[1] if len(sys.argv) > 1 else "spectral"
+    mi.set_variant("cuda_b200_rgb")
+    if what == "spectral":
+        sd = scenes.c3_scene()
+        sd.mode = "spectral"
+        sc = mi.Scene(sd, device=0)
+        for i in range(2):
+            sc.film_clear()
+            sc.render_accumulate(spp=2, seed=i, spp_begin=0, spp_total=2)
+    else:
+        sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"))
+        mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
+        sc = mi.Scene(sd, device=0)
+        dl = np.random.default_rng(0).normal(size=(512, 512, 3)).astype(np.float32)
+        sc.render_grad(dl, spp=8, seed=1, tex_id=tex, mesh_id=mid)
+    print("done", what)
+
+
+if __name__ == "__main__":
+    main()
