@@ -212,6 +212,10 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
 
     const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
     grad.on_bsdf(sc, b, path_id, si, bsdf);
+    // spectral mode: one texture lookup shared by eval and sample (spectrum evaluations are expensive); the rgb kernel
+    // re-reads the few floats at each use instead of keeping them live (it is compiled for 48 registers)
+    BsdfTexT<M> btex;
+    if (M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
     // ---- emitter sampling (path.cpp:155-172, scene.cpp:141-189)
     if (bsdf_is_smooth(bsdf)) {
         float sx = rng.next_f32(), sy = rng.next_f32();
@@ -220,7 +224,8 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
             if (ds.pdf != 0.f) {
                 float3 wo = si.sh.to_local(ds.d);
                 Spec bval; float bpdf;
-                bsdf_eval_pdf<M>(sc, bsdf, si, wo, bval, bpdf, wav);
+                if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
+                bsdf_eval_pdf<M>(sc, bsdf, si, wo, bval, bpdf, btex);
                 float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
                 Spec c = thr * bval * ds.value * mis;
                 if (!is_black(c)) {
@@ -235,7 +240,8 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     }
     // ---- BSDF sampling (path.cpp:177-190)
     float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
-    BsdfSampleT<M> bs = bsdf_sample<M>(sc, bsdf, si, s1, s2x, s2y, wav);
+    if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
+    BsdfSampleT<M> bs = bsdf_sample<M>(sc, bsdf, si, s1, s2x, s2y, btex);
     thr *= bs.weight;
     if (is_black(thr)) return out;
     eta *= bs.eta;

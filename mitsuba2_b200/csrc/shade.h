@@ -75,7 +75,13 @@ HD float3 tex_eval_rgb(const SceneDev &sc, int id, float u, float v) {
 }
 // Spectral mode: the same textures hold sRGB-model coefficients (srgb.cpp:44-48; bitmap.cpp:262-275 evaluates the model at
 // the four texels and blends the spectra), or a tabulated / uniform spectrum; emitters multiply by D65 (srgb_d65.cpp:60-62).
-HD float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wav) {
+// one out-of-line copy: the five texture kinds times the call sites of a shade launch otherwise inline to ~39 k SASS lines
+#ifndef MTSB_TEXSPEC_INLINE
+__host__ __device__ __noinline__
+#else
+HD
+#endif
+float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wav) {
     const TexDev &t = sc.tex[id];
     float4 r;
     if (t.type == 0) r = srgb_model_eval(t.value, wav);
@@ -277,8 +283,25 @@ struct Microfacet {
 };
 
 // ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
+// The textures of a BSDF at one surface point, looked up once per path vertex and shared by eval (emitter sample) and
+// sample: diffuse a = reflectance; roughconductor a = eta, b = k, c = specular_reflectance (1 if absent);
+// dielectric a = specular_reflectance, b = specular_transmittance (1 if absent).
+template <typename M> struct BsdfTexT { typename M::Spec a, b, c; };
 template <typename M>
-HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav) {
+HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, float v, float4 wav) {
+    BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f);
+    if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
+    else if (b.type == 1) {
+        t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
+        if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
+    } else {
+        if (b.spec_r >= 0) t.a = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
+        if (b.spec_t >= 0) t.b = tex_eval_m<M>(sc, b.spec_t, u, v, wav);
+    }
+    return t;
+}
+template <typename M>
+HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, const BsdfTexT<M> &tx) {
     typedef typename M::Spec Spec;
     BsdfSampleT<M> bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 1.f; bs.delta = false; bs.weight = M::splat(0.f);
     float cos_i = si.wi.z;
@@ -286,7 +309,7 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         if (!(cos_i > 0.f)) return bs;
         bs.wo = square_to_cosine_hemisphere(sx, sy);
         bs.pdf = kInvPi * bs.wo.z;
-        if (bs.pdf > 0.f) bs.weight = tex_eval_m<M>(sc, b.refl, si.u, si.v, wav);
+        if (bs.pdf > 0.f) bs.weight = tx.a;
         return bs;
     }
     if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:196-276
@@ -298,9 +321,8 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         float weight = b.sample_visible ? distr.smith_g1(bs.wo, m)
                                         : distr.G(si.wi, bs.wo, m) * dot(si.wi, m) / (cos_i * m.z);
         bs.pdf /= 4.f * dot(bs.wo, m);
-        Spec eta = tex_eval_m<M>(sc, b.eta, si.u, si.v, wav), k = tex_eval_m<M>(sc, b.k, si.u, si.v, wav);
-        Spec F = fresnel_conductor(dot(si.wi, m), eta, k);
-        if (b.spec_r >= 0) F *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav);
+        Spec F = fresnel_conductor(dot(si.wi, m), tx.a, tx.b);
+        if (b.spec_r >= 0) F *= tx.c;
         bs.weight = active ? F * weight : M::splat(0.f);
         return bs;
     }
@@ -314,19 +336,19 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
     bs.wo = sel_r ? mk3(-si.wi.x, -si.wi.y, si.wi.z) : mk3(-eta_ti * si.wi.x, -eta_ti * si.wi.y, cos_t);
     bs.eta = sel_r ? 1.f : eta_it;
     Spec w = M::splat(1.f);
-    if (sel_r) { if (b.spec_r >= 0) w *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav); }
-    else { if (b.spec_t >= 0) w *= tex_eval_m<M>(sc, b.spec_t, si.u, si.v, wav); w *= sqr(eta_ti); }
+    if (sel_r) { if (b.spec_r >= 0) w *= tx.a; }
+    else { if (b.spec_t >= 0) w *= tx.b; w *= sqr(eta_ti); }
     bs.weight = w;
     return bs;
 }
 
 template <typename M>
-HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav) {
+HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, const BsdfTexT<M> &tx) {
     typedef typename M::Spec Spec;
     val = M::splat(0.f); pdf = 0.f;
     float ci = si.wi.z, co = wo.z;
     if (b.type == 0) {            // src/bsdfs/diffuse.cpp:105-135
-        if (ci > 0.f && co > 0.f) { val = tex_eval_m<M>(sc, b.refl, si.u, si.v, wav) * kInvPi * co; pdf = kInvPi * co; }
+        if (ci > 0.f && co > 0.f) { val = tx.a * kInvPi * co; pdf = kInvPi * co; }
         return;
     }
     if (b.type == 1) {            // src/bsdfs/roughconductor.cpp:278-394
@@ -337,9 +359,8 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
         if (D != 0.f) {
             float G = distr.G(si.wi, wo, H);
             float res = D * G / (4.f * ci);
-            Spec eta = tex_eval_m<M>(sc, b.eta, si.u, si.v, wav), k = tex_eval_m<M>(sc, b.k, si.u, si.v, wav);
-            Spec F = fresnel_conductor(dot(si.wi, H), eta, k);
-            if (b.spec_r >= 0) F *= tex_eval_m<M>(sc, b.spec_r, si.u, si.v, wav);
+            Spec F = fresnel_conductor(dot(si.wi, H), tx.a, tx.b);
+            if (b.spec_r >= 0) F *= tx.c;
             val = F * res;
         }
         if (dot(si.wi, H) > 0.f && dot(wo, H) > 0.f)
@@ -351,20 +372,29 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
 // `twosided` (src/bsdfs/twosided.cpp:98-200): on the back side mirror wi (and wo) about the surface and use the
 // nested BRDF; cos(wi) == 0 belongs to neither side.  One call site each, so the nested code is not duplicated.
 template <typename M = Rgb>
-HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav = float4()) {
+HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, const BsdfTexT<M> &tx) {
     bool back = b.two_sided && si.wi.z < 0.f;
     SI s2 = si;
     if (back) s2.wi.z = -s2.wi.z;
-    BsdfSampleT<M> bs = bsdf_sample_one_sided<M>(sc, b, s2, s1, sx, sy, wav);
+    BsdfSampleT<M> bs = bsdf_sample_one_sided<M>(sc, b, s2, s1, sx, sy, tx);
     if (back) bs.wo.z = -bs.wo.z;
     return bs;
 }
 template <typename M = Rgb>
-HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
+HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, const BsdfTexT<M> &tx) {
     bool back = b.two_sided && si.wi.z < 0.f;
     SI s2 = si;
     if (back) { s2.wi.z = -s2.wi.z; wo.z = -wo.z; }
-    bsdf_eval_pdf_one_sided<M>(sc, b, s2, wo, val, pdf, wav);
+    bsdf_eval_pdf_one_sided<M>(sc, b, s2, wo, val, pdf, tx);
+}
+// stand-alone forms (parity hooks, adjoint): look the textures up themselves
+template <typename M = Rgb>
+HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav = float4()) {
+    return bsdf_sample<M>(sc, b, si, s1, sx, sy, bsdf_textures<M>(sc, b, si.u, si.v, wav));
+}
+template <typename M = Rgb>
+HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
+    bsdf_eval_pdf<M>(sc, b, si, wo, val, pdf, bsdf_textures<M>(sc, b, si.u, si.v, wav));
 }
 HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
 

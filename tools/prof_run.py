@@ -17,7 +17,18 @@ from mitsuba2_b200 import scenes        # noqa: E402
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "spectral"
     mi.set_variant("cuda_b200_rgb")
-    if what == "spectral":
+    if what in ("spectral_time", "rgb_time"):      # stage timing of the C3 step (not a bench value: no clock sampling)
+        sd = scenes.c3_scene()
+        if what == "spectral_time":
+            sd.mode = "spectral"
+        sc = mi.Scene(sd, device=0)
+        sc.set_profiling(True)
+        for i in range(6):
+            sc.film_clear()
+            st = sc.render_accumulate(spp=16, seed=i, spp_begin=0, spp_total=16)
+            if i >= 3:
+                print({k: round(st[k], 3) for k in ("ms_total", "ms_closest", "ms_shade", "ms_any")})
+    elif what == "spectral":
         sd = scenes.c3_scene()
         sd.mode = "spectral"
         sc = mi.Scene(sd, device=0)
