@@ -257,25 +257,30 @@ template <typename Add, bool Vtx = true> struct ReplayGrad {
     HD void on_bsdf(const SceneDev &sc, const RenderBatch &b, uint32_t path_id, const SI &si, const BsdfDev &bsdf) const {
         if (g.grad_tex != nullptr) texture_adjoint(sc, b, g, path_id, si, bsdf, add);
     }
-    // emitter sample at x_k: factor f_s(x_{k-1}, x_k, y) G~(x_k, y), weighted by the sample's own contribution when
-    // the shadow ray is free (tested here; the primal k_shadow pass adds the contribution itself)
-    template <typename DS>
-    HD void on_nee(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, uint32_t path_id, uint32_t depth,
-                   const SI &si, const DS &ds, float3 c) const {
-        if (g.grad_pos == nullptr) return;
-        uint2 fast[8]; TravStack<8, 56> st; st.fast = fast; st.stride = 1; Hit h;
-        if (bvh_trace<true>(sc.bvh, si.p, ds.d, kRayEpsilon * (1.f + hmax(abs3(si.p))), ds.dist * (1.f - kShadowEpsilon), st, h)) return;
-        VtxRec recA; recA.prim = 0xffffffffu; recA.b1 = recA.b2 = 0.f;
-        float3 xA = g.cam_o;
-        if (depth > 1) { recA = vtx_rec(q.prev1[i]); xA = tri_point(tri_geo(sc, recA.prim), recA); }
-        float4 hc = q.hit[i];
-        VtxRec recB; recB.prim = si.prim; recB.b1 = hc.y; recB.b2 = hc.z;
-        // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point
-        int kind = ds.etype == 0 ? kEndFixedArea : (ds.etype == 3 ? kEndFixedPoint : kEndDirection);
-        float3 xC = kind == kEndDirection ? ds.d : ds.p;
-        vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recB, ds.n, weight(b, path_id, c), add);
-    }
 };
+
+// emitter sample at x_k, differentiated once its shadow ray is known to be free (k_nee_grad after k_shadow): factor
+// f_s(x_{k-1}, x_k, y) G~(x_k, y), weighted by the sample's own contribution.  `rec` = ShadowQueue::nee_rec (queue index of
+// the vertex, the two sampling numbers, depth; depth 0 = path already passed a delta vertex), `contrib` = the shadow
+// record's contribution and path id.  The queue entry of the vertex is still intact at that point of the batch.
+template <typename Add>
+HD void nee_adjoint(const SceneDev &sc, const GradCtx &g, const PathQueue &q, const RenderBatch &b, float4 rec, float4 contrib, Add add) {
+    uint32_t i = f2u(rec.x), depth = f2u(rec.w), path_id = f2u(contrib.w);
+    if (depth == 0u || g.grad_pos == nullptr) return;
+    float4 o4 = q.o_mint[i], d4 = q.d_maxt[i], hc = q.hit[i];
+    SI si = make_si(sc, xyz(o4), xyz(d4), hc);
+    DirSample ds = sample_emitter_direction(sc, si.p, rec.y, rec.z);
+    VtxRec recA; recA.prim = 0xffffffffu; recA.b1 = recA.b2 = 0.f;
+    float3 xA = g.cam_o;
+    if (depth > 1) { recA = vtx_rec(q.prev1[i]); xA = tri_point(tri_geo(sc, recA.prim), recA); }
+    VtxRec recB; recB.prim = si.prim; recB.b1 = hc.y; recB.b2 = hc.z;
+    // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point
+    int kind = ds.etype == 0 ? kEndFixedArea : (ds.etype == 3 ? kEndFixedPoint : kEndDirection);
+    float3 xC = kind == kEndDirection ? ds.d : ds.p;
+    uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
+    float3 w = ld3(g.dL_dimage, pixel) * xyz(contrib) * g.scale;
+    vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recB, ds.n, w, add);
+}
 
 // ---- boundary term: edge sampling on the film plane ---------------------------------------------------------------
 struct EdgeCtx {

@@ -98,6 +98,7 @@ struct mtsb_scene {
     DevBuf<float4> q_p1[2], q_p2[2];         // vertex-gradient replay: previous two path vertices per queue entry
     std::map<int, std::unique_ptr<DevBuf<uint4>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
     int grad_boundary = 2; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
+    DevBuf<float4> s_nee; DevBuf<uint32_t> s_occ;     // vertex-gradient replay: ShadowQueue::nee_rec / occluded
     DevBuf<float4> edge_aux;                 // boundary term seen from x1: 4 float4 per sample
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
     mtsb_stats build_stats;
@@ -583,6 +584,8 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     cudaStream_t st = s->ctx->stream;
     const uint32_t n = b.n_paths;
     ShadowQueue sq; sq.o_mint = s->s_o.p; sq.d_maxt = s->s_d.p; sq.contrib_id = s->s_c.p;
+    const bool vgrad = grad && grad->grad_pos;
+    sq.nee_rec = vgrad ? s->s_nee.p : nullptr; sq.occluded = vgrad ? s->s_occ.p : nullptr;
     int max_iter = s->dev.max_depth < 1000 ? s->dev.max_depth : 1000;
     bool poll = s->dev.max_depth > 16;
     CU(cudaMemsetAsync(s->counters.p, 0, kCounterWords * sizeof(uint32_t), st));
@@ -620,6 +623,7 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
         if (depth < s->dev.max_depth) {
             { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
             launches++;
+            if (vgrad) { StageTimer t(s->ctx, ST_SHADE); k_nee_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, sq, s->counters.p, (uint32_t) depth, n, *grad); launches++; }
         }
         cur ^= 1;
         if (poll) {

@@ -96,7 +96,8 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     if (grad_vertices && pool < 2) pool = 2;
     RC(ensure_pool(s, pool));
     CU(s->final_radiance.alloc(s->pool));
-    if (grad_vertices) for (int k = 0; k < 2; ++k) { CU(s->q_p1[k].alloc(s->pool)); CU(s->q_p2[k].alloc(s->pool)); }
+    if (grad_vertices) { for (int k = 0; k < 2; ++k) { CU(s->q_p1[k].alloc(s->pool)); CU(s->q_p2[k].alloc(s->pool)); }
+                         CU(s->s_nee.alloc(s->pool)); CU(s->s_occ.alloc(s->pool)); }
     Staging sg; const float *d_dl;
     RC(sg.in(dL_dimage, 3 * npix, mem, st, &d_dl));
     DevBuf<float> gbuf, vbuf;

@@ -284,7 +284,15 @@ k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQu
         if (Vtx) { qout.prev1[slot] = out.prev1; qout.prev2[slot] = out.prev2; }
     }
     uint32_t sslot = warp_alloc(&counters[1024 + depth], out.shadow);
-    if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id; }
+    if (out.shadow) { sq.o_mint[sslot] = out.s_o_mint; sq.d_maxt[sslot] = out.s_d_maxt; sq.contrib_id[sslot] = out.s_contrib_id;
+                      if (Vtx) sq.nee_rec[sslot] = out.s_nee_rec; }
+}
+// vertex adjoint of the emitter samples of one depth, after k_shadow has told which of them were unoccluded
+__global__ void __launch_bounds__(kBlock)
+k_nee_grad(SceneDev sc, RenderBatch b, PathQueue qin, ShadowQueue sq, const uint32_t *counters, uint32_t depth, uint32_t count_max, GradCtx g) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t count = min(counters[1024 + depth], count_max);
+    if (j < count && sq.occluded[j] == 0u) nee_adjoint(sc, g, qin, b, sq.nee_rec[j], sq.contrib_id[j], DevAdd());
 }
 // boundary term of the vertex adjoint (adjoint.h): projected edge lengths, two primary rays per edge sample, scatter
 __global__ void k_edge_len(SceneDev sc, EdgeCtx e, float3 cam_o, float *len) {
@@ -312,6 +320,7 @@ k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[1], (unsigned long long) count);
     trace_persistent<true>(bvh, count, sq.o_mint, sq.d_maxt, work, refill, s_stack,
         [=](uint32_t i, bool found, const Hit &) {
+            if (sq.occluded != nullptr) sq.occluded[i] = found ? 1u : 0u;
             if (found) return;
             float4 c = sq.contrib_id[i];
             uint32_t pid = f2u(c.w);            // one shadow ray per path and depth: no concurrent writer

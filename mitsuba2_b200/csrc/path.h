@@ -21,6 +21,9 @@ struct PathQueue {
 struct ShadowQueue {
     float4 *o_mint, *d_maxt;   // shadow ray
     float4 *contrib_id;        // mis * throughput * bsdf * Le/pdf (rgb; spectral mode: already converted to XYZ), path_id (bits)
+    // vertex-gradient replay only (else null): what k_nee_grad needs to differentiate the emitter sample once the shadow ray
+    // is known to be free -- (queue index of the vertex, the two emitter-sampling random numbers, depth) and the any-hit result
+    float4 *nee_rec; uint32_t *occluded;
 };
 struct RenderBatch {
     uint32_t n_paths;          // paths in this batch
@@ -79,6 +82,7 @@ struct ShadeOut {
     float4 o_mint, d_maxt, thr_eta; uint4 misc, rng; float2 wav_eta;   // extension record
     float4 s_o_mint, s_d_maxt, s_contrib_id;                  // shadow record
     float4 prev1, prev2;                                       // vertex-gradient replay: records carried to the next vertex
+    float4 s_nee_rec;                                          // vertex-gradient replay: ShadowQueue::nee_rec of the shadow record
     // adjoint bookkeeping (filled always; cheap): first-hit info of this vertex
     float3 emitted;                                            // radiance added at this vertex (already weighted)
 };
@@ -113,15 +117,12 @@ struct GradCtx {
 };
 // Hooks the adjoint replays plug into shade_body (all empty for the primal render):
 //   on_vertex: a path vertex was reconstructed (before its emission is added to the result);
-//   on_bsdf:   the vertex's BSDF is going to be used (after emission, Russian roulette and the depth cut);
-//   on_nee:    an emitter sample with non-zero contribution `c` was generated at the vertex.
-template <typename M> struct DirSampleT;
+//   on_bsdf:   the vertex's BSDF is going to be used (after emission, Russian roulette and the depth cut).
+// (Emitter samples are differentiated after the shadow pass, from ShadowQueue::nee_rec -- nee_adjoint() in adjoint.h.)
 struct NoGrad {
     static constexpr bool kVertex = false;
     HD void on_vertex(const SceneDev &, const PathQueue &, const RenderBatch &, uint32_t, uint32_t, uint32_t, float3, float3, const SI &) const { }
     HD void on_bsdf(const SceneDev &, const RenderBatch &, uint32_t, const SI &, const BsdfDev &) const { }
-    template <typename DS> HD void on_nee(const SceneDev &, const PathQueue &, const RenderBatch &, uint32_t, uint32_t, uint32_t, const SI &,
-                                          const DS &, float3) const { }
 };
 
 template <typename AddFn>
@@ -229,7 +230,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
                 float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
                 Spec c = thr * bval * ds.value * mis;
                 if (!is_black(c)) {
-                    if (GradFn::kVertex && !M::spectral && chain_ok) grad.on_nee(sc, q, b, i, path_id, depth, si, ds, to_result(sc, c, wav, ray_weight));
+                    if (GradFn::kVertex) out.s_nee_rec = make_float4(u2f(i), sx, sy, u2f(chain_ok ? depth : 0u));
                     out.shadow = true;
                     out.s_o_mint = mk4(si.p, kRayEpsilon * (1.f + hmax(abs3(si.p))));
                     out.s_d_maxt = mk4(ds.d, ds.dist * (1.f - kShadowEpsilon));

@@ -231,15 +231,20 @@ extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const floa
 
 // The wavefront loop of mtsb_render (run_batch in api.cu), stage by stage, with sequential "threads".
 struct HsPool {
-    std::vector<float4> qo[2], qd[2], qh[2], qt[2], so, sdv, scv, result;
+    std::vector<float4> qo[2], qd[2], qh[2], qt[2], so, sdv, scv, snee, result;
     std::vector<uint4> qm[2], qr[2]; std::vector<float2> qw[2]; std::vector<float4> p1[2], p2[2];
-    explicit HsPool(uint32_t pool) : so(pool), sdv(pool), scv(pool), result(pool) {
+    explicit HsPool(uint32_t pool) : so(pool), sdv(pool), scv(pool), snee(pool), result(pool) {
         for (int k = 0; k < 2; ++k) { qo[k].resize(pool); qd[k].resize(pool); qh[k].resize(pool); qt[k].resize(pool); qm[k].resize(pool); qr[k].resize(pool); qw[k].resize(pool);
                                       p1[k].resize(pool); p2[k].resize(pool); }
     }
     PathQueue queue(int k) { PathQueue q; q.o_mint = qo[k].data(); q.d_maxt = qd[k].data(); q.hit = qh[k].data(); q.thr_eta = qt[k].data(); q.misc = qm[k].data(); q.rng = qr[k].data(); q.wav_eta = qw[k].data();
                              q.prev1 = p1[k].data(); q.prev2 = p2[k].data(); return q; }
 };
+// k_nee_grad: vertex adjoint of an unoccluded emitter sample (no-op for the primal render)
+static void hs_nee(const NoGrad &, const SceneDev &, const PathQueue &, const RenderBatch &, float4, float4) { }
+template <typename G> static void hs_nee(const G &grad, const SceneDev &sc, const PathQueue &q, const RenderBatch &b, float4 rec, float4 c) {
+    nee_adjoint(sc, grad.g, q, b, rec, c, grad.add);
+}
 template <typename M, typename GradFn>
 static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b, HsPool &P, uint64_t *cnt, GradFn grad, bool raygen = true,
                          const Edge2Ctx *edge2 = nullptr) {
@@ -269,12 +274,14 @@ static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b,
             ShadeOut out = shade_body<M>(s->dev, qin, b, i, grad);
             if (out.extend) { qout.o_mint[next] = out.o_mint; qout.d_maxt[next] = out.d_maxt; qout.thr_eta[next] = out.thr_eta; qout.misc[next] = out.misc; qout.rng[next] = out.rng; if (M::spectral) qout.wav_eta[next] = out.wav_eta;
                               if (GradFn::kVertex) { qout.prev1[next] = out.prev1; qout.prev2[next] = out.prev2; } next++; }
-            if (out.shadow) { P.so[nshadow] = out.s_o_mint; P.sdv[nshadow] = out.s_d_maxt; P.scv[nshadow] = out.s_contrib_id; nshadow++; }
+            if (out.shadow) { P.so[nshadow] = out.s_o_mint; P.sdv[nshadow] = out.s_d_maxt; P.scv[nshadow] = out.s_contrib_id;
+                              if (GradFn::kVertex) P.snee[nshadow] = out.s_nee_rec; nshadow++; }
         }
         for (uint32_t i = 0; i < nshadow; ++i) {
             TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
             if (!bvh_trace<true>(s->dev.bvh, xyz(P.so[i]), xyz(P.sdv[i]), P.so[i].w, P.sdv[i].w, st, h)) {
-                uint32_t pid = f2u(P.scv[i].w); P.result[pid].x += P.scv[i].x; P.result[pid].y += P.scv[i].y; P.result[pid].z += P.scv[i].z; }
+                uint32_t pid = f2u(P.scv[i].w); P.result[pid].x += P.scv[i].x; P.result[pid].y += P.scv[i].y; P.result[pid].z += P.scv[i].z;
+                hs_nee(grad, s->dev, qin, b, P.snee[i], P.scv[i]); }      // k_nee_grad
         }
         cnt[1] += nshadow;
         count = next; cur ^= 1;

@@ -28,6 +28,17 @@ def main():
             st = sc.render_accumulate(spp=16, seed=i, spp_begin=0, spp_total=16)
             if i >= 3:
                 print({k: round(st[k], 3) for k in ("ms_total", "ms_closest", "ms_shade", "ms_any")})
+    elif what == "grad_time":      # C4 gradient pass (texture + vertices), stage timing
+        import torch
+        sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"))
+        mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
+        sc = mi.Scene(sd, device=0)
+        sc.set_profiling(True)
+        dl = torch.randn(512 * 512 * 3, device="cuda:0")
+        for i in range(5):
+            sc.render_grad(dl, spp=64, seed=i, tex_id=tex, mesh_id=mid)
+            if i >= 2:
+                print({k: round(sc.last_stats[k], 3) for k in ("ms_total", "ms_closest", "ms_shade", "ms_any")})
     elif what == "spectral":
         sd = scenes.c3_scene()
         sd.mode = "spectral"
