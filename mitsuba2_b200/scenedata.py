@@ -189,7 +189,12 @@ class SceneData:
     def _radiance(self, value):
         """rgb triple / scalar -> {"radiance"}; a spectrum ({"wavelengths", "values"}, spectral mode) -> + {"radiance_tex"}"""
         if isinstance(value, dict):
-            return {"radiance": [0.0, 0.0, 0.0], "radiance_tex": self.add_texture_spectrum(value["wavelengths"], value["values"])}
+            # src/libcore/xml.cpp:1086-1145 (within_emitter): values are scaled by MTS_CIE_Y_NORMALIZATION; spectral variants
+            # keep the spectrum, the others pre-integrate it to an (unclamped above) colour
+            from .xml import spectrum_to_rgb, CIE_Y_NORMALIZATION
+            vals = np.asarray(value["values"], np.float32) * np.float32(CIE_Y_NORMALIZATION)
+            return {"radiance": spectrum_to_rgb(value["wavelengths"], vals, bounded=False),
+                    "radiance_tex": self.add_texture_spectrum(value["wavelengths"], vals)}
         return {"radiance": [float(value)] * 3 if np.isscalar(value) else [float(x) for x in value]}
 
     def make_two_sided(self, bsdf_id):
@@ -292,9 +297,12 @@ class SceneData:
                         texs.append({"type": A.TEX_CONSTANT, "value": [float(x) for x in coeff], "d65_scale": float(scale)})
                         emit_tex[i] = len(texs) - 1
         else:
-            for t in texs:
+            used = {v for b in self.bsdfs for k, v in b.items() if k.endswith("_tex") and isinstance(v, int) and v >= 0}
+            for i, t in enumerate(texs):
                 if t["type"] not in (A.TEX_CONSTANT, A.TEX_BITMAP) or t.get("coeff"):
-                    raise ValueError("spectrum textures need mode='spectral' (rgb variants take pre-integrated colours)")
+                    if i in used:
+                        raise ValueError("spectrum textures need mode='spectral' (rgb variants take pre-integrated colours)")
+                    texs[i] = {"type": A.TEX_CONSTANT, "value": [0.0, 0.0, 0.0]}     # an emitter's spectrum: rgb mode uses its colour
         td = (A.TextureDesc * max(1, len(texs)))()
         for i, t in enumerate(texs):
             td[i].type = t["type"]

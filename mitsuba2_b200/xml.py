@@ -35,6 +35,32 @@ def _natural_key(s):
     return [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", s)]
 
 
+CIE_Y_NORMALIZATION = 1.0 / 106.7502593994140625       # MTS_CIE_Y_NORMALIZATION (include/mitsuba/core/spectrum.h:15-20)
+
+
+def spectrum_to_rgb(wavelengths, values, bounded=True):
+    """``spectrum_to_rgb`` (src/libcore/spectrum.cpp:41-84): what a non-spectral variant does with a
+    ``<spectrum value="w0:v0, w1:v1, ..."/>`` -- 1000-step Riemann sum of the piecewise-linear spectrum against the CIE 1931
+    curves over 360..830 nm, XYZ -> linear sRGB, clamp.  The caller applies MTS_CIE_Y_NORMALIZATION to the values
+    (src/libcore/xml.cpp:1086-1096)."""
+    from ._cie import CIE_X, CIE_Y, CIE_Z
+    w, v = np.asarray(wavelengths, np.float32), np.asarray(values, np.float32)
+    steps = 1000
+    x = (np.float32(360.0) + (np.arange(steps, dtype=np.float32) / np.float32(steps - 1)) * np.float32(830.0 - 360.0)).astype(np.float32)
+    x = x[(x >= w[0]) & (x <= w[-1])]
+    idx = np.clip(np.searchsorted(w, x, side="right") - 1, 0, len(w) - 2)          # math::find_interval
+    x0, x1, y0, y1 = w[idx], w[idx + 1], v[idx], v[idx + 1]
+    y = (x * y0 - x1 * y0 - x * y1 + x0 * y1) / (x0 - x1)
+    t = (x - np.float32(360.0)) * np.float32(94.0 / 470.0)                           # cie1931_xyz: 95-entry table, lerp
+    i0 = np.clip(t.astype(np.int32), 0, 93)
+    w1 = t - i0
+    xyz = np.stack([(1 - w1) * np.asarray(c, np.float32)[i0] + w1 * np.asarray(c, np.float32)[i0 + 1] for c in (CIE_X, CIE_Y, CIE_Z)], 1)
+    color = (xyz * y[:, None]).astype(np.float32).sum(0, dtype=np.float32) * np.float32((830.0 - 360.0) / steps)
+    M = np.array([[3.240479, -1.537150, -0.498535], [-0.969256, 1.875991, 0.041556], [0.055648, -0.204043, 1.057311]], np.float32)
+    color = M @ color
+    return [float(c) for c in (np.clip(color, 0.0, 1.0) if bounded else np.maximum(color, 0.0))]
+
+
 def _floats(s):
     return [float(x) for x in re.split(r"[\s,]+", s.strip()) if x]
 
@@ -170,14 +196,20 @@ class _Loader:
         return m
 
     # -- plugins ----------------------------------------------------------------------------------------
-    def texture_index(self, value, default):
+    def texture_index(self, value, default, name="reflectance"):
         if value is None:
             return self.sd.add_texture_rgb(default)
         kind, v = value
         if kind == "rgb":
             return self.sd.add_texture_rgb(v)
         if kind == "spectrum":
-            return self.sd.add_texture_spectrum(v["wavelengths"], v["values"])
+            # xml.cpp:1060-1145: spectral variants keep the tabulated spectrum, the others pre-integrate it to a colour
+            # (unbounded for eta / k / *_ior, xml.cpp:1041-1045); one texture carries both forms
+            unbounded = name in ("eta", "k", "int_ior", "ext_ior")
+            rgb = spectrum_to_rgb(v["wavelengths"], np.asarray(v["values"], np.float32) * np.float32(CIE_Y_NORMALIZATION), not unbounded)
+            idx = self.sd.add_texture_rgb(rgb)
+            self.sd.textures[idx]["spectrum"] = (v["wavelengths"], v["values"])
+            return idx
         el = v
         ty = self.attr(el, "type")
         if ty != "bitmap":
@@ -331,6 +363,11 @@ class _Loader:
                 self.sensor(el)
             elif el.tag == "integrator":
                 ty = self.attr(el, "type")
+                if ty == "moment":        # src/integrators/moment.cpp wraps an integrator and adds moment AOVs; channel 0..2 =
+                    inner = [c for c in el if c.tag == "integrator"]     # the nested integrator's image, which is what we render
+                    if len(inner) != 1:
+                        raise NotImplementedError("moment: exactly one nested integrator is supported")
+                    el, ty = inner[0], self.attr(inner[0], "type")
                 if ty != "path":
                     raise NotImplementedError(f"integrator '{ty}' is outside the hot-path scope (path)")
                 p = self.props(el)
