@@ -256,6 +256,11 @@ class _Loader:
             idx = self.sd.add_dielectric(ior("int_ior", "bk7"), ior("ext_ior", "air"),
                                          p["specular_reflectance"][1] if "specular_reflectance" in p else None,
                                          p["specular_transmittance"][1] if "specular_transmittance" in p else None)
+        elif self.params.get("_placeholder_unsupported"):
+            # parity harness only (tests/test_reference_renders.py): keep the geometry of a shape whose BSDF plugin is out of
+            # scope (it still occludes), render it black, and remember it so its pixels can be left out of the comparison
+            idx = self.sd.add_diffuse(0.0)
+            self.sd.placeholder_bsdfs = getattr(self.sd, "placeholder_bsdfs", set()) | {idx}
         else:
             raise NotImplementedError(f"BSDF plugin '{ty}' is outside the hot-path scope (diffuse, roughconductor, dielectric)")
         self.bsdf_cache[id(el)] = idx
