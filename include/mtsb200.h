@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 4
+#define MTSB_ABI_VERSION 5
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -54,21 +54,25 @@ typedef struct mtsb_texture_desc {
 
 /* BSDF: `BSDF::sample/eval/pdf` (include/mitsuba/render/bsdf.h).
  * DIFFUSE src/bsdfs/diffuse.cpp:78-135, ROUGHCONDUCTOR src/bsdfs/roughconductor.cpp:196-394,
- * DIELECTRIC src/bsdfs/dielectric.cpp:201-326. Texture ids index mtsb_scene_desc.textures; -1 = absent. */
-enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2 };
+ * DIELECTRIC src/bsdfs/dielectric.cpp:201-326, CONDUCTOR src/bsdfs/conductor.cpp (smooth: delta reflection),
+ * PLASTIC src/bsdfs/plastic.cpp (smooth dielectric coating over a diffuse base).
+ * Texture ids index mtsb_scene_desc.textures; -1 = absent. */
+enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2, MTSB_BSDF_CONDUCTOR = 3, MTSB_BSDF_PLASTIC = 4 };
 enum { MTSB_MF_BECKMANN = 0, MTSB_MF_GGX = 1 };
 typedef struct mtsb_bsdf_desc {
     int32_t type;
-    int32_t reflectance_tex;        /* DIFFUSE: reflectance */
-    int32_t eta_tex, k_tex;         /* ROUGHCONDUCTOR: complex IOR (rgb) */
-    int32_t specular_reflectance_tex;   /* ROUGHCONDUCTOR / DIELECTRIC, -1 = 1.0 */
+    int32_t reflectance_tex;        /* DIFFUSE: reflectance; PLASTIC: diffuse_reflectance */
+    int32_t eta_tex, k_tex;         /* ROUGHCONDUCTOR / CONDUCTOR: complex IOR (rgb) */
+    int32_t specular_reflectance_tex;   /* ROUGHCONDUCTOR / CONDUCTOR / DIELECTRIC / PLASTIC, -1 = 1.0 */
     int32_t specular_transmittance_tex; /* DIELECTRIC, -1 = 1.0 */
     float   alpha_u, alpha_v;       /* ROUGHCONDUCTOR */
     int32_t distribution;           /* MTSB_MF_* */
     int32_t sample_visible;         /* bool */
-    float   eta;                    /* DIELECTRIC: int_ior / ext_ior */
+    float   eta;                    /* DIELECTRIC / PLASTIC: int_ior / ext_ior */
     int32_t two_sided;              /* bool: wrapped in `twosided` with the same BRDF on both sides
                                        (src/bsdfs/twosided.cpp:66-200); not allowed for DIELECTRIC */
+    int32_t nonlinear;              /* PLASTIC: `nonlinear` (plastic.cpp:154)                          (since ABI 5) */
+    float   specular_sampling_weight;   /* PLASTIC: s_mean / (d_mean + s_mean) of the texture means (plastic.cpp:165-176) */
 } mtsb_bsdf_desc;
 
 /* Emitter: `Emitter::sample_direction/pdf_direction/eval`.

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
 MEM_HOST, MEM_DEVICE = 0, 1
 TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM = 0, 1, 2, 3, 4
 MODE_RGB, MODE_SPECTRAL = 0, 1
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC = 0, 1, 2
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = 0, 1, 2, 3, 4
 MF_BECKMANN, MF_GGX = 0, 1
 EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN, RFILTER_MITCHELL, RFILTER_CATMULLROM, RFILTER_LANCZOS = 0, 1, 2, 3, 4, 5
@@ -33,7 +33,8 @@ class BsdfDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("reflectance_tex", C.c_int32), ("eta_tex", C.c_int32), ("k_tex", C.c_int32),
                 ("specular_reflectance_tex", C.c_int32), ("specular_transmittance_tex", C.c_int32),
                 ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("distribution", C.c_int32),
-                ("sample_visible", C.c_int32), ("eta", C.c_float), ("two_sided", C.c_int32)]
+                ("sample_visible", C.c_int32), ("eta", C.c_float), ("two_sided", C.c_int32), ("nonlinear", C.c_int32),
+                ("specular_sampling_weight", C.c_float)]
 
 
 class EmitterDesc(C.Structure):

@@ -263,7 +263,7 @@ static int upload_struct_arrays(mtsb_scene *s) {
         size_t np = 0; for (const MeshDev &m : s->meshes) np += m.face_count;
         std::vector<uint8_t> cls(np ? np : 1, 0);
         for (const MeshDev &m : s->meshes)
-            for (uint32_t f = 0; f < m.face_count; ++f) cls[m.face_begin + f] = (uint8_t) (1 + s->bsdfs[m.bsdf].type);
+            for (uint32_t f = 0; f < m.face_count; ++f) cls[m.face_begin + f] = (uint8_t) (1 + (s->bsdfs[m.bsdf].type < 2 ? s->bsdfs[m.bsdf].type : 2));   // 2 bits: the rest share a class
         CU(s->prim_class.upload(cls.data(), cls.size(), st));
     }
     CU(cudaStreamSynchronize(st));
@@ -392,6 +392,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex;
         bd.spec_t = b.specular_transmittance_tex; bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution;
         bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
+        bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight;
         if (b.two_sided && b.type == MTSB_BSDF_DIELECTRIC) return fail(MTSB_E_INVALID, "twosided: only materials without a transmission component can be nested");
         if (b.type == MTSB_BSDF_DIFFUSE) CHECK_ARG(tex_ok(b.reflectance_tex, false));
         else if (b.type == MTSB_BSDF_ROUGHCONDUCTOR) CHECK_ARG(tex_ok(b.eta_tex, false) && tex_ok(b.k_tex, false) && tex_ok(b.specular_reflectance_tex, true));

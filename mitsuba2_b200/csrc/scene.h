@@ -17,6 +17,7 @@ struct BsdfDev {
     int type; int refl, eta, k, spec_r, spec_t;
     float alpha_u, alpha_v; int distr; int sample_visible; float eta_f;
     int two_sided;          // `twosided` adapter, same BRDF on both sides (src/bsdfs/twosided.cpp)
+    int nonlinear; float spec_weight;   // plastic (type 4): `nonlinear`, specular sampling weight; type 3 = smooth conductor
 };
 constexpr int kMaxEnvLevels = 20;
 struct EmitterDev {

@@ -285,13 +285,25 @@ struct Microfacet {
 // ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
 // The textures of a BSDF at one surface point, looked up once per path vertex and shared by eval (emitter sample) and
 // sample: diffuse a = reflectance; roughconductor a = eta, b = k, c = specular_reflectance (1 if absent);
-// dielectric a = specular_reflectance, b = specular_transmittance (1 if absent).
+// dielectric a = specular_reflectance, b = specular_transmittance (1 if absent); conductor like roughconductor;
+// plastic a = diffuse_reflectance, b = specular_reflectance (1 if absent).
 template <typename M> struct BsdfTexT { typename M::Spec a, b, c; };
+// fresnel_diffuse_reflectance (include/mitsuba/render/fresnel.h:324-358)
+HD float fresnel_diffuse_reflectance(float eta) {
+    if (eta < 1.f) return -1.4399f * (eta * eta) + 0.7099f * eta + 0.6681f + 0.0636f / eta;
+    float i1 = 1.f / eta, i2 = i1 * i1, i3 = i2 * i1, i4 = i3 * i1, i5 = i4 * i1;
+    return 0.919317f - 3.4793f * i1 + 6.75335f * i2 - 7.80989f * i3 + 4.98554f * i4 - 1.36881f * i5;
+}
+// plastic.cpp:236,262: diffuse reflectance divided by 1 - fdr_int (times the reflectance itself when `nonlinear`)
+HD float3 plastic_div(float3 d, float f, bool nl) { return mk3(d.x / (1.f - (nl ? d.x * f : f)), d.y / (1.f - (nl ? d.y * f : f)), d.z / (1.f - (nl ? d.z * f : f))); }
+HD float4 plastic_div(float4 d, float f, bool nl) { return make_float4(d.x / (1.f - (nl ? d.x * f : f)), d.y / (1.f - (nl ? d.y * f : f)), d.z / (1.f - (nl ? d.z * f : f)), d.w / (1.f - (nl ? d.w * f : f))); }
+template <typename M> HD typename M::Spec plastic_diffuse(const BsdfDev &b, typename M::Spec d) { return plastic_div(d, fresnel_diffuse_reflectance(1.f / b.eta_f), b.nonlinear != 0); }
 template <typename M>
 HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, float v, float4 wav) {
     BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f);
     if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
-    else if (b.type == 1) {
+    else if (b.type == 4) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
+    else if (b.type == 1 || b.type == 3) {
         t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
         if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
     } else {
@@ -324,6 +336,31 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         Spec F = fresnel_conductor(dot(si.wi, m), tx.a, tx.b);
         if (b.spec_r >= 0) F *= tx.c;
         bs.weight = active ? F * weight : M::splat(0.f);
+        return bs;
+    }
+    if (b.type == 3) {            // src/bsdfs/conductor.cpp (sample): delta reflection, weight = reflectance * F(cos_i)
+        if (!(cos_i > 0.f)) return bs;
+        bs.wo = mk3(-si.wi.x, -si.wi.y, si.wi.z); bs.pdf = 1.f; bs.delta = true;
+        Spec F = fresnel_conductor(cos_i, tx.a, tx.b);
+        if (b.spec_r >= 0) F = tx.c * F;
+        bs.weight = F;
+        return bs;
+    }
+    if (b.type == 4) {            // src/bsdfs/plastic.cpp:178-245
+        if (!(cos_i > 0.f)) return bs;
+        float f_i, ct, e1, e2; fresnel_dielectric(cos_i, b.eta_f, f_i, ct, e1, e2);
+        float prob_specular = f_i * b.spec_weight, prob_diffuse = (1.f - f_i) * (1.f - b.spec_weight);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+        if (s1 < prob_specular) {
+            bs.wo = mk3(-si.wi.x, -si.wi.y, si.wi.z); bs.pdf = prob_specular; bs.delta = true;
+            Spec value = M::splat(f_i / bs.pdf);
+            if (b.spec_r >= 0) value *= tx.b;
+            bs.weight = value;
+        } else {
+            bs.wo = square_to_cosine_hemisphere(sx, sy); bs.pdf = prob_diffuse * (kInvPi * bs.wo.z);
+            float f_o; fresnel_dielectric(bs.wo.z, b.eta_f, f_o, ct, e1, e2);
+            bs.weight = plastic_diffuse<M>(b, tx.a) * ((1.f / (b.eta_f * b.eta_f)) * (1.f - f_i) * (1.f - f_o) / prob_diffuse);
+        }
         return bs;
     }
     // src/bsdfs/dielectric.cpp:201-316
@@ -367,6 +404,13 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
             pdf = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
         return;
     }
+    if (b.type == 4) {            // src/bsdfs/plastic.cpp:247-296: the diffuse lobe (the specular one is a delta)
+        if (!(ci > 0.f && co > 0.f)) return;
+        float f_i, f_o, ct, e1, e2; fresnel_dielectric(ci, b.eta_f, f_i, ct, e1, e2); fresnel_dielectric(co, b.eta_f, f_o, ct, e1, e2);
+        val = plastic_diffuse<M>(b, tx.a) * ((kInvPi * co) * (1.f / (b.eta_f * b.eta_f)) * (1.f - f_i) * (1.f - f_o));
+        float prob_specular = f_i * b.spec_weight, prob_diffuse = (1.f - f_i) * (1.f - b.spec_weight);
+        pdf = (kInvPi * co) * (prob_diffuse / (prob_specular + prob_diffuse));
+    }
 }
 
 // `twosided` (src/bsdfs/twosided.cpp:98-200): on the back side mirror wi (and wo) about the surface and use the
@@ -396,6 +440,6 @@ template <typename M = Rgb>
 HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
     bsdf_eval_pdf<M>(sc, b, si, wo, val, pdf, bsdf_textures<M>(sc, b, si.u, si.v, wav));
 }
-HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2; }
+HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2 && b.type != 3; }      // dielectric and smooth conductor are all-delta
 
 } // namespace mtsb

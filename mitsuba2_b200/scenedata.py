@@ -178,6 +178,30 @@ class SceneData:
                            "specular_transmittance_tex": -1 if specular_transmittance is None else self.add_texture_rgb(specular_transmittance)})
         return len(self.bsdfs) - 1
 
+    def add_conductor(self, eta=None, k=None, specular_reflectance=None, material=None):
+        """Smooth ``conductor`` (src/bsdfs/conductor.cpp): delta reflection weighted by the conductor Fresnel term."""
+        idx = self.add_roughconductor(eta, k, specular_reflectance=specular_reflectance, material=material)
+        b = self.bsdfs[idx]
+        self.bsdfs[idx] = {"type": A.BSDF_CONDUCTOR, "eta_tex": b["eta_tex"], "k_tex": b["k_tex"],
+                           "specular_reflectance_tex": b["specular_reflectance_tex"]}
+        return idx
+
+    def _texture_mean(self, tex_id):
+        """``Texture::mean`` of an rgb variant: srgb.cpp:52-57 (mean of the colour), bitmap.cpp:333 (mean of the texels)."""
+        t = self.textures[tex_id]
+        return float(np.mean(t["value"])) if t["type"] == A.TEX_CONSTANT else float(np.mean(t["data"]))
+
+    def add_plastic(self, diffuse_reflectance=0.5, int_ior=1.49, ext_ior=1.000277, specular_reflectance=None, nonlinear=False):
+        """Smooth ``plastic`` (src/bsdfs/plastic.cpp): dielectric coating (delta reflection) over a diffuse base; defaults
+        `polypropylene` / `air` (:138-141).  The lobe-selection weight uses the textures' rgb means in both colour modes."""
+        d = self._tex(diffuse_reflectance)
+        s_id = -1 if specular_reflectance is None else self._tex(specular_reflectance)
+        d_mean, s_mean = self._texture_mean(d), (1.0 if s_id < 0 else self._texture_mean(s_id))
+        self.bsdfs.append({"type": A.BSDF_PLASTIC, "reflectance_tex": d, "specular_reflectance_tex": s_id,
+                           "eta": float(int_ior) / float(ext_ior), "nonlinear": int(bool(nonlinear)),
+                           "specular_sampling_weight": s_mean / (d_mean + s_mean)})
+        return len(self.bsdfs) - 1
+
     def add_mesh(self, mesh, area_radiance=None):
         self.meshes.append(mesh)
         mid = len(self.meshes) - 1
@@ -265,6 +289,8 @@ class SceneData:
             bd[i].distribution, bd[i].sample_visible = b.get("distribution", 0), b.get("sample_visible", 1)
             bd[i].eta = b.get("eta", 1.0)
             bd[i].two_sided = int(b.get("two_sided", 0))
+            bd[i].nonlinear = int(b.get("nonlinear", 0))
+            bd[i].specular_sampling_weight = float(b.get("specular_sampling_weight", 0.5))
         spectral = self.mode == "spectral"
         if self.mode not in ("rgb", "spectral"):
             raise ValueError("SceneData.mode must be 'rgb' or 'spectral'")

@@ -237,7 +237,15 @@ class _Loader:
             idx = len(self.sd.bsdfs) - 1
         elif ty == "diffuse":
             idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
-        elif ty == "roughconductor":
+        elif ty == "plastic":
+            def pior(v, d):
+                v = p.get(v, d)
+                return IOR_NAMES[v.lower()] if isinstance(v, str) else float(v)
+            idx = self.sd.add_plastic(self.texture_index(p.get("diffuse_reflectance"), 0.5), pior("int_ior", "polypropylene"),
+                                      pior("ext_ior", "air"),
+                                      self.texture_index(p["specular_reflectance"], 1.0) if "specular_reflectance" in p else None,
+                                      p.get("nonlinear", False))
+        elif ty in ("roughconductor", "conductor"):
             material = None
             if "eta" in p or "k" in p:
                 eta, k = p.get("eta", ("rgb", [0.0] * 3))[1], p.get("k", ("rgb", [1.0] * 3))[1]
@@ -246,9 +254,12 @@ class _Loader:
                 if material.lower() not in CONDUCTORS_RGB:
                     raise NotImplementedError(f"conductor material '{material}' is not in the built-in table")
             alpha = p.get("alpha", 0.1)
-            idx = self.sd.add_roughconductor(eta, k, p.get("alpha_u", alpha), p.get("alpha_v", alpha), p.get("distribution", "beckmann"),
-                                             p.get("sample_visible", True),
-                                             p["specular_reflectance"][1] if "specular_reflectance" in p else None, material=material)
+            spec_r = p["specular_reflectance"][1] if "specular_reflectance" in p else None
+            if ty == "conductor":
+                idx = self.sd.add_conductor(eta, k, spec_r, material=material)
+            else:
+                idx = self.sd.add_roughconductor(eta, k, p.get("alpha_u", alpha), p.get("alpha_v", alpha), p.get("distribution", "beckmann"),
+                                                 p.get("sample_visible", True), spec_r, material=material)
         elif ty == "dielectric":
             def ior(v, d):
                 v = p.get(v, d)
@@ -262,7 +273,7 @@ class _Loader:
             idx = self.sd.add_diffuse(0.0)
             self.sd.placeholder_bsdfs = getattr(self.sd, "placeholder_bsdfs", set()) | {idx}
         else:
-            raise NotImplementedError(f"BSDF plugin '{ty}' is outside the hot-path scope (diffuse, roughconductor, dielectric)")
+            raise NotImplementedError(f"BSDF plugin '{ty}' is outside the hot-path scope (diffuse, roughconductor, dielectric, conductor, plastic)")
         self.bsdf_cache[id(el)] = idx
         return idx
 

@@ -711,6 +711,12 @@ static col tex_eval(const orc_scene *s, int id, float u, float v, const float *w
     return r;
 }
 typedef struct { v3 wo; col weight; float pdf, eta; int delta; } obs;
+/* fresnel_diffuse_reflectance (include/mitsuba/render/fresnel.h:324-358) */
+static float fresnel_diffuse_reflectance(float eta) {
+    if (eta < 1.f) return -1.4399f * (eta * eta) + 0.7099f * eta + 0.6681f + 0.0636f / eta;
+    float i1 = 1.f / eta, i2 = i1 * i1, i3 = i2 * i1, i4 = i3 * i1, i5 = i4 * i1;
+    return 0.919317f - 3.4793f * i1 + 6.75335f * i2 - 7.80989f * i3 + 4.98554f * i4 - 1.36881f * i5;
+}
 static col fresnel_conductor_col(float c, col eta, col k) { col r; for (int i = 0; i < 4; ++i) r.c[i] = orc_fresnel_conductor(c, eta.c[i], k.c[i]); return r; }
 static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
@@ -734,6 +740,35 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         col F = fresnel_conductor_col(vdot(si->wi, m), eta, k);
         if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
         bs.weight = active ? cscale(F, weight) : C1(0.f);
+        return bs;
+    }
+    if (b->type == MTSB_BSDF_CONDUCTOR) {              /* conductor.cpp: sample (delta reflection, weight = R * F(cos_i)) */
+        if (!(cos_theta_i > 0.f)) return bs;
+        bs.wo = V(-si->wi.x, -si->wi.y, si->wi.z); bs.pdf = 1.f; bs.delta = 1;
+        col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+        col F = fresnel_conductor_col(cos_theta_i, eta, k);
+        if (b->specular_reflectance_tex >= 0) F = cmul(tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav), F);
+        bs.weight = F; return bs;
+    }
+    if (b->type == MTSB_BSDF_PLASTIC) {                /* plastic.cpp:178-245 */
+        if (!(cos_theta_i > 0.f)) return bs;
+        float f_i, ct, e1, e2; fresnel(cos_theta_i, b->eta, &f_i, &ct, &e1, &e2);
+        float ssw = b->specular_sampling_weight;
+        float prob_specular = f_i * ssw, prob_diffuse = (1.f - f_i) * (1.f - ssw);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+        if (s1 < prob_specular) {
+            bs.wo = V(-si->wi.x, -si->wi.y, si->wi.z); bs.pdf = prob_specular; bs.delta = 1;
+            col value = C1(f_i / bs.pdf);
+            if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            bs.weight = value;
+        } else {
+            bs.wo = cosine_hemisphere(sx, sy); bs.pdf = prob_diffuse * (INV_PI_F * bs.wo.z);
+            float f_o; fresnel(bs.wo.z, b->eta, &f_o, &ct, &e1, &e2);
+            float fdr_int = fresnel_diffuse_reflectance(1.f / b->eta), inv_eta_2 = 1.f / (b->eta * b->eta);
+            col value = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+            for (int i = 0; i < 4; ++i) value.c[i] /= 1.f - (b->nonlinear ? value.c[i] * fdr_int : fdr_int);
+            bs.weight = cscale(value, inv_eta_2 * (1.f - f_i) * (1.f - f_o) / prob_diffuse);
+        }
         return bs;
     }
     /* dielectric.cpp:201-316 */
@@ -768,6 +803,17 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         }
         if (vdot(si->wi, H) > 0.f && vdot(wo, H) > 0.f)
             *pdf = b->sample_visible ? D * mf_g1(&distr, si->wi, H) / (4.f * cos_theta_i) : mf_pdf(&distr, si->wi, H) / (4.f * vdot(wo, H));
+        return;
+    }
+    if (b->type == MTSB_BSDF_PLASTIC) {                /* plastic.cpp:247-296 (the diffuse lobe; the specular one is a delta) */
+        if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return;
+        float f_i, f_o, ct, e1, e2; fresnel(cos_theta_i, b->eta, &f_i, &ct, &e1, &e2); fresnel(cos_theta_o, b->eta, &f_o, &ct, &e1, &e2);
+        float fdr_int = fresnel_diffuse_reflectance(1.f / b->eta), inv_eta_2 = 1.f / (b->eta * b->eta);
+        col diff = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+        for (int i = 0; i < 4; ++i) diff.c[i] /= 1.f - (b->nonlinear ? diff.c[i] * fdr_int : fdr_int);
+        *val = cscale(diff, (INV_PI_F * cos_theta_o) * inv_eta_2 * (1.f - f_i) * (1.f - f_o));
+        float ssw = b->specular_sampling_weight, prob_specular = f_i * ssw, prob_diffuse = (1.f - f_i) * (1.f - ssw);
+        *pdf = (INV_PI_F * cos_theta_o) * (prob_diffuse / (prob_specular + prob_diffuse));
     }
 }
 /* TwoSidedBRDF::sample / eval / pdf (twosided.cpp:98-200) with the same nested BRDF on both sides: on the back side flip
@@ -991,7 +1037,7 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
         }
         if ((uint32_t) depth >= (uint32_t) s->max_depth) break;
         const mtsb_bsdf_desc *bsdf = &s->bsdfs[s->meshes[si.mesh].bsdf];
-        if (bsdf->type != MTSB_BSDF_DIELECTRIC) {     /* has a Smooth lobe */
+        if (bsdf->type != MTSB_BSDF_DIELECTRIC && bsdf->type != MTSB_BSDF_CONDUCTOR) {     /* has a Smooth lobe */
             float sx = pcg_float(rng), sy = pcg_float(rng);
             if (s->n_emitters > 0) {
                 ods ds = sample_emitter_direction(s, si.p, sx, sy, wav);

@@ -253,6 +253,12 @@ class HostSim:
         self.lib().hs_sample_emitter_direction(self.h, ref_p.shape[0], _p(ref_p), _p(s2), _p(out))
         return out
 
+    def bsdf_sample(self, bsdf_id, wi, uv, s1, s2):
+        wi, uv, s1, s2 = _f32(wi), _f32(uv), _f32(s1), _f32(s2)
+        out = np.empty((wi.shape[0], 9), np.float32)
+        self.lib().hs_bsdf_sample(self.h, bsdf_id, wi.shape[0], _p(wi), _p(uv), _p(s1), _p(s2), _p(out))
+        return out
+
     def render_grad(self, dL_dimage, tex_id, sensor=0, spp=None, seed=0, spp_begin=0, spp_total=None):
         spp = self.data.spp if spp is None else spp
         spp_total = spp_begin + spp if spp_total is None else spp_total
@@ -351,6 +357,33 @@ def material_scene(res=(48, 32), spp=8, envmap=True, area=True, named_conductor=
         sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
     if envmap:
         sd.add_envmap(synthetic_envmap())
+    sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 6, 5, spp
+    return sd
+
+
+def n4_scene(res=(48, 32), spp=8):
+    """SURVEY 8f N4 plugins: smooth `conductor` (Au) and `plastic` (plain and nonlinear, textured base) spheres on a
+    diffuse ground under an area light and a constant background."""
+    sd = SceneData()
+    rng = np.random.default_rng(5)
+    ground = M.quad([-10, -1.2, -10], [-10, -1.2, 10], [10, -1.2, 10], [10, -1.2, -10])
+    ground.bsdf = sd.add_diffuse([0.5, 0.45, 0.4])
+    sd.add_mesh(ground)
+    s1 = M.displaced_sphere(16, 32, radius=0.7, center=(-1.2, -0.5, 0), displace=False)
+    s1.bsdf = sd.add_conductor(material="Au")
+    sd.add_mesh(s1)
+    s2 = M.displaced_sphere(16, 32, radius=0.7, center=(0.3, -0.5, 0), displace=False)
+    s2.bsdf = sd.add_plastic([0.1, 0.27, 0.36], int_ior=1.9)
+    sd.add_mesh(s2)
+    s3 = M.displaced_sphere(16, 32, radius=0.5, center=(1.6, -0.7, -0.4), displace=False)
+    s3.bsdf = sd.add_plastic(sd.add_texture_bitmap(0.2 + 0.6 * rng.random((8, 8, 3)).astype(np.float32)), specular_reflectance=[0.9, 0.8, 0.7],
+                             nonlinear=True)
+    sd.add_mesh(s3)
+    light = M.quad([-0.5, 3, -0.5], [0.5, 3, -0.5], [0.5, 3, 0.5], [-0.5, 3, 0.5])
+    light.bsdf = sd.add_diffuse(0.5)
+    sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
+    sd.add_constant([0.4, 0.5, 0.7])
     sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
     sd.max_depth, sd.rr_depth, sd.spp = 6, 5, spp
     return sd

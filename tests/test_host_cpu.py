@@ -88,6 +88,29 @@ def test_hostsim_material_film_close_to_oracle():
     assert bad.mean() < 0.02                               # a path through a specular chain may flip at an edge
 
 
+def test_hostsim_n4_plugins_match_oracle():
+    """`conductor` and `plastic` (src/bsdfs/{conductor,plastic}.cpp): BSDF::sample of the product's stage bodies vs the
+    oracle on random inputs, and the films of a scene that uses them on the same sample streams."""
+    sd = H.n4_scene(res=(24, 16), spp=4)
+    orc, hs = Oracle(sd), HostSim(sd)
+    rng = np.random.default_rng(2)
+    n = 2048
+    wi = rng.normal(size=(n, 3)); wi[:, 2] = np.abs(wi[:, 2]) + 0.02; wi /= np.linalg.norm(wi, axis=1, keepdims=True)
+    wi[: n // 8, 2] *= -1
+    uv, s1, s2 = rng.random((n, 2)), rng.random(n), rng.random((n, 2))
+    for bid in range(len(sd.bsdfs)):
+        a, b = orc.bsdf_sample(bid, wi, uv, s1, s2), hs.bsdf_sample(bid, wi, uv, s1, s2)
+        assert np.allclose(a, b, rtol=1e-4, atol=1e-6), bid
+    # plastic KAT: normal incidence on eta = 1.9 -> F = ((eta - 1) / (eta + 1))^2; specular lobe weight = F / P(specular)
+    pl = next(i for i, b in enumerate(sd.bsdfs) if b["type"] == H.A.BSDF_PLASTIC)
+    out = orc.bsdf_sample(pl, np.array([[0, 0, 1.0]]), np.zeros((1, 2)), np.array([0.0]), np.zeros((1, 2)))[0]
+    F = ((1.9 / 1.000277 - 1) / (1.9 / 1.000277 + 1)) ** 2
+    assert out[8] == 1 and np.allclose(out[:3], [0, 0, 1]) and abs(out[3] * out[5] - F) < 1e-5
+    a, b = orc.render_xyzaw(seed=1), hs.render_xyzaw(seed=1)
+    bad = np.abs(a - b).max(axis=2) > 1e-3 * (1 + np.abs(a).max(axis=2))
+    assert bad.mean() < 0.02
+
+
 def test_sample_range_union_equals_full_render():
     sd = H.cbox_scene(res=12, spp=6)
     h = HostSim(sd)
