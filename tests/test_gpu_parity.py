@@ -98,6 +98,7 @@ def test_empty_and_tiny_scenes(mi):
     (lambda: H.cbox_scene(48, 8, "mitchell"), 8, 2e-3),
     (lambda: H.cbox_scene(48, 8, "lanczos"), 8, 2e-3),
     (lambda: H.material_scene((96, 64), 16), 16, 2e-2),
+    (lambda: H.n4_scene((96, 64), 16), 16, 2e-2),          # smooth conductor + plastic
 ])
 def test_render_matches_oracle_per_sample_streams(mi, scene_fn, spp, tol):
     """Same per-sample PCG32 streams on both sides => images agree up to float noise / rare path divergence."""
