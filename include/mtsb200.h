@@ -57,7 +57,8 @@ typedef struct mtsb_texture_desc {
  * DIELECTRIC src/bsdfs/dielectric.cpp:201-326, CONDUCTOR src/bsdfs/conductor.cpp (smooth: delta reflection),
  * PLASTIC src/bsdfs/plastic.cpp (smooth dielectric coating over a diffuse base).
  * Texture ids index mtsb_scene_desc.textures; -1 = absent. */
-enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2, MTSB_BSDF_CONDUCTOR = 3, MTSB_BSDF_PLASTIC = 4 };
+enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2, MTSB_BSDF_CONDUCTOR = 3, MTSB_BSDF_PLASTIC = 4,
+       MTSB_BSDF_ROUGHDIELECTRIC = 5 };   /* src/bsdfs/roughdielectric.cpp: microfacet reflection + transmission */
 enum { MTSB_MF_BECKMANN = 0, MTSB_MF_GGX = 1 };
 typedef struct mtsb_bsdf_desc {
     int32_t type;
@@ -65,10 +66,10 @@ typedef struct mtsb_bsdf_desc {
     int32_t eta_tex, k_tex;         /* ROUGHCONDUCTOR / CONDUCTOR: complex IOR (rgb) */
     int32_t specular_reflectance_tex;   /* ROUGHCONDUCTOR / CONDUCTOR / DIELECTRIC / PLASTIC, -1 = 1.0 */
     int32_t specular_transmittance_tex; /* DIELECTRIC, -1 = 1.0 */
-    float   alpha_u, alpha_v;       /* ROUGHCONDUCTOR */
+    float   alpha_u, alpha_v;       /* ROUGHCONDUCTOR / ROUGHDIELECTRIC */
     int32_t distribution;           /* MTSB_MF_* */
     int32_t sample_visible;         /* bool */
-    float   eta;                    /* DIELECTRIC / PLASTIC: int_ior / ext_ior */
+    float   eta;                    /* DIELECTRIC / PLASTIC / ROUGHDIELECTRIC: int_ior / ext_ior */
     int32_t two_sided;              /* bool: wrapped in `twosided` with the same BRDF on both sides
                                        (src/bsdfs/twosided.cpp:66-200); not allowed for DIELECTRIC */
     int32_t nonlinear;              /* PLASTIC: `nonlinear` (plastic.cpp:154)                          (since ABI 5) */

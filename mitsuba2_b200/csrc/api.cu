@@ -398,7 +398,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         else if (b.type == MTSB_BSDF_ROUGHCONDUCTOR || b.type == MTSB_BSDF_CONDUCTOR) CHECK_ARG(tex_ok(b.eta_tex, false) && tex_ok(b.k_tex, false) && tex_ok(b.specular_reflectance_tex, true));
         else if (b.type == MTSB_BSDF_PLASTIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.reflectance_tex, false) && tex_ok(b.specular_reflectance_tex, true) &&
                                                          b.specular_sampling_weight >= 0.f && b.specular_sampling_weight <= 1.f);
-        else if (b.type == MTSB_BSDF_DIELECTRIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.specular_reflectance_tex, true) && tex_ok(b.specular_transmittance_tex, true));
+        else if (b.type == MTSB_BSDF_DIELECTRIC || b.type == MTSB_BSDF_ROUGHDIELECTRIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.specular_reflectance_tex, true) && tex_ok(b.specular_transmittance_tex, true));
         else return fail(MTSB_E_INVALID, "unknown BSDF type");
         s->bsdfs.push_back(bd);
     }

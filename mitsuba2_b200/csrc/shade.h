@@ -306,7 +306,7 @@ HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, floa
     else if (b.type == 1 || b.type == 3) {
         t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
         if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
-    } else {
+    } else {                      // dielectric, rough dielectric
         if (b.spec_r >= 0) t.a = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
         if (b.spec_t >= 0) t.b = tex_eval_m<M>(sc, b.spec_t, u, v, wav);
     }
@@ -363,6 +363,37 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         }
         return bs;
     }
+    if (b.type == 5) {            // src/bsdfs/roughdielectric.cpp (sample): microfacet normal, then Fresnel lobe choice
+        if (cos_i == 0.f) return bs;
+        Microfacet distr(b.distr, b.alpha_u, b.alpha_v, b.sample_visible != 0), sample_distr = distr;
+        if (!b.sample_visible) { float sc_ = 1.2f - 0.2f * sqrtf(fabsf(cos_i)); sample_distr.au *= sc_; sample_distr.av *= sc_; }
+        float3 wi_up = mk3(mulsign(si.wi.x, cos_i), mulsign(si.wi.y, cos_i), mulsign(si.wi.z, cos_i));
+        float3 m = sample_distr.sample(wi_up, sx, sy, bs.pdf);
+        if (bs.pdf == 0.f) return bs;
+        float F, cos_t, eta_it, eta_ti, wim = dot(si.wi, m);
+        fresnel_dielectric(wim, b.eta_f, F, cos_t, eta_it, eta_ti);
+        bool sel_r = s1 <= F;
+        Spec weight = M::splat(1.f);
+        bs.pdf *= sel_r ? F : 1.f - F;
+        bs.eta = sel_r ? 1.f : eta_it;
+        float dwh_dwo;
+        if (sel_r) {
+            bs.wo = m * (2.f * wim) - si.wi;
+            if (b.spec_r >= 0) weight *= tx.a;
+            dwh_dwo = 1.f / (4.f * dot(bs.wo, m));
+        } else {
+            bs.wo = m * fmaf(wim, eta_ti, cos_t) - si.wi * eta_ti;
+            Spec factor = M::splat(sqr(eta_ti));
+            if (b.spec_t >= 0) factor *= tx.b;
+            weight *= factor;
+            dwh_dwo = (sqr(bs.eta) * dot(bs.wo, m)) / sqr(wim + bs.eta * dot(bs.wo, m));
+        }
+        if (b.sample_visible) weight *= distr.smith_g1(bs.wo, m);
+        else weight *= distr.G(si.wi, bs.wo, m) * wim / (cos_i * m.z);
+        bs.pdf *= fabsf(dwh_dwo);
+        bs.weight = weight;
+        return bs;
+    }
     // src/bsdfs/dielectric.cpp:201-316
     float r_i, cos_t, eta_it, eta_ti;
     fresnel_dielectric(cos_i, b.eta_f, r_i, cos_t, eta_it, eta_ti);
@@ -402,6 +433,32 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
         }
         if (dot(si.wi, H) > 0.f && dot(wo, H) > 0.f)
             pdf = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
+        return;
+    }
+    if (b.type == 5) {            // src/bsdfs/roughdielectric.cpp (eval, pdf)
+        if (ci == 0.f) return;
+        bool reflect = ci * co > 0.f;
+        float eta = ci > 0.f ? b.eta_f : 1.f / b.eta_f, inv_eta = ci > 0.f ? 1.f / b.eta_f : b.eta_f;
+        float3 m = normalize(si.wi + wo * (reflect ? 1.f : eta));
+        m = mk3(mulsign(m.x, m.z), mulsign(m.y, m.z), mulsign(m.z, m.z));
+        Microfacet distr(b.distr, b.alpha_u, b.alpha_v, b.sample_visible != 0), sample_distr = distr;
+        float wim = dot(si.wi, m), wom = dot(wo, m);
+        float D = distr.eval(m), F, ct, e1, e2;
+        fresnel_dielectric(wim, b.eta_f, F, ct, e1, e2);
+        float G = distr.G(si.wi, wo, m);
+        if (reflect) {
+            val = M::splat(F * D * G / (4.f * fabsf(ci)));
+            if (b.spec_r >= 0) val *= tx.a;
+        } else {
+            val = M::splat(fabsf((sqr(inv_eta) * (1.f - F) * D * G * eta * eta * wim * wom) / (ci * sqr(wim + eta * wom))));
+            if (b.spec_t >= 0) val *= tx.b;
+        }
+        if (!(wim * ci > 0.f && wom * co > 0.f)) return;          // pdf only: micro / macro surface disagree on the side
+        float dwh_dwo = reflect ? 1.f / (4.f * wom) : (eta * eta * wom) / sqr(wim + eta * wom);
+        if (!b.sample_visible) { float sc_ = 1.2f - 0.2f * sqrtf(fabsf(ci)); sample_distr.au *= sc_; sample_distr.av *= sc_; }
+        float prob = sample_distr.pdf(mk3(mulsign(si.wi.x, ci), mulsign(si.wi.y, ci), mulsign(si.wi.z, ci)), m);
+        prob *= reflect ? F : 1.f - F;
+        pdf = prob * fabsf(dwh_dwo);
         return;
     }
     if (b.type == 4) {            // src/bsdfs/plastic.cpp:247-296: the diffuse lobe (the specular one is a delta)

@@ -202,6 +202,17 @@ class SceneData:
                            "specular_sampling_weight": s_mean / (d_mean + s_mean)})
         return len(self.bsdfs) - 1
 
+    def add_roughdielectric(self, int_ior=1.5046, ext_ior=1.000277, alpha=0.1, alpha_v=None, distribution="beckmann", sample_visible=True,
+                            specular_reflectance=None, specular_transmittance=None):
+        """``roughdielectric`` (src/bsdfs/roughdielectric.cpp): microfacet reflection and refraction."""
+        self.bsdfs.append({"type": A.BSDF_ROUGHDIELECTRIC, "eta": float(int_ior) / float(ext_ior), "alpha_u": float(alpha),
+                           "alpha_v": float(alpha if alpha_v is None else alpha_v),
+                           "distribution": A.MF_GGX if distribution.lower() == "ggx" else A.MF_BECKMANN,
+                           "sample_visible": int(bool(sample_visible)),
+                           "specular_reflectance_tex": -1 if specular_reflectance is None else self.add_texture_rgb(specular_reflectance),
+                           "specular_transmittance_tex": -1 if specular_transmittance is None else self.add_texture_rgb(specular_transmittance)})
+        return len(self.bsdfs) - 1
+
     def add_mesh(self, mesh, area_radiance=None):
         self.meshes.append(mesh)
         mid = len(self.meshes) - 1
@@ -223,7 +234,7 @@ class SceneData:
 
     def make_two_sided(self, bsdf_id):
         """``twosided`` adapter with the same BRDF on both sides (src/bsdfs/twosided.cpp); returns the id."""
-        if self.bsdfs[bsdf_id]["type"] == A.BSDF_DIELECTRIC:
+        if self.bsdfs[bsdf_id]["type"] in (A.BSDF_DIELECTRIC, A.BSDF_ROUGHDIELECTRIC):
             raise ValueError("Only materials without a transmission component can be nested!")
         self.bsdfs[bsdf_id]["two_sided"] = 1
         return bsdf_id

@@ -260,13 +260,18 @@ class _Loader:
             else:
                 idx = self.sd.add_roughconductor(eta, k, p.get("alpha_u", alpha), p.get("alpha_v", alpha), p.get("distribution", "beckmann"),
                                                  p.get("sample_visible", True), spec_r, material=material)
-        elif ty == "dielectric":
+        elif ty in ("dielectric", "roughdielectric"):
             def ior(v, d):
                 v = p.get(v, d)
                 return IOR_NAMES[v.lower()] if isinstance(v, str) else float(v)
-            idx = self.sd.add_dielectric(ior("int_ior", "bk7"), ior("ext_ior", "air"),
-                                         p["specular_reflectance"][1] if "specular_reflectance" in p else None,
-                                         p["specular_transmittance"][1] if "specular_transmittance" in p else None)
+            sr = p["specular_reflectance"][1] if "specular_reflectance" in p else None
+            st = p["specular_transmittance"][1] if "specular_transmittance" in p else None
+            if ty == "dielectric":
+                idx = self.sd.add_dielectric(ior("int_ior", "bk7"), ior("ext_ior", "air"), sr, st)
+            else:
+                alpha = p.get("alpha", 0.1)
+                idx = self.sd.add_roughdielectric(ior("int_ior", "bk7"), ior("ext_ior", "air"), p.get("alpha_u", alpha), p.get("alpha_v", alpha),
+                                                  p.get("distribution", "beckmann"), p.get("sample_visible", True), sr, st)
         elif self.params.get("_placeholder_unsupported"):
             # parity harness only (tests/test_reference_renders.py): keep the geometry of a shape whose BSDF plugin is out of
             # scope (it still occludes), render it black, and remember it so its pixels can be left out of the comparison

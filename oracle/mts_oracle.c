@@ -771,6 +771,36 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         }
         return bs;
     }
+    if (b->type == MTSB_BSDF_ROUGHDIELECTRIC) {        /* roughdielectric.cpp: sample */
+        if (cos_theta_i == 0.f) return bs;
+        mf_t distr = mf_make(b->distribution, b->alpha_u, b->alpha_v, b->sample_visible), sample_distr = distr;
+        if (!b->sample_visible) { float sc = 1.2f - .2f * sqrtf(fabsf(cos_theta_i)); sample_distr.au *= sc; sample_distr.av *= sc; }
+        v3 wi_up = V(mulsign(si->wi.x, cos_theta_i), mulsign(si->wi.y, cos_theta_i), mulsign(si->wi.z, cos_theta_i));
+        v3 m = mf_sample(&sample_distr, wi_up, sx, sy, &bs.pdf);
+        if (bs.pdf == 0.f) return bs;
+        float F, cos_theta_t, eta_it, eta_ti, wim = vdot(si->wi, m);
+        fresnel(wim, b->eta, &F, &cos_theta_t, &eta_it, &eta_ti);
+        int selected_r = s1 <= F;
+        col weight = C1(1.f);
+        bs.pdf *= selected_r ? F : 1.f - F;
+        bs.eta = selected_r ? 1.f : eta_it;
+        float dwh_dwo;
+        if (selected_r) {
+            bs.wo = vsub(vscale(m, 2.f * wim), si->wi);
+            if (b->specular_reflectance_tex >= 0) weight = cmul(weight, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            dwh_dwo = 1.f / (4.f * vdot(bs.wo, m));
+        } else {
+            bs.wo = vsub(vscale(m, fmaf(wim, eta_ti, cos_theta_t)), vscale(si->wi, eta_ti));
+            col factor = C1(sqrf(eta_ti));
+            if (b->specular_transmittance_tex >= 0) factor = cmul(factor, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav));
+            weight = cmul(weight, factor);
+            dwh_dwo = (sqrf(bs.eta) * vdot(bs.wo, m)) / sqrf(wim + bs.eta * vdot(bs.wo, m));
+        }
+        if (b->sample_visible) weight = cscale(weight, mf_g1(&distr, bs.wo, m));
+        else weight = cscale(weight, mf_g1(&distr, si->wi, m) * mf_g1(&distr, bs.wo, m) * wim / (cos_theta_i * m.z));
+        bs.pdf *= fabsf(dwh_dwo);
+        bs.weight = weight; return bs;
+    }
     /* dielectric.cpp:201-316 */
     float r_i, cos_theta_t, eta_it, eta_ti; fresnel(cos_theta_i, b->eta, &r_i, &cos_theta_t, &eta_it, &eta_ti);
     float t_i = 1.f - r_i; int selected_r = s1 <= r_i;
@@ -803,6 +833,31 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         }
         if (vdot(si->wi, H) > 0.f && vdot(wo, H) > 0.f)
             *pdf = b->sample_visible ? D * mf_g1(&distr, si->wi, H) / (4.f * cos_theta_i) : mf_pdf(&distr, si->wi, H) / (4.f * vdot(wo, H));
+        return;
+    }
+    if (b->type == MTSB_BSDF_ROUGHDIELECTRIC) {        /* roughdielectric.cpp: eval, pdf */
+        if (cos_theta_i == 0.f) return;
+        int reflect = cos_theta_i * cos_theta_o > 0.f;
+        float eta = cos_theta_i > 0.f ? b->eta : 1.f / b->eta, inv_eta = cos_theta_i > 0.f ? 1.f / b->eta : b->eta;
+        v3 m = vnormalize(vadd(si->wi, vscale(wo, reflect ? 1.f : eta)));
+        m = V(mulsign(m.x, m.z), mulsign(m.y, m.z), mulsign(m.z, m.z));
+        mf_t distr = mf_make(b->distribution, b->alpha_u, b->alpha_v, b->sample_visible), sample_distr = distr;
+        float wim = vdot(si->wi, m), wom = vdot(wo, m);
+        float D = mf_eval(&distr, m), F, ct, e1, e2; fresnel(wim, b->eta, &F, &ct, &e1, &e2);
+        float G = mf_g1(&distr, si->wi, m) * mf_g1(&distr, wo, m);
+        if (reflect) {
+            *val = C1(F * D * G / (4.f * fabsf(cos_theta_i)));
+            if (b->specular_reflectance_tex >= 0) *val = cmul(*val, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+        } else {
+            *val = C1(fabsf((sqrf(inv_eta) * (1.f - F) * D * G * eta * eta * wim * wom) / (cos_theta_i * sqrf(wim + eta * wom))));
+            if (b->specular_transmittance_tex >= 0) *val = cmul(*val, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav));
+        }
+        if (!(wim * cos_theta_i > 0.f && wom * cos_theta_o > 0.f)) return;
+        float dwh_dwo = reflect ? 1.f / (4.f * wom) : (eta * eta * wom) / sqrf(wim + eta * wom);
+        if (!b->sample_visible) { float sc = 1.2f - .2f * sqrtf(fabsf(cos_theta_i)); sample_distr.au *= sc; sample_distr.av *= sc; }
+        float prob = mf_pdf(&sample_distr, V(mulsign(si->wi.x, cos_theta_i), mulsign(si->wi.y, cos_theta_i), mulsign(si->wi.z, cos_theta_i)), m);
+        prob *= reflect ? F : 1.f - F;
+        *pdf = prob * fabsf(dwh_dwo);
         return;
     }
     if (b->type == MTSB_BSDF_PLASTIC) {                /* plastic.cpp:247-296 (the diffuse lobe; the specular one is a delta) */

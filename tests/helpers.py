@@ -363,8 +363,9 @@ def material_scene(res=(48, 32), spp=8, envmap=True, area=True, named_conductor=
 
 
 def n4_scene(res=(48, 32), spp=8):
-    """SURVEY 8f N4 plugins: smooth `conductor` (Au) and `plastic` (plain and nonlinear, textured base) spheres on a
-    diffuse ground under an area light and a constant background."""
+    """SURVEY 8f N4 plugins: smooth `conductor` (Au), `plastic` (plain and nonlinear, textured base) and `roughdielectric`
+    (GGX visible-normal sampling; anisotropic Beckmann with plain sampling) spheres on a diffuse ground under an area light
+    and a constant background."""
     sd = SceneData()
     rng = np.random.default_rng(5)
     ground = M.quad([-10, -1.2, -10], [-10, -1.2, 10], [10, -1.2, 10], [10, -1.2, -10])
@@ -380,6 +381,12 @@ def n4_scene(res=(48, 32), spp=8):
     s3.bsdf = sd.add_plastic(sd.add_texture_bitmap(0.2 + 0.6 * rng.random((8, 8, 3)).astype(np.float32)), specular_reflectance=[0.9, 0.8, 0.7],
                              nonlinear=True)
     sd.add_mesh(s3)
+    s4 = M.displaced_sphere(16, 32, radius=0.45, center=(-0.3, -0.75, -1.3), displace=False)
+    s4.bsdf = sd.add_roughdielectric(alpha=0.1, distribution="ggx")
+    sd.add_mesh(s4)
+    s5 = M.displaced_sphere(16, 32, radius=0.4, center=(0.9, -0.8, -1.4), displace=False)
+    s5.bsdf = sd.add_roughdielectric(alpha=0.15, alpha_v=0.05, sample_visible=False, specular_transmittance=[0.9, 0.95, 1.0])
+    sd.add_mesh(s5)
     light = M.quad([-0.5, 3, -0.5], [0.5, 3, -0.5], [0.5, 3, 0.5], [-0.5, 3, 0.5])
     light.bsdf = sd.add_diffuse(0.5)
     sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
