@@ -36,13 +36,16 @@ def _z_test_pass_fraction(xyz_mean, spp, ref, ref_var, significance=0.01):
     return np.count_nonzero(p > alpha) / 3 / npix
 
 
-@pytest.mark.parametrize("renderer,mode", [("oracle", "rgb"), ("hostsim", "rgb"), ("oracle", "spectral"), ("hostsim", "spectral")])
-def test_textured_diffuse_scene_passes_the_reference_z_test(renderer, mode):
+@pytest.mark.parametrize("renderer,mode,scene", [("oracle", "rgb", "test_textured_diffuse"), ("hostsim", "rgb", "test_textured_diffuse"),
+                                                 ("oracle", "spectral", "test_textured_diffuse"), ("hostsim", "spectral", "test_textured_diffuse"),
+                                                 ("oracle", "rgb", "test_roughdielectric"), ("hostsim", "rgb", "test_roughdielectric")])
+def test_single_sphere_scenes_pass_the_reference_z_test(renderer, mode, scene):
     """test_textured_diffuse.xml: OBJ sphere with a bitmap (JPEG) diffuse texture, area light + envmap + point light,
-    `moment(path, max_depth 2)`, box filter, 48 x 48 -- every plugin on the hot path except the rough conductor."""
+    `moment(path, max_depth 2)`, box filter, 48 x 48 -- every plugin on the hot path except the rough conductor.
+    test_roughdielectric.xml: the same with a Beckmann (alpha 0.02) rough dielectric sphere."""
     from mitsuba2_b200 import xml
     spp = int(2e6) // (48 * 48)                                                # test_renders.py:102-105
-    sd = xml.load_file(os.path.join(SCENES, "test_textured_diffuse.xml"), spp=spp)
+    sd = xml.load_file(os.path.join(SCENES, scene + ".xml"), spp=spp)
     sd.mode = mode                      # `scalar_rgb` / `scalar_spectral` references (get_ref_fname, test_renders.py:31-38)
     if mode == "spectral":
         # needs the reference-resolution (64^3) sRGB -> spectrum table: a 16^3 one fails this z-test.  Building it takes
@@ -52,8 +55,8 @@ def test_textured_diffuse_scene_passes_the_reference_z_test(renderer, mode):
         cache = os.path.join(os.path.dirname(mitsuba2_b200.__file__), "_srgb_coeff_64.npz")
         if not os.path.exists(cache) and os.environ.get("MTSB_BUILD_SRGB_TABLE") != "1":
             pytest.skip("64^3 rgb2spec table not cached (set MTSB_BUILD_SRGB_TABLE=1 to build it)")
-    ref = _read_exr_xyz(os.path.join(SCENES, "refs", f"test_textured_diffuse_ref_{mode}.exr"))
-    var = _read_exr_xyz(os.path.join(SCENES, "refs", f"test_textured_diffuse_ref_{mode}_var.exr"))
+    ref = _read_exr_xyz(os.path.join(SCENES, "refs", f"{scene}_ref_{mode}.exr"))
+    var = _read_exr_xyz(os.path.join(SCENES, "refs", f"{scene}_ref_{mode}_var.exr"))
     r = H.Oracle(sd) if renderer == "oracle" else H.HostSim(sd)
     film = r.render_xyzaw(spp=spp, seed=7).astype(np.float64)
     xyz = film[:, :, :3] / np.maximum(film[:, :, 4:5], 1e-12)
