@@ -74,6 +74,8 @@ typedef struct mtsb_bsdf_desc {
                                        (src/bsdfs/twosided.cpp:66-200); not allowed for DIELECTRIC */
     int32_t nonlinear;              /* PLASTIC: `nonlinear` (plastic.cpp:154)                          (since ABI 5) */
     float   specular_sampling_weight;   /* PLASTIC: s_mean / (d_mean + s_mean) of the texture means (plastic.cpp:165-176) */
+    int32_t opacity_tex_plus1;      /* 0 = plain BSDF (so that zero-initialised descriptors stay valid); otherwise 1 + the id of
+                                       the single-channel opacity texture of a `mask` adapter around it (src/bsdfs/mask.cpp) */
 } mtsb_bsdf_desc;
 
 /* Emitter: `Emitter::sample_direction/pdf_direction/eval`.

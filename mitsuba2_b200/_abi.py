@@ -34,7 +34,7 @@ class BsdfDesc(C.Structure):
                 ("specular_reflectance_tex", C.c_int32), ("specular_transmittance_tex", C.c_int32),
                 ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("distribution", C.c_int32),
                 ("sample_visible", C.c_int32), ("eta", C.c_float), ("two_sided", C.c_int32), ("nonlinear", C.c_int32),
-                ("specular_sampling_weight", C.c_float)]
+                ("specular_sampling_weight", C.c_float), ("opacity_tex_plus1", C.c_int32)]
 
 
 class EmitterDesc(C.Structure):

@@ -399,7 +399,8 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex;
         bd.spec_t = b.specular_transmittance_tex; bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution;
         bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
-        bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight;
+        bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight; bd.opacity = b.opacity_tex_plus1 - 1;
+        CHECK_ARG(tex_ok(b.opacity_tex_plus1 - 1, true));
         if (b.two_sided && b.type == MTSB_BSDF_DIELECTRIC) return fail(MTSB_E_INVALID, "twosided: only materials without a transmission component can be nested");
         if (b.type == MTSB_BSDF_DIFFUSE) CHECK_ARG(tex_ok(b.reflectance_tex, false));
         else if (b.type == MTSB_BSDF_ROUGHCONDUCTOR || b.type == MTSB_BSDF_CONDUCTOR) CHECK_ARG(tex_ok(b.eta_tex, false) && tex_ok(b.k_tex, false) && tex_ok(b.specular_reflectance_tex, true));

@@ -18,6 +18,7 @@ struct BsdfDev {
     float alpha_u, alpha_v; int distr; int sample_visible; float eta_f;
     int two_sided;          // `twosided` adapter, same BRDF on both sides (src/bsdfs/twosided.cpp)
     int nonlinear; float spec_weight;   // plastic (type 4): `nonlinear`, specular sampling weight; type 3 = smooth conductor
+    int opacity;            // >= 0: `mask` adapter (src/bsdfs/mask.cpp) with this single-channel opacity texture
 };
 constexpr int kMaxEnvLevels = 20;
 struct EmitterDev {

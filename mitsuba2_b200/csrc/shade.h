@@ -308,7 +308,7 @@ struct Microfacet {
 // sample: diffuse a = reflectance; roughconductor a = eta, b = k, c = specular_reflectance (1 if absent);
 // dielectric a = specular_reflectance, b = specular_transmittance (1 if absent); conductor like roughconductor;
 // plastic a = diffuse_reflectance, b = specular_reflectance (1 if absent).
-template <typename M> struct BsdfTexT { typename M::Spec a, b, c; };
+template <typename M> struct BsdfTexT { typename M::Spec a, b, c; float opacity; /* `mask` adapter: clamp(opacity texture), else 1 */ };
 // fresnel_diffuse_reflectance (include/mitsuba/render/fresnel.h:324-358)
 HD float fresnel_diffuse_reflectance(float eta) {
     if (eta < 1.f) return -1.4399f * (eta * eta) + 0.7099f * eta + 0.6681f + 0.0636f / eta;
@@ -321,7 +321,8 @@ HD float4 plastic_div(float4 d, float f, bool nl) { return make_float4(d.x / (1.
 template <typename M> HD typename M::Spec plastic_diffuse(const BsdfDev &b, typename M::Spec d) { return plastic_div(d, fresnel_diffuse_reflectance(1.f / b.eta_f), b.nonlinear != 0); }
 template <typename M>
 HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, float v, float4 wav) {
-    BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f);
+    BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f); t.opacity = 1.f;
+    if (b.opacity >= 0) t.opacity = fminf(fmaxf(tex_eval_m<M>(sc, b.opacity, u, v, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
     if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
     else if (b.type == 4) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
     else if (b.type == 1 || b.type == 3) {
@@ -495,6 +496,13 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
 // nested BRDF; cos(wi) == 0 belongs to neither side.  One call site each, so the nested code is not duplicated.
 template <typename M = Rgb>
 HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, const BsdfTexT<M> &tx) {
+    if (b.opacity >= 0) {         // src/bsdfs/mask.cpp:95-128: null lobe with probability 1 - opacity, else the nested BSDF with
+        if (!(s1 < tx.opacity)) { // sample1 rescaled; the nested sample's pdf is NOT multiplied by the opacity (as in the reference)
+            BsdfSampleT<M> bs; bs.wo = -si.wi; bs.eta = 1.f; bs.pdf = 1.f - tx.opacity; bs.delta = true; bs.weight = M::splat(1.f);
+            return bs;
+        }
+        s1 /= tx.opacity;
+    }
     bool back = b.two_sided && si.wi.z < 0.f;
     SI s2 = si;
     if (back) s2.wi.z = -s2.wi.z;
@@ -508,6 +516,7 @@ HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3
     SI s2 = si;
     if (back) { s2.wi.z = -s2.wi.z; wo.z = -wo.z; }
     bsdf_eval_pdf_one_sided<M>(sc, b, s2, wo, val, pdf, tx);
+    if (b.opacity >= 0) { val *= tx.opacity; pdf *= tx.opacity; }      // mask.cpp:130-155
 }
 // stand-alone forms (parity hooks, adjoint): look the textures up themselves
 template <typename M = Rgb>

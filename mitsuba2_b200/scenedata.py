@@ -213,6 +213,20 @@ class SceneData:
                            "specular_transmittance_tex": -1 if specular_transmittance is None else self.add_texture_rgb(specular_transmittance)})
         return len(self.bsdfs) - 1
 
+    def add_mask(self, nested_bsdf_id, opacity=0.5):
+        """``mask`` adapter (src/bsdfs/mask.cpp) around an existing BSDF: with probability 1 - opacity the ray passes straight
+        through.  `opacity`: a scalar or an image (H,W) / (H,W,3); stored as a single-channel bitmap, i.e. what `eval_1` of
+        the reference's texture returns (luminance for colour images, bitmap.cpp:215-231)."""
+        o = np.asarray(opacity, np.float32)
+        if o.ndim == 0:
+            o = np.full((2, 2), float(o), np.float32)
+        if o.ndim == 3:
+            o = o[:, :, :3] @ np.array([0.212671, 0.715160, 0.072169], np.float32) if o.shape[2] >= 3 else o[:, :, 0]
+        b = dict(self.bsdfs[nested_bsdf_id])
+        b["opacity_tex"] = self.add_texture_bitmap(np.ascontiguousarray(o[:, :, None], np.float32))
+        self.bsdfs.append(b)
+        return len(self.bsdfs) - 1
+
     def add_mesh(self, mesh, area_radiance=None):
         self.meshes.append(mesh)
         mid = len(self.meshes) - 1
@@ -302,6 +316,7 @@ class SceneData:
             bd[i].two_sided = int(b.get("two_sided", 0))
             bd[i].nonlinear = int(b.get("nonlinear", 0))
             bd[i].specular_sampling_weight = float(b.get("specular_sampling_weight", 0.5))
+            bd[i].opacity_tex_plus1 = int(b.get("opacity_tex", -1)) + 1
         spectral = self.mode == "spectral"
         if self.mode not in ("rgb", "spectral"):
             raise ValueError("SceneData.mode must be 'rgb' or 'spectral'")

@@ -235,6 +235,20 @@ class _Loader:
             b["two_sided"] = 1
             self.sd.bsdfs.append(b)
             idx = len(self.sd.bsdfs) - 1
+        elif ty == "mask":        # src/bsdfs/mask.cpp: opacity (default 0.5) + one nested BSDF
+            inner = [c for c in el if c.tag in ("bsdf", "ref")]
+            if len(inner) != 1:
+                raise ValueError("mask: exactly one nested BSDF is required")
+            op = p.get("opacity", ("rgb", [0.5] * 3))
+            if op[0] == "rgb":
+                opacity = float(np.dot(op[1], [0.212671, 0.715160, 0.072169])) if len(set(op[1])) > 1 else float(op[1][0])
+            elif op[0] == "spectrum":
+                raise NotImplementedError("mask: tabulated opacity spectrum")
+            else:
+                if self.attr(op[1], "type") != "bitmap":
+                    raise NotImplementedError("mask: only constant and bitmap opacities are supported")
+                opacity = load_image(self.resolve(op[1], self.props(op[1])["filename"]))
+            idx = self.sd.add_mask(self.bsdf_index(inner[0]), opacity)
         elif ty == "diffuse":
             idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
         elif ty == "plastic":

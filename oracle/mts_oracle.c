@@ -873,7 +873,19 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
 }
 /* TwoSidedBRDF::sample / eval / pdf (twosided.cpp:98-200) with the same nested BRDF on both sides: on the back side flip
  * wi (and wo) about the surface; cos(wi) == 0 is neither front nor back */
+/* MaskBSDF::eval_opacity (mask.cpp): clamp(opacity->eval_1(si), 0, 1); the texture is single-channel */
+static float mask_opacity(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, const float *wav) {
+    return fminf(fmaxf(tex_eval(s, b->opacity_tex_plus1 - 1, si->u, si->v, wav).c[0], 0.f), 1.f);
+}
 static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
+    if (b->opacity_tex_plus1 > 0) {                          /* mask.cpp:95-128 */
+        float opacity = mask_opacity(s, b, si, wav);
+        if (!(s1 < opacity)) {
+            obs bs; memset(&bs, 0, sizeof(bs)); bs.wo = V(-si->wi.x, -si->wi.y, -si->wi.z); bs.eta = 1.f; bs.pdf = 1.f - opacity; bs.delta = 1; bs.weight = C1(1.f);
+            return bs;
+        }
+        s1 /= opacity;
+    }
     if (!b->two_sided || si->wi.z > 0.f) return bsdf_sample_nested(s, b, si, s1, sx, sy, wav);
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
     if (!(si->wi.z < 0.f)) return bs;
@@ -882,7 +894,12 @@ static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *s
     bs.wo.z *= -1.f;
     return bs;
 }
+static void bsdf_eval_pdf_unmasked(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav);
 static void bsdf_eval_pdf(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav) {
+    bsdf_eval_pdf_unmasked(s, b, si, wo, val, pdf, wav);
+    if (b->opacity_tex_plus1 > 0) { float opacity = mask_opacity(s, b, si, wav); *val = cscale(*val, opacity); *pdf *= opacity; }    /* mask.cpp:130-155 */
+}
+static void bsdf_eval_pdf_unmasked(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav) {
     if (!b->two_sided || si->wi.z > 0.f) { bsdf_eval_pdf_nested(s, b, si, wo, val, pdf, wav); return; }
     *val = C1(0.f); *pdf = 0.f;
     if (!(si->wi.z < 0.f)) return;

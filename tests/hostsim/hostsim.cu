@@ -164,7 +164,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         const mtsb_bsdf_desc &b = d->bsdfs[i]; BsdfDev bd; memset(&bd, 0, sizeof(bd));
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex; bd.spec_t = b.specular_transmittance_tex;
         bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
-        bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight;
+        bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight; bd.opacity = b.opacity_tex_plus1 - 1;
         s->bsdfs.push_back(bd);
     }
     hs_build_bvh(s);
