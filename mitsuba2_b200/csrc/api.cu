@@ -77,7 +77,7 @@ struct mtsb_scene {
     std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
     std::vector<float> h_pos, h_nrm;
     // device
-    DevBuf<float> pos, nrm, uv; DevBuf<uint4> faces; DevBuf<float4> stri;
+    DevBuf<float> pos, nrm, uv; DevBuf<uint4> faces;
     DevBuf<MeshDev> d_meshes; DevBuf<TexDev> d_tex; DevBuf<BsdfDev> d_bsdfs; DevBuf<EmitterDev> d_emitters;
     std::vector<std::unique_ptr<DevBuf<float>>> tables;       // texture data, cdfs, envmap levels
     std::vector<int> tex_table;                               // texture id -> tables index (-1 constant)
@@ -268,13 +268,6 @@ static int upload_struct_arrays(mtsb_scene *s) {
     }
     CU(cudaStreamSynchronize(st));
     s->dev.pos = s->pos.p; s->dev.nrm = s->nrm.p; s->dev.uv = s->uv.p; s->dev.faces = s->faces.p;
-    s->dev.stri = nullptr;
-    if (s->faces.n > 0 && !getenv("MTSB_NO_SHADE_TRIS")) {      // per-primitive shading records (shade.h); rebuilt after vertex updates
-        CU(s->stri.alloc(6 * s->faces.n));
-        k_pack_shade_tris<<<grid_for(s->faces.n), kBlock, 0, st>>>(s->pos.p, s->nrm.p, s->uv.p, s->faces.p, (uint32_t) s->faces.n, s->stri.p);
-        CU(cudaStreamSynchronize(st));
-        s->dev.stri = s->stri.p;
-    }
     s->dev.meshes = s->d_meshes.p; s->dev.tex = s->d_tex.p; s->dev.bsdfs = s->d_bsdfs.p; s->dev.emitters = s->d_emitters.p;
     return MTSB_OK;
 }

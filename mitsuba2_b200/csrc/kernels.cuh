@@ -79,11 +79,6 @@ __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
     if (i < end) collapse_body(b, i);
 }
 
-__global__ void k_pack_shade_tris(const float *pos, const float *nrm, const float *uv, const uint4 *faces, uint32_t n, float4 *out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) pack_shade_tri(pos, nrm, uv, faces, i, out);
-}
-
 // ---------------- traversal ----------------------------------------------------------------------
 // Persistent-warp traversal with dynamic ray fetch (after Aila & Laine 2009): the grid is sized to fill the SMs once;
 // every warp claims chunks of kFetchChunk consecutive rays from a global work counter and hands them to lanes whose

@@ -49,7 +49,6 @@ struct SceneDev {
     Bvh bvh;
     const float *pos, *nrm, *uv;
     const uint4 *faces;
-    const float4 *stri;     // per-primitive shading record, 6 x float4 (pack_shade_tri in shade.h); null: gather through faces
     const MeshDev *meshes; const TexDev *tex; const BsdfDev *bsdfs; const EmitterDev *emitters;
     int n_emitters, env_emitter;
     int max_depth, rr_depth;

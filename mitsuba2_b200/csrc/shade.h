@@ -12,20 +12,6 @@ HD float3 ld3(const float *a, uint32_t i) { return mk3(a[3 * i], a[3 * i + 1], a
 
 // ShapeKDTree::create_surface_interaction (include/mitsuba/render/kdtree.h:2334-2368) +
 // Mesh::fill_surface_interaction (src/librender/mesh.cpp:399-462); miss: scene_native.inl:29-31.
-// Per-primitive shading record: the three vertices' positions, normals and texture coordinates in 96 contiguous bytes
-//   r0 = (p0, u0)  r1 = (p1, v0)  r2 = (p2, u1)  r3 = (n0, v1)  r4 = (n1, u2)  r5 = (n2, v2)
-// so that a hit costs six 128-bit loads from one place instead of ~25 dependent 32-bit gathers (index -> vertex arrays).
-// Same values, same arithmetic in make_si: results are bit-identical with the gathered path.
-HD void pack_shade_tri(const float *pos, const float *nrm, const float *uv, const uint4 *faces, uint32_t prim, float4 *out) {
-    uint4 f = faces[prim];
-    float4 *r = out + 6 * (size_t) prim;
-    r[0] = make_float4(pos[3 * f.x], pos[3 * f.x + 1], pos[3 * f.x + 2], uv[2 * f.x]);
-    r[1] = make_float4(pos[3 * f.y], pos[3 * f.y + 1], pos[3 * f.y + 2], uv[2 * f.x + 1]);
-    r[2] = make_float4(pos[3 * f.z], pos[3 * f.z + 1], pos[3 * f.z + 2], uv[2 * f.y]);
-    r[3] = make_float4(nrm[3 * f.x], nrm[3 * f.x + 1], nrm[3 * f.x + 2], uv[2 * f.y + 1]);
-    r[4] = make_float4(nrm[3 * f.y], nrm[3 * f.y + 1], nrm[3 * f.y + 2], uv[2 * f.z]);
-    r[5] = make_float4(nrm[3 * f.z], nrm[3 * f.z + 1], nrm[3 * f.z + 2], uv[2 * f.z + 1]);
-}
 constexpr uint32_t kPrimMask = 0x3fffffffu;     // primitive ids use 30 bits; the top two carry the shade class in the queues
 HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     SI si;
@@ -35,18 +21,7 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     si.mesh = (int) f.w;
     const MeshDev m = sc.meshes[f.w];
     float b1 = hit.y, b2 = hit.z, b0 = 1.f - b1 - b2;
-    float3 p0, p1, p2, n0 = mk3(0.f), n1 = mk3(0.f), n2 = mk3(0.f);
-    float u0 = 0.f, v0 = 0.f, u1 = 0.f, v1 = 0.f, u2 = 0.f, v2 = 0.f;
-    if (sc.stri != nullptr) {
-        const float4 *r = sc.stri + 6 * (size_t) si.prim;
-        float4 a = r[0], b = r[1], c = r[2];
-        p0 = xyz(a); p1 = xyz(b); p2 = xyz(c); u0 = a.w; v0 = b.w; u1 = c.w;
-        if (m.has_uv || m.has_normals) { float4 d4 = r[3], e = r[4], g = r[5]; n0 = xyz(d4); n1 = xyz(e); n2 = xyz(g); v1 = d4.w; u2 = e.w; v2 = g.w; }
-    } else {
-        p0 = ld3(sc.pos, f.x); p1 = ld3(sc.pos, f.y); p2 = ld3(sc.pos, f.z);
-        if (m.has_uv) { u0 = sc.uv[2 * f.x]; v0 = sc.uv[2 * f.x + 1]; u1 = sc.uv[2 * f.y]; v1 = sc.uv[2 * f.y + 1]; u2 = sc.uv[2 * f.z]; v2 = sc.uv[2 * f.z + 1]; }
-        if (m.has_normals) { n0 = ld3(sc.nrm, f.x); n1 = ld3(sc.nrm, f.y); n2 = ld3(sc.nrm, f.z); }
-    }
+    float3 p0 = ld3(sc.pos, f.x), p1 = ld3(sc.pos, f.y), p2 = ld3(sc.pos, f.z);
     float3 dp0 = p1 - p0, dp1 = p2 - p0;
     si.p = p0 * b0 + p1 * b1 + p2 * b2;
     float3 n = normalize(cross(dp0, dp1));
@@ -55,6 +30,8 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     coordinate_system(n, dp_du, dp_dv);
     si.u = b1; si.v = b2;
     if (m.has_uv) {
+        float u0 = sc.uv[2 * f.x], v0 = sc.uv[2 * f.x + 1], u1 = sc.uv[2 * f.y], v1 = sc.uv[2 * f.y + 1],
+              u2 = sc.uv[2 * f.z], v2 = sc.uv[2 * f.z + 1];
         si.u = u0 * b0 + u1 * b1 + u2 * b2; si.v = v0 * b0 + v1 * b1 + v2 * b2;
         float du0 = u1 - u0, dv0 = v1 - v0, du1 = u2 - u0, dv1 = v2 - v0;
         float det = fmaf(du0, dv1, -(dv0 * du1));
@@ -65,8 +42,10 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
         }
     }
     float3 ns = n;
-    if (m.has_normals)
+    if (m.has_normals) {
+        float3 n0 = ld3(sc.nrm, f.x), n1 = ld3(sc.nrm, f.y), n2 = ld3(sc.nrm, f.z);
         ns = normalize(n0 * b0 + n1 * b1 + n2 * b2);
+    }
     si.sh.n = ns;
     si.sh.s = normalize(dp_du - ns * dot(ns, dp_du));
     si.sh.t = cross(ns, si.sh.s);

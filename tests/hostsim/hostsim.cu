@@ -18,7 +18,7 @@ using namespace mtsb;
 struct hs_scene {
     std::vector<MeshDev> meshes; std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
     std::vector<SensorDev> sensors;
-    std::vector<float> pos, nrm, uv; std::vector<uint4> faces; std::vector<float4> stri;
+    std::vector<float> pos, nrm, uv; std::vector<uint4> faces;
     std::vector<std::vector<float>> tables; std::vector<float4> env_rgba; std::vector<float> cie; bool spectral = false;
     std::vector<uint4> nodes; std::vector<float4> tris;
     std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
@@ -212,9 +212,6 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     for (size_t i = 0; i < s->sensors.size(); ++i) { s->sensors[i].film_xyza = s->film_xyza[i].data(); s->sensors[i].film_w = s->film_w[i].data(); }
     s->dev.max_depth = d->integrator.max_depth < 0 ? (1 << 30) : d->integrator.max_depth; s->dev.rr_depth = d->integrator.rr_depth;
     s->dev.pos = s->pos.data(); s->dev.nrm = s->nrm.data(); s->dev.uv = s->uv.data(); s->dev.faces = s->faces.data();
-    s->stri.resize(6 * s->faces.size());
-    for (uint32_t i = 0; i < s->faces.size(); ++i) pack_shade_tri(s->pos.data(), s->nrm.data(), s->uv.data(), s->faces.data(), i, s->stri.data());
-    s->dev.stri = getenv("MTSB_NO_SHADE_TRIS") ? nullptr : s->stri.data();
     s->dev.meshes = s->meshes.data(); s->dev.tex = s->tex.data(); s->dev.bsdfs = s->bsdfs.data(); s->dev.emitters = s->emitters.data();
     return s;
 }
