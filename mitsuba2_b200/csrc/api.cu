@@ -84,6 +84,7 @@ struct mtsb_scene {
     std::vector<int> emitter_cdf_table;
     DevBuf<float4> env_rgba;
     bool spectral = false;                   // MTSB_MODE_SPECTRAL: 4 wavelengths per path
+    bool ext = false;                        // some BSDF is a conductor / plastic / rough dielectric or masked: RgbX / SpectralX kernels
     DevBuf<float> cie;                       // spectral mode: CIE 1931 x/y/z + D65/10568 (cie_tables.h)
     DevBuf<float2> q_we[2];                  // spectral mode: wavelength sample + eta per queue entry
     DevBuf<uint4> nodes; DevBuf<float4> tris;
@@ -393,6 +394,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         bd.spec_t = b.specular_transmittance_tex; bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution;
         bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
         bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight; bd.opacity = b.opacity_tex_plus1 - 1;
+        if (b.type >= MTSB_BSDF_CONDUCTOR || bd.opacity >= 0) s->ext = true;
         CHECK_ARG(tex_ok(b.opacity_tex_plus1 - 1, true));
         if (b.two_sided && b.type == MTSB_BSDF_DIELECTRIC) return fail(MTSB_E_INVALID, "twosided: only materials without a transmission component can be nested");
         if (b.type == MTSB_BSDF_DIFFUSE) CHECK_ARG(tex_ok(b.reflectance_tex, false));
@@ -581,6 +583,10 @@ static PathQueue make_queue(mtsb_scene *s, int k) {
 
 // One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
 // (k_shade_grad scatters texel gradients); `splat` adds the finished paths to the film.
+// the shade kernel has four instances: colour mode x (lean | with the N4 plugins: conductor, plastic, rough dielectric, mask)
+#define LAUNCH_SHADE(grid, ...) do { \
+    if (s->spectral) { if (s->ext) k_shade<SpectralX><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); else k_shade<Spectral><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); } \
+    else { if (s->ext) k_shade<RgbX><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); else k_shade<Rgb><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); } } while (0)
 struct EdgeLaunch { EdgeCtx e; const float *total_len; };     // primary rays come from edge samples instead of the film
 struct Edge2Launch { Edge2Ctx e; const float *total_len; };   // depth-2 rays come from edge samples seen from the primary hits
 static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches,
@@ -610,17 +616,17 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
         { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE);
-          if (grad && grad->grad_pos) k_shade_grad<true><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
-          else if (grad) k_shade_grad<false><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+          if (grad && grad->grad_pos) { if (s->ext) k_shade_grad<true, RgbX><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+                                        else k_shade_grad<true, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }
+          else if (grad) { if (s->ext) k_shade_grad<false, RgbX><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
+                           else k_shade_grad<false, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }
           else if (depth == 1 || !s->ctx->bin_materials) {      // primary hits are already coherent: identity lists
               ShadeBins bins; bins.lists = nullptr; bins.counts = s->counters.p + depth; bins.pool = 0;
-              if (s->spectral) k_shade<Spectral><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
-              else k_shade<Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              LAUNCH_SHADE(grid_for(n), s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
           } else {
               ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + 4 * depth; bins.pool = s->pool;
               k_classify<<<grid_for(n), kBlock, 0, st>>>(s->counters.p + depth, qin.hit, bins);
-              if (s->spectral) k_shade<Spectral><<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
-              else k_shade<Rgb><<<grid_for((size_t) n + 32 * kShadeClasses), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
+              LAUNCH_SHADE(grid_for((size_t) n + 32 * kShadeClasses), s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
               launches++;
           } }
         launches += 2;

@@ -9,9 +9,9 @@ typedef DirSampleT<Rgb> DirSample;
 
 // radiance (area, constant) / intensity (point) of an emitter: an rgb triple, or in spectral mode a texture
 // (srgb_d65 for rgb input, or any tabulated spectrum)
-template <typename M> HD typename M::Spec emitter_radiance(const SceneDev &sc, const EmitterDev &e, float4 wav);
-template <> HD float3 emitter_radiance<Rgb>(const SceneDev &, const EmitterDev &e, float4) { return e.radiance; }
-template <> HD float4 emitter_radiance<Spectral>(const SceneDev &sc, const EmitterDev &e, float4 wav) { return tex_eval_spectral(sc, e.radiance_tex, 0.f, 0.f, wav); }
+template <typename M> HD typename M::Spec emitter_radiance(const SceneDev &sc, const EmitterDev &e, float4 wav) {
+    if constexpr (M::spectral) return tex_eval_spectral(sc, e.radiance_tex, 0.f, 0.f, wav); else return e.radiance;
+}
 
 // enoki::binary_search (ext/enoki/include/enoki/array_utils.h:153-171)
 template <typename Pred> HD uint32_t binary_search(uint32_t start, uint32_t end, Pred pred) {
@@ -48,9 +48,9 @@ HD float4 env_lookup_spectral(const SceneDev &sc, const EmitterDev &e, float u, 
     float f = by(bx(v00.w, v10.w), bx(v01.w, v11.w));
     return map_spec(s0, s1, by) * d65_eval(sc, wav) * f * e.scale;
 }
-template <typename M> HD typename M::Spec env_lookup_m(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav);
-template <> HD float3 env_lookup_m<Rgb>(const SceneDev &, const EmitterDev &e, float u, float v, float4) { return env_lookup(e, u, v); }
-template <> HD float4 env_lookup_m<Spectral>(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav) { return env_lookup_spectral(sc, e, u, v, wav); }
+template <typename M> HD typename M::Spec env_lookup_m(const SceneDev &sc, const EmitterDev &e, float u, float v, float4 wav) {
+    if constexpr (M::spectral) return env_lookup_spectral(sc, e, u, v, wav); else return env_lookup(e, u, v);
+}
 HD void env_dir_to_uv(const EmitterDev &e, float3 dworld, float &u, float &v, float3 &dl) {
     dl = xform_vec(e.to_local, dworld);
     u = atan2f(dl.x, -dl.z) * kInvTwoPi; v = safe_acos(dl.y) * kInvPi;

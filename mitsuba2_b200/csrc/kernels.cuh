@@ -267,7 +267,7 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
 // adjoint replay of k_shade: identical control flow, plus the texel-gradient scatter of texture_adjoint() and, with
 // Vtx, the vertex-position adjoint of adjoint.h (which carries the two previous path vertices through the queue)
 struct DevAdd { __device__ __forceinline__ void operator()(float *dst, float v) const { if (v != 0.f) atomicAdd(dst, v); } };
-template <bool Vtx>
+template <bool Vtx, typename M>
 __global__ void __launch_bounds__(kBlock)
 k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
              unsigned long long *stats, uint32_t depth, GradCtx g) {
@@ -276,7 +276,7 @@ k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQu
     if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
     bool live = i < count;
     ShadeOut out; out.extend = false; out.shadow = false;
-    if (live) { ReplayGrad<DevAdd, Vtx> rg; rg.g = g; out = shade_body<Rgb>(sc, qin, b, i, rg); }
+    if (live) { ReplayGrad<DevAdd, Vtx> rg; rg.g = g; out = shade_body<M>(sc, qin, b, i, rg); }
     uint32_t slot = warp_alloc(&counters[depth + 1], out.extend);
     if (out.extend) {
         qout.o_mint[slot] = out.o_mint; qout.d_maxt[slot] = out.d_maxt; qout.thr_eta[slot] = out.thr_eta;

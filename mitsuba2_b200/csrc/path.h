@@ -301,10 +301,8 @@ HD void film_put(const SensorDev &sn, float px, float py, float4 xyza, float wgt
 }
 
 // src/librender/integrator.cpp:254-270: rgb -> XYZ (core/spectrum.h:220-227), aovs = {X,Y,Z,alpha,1}
-template <typename M> HD float4 result_to_xyza(float4 r);
 HD float4 radiance_to_xyza(float4 r);
-template <> HD float4 result_to_xyza<Spectral>(float4 r) { return r; }
-template <> HD float4 result_to_xyza<Rgb>(float4 r) { return radiance_to_xyza(r); }
+template <typename M> HD float4 result_to_xyza(float4 r) { if constexpr (M::spectral) return r; else return radiance_to_xyza(r); }
 HD float4 radiance_to_xyza(float4 r) {
     return make_float4(0.412453f * r.x + 0.357580f * r.y + 0.180423f * r.z,
                        0.212671f * r.x + 0.715160f * r.y + 0.072169f * r.z,

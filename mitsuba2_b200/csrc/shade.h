@@ -110,9 +110,9 @@ float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wa
     if (t.d65_scale != 0.f) r = d65_eval(sc, wav) * t.d65_scale * r;
     return r;
 }
-template <typename M> HD typename M::Spec tex_eval_m(const SceneDev &sc, int id, float u, float v, float4 wav);
-template <> HD float3 tex_eval_m<Rgb>(const SceneDev &sc, int id, float u, float v, float4) { return tex_eval_rgb(sc, id, u, v); }
-template <> HD float4 tex_eval_m<Spectral>(const SceneDev &sc, int id, float u, float v, float4 wav) { return tex_eval_spectral(sc, id, u, v, wav); }
+template <typename M> HD typename M::Spec tex_eval_m(const SceneDev &sc, int id, float u, float v, float4 wav) {
+    if constexpr (M::spectral) return tex_eval_spectral(sc, id, u, v, wav); else return tex_eval_rgb(sc, id, u, v);
+}
 HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) { return tex_eval_rgb(sc, id, u, v); }
 // texel footprint of a bitmap lookup (for the adjoint scatter): indices of the 4 texels + weights
 HD bool tex_footprint(const TexDev &t, float u, float v, uint32_t idx[4], float w[4]) {
@@ -146,7 +146,7 @@ HD float3 square_to_cosine_hemisphere(float sx, float sy) {
 }
 
 template <typename M> struct BsdfSampleT { float3 wo; float pdf, eta; bool delta; typename M::Spec weight; };
-typedef BsdfSampleT<Rgb> BsdfSample;
+typedef BsdfSampleT<RgbX> BsdfSample;       // stand-alone hooks handle every plugin
 
 // ---- fresnel (include/mitsuba/render/fresnel.h:34-76, 92-116) ------------------------------------
 HD void fresnel_dielectric(float cos_i, float eta, float &r, float &cos_t, float &eta_it, float &eta_ti) {
@@ -301,10 +301,10 @@ template <typename M> HD typename M::Spec plastic_diffuse(const BsdfDev &b, type
 template <typename M>
 HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, float v, float4 wav) {
     BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f); t.opacity = 1.f;
-    if (b.opacity >= 0) t.opacity = fminf(fmaxf(tex_eval_m<M>(sc, b.opacity, u, v, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
+    if (M::ext && b.opacity >= 0) t.opacity = fminf(fmaxf(tex_eval_m<M>(sc, b.opacity, u, v, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
     if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
-    else if (b.type == 4) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
-    else if (b.type == 1 || b.type == 3) {
+    else if (M::ext && b.type == 4) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
+    else if (b.type == 1 || (M::ext && b.type == 3)) {
         t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
         if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
     } else {                      // dielectric, rough dielectric
@@ -339,7 +339,7 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         bs.weight = active ? F * weight : M::splat(0.f);
         return bs;
     }
-    if (b.type == 3) {            // src/bsdfs/conductor.cpp (sample): delta reflection, weight = reflectance * F(cos_i)
+    if (M::ext && b.type == 3) {  // src/bsdfs/conductor.cpp (sample): delta reflection, weight = reflectance * F(cos_i)
         if (!(cos_i > 0.f)) return bs;
         bs.wo = mk3(-si.wi.x, -si.wi.y, si.wi.z); bs.pdf = 1.f; bs.delta = true;
         Spec F = fresnel_conductor(cos_i, tx.a, tx.b);
@@ -347,7 +347,7 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         bs.weight = F;
         return bs;
     }
-    if (b.type == 4) {            // src/bsdfs/plastic.cpp:178-245
+    if (M::ext && b.type == 4) {  // src/bsdfs/plastic.cpp:178-245
         if (!(cos_i > 0.f)) return bs;
         float f_i, ct, e1, e2; fresnel_dielectric(cos_i, b.eta_f, f_i, ct, e1, e2);
         float prob_specular = f_i * b.spec_weight, prob_diffuse = (1.f - f_i) * (1.f - b.spec_weight);
@@ -364,7 +364,7 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
         }
         return bs;
     }
-    if (b.type == 5) {            // src/bsdfs/roughdielectric.cpp (sample): microfacet normal, then Fresnel lobe choice
+    if (M::ext && b.type == 5) {  // src/bsdfs/roughdielectric.cpp (sample): microfacet normal, then Fresnel lobe choice
         if (cos_i == 0.f) return bs;
         Microfacet distr(b.distr, b.alpha_u, b.alpha_v, b.sample_visible != 0), sample_distr = distr;
         if (!b.sample_visible) { float sc_ = 1.2f - 0.2f * sqrtf(fabsf(cos_i)); sample_distr.au *= sc_; sample_distr.av *= sc_; }
@@ -436,7 +436,7 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
             pdf = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
         return;
     }
-    if (b.type == 5) {            // src/bsdfs/roughdielectric.cpp (eval, pdf)
+    if (M::ext && b.type == 5) {  // src/bsdfs/roughdielectric.cpp (eval, pdf)
         if (ci == 0.f) return;
         bool reflect = ci * co > 0.f;
         float eta = ci > 0.f ? b.eta_f : 1.f / b.eta_f, inv_eta = ci > 0.f ? 1.f / b.eta_f : b.eta_f;
@@ -462,7 +462,7 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
         pdf = prob * fabsf(dwh_dwo);
         return;
     }
-    if (b.type == 4) {            // src/bsdfs/plastic.cpp:247-296: the diffuse lobe (the specular one is a delta)
+    if (M::ext && b.type == 4) {  // src/bsdfs/plastic.cpp:247-296: the diffuse lobe (the specular one is a delta)
         if (!(ci > 0.f && co > 0.f)) return;
         float f_i, f_o, ct, e1, e2; fresnel_dielectric(ci, b.eta_f, f_i, ct, e1, e2); fresnel_dielectric(co, b.eta_f, f_o, ct, e1, e2);
         val = plastic_diffuse<M>(b, tx.a) * ((kInvPi * co) * (1.f / (b.eta_f * b.eta_f)) * (1.f - f_i) * (1.f - f_o));
@@ -475,7 +475,7 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
 // nested BRDF; cos(wi) == 0 belongs to neither side.  One call site each, so the nested code is not duplicated.
 template <typename M = Rgb>
 HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, const BsdfTexT<M> &tx) {
-    if (b.opacity >= 0) {         // src/bsdfs/mask.cpp:95-128: null lobe with probability 1 - opacity, else the nested BSDF with
+    if (M::ext && b.opacity >= 0) { // src/bsdfs/mask.cpp:95-128: null lobe with probability 1 - opacity, else the nested BSDF with
         if (!(s1 < tx.opacity)) { // sample1 rescaled; the nested sample's pdf is NOT multiplied by the opacity (as in the reference)
             BsdfSampleT<M> bs; bs.wo = -si.wi; bs.eta = 1.f; bs.pdf = 1.f - tx.opacity; bs.delta = true; bs.weight = M::splat(1.f);
             return bs;
@@ -495,14 +495,14 @@ HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3
     SI s2 = si;
     if (back) { s2.wi.z = -s2.wi.z; wo.z = -wo.z; }
     bsdf_eval_pdf_one_sided<M>(sc, b, s2, wo, val, pdf, tx);
-    if (b.opacity >= 0) { val *= tx.opacity; pdf *= tx.opacity; }      // mask.cpp:130-155
+    if (M::ext && b.opacity >= 0) { val *= tx.opacity; pdf *= tx.opacity; }      // mask.cpp:130-155
 }
 // stand-alone forms (parity hooks, adjoint): look the textures up themselves
-template <typename M = Rgb>
+template <typename M = RgbX>
 HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav = float4()) {
     return bsdf_sample<M>(sc, b, si, s1, sx, sy, bsdf_textures<M>(sc, b, si.u, si.v, wav));
 }
-template <typename M = Rgb>
+template <typename M = RgbX>
 HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
     bsdf_eval_pdf<M>(sc, b, si, wo, val, pdf, bsdf_textures<M>(sc, b, si.u, si.v, wav));
 }

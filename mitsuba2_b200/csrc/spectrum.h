@@ -22,8 +22,13 @@ template <typename F> HD float3 map_spec(float3 a, float3 b, F f) { return mk3(f
 template <typename F> HD float4 map_spec(float4 a, float4 b, F f) { return make_float4(f(a.x, b.x), f(a.y, b.y), f(a.z, b.z), f(a.w, b.w)); }
 template <typename F> HD float4 map_spec(float4 a, F f) { return make_float4(f(a.x), f(a.y), f(a.z), f(a.w)); }
 
-struct Rgb      { typedef float3 Spec; static constexpr bool spectral = false; static HD float3 splat(float v) { return mk3(v); } };
-struct Spectral { typedef float4 Spec; static constexpr bool spectral = true;  static HD float4 splat(float v) { return mk4(v); } };
+// `ext`: the stage bodies also handle the SURVEY-8f-N4 plugins (smooth conductor, plastic, rough dielectric, mask).  Scenes
+// that use none of them run the lean instances, whose shade kernel keeps its register budget (48 registers / 10 blocks per SM
+// in rgb); the host picks the instance per scene.
+struct Rgb      { typedef float3 Spec; static constexpr bool spectral = false, ext = false; static HD float3 splat(float v) { return mk3(v); } };
+struct Spectral { typedef float4 Spec; static constexpr bool spectral = true,  ext = false; static HD float4 splat(float v) { return mk4(v); } };
+struct RgbX : Rgb           { static constexpr bool ext = true; };
+struct SpectralX : Spectral { static constexpr bool ext = true; };
 
 // ---- wavelength sampling: sample_wavelength = sample_rgb_spectrum(sample_shifted(u)) (core/spectrum.h:270-285, 304-316;
 //      core/math.h:418-442) --------------------------------------------------------------------------------------

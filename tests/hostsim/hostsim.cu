@@ -19,7 +19,7 @@ struct hs_scene {
     std::vector<MeshDev> meshes; std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
     std::vector<SensorDev> sensors;
     std::vector<float> pos, nrm, uv; std::vector<uint4> faces;
-    std::vector<std::vector<float>> tables; std::vector<float4> env_rgba; std::vector<float> cie; bool spectral = false;
+    std::vector<std::vector<float>> tables; std::vector<float4> env_rgba; std::vector<float> cie; bool spectral = false, ext = false;
     std::vector<uint4> nodes; std::vector<float4> tris;
     std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
     SceneDev dev; uint32_t bvh_nodes = 0, bvh_depth = 0;
@@ -165,6 +165,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         bd.type = b.type; bd.refl = b.reflectance_tex; bd.eta = b.eta_tex; bd.k = b.k_tex; bd.spec_r = b.specular_reflectance_tex; bd.spec_t = b.specular_transmittance_tex;
         bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
         bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight; bd.opacity = b.opacity_tex_plus1 - 1;
+        if (b.type >= MTSB_BSDF_CONDUCTOR || bd.opacity >= 0) s->ext = true;
         s->bsdfs.push_back(bd);
     }
     hs_build_bvh(s);
@@ -299,7 +300,8 @@ extern "C" void hs_render(hs_scene *s, uint32_t sensor_id, uint32_t spp_begin, u
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
-        if (s->spectral) hs_run_batch<Spectral>(s, sn, b, P, cnt, NoGrad()); else hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad());
+        if (s->spectral) { if (s->ext) hs_run_batch<SpectralX>(s, sn, b, P, cnt, NoGrad()); else hs_run_batch<Spectral>(s, sn, b, P, cnt, NoGrad()); }
+        else { if (s->ext) hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad()); else hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad()); }
         for (uint32_t i = 0; i < n; ++i) {
             float fx, fy; path_film_pos(sn, b, i, fx, fy);
             film_put(sn, fx, fy, s->spectral ? result_to_xyza<Spectral>(P.result[i]) : result_to_xyza<Rgb>(P.result[i]), 1.f, [&](uint32_t pix, float4 v, float w) {
@@ -339,10 +341,10 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
-        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad());
+        hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad());
         std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
         ReplayGrad<HostAdd> rg; rg.g = g;
-        hs_run_batch<Rgb>(s, sn, b, P, cnt, rg);
+        hs_run_batch<RgbX>(s, sn, b, P, cnt, rg);
     }
     if (!grad_vertices || !boundary) return;
     // ---- boundary term: unique edges of the mesh, projected-length cdf, two paths per edge sample
@@ -374,7 +376,7 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         e.first = off;
         RenderBatch b; b.n_paths = 2 * nb; b.offset = 0; b.spp_begin = 0; b.spp_batch = 1; b.spp_total = 1; b.seed = seed; b.result = P.result.data();
         for (uint32_t j = 0; j < nb; ++j) edge_raygen_body(s->dev, sn, e, b, P.queue(0), j);
-        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad(), false);
+        hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad(), false);
         for (uint32_t j = 0; j < nb; ++j) edge_scatter_body(s->dev, e, g, P.result.data(), j, HostAdd());
     }
     if (boundary < 2) return;
@@ -392,7 +394,7 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         uint32_t n2 = (uint32_t) std::min<uint64_t>(pool, total2 - off);
         RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
         b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = P.result.data();
-        hs_run_batch<Rgb>(s, sn, b, P, cnt, NoGrad(), true, &e2);
+        hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad(), true, &e2);
         for (uint32_t j = 0; j < n2; ++j) edge2_scatter_body(s->dev, e2, g2, b, j, HostAdd());
     }
 }
