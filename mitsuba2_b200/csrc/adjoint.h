@@ -204,7 +204,18 @@ HD void vertex_triple(const SceneDev &sc, const GradCtx &g, float3 xA, VtxRec re
     TriGeo tB = tri_geo(sc, recB.prim);
     scatter_point(g, tB, recB, B_primary, siB.p, -(g_din + g_dout), add);
     float lN = norm(tB.N);
-    if (lN > 0.f) {
+    if (g.grad_vnrm != nullptr && tB.mesh == g.mesh_id && sc.meshes[tB.mesh].has_normals) {
+        // smooth shading: n_s = normalize(sum b_i n_i); hand the adjoint to the three vertex normals (their dependence on
+        // the positions -- Mesh::recompute_vertex_normals, mesh.cpp:199-276 -- is back-propagated once, after the replay)
+        float3 n0 = ld3(sc.nrm, tB.i0), n1 = ld3(sc.nrm, tB.i1), n2 = ld3(sc.nrm, tB.i2);
+        float b0 = 1.f - recB.b1 - recB.b2;
+        float L = norm(n0 * b0 + n1 * recB.b1 + n2 * recB.b2);
+        if (L > 0.f) {
+            float3 gm = (g_n - n * dot(n, g_n)) / L;
+            GradCtx gv = g; gv.grad_pos = g.grad_vnrm;
+            add_vertex(gv, tB.i0, gm * b0, add); add_vertex(gv, tB.i1, gm * recB.b1, add); add_vertex(gv, tB.i2, gm * recB.b2, add);
+        }
+    } else if (lN > 0.f) {
         // dn_g = P dN / |N|; the shading normal turns with the face: dn_s = (n_g x dn_g) x n_s (= dn_g for flat shading)
         float3 ng = tB.N / lN;
         float3 g_ng = g_n * dot(ng, n) - n * dot(g_n, ng);
@@ -226,6 +237,53 @@ HD void vertex_triple(const SceneDev &sc, const GradCtx &g, float3 xA, VtxRec re
         }
     }
     if (kindC == kEndSurface) { scatter_point(g, tC, recC, false, xC, g_dout, add); scatter_normal(g, tC, g_NC, add); }
+}
+
+// ---- vertex normals: n_v = normalize(a_v), a_v = sum over the faces around v of (corner angle) x (unit face normal) ----------
+// (Mesh::recompute_vertex_normals, src/librender/mesh.cpp:199-276, run by parameters_changed after a position update).
+// vnormal_accum_body rebuilds a_v; vnormal_adjoint_body takes the adjoint of the vertex normals gathered during the replay
+// back to the positions: through the normalisation, the unit face normal and the corner angles.
+HD float corner_angle(float3 d0, float3 d1) {          // enoki unit_angle
+    float dp = dot(d0, d1);
+    float temp = 2.f * asinf(fminf(1.f, 0.5f * norm(d1 - (dp < 0.f ? -d0 : d0))));
+    return dp >= 0.f ? temp : kPi - temp;
+}
+template <typename Add> HD void vnormal_accum_body(const SceneDev &sc, const GradCtx &g, uint32_t prim, float *acc, Add add) {
+    TriGeo t = tri_geo(sc, prim);
+    float l = norm(t.N);
+    if (!(l > 0.f)) return;
+    float3 nf = t.N / l, v[3] = { t.p0, t.p0 + t.e1, t.p0 + t.e2 };
+    uint32_t idx[3] = { t.i0, t.i1, t.i2 };
+    GradCtx ga = g; ga.grad_pos = acc;
+    for (int k = 0; k < 3; ++k)
+        add_vertex(ga, idx[k], nf * corner_angle(normalize(v[(k + 1) % 3] - v[k]), normalize(v[(k + 2) % 3] - v[k])), add);
+}
+template <typename Add> HD void vnormal_adjoint_body(const SceneDev &sc, const GradCtx &g, const float *acc, uint32_t prim, Add add) {
+    TriGeo t = tri_geo(sc, prim);
+    float l = norm(t.N);
+    if (!(l > 0.f)) return;
+    float3 nf = t.N / l, v[3] = { t.p0, t.p0 + t.e1, t.p0 + t.e2 }, g_nf = mk3(0.f);
+    uint32_t idx[3] = { t.i0, t.i1, t.i2 };
+    for (int k = 0; k < 3; ++k) {
+        uint32_t vi = idx[k] - g.vert_begin;
+        float3 a = ld3(acc, vi), gn = ld3(g.grad_vnrm, vi);
+        float la = norm(a);
+        if (!(la > 0.f) || (gn.x == 0.f && gn.y == 0.f && gn.z == 0.f)) continue;
+        float3 nv = a / la, ga = (gn - nv * dot(nv, gn)) / la;          // through n_v = a / |a|
+        uint32_t k1 = (k + 1) % 3, k2 = (k + 2) % 3;
+        float3 e0 = v[k1] - v[k], e1 = v[k2] - v[k];
+        float l0 = norm(e0), l1 = norm(e1);
+        float3 d0 = e0 / l0, d1 = e1 / l1;
+        float theta = corner_angle(d0, d1), c = dot(d0, d1);
+        g_nf += ga * theta;                                               // a += theta * n_f
+        float s2 = 1.f - c * c;
+        if (s2 > 1e-12f) {
+            float gc = -dot(ga, nf) / sqrtf(s2);                          // theta = acos(c)
+            float3 ge0 = (d1 - d0 * c) * (gc / l0), ge1 = (d0 - d1 * c) * (gc / l1);
+            add_vertex(g, idx[k1], ge0, add); add_vertex(g, idx[k2], ge1, add); add_vertex(g, idx[k], -(ge0 + ge1), add);
+        }
+    }
+    scatter_normal(g, t, (g_nf - nf * dot(nf, g_nf)) / l, add);           // n_f = N / |N|
 }
 
 // ---- replay hooks (plugged into shade_body, path.h) ----------------------------------------------------------------

@@ -112,7 +112,13 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     }
     GradCtx g; g.final_radiance = s->final_radiance.p; g.dL_dimage = d_dl; g.grad_tex = d_g; g.tex_id = grad_texture ? tex_id : -1;
     g.scale = 1.f / (float) spp_total;
-    g.grad_pos = d_v; g.mesh_id = grad_vertices ? mesh_id : -1; g.vert_begin = g.vert_count = 0;
+    g.grad_pos = d_v; g.grad_vnrm = nullptr; g.mesh_id = grad_vertices ? mesh_id : -1; g.vert_begin = g.vert_count = 0;
+    DevBuf<float> vnrm_adj, vnrm_acc;        // smooth-shaded mesh: adjoint of its vertex normals, and the unnormalised normals
+    if (grad_vertices && s->meshes[mesh_id].has_normals) {
+        CU(vnrm_adj.alloc(nvert)); CU(vnrm_acc.alloc(nvert));
+        CU(cudaMemsetAsync(vnrm_adj.p, 0, nvert * sizeof(float), st)); CU(cudaMemsetAsync(vnrm_acc.p, 0, nvert * sizeof(float), st));
+        g.grad_vnrm = vnrm_adj.p;
+    }
     if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
     g.cam_o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
@@ -126,6 +132,12 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         RC(run_batch(s, sn, b, nullptr, false, launches));
         CU(cudaMemcpyAsync(s->final_radiance.p, s->result.p, (size_t) n * sizeof(float4), cudaMemcpyDeviceToDevice, st));
         RC(run_batch(s, sn, b, &g, false, launches));
+    }
+    if (g.grad_vnrm != nullptr) {        // vertex normals -> positions (Mesh::recompute_vertex_normals), once per call
+        const MeshDev &m = s->meshes[mesh_id];
+        k_vnormal_accum<<<grid_for(m.face_count), kBlock, 0, st>>>(s->dev, g, m.face_begin, m.face_count, vnrm_acc.p);
+        k_vnormal_adjoint<<<grid_for(m.face_count), kBlock, 0, st>>>(s->dev, g, m.face_begin, m.face_count, vnrm_acc.p);
+        launches += 2;
     }
     uint64_t edge_samples = 0;
     if (grad_vertices && s->grad_boundary && s->grad_edge_fraction > 0.f) {

@@ -294,6 +294,15 @@ k_nee_grad(SceneDev sc, RenderBatch b, PathQueue qin, ShadowQueue sq, const uint
     uint32_t count = min(counters[1024 + depth], count_max);
     if (j < count && sq.occluded[j] == 0u) nee_adjoint(sc, g, qin, b, sq.nee_rec[j], sq.contrib_id[j], DevAdd());
 }
+// vertex-normal adjoint (adjoint.h): per face of the differentiated mesh
+__global__ void k_vnormal_accum(SceneDev sc, GradCtx g, uint32_t face_begin, uint32_t face_count, float *acc) {
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < face_count) vnormal_accum_body(sc, g, face_begin + f, acc, DevAdd());
+}
+__global__ void k_vnormal_adjoint(SceneDev sc, GradCtx g, uint32_t face_begin, uint32_t face_count, const float *acc) {
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < face_count) vnormal_adjoint_body(sc, g, acc, face_begin + f, DevAdd());
+}
 // boundary term of the vertex adjoint (adjoint.h): projected edge lengths, two primary rays per edge sample, scatter
 __global__ void k_edge_len(SceneDev sc, EdgeCtx e, float3 cam_o, float *len) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;

@@ -112,6 +112,8 @@ struct GradCtx {
     float scale;                    // d(developed pixel)/d(sample radiance) = 1/spp_total (box filter)
     // vertex-position adjoint (adjoint.h); grad_pos == nullptr: texture gradient only
     float *grad_pos;                // 3 floats per vertex of mesh `mesh_id`
+    float *grad_vnrm;               // same indexing: adjoint of the mesh's VERTEX NORMALS (smooth-shaded mesh), turned into
+                                    // position gradients after the replay by vnormal_adjoint_body (adjoint.h); may be null
     int mesh_id; uint32_t vert_begin, vert_count;
     float3 cam_o;                   // sensor origin (x0 of every path)
 };

@@ -335,9 +335,11 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     std::vector<float4> fin(pool);
     uint64_t cnt[3] = { 0, 0, 0 };
     GradCtx g; g.final_radiance = fin.data(); g.dL_dimage = dL_dimage; g.grad_tex = grad_texture; g.tex_id = grad_texture ? tex_id : -1; g.scale = 1.f / (float) spp_total;
-    g.grad_pos = grad_vertices; g.mesh_id = mesh_id; g.vert_begin = g.vert_count = 0;
+    g.grad_pos = grad_vertices; g.grad_vnrm = nullptr; g.mesh_id = mesh_id; g.vert_begin = g.vert_count = 0;
     g.cam_o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
     if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
+    std::vector<float> vnrm_adj, vnrm_acc;
+    if (grad_vertices && s->meshes[mesh_id].has_normals) { vnrm_adj.assign(3 * (size_t) g.vert_count, 0.f); vnrm_acc.assign(3 * (size_t) g.vert_count, 0.f); g.grad_vnrm = vnrm_adj.data(); }
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
@@ -345,6 +347,11 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
         ReplayGrad<HostAdd> rg; rg.g = g;
         hs_run_batch<RgbX>(s, sn, b, P, cnt, rg);
+    }
+    if (g.grad_vnrm != nullptr) {        // k_vnormal_accum, k_vnormal_adjoint
+        const MeshDev &mm = s->meshes[mesh_id];
+        for (uint32_t f = 0; f < mm.face_count; ++f) vnormal_accum_body(s->dev, g, mm.face_begin + f, vnrm_acc.data(), HostAdd());
+        for (uint32_t f = 0; f < mm.face_count; ++f) vnormal_adjoint_body(s->dev, g, vnrm_acc.data(), mm.face_begin + f, HostAdd());
     }
     if (!grad_vertices || !boundary) return;
     // ---- boundary term: unique edges of the mesh, projected-length cdf, two paths per edge sample
