@@ -654,7 +654,6 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
-    if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");
     uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
     RC(ensure_pool(s, pool));
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));

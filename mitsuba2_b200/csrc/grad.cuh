@@ -91,7 +91,6 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     if (sn.rfilter != 0 || sn.radius > 1.f)      // single-pixel splat of weight 1 (imageblock.cpp:162-169)
         return fail(MTSB_E_INVALID, "mtsb_render_grad: only the box reconstruction filter is supported");
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
-    if (npix * spp_total > 0xffffffffull) return fail(MTSB_E_INVALID, "pixels * spp_total exceeds the 32-bit sample-stream index");
     uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
     if (grad_vertices && pool < 2) pool = 2;
     RC(ensure_pool(s, pool));

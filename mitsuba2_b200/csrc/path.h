@@ -41,11 +41,15 @@ HD Pcg32 rng_load(uint4 v) {
     return r;
 }
 
-HD void path_ids(const RenderBatch &b, uint32_t i, uint32_t &pixel, uint32_t &stream) {
+// Sample stream of path i = pixel * spp_total + sample index, independent of how the samples are split into batches and
+// ranks.  The sampler takes a 32-bit index (TEA pair, integrator.cpp:144-169); a job with more than 2^32 samples folds the
+// high half of the 64-bit index into the seed, so indices below 2^32 seed exactly as before.
+HD void path_ids(const RenderBatch &b, uint32_t i, uint32_t &pixel, uint32_t &stream, uint64_t &seed) {
     uint64_t g = b.offset + i;
     pixel = (uint32_t) (g / b.spp_batch);
     uint32_t s = b.spp_begin + (uint32_t) (g % b.spp_batch);
-    stream = pixel * b.spp_total + s;
+    uint64_t idx = (uint64_t) pixel * b.spp_total + s;
+    stream = (uint32_t) idx; seed = b.seed + (idx >> 32);
 }
 
 // PerspectiveCamera::sample_ray (src/sensors/perspective.cpp:151-188); pos in [0,1]^2
@@ -60,8 +64,8 @@ HD void sensor_sample_ray(const SensorDev &sn, float px, float py, float4 &o_min
 
 template <typename M = Rgb>
 HD void raygen_body(const SensorDev &sn, const RenderBatch &b, const PathQueue &q, uint32_t i) {
-    uint32_t pixel, stream; path_ids(b, i, pixel, stream);
-    Pcg32 rng = sampler_seed(b.seed, stream);
+    uint32_t pixel, stream; uint64_t seed; path_ids(b, i, pixel, stream, seed);
+    Pcg32 rng = sampler_seed(seed, stream);
     float jx = rng.next_f32(), jy = rng.next_f32();
     float wavelength_sample = rng.next_f32();    // integrator.cpp:237; drawn in every mode, used by the spectral one
     if (M::spectral) q.wav_eta[i] = make_float2(wavelength_sample, 1.f);
@@ -312,8 +316,8 @@ HD float4 radiance_to_xyza(float4 r) {
 }
 // position sample of path i (re-derived from the RNG stream instead of stored)
 HD void path_film_pos(const SensorDev &sn, const RenderBatch &b, uint32_t i, float &fx, float &fy) {
-    uint32_t pixel, stream; path_ids(b, i, pixel, stream);
-    Pcg32 rng = sampler_seed(b.seed, stream);
+    uint32_t pixel, stream; uint64_t seed; path_ids(b, i, pixel, stream, seed);
+    Pcg32 rng = sampler_seed(seed, stream);
     float jx = rng.next_f32(), jy = rng.next_f32();
     fx = (float) (pixel % sn.width) + jx; fy = (float) (pixel / sn.width) + jy;
 }

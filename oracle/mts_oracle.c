@@ -1226,7 +1226,8 @@ void orc_render(const orc_scene *s, uint32_t id, uint32_t spp_begin, uint32_t sp
     for (int64_t p = 0; p < npix; ++p) {
         for (uint32_t k = 0; k < spp_count; ++k) {
             float pos[2], r[4]; uint64_t cnt[4] = { 0, 0, 0, 0 };
-            render_one(s, sn, (uint32_t) p, (uint32_t) p * spp_total + spp_begin + k, seed, pos, r, cnt);
+            uint64_t idx = (uint64_t) p * spp_total + spp_begin + k;      /* >= 2^32 samples: the high half goes into the seed */
+            render_one(s, sn, (uint32_t) p, (uint32_t) idx, seed + (idx >> 32), pos, r, cnt);
             float v5[5] = { 0.412453f * r[0] + 0.357580f * r[1] + 0.180423f * r[2], 0.212671f * r[0] + 0.715160f * r[1] + 0.072169f * r[2],
                             0.019334f * r[0] + 0.119193f * r[1] + 0.950227f * r[2], r[3], 1.f };     /* spectrum.h:220-227 */
             if (s->spectral) { v5[0] = r[0]; v5[1] = r[1]; v5[2] = r[2]; }

@@ -363,3 +363,16 @@ def test_serialized_loader(tmp_path, version, double):
         assert np.allclose(m.positions[[0, 2, 3]], [[-2.85, 0, -7.6], [2.85, 0, 0.6], [2.85, 0, -7.6]], atol=1e-3)
         assert np.allclose(m.texcoords[[0, 2, 3]], [[0.950589, 1 - 0.988416], [0.025105, 1 - 0.689127], [0.950589, 1 - 0.689127]], atol=1e-3)
         assert np.allclose(m.normals, [[0, 1, 0]] * 4)
+
+
+def test_sample_stream_index_beyond_32_bits():
+    """pixels * spp_total > 2^32 (e.g. 1080p x 2304 spp over 8 ranks): the sample-stream index is 64-bit, its high half is
+    folded into the sampler seed; streams below 2^32 are unchanged, the ones above differ from them and agree with the oracle."""
+    sd = H.cbox_scene(res=4, spp=2)
+    big = 1 << 29                                       # 16 pixels x 2^29 = 2^33 streams
+    o, h = Oracle(sd), HostSim(sd)
+    a = o.render_xyzaw(seed=5, spp=2, spp_begin=big - 2, spp_total=big)
+    b = h.render_xyzaw(seed=5, spp=2, spp_begin=big - 2, spp_total=big)
+    assert np.abs(a - b).max() < 2e-3 * max(1.0, np.abs(a).max())
+    # pixel 8 of this job (index 2^32 + 2^29 - 2, seed + 1) must not reuse the streams of pixel 0 (index 2^29 - 2, seed)
+    assert not np.allclose(a.reshape(-1, 5)[8, :3], a.reshape(-1, 5)[0, :3])
