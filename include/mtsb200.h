@@ -58,7 +58,10 @@ typedef struct mtsb_texture_desc {
  * PLASTIC src/bsdfs/plastic.cpp (smooth dielectric coating over a diffuse base).
  * Texture ids index mtsb_scene_desc.textures; -1 = absent. */
 enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_DIELECTRIC = 2, MTSB_BSDF_CONDUCTOR = 3, MTSB_BSDF_PLASTIC = 4,
-       MTSB_BSDF_ROUGHDIELECTRIC = 5 };   /* src/bsdfs/roughdielectric.cpp: microfacet reflection + transmission */
+       MTSB_BSDF_ROUGHDIELECTRIC = 5,     /* src/bsdfs/roughdielectric.cpp: microfacet reflection + transmission */
+       MTSB_BSDF_ROUGHPLASTIC = 6 };      /* src/bsdfs/roughplastic.cpp: rough dielectric coating over a diffuse base (alpha_u,
+                                             distribution, sample_visible, eta, reflectance_tex = diffuse_reflectance, nonlinear,
+                                             specular_sampling_weight); the transmittance tables are computed at scene creation */
 enum { MTSB_MF_BECKMANN = 0, MTSB_MF_GGX = 1 };
 typedef struct mtsb_bsdf_desc {
     int32_t type;

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
 MEM_HOST, MEM_DEVICE = 0, 1
 TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM = 0, 1, 2, 3, 4
 MODE_RGB, MODE_SPECTRAL = 0, 1
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHDIELECTRIC, BSDF_ROUGHPLASTIC = 0, 1, 2, 3, 4, 5, 6
 MF_BECKMANN, MF_GGX = 0, 1
 EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN, RFILTER_MITCHELL, RFILTER_CATMULLROM, RFILTER_LANCZOS = 0, 1, 2, 3, 4, 5

@@ -402,6 +402,23 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         else if (b.type == MTSB_BSDF_PLASTIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.reflectance_tex, false) && tex_ok(b.specular_reflectance_tex, true) &&
                                                          b.specular_sampling_weight >= 0.f && b.specular_sampling_weight <= 1.f);
         else if (b.type == MTSB_BSDF_DIELECTRIC || b.type == MTSB_BSDF_ROUGHDIELECTRIC) CHECK_ARG(b.eta > 0.f && tex_ok(b.specular_reflectance_tex, true) && tex_ok(b.specular_transmittance_tex, true));
+        else if (b.type == MTSB_BSDF_ROUGHPLASTIC) {
+            CHECK_ARG(b.eta > 0.f && b.alpha_u > 0.f && tex_ok(b.reflectance_tex, false) && tex_ok(b.specular_reflectance_tex, true) &&
+                      b.specular_sampling_weight >= 0.f && b.specular_sampling_weight <= 1.f);
+            // roughplastic.cpp parameters_changed: external transmittance at 64 cosines + mean internal reflectance, integrated on the GPU
+            std::vector<float> n32, w32, n128, w128;
+            gauss_legendre_rule(32, n32, w32); gauss_legendre_rule(128, n128, w128);
+            DevBuf<float> d_n32, d_w32, d_n128, d_w128;
+            CU(d_n32.upload(n32.data(), 32, st)); CU(d_w32.upload(w32.data(), 32, st)); CU(d_n128.upload(n128.data(), 128, st)); CU(d_w128.upload(w128.data(), 128, st));
+            s->tables.emplace_back(new DevBuf<float>());
+            DevBuf<float> &tab = *s->tables.back();
+            CU(tab.alloc(2 * kRoughTransRes));
+            k_rough_tables<<<1, 2 * kRoughTransRes, 0, st>>>(b.distribution, b.alpha_u, b.eta, d_n32.p, d_w32.p, d_n128.p, d_w128.p, tab.p);
+            float h[2 * kRoughTransRes];
+            CU(cudaMemcpyAsync(h, tab.p, sizeof(h), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st));
+            double acc = 0; for (int k = 0; k < kRoughTransRes; ++k) acc += (double) h[kRoughTransRes + k] * rough_table_mu(k);
+            bd.rough_t = tab.p; bd.internal_refl = (float) (acc / kRoughTransRes) * 2.f;
+        }
         else return fail(MTSB_E_INVALID, "unknown BSDF type");
         s->bsdfs.push_back(bd);
     }

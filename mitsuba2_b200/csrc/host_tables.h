@@ -1,5 +1,7 @@
 // host_tables.h -- host-side construction of sampling tables uploaded once per scene.
 #pragma once
+#include <cmath>
+#include <vector>
 #include <vector>
 #include <cmath>
 #include <cstdint>
@@ -111,3 +113,28 @@ inline bool invert4x4(const float *m, float *inv) {
 }
 
 } // namespace mtsb
+
+// quad::gauss_legendre (include/mitsuba/core/quad.h:26, src/libcore/quad.cpp): nodes and weights of the n-point rule on
+// [-1, 1] -- Newton iteration on the Legendre polynomial from the Chebyshev guess, in double.
+inline void gauss_legendre_rule(int n, std::vector<float> &nodes, std::vector<float> &weights) {
+    nodes.assign(n, 0.f); weights.assign(n, 0.f);
+    const double pi = 3.14159265358979323846;
+    for (int i = 0; i < (n + 1) / 2; ++i) {
+        double x = -std::cos((2 * i + 1) / (double) (2 * n) * pi), dp = 1.0;
+        for (int it = 0; it < 100; ++it) {
+            double p0 = 1.0, p1 = x;
+            for (int k = 2; k <= n; ++k) { double p2 = ((2 * k - 1) * x * p1 - (k - 1) * p0) / k; p0 = p1; p1 = p2; }
+            dp = n * (x * p1 - p0) / (x * x - 1.0);
+            double step = p1 / dp;
+            x -= step;
+            if (std::fabs(step) <= 4e-16 * std::fabs(x)) break;
+        }
+        double p0 = 1.0, p1 = x;
+        for (int k = 2; k <= n; ++k) { double p2 = ((2 * k - 1) * x * p1 - (k - 1) * p0) / k; p0 = p1; p1 = p2; }
+        dp = n * (x * p1 - p0) / (x * x - 1.0);
+        double w = 2.0 / ((1.0 - x * x) * dp * dp);
+        nodes[i] = (float) x; nodes[n - 1 - i] = (float) -x; weights[i] = weights[n - 1 - i] = (float) w;
+    }
+    if (n % 2 == 1) nodes[n / 2] = 0.f;
+}
+

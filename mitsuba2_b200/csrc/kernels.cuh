@@ -79,6 +79,16 @@ __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
     if (i < end) collapse_body(b, i);
 }
 
+// rough plastic tables (shade.h): thread i < 64: external transmittance at cosine mu_i; 64 <= i < 128: internal reflectance
+__global__ void k_rough_tables(int distr_type, float alpha, float eta, const float *n32, const float *w32, const float *n128, const float *w128, float *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * kRoughTransRes) return;
+    bool transmit = i < (uint32_t) kRoughTransRes;
+    float e = transmit ? eta : 1.f / eta;
+    int res = rough_table_res(e);
+    out[i] = rough_boundary_integral(distr_type, alpha, e, rough_table_mu((int) (i % kRoughTransRes)), res == 32 ? n32 : n128, res == 32 ? w32 : w128, res, transmit);
+}
+
 // ---------------- traversal ----------------------------------------------------------------------
 // Persistent-warp traversal with dynamic ray fetch (after Aila & Laine 2009): the grid is sized to fill the SMs once;
 // every warp claims chunks of kFetchChunk consecutive rays from a global work counter and hands them to lanes whose

@@ -19,6 +19,8 @@ struct BsdfDev {
     int two_sided;          // `twosided` adapter, same BRDF on both sides (src/bsdfs/twosided.cpp)
     int nonlinear; float spec_weight;   // plastic (type 4): `nonlinear`, specular sampling weight; type 3 = smooth conductor
     int opacity;            // >= 0: `mask` adapter (src/bsdfs/mask.cpp) with this single-channel opacity texture
+    const float *rough_t;   // rough plastic (type 6): external transmittance at 64 cosines (roughplastic.cpp parameters_changed)
+    float internal_refl;    // rough plastic: mean internal reflectance
 };
 constexpr int kMaxEnvLevels = 20;
 struct EmitterDev {

@@ -282,6 +282,40 @@ struct Microfacet {
     }
 };
 
+// ---- rough plastic tables (roughplastic.cpp: parameters_changed; microfacet.h:454-552 eval_reflectance / eval_transmittance) ----
+// One entry: the hemispherical transmittance (or reflectance) of a rough dielectric boundary for incidence cosine mu, by a
+// res x res Gauss-Legendre rule over the visible-normal sample square.  nodes / weights: the rule on [-1, 1].
+constexpr int kRoughTransRes = 64;       // MTS_ROUGH_TRANSMITTANCE_RES
+HD float rough_boundary_integral(int distr_type, float alpha, float eta, float mu, const float *nodes, const float *weights, int res, bool transmit) {
+    Microfacet distr(distr_type, alpha, alpha, true);
+    float3 wi = mk3(sqrtf(1.f - mu * mu), 0.f, mu);
+    float accum = 0.f;
+    for (int a = 0; a < res; ++a)
+        for (int b = 0; b < res; ++b) {
+            float pdf; float3 m = distr.sample(wi, fmaf(nodes[b], 0.5f, 0.5f), fmaf(nodes[a], 0.5f, 0.5f), pdf);
+            float f, cos_t, eta_it, eta_ti, wim = dot(wi, m);
+            fresnel_dielectric(wim, eta, f, cos_t, eta_it, eta_ti);
+            float smith;
+            if (transmit) {
+                float3 wo = m * fmaf(wim, eta_ti, cos_t) - wi * eta_ti;
+                smith = wo.z * wi.z >= 0.f ? 0.f : distr.smith_g1(wo, m) * (1.f - f);
+            } else {
+                float3 wo = m * (2.f * wim) - wi;
+                smith = (wo.z <= 0.f || wi.z <= 0.f) ? 0.f : distr.smith_g1(wo, m) * f;
+            }
+            accum += smith * (weights[a] * weights[b]);
+        }
+    return accum * 0.25f;
+}
+HD int rough_table_res(float eta) { return eta > 1.f ? 32 : 128; }          // microfacet.h:468-472 (already multiples of the packet size)
+HD float rough_table_mu(int i) { return fmaxf(1e-6f, (float) i / (float) (kRoughTransRes - 1)); }
+// roughplastic.cpp: lerp_gather over the 64-entry table
+HD float rough_lerp(const float *data, float x) {
+    x *= (float) (kRoughTransRes - 1);
+    uint32_t index = min((uint32_t) x, (uint32_t) kRoughTransRes - 2u);
+    return lerpf(data[index], data[index + 1], x - (float) index);
+}
+
 // ---- BSDF::sample / eval / pdf --------------------------------------------------------------------
 // The textures of a BSDF at one surface point, looked up once per path vertex and shared by eval (emitter sample) and
 // sample: diffuse a = reflectance; roughconductor a = eta, b = k, c = specular_reflectance (1 if absent);
@@ -303,7 +337,7 @@ HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, floa
     BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f); t.opacity = 1.f;
     if (M::ext && b.opacity >= 0) t.opacity = fminf(fmaxf(tex_eval_m<M>(sc, b.opacity, u, v, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
     if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
-    else if (M::ext && b.type == 4) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
+    else if (M::ext && (b.type == 4 || b.type == 6)) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
     else if (b.type == 1 || (M::ext && b.type == 3)) {
         t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
         if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
@@ -313,6 +347,8 @@ HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, floa
     }
     return t;
 }
+template <typename M>
+HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, const BsdfTexT<M> &tx);
 template <typename M>
 HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, const BsdfTexT<M> &tx) {
     typedef typename M::Spec Spec;
@@ -362,6 +398,22 @@ HD BsdfSampleT<M> bsdf_sample_one_sided(const SceneDev &sc, const BsdfDev &b, co
             float f_o; fresnel_dielectric(bs.wo.z, b.eta_f, f_o, ct, e1, e2);
             bs.weight = plastic_diffuse<M>(b, tx.a) * ((1.f / (b.eta_f * b.eta_f)) * (1.f - f_i) * (1.f - f_o) / prob_diffuse);
         }
+        return bs;
+    }
+    if (M::ext && b.type == 6) {  // src/bsdfs/roughplastic.cpp (sample): pick a lobe, then weight = eval / pdf of BOTH lobes
+        if (!(cos_i > 0.f)) return bs;
+        float t_i = rough_lerp(b.rough_t, cos_i);
+        float prob_specular = (1.f - t_i) * b.spec_weight, prob_diffuse = t_i * (1.f - b.spec_weight);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse);
+        if (s1 < prob_specular) {
+            Microfacet distr(b.distr, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+            float unused; float3 m = distr.sample(si.wi, sx, sy, unused);
+            bs.wo = m * (2.f * dot(si.wi, m)) - si.wi;
+        } else
+            bs.wo = square_to_cosine_hemisphere(sx, sy);
+        Spec val; bsdf_eval_pdf_one_sided<M>(sc, b, si, bs.wo, val, bs.pdf, tx);
+        bs.weight = bs.pdf > 0.f ? val * (1.f / bs.pdf) : M::splat(0.f);
+        if (!(bs.pdf > 0.f)) bs.pdf = 0.f;
         return bs;
     }
     if (M::ext && b.type == 5) {  // src/bsdfs/roughdielectric.cpp (sample): microfacet normal, then Fresnel lobe choice
@@ -460,6 +512,22 @@ HD void bsdf_eval_pdf_one_sided(const SceneDev &sc, const BsdfDev &b, const SI &
         float prob = sample_distr.pdf(mk3(mulsign(si.wi.x, ci), mulsign(si.wi.y, ci), mulsign(si.wi.z, ci)), m);
         prob *= reflect ? F : 1.f - F;
         pdf = prob * fabsf(dwh_dwo);
+        return;
+    }
+    if (M::ext && b.type == 6) {  // src/bsdfs/roughplastic.cpp (eval, pdf)
+        if (!(ci > 0.f && co > 0.f)) return;
+        Microfacet distr(b.distr, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+        float3 H = normalize(wo + si.wi);
+        float D = distr.eval(H), F, ct, e1, e2;
+        fresnel_dielectric(dot(si.wi, H), b.eta_f, F, ct, e1, e2);
+        Spec value = M::splat(F * D * distr.G(si.wi, wo, H) / (4.f * ci));
+        if (b.spec_r >= 0) value *= tx.b;
+        float t_i = rough_lerp(b.rough_t, ci), t_o = rough_lerp(b.rough_t, co);
+        val = value + plastic_div(tx.a, b.internal_refl, b.nonlinear != 0) * (kInvPi * (1.f / (b.eta_f * b.eta_f)) * co * t_i * t_o);
+        float prob_specular = (1.f - t_i) * b.spec_weight, prob_diffuse = t_i * (1.f - b.spec_weight);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+        float r = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
+        pdf = r * prob_specular + prob_diffuse * (kInvPi * co);
         return;
     }
     if (M::ext && b.type == 4) {  // src/bsdfs/plastic.cpp:247-296: the diffuse lobe (the specular one is a delta)

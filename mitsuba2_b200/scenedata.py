@@ -202,6 +202,20 @@ class SceneData:
                            "specular_sampling_weight": s_mean / (d_mean + s_mean)})
         return len(self.bsdfs) - 1
 
+    def add_roughplastic(self, diffuse_reflectance=0.5, int_ior=1.49, ext_ior=1.000277, alpha=0.1, distribution="beckmann",
+                         sample_visible=True, specular_reflectance=None, nonlinear=False):
+        """``roughplastic`` (src/bsdfs/roughplastic.cpp): rough dielectric coating over a diffuse base.  The library computes the
+        transmittance tables of the coating when the scene is created."""
+        d = self._tex(diffuse_reflectance)
+        s_id = -1 if specular_reflectance is None else self._tex(specular_reflectance)
+        d_mean, s_mean = self._texture_mean(d), (1.0 if s_id < 0 else self._texture_mean(s_id))
+        self.bsdfs.append({"type": A.BSDF_ROUGHPLASTIC, "reflectance_tex": d, "specular_reflectance_tex": s_id,
+                           "eta": float(int_ior) / float(ext_ior), "alpha_u": float(alpha), "alpha_v": float(alpha),
+                           "distribution": A.MF_GGX if distribution.lower() == "ggx" else A.MF_BECKMANN,
+                           "sample_visible": int(bool(sample_visible)), "nonlinear": int(bool(nonlinear)),
+                           "specular_sampling_weight": s_mean / (d_mean + s_mean)})
+        return len(self.bsdfs) - 1
+
     def add_roughdielectric(self, int_ior=1.5046, ext_ior=1.000277, alpha=0.1, alpha_v=None, distribution="beckmann", sample_visible=True,
                             specular_reflectance=None, specular_transmittance=None):
         """``roughdielectric`` (src/bsdfs/roughdielectric.cpp): microfacet reflection and refraction."""

@@ -251,6 +251,15 @@ class _Loader:
             idx = self.sd.add_mask(self.bsdf_index(inner[0]), opacity)
         elif ty == "diffuse":
             idx = self.sd.add_diffuse(self.texture_index(p.get("reflectance"), 0.5))
+        elif ty == "roughplastic":
+            def rior(v, d):
+                v = p.get(v, d)
+                return IOR_NAMES[v.lower()] if isinstance(v, str) else float(v)
+            idx = self.sd.add_roughplastic(self.texture_index(p.get("diffuse_reflectance"), 0.5), rior("int_ior", "polypropylene"),
+                                           rior("ext_ior", "air"), p.get("alpha", 0.1), p.get("distribution", "beckmann"),
+                                           p.get("sample_visible", True),
+                                           self.texture_index(p["specular_reflectance"], 1.0) if "specular_reflectance" in p else None,
+                                           p.get("nonlinear", False))
         elif ty == "plastic":
             def pior(v, d):
                 v = p.get(v, d)

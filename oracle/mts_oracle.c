@@ -315,7 +315,10 @@ struct orc_scene {
     int env_emitter; int max_depth, rr_depth;
     int spectral, nch;        /* MTSB_MODE_SPECTRAL: 4 wavelengths per path */
     v3 bbox_lo, bbox_hi;
+    float *rough_tab;         /* per BSDF: 64 external transmittances + mean internal reflectance (roughplastic.cpp) */
 };
+static void rough_plastic_tables(const mtsb_bsdf_desc *b, float *tab);
+static float rough_lerp(const float *data, float x);
 
 /* ---- a plain median-split BVH so the oracle finishes in seconds on 1M triangles; hit semantics are those of
  *      ShapeKDTree::ray_intersect_scalar (kdtree.h:2080-2175): closest t in [mint,maxt], test `t <= maxt`. */
@@ -511,6 +514,8 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
         vb += m->vertex_count; fb += m->face_count;
     }
     s->bsdfs = calloc(d->n_bsdfs ? d->n_bsdfs : 1, sizeof(mtsb_bsdf_desc)); memcpy(s->bsdfs, d->bsdfs, sizeof(mtsb_bsdf_desc) * d->n_bsdfs);
+    s->rough_tab = calloc((d->n_bsdfs ? d->n_bsdfs : 1) * 65, sizeof(float));
+    for (uint32_t i = 0; i < d->n_bsdfs; ++i) if (d->bsdfs[i].type == MTSB_BSDF_ROUGHPLASTIC) rough_plastic_tables(&d->bsdfs[i], s->rough_tab + 65 * (size_t) i);
     s->sensors = calloc(d->n_sensors ? d->n_sensors : 1, sizeof(mtsb_sensor_desc)); memcpy(s->sensors, d->sensors, sizeof(mtsb_sensor_desc) * d->n_sensors);
     s->spectral = d->mode == MTSB_MODE_SPECTRAL; s->nch = s->spectral ? 4 : 3;
     s->tex = calloc(d->n_textures ? d->n_textures : 1, sizeof(otex));
@@ -554,7 +559,7 @@ void orc_scene_destroy(orc_scene *s) {
     for (uint32_t i = 0; i < s->n_tex; ++i) free(s->tex[i].data);
     for (uint32_t i = 0; i < s->n_emitters; ++i) { oemitter *e = &s->emitters[i]; free(e->cdf); free(e->rgba);
         for (int l = 0; l < e->warp.n_levels; ++l) free(e->warp.levels[l]); free(e->warp.levels); free(e->warp.widths); }
-    free(s->meshes); free(s->bsdfs); free(s->tex); free(s->emitters); free(s->sensors); free(s->pos); free(s->nrm); free(s->uv);
+    free(s->rough_tab); free(s->meshes); free(s->bsdfs); free(s->tex); free(s->emitters); free(s->sensors); free(s->pos); free(s->nrm); free(s->uv);
     free(s->faces); free(s->face_mesh); free(s->nodes); free(s->order); free(s);
 }
 void orc_scene_update_texture(orc_scene *s, uint32_t id, const float *data) {
@@ -718,6 +723,7 @@ static float fresnel_diffuse_reflectance(float eta) {
     return 0.919317f - 3.4793f * i1 + 6.75335f * i2 - 7.80989f * i3 + 4.98554f * i4 - 1.36881f * i5;
 }
 static col fresnel_conductor_col(float c, col eta, col k) { col r; for (int i = 0; i < 4; ++i) r.c[i] = orc_fresnel_conductor(c, eta.c[i], k.c[i]); return r; }
+static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav);
 static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
     obs bs; memset(&bs, 0, sizeof(bs)); bs.eta = 1.f;
     float cos_theta_i = si->wi.z;
@@ -769,6 +775,23 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
             for (int i = 0; i < 4; ++i) value.c[i] /= 1.f - (b->nonlinear ? value.c[i] * fdr_int : fdr_int);
             bs.weight = cscale(value, inv_eta_2 * (1.f - f_i) * (1.f - f_o) / prob_diffuse);
         }
+        return bs;
+    }
+    if (b->type == MTSB_BSDF_ROUGHPLASTIC) {           /* roughplastic.cpp: sample (choose a lobe; weight = eval / pdf over both) */
+        if (!(cos_theta_i > 0.f)) return bs;
+        const float *tab = s->rough_tab + 65 * (size_t) (b - s->bsdfs);
+        float t_i = rough_lerp(tab, cos_theta_i), ssw = b->specular_sampling_weight;
+        float prob_specular = (1.f - t_i) * ssw, prob_diffuse = t_i * (1.f - ssw);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse);
+        if (s1 < prob_specular) {
+            mf_t distr = mf_make(b->distribution, b->alpha_u, b->alpha_u, b->sample_visible);
+            float unused; v3 m = mf_sample(&distr, si->wi, sx, sy, &unused);
+            bs.wo = vsub(vscale(m, 2.f * vdot(si->wi, m)), si->wi);
+        } else
+            bs.wo = cosine_hemisphere(sx, sy);
+        col val; bsdf_eval_pdf_nested(s, b, si, bs.wo, &val, &bs.pdf, wav);
+        bs.weight = bs.pdf > 0.f ? cscale(val, 1.f / bs.pdf) : C1(0.f);
+        if (!(bs.pdf > 0.f)) bs.pdf = 0.f;
         return bs;
     }
     if (b->type == MTSB_BSDF_ROUGHDIELECTRIC) {        /* roughdielectric.cpp: sample */
@@ -860,6 +883,25 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         *pdf = prob * fabsf(dwh_dwo);
         return;
     }
+    if (b->type == MTSB_BSDF_ROUGHPLASTIC) {           /* roughplastic.cpp: eval, pdf */
+        if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return;
+        const float *tab = s->rough_tab + 65 * (size_t) (b - s->bsdfs);
+        mf_t distr = mf_make(b->distribution, b->alpha_u, b->alpha_u, b->sample_visible);
+        v3 H = vnormalize(vadd(wo, si->wi));
+        float D = mf_eval(&distr, H), F, ct, e1, e2; fresnel(vdot(si->wi, H), b->eta, &F, &ct, &e1, &e2);
+        col value = C1(F * D * (mf_g1(&distr, si->wi, H) * mf_g1(&distr, wo, H)) / (4.f * cos_theta_i));
+        if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+        float t_i = rough_lerp(tab, cos_theta_i), t_o = rough_lerp(tab, cos_theta_o);
+        col diff = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+        for (int i = 0; i < 4; ++i) diff.c[i] /= 1.f - (b->nonlinear ? diff.c[i] * tab[64] : tab[64]);
+        diff = cscale(diff, INV_PI_F * (1.f / (b->eta * b->eta)) * cos_theta_o * t_i * t_o);
+        for (int i = 0; i < 4; ++i) val->c[i] = value.c[i] + diff.c[i];
+        float ssw = b->specular_sampling_weight, prob_specular = (1.f - t_i) * ssw, prob_diffuse = t_i * (1.f - ssw);
+        prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+        float r = b->sample_visible ? D * mf_g1(&distr, si->wi, H) / (4.f * cos_theta_i) : mf_pdf(&distr, si->wi, H) / (4.f * vdot(wo, H));
+        *pdf = r * prob_specular + prob_diffuse * (INV_PI_F * cos_theta_o);
+        return;
+    }
     if (b->type == MTSB_BSDF_PLASTIC) {                /* plastic.cpp:247-296 (the diffuse lobe; the specular one is a delta) */
         if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return;
         float f_i, f_o, ct, e1, e2; fresnel(cos_theta_i, b->eta, &f_i, &ct, &e1, &e2); fresnel(cos_theta_o, b->eta, &f_o, &ct, &e1, &e2);
@@ -873,6 +915,52 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
 }
 /* TwoSidedBRDF::sample / eval / pdf (twosided.cpp:98-200) with the same nested BRDF on both sides: on the back side flip
  * wi (and wo) about the surface; cos(wi) == 0 is neither front nor back */
+/* ---- roughplastic.cpp: precomputed boundary integrals (parameters_changed; microfacet.h:454-552) and lerp_gather ---- */
+static void gauss_legendre(int n, double *x, double *w) {      /* quad::gauss_legendre: Newton on P_n from the Chebyshev guess */
+    for (int i = 0; i < (n + 1) / 2; ++i) {
+        double z = -cos((2 * i + 1) / (double) (2 * n) * 3.14159265358979323846), dp = 1.0;
+        for (int it = 0; it < 100; ++it) {
+            double p0 = 1.0, p1 = z;
+            for (int k = 2; k <= n; ++k) { double p2 = ((2 * k - 1) * z * p1 - (k - 1) * p0) / k; p0 = p1; p1 = p2; }
+            dp = n * (z * p1 - p0) / (z * z - 1.0);
+            double step = p1 / dp; z -= step;
+            if (fabs(step) <= 4e-16 * fabs(z)) break;
+        }
+        double p0 = 1.0, p1 = z;
+        for (int k = 2; k <= n; ++k) { double p2 = ((2 * k - 1) * z * p1 - (k - 1) * p0) / k; p0 = p1; p1 = p2; }
+        dp = n * (z * p1 - p0) / (z * z - 1.0);
+        x[i] = z; x[n - 1 - i] = -z; w[i] = w[n - 1 - i] = 2.0 / ((1.0 - z * z) * dp * dp);
+    }
+}
+static float rough_boundary_integral(int type, float alpha, float eta, float mu, int transmit) {
+    int res = eta > 1.f ? 32 : 128;
+    double xs[128], ws[128]; gauss_legendre(res, xs, ws);
+    mf_t distr = mf_make(type, alpha, alpha, 1);
+    v3 wi = V(sqrtf(1.f - mu * mu), 0.f, mu);
+    float accum = 0.f;
+    for (int a = 0; a < res; ++a) for (int b = 0; b < res; ++b) {
+        float pdf; v3 m = mf_sample(&distr, wi, fmaf((float) xs[b], .5f, .5f), fmaf((float) xs[a], .5f, .5f), &pdf);
+        float f, ct, eit, eti, wim = vdot(wi, m); fresnel(wim, eta, &f, &ct, &eit, &eti);
+        float smith;
+        if (transmit) { v3 wo = vsub(vscale(m, fmaf(wim, eti, ct)), vscale(wi, eti)); smith = wo.z * wi.z >= 0.f ? 0.f : mf_g1(&distr, wo, m) * (1.f - f); }
+        else { v3 wo = vsub(vscale(m, 2.f * wim), wi); smith = (wo.z <= 0.f || wi.z <= 0.f) ? 0.f : mf_g1(&distr, wo, m) * f; }
+        accum += smith * ((float) ws[a] * (float) ws[b]);
+    }
+    return accum * .25f;
+}
+static void rough_plastic_tables(const mtsb_bsdf_desc *b, float *tab /* 64 transmittances, then the internal reflectance */) {
+    double acc = 0;
+    for (int i = 0; i < 64; ++i) {
+        float mu = fmaxf(1e-6f, (float) i / 63.f);
+        tab[i] = rough_boundary_integral(b->distribution, b->alpha_u, b->eta, mu, 1);
+        acc += (double) rough_boundary_integral(b->distribution, b->alpha_u, 1.f / b->eta, mu, 0) * mu;
+    }
+    tab[64] = (float) (acc / 64.0) * 2.f;
+}
+static float rough_lerp(const float *data, float x) {
+    x *= 63.f; uint32_t index = (uint32_t) x; if (index > 62u) index = 62u;
+    return lerp_(data[index], data[index + 1], x - (float) index);
+}
 /* MaskBSDF::eval_opacity (mask.cpp): clamp(opacity->eval_1(si), 0, 1); the texture is single-channel */
 static float mask_opacity(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, const float *wav) {
     return fminf(fmaxf(tex_eval(s, b->opacity_tex_plus1 - 1, si->u, si->v, wav).c[0], 0.f), 1.f);

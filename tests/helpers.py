@@ -387,6 +387,9 @@ def n4_scene(res=(48, 32), spp=8):
     s5 = M.displaced_sphere(16, 32, radius=0.4, center=(0.9, -0.8, -1.4), displace=False)
     s5.bsdf = sd.add_roughdielectric(alpha=0.15, alpha_v=0.05, sample_visible=False, specular_transmittance=[0.9, 0.95, 1.0])
     sd.add_mesh(s5)
+    s6 = M.displaced_sphere(16, 32, radius=0.4, center=(1.9, -0.8, -1.2), displace=False)
+    s6.bsdf = sd.add_roughplastic([0.5, 0.3, 0.2], alpha=0.1, nonlinear=True)
+    sd.add_mesh(s6)
     leaf = M.quad([-2.4, -1.1, 0.8], [-1.0, -1.1, 0.8], [-1.0, 0.4, 0.8], [-2.4, 0.4, 0.8])       # `mask` over a two-sided diffuse BRDF
     yy, xx = np.mgrid[0:16, 0:16]
     leaf.bsdf = sd.add_mask(sd.make_two_sided(sd.add_diffuse([0.1, 0.8, 0.1])), (((xx // 2 + yy // 2) % 2) * 0.8 + 0.1).astype(np.float32))

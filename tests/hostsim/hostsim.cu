@@ -166,6 +166,15 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         bd.alpha_u = b.alpha_u; bd.alpha_v = b.alpha_v; bd.distr = b.distribution; bd.sample_visible = b.sample_visible; bd.eta_f = b.eta; bd.two_sided = b.two_sided ? 1 : 0;
         bd.nonlinear = b.nonlinear; bd.spec_weight = b.specular_sampling_weight; bd.opacity = b.opacity_tex_plus1 - 1;
         if (b.type >= MTSB_BSDF_CONDUCTOR || bd.opacity >= 0) s->ext = true;
+        if (b.type == MTSB_BSDF_ROUGHPLASTIC) {      // k_rough_tables + the host reduction of mtsb_scene_create
+            std::vector<float> n32, w32, n128, w128; gauss_legendre_rule(32, n32, w32); gauss_legendre_rule(128, n128, w128);
+            s->tables.emplace_back(2 * kRoughTransRes);
+            std::vector<float> &tab = s->tables.back();
+            for (int k = 0; k < 2 * kRoughTransRes; ++k) { bool tr = k < kRoughTransRes; float e = tr ? b.eta : 1.f / b.eta; int res = rough_table_res(e);
+                tab[k] = rough_boundary_integral(b.distribution, b.alpha_u, e, rough_table_mu(k % kRoughTransRes), res == 32 ? n32.data() : n128.data(), res == 32 ? w32.data() : w128.data(), res, tr); }
+            double acc = 0; for (int k = 0; k < kRoughTransRes; ++k) acc += (double) tab[kRoughTransRes + k] * rough_table_mu(k);
+            bd.rough_t = tab.data(); bd.internal_refl = (float) (acc / kRoughTransRes) * 2.f;
+        }
         s->bsdfs.push_back(bd);
     }
     hs_build_bvh(s);

@@ -39,6 +39,23 @@ def main():
             sc.render_grad(dl, spp=64, seed=i, tex_id=tex, mesh_id=mid)
             if i >= 2:
                 print({k: round(sc.last_stats[k], 3) for k in ("ms_total", "ms_closest", "ms_shade", "ms_any")})
+    elif what == "update_time":    # cost of one parameter update of the C4 sphere (vertex upload, normals, BVH rebuild) + a small render
+        import time
+        import torch
+        sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=256, spp=32)
+        mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
+        sc = mi.Scene(sd, device=0)
+        P = torch.from_numpy(np.asarray(sd.meshes[mid].positions, np.float32).copy()).cuda()
+        dl = torch.randn(256 * 256 * 3, device="cuda:0")
+        for name, fn in (("update_vertices(device tensor)", lambda: sc.update_vertices(mid, P)),
+                         ("render 256^2 x 32", lambda: sc.render(spp=32, seed=1)),
+                         ("render_grad vertices 256^2 x 32", lambda: sc.render_grad(dl, spp=32, seed=1, mesh_id=mid))):
+            fn(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            print(f"{name}: {(time.perf_counter() - t0) / 5 * 1e3:.2f} ms")
     elif what == "spectral":
         sd = scenes.c3_scene()
         sd.mode = "spectral"
