@@ -255,7 +255,10 @@ __device__ __forceinline__ bool shade_index(const ShadeBins &bins, uint32_t t, u
 // M = Rgb (3 channels) or Spectral (4 wavelengths; the spectral instance needs more registers, so it is not held to
 // the rgb kernel's occupancy target)
 template <typename M>
-__global__ void __launch_bounds__(kBlock, M::spectral ? 4 : kShadeBlocksPerSM)
+#ifndef MTSB_SPECTRAL_BLOCKS
+#define MTSB_SPECTRAL_BLOCKS 5      // measured on C3 spectral: 4 -> 22.1 ms, 5 -> 21.4 ms, 6 -> 22.8 ms (spills)
+#endif
+__global__ void __launch_bounds__(kBlock, M::spectral ? MTSB_SPECTRAL_BLOCKS : kShadeBlocksPerSM)
 k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue sq, uint32_t *counters,
         unsigned long long *stats, uint32_t depth, ShadeBins bins) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x, i = 0;
