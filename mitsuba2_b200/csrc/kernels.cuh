@@ -100,7 +100,7 @@ constexpr uint32_t kFetchChunk = 64;
 #endif
 constexpr int kTraceBlocksPerSM = MTSB_TRACE_BLOCKS;
 #ifndef MTSB_SHADE_BLOCKS
-#define MTSB_SHADE_BLOCKS 10
+#define MTSB_SHADE_BLOCKS 8      // re-measured at the end of round 1 (ms of shade per C3 step): 6: 12.81, 7: 12.43, 8: 12.31, 9: 12.40, 10: 12.52, 12: 12.69
 #endif
 constexpr int kShadeBlocksPerSM = MTSB_SHADE_BLOCKS;      // resident 128-thread blocks the shade kernel is compiled for
 template <bool AnyHit, typename Sink>
