@@ -23,7 +23,7 @@
 //   Every edge is a candidate, so shading discontinuities of flat-shaded meshes are covered as well as silhouettes.
 // * Boundary term seen from the first path vertex (edge2_* bodies, end of this file): silhouette edges as seen from x1.
 // Not covered (documented in DESIGN.md): visibility changes seen from the second and later vertices, paths beyond a delta
-// (dielectric) vertex, texture-coordinate sliding at x1, mesh-mesh intersections, emitter meshes.
+// (dielectric) vertex, mesh-mesh intersections, emitter meshes.
 #pragma once
 #include "path.h"
 
@@ -164,6 +164,25 @@ template <typename Add> HD void scatter_normal(const GradCtx &g, const TriGeo &t
     add_vertex(g, t.i1, ge1, add); add_vertex(g, t.i2, ge2, add); add_vertex(g, t.i0, -(ge1 + ge2), add);
 }
 
+// value and uv-gradient of a bitmap texture lookup (tex_eval_rgb in shade.h: repeat, bilinear); false for other textures
+HD bool tex_grad_rgb(const SceneDev &sc, int id, float u, float v, float3 &a, float3 &da_du, float3 &da_dv) {
+    const TexDev &t = sc.tex[id];
+    if (t.type != 1) return false;
+    float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];
+    tu -= floorf(tu); tv -= floorf(tv);
+    tu *= (float) (t.w - 1); tv *= (float) (t.h - 1);
+    uint32_t px = min((uint32_t) tu, t.w - 2), py = min((uint32_t) tv, t.h - 2);
+    float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    uint32_t i = px + py * t.w;
+    float3 v00, v10, v01, v11;
+    if (t.ch == 1) { v00 = mk3(t.data[i]); v10 = mk3(t.data[i + 1]); v01 = mk3(t.data[i + t.w]); v11 = mk3(t.data[i + t.w + 1]); }
+    else { v00 = ld3(t.data, i); v10 = ld3(t.data, i + 1); v01 = ld3(t.data, i + t.w); v11 = ld3(t.data, i + t.w + 1); }
+    a = (v00 * w0x + v10 * w1x) * w0y + (v01 * w0x + v11 * w1x) * w1y;
+    float3 dx = ((v10 - v00) * w0y + (v11 - v01) * w1y) * (float) (t.w - 1), dy = ((v01 - v00) * w0x + (v11 - v10) * w1x) * (float) (t.h - 1);
+    da_du = dx * t.to_uv[0] + dy * t.to_uv[3]; da_dv = dx * t.to_uv[1] + dy * t.to_uv[4];
+    return true;
+}
+
 // ---- one local factor S = f_s(A, B, C) * G~(B, C) --------------------------------------------------------------------
 enum { kEndSurface = 0, kEndDirection = 1, kEndFixedArea = 2, kEndFixedPoint = 3 };
 // A = previous vertex (position xA; recA.prim ~0: camera), B = the vertex whose BSDF is used (siB reconstructed by
@@ -221,16 +240,29 @@ HD void vertex_triple(const SceneDev &sc, const GradCtx &g, float3 xA, VtxRec re
         float3 g_ng = g_n * dot(ng, n) - n * dot(g_n, ng);
         scatter_normal(g, tB, (g_ng - ng * dot(ng, g_ng)) / lN, add);
     }
-    if (B_primary && tB.mesh == g.mesh_id && sc.meshes[tB.mesh].has_normals && lN > 0.f) {
-        // x1 slides over the triangle when the vertices move under a fixed camera ray, so the INTERPOLATED normal
-        // changes through the barycentrics: r = dt d - u (in-plane), db1 = r . (e2 x N)/|N|^2, db2 = r . (N x e1)/|N|^2
-        float3 n0 = ld3(sc.nrm, tB.i0), n1 = ld3(sc.nrm, tB.i1), n2 = ld3(sc.nrm, tB.i2);
-        float b0 = 1.f - recB.b1 - recB.b2;
-        float L = norm(n0 * b0 + n1 * recB.b1 + n2 * recB.b2);
+    if (B_primary && tB.mesh == g.mesh_id && lN > 0.f && (sc.meshes[tB.mesh].has_normals || sc.meshes[tB.mesh].has_uv)) {
+        // x1 slides over the triangle when the vertices move under a fixed camera ray: r = dt d - u (in-plane),
+        // db1 = r . (e2 x N)/|N|^2, db2 = r . (N x e1)/|N|^2.  Through the barycentrics this changes the INTERPOLATED normal
+        // and the texture coordinates (a bitmap reflectance slides under the pixel).
+        float b0 = 1.f - recB.b1 - recB.b2, gb1 = 0.f, gb2 = 0.f;
+        if (sc.meshes[tB.mesh].has_normals) {
+            float3 n0 = ld3(sc.nrm, tB.i0), n1 = ld3(sc.nrm, tB.i1), n2 = ld3(sc.nrm, tB.i2);
+            float L = norm(n0 * b0 + n1 * recB.b1 + n2 * recB.b2);
+            if (L > 0.f) { float3 gm = (g_n - n * dot(n, g_n)) / L; gb1 += dot(gm, n1 - n0); gb2 += dot(gm, n2 - n0); }
+        }
+        int tid = bsdf.type == 0 ? bsdf.refl : (bsdf.type == 1 ? bsdf.spec_r : -1);
+        if (sc.meshes[tB.mesh].has_uv && tid >= 0) {
+            float3 a, da_du, da_dv;
+            if (tex_grad_rgb(sc, tid, siB.u, siB.v, a, da_du, da_dv)) {      // f_c is proportional to the texel mix a_c: dlog f_c = da_c / a_c
+                float3 ga = mk3(a.x > 1e-8f ? w.x / a.x : 0.f, a.y > 1e-8f ? w.y / a.y : 0.f, a.z > 1e-8f ? w.z / a.z : 0.f);
+                float gu_ = dot(ga, da_du), gv_ = dot(ga, da_dv);
+                float u0 = sc.uv[2 * tB.i0], v0 = sc.uv[2 * tB.i0 + 1];
+                gb1 += gu_ * (sc.uv[2 * tB.i1] - u0) + gv_ * (sc.uv[2 * tB.i1 + 1] - v0);
+                gb2 += gu_ * (sc.uv[2 * tB.i2] - u0) + gv_ * (sc.uv[2 * tB.i2 + 1] - v0);
+            }
+        }
         float3 d = siB.p - g.cam_o; float nd = dot(tB.N, d);
-        if (L > 0.f && fabsf(nd) > 1e-20f) {
-            float3 gm = (g_n - n * dot(n, g_n)) / L;
-            float gb1 = dot(gm, n1 - n0), gb2 = dot(gm, n2 - n0);
+        if ((gb1 != 0.f || gb2 != 0.f) && fabsf(nd) > 1e-20f) {
             float3 gr = (cross(tB.e2, tB.N) * gb1 + cross(tB.N, tB.e1) * gb2) / (lN * lN);
             float3 gu = tB.N * (dot(d, gr) / nd) - gr;
             add_vertex(g, tB.i0, gu * b0, add); add_vertex(g, tB.i1, gu * recB.b1, add); add_vertex(g, tB.i2, gu * recB.b2, add);

@@ -655,6 +655,13 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         P[:, 2] += 0.15 * np.sin(2.0 * P[:, 0]) * np.cos(1.5 * P[:, 1])
         sd.add_mesh(Mesh(P, F, normals=M.compute_vertex_normals(P, F).astype(np.float32), bsdf=b))
         sd.add_point([500.0, 1000.0, -1000.0], [8e6, 8e6, 8e6])
+    if kind == "texplane":  # a plane with a bitmap reflectance filling the view: in-plane motion slides the texture under the pixels
+        P, F = grid_mesh(4, 4, 8.0, [0, 0, 1.0], [1, 0, 0], [0, -1, 0])
+        uvs = ((P[:, :2] + 4.0) / 8.0).astype(np.float32)
+        yy, xx = np.mgrid[0:12, 0:12]
+        img = np.stack([0.5 + 0.4 * np.sin(0.9 * xx + 0.3 * yy), 0.5 + 0.4 * np.cos(0.5 * yy), 0.3 + 0.02 * xx], -1).astype(np.float32)
+        sd.add_mesh(Mesh(P, F, texcoords=uvs, bsdf=sd.add_diffuse(sd.add_texture_bitmap(img))))
+        sd.add_point([0.5, 1.0, -1.0], [8, 8, 8])
     if kind == "quadshadow":      # quad above a lit plane under a constant sky: its shadow on the plane moves with it
         P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P, F, bsdf=b))
@@ -666,7 +673,7 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         sd.add_mesh(Mesh(P, F, bsdf=b))
         sd.add_constant([1.0, 1.0, 1.0])
     sd.add_perspective(look_at([0, 0, -3.0], [0, 0, 0], [0, 1, 0]), 40.0, 0.01, 100.0, res, res, "box")
-    sd.max_depth, sd.rr_depth, sd.spp = (2 if kind == "wavy" else 4), 100, spp
+    sd.max_depth, sd.rr_depth, sd.spp = (2 if kind in ("wavy", "texplane") else 4), 100, spp
     return sd
 
 

@@ -165,3 +165,18 @@ def test_vertex_gradient_sample_ranges_add_up():
     parts = h.render_grad_vertices(wgt, 0, seed=2, spp=2, spp_begin=0, spp_total=6, boundary=2, edge_fraction=0.5) + \
         h.render_grad_vertices(wgt, 0, seed=2, spp=4, spp_begin=2, spp_total=6, boundary=2, edge_fraction=0.5)
     assert np.allclose(full, parts, rtol=1e-4, atol=1e-5 * np.abs(full).max())
+
+
+def test_vertex_gradient_texture_sliding_matches_fd():
+    """A bitmap-textured plane: moving it in its own plane slides the texture under the fixed pixels (the barycentrics of
+    x1 change -> the interpolated uv changes -> the texel mix changes).  Direct light only; FD of the oracle, 2 %."""
+    sd = H.vgrad_scene("texplane", "diffuse", res=16, spp=8)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    g = HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=False).reshape(-1, 3)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 1e-3, 8, 3) for n in ("tx", "ty", "tz", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    assert abs(fds["tx"]) > 0.02 * ref and abs(fds["ty"]) > 0.02 * ref              # the sliding term is not negligible here
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < 0.02 * ref, (n, float((g * F[n]).sum()), fd)
