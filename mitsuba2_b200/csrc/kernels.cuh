@@ -94,7 +94,10 @@ __global__ void k_rough_tables(int distr_type, float alpha, float eta, const flo
 // every warp claims chunks of kFetchChunk consecutive rays from a global work counter and hands them to lanes whose
 // previous ray has finished as soon as fewer than `refill` lanes are still traversing, so short rays do not leave
 // lanes idle until the longest ray of the warp is done.  `Sink` consumes a finished ray.
-constexpr uint32_t kFetchChunk = 64;
+#ifndef MTSB_FETCH_CHUNK
+#define MTSB_FETCH_CHUNK 64
+#endif
+constexpr uint32_t kFetchChunk = MTSB_FETCH_CHUNK;
 #ifndef MTSB_TRACE_BLOCKS
 #define MTSB_TRACE_BLOCKS 7
 #endif
