@@ -302,6 +302,8 @@ k_shade(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQueue s
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x, i = 0;
     uint32_t count = counters[depth];
     if (t == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
+    // the grid is sized for the batch; at depth d only the live entries (padded per class) have work: whole blocks leave
+    if (blockIdx.x * blockDim.x >= count + 32u * kShadeClasses) return;
     bool live = shade_index(bins, t, i);
     ShadeOut out; out.extend = false; out.shadow = false;
     if (live) out = shade_body<M>(sc, qin, b, i);
@@ -325,6 +327,7 @@ k_shade_grad(SceneDev sc, RenderBatch b, PathQueue qin, PathQueue qout, ShadowQu
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t count = counters[depth];
     if (i == 0) { atomicAdd(&stats[0], (unsigned long long) count); atomicAdd(&stats[2], (unsigned long long) count); }
+    if (blockIdx.x * blockDim.x >= count) return;          // whole block beyond the live entries
     bool live = i < count;
     ShadeOut out; out.extend = false; out.shadow = false;
     if (live) { ReplayGrad<DevAdd, Vtx> rg; rg.g = g; out = shade_body<M>(sc, qin, b, i, rg); }
