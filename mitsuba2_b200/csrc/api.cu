@@ -376,7 +376,12 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             else for (uint32_t k = 1; k < t.width; ++k) CHECK_ARG(t.data[k] > t.data[k - 1]);     // IrregularContinuousDistribution: nodes strictly increasing
             td.w = t.width; td.lambda_min = t.lambda_min; td.lambda_max = t.lambda_max;
             s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1;
-            CU(s->tables[ti]->upload(t.data, (size_t) t.width * (t.type == MTSB_TEX_IRREGULAR ? 2 : 1), st));
+            if (t.type == MTSB_TEX_IRREGULAR) {       // nodes, values + the bucket index of host_tables.h
+                std::vector<float> packed = irregular_with_buckets(t.data, t.width);
+                td.h = kIrregularBuckets;
+                CU(s->tables[ti]->upload(packed.data(), packed.size(), st));
+                CU(cudaStreamSynchronize(st));
+            } else CU(s->tables[ti]->upload(t.data, (size_t) t.width, st));
             CU(cudaStreamSynchronize(st));
             td.data = s->tables[ti]->p;
         } else if (t.type == MTSB_TEX_UNIFORM) {

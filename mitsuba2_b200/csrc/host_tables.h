@@ -138,3 +138,22 @@ inline void gauss_legendre_rule(int n, std::vector<float> &nodes, std::vector<fl
     if (n % 2 == 1) nodes[n / 2] = 0.f;
 }
 
+// `irregular` spectrum = nodes then values; appended here: a uniform bucket index over [node_0, node_last] so that the device
+// finds the interval of a wavelength in ~2 steps instead of a 6-step binary search (same interval, same result).
+// Layout after the 2 w floats: nb start indices (as floats), then the scale nb / (node_last - node_0).  Bucket j stores the
+// last node strictly below the lower bound of bucket j - 1 (one bucket of slack against rounding of the bucket number).
+constexpr uint32_t kIrregularBuckets = 64;
+inline std::vector<float> irregular_with_buckets(const float *data, uint32_t w) {
+    std::vector<float> out(data, data + 2 * (size_t) w);
+    const uint32_t nb = kIrregularBuckets;
+    double lo = data[0], width = ((double) data[w - 1] - lo) / nb;
+    for (uint32_t j = 0; j < nb; ++j) {
+        double bound = lo + width * (j > 0 ? j - 1 : 0);
+        uint32_t idx = 0;
+        while (idx + 2 < w && (double) data[idx + 1] < bound) ++idx;
+        out.push_back((float) idx);
+    }
+    out.push_back((float) (nb / ((double) data[w - 1] - lo)));
+    return out;
+}
+

@@ -87,7 +87,7 @@ float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wa
     if (t.type == 0) r = srgb_model_eval(t.value, wav);
     else if (t.type == 2) { float inv = (float) (t.w - 1) / (t.lambda_max - t.lambda_min);
         r = map_spec(wav, [&](float l) { return regular_eval1(t.data, t.w, t.lambda_min, t.lambda_max, inv, l); }); }
-    else if (t.type == 3) r = map_spec(wav, [&](float l) { return irregular_eval1(t.data, t.data + t.w, t.w, l); });
+    else if (t.type == 3) r = map_spec(wav, [&](float l) { return irregular_eval1(t.data, t.data + t.w, t.w, l, t.data + 2 * t.w, t.h); });
     else if (t.type == 4) r = mk4(t.value.x);
     else {
         float tu = t.to_uv[0] * u + t.to_uv[1] * v + t.to_uv[2], tv = t.to_uv[3] * u + t.to_uv[4] * v + t.to_uv[5];

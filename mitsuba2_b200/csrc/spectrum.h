@@ -58,15 +58,24 @@ HD float regular_eval1(const float *values, uint32_t n, float lo, float hi, floa
     float w1 = x - (float) idx, w0 = 1.f - w1;
     return fmaf(w0, values[idx], w1 * values[idx + 1]);
 }
-HD float irregular_eval1(const float *nodes, const float *values, uint32_t n, float x) {
+// buckets (optional, host_tables.h): nb start indices + scale after the values; the interval found is the one the reference's
+// binary search finds (first node >= x, minus one), so the value is identical
+HD float irregular_eval1(const float *nodes, const float *values, uint32_t n, float x, const float *buckets = nullptr, uint32_t nb = 0) {
     if (!(x >= nodes[0] && x <= nodes[n - 1])) return 0.f;
-    uint32_t start = 0, end = n;                                   // enoki::binary_search (array_utils.h:153-171)
-    uint32_t it = (uint32_t) (31 - clz32(n)) + 1u;
-    for (uint32_t i = 0; i < it; ++i) {
-        uint32_t mid = (start + end) >> 1;
-        if (nodes[min(mid, n - 1)] < x && mid < n) start = min(mid + 1, end); else end = mid;
+    uint32_t idx;
+    if (nb != 0) {
+        uint32_t j = min((uint32_t) ((x - nodes[0]) * buckets[nb]), nb - 1u);
+        idx = (uint32_t) buckets[j];
+        while (idx + 2 < n && nodes[idx + 1] < x) ++idx;
+    } else {
+        uint32_t start = 0, end = n;                               // enoki::binary_search (array_utils.h:153-171)
+        uint32_t it = (uint32_t) (31 - clz32(n)) + 1u;
+        for (uint32_t i = 0; i < it; ++i) {
+            uint32_t mid = (start + end) >> 1;
+            if (nodes[min(mid, n - 1)] < x && mid < n) start = min(mid + 1, end); else end = mid;
+        }
+        idx = max(min(start, n - 1), 1u) - 1u;
     }
-    uint32_t idx = max(min(start, n - 1), 1u) - 1u;
     float x0 = nodes[idx], x1 = nodes[idx + 1], y0 = values[idx], y1 = values[idx + 1];
     x = (x - x0) / (x1 - x0);
     return fmaf(x, y1 - y0, y0);

@@ -156,7 +156,9 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         if (t.type == MTSB_TEX_BITMAP) { td.w = t.width; td.h = t.height; td.ch = t.channels; memcpy(td.to_uv, t.to_uv, sizeof(td.to_uv));
             s->tables.emplace_back(t.data, t.data + (size_t) t.width * t.height * t.channels); td.data = s->tables.back().data(); }
         if (t.type == MTSB_TEX_REGULAR || t.type == MTSB_TEX_IRREGULAR) { td.w = t.width; td.lambda_min = t.lambda_min; td.lambda_max = t.lambda_max;
-            s->tables.emplace_back(t.data, t.data + (size_t) t.width * (t.type == MTSB_TEX_IRREGULAR ? 2 : 1)); td.data = s->tables.back().data(); }
+            if (t.type == MTSB_TEX_IRREGULAR) { s->tables.emplace_back(irregular_with_buckets(t.data, t.width)); td.h = kIrregularBuckets; }
+            else s->tables.emplace_back(t.data, t.data + (size_t) t.width);
+            td.data = s->tables.back().data(); }
         td.d65_scale = t.d65_scale;
         s->tex.push_back(td);
     }
