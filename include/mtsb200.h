@@ -202,6 +202,18 @@ int mtsb_intersect_any(mtsb_scene *scene, uint64_t n, const float *o_mint, const
 /* brute-force variant of the above = `Scene::ray_intersect_naive` (scene.cpp:118-129); test hook */
 int mtsb_intersect_naive(mtsb_scene *scene, uint64_t n, const float *o_mint, const float *d_maxt,
                          float *hits, int mem);
+/* Allocation-free variant of mtsb_intersect_closest.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernel, same results (bit-identical hits), but the call performs no cudaMalloc / cudaFree /
+ * allocating library call: the traversal's work counter and -- for MTSB_MEM_HOST callers -- the staging copies of rays
+ * and hits live in one fixed file-scope device array (12 MiB + 256 B per GPU, held from library load until exit).
+ * Limit: n <= mtsb_noalloc_max_rays() = 262144 rays per call; larger n fails with MTSB_E_INVALID and a message (no
+ * fallback to the allocating path).  The array is shared by every context and scene on the device and keeps the last
+ * call's contents (the work counter is cleared at the start of every call): calls that overlap on one GPU race.
+ * With MTSB_MEM_DEVICE the caller's buffers are used directly and only the 256-byte counter block is touched. */
+int mtsb_intersect_closest_noalloc(mtsb_scene *scene, uint64_t n, const float *o_mint, const float *d_maxt,
+                                   float *hits, int mem, mtsb_stats *stats);
+uint64_t mtsb_noalloc_max_rays(void);
 
 /* `SamplingIntegrator::render` (src/librender/integrator.cpp:52-176), GPU branch semantics (:144-169):
  * renders samples [spp_begin, spp_begin+spp_count) of every pixel of sensor `sensor_id`, sample s of pixel p

@@ -94,6 +94,8 @@ SYMBOLS = [
     ("mtsb_intersect_closest", C.c_int, [vp, C.c_uint64, vp, vp, vp, C.c_int, C.POINTER(Stats)]),
     ("mtsb_intersect_any", C.c_int, [vp, C.c_uint64, vp, vp, vp, C.c_int, C.POINTER(Stats)]),
     ("mtsb_intersect_naive", C.c_int, [vp, C.c_uint64, vp, vp, vp, C.c_int]),
+    ("mtsb_intersect_closest_noalloc", C.c_int, [vp, C.c_uint64, vp, vp, vp, C.c_int, C.POINTER(Stats)]),
+    ("mtsb_noalloc_max_rays", C.c_uint64, []),
     ("mtsb_render", C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(Stats)]),
     ("mtsb_film_clear", C.c_int, [vp, C.c_uint32]),
     ("mtsb_film_read", C.c_int, [vp, C.c_uint32, vp, C.c_int]),

@@ -906,6 +906,73 @@ extern "C" int mtsb_sample_emitter_direction(mtsb_scene *s, uint64_t n, const fl
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Allocation-free closest-hit entry point (mtsb_intersect_closest_noalloc).  No counterpart in the reference: added
+// for callers that must not call cudaMalloc (CUDA graph capture, tight serving
+// loops).  It runs the same k_trace<false> as mtsb_intersect_closest; everything that kernel and the host-pointer
+// staging need beyond the caller's buffers lives in ONE file-scope device array, so the call makes no cudaMalloc /
+// cudaFree / allocating library call.
+//   layout of g_noalloc_scratch: [0, 256) the dynamic-fetch work counter of the persistent traversal (one uint32, must be
+//   zero at launch: cleared by cudaMemsetAsync on the context's stream in every call); then, used for MTSB_MEM_HOST
+//   callers only, o_mint | d_maxt | hits, kNoAllocMaxRays float4 each.
+// Every context and scene of one device shares the array and it keeps the last call's contents: two calls that overlap
+// on the GPU (different contexts / streams on one device, or different host threads) race on it.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint64_t kNoAllocMaxRays = 1ull << 18;                      // 262 144 rays per call
+constexpr size_t kNoAllocHeader = 256;
+constexpr size_t kNoAllocBytes = kNoAllocHeader + 3 * kNoAllocMaxRays * sizeof(float4);      // 12 MiB + 256 B per device
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+// In host code `g_noalloc_scratch` is only a handle of the symbol, not a device address: resolve it once per device, with
+// that device current, and hand the resolved pointer to the kernel / copies.
+constexpr int kNoAllocMaxDevices = 64;
+static unsigned char *g_noalloc_ptr[kNoAllocMaxDevices];             // zero-initialised: not resolved yet
+static int noalloc_scratch(int device, unsigned char **out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(MTSB_E_INVALID, "mtsb_intersect_closest_noalloc: device index beyond the scratch table");
+    if (g_noalloc_ptr[device] == nullptr) {
+        CU(cudaSetDevice(device));
+        void *p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (p == nullptr) return fail(MTSB_E_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[device] = (unsigned char *) p;
+    }
+    *out = g_noalloc_ptr[device];
+    return MTSB_OK;
+}
+extern "C" uint64_t mtsb_noalloc_max_rays(void) { return kNoAllocMaxRays; }
+extern "C" int mtsb_intersect_closest_noalloc(mtsb_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, float *hits,
+                                              int mem, mtsb_stats *stats) {
+    CHECK_ARG(s && (n == 0 || (o_mint && d_maxt && hits)) && (mem == MTSB_MEM_HOST || mem == MTSB_MEM_DEVICE));
+    if (n > kNoAllocMaxRays)
+        return fail(MTSB_E_INVALID, "mtsb_intersect_closest_noalloc: " + std::to_string(n) + " rays exceed the fixed scratch capacity of " +
+                                    std::to_string(kNoAllocMaxRays) + " rays per call; split the batch or use mtsb_intersect_closest");
+    CU(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n == 0) return MTSB_OK;
+    unsigned char *scratch = nullptr;
+    RC(noalloc_scratch(s->ctx->device, &scratch));
+    uint32_t *work = (uint32_t *) scratch;
+    const float4 *d_o = (const float4 *) o_mint, *d_d = (const float4 *) d_maxt; float4 *d_h = (float4 *) hits;
+    if (mem == MTSB_MEM_HOST) {        // stage through the fixed array (plain copies; nothing is allocated)
+        float4 *so = (float4 *) (scratch + kNoAllocHeader), *sd = so + kNoAllocMaxRays, *sh = sd + kNoAllocMaxRays;
+        CU(cudaMemcpyAsync(so, o_mint, n * sizeof(float4), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(sd, d_maxt, n * sizeof(float4), cudaMemcpyHostToDevice, st));
+        d_o = so; d_d = sd; d_h = sh;
+    }
+    CU(cudaMemsetAsync(work, 0, kNoAllocHeader, st));          // the fetch cursor must start at zero; the previous call left it at >= its n
+    CU(cudaEventRecord(s->ctx->ev0, st));
+    k_trace<false><<<trace_grid_for(s->ctx, n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, d_o, d_d, d_h, nullptr, work, s->ctx->refill, nullptr);
+    CU(cudaEventRecord(s->ctx->ev1, st));
+    CU(cudaGetLastError());
+    if (mem == MTSB_MEM_HOST) CU(cudaMemcpyAsync(hits, d_h, n * sizeof(float4), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (stats) {
+        CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
+        stats->kernel_launches = 1; stats->closest_rays = n; stats->ms_closest = stats->ms_total;
+    }
+    return MTSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Gradient pass (implemented in grad.cuh)
 // ---------------------------------------------------------------------------------------------------
 #include "grad.cuh"
