@@ -160,6 +160,7 @@ class SceneData:
             spd = CONDUCTORS_SPD.get(name)
             eta_id = self.add_texture_rgb(CONDUCTORS_RGB[name][0])
             k_id = self.add_texture_rgb(CONDUCTORS_RGB[name][1])
+            self.textures[eta_id]["material"] = self.textures[k_id]["material"] = material      # kept for export.py
             if spd is not None:      # spectral alternative of the same two textures
                 self.textures[eta_id]["spectrum"] = (spd["wavelengths"], spd["eta"])
                 self.textures[k_id]["spectrum"] = (spd["wavelengths"], spd["k"])

@@ -693,3 +693,80 @@ def oracle_fd_vertices(sd, mesh_id, wgt, D, eps, spp, seed):
         orc.update_vertices(mesh_id, (P0 + sgn * eps * D).astype(np.float32))
         vals.append(float((orc.render(spp=spp, seed=seed).astype(np.float64) * wgt).sum()))
     return (vals[0] - vals[1]) / (2 * eps)
+
+
+# ---- the reference itself (oracle/_ref/mitsuba, built by oracle/build_reference.sh; test infrastructure) -----------------
+class RefBuild:
+    """The UNMODIFIED reference built from /root/reference: `dist/mitsuba` (CLI, scalar_rgb / scalar_spectral) and
+    `ref_query` (oracle/ref_query.cpp linked against its libraries).  `available()` is False where it was not built."""
+    DIR = os.path.join(ROOT, "oracle", "_ref", "mitsuba")
+    DIST = os.path.join(DIR, "dist")
+    CLI = os.path.join(DIST, "mitsuba")
+    QUERY = os.path.join(DIR, "ref_query")
+
+    @classmethod
+    def available(cls, query=False):
+        return os.path.exists(cls.CLI) and (not query or os.path.exists(cls.QUERY))
+
+    @classmethod
+    def _env(cls):
+        return dict(os.environ, LD_LIBRARY_PATH=cls.DIST + os.pathsep + os.environ.get("LD_LIBRARY_PATH", ""))
+
+    def __init__(self, sd, directory=None, spp=None):
+        import tempfile
+        from mitsuba2_b200 import export
+        self.sd = sd
+        self._tmp = None
+        if directory is None:
+            self._tmp = tempfile.TemporaryDirectory(prefix="mtsref_")
+            directory = self._tmp.name
+        self.dir = directory
+        self.xml = export.write_mitsuba_scene(sd, directory, spp=spp)
+
+    def render(self, spp, threads=None, variant="scalar_rgb", timeout=3600):
+        """`mitsuba -m variant -t threads` -> (developed linear RGB image (H,W,3), seconds of the "Rendering finished"
+        line = src/librender/integrator.cpp:171-173)."""
+        import re
+        import subprocess
+        from mitsuba2_b200 import export, imageio
+        export.write_mitsuba_scene(self.sd, self.dir, spp=spp)
+        out = os.path.join(self.dir, "out.pfm")
+        r = subprocess.run([self.CLI, "-m", variant, "-t", str(threads or os.cpu_count() or 1), "-o", out, self.xml],
+                           env=self._env(), capture_output=True, text=True, timeout=timeout)
+        if r.returncode != 0:
+            raise RuntimeError("reference mitsuba failed: " + (r.stdout + r.stderr)[-2000:])
+        m = re.search(r"Rendering finished\. \(took ([0-9.]+)(ms|s|m|h)\)", r.stdout + r.stderr)
+        secs = float(m.group(1)) * {"ms": 1e-3, "s": 1.0, "m": 60.0, "h": 3600.0}[m.group(2)] if m else float("nan")
+        return imageio.read_pfm(out), secs
+
+    def _query(self, cmd, arr, width_out, threads=1, arg=0, timeout=3600):
+        import subprocess
+        fin, fout = os.path.join(self.dir, f"q_{cmd}_in.bin"), os.path.join(self.dir, f"q_{cmd}_out.bin")
+        np.ascontiguousarray(arr, np.float32).tofile(fin)
+        r = subprocess.run([self.QUERY, self.xml, cmd, fin, fout, str(threads), str(arg)], env=self._env(), capture_output=True,
+                           text=True, timeout=timeout)
+        if r.returncode != 0:
+            raise RuntimeError("ref_query failed: " + (r.stdout + r.stderr)[-2000:])
+        self.last_seconds = float(r.stdout.split("query_seconds")[1].split()[0])
+        return np.fromfile(fout, np.float32).reshape(-1, width_out)
+
+    def intersect(self, om, dm, naive=False, threads=None):
+        """-> (n,16): t, uv, global prim bits, p, n, sh_n, wi  (`Scene::ray_intersect[_naive]`)"""
+        rays = np.concatenate([_f32(om), _f32(dm)], axis=1)
+        return self._query("naive" if naive else "intersect", rays, 16, threads or os.cpu_count() or 1)
+
+    def ray_test(self, om, dm, threads=None):
+        rays = np.concatenate([_f32(om), _f32(dm)], axis=1)
+        return self._query("test", rays, 1, threads or os.cpu_count() or 1)[:, 0] > 0.5
+
+    def bsdf(self, shape, wi, uv, s1, s2, wo):
+        """-> (n,13): sample (wo, pdf, eta, weight rgb, delta), eval(wo) rgb, pdf(wo) of the BSDF of shape `shape`"""
+        q = np.concatenate([_f32(wi), _f32(uv), _f32(s1).reshape(-1, 1), _f32(s2), _f32(wo)], axis=1)
+        return self._query("bsdf", q, 13, 1, shape)
+
+    def sample_emitter_direction(self, ref_p, s2):
+        return self._query("emitter", np.concatenate([_f32(ref_p), _f32(s2)], axis=1), 11)
+
+    def sensor_sample_ray(self, pos, sensor=0):
+        r = self._query("sensor", _f32(pos), 8, 1, sensor)
+        return r[:, :4].copy(), r[:, 4:].copy()
