@@ -123,6 +123,16 @@ def parity_gates(mi, local):
     hit-id mismatch rate, image agreement at identical sample streams, gradient cosine vs finite differences."""
     import helpers as H
     g = {}
+    # at the sizes the numbers are quoted on (same functions as tests/test_gpu_bench_parity.py): C1 cbox 256^2 x 64 spp
+    # (vs the oracle, the committed reference-CLI render and a live reference render), C2 1M-triangle hit ids (vs the
+    # oracle and the reference kd-tree), C3 4.1M-triangle film crop (same streams + z-test vs the oracle)
+    try:
+        import test_gpu_bench_parity as BP
+        g["c1_cbox_256x256x64spp"] = BP.c1_parity(mi, local)
+        g["c2_1M_triangles"] = BP.c2_parity(mi, device=local)
+        g["c3_4M_triangles_crop"] = BP.c3_parity(mi, local, run_spp=32, gpu_runs=32, cpu_runs=8)
+    except Exception as e:
+        g["bench_size_error"] = repr(e)
     sd = H.sphere_scene(n_theta=128, n_phi=256)
     sc, orc = mi.Scene(sd, device=local), H.Oracle(sd)
     om, dm = H.random_rays(200000, 5, radius=1.5)
@@ -175,14 +185,19 @@ def parity_gates(mi, local):
     return g
 
 
-def ncu_traffic(kernel="k_trace<0>"):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu capture of this same
-    command (profiles/r1_kernel_traffic.json, made by profiles/README.md's recipe); None if absent."""
-    path = os.path.join(ROOT, "profiles", "r1_kernel_traffic.json")
-    try:
-        return float(json.load(open(path))[kernel]["dram_bytes_per_launch"])
-    except Exception:
-        return None
+def ncu_profile(kernel="k_trace<0>"):
+    """Per-launch ncu numbers of `kernel` from the committed capture of this same command (profiles/r2_kernel_profile.json,
+    recipe in profiles/README.md; falls back to the round-1 file): DRAM bytes per launch (`roofline.traffic`), thread
+    instructions per ray and active threads per instruction -- the two numbers that actually bound this kernel."""
+    for name in ("r2_kernel_profile.json", "r1_kernel_traffic.json"):
+        try:
+            d = json.load(open(os.path.join(ROOT, "profiles", name)))[kernel]
+            d = dict(d)
+            d["source"] = f"ncu per k_trace<closest> launch, profiles/{name}"
+            return d
+        except Exception:
+            continue
+    return {}
 
 
 def peaks():
@@ -226,52 +241,98 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+REF_SPP_PER_STEP = 2          # reference arm: one step = the full 1920x1080 film at 2 spp (4.1 M samples, ~2.5 s on 16 cores)
+
+
+def reference_render_seconds(sd, spp, reps, threads, workdir):
+    """Times `Integrator::render` of the UNMODIFIED reference (oracle/_ref/mitsuba, built by oracle/build_reference.sh) on
+    the exported scene: oracle/ref_query.cpp loads the XML once with the reference's loader and calls the scene's `path`
+    integrator `reps` times (src/librender/integrator.cpp:52-176; scene loading and kd-tree build are outside, like the
+    CLI's "Rendering finished" timer).  -> list of seconds per repetition, or None when the build is absent / fails."""
+    import helpers
+    if not helpers.RefBuild.available(query=True):
+        return None
+    try:
+        ref = helpers.RefBuild(sd, workdir, spp=spp)
+        r = subprocess.run([ref.QUERY, ref.xml, "render", "/dev/null", os.path.join(workdir, "render_out.bin"), str(threads), str(reps)],
+                           env=ref._env(), capture_output=True, text=True, timeout=3000)
+        import re
+        secs = [float(x) for x in re.findall(r"render_seconds ([0-9.]+)", r.stdout)]
+        return secs if r.returncode == 0 and len(secs) == reps else None
+    except Exception as e:      # e.g. a host CPU without the instruction set the reference was compiled for
+        print(f"[bench] reference build unusable here ({e!r}); falling back to the oracle port", file=sys.stderr)
+        return None
+
+
 def run_reference(args):
-    """Reference arm for this tier: the CPU restatement of the reference's path (oracle/), all host threads."""
+    """Reference arm: the reference's own CPU implementation of the path on this box's host cores -- the unmodified
+    `scalar_rgb` build (kind "reference") where oracle/_ref/mitsuba travelled with the repo, else the C oracle (kind "port")."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    import tempfile
     import helpers
     sd = build_scene(args.workload)
     cores = os.cpu_count() or 1
-    # bounded sample of the same workload: same scene and camera, 1/4-resolution film, 1 spp per step
     s = sd.sensors[0]
-    from mitsuba2_b200.scenedata import perspective_sample_to_camera
-    s["width"], s["height"] = max(16, s["width"] // 4), max(9, s["height"] // 4)
-    s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], s["width"] / s["height"]).reshape(16)
-    orc = helpers.Oracle(sd, threads=cores)
-    SPP = 8                                 # ~1.2 s of CPU work per step on 16 cores
-    samples = s["width"] * s["height"] * SPP
-    total = (args.warmup + args.steps) * SPP
-    for i in range(args.warmup):
-        orc.render_xyzaw(spp=SPP, seed=1, spp_begin=i * SPP, spp_total=total)
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        orc.render_xyzaw(spp=SPP, seed=1, spp_begin=(args.warmup + i) * SPP, spp_total=total)
-    dt = time.perf_counter() - t0
-    value = samples * args.steps / dt / 1e6
-    sample = f"{s['width']}x{s['height']} x {SPP} spp per step of the same scene/camera ({samples} samples/step)"
+    W, K = args.warmup, args.steps
+    with tempfile.TemporaryDirectory(prefix="mtsb_ref_") as tmp:
+        secs = reference_render_seconds(sd, REF_SPP_PER_STEP, W + K, cores, tmp)
+    if secs is not None:
+        samples = s["width"] * s["height"] * REF_SPP_PER_STEP
+        dt = sum(secs[W:])
+        kind = "reference"
+        sample = (f"full {s['width']}x{s['height']} film x {REF_SPP_PER_STEP} spp per step ({samples} samples/step), unmodified Mitsuba 2 "
+                  f"scalar_rgb `path` integrator (kd-tree), TBB on {cores} threads; Msamples/s does not depend on spp")
+    else:
+        # bounded sample of the same workload: same scene and camera, 1/4-resolution film
+        from mitsuba2_b200.scenedata import perspective_sample_to_camera
+        s["width"], s["height"] = max(16, s["width"] // 4), max(9, s["height"] // 4)
+        s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], s["width"] / s["height"]).reshape(16)
+        orc = helpers.Oracle(sd, threads=cores)
+        SPP = 8
+        samples = s["width"] * s["height"] * SPP
+        total = (W + K) * SPP
+        for i in range(W):
+            orc.render_xyzaw(spp=SPP, seed=1, spp_begin=i * SPP, spp_total=total)
+        t0 = time.perf_counter()
+        for i in range(K):
+            orc.render_xyzaw(spp=SPP, seed=1, spp_begin=(W + i) * SPP, spp_total=total)
+        dt = time.perf_counter() - t0
+        kind = "port"
+        sample = f"{s['width']}x{s['height']} x {SPP} spp per step of the same scene/camera ({samples} samples/step), C oracle (reference build absent)"
+    value = samples * K / dt / 1e6
     print(json.dumps({
         "impl": "reference", "metric": "path_tracing_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "steps": K, "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload]["desc"], "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
 
 def cpu_baseline(sd_full, budget_s=20.0):
-    """Oracle ("port" of the reference path) timed on this box's host cores on a bounded sample of the workload."""
+    """CPU baseline timed on this box's host cores on a bounded sample of the workload: the unmodified reference
+    (kind "reference": full film, 2 spp, 1 warm-up + 3 timed renders) where its build is present, else the oracle port."""
     import copy
+    import tempfile
     import helpers
     from mitsuba2_b200.scenedata import perspective_sample_to_camera
+    cores = os.cpu_count() or 1
+    s0 = sd_full.sensors[0]
+    with tempfile.TemporaryDirectory(prefix="mtsb_ref_") as tmp:
+        secs = reference_render_seconds(sd_full, REF_SPP_PER_STEP, 4, cores, tmp)
+    if secs is not None:
+        samples = s0["width"] * s0["height"] * REF_SPP_PER_STEP
+        return {"value": samples * 3 / sum(secs[1:]) / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "reference",
+                "sample": f"full {s0['width']}x{s0['height']} film x {REF_SPP_PER_STEP} spp, 3 renders after 1 warm-up ({3 * samples} samples, "
+                          f"{sum(secs[1:]):.1f} s), unmodified Mitsuba 2 scalar_rgb path integrator on {cores} TBB threads"}
     sd = copy.copy(sd_full)
     sd.sensors = [dict(sd_full.sensors[0])]
     s = sd.sensors[0]
     s["width"], s["height"] = max(16, s["width"] // 4), max(9, s["height"] // 4)
     s["sample_to_camera"] = perspective_sample_to_camera(s["fov_x"], s["near"], s["far"], s["width"] / s["height"]).reshape(16)
-    cores = os.cpu_count() or 1
     orc = helpers.Oracle(sd, threads=cores)
     orc.render_xyzaw(spp=1, seed=1, spp_begin=0, spp_total=64)          # warm-up
     n, t0 = 0, time.perf_counter()
@@ -283,7 +344,7 @@ def cpu_baseline(sd_full, budget_s=20.0):
     dt = time.perf_counter() - t0
     samples = s["width"] * s["height"] * n
     return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
-            "sample": f"{s['width']}x{s['height']} film of the same scene/camera, {n} spp ({samples} samples, {dt:.1f} s)"}
+            "sample": f"{s['width']}x{s['height']} film of the same scene/camera, {n} spp ({samples} samples, {dt:.1f} s), C oracle"}
 
 
 def main():
@@ -294,6 +355,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
     ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--strong-spp", type=int, default=256, help="fixed total spp of the strong-scaling side measurement (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-side-metrics", action="store_true", help="skip the C2 intersect / C4 gradient side measurements")
     args = ap.parse_args()
@@ -302,10 +364,13 @@ def main():
 
     import torch
     import mitsuba2_b200 as mi
+    from mitsuba2_b200 import distributed as D
+    A = mi._abi
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -320,76 +385,137 @@ def main():
     npix = s["width"] * s["height"]
     spp, W, K = args.spp_per_step, args.warmup, args.steps
     spp_total = (2 * (W + K) + 2) * world * spp
-    film_t = torch.empty(npix * 5, dtype=torch.float32, device=f"cuda:{local}")
+    film_t = [torch.empty(npix * 5, dtype=torch.float32, device=dev) for _ in range(2)]
+    ev = lambda: torch.cuda.Event(enable_timing=True)      # noqa: E731
 
-    def step(i, profile=False):
-        """one bench step on this rank: render this rank's sample range, then reduce the film over ranks."""
-        st = scene.render_accumulate(spp=spp, seed=1, spp_begin=(i * world + rank) * spp, spp_total=spp_total)
-        t_red = 0.0
+    def render_step(i):
+        """one bench step on this rank: this rank's disjoint sample-index range of the job, accumulated into its device film"""
+        return scene.render_accumulate(spp=spp, seed=1, spp_begin=(i * world + rank) * spp, spp_total=spp_total)
+
+    def film_to(t):
+        A.check(A.lib().mtsb_film_read(scene._h, 0, t.data_ptr(), A.MEM_DEVICE))      # k_film_pack straight into t (1 launch)
+
+    def reduce_film(t):
+        """the job's ONE film reduce: pack this rank's XYZAW sums and all-reduce them; -> device ms"""
+        e0, e1 = ev(), ev()
+        e0.record()
+        film_to(t)
         if world > 1:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            mi._abi.check(mi._abi.lib().mtsb_film_read(scene._h, 0, film_t.data_ptr(), mi._abi.MEM_DEVICE))
-            e0.record()
-            dist.all_reduce(film_t)
-            e1.record()
-            e1.synchronize()
-            t_red = e0.elapsed_time(e1)
-        return st, t_red
+            dist.all_reduce(t)
+        e1.record()
+        e1.synchronize()
+        return e0.elapsed_time(e1)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(*vals):
+        if world == 1:
+            return list(vals)
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
+
     scene.set_profiling(True)
     scene.film_clear()
     clocks = ClockSampler(local)
     clocks.start()
     for i in range(W):
-        step(i)
+        render_step(i)
+    reduce_film(film_t[0])
+    scene.film_clear()
     barrier()
+    # ---- timed region: K steps of the job (film accumulates on the device) + the job's one film reduce
     t0 = time.perf_counter()
     dev_ms, launches, agg = 0.0, 0, {}
     for i in range(W, W + K):
-        st, t_red = step(i)
-        dev_ms += st["ms_total"] + t_red
-        launches += st["kernel_launches"] + (1 if world > 1 else 0)
+        st = render_step(i)
+        dev_ms += st["ms_total"]
+        launches += st["kernel_launches"]
         for k in ("samples", "closest_rays", "shadow_rays", "segments", "ms_closest", "ms_any", "ms_shade", "ms_raygen", "ms_film"):
             agg[k] = agg.get(k, 0) + st[k]
+    reduce_ms = reduce_film(film_t[0])
+    dev_ms += reduce_ms
+    launches += 1 + (1 if world > 1 else 0)
     barrier()
     t1 = time.perf_counter()
     wall_ms = (t1 - t0) * 1e3
     clk = clocks.stop(t0, t1)
-    # max over ranks of the device time and wall time
-    if world > 1:
-        t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms = t.tolist()
+    dev_ms, wall_ms, reduce_ms = max_over_ranks(dev_ms, wall_ms, reduce_ms)
     samples_all = npix * spp * K * world
     value = samples_all / (dev_ms * 1e-3) / 1e6
 
-    # ---- e2e: the user's call with HOST buffers: upload the albedo texture (pinned), render, read the film back
-    tex_id = next(i for i, t in enumerate(sd.textures) if t["type"] == mi._abi.TEX_BITMAP)
+    # ---- N-rank film == 1-rank film of the union of the sample indices (one extra 1-spp step; checked inside the run
+    # because the driver's GPU test box has one GPU)
+    mg_parity = None
+    if world > 1:
+        scene.film_clear()
+        scene.render_accumulate(spp=1, seed=5, spp_begin=rank, spp_total=world)
+        reduce_film(film_t[0])
+        if rank == 0:
+            scene.film_clear()
+            scene.render_accumulate(spp=world, seed=5, spp_begin=0, spp_total=world)
+            film_to(film_t[1])
+            a, b = film_t[0], film_t[1]
+            mg_parity = {"max_abs": float((a - b).abs().max()), "max_abs_over_max": float((a - b).abs().max() / b.abs().max()),
+                         "rel_l1": float((a - b).abs().sum() / b.abs().sum()), "spp": world}
+        barrier()
+
+    # ---- strong scaling: ONE fixed job (full film x --strong-spp), sample indices split by distributed.sample_share,
+    # one film reduce at the end; the same job at every N, so time(1) / (N time(N)) is the strong-scaling efficiency
+    strong = None
+    if args.strong_spp > 0:
+        begin, count = D.sample_share(args.strong_spp, rank, world)
+        scene.film_clear()
+        barrier()
+        ms = 0.0
+        if count > 0:
+            ms = scene.render_accumulate(spp=count, seed=2, spp_begin=begin, spp_total=args.strong_spp)["ms_total"]
+        ms += reduce_film(film_t[0])
+        (ms,) = max_over_ranks(ms)
+        strong = {"job": f"{s['width']}x{s['height']} x {args.strong_spp} spp, spp-sharded over {world} GPU(s), one film all-reduce",
+                  "ms": ms, "msamples_per_s": npix * args.strong_spp / (ms * 1e-3) / 1e6, "spp_per_rank": count}
+
+    # ---- e2e: the user's call with HOST buffers.  Every step: upload the albedo texture from pinned memory (every rank),
+    # clear, render this rank's share, reduce the film over the ranks and read the step's film back into pinned host memory
+    # (rank 0).  At N > 1 the reduce + read-back of step i run on a side stream under the render of step i+1 (double buffered).
+    tex_id = next(i for i, t in enumerate(sd.textures) if t["type"] == A.TEX_BITMAP)
     tex_host = torch.from_numpy(sd.textures[tex_id]["data"].copy()).pin_memory()
-    film_host = torch.empty(npix * 5, dtype=torch.float32).pin_memory()
+    film_host = [torch.empty(npix * 5, dtype=torch.float32).pin_memory() for _ in range(2)]
+    side = torch.cuda.Stream(device=dev)
+    done = [None, None]
     barrier()
     t0 = time.perf_counter()
-    for i in range(W + K, W + 2 * K):
+    for n, i in enumerate(range(W + K, W + 2 * K)):
+        k = n & 1
         scene.update_texture(tex_id, tex_host.numpy())
         scene.film_clear()
-        step(i)
-        mi._abi.check(mi._abi.lib().mtsb_film_read(scene._h, 0, film_host.data_ptr(), mi._abi.MEM_HOST))
+        render_step(i)
+        if world == 1:
+            A.check(A.lib().mtsb_film_read(scene._h, 0, film_host[k].data_ptr(), A.MEM_HOST))
+        else:
+            if done[k] is not None:
+                done[k].synchronize()          # buffer k is free again
+            film_to(film_t[k])                  # returns after the pack kernel finished (library stream synchronised)
+            with torch.cuda.stream(side):
+                dist.all_reduce(film_t[k])
+                if rank == 0:
+                    film_host[k].copy_(film_t[k], non_blocking=True)
+                done[k] = torch.cuda.Event()
+                done[k].record(side)
+    side.synchronize()
     barrier()
     e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = t.item()
-    e2e = {"value": samples_all / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(tex_host.numel() * 4),
-           "d2h_bytes_per_step": int(film_host.numel() * 4)}
+    (e2e_s,) = max_over_ranks(e2e_s)
+    e2e = {"value": samples_all / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(tex_host.numel() * 4) * world,
+           "d2h_bytes_per_step": int(film_host[0].numel() * 4),
+           "note": "per step: pinned texture upload on every rank, render, film all-reduce, rank 0 reads the film back"}
 
     if rank == 0:
         peak, peak_src = peaks()
+        prof = ncu_profile()
         # dominant kernel = closest-hit traversal; algorithmic bytes = 48 B per ray (32 B ray in + 16 B hit out)
         ms_c = max(agg["ms_closest"], 1e-9)
         pool = int(os.environ.get("MTSB_POOL", 1 << 25))
@@ -401,22 +527,28 @@ def main():
             "metric": "path_tracing_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload]["desc"], "spp_per_step_per_gpu": spp,
-                       "samples_per_step": npix * spp * world, "parallelism": f"spp-sharded x{world} + film all-reduce",
+            "config": {"workload": WORKLOADS[args.workload]["desc"], "envmap": getattr(sd, "envmap_name", "synthetic sky 1024x512"),
+                       "spp_per_step_per_gpu": spp, "samples_per_step": npix * spp * world,
+                       "parallelism": f"spp-sharded x{world}; the K-step job accumulates on each GPU and its film is all-reduced ONCE, inside the timed region",
                        "l2": "queues per step (>1 GB) exceed L2; no flush needed", "timing": "CUDA events on the launching stream, max over ranks"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": prof.get("dram_bytes_per_launch"), "peak_source": peak_src,
                          "algorithmic_bytes": "48 B/ray x rays per launch",
                          "algorithmic_bytes_per_launch": agg["closest_rays"] * 48 / max(1, n_trace_launches),
-                         "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per k_trace<closest> launch, profiles/r1_kernel_traffic.json",
-                         "limiter": "SM instruction issue / ALU pipe (ncu: issue slots 78% busy, ALU pipe 58%, DRAM 2% of peak), see profiles/", "mrays_per_s": agg["closest_rays"] / (ms_c * 1e-3) / 1e6},
-            "extra": {"wall_ms_per_step": wall_ms / K, "stage_ms_per_step": stage_ms, "rays_per_sample": agg["closest_rays"] / agg["samples"],
+                         "traffic_source": prof.get("source"),
+                         "limiter": "SM instruction issue / ALU pipe, not HBM (the kernel walks L1/L2-resident BVH nodes); see profiles/",
+                         "thread_instructions_per_ray": prof.get("thread_inst_per_ray"),
+                         "active_threads_per_instruction": prof.get("threads_per_inst"),
+                         "issue_slots_busy_pct": prof.get("issue_slots_busy_pct"),
+                         "mrays_per_s": agg["closest_rays"] / (ms_c * 1e-3) / 1e6},
+            "extra": {"wall_ms_per_step": wall_ms / K, "stage_ms_per_step": stage_ms, "film_reduce_ms_per_job": reduce_ms,
+                      "rays_per_sample": agg["closest_rays"] / agg["samples"],
                       "shadow_rays_per_sample": agg["shadow_rays"] / agg["samples"], "algorithmic_bytes_per_sample": bytes_per_sample,
                       "whole_step_gbs": bytes_per_sample * agg["samples"] / (sum(stage_ms.values()) * K * 1e-3) / 1e9,
                       "any_hit_mrays_per_s": agg["shadow_rays"] / max(agg["ms_any"], 1e-9) / 1e3,
                       "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"]},
-                      "scene_setup_s": t_build},
+                      "scene_setup_s": t_build, "strong_scaling": strong, "multi_gpu_parity": mg_parity},
         }
         if world == 1 and not args.no_side_metrics:
             del scene

@@ -673,8 +673,9 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
 
 extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
                            uint64_t seed, mtsb_stats *stats) {
-    CHECK_ARG(s && sensor_id < s->sensors.size() && spp_count > 0 && spp_begin + spp_count <= spp_total);
+    CHECK_ARG(s && sensor_id < s->sensors.size() && spp_count > 0 && (uint64_t) spp_begin + spp_count <= (uint64_t) spp_total);
     CU(cudaSetDevice(s->ctx->device));
+    s->ctx->cancel = 0;      // like `m_stop = false` at the top of SamplingIntegrator::render (integrator.cpp:54): a stale cancel does not abort this render
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
@@ -729,8 +730,11 @@ extern "C" int mtsb_film_read(mtsb_scene *s, uint32_t sensor_id, float *xyzaw, i
     CHECK_ARG(s && sensor_id < s->sensors.size() && xyzaw);
     CU(cudaSetDevice(s->ctx->device));
     SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
-    k_film_pack<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, sh.packed.p);
-    CU(cudaMemcpyAsync(xyzaw, sh.packed.p, 5 * npx * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s->ctx->stream));
+    if (mem == MTSB_MEM_DEVICE) k_film_pack<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, xyzaw);      // straight into the caller's buffer
+    else {
+        k_film_pack<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, sh.packed.p);
+        CU(cudaMemcpyAsync(xyzaw, sh.packed.p, 5 * npx * sizeof(float), cudaMemcpyDeviceToHost, s->ctx->stream));
+    }
     CU(cudaStreamSynchronize(s->ctx->stream));
     return MTSB_OK;
 }

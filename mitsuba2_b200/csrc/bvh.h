@@ -307,10 +307,11 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
         while (ceilf(ext[a] / exp2f((float) e)) > 254.f) e++;   // one unit of slack for the safety pass below
         ex[a] = e; sc[a] = exp2f((float) e);
     }
-    uint8_t qlo[3][8], qhi[3][8], meta[8];
-    for (int s = 0; s < 8; ++s) { meta[s] = 0; for (int a = 0; a < 3; ++a) { qlo[a][s] = 255; qhi[a][s] = 0; } }
-    uint32_t imask = 0;
-    // internal children take consecutive indices in slot order; leaves take triangle offsets in slot order
+    uint8_t qlo[3][8], qhi[3][8];
+    for (int s = 0; s < 8; ++s) for (int a = 0; a < 3; ++a) { qlo[a][s] = 255; qhi[a][s] = 0; }   // empty slot: inverted box, never hit
+    uint32_t imask = 0, valid24 = 0;
+    // internal children take consecutive indices in slot order; leaf triangles are stored in slot order too: candidate bit
+    // 3*slot + k (k < kMaxLeafTris) of `valid24` <-> triangle tri_base + popc(valid24 below that bit)
     int kid_of_slot[8];
     for (int s = 0; s < 8; ++s) kid_of_slot[s] = -1;
     for (int k = 0; k < nch; ++k) kid_of_slot[slot_of[k]] = k;
@@ -331,12 +332,11 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
         }
         if (internal[k]) {
             imask |= 1u << s;
-            meta[s] = (uint8_t) ((1u << 5) | (24u + s));
             b.wide_bin[child_base + int_rank] = ch[k];
             int_rank++;
         } else {
             uint32_t cnt = bin_count(b, ch[k]), first = bin_first(b, ch[k]);
-            meta[s] = (uint8_t) ((((1u << cnt) - 1u) << 5) | tri_off);
+            valid24 |= ((1u << cnt) - 1u) << (3 * s);
             for (uint32_t q = 0; q < cnt; ++q) {
                 uint32_t prim = b.order[first + q];
                 uint4 f = b.faces[prim];
@@ -352,7 +352,7 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
     uint4 *o = b.nodes + 5 * (size_t) w;
     uint32_t ew = (uint32_t) (ex[0] + 127) | ((uint32_t) (ex[1] + 127) << 8) | ((uint32_t) (ex[2] + 127) << 16) | (imask << 24);
     o[0] = make_uint4(f2u(lo.x), f2u(lo.y), f2u(lo.z), ew);
-    o[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+    o[1] = make_uint4(child_base, tri_base, valid24, 0u);
     o[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
     o[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
     o[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
@@ -429,8 +429,26 @@ template <int NFast, int NSlow> struct TravStack {
 
 HD uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
 
-// Intersect the 8 quantised child boxes of `node`; returns the hit mask word: bits 24..31 internal children in
-// near-to-far priority (bit = 24 + (slot ^ octinv)), bits 0..23 candidate triangles.
+// Node words: n0 = (origin xyz, ex | ey<<8 | ez<<16 | imask<<24), n1 = (first child, first triangle, valid24, -),
+// n2..n4 = quantised planes lo x,y,z / hi x,y,z, 8 bytes each.  valid24: bit 3*slot+k set <-> leaf child `slot` holds a k-th
+// triangle; triangles of a node are stored in that bit order, so candidate bit b is triangle n1.y + popc(valid24 below b).
+// Hit mask word of a node test: bits 24..31 inner children in near-to-far priority (bit = 24 + (slot ^ octinv)), bits
+// 0..23 candidate triangles (the valid24 bits of the leaf children whose box is hit).
+HD uint32_t perm_xor8(uint32_t x, uint32_t k) {       // bit i of x -> bit i ^ k, 8 bits
+    if (k & 1u) x = ((x & 0x55u) << 1) | ((x >> 1) & 0x55u);
+    if (k & 2u) x = ((x & 0x33u) << 2) | ((x >> 2) & 0x33u);
+    if (k & 4u) x = ((x & 0x0fu) << 4) | ((x >> 4) & 0x0fu);
+    return x;
+}
+HD uint32_t spread3x8(uint32_t x) {                   // bit s of x -> bits 3s, 3s+1, 3s+2
+    x = (x | (x << 8)) & 0x00f00fu;
+    x = (x | (x << 4)) & 0x0c30c3u;
+    x = (x | (x << 2)) & 0x249249u;
+    return x * 7u;
+}
+HD uint32_t hitmask_from_slots(uint32_t h8, uint32_t imask, uint32_t valid24, uint32_t octinv) {
+    return (perm_xor8(h8 & imask, octinv) << 24) | (spread3x8(h8) & valid24);
+}
 // Reference (host / test) formulation: integer -> float conversion per plane.
 HD uint32_t node_hitmask_ref(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
                              float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
@@ -438,40 +456,35 @@ HD uint32_t node_hitmask_ref(const uint4 n0, const uint4 n1, const uint4 n2, con
     float sx = u2f(byte_of(n0.w, 0) << 23), sy = u2f(byte_of(n0.w, 1) << 23), sz = u2f(byte_of(n0.w, 2) << 23);
     float3 adir = mk3(sx * idir.x, sy * idir.y, sz * idir.z);
     float3 org = mk3((p.x - o.x) * idir.x, (p.y - o.y) * idir.y, (p.z - o.z) * idir.z);
-    uint32_t imask = n0.w >> 24;
-    uint32_t hit = 0;
+    uint32_t h8 = 0;
     bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
     for (int half = 0; half < 2; ++half) {
-        uint32_t meta4 = half ? n1.w : n1.z;
         uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
         uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
         uint32_t ax = nx ? hix : lox, bx = nx ? lox : hix;
         uint32_t ay = ny ? hiy : loy, by = ny ? loy : hiy;
         uint32_t az = nz ? hiz : loz, bz = nz ? loz : hiz;
         for (int j = 0; j < 4; ++j) {
-            uint32_t meta = byte_of(meta4, j);
             float t0x = fmaf((float) byte_of(ax, j), adir.x, org.x), t1x = fmaf((float) byte_of(bx, j), adir.x, org.x);
             float t0y = fmaf((float) byte_of(ay, j), adir.y, org.y), t1y = fmaf((float) byte_of(by, j), adir.y, org.y);
             float t0z = fmaf((float) byte_of(az, j), adir.z, org.z), t1z = fmaf((float) byte_of(bz, j), adir.z, org.z);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-            if (meta != 0 && tn <= tf * 1.0000004f) {
-                int s = half * 4 + j;
-                if (imask & (1u << s)) hit |= 1u << (24 + ((uint32_t) s ^ octinv));
-                else hit |= (meta >> 5) << (meta & 31u);
-            }
+            if (tn <= tf * 1.0000004f) h8 |= 1u << (half * 4 + j);
         }
     }
-    return hit;
+    return hitmask_from_slots(h8, n0.w >> 24, n1.z, octinv);
 }
 
-#ifdef __CUDA_ARCH__
+#ifdef __CUDACC__
 // Device formulation: no I2F and no branches.  A quantised byte q is turned into the float 1 + q*2^-15 with one PRMT
 // (byte placed at mantissa bits 8..15 of 1.0f); the plane distance is then one FFMA: t = f*A + B with A = adir*2^15 and
 // B = org - A.  B carries a rounding error <= |adir|*2^-9 (1/512 of a grid cell); the near/far offsets are padded by
-// |adir|*2^-7 so the slab test stays conservative.  Bit positions of the hit mask are derived 4 children at a time.
-__device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
-                                                 float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+// |adir|*2^-7 so the slab test stays conservative.  The outcome of child j is the sign bit of tf - tn (one FADD on the FMA
+// pipe), shifted into the slot mask by one funnel shift -- the ALU pipe is this kernel's limiter (ncu: 64 % of its peak),
+// so compares / selects / per-child bit arithmetic were moved off it.  Returns the 8-bit mask of the child slots hit.
+__device__ __forceinline__ uint32_t node_slots_hit(const uint4 n0, const uint4 n2, const uint4 n3, const uint4 n4,
+                                                   float3 o, float3 idir, float tmin, float tmax) {
     float sx = __uint_as_float((n0.w & 0xffu) << 23), sy = __uint_as_float((n0.w & 0xff00u) << 15), sz = __uint_as_float((n0.w & 0xff0000u) << 7);
     float ax_ = sx * idir.x, ay_ = sy * idir.y, az_ = sz * idir.z;
     float Ax = ax_ * 32768.f, Ay = ay_ * 32768.f, Az = az_ * 32768.f;
@@ -479,27 +492,18 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1,
     float px = fabsf(ax_) * 0.0078125f, py = fabsf(ay_) * 0.0078125f, pz = fabsf(az_) * 0.0078125f;
     float Bnx = ox - px, Bny = oy - py, Bnz = oz - pz, Bfx = ox + px, Bfy = oy + py, Bfz = oz + pz;
     bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
-    uint32_t octinv4 = octinv * 0x01010101u;
-    uint32_t hit = 0;
+    uint32_t miss = 0;
     const uint32_t one = 0x3f800000u;
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        uint32_t meta4 = half ? n1.w : n1.z;
+    for (int half = 1; half >= 0; --half) {
         uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
         uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
         uint32_t ax = nx ? hix : lox, bx = nx ? lox : hix;
         uint32_t ay = ny ? hiy : loy, by = ny ? loy : hiy;
         uint32_t az = nz ? hiz : loz, bz = nz ? loz : hiz;
-        uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-        uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            // result bytes: 0x00, q_j, 0x80, 0x3f.  The constant is the FIRST source (a register that stays live), the
-            // selector an immediate: with the constant as the third source the selector had to be re-materialised
-            // from a uniform register before every PRMT (41 extra moves per node in the SASS).
-            const uint32_t sel = 0x3240u + ((uint32_t) j << 4);
+        for (int j = 3; j >= 0; --j) {      // slot 7 first: every funnel shift moves the earlier outcomes one bit up
+            const uint32_t sel = 0x3240u + ((uint32_t) j << 4);      // result bytes: 0x00, q_j, 0x80, 0x3f
             float t0x = fmaf(__uint_as_float(__byte_perm(one, ax, sel)), Ax, Bnx);
             float t0y = fmaf(__uint_as_float(__byte_perm(one, ay, sel)), Ay, Bny);
             float t0z = fmaf(__uint_as_float(__byte_perm(one, az, sel)), Az, Bnz);
@@ -508,18 +512,20 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4 n0, const uint4 n1,
             float t1z = fmaf(__uint_as_float(__byte_perm(one, bz, sel)), Az, Bfz);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-            uint32_t bits = ((child_bits4 >> (8 * j)) & 0xffu) << ((bit_index4 >> (8 * j)) & 0xffu);
-            hit |= (tn <= tf) ? bits : 0u;
+            miss = __funnelshift_l(__float_as_uint(tf - tn), miss, 1);      // (miss << 1) | sign(tf - tn)
         }
     }
-    return hit;
-}
-#else
-HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
-                         float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
-    return node_hitmask_ref(n0, n1, n2, n3, n4, o, idir, octinv, tmin, tmax);
+    return ~miss & 0xffu;
 }
 #endif
+HD uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                         float3 o, float3 idir, uint32_t octinv, float tmin, float tmax) {
+#ifdef __CUDA_ARCH__
+    return hitmask_from_slots(node_slots_hit(n0, n2, n3, n4, o, idir, tmin, tmax), n0.w >> 24, n1.z, octinv);
+#else
+    return node_hitmask_ref(n0, n1, n2, n3, n4, o, idir, octinv, tmin, tmax);
+#endif
+}
 
 HD uint4 ldg4(const uint4 *p) {
 #ifdef __CUDA_ARCH__
@@ -595,7 +601,7 @@ HD bool trav_step(const Bvh &bvh, Trav &tr, Stack &st) {
         while (tm) {
             uint32_t b = 31u - (uint32_t) clz32(tm);
             tm &= ~(1u << b);
-            const float4 *tp = bvh.tris + 3 * (size_t) (tb + b);
+            const float4 *tp = bvh.tris + 3 * (size_t) (tb + (uint32_t) popc32(n1.z & ((1u << b) - 1u)));
             float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
             float t, u, v;
             TRAV_TRI();

@@ -123,6 +123,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaEventRecord(s->ctx->ev0, st));
     uint64_t launches = 0;
+    s->ctx->cancel = 0;      // a cancel that arrived before this call does not abort it (integrator.cpp:54)
     for (uint64_t off = 0; off < total; off += pool) {
         if (s->ctx->cancel) { s->ctx->cancel = 0; cudaStreamSynchronize(st); return fail(MTSB_E_CANCELLED, "render cancelled"); }
         uint32_t n = (uint32_t) ((total - off) < pool ? (total - off) : pool);

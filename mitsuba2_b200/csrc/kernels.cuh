@@ -106,22 +106,54 @@ constexpr int kTraceBlocksPerSM = MTSB_TRACE_BLOCKS;
 #define MTSB_SHADE_BLOCKS 8      // re-measured at the end of round 1 (ms of shade per C3 step): 6: 12.81, 7: 12.43, 8: 12.31, 9: 12.40, 10: 12.52, 12: 12.69
 #endif
 constexpr int kShadeBlocksPerSM = MTSB_SHADE_BLOCKS;      // resident 128-thread blocks the shade kernel is compiled for
+// Inside a warp the two halves of a traversal step are scheduled differently:
+//   * node test: one lane = one ray (every lane whose ray has no triangle candidates pending pops one child of its
+//     current node group and intersects its 8 quantised boxes) -- ~28 of 32 lanes busy;
+//   * triangle test: WARP-COOPERATIVE.  A node test leaves 0..24 candidate triangles per ray (~0.7 on average), so a
+//     per-ray triangle loop runs at ~5 of 32 lanes and was half of all issued instructions (ncu, profiles/r1c_*).  Instead
+//     the lanes publish their (ray lane, candidate) pairs into a per-warp list in shared memory, every lane -- idle ones
+//     too -- tests ONE pair against the owner's ray (its Woop row vectors live in shared memory), the closest accepted hit
+//     per ray is resolved by a 64-bit shared atomicMin on (t, pair index) and read back by the owning lane, which updates
+//     tmax before its next node test (so node culling sees the same tmax as with a serial loop).
+// Result of a ray = closest t among all accepted candidates, ties resolved by pair order: the same set a serial loop accepts.
+constexpr int kCoopCap = 96;              // candidate pairs a warp tests per iteration (3 passes of 32); the rest stay pending
+struct __align__(16) WarpCoop {
+    float4 ray[4][32];                    // per lane: (o, mint) (rx, tmax) (ry, -) (rz, -)
+    float4 hitrec[32];                    // (t, u, v, prim) of the hit found by each TESTING lane in the current pass
+    unsigned long long best[32];          // per owning lane: min over accepted hits of (ordered t bits << 32 | testing lane)
+    uint32_t items[kCoopCap];             // owner lane << 5 | candidate bit
+};
+__device__ __forceinline__ uint32_t float_order_bits(float t) {      // monotone float -> uint map
+    uint32_t b = __float_as_uint(t);
+    return b ^ ((uint32_t) ((int32_t) b >> 31) | 0x80000000u);
+}
 template <bool AnyHit, typename Sink>
 __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count, const float4 *__restrict__ o_mint,
-                                                 const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill,
-                                                 uint2 *s_stack, Sink sink) {
-    typedef TravStack<kStackFast, kStackSlow> Stack;
+                                                 const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill, Sink sink) {
+    __shared__ uint2 s_stack[kStackFast * kBlock];
+    __shared__ WarpCoop s_coop[kBlock / 32];
+    // decode tables of the node test (LSU pipe instead of ALU bit arithmetic): slot mask -> inner children in near-to-far
+    // bit order for each ray octant, slot mask -> 3 candidate bits per slot
+    __shared__ uint8_t s_perm[8 * 256];
+    __shared__ uint32_t s_spread[256];
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) s_perm[i] = (uint8_t) perm_xor8(i & 255u, i >> 8);
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) s_spread[i] = spread3x8(i);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    Trav tr; Stack st; st.fast = s_stack + threadIdx.x; st.stride = kBlock; st.sp = 0;
+    WarpCoop &ws = s_coop[threadIdx.x >> 5];
+    uint2 slow[kStackSlow];
+    int sp = 0;
+    float3 o = mk3(0.f), idir = mk3(0.f); float mint = 0.f, tmax = 0.f; uint32_t octinv = 0; uint2 G = make_uint2(0u, 0u);
+    uint32_t tm = 0u, tb = 0u, valid = 0u;   // pending triangle candidates of the current node: bit mask, first triangle, valid24
+    Hit hit; hit.t = INFINITY; hit.u = hit.v = 0.f; hit.prim = 0xffffffffu; bool found = false;
     bool active = false, exhausted = (count == 0 || bvh.n_tris == 0);
     uint32_t ray = 0, w_next = 0, w_end = 0;
     if (bvh.n_tris == 0) {      // empty scene: every ray misses
-        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-            Hit h; h.t = INFINITY; h.u = h.v = 0.f; h.prim = 0xffffffffu;
-            sink(i, false, h);
-        }
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) sink(i, false, hit);
         return;
     }
+    ws.best[lane] = ~0ull;
+    __syncwarp();
     while (true) {
         uint32_t idle = __ballot_sync(0xffffffffu, !active);
         if (idle && !exhausted) {
@@ -136,20 +168,92 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
             uint32_t r = (uint32_t) __popc(idle & lt);
             if (!active && r < take) {
                 ray = w_next + r;
-                float4 o = o_mint[ray], d = d_maxt[ray];
-                trav_init(tr, st, xyz(o), xyz(d), o.w, d.w);
+                float4 ro = o_mint[ray], rd = d_maxt[ray];
+                const float big = 1e30f;
+                float3 d = xyz(rd);
+                o = xyz(ro); mint = ro.w; tmax = rd.w;
+                idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x), fabsf(d.y) > 1e-30f ? 1.f / d.y : copysignf(big, d.y),
+                           fabsf(d.z) > 1e-30f ? 1.f / d.z : copysignf(big, d.z));
+                octinv = 7u ^ ((d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u));
+                RayWoop rw = woop_setup(o, d);
+                ws.ray[0][lane] = mk4(o, mint); ws.ray[1][lane] = mk4(rw.rx, tmax); ws.ray[2][lane] = mk4(rw.ry, 0.f); ws.ray[3][lane] = mk4(rw.rz, 0.f);
+                G = make_uint2(0u, 0x80000000u); tm = 0u; sp = 0;
+                hit.t = INFINITY; hit.u = hit.v = 0.f; hit.prim = 0xffffffffu; found = false;
                 active = true;
             }
             w_next += take;
+            __syncwarp();
         }
         if (__ballot_sync(0xffffffffu, active) == 0u) {
             if (exhausted) break;
             continue;
         }
         while (true) {
-            if (active && trav_step<AnyHit>(bvh, tr, st)) {
-                sink(ray, tr.found, tr.hit);
-                active = false;
+            // ---- node phase: one child of the current group per lane (lanes with pending candidates wait)
+            if (active && tm == 0u && (G.y & 0xff000000u)) {
+                uint32_t bit = 31u - (uint32_t) __clz((int) G.y);
+                G.y &= ~(1u << bit);
+                if (G.y & 0xff000000u) { if (sp < kStackFast) s_stack[sp * kBlock + threadIdx.x] = G; else if (sp - kStackFast < kStackSlow) slow[sp - kStackFast] = G; sp++; }
+                uint32_t slot = (bit - 24u) ^ octinv;
+                uint32_t rel = (uint32_t) __popc(G.y & ((1u << slot) - 1u) & 0xffu);
+                const uint4 *np = bvh.nodes + 5 * (size_t) (G.x + rel);
+                uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                uint32_t h8 = node_slots_hit(n0, n2, n3, n4, o, idir, mint, tmax), im = n0.w >> 24;
+                G = make_uint2(n1.x, ((uint32_t) s_perm[octinv * 256u + (h8 & im)] << 24) | im);
+                tb = n1.y; valid = n1.z; tm = s_spread[h8] & valid;
+            }
+            // ---- triangle phase: pool the candidates of all lanes, one (ray, triangle) pair per lane and pass
+            uint32_t pend = __ballot_sync(0xffffffffu, tm != 0u);
+            if (pend) {
+                uint32_t n_items = 0;
+                do {      // publishing rounds: every lane with candidates appends its highest one (one ballot per round)
+                    if (tm) {
+                        uint32_t b = 31u - (uint32_t) __clz((int) tm);
+                        tm &= ~(1u << b);
+                        // owner lane << 5 | rank of the candidate = offset from the node's first triangle
+                        ws.items[n_items + (uint32_t) __popc(pend & lt)] = (lane << 5) | (uint32_t) __popc(valid & ((1u << b) - 1u));
+                    }
+                    n_items += (uint32_t) __popc(pend);
+                    pend = __ballot_sync(0xffffffffu, tm != 0u);
+                } while (pend && n_items <= (uint32_t) (kCoopCap - 32));      // what does not fit stays pending in tm
+                __syncwarp();
+                for (uint32_t base = 0; base < n_items; base += 32u) {
+                    uint32_t j = base + lane;
+                    bool mine = j < n_items;
+                    uint32_t it = mine ? ws.items[j] : 0u, src = it >> 5;
+                    uint32_t stb = __shfl_sync(0xffffffffu, tb, src);
+                    if (mine) {
+                        const float4 *tp = bvh.tris + 3 * (size_t) (stb + (it & 31u));
+                        float4 a0 = __ldg(tp), a1 = __ldg(tp + 1), a2 = __ldg(tp + 2);
+                        float4 r0 = ws.ray[0][src], r1 = ws.ray[1][src], r2 = ws.ray[2][src], r3 = ws.ray[3][src];
+                        RayWoop rw; rw.rx = xyz(r1); rw.ry = xyz(r2); rw.rz = xyz(r3);
+                        float t, u, v;
+                        if (woop_intersect(rw, xyz(r0), xyz(a0), xyz(a1), xyz(a2), r0.w, r1.w, t, u, v)) {
+                            ws.hitrec[lane] = make_float4(t, u, v, a0.w);
+                            atomicMin(&ws.best[src], ((unsigned long long) float_order_bits(t) << 32) | lane);
+                        }
+                    }
+                    __syncwarp();
+                    unsigned long long bk = ws.best[lane];
+                    if (bk != ~0ull) {      // the closest accepted candidate of my ray was tested by lane (bk & 31)
+                        float4 r = ws.hitrec[(uint32_t) bk & 31u];
+                        found = true; tmax = r.x;
+                        hit.t = r.x; hit.u = r.y; hit.v = r.z; hit.prim = f2u(r.w);
+                        ws.ray[1][lane].w = r.x;
+                        ws.best[lane] = ~0ull;
+                    }
+                    __syncwarp();
+                }
+            }
+            // ---- next group / completion
+            if (active) {
+                bool done = false;
+                if (AnyHit && found) done = true;
+                else if (tm == 0u && (G.y & 0xff000000u) == 0u) {
+                    if (sp == 0) done = true;
+                    else { sp--; G = sp < kStackFast ? s_stack[sp * kBlock + threadIdx.x] : slow[(sp - kStackFast) < kStackSlow ? (sp - kStackFast) : kStackSlow - 1]; }
+                }
+                if (done) { sink(ray, found, hit); active = false; tm = 0u; }
             }
             uint32_t a = __ballot_sync(0xffffffffu, active);
             if (a == 0u || (!exhausted && (uint32_t) __popc(a) < refill)) break;
@@ -162,9 +266,8 @@ __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_trace(Bvh bvh, const uint32_t *count_ptr, uint32_t count_max, const float4 *__restrict__ o_mint,
         const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded,
         uint32_t *work, uint32_t refill, const uint8_t *__restrict__ prim_class) {
-    __shared__ uint2 s_stack[kStackFast * kBlock];
     uint32_t count = count_ptr ? min(*count_ptr, count_max) : count_max;
-    trace_persistent<AnyHit>(bvh, count, o_mint, d_maxt, work, refill, s_stack,
+    trace_persistent<AnyHit>(bvh, count, o_mint, d_maxt, work, refill,
         [=](uint32_t i, bool found, const Hit &h) {
             if (AnyHit) occluded[i] = found ? 1u : 0u;
             else {
@@ -378,10 +481,9 @@ __global__ void k_edge_scatter(SceneDev sc, EdgeCtx e, const float *total_len, G
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *stats, uint32_t depth, uint32_t count_max,
          float4 *result, uint32_t *work, uint32_t refill) {
-    __shared__ uint2 s_stack[kStackFast * kBlock];
     uint32_t count = min(counters[1024 + depth], count_max);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[1], (unsigned long long) count);
-    trace_persistent<true>(bvh, count, sq.o_mint, sq.d_maxt, work, refill, s_stack,
+    trace_persistent<true>(bvh, count, sq.o_mint, sq.d_maxt, work, refill,
         [=](uint32_t i, bool found, const Hit &) {
             if (sq.occluded != nullptr) sq.occluded[i] = found ? 1u : 0u;
             if (found) return;

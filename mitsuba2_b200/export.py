@@ -144,7 +144,7 @@ class _Writer:
             raise ValueError("area emitters are written with their shape")
 
 
-def write_mitsuba_scene(sd, directory, spp=None, sensor=0, file_format="pfm", variant_hint="scalar_rgb"):
+def write_mitsuba_scene(sd, directory, spp=None, sensor=0, file_format="pfm", variant_hint="scalar_rgb", integrator="path"):
     """-> path of scene.xml.  Meshes go to mesh_<i>.ply (normals and texcoords included when the mesh has them; a mesh
     without normals is loaded with face_normals=true, which is what `normals is None` means on the device)."""
     os.makedirs(directory, exist_ok=True)
@@ -152,7 +152,7 @@ def write_mitsuba_scene(sd, directory, spp=None, sensor=0, file_format="pfm", va
     spp = int(sd.spp if spp is None else spp)
     w.lines.append(f'<!-- written by mitsuba2_b200.export for {variant_hint} -->')
     w.lines.append('<scene version="2.1.0">')
-    w.w(f'<integrator type="path"><integer name="max_depth" value="{int(sd.max_depth)}"/>'
+    w.w(f'<integrator type="{integrator}"><integer name="max_depth" value="{int(sd.max_depth)}"/>'
         f'<integer name="rr_depth" value="{int(sd.rr_depth)}"/></integrator>')
     s = sd.sensors[sensor]
     w.w('<sensor type="perspective">')

@@ -28,10 +28,20 @@ def _is_torch_cuda(x):
     return hasattr(x, "is_cuda") and x.is_cuda
 
 
-def _arg(x, dtype, n_expected=None):
+def _arg(x, dtype, n_expected=None, device=None):
     """-> (pointer, mem, keepalive) for a numpy array or a CUDA torch tensor."""
     if _is_torch_cuda(x):
+        import torch
+        want = {np.float32: torch.float32, np.uint32: torch.int32, np.int32: torch.int32}.get(dtype, torch.float32)
+        if x.dtype != want and not (dtype == np.uint32 and x.dtype == torch.uint32):
+            raise TypeError(f"CUDA tensor of dtype {x.dtype} passed where {want} is required (the library reads raw device memory)")
+        if device is not None and x.device.index != int(device):
+            raise ValueError(f"CUDA tensor lives on cuda:{x.device.index}, the scene on cuda:{device}")
         x = x.contiguous()
+        if n_expected is not None and x.numel() != n_expected:
+            raise ValueError(f"expected {n_expected} elements, got {x.numel()}")
+        # the library works on its own non-blocking stream: everything torch has queued for this tensor must be done first
+        torch.cuda.current_stream(x.device).synchronize()
         return C.c_void_p(x.data_ptr()), A.MEM_DEVICE, x
     a = np.ascontiguousarray(x, dtype=dtype)
     if n_expected is not None and a.size != n_expected:
@@ -86,8 +96,8 @@ class Scene:
 
     def intersect_closest_raw(self, o_mint, d_maxt, hits=None, naive=False):
         """SoA entry: o_mint/d_maxt (n,4) float32 numpy or CUDA torch; returns hits (n,4) = t,u,v,prim bits."""
-        po, mem, k0 = _arg(o_mint, np.float32)
-        pd, mem2, k1 = _arg(d_maxt, np.float32)
+        po, mem, k0 = _arg(o_mint, np.float32, device=self.device)
+        pd, mem2, k1 = _arg(d_maxt, np.float32, device=self.device)
         assert mem == mem2
         n = (k0.numel() if mem == A.MEM_DEVICE else k0.size) // 4
         if hits is None:
@@ -106,8 +116,8 @@ class Scene:
         return hits
 
     def intersect_any_raw(self, o_mint, d_maxt, out=None):
-        po, mem, k0 = _arg(o_mint, np.float32)
-        pd, mem2, k1 = _arg(d_maxt, np.float32)
+        po, mem, k0 = _arg(o_mint, np.float32, device=self.device)
+        pd, mem2, k1 = _arg(d_maxt, np.float32, device=self.device)
         assert mem == mem2
         n = (k0.numel() if mem == A.MEM_DEVICE else k0.size) // 4
         if out is None:
@@ -169,7 +179,7 @@ class Scene:
         return out
 
     def film_accumulate(self, xyzaw, sensor=0):
-        p, mem, keep = _arg(xyzaw, np.float32)
+        p, mem, keep = _arg(xyzaw, np.float32, device=self.device)
         A.check(A.lib().mtsb_film_accumulate(self._h, sensor, p, mem))
 
     def film_develop(self, sensor=0):
@@ -216,13 +226,13 @@ class Scene:
 
     # ---- parameter updates (traverse()/parameters_changed) ------------------------------------------
     def update_vertices(self, mesh_id, positions):
-        p, mem, keep = _arg(positions, np.float32)
+        p, mem, keep = _arg(positions, np.float32, device=self.device)
         A.check(A.lib().mtsb_scene_update_vertices(self._h, mesh_id, p, mem))
         if mem == A.MEM_HOST:
             self.data.meshes[mesh_id].positions = keep.reshape(-1, 3).copy()
 
     def update_texture(self, tex_id, data):
-        p, mem, keep = _arg(data, np.float32)
+        p, mem, keep = _arg(data, np.float32, device=self.device)
         A.check(A.lib().mtsb_scene_update_texture(self._h, tex_id, p, mem))
 
     # ---- gradient pass ----------------------------------------------------------------------------
@@ -238,7 +248,7 @@ class Scene:
         sum(dL_dimage * developed image); either is None when its id is negative."""
         spp = self.data.spp if spp is None else int(spp)
         spp_total = spp_begin + spp if spp_total is None else int(spp_total)
-        pd, mem, k = _arg(dL_dimage, np.float32)
+        pd, mem, k = _arg(dL_dimage, np.float32, device=self.device)
         gt = gv = None
         if mem == A.MEM_DEVICE:
             import torch
@@ -251,6 +261,7 @@ class Scene:
                 gv = torch.zeros(self.data.meshes[mesh_id].positions.size, dtype=torch.float32, device=dev)
             pgt = C.c_void_p(gt.data_ptr()) if gt is not None else None
             pgv = C.c_void_p(gv.data_ptr()) if gv is not None else None
+            torch.cuda.current_stream(dev).synchronize()      # the zero fills above run on torch's stream, the kernels on the library's
         else:
             if tex_id >= 0:
                 t = self.data.textures[tex_id]

@@ -56,6 +56,21 @@ def main():
                 fn()
             torch.cuda.synchronize()
             print(f"{name}: {(time.perf_counter() - t0) / 5 * 1e3:.2f} ms")
+    elif what in ("c2", "c2_time"):      # C2 intersection launches: coherent closest, incoherent closest, coherent any, incoherent any
+        import torch
+        sd = scenes.c2_scene()
+        sc = mi.Scene(sd, device=0)
+        for kind in ("coherent", "incoherent"):
+            om, dm = scenes.c2_rays(sd, kind)
+            _, dms = scenes.c2_rays(sd, kind + "_shadow")
+            o_t, d_t, ds_t = (torch.from_numpy(x).cuda() for x in (om, dm, dms))
+            reps = 12 if what == "c2_time" else 1
+            for mode, fn, dd in (("closest", sc.intersect_closest_raw, d_t), ("any", sc.intersect_any_raw, ds_t)):
+                ms = []
+                for _ in range(reps):
+                    fn(o_t, dd)
+                    ms.append(sc.last_stats["ms_total"])
+                print(kind, mode, f"{om.shape[0] / (float(np.median(ms)) * 1e-3) / 1e6:.1f} Mrays/s")
     elif what == "spectral":
         sd = scenes.c3_scene()
         sd.mode = "spectral"
