@@ -180,6 +180,10 @@ int mtsb_ctx_create(int device, mtsb_ctx **out);
 int mtsb_ctx_destroy(mtsb_ctx *ctx);
 /* `Integrator::cancel()` (include/mitsuba/render/integrator.h:51): async-signal-safe flag */
 int mtsb_cancel(mtsb_ctx *ctx);
+/* `timeout` property of SamplingIntegrator (src/librender/integrator.cpp:36, should_stop() integrator.h:143-146): a render
+ * that has run longer than `seconds` stops starting new batches and returns MTSB_OK with what was rendered
+ * (mtsb_stats.samples < requested); <= 0 disables.  Like mtsb_cancel it acts within two wavefront batches. */
+int mtsb_set_timeout(mtsb_ctx *ctx, float seconds);
 /* per-stage CUDA-event timing (the reference's SIGPROF phase profiler, src/libcore/profiler.cpp, re-stated as
  * event pairs around every launch on the launching stream); fills mtsb_stats.ms_{raygen,closest,shade,any,film} */
 int mtsb_set_profiling(mtsb_ctx *ctx, int on);
@@ -222,6 +226,11 @@ uint64_t mtsb_noalloc_max_rays(void);
 int mtsb_render(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
                 uint32_t spp_total, uint64_t seed, mtsb_stats *stats);
 int mtsb_film_clear(mtsb_scene *scene, uint32_t sensor_id);
+/* `moment` integrator (src/integrators/moment.cpp:55-90): when enabled, every splat also accumulates the squares of the
+ * sample's X, Y, Z with the same filter weight -- the `m2_<nested>.X/Y/Z` AOV channels.  mtsb_film_read_moments returns
+ * width*height*3 float32 SUMS (divide by the film's W channel like every other channel); mtsb_film_clear clears them. */
+int mtsb_film_enable_moments(mtsb_scene *scene, uint32_t sensor_id, int on);
+int mtsb_film_read_moments(mtsb_scene *scene, uint32_t sensor_id, float *m2_xyz, int mem);
 /* `Film::put(ImageBlock*)`-side export: packed float32 XYZAW, width*height*5 (integrator.cpp:72-74) */
 int mtsb_film_read(mtsb_scene *scene, uint32_t sensor_id, float *xyzaw, int mem);
 /* add an external XYZAW buffer into the device film (used after the NCCL reduce and for resume) */

@@ -86,6 +86,7 @@ SYMBOLS = [
     ("mtsb_ctx_destroy", C.c_int, [vp]),
     ("mtsb_cancel", C.c_int, [vp]),
     ("mtsb_set_profiling", C.c_int, [vp, C.c_int]),
+    ("mtsb_set_timeout", C.c_int, [vp, C.c_float]),
     ("mtsb_scene_create", C.c_int, [vp, C.POINTER(SceneDesc), C.POINTER(vp)]),
     ("mtsb_scene_destroy", C.c_int, [vp]),
     ("mtsb_scene_stats", C.c_int, [vp, C.POINTER(Stats)]),
@@ -99,6 +100,8 @@ SYMBOLS = [
     ("mtsb_render", C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(Stats)]),
     ("mtsb_film_clear", C.c_int, [vp, C.c_uint32]),
     ("mtsb_film_read", C.c_int, [vp, C.c_uint32, vp, C.c_int]),
+    ("mtsb_film_enable_moments", C.c_int, [vp, C.c_uint32, C.c_int]),
+    ("mtsb_film_read_moments", C.c_int, [vp, C.c_uint32, vp, C.c_int]),
     ("mtsb_film_accumulate", C.c_int, [vp, C.c_uint32, vp, C.c_int]),
     ("mtsb_film_develop", C.c_int, [vp, C.c_uint32, vp, C.c_int]),
     ("mtsb_film_device_ptr", C.c_int, [vp, C.c_uint32, C.POINTER(vp), C.POINTER(C.c_uint64)]),

@@ -13,6 +13,7 @@
 #include <memory>
 #include <cstring>
 #include <cstdio>
+#include <chrono>
 
 using namespace mtsb;
 
@@ -43,6 +44,8 @@ template <typename T> struct DevBuf {
 
 struct mtsb_ctx {
     int device; cudaStream_t stream; cudaEvent_t ev0, ev1; volatile int cancel;
+    cudaEvent_t ring[2];                     // one event per in-flight render batch (mtsb_render keeps at most two queued)
+    float timeout = -1.f;                    // seconds; <= 0: none (mtsb_set_timeout)
     int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
     int bin_materials = 1;                   // sort queue entries by material class before shading (MTSB_BIN=0 disables)
     unsigned trace_grid = 148 * 8, refill = 22; // persistent traversal launch shape (set in mtsb_ctx_create)
@@ -68,10 +71,15 @@ static void collect_stage_times(mtsb_ctx *c, mtsb_stats *st) {   // call after t
     if (st) { st->ms_raygen = acc[ST_RAYGEN]; st->ms_closest = acc[ST_CLOSEST]; st->ms_shade = acc[ST_SHADE]; st->ms_any = acc[ST_ANY]; st->ms_film = acc[ST_FILM]; }
 }
 
-struct SensorHost { SensorDev dev; DevBuf<float4> xyza; DevBuf<float> w; DevBuf<float> packed; };
+struct SensorHost { SensorDev dev; DevBuf<float4> xyza, m2; DevBuf<float> w; DevBuf<float> packed; };
 
+struct BuildScratch {
+    DevBuf<float4> tlo, thi, nlo, nhi; DevBuf<uint64_t> keys, keys2; DevBuf<uint32_t> order, order2, rfirst, rlast, flags, counters;
+    DevBuf<int> left, right, parent, wide_bin, d_count; DevBuf<float> bounds; DevBuf<unsigned char> sort_tmp, select_tmp;
+};
 struct mtsb_scene {
     mtsb_ctx *ctx;
+    BuildScratch build_scratch;
     // host copies needed for updates
     std::vector<MeshDev> meshes; std::vector<std::vector<uint32_t>> mesh_faces; std::vector<bool> computed_normals;
     std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
@@ -119,6 +127,7 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
     c->device = device; c->cancel = 0;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1));
+    CU(cudaEventCreateWithFlags(&c->ring[0], cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&c->ring[1], cudaEventDisableTiming));
     {   // persistent traversal grid: resident blocks per SM x SM count (tunable for experiments)
         int sms = 148, per_sm = 8, occ = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
@@ -136,11 +145,12 @@ extern "C" int mtsb_ctx_destroy(mtsb_ctx *c) {
     if (!c) return MTSB_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaStreamDestroy(c->stream);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ring[0]); cudaEventDestroy(c->ring[1]); cudaStreamDestroy(c->stream);
     delete c;
     return MTSB_OK;
 }
 extern "C" int mtsb_cancel(mtsb_ctx *c) { if (c) c->cancel = 1; return MTSB_OK; }
+extern "C" int mtsb_set_timeout(mtsb_ctx *c, float seconds) { if (!c) return fail(MTSB_E_INVALID, "null context"); c->timeout = seconds; return MTSB_OK; }
 extern "C" int mtsb_set_profiling(mtsb_ctx *c, int on) { if (!c) return fail(MTSB_E_INVALID, "null context"); c->profiling = on; return MTSB_OK; }
 
 static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) / kBlock); }
@@ -163,8 +173,11 @@ static int build_bvh(mtsb_scene *s) {
     s->build_stats.bvh_nodes = 0; s->build_stats.bvh_depth = 0;
     if (n == 0) { s->dev.bvh.nodes = nullptr; s->dev.bvh.tris = nullptr; return MTSB_OK; }
     CU(cudaEventRecord(s->ctx->ev0, st));
-    DevBuf<float4> tlo, thi, nlo, nhi; DevBuf<uint64_t> keys, keys2; DevBuf<uint32_t> order, order2, rfirst, rlast, flags, counters;
-    DevBuf<int> left, right, parent, wide_bin; DevBuf<float> bounds;
+    // build scratch lives in a per-scene arena: a rebuild after `parameters_changed` allocates nothing (DevBuf::alloc keeps a large-enough buffer)
+    BuildScratch &bs = s->build_scratch;
+    DevBuf<float4> &tlo = bs.tlo, &thi = bs.thi, &nlo = bs.nlo, &nhi = bs.nhi; DevBuf<uint64_t> &keys = bs.keys, &keys2 = bs.keys2;
+    DevBuf<uint32_t> &order = bs.order, &order2 = bs.order2, &rfirst = bs.rfirst, &rlast = bs.rlast, &flags = bs.flags, &counters = bs.counters;
+    DevBuf<int> &left = bs.left, &right = bs.right, &parent = bs.parent, &wide_bin = bs.wide_bin; DevBuf<float> &bounds = bs.bounds;
     CU(tlo.alloc(n)); CU(thi.alloc(n)); CU(nlo.alloc(2 * (size_t) n)); CU(nhi.alloc(2 * (size_t) n));
     CU(keys.alloc(n)); CU(keys2.alloc(n)); CU(order.alloc(n)); CU(order2.alloc(n));
     CU(rfirst.alloc(n)); CU(rlast.alloc(n)); CU(flags.alloc(n)); CU(counters.alloc(2));
@@ -188,7 +201,7 @@ static int build_bvh(mtsb_scene *s) {
     {   // radix sort (library primitive; the build is not on the per-ray hot path)
         size_t tmp_bytes = 0;
         CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys2.p, order.p, order2.p, (int) n, 0, 63, st));
-        DevBuf<unsigned char> tmp; CU(tmp.alloc(tmp_bytes));
+        DevBuf<unsigned char> &tmp = bs.sort_tmp; CU(tmp.alloc(tmp_bytes));
         CU(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, keys2.p, order.p, order2.p, (int) n, 0, 63, st));
         CU(cudaStreamSynchronize(st));
         b.keys = keys2.p; b.order = order2.p;
@@ -203,7 +216,7 @@ static int build_bvh(mtsb_scene *s) {
         uint32_t zero = 0;
         CU(cudaMemcpyAsync(counters.p, &zero, sizeof(zero), cudaMemcpyHostToDevice, st));
         k_ploc_init<<<grid_for(n), kBlock, 0, st>>>(b, cur);
-        DevBuf<unsigned char> tmp; DevBuf<int> d_count; CU(d_count.alloc(1));
+        DevBuf<unsigned char> &tmp = bs.select_tmp; DevBuf<int> &d_count = bs.d_count; CU(d_count.alloc(1));
         size_t tmp_bytes = 0;
         CU(cub::DeviceSelect::If(nullptr, tmp_bytes, nxt, cur, d_count.p, (int) n, PlocAlive(), st));
         CU(tmp.alloc(tmp_bytes));
@@ -683,13 +696,19 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
     RC(ensure_pool(s, pool));
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaEventRecord(s->ctx->ev0, st));
-    uint64_t launches = 0;
+    uint64_t launches = 0, started = 0; int nb = 0;
+    const auto t_start = std::chrono::steady_clock::now();
     for (uint64_t off = 0; off < total; off += pool) {
+        // at most two batches are queued ahead of the GPU, so `cancel` and `timeout` (Integrator::should_stop,
+        // include/mitsuba/render/integrator.h:143-146) act within two batch times instead of after the whole job was enqueued
+        if (nb >= 2) CU(cudaEventSynchronize(s->ctx->ring[nb & 1]));
         if (s->ctx->cancel) { s->ctx->cancel = 0; cudaStreamSynchronize(st); return fail(MTSB_E_CANCELLED, "render cancelled"); }
+        if (s->ctx->timeout > 0.f && std::chrono::duration<float>(std::chrono::steady_clock::now() - t_start).count() > s->ctx->timeout) break;
         uint32_t n = (uint32_t) ((total - off) < pool ? (total - off) : pool);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total;
         b.seed = seed; b.result = s->result.p;
         RC(run_batch(s, sn, b, nullptr, true, launches));
+        CU(cudaEventRecord(s->ctx->ring[nb & 1], st)); nb++; started += n;
     }
     CU(cudaEventRecord(s->ctx->ev1, st));
     unsigned long long hs[4];
@@ -698,7 +717,7 @@ extern "C" int mtsb_render(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_begin
     CU(cudaGetLastError());
     if (stats) {
         memset(stats, 0, sizeof(*stats));
-        stats->samples = total; stats->closest_rays = hs[0]; stats->shadow_rays = hs[1]; stats->segments = hs[2];
+        stats->samples = started; stats->closest_rays = hs[0];      // < total when the timeout stopped the job (the film holds what was rendered) stats->shadow_rays = hs[1]; stats->segments = hs[2];
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, s->ctx->ev0, s->ctx->ev1));
     }
@@ -714,6 +733,30 @@ extern "C" int mtsb_film_clear(mtsb_scene *s, uint32_t sensor_id) {
     CU(cudaSetDevice(s->ctx->device));
     SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
     CU(cudaMemsetAsync(sh.xyza.p, 0, npx * sizeof(float4), s->ctx->stream)); CU(cudaMemsetAsync(sh.w.p, 0, npx * sizeof(float), s->ctx->stream));
+    if (sh.dev.film_m2) CU(cudaMemsetAsync(sh.m2.p, 0, npx * sizeof(float4), s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return MTSB_OK;
+}
+// `moment` integrator (src/integrators/moment.cpp): second-moment AOVs of the nested integrator's XYZ value
+extern "C" int mtsb_film_enable_moments(mtsb_scene *s, uint32_t sensor_id, int on) {
+    CHECK_ARG(s && sensor_id < s->sensors.size());
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    if (on) {
+        CU(sh.m2.alloc(npx));
+        CU(cudaMemsetAsync(sh.m2.p, 0, npx * sizeof(float4), s->ctx->stream)); CU(cudaStreamSynchronize(s->ctx->stream));
+        sh.dev.film_m2 = sh.m2.p;
+    } else sh.dev.film_m2 = nullptr;
+    return MTSB_OK;
+}
+extern "C" int mtsb_film_read_moments(mtsb_scene *s, uint32_t sensor_id, float *m2_xyz, int mem) {
+    CHECK_ARG(s && sensor_id < s->sensors.size() && m2_xyz);
+    CU(cudaSetDevice(s->ctx->device));
+    SensorHost &sh = *s->sensors[sensor_id]; size_t npx = (size_t) sh.dev.width * sh.dev.height;
+    if (!sh.dev.film_m2) return fail(MTSB_E_INVALID, "second moments are not enabled for this sensor (mtsb_film_enable_moments)");
+    Staging sg; float *d_out; RC(sg.out(m2_xyz, 3 * npx, mem, &d_out));
+    k_film_pack_m2<<<grid_for(npx), kBlock, 0, s->ctx->stream>>>(sh.dev, d_out);
+    RC(sg.back(m2_xyz, d_out, 3 * npx, mem, s->ctx->stream));
     CU(cudaStreamSynchronize(s->ctx->stream));
     return MTSB_OK;
 }
@@ -773,50 +816,26 @@ extern "C" int mtsb_film_put(mtsb_scene *s, uint32_t sensor_id, uint64_t n, cons
 // ---------------------------------------------------------------------------------------------------
 // Parameter updates (Mesh::parameters_changed, BitmapTexture::parameters_changed)
 // ---------------------------------------------------------------------------------------------------
-// Mesh::recompute_vertex_normals (src/librender/mesh.cpp:199-276, dynamic-array branch: angle-weighted)
-static void host_recompute_normals(const float *pos, const uint32_t *faces, uint32_t nf, uint32_t nv, float *out) {
-    std::vector<double> acc(3 * (size_t) nv, 0.0);
-    for (uint32_t f = 0; f < nf; ++f) {
-        uint32_t idx[3] = { faces[3 * f], faces[3 * f + 1], faces[3 * f + 2] };
-        float3 v[3]; for (int k = 0; k < 3; ++k) v[k] = mk3(pos[3 * idx[k]], pos[3 * idx[k] + 1], pos[3 * idx[k] + 2]);
-        float3 n = cross(v[1] - v[0], v[2] - v[0]);
-        float l2 = dot(n, n);
-        if (!(l2 > 0.f)) continue;
-        n = n * (1.f / sqrtf(l2));
-        for (int k = 0; k < 3; ++k) {
-            float3 d0 = normalize(v[(k + 1) % 3] - v[k]), d1 = normalize(v[(k + 2) % 3] - v[k]);
-            // enoki unit_angle: numerically robust angle between unit vectors
-            float dp = dot(d0, d1);
-            float3 df = d1 - (dp < 0.f ? -d0 : d0);
-            float temp = 2.f * asinf(fminf(1.f, 0.5f * norm(df)));
-            float ang = dp >= 0.f ? temp : kPi - temp;
-            acc[3 * idx[k]] += n.x * ang; acc[3 * idx[k] + 1] += n.y * ang; acc[3 * idx[k] + 2] += n.z * ang;
-        }
-    }
-    for (uint32_t i = 0; i < nv; ++i) {
-        double x = acc[3 * i], y = acc[3 * i + 1], z = acc[3 * i + 2], l = sqrt(x * x + y * y + z * z);
-        if (l != 0.0) { out[3 * i] = (float) (x / l); out[3 * i + 1] = (float) (y / l); out[3 * i + 2] = (float) (z / l); }
-        else { out[3 * i] = 1.f; out[3 * i + 1] = 0.f; out[3 * i + 2] = 0.f; }
-    }
-}
-
 extern "C" int mtsb_scene_update_vertices(mtsb_scene *s, uint32_t mesh_id, const float *positions, int mem) {
     CHECK_ARG(s && mesh_id < s->meshes.size() && positions);
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     const MeshDev &m = s->meshes[mesh_id];
-    float *hp = s->h_pos.data() + 3 * (size_t) m.vert_begin;
-    if (mem == MTSB_MEM_DEVICE) { CU(cudaMemcpyAsync(hp, positions, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
-    else memcpy(hp, positions, 3 * (size_t) m.vert_count * sizeof(float));
-    CU(cudaMemcpyAsync(s->pos.p + 3 * (size_t) m.vert_begin, hp, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyHostToDevice, st));
-    if (m.has_normals) {
-        float *hn = s->h_nrm.data() + 3 * (size_t) m.vert_begin;
-        host_recompute_normals(hp, s->mesh_faces[mesh_id].data(), m.face_count, m.vert_count, hn);
-        CU(cudaMemcpyAsync(s->nrm.p + 3 * (size_t) m.vert_begin, hn, 3 * (size_t) m.vert_count * sizeof(float), cudaMemcpyHostToDevice, st));
+    const size_t nf = 3 * (size_t) m.vert_count;
+    float *dp = s->pos.p + 3 * (size_t) m.vert_begin, *hp = s->h_pos.data() + 3 * (size_t) m.vert_begin;
+    // positions go straight to the device array (device callers: one D2D copy, no host round trip); the host copy is only
+    // refreshed for emitter meshes, whose area CDF is rebuilt on the host in double like the reference (distr_1d.h:49-88)
+    CU(cudaMemcpyAsync(dp, positions, nf * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    if (mem == MTSB_MEM_HOST) memcpy(hp, positions, nf * sizeof(float));
+    else if (m.emitter >= 0) { CU(cudaMemcpyAsync(hp, positions, nf * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+    if (m.has_normals) {      // Mesh::parameters_changed -> recompute_vertex_normals (mesh.cpp:794-804, 199-276), on the device
+        float *dn = s->nrm.p + 3 * (size_t) m.vert_begin;
+        CU(cudaMemsetAsync(dn, 0, nf * sizeof(float), st));
+        k_vnormal_faces<<<grid_for(m.face_count), kBlock, 0, st>>>(s->pos.p, s->faces.p, m.face_begin, m.face_count, s->nrm.p);
+        k_vnormal_normalize<<<grid_for(m.vert_count), kBlock, 0, st>>>(dn, m.vert_count);
     }
-    CU(cudaStreamSynchronize(st));
     RC(build_bvh(s));
-    RC(build_area_tables(s));
+    if (m.emitter >= 0) RC(build_area_tables(s));
     update_env_bsphere(s);
     return upload_struct_arrays(s);
 }

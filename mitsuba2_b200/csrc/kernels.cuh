@@ -89,6 +89,41 @@ __global__ void k_rough_tables(int distr_type, float alpha, float eta, const flo
     out[i] = rough_boundary_integral(distr_type, alpha, e, rough_table_mu((int) (i % kRoughTransRes)), res == 32 ? n32 : n128, res == 32 ? w32 : w128, res, transmit);
 }
 
+// ---------------- Mesh::recompute_vertex_normals on the device (src/librender/mesh.cpp:199-276) ------------------------
+// Angle-weighted face normals (Thuermer & Wuethrich 1998) scattered to the three corners with float atomics -- the
+// reference's own vectorised branch does the same with scatter_add (:258-275); its scalar branch accumulates in float in
+// face order, so the two differ by float association only (tests: <= 2e-6 per component).
+__global__ void k_vnormal_faces(const float *__restrict__ pos, const uint4 *__restrict__ faces, uint32_t face_begin, uint32_t face_count, float *nrm) {
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= face_count) return;
+    uint4 fi = faces[face_begin + f];
+    uint32_t idx[3] = { fi.x, fi.y, fi.z };
+    float3 v[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) v[k] = mk3(pos[3 * idx[k]], pos[3 * idx[k] + 1], pos[3 * idx[k] + 2]);
+    float3 n = cross(v[1] - v[0], v[2] - v[0]);
+    float l2 = dot(n, n);
+    if (!(l2 > 0.f)) return;
+    n = n * (1.f / sqrtf(l2));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float3 d0 = normalize(v[(k + 1) % 3] - v[k]), d1 = normalize(v[(k + 2) % 3] - v[k]);
+        float dp = dot(d0, d1);                                   // enoki unit_angle: robust angle between unit vectors
+        float3 df = d1 - (dp < 0.f ? -d0 : d0);
+        float temp = 2.f * asinf(fminf(1.f, 0.5f * norm(df)));
+        float ang = dp >= 0.f ? temp : kPi - temp;
+        atomicAdd(&nrm[3 * idx[k]], n.x * ang); atomicAdd(&nrm[3 * idx[k] + 1], n.y * ang); atomicAdd(&nrm[3 * idx[k] + 2], n.z * ang);
+    }
+}
+__global__ void k_vnormal_normalize(float *nrm, uint32_t count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float3 n = mk3(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]);
+    float l = norm(n);
+    n = l != 0.f ? n * (1.f / l) : mk3(1.f, 0.f, 0.f);          // "some bogus value" (mesh.cpp:247)
+    nrm[3 * i] = n.x; nrm[3 * i + 1] = n.y; nrm[3 * i + 2] = n.z;
+}
+
 // ---------------- traversal ----------------------------------------------------------------------
 // Persistent-warp traversal with dynamic ray fetch (after Aila & Laine 2009): the grid is sized to fill the SMs once;
 // every warp claims chunks of kFetchChunk consecutive rays from a global work counter and hands them to lanes whose
@@ -505,6 +540,12 @@ __device__ __forceinline__ void film_atomic_add(const SensorDev &sn, uint32_t pi
     atomicAdd(&sn.film_w[pix], w);
 }
 
+// second moments of the per-sample XYZ value, weighted like every other film channel: the `m2_<nested>.X/Y/Z` AOVs of the
+// `moment` integrator (src/integrators/moment.cpp:55-90); v = filter weight * xyz, x = xyz
+__device__ __forceinline__ void film_atomic_add_m2(const SensorDev &sn, uint32_t pix, float4 v, float4 x) {
+    atomicAdd(&sn.film_m2[pix], make_float4(v.x * x.x, v.y * x.y, v.z * x.z, 0.f));
+}
+
 // film splat at batch end with warp-aggregated atomics (one atomic set per warp when the warp's samples share a pixel)
 template <typename M>
 __global__ void __launch_bounds__(kBlock)
@@ -519,17 +560,22 @@ k_splat(SensorDev sn, RenderBatch b) {
         uint32_t pix = ok ? (uint32_t) (ly * (int) sn.width + lx) : 0xffffffffu;
         if (!ok) { xyza = make_float4(0.f, 0.f, 0.f, 0.f); wgt = 0.f; }
         uint32_t p0 = __shfl_sync(0xffffffffu, pix, 0);
+        const bool m2 = sn.film_m2 != nullptr;
+        float4 sq = make_float4(xyza.x * xyza.x, xyza.y * xyza.y, xyza.z * xyza.z, 0.f);
         if (__all_sync(0xffffffffu, pix == p0)) {
             for (int o = 16; o > 0; o >>= 1) {
                 xyza.x += __shfl_xor_sync(0xffffffffu, xyza.x, o); xyza.y += __shfl_xor_sync(0xffffffffu, xyza.y, o);
                 xyza.z += __shfl_xor_sync(0xffffffffu, xyza.z, o); xyza.w += __shfl_xor_sync(0xffffffffu, xyza.w, o);
                 wgt += __shfl_xor_sync(0xffffffffu, wgt, o);
+                if (m2) { sq.x += __shfl_xor_sync(0xffffffffu, sq.x, o); sq.y += __shfl_xor_sync(0xffffffffu, sq.y, o); sq.z += __shfl_xor_sync(0xffffffffu, sq.z, o); }
             }
-            if ((threadIdx.x & 31) == 0 && pix != 0xffffffffu) film_atomic_add(sn, pix, xyza, wgt);
-        } else if (ok)
+            if ((threadIdx.x & 31) == 0 && pix != 0xffffffffu) { film_atomic_add(sn, pix, xyza, wgt); if (m2) atomicAdd(&sn.film_m2[pix], sq); }
+        } else if (ok) {
             film_atomic_add(sn, pix, xyza, wgt);
+            if (m2) atomicAdd(&sn.film_m2[pix], sq);
+        }
     } else if (live) {
-        film_put(sn, fx, fy, xyza, wgt, [&](uint32_t pix, float4 v, float w) { film_atomic_add(sn, pix, v, w); });
+        film_put(sn, fx, fy, xyza, wgt, [&](uint32_t pix, float4 v, float w) { film_atomic_add(sn, pix, v, w); if (sn.film_m2 != nullptr) film_atomic_add_m2(sn, pix, v, xyza); });
     }
 }
 
@@ -547,6 +593,12 @@ __global__ void k_film_pack(SensorDev sn, float *xyzaw) {
     if (i >= sn.width * sn.height) return;
     float4 v = sn.film_xyza[i];
     xyzaw[5 * i] = v.x; xyzaw[5 * i + 1] = v.y; xyzaw[5 * i + 2] = v.z; xyzaw[5 * i + 3] = v.w; xyzaw[5 * i + 4] = sn.film_w[i];
+}
+__global__ void k_film_pack_m2(SensorDev sn, float *m2) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sn.width * sn.height) return;
+    float4 v = sn.film_m2[i];
+    m2[3 * i] = v.x; m2[3 * i + 1] = v.y; m2[3 * i + 2] = v.z;
 }
 __global__ void k_film_unpack_add(SensorDev sn, const float *xyzaw, int replace) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -46,6 +46,7 @@ struct SensorDev {
     int rfilter; float radius, stddev;   // radius already includes box RayEpsilon; stddev doubles as Mitchell's B
     float filter_c;                      // Mitchell's C
     float4 *film_xyza; float *film_w;    // device film accumulators
+    float4 *film_m2;                     // optional second-moment plane (sum of w X^2, w Y^2, w Z^2): `moment` integrator AOVs
 };
 struct SceneDev {
     Bvh bvh;

@@ -64,11 +64,11 @@ HD float3 tex_eval_rgb(const SceneDev &sc, int id, float u, float v) {
     float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
     uint32_t idx = px + py * t.w;
     if (t.ch == 1) {
-        float v00 = t.data[idx], v10 = t.data[idx + 1], v01 = t.data[idx + t.w], v11 = t.data[idx + t.w + 1];
+        float v00 = ldgf(t.data + idx), v10 = ldgf(t.data + idx + 1), v01 = ldgf(t.data + idx + t.w), v11 = ldgf(t.data + idx + t.w + 1);
         float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
         return mk3(fmaf(w0y, v0, w1y * v1));
     }
-    float3 v00 = ld3(t.data, idx), v10 = ld3(t.data, idx + 1), v01 = ld3(t.data, idx + t.w), v11 = ld3(t.data, idx + t.w + 1);
+    float3 v00 = ldg3(t.data, idx), v10 = ldg3(t.data, idx + 1), v01 = ldg3(t.data, idx + t.w), v11 = ldg3(t.data, idx + t.w + 1);
     float3 v0 = mk3(fmaf(w0x, v00.x, w1x * v10.x), fmaf(w0x, v00.y, w1x * v10.y), fmaf(w0x, v00.z, w1x * v10.z));
     float3 v1 = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
     return mk3(fmaf(w0y, v0.x, w1y * v1.x), fmaf(w0y, v0.y, w1y * v1.y), fmaf(w0y, v0.z, w1y * v1.z));
@@ -98,11 +98,11 @@ float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wa
         uint32_t idx = px + py * t.w;
         auto blend = [&](float a, float b) { return fmaf(w0x, a, w1x * b); };
         if (t.ch == 1) {
-            float v0 = blend(t.data[idx], t.data[idx + 1]), v1 = blend(t.data[idx + t.w], t.data[idx + t.w + 1]);
+            float v0 = blend(ldgf(t.data + idx), ldgf(t.data + idx + 1)), v1 = blend(ldgf(t.data + idx + t.w), ldgf(t.data + idx + t.w + 1));
             r = mk4(fmaf(w0y, v0, w1y * v1));
         } else {
-            float4 c00 = srgb_model_eval(ld3(t.data, idx), wav), c10 = srgb_model_eval(ld3(t.data, idx + 1), wav),
-                   c01 = srgb_model_eval(ld3(t.data, idx + t.w), wav), c11 = srgb_model_eval(ld3(t.data, idx + t.w + 1), wav);
+            float4 c00 = srgb_model_eval(ldg3(t.data, idx), wav), c10 = srgb_model_eval(ldg3(t.data, idx + 1), wav),
+                   c01 = srgb_model_eval(ldg3(t.data, idx + t.w), wav), c11 = srgb_model_eval(ldg3(t.data, idx + t.w + 1), wav);
             float4 c0 = map_spec(c00, c10, blend), c1 = map_spec(c01, c11, blend);
             r = map_spec(c0, c1, [&](float a, float b) { return fmaf(w0y, a, w1y * b); });
         }

@@ -59,6 +59,9 @@ class Scene:
         A.check(A.lib().mtsb_scene_create(self._ctx, C.byref(desc), C.byref(self._h)))
         del keep
         self.last_stats = None
+        if getattr(data, "moment", False):      # <integrator type="moment"> around `path` (src/integrators/moment.cpp)
+            for i in range(len(data.sensors)):
+                self.enable_moments(True, i)
         prim_counts = [m.faces.shape[0] for m in data.meshes]
         self.primitive_map = np.concatenate([[0], np.cumsum(prim_counts)]).astype(np.int64)
 
@@ -159,11 +162,41 @@ class Scene:
         self.last_stats = st.as_dict()
         return self.last_stats
 
-    def render(self, sensor=0, spp=None, seed=0):
-        """``Integrator.render`` + ``Film.bitmap()``: clears the film, renders, returns linear RGB (H,W,3) float32."""
+    def render(self, sensor=0, spp=None, seed=0, samples_per_pass=None, timeout=None, progress=None):
+        """``Integrator.render`` + ``Film.bitmap()``: clears the film, renders, returns linear RGB (H,W,3) float32.
+
+        ``samples_per_pass`` / ``timeout`` are the properties of ``SamplingIntegrator`` (src/librender/integrator.cpp:35-36,
+        60-66): the job runs as spp / samples_per_pass passes over the film (``progress(pass_index, n_passes, scene)`` is called
+        after each, e.g. to develop a preview), and a job that exceeds ``timeout`` seconds stops early and returns the partial
+        film, as the reference does.  A concurrent :meth:`cancel` raises :class:`~mitsuba2_b200._abi.MtsbError` (code -4)."""
+        import time
+        spp = int(self.data.spp if spp is None else spp)
+        per_pass = spp if samples_per_pass in (None, -1) else min(int(samples_per_pass), spp)
+        if per_pass <= 0 or spp % per_pass != 0:
+            raise ValueError(f"sample_count ({spp}) must be a multiple of samples_per_pass ({samples_per_pass}).")
+        n_passes, t0 = spp // per_pass, time.perf_counter()
         self.film_clear(sensor)
-        self.render_accumulate(sensor, spp, seed)
+        try:
+            for k in range(n_passes):
+                if timeout is not None and timeout > 0:
+                    left = timeout - (time.perf_counter() - t0)
+                    if left <= 0:
+                        break
+                    self.set_timeout(left)
+                self.render_accumulate(sensor, per_pass, seed, k * per_pass, spp)
+                if progress is not None:
+                    progress(k, n_passes, self)
+        finally:
+            if timeout is not None:
+                self.set_timeout(-1.0)
         return self.film_develop(sensor)
+
+    def cancel(self):
+        """``Integrator.cancel()`` (include/mitsuba/render/integrator.h:51): may be called from another thread."""
+        A.check(A.lib().mtsb_cancel(self._ctx))
+
+    def set_timeout(self, seconds):
+        A.check(A.lib().mtsb_set_timeout(self._ctx, float(seconds)))
 
     def film_clear(self, sensor=0):
         A.check(A.lib().mtsb_film_clear(self._h, sensor))
@@ -177,6 +210,27 @@ class Scene:
         out = np.empty((h, w, 5), np.float32)
         A.check(A.lib().mtsb_film_read(self._h, sensor, C.c_void_p(out.ctypes.data), A.MEM_HOST))
         return out
+
+    def enable_moments(self, on=True, sensor=0):
+        """Second-moment AOVs of the ``moment`` integrator (src/integrators/moment.cpp:55-90) for later renders."""
+        A.check(A.lib().mtsb_film_enable_moments(self._h, sensor, int(bool(on))))
+
+    def film_moments(self, sensor=0):
+        """(H,W,3) sums of w X^2, w Y^2, w Z^2 -- the ``m2_<nested>.X/Y/Z`` channels before the division by W."""
+        h, w = self._film_shape(sensor)
+        out = np.empty((h, w, 3), np.float32)
+        A.check(A.lib().mtsb_film_read_moments(self._h, sensor, C.c_void_p(out.ctypes.data), A.MEM_HOST))
+        return out
+
+    def render_moments(self, sensor=0, spp=None, seed=0):
+        """``moment(path)``: -> (E[xyz], E[xyz^2]) per pixel, float64 (H,W,3) each, what the reference's render tests feed to
+        their z-test (src/librender/tests/test_renders.py:60-126: var = E[x^2] - E[x]^2)."""
+        self.enable_moments(True, sensor)
+        self.film_clear(sensor)
+        self.render_accumulate(sensor, spp, seed)
+        f = self.film_xyzaw(sensor).astype(np.float64)
+        w = np.maximum(f[:, :, 4:5], 1e-12)
+        return f[:, :, :3] / w, self.film_moments(sensor).astype(np.float64) / w
 
     def film_accumulate(self, xyzaw, sensor=0):
         p, mem, keep = _arg(xyzaw, np.float32, device=self.device)

@@ -18,6 +18,16 @@ def synthetic_envmap(w=1024, h=512, seed=7):
     return img.astype(np.float32)
 
 
+def c3_envmap():
+    """-> (rgb image, name): resources/data/envmap/museum.exr of the reference where tools/fetch_reference_data.py has
+    copied it into mitsuba2_b200/data/ (SURVEY 8(d) names it for C3), else the synthetic sky.  MTSB_C3_ENVMAP=synthetic forces the latter."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "museum_envmap.npy")
+    if os.environ.get("MTSB_C3_ENVMAP", "") != "synthetic" and os.path.exists(path):
+        return np.load(path), "museum.exr 1000x500 (reference resources/data/envmap)"
+    return synthetic_envmap(), "synthetic sky 1024x512 (museum.exr not present)"
+
+
 def c2_scene(n_theta=500, n_phi=1000, width=1920, height=1080):
     """C2: 1M-triangle displaced sphere, camera (0,0,-3.2)->0, fov 45 (x), near .01 far 100."""
     sd = SceneData()
@@ -77,7 +87,8 @@ def c3_scene(n_theta=1000, n_phi=2000, width=1920, height=1080, small=(158, 316)
     light = M.quad([-0.5, 3, -0.5], [0.5, 3, -0.5], [0.5, 3, 0.5], [-0.5, 3, 0.5])
     light.bsdf = sd.add_diffuse(0.5)
     sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
-    sd.add_envmap(synthetic_envmap())
+    env, sd.envmap_name = c3_envmap()
+    sd.add_envmap(env)
     sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, width, height, "box")
     sd.max_depth, sd.rr_depth, sd.spp = 6, 5, 1024
     return sd

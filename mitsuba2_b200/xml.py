@@ -383,6 +383,13 @@ class _Loader:
         self.sd.add_perspective(p.get("to_world", np.eye(4)), fov, p.get("near_clip", 1e-2), p.get("far_clip", 1e4), w, h,
                                 rtype, rp.get("stddev", 0.5), rp.get("radius"), rp.get("B", 1.0 / 3.0), rp.get("C", 1.0 / 3.0),
                                 rp.get("lobes", 3), crop)
+        # `high_quality_edges` (src/librender/film.cpp:32): parsed and reported (`Film::has_high_quality_edges`) but consulted
+        # by nothing in this reference snapshot -- neither Spiral nor render_sample extend the rendered region by the filter
+        # border -- so, like there, it does not change the render
+        self.sd.sensors[-1]["high_quality_edges"] = bool(fp.get("high_quality_edges", False))
+        for k in ("pixel_format", "component_format", "file_format"):      # hdrfilm.cpp:95-130 output encoding (host side)
+            if k in fp:
+                self.sd.sensors[-1][k] = fp[k]
 
     def load(self, root, base_dir):
         items = self.expand(root, base_dir)
@@ -412,6 +419,7 @@ class _Loader:
                     if len(inner) != 1:
                         raise NotImplementedError("moment: exactly one nested integrator is supported")
                     el, ty = inner[0], self.attr(inner[0], "type")
+                    self.sd.moment = True     # Scene enables the second-moment film plane (mtsb_film_enable_moments)
                 if ty != "path":
                     raise NotImplementedError(f"integrator '{ty}' is outside the hot-path scope (path)")
                 p = self.props(el)
