@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 5
+#define MTSB_ABI_VERSION 6
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -36,7 +36,11 @@ enum { MTSB_TEX_CONSTANT = 0, MTSB_TEX_BITMAP = 1,
        /* spectral mode only (MTSB_MODE_SPECTRAL): tabulated spectra, wavelengths in nm */
        MTSB_TEX_REGULAR = 2,    /* src/spectra/regular.cpp: `width` samples evenly spaced over [lambda_min, lambda_max] */
        MTSB_TEX_IRREGULAR = 3,  /* src/spectra/irregular.cpp: data = `width` wavelengths followed by `width` values */
-       MTSB_TEX_UNIFORM = 4 };  /* src/spectra/uniform.cpp: value[0] at every wavelength */
+       MTSB_TEX_UNIFORM = 4,    /* src/spectra/uniform.cpp: value[0] at every wavelength */
+       /* src/textures/mesh_attribute.cpp (-> Mesh::eval_attribute, include/mitsuba/render/mesh.h:278-318): attribute buffer of the
+        * mesh(es) whose BSDF uses the texture: `width` elements of `channels` (1 | 3) floats in `data`, `height` = 1: one
+        * element per face, 0: per vertex (barycentric interpolation); value[0] = `scale`.  Any colour mode (since ABI 6). */
+       MTSB_TEX_MESH_ATTRIBUTE = 5 };
 /* In spectral mode the host hands over what the reference's texture plugins store in that mode: CONSTANT `value` and
    3-channel BITMAP texels are sRGB-model coefficients (srgb_model_fetch, src/librender/srgb.cpp:15-42; srgb.cpp:44-48,
    bitmap.cpp:262-275), not colours.  d65_scale != 0 multiplies the value by the D65 whitepoint spectrum times d65_scale:
@@ -111,6 +115,9 @@ typedef struct mtsb_mesh_desc {
     uint32_t face_count, vertex_count;
     int32_t  bsdf_id;           /* index into bsdfs[] */
     int32_t  emitter_id;        /* index into emitters[] or -1 */
+    int32_t  mem;               /* MTSB_MEM_HOST (0, default) or MTSB_MEM_DEVICE: where faces / positions / normals / texcoords
+                                   live.  Either way the buffers are copied straight into the scene's device arrays (no host
+                                   staging copy); device buffers make scene creation a set of device-to-device copies (since ABI 6) */
 } mtsb_mesh_desc;
 
 /* Sensor + film: src/sensors/perspective.cpp:106-222, src/films/hdrfilm.cpp, rfilters. */

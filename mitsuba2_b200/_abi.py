@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
 
 MEM_HOST, MEM_DEVICE = 0, 1
-TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM = 0, 1, 2, 3, 4
+TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM, TEX_MESH_ATTRIBUTE = 0, 1, 2, 3, 4, 5
 MODE_RGB, MODE_SPECTRAL = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHDIELECTRIC, BSDF_ROUGHPLASTIC = 0, 1, 2, 3, 4, 5, 6
 MF_BECKMANN, MF_GGX = 0, 1
@@ -46,7 +46,7 @@ class EmitterDesc(C.Structure):
 class MeshDesc(C.Structure):
     _fields_ = [("faces", c_u32_p), ("positions", c_float_p), ("normals", c_float_p), ("texcoords", c_float_p),
                 ("face_count", C.c_uint32), ("vertex_count", C.c_uint32), ("bsdf_id", C.c_int32),
-                ("emitter_id", C.c_int32)]
+                ("emitter_id", C.c_int32), ("mem", C.c_int32)]
 
 
 class SensorDesc(C.Structure):

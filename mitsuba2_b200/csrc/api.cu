@@ -83,7 +83,7 @@ struct mtsb_scene {
     // host copies needed for updates
     std::vector<MeshDev> meshes; std::vector<std::vector<uint32_t>> mesh_faces; std::vector<bool> computed_normals;
     std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
-    std::vector<float> h_pos, h_nrm;
+    std::map<int, std::vector<float>> emitter_pos;   // host positions of EMITTER meshes only (area CDF is built on the host in double)
     // device
     DevBuf<float> pos, nrm, uv; DevBuf<uint4> faces;
     DevBuf<MeshDev> d_meshes; DevBuf<TexDev> d_tex; DevBuf<BsdfDev> d_bsdfs; DevBuf<EmitterDev> d_emitters;
@@ -123,7 +123,8 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
     CU(cudaGetDeviceCount(&n));
     if (device < 0 || device >= n) return fail(MTSB_E_INVALID, "no such CUDA device");
     CU(cudaSetDevice(device));
-    mtsb_ctx *c = new mtsb_ctx();
+    std::unique_ptr<mtsb_ctx> holder(new mtsb_ctx());       // released on any early return below
+    mtsb_ctx *c = holder.get();
     c->device = device; c->cancel = 0;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1));
@@ -138,7 +139,7 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
         c->trace_grid = (unsigned) (sms * per_sm);
         if (const char *e = getenv("MTSB_BIN")) c->bin_materials = atoi(e) != 0;
     }
-    *out = c;
+    *out = holder.release();
     return MTSB_OK;
 }
 extern "C" int mtsb_ctx_destroy(mtsb_ctx *c) {
@@ -293,7 +294,7 @@ static int build_area_tables(mtsb_scene *s) {
         if (em.type != MTSB_EMITTER_AREA) continue;
         const MeshDev &m = s->meshes[em.mesh];
         AreaTable t;
-        try { t = build_area_table(s->h_pos.data() + 3 * (size_t) m.vert_begin, s->mesh_faces[em.mesh].data(), m.face_count); }
+        try { t = build_area_table(s->emitter_pos.at(em.mesh).data(), s->mesh_faces[em.mesh].data(), m.face_count); }
         catch (const std::exception &ex) { return fail(MTSB_E_INVALID, ex.what()); }
         int ti = s->emitter_cdf_table[e];
         if (ti < 0) { s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1; s->emitter_cdf_table[e] = ti; }
@@ -328,35 +329,51 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
     s->ctx = ctx;
     memset(&s->dev, 0, sizeof(SceneDev)); memset(&s->build_stats, 0, sizeof(mtsb_stats));
     // ---- meshes
-    std::vector<float> h_uv; std::vector<uint4> h_faces;
+    // Direct-to-device upload: vertex data goes from the caller's buffers (host or device, mtsb_mesh_desc.mem) straight into
+    // the concatenated device arrays, faces are expanded to (i0, i1, i2, mesh) with global vertex indices by a kernel.
+    // Host copies are kept only where the host needs them: face indices (edge lists, area tables) and emitter positions.
+    size_t nv_total = 0, nf_total = 0;
+    for (uint32_t i = 0; i < d->n_meshes; ++i) { nv_total += d->meshes[i].vertex_count; nf_total += d->meshes[i].face_count; }
+    if (nf_total > (size_t) kPrimMask) return fail(MTSB_E_INVALID, "more than 2^30 - 1 triangles");
+    CU(s->pos.alloc(3 * nv_total)); CU(s->nrm.alloc(3 * nv_total)); CU(s->uv.alloc(2 * nv_total)); CU(s->faces.alloc(nf_total));
+    DevBuf<uint32_t> raw_faces;
     uint32_t vbase = 0, fbase = 0;
     for (uint32_t i = 0; i < d->n_meshes; ++i) {
         const mtsb_mesh_desc &m = d->meshes[i];
         CHECK_ARG(m.positions && (m.faces || m.face_count == 0));
         CHECK_ARG(m.bsdf_id >= 0 && (uint32_t) m.bsdf_id < d->n_bsdfs);
         CHECK_ARG(m.emitter_id < (int32_t) d->n_emitters);
+        CHECK_ARG(m.mem == MTSB_MEM_HOST || m.mem == MTSB_MEM_DEVICE);
+        const cudaMemcpyKind kind = m.mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
         MeshDev md; md.face_begin = fbase; md.face_count = m.face_count; md.vert_begin = vbase; md.vert_count = m.vertex_count;
         md.bsdf = m.bsdf_id; md.emitter = m.emitter_id; md.has_normals = m.normals != nullptr; md.has_uv = m.texcoords != nullptr;
         s->meshes.push_back(md);
-        s->h_pos.insert(s->h_pos.end(), m.positions, m.positions + 3 * (size_t) m.vertex_count);
-        if (m.normals) s->h_nrm.insert(s->h_nrm.end(), m.normals, m.normals + 3 * (size_t) m.vertex_count);
-        else s->h_nrm.insert(s->h_nrm.end(), 3 * (size_t) m.vertex_count, 0.f);
-        if (m.texcoords) h_uv.insert(h_uv.end(), m.texcoords, m.texcoords + 2 * (size_t) m.vertex_count);
-        else h_uv.insert(h_uv.end(), 2 * (size_t) m.vertex_count, 0.f);
-        s->mesh_faces.emplace_back(m.faces, m.faces + 3 * (size_t) m.face_count);
-        s->computed_normals.push_back(false);
-        if ((size_t) h_faces.size() + m.face_count > (size_t) kPrimMask) return fail(MTSB_E_INVALID, "more than 2^30 - 1 triangles");
-        for (uint32_t f = 0; f < m.face_count; ++f) {
-            uint32_t a = m.faces[3 * f], b = m.faces[3 * f + 1], c = m.faces[3 * f + 2];
-            if (a >= m.vertex_count || b >= m.vertex_count || c >= m.vertex_count) return fail(MTSB_E_INVALID, "face index out of range");
-            h_faces.push_back(make_uint4(a + vbase, b + vbase, c + vbase, i));
+        const size_t nv = m.vertex_count, nf = m.face_count;
+        CU(cudaMemcpyAsync(s->pos.p + 3 * (size_t) vbase, m.positions, 3 * nv * sizeof(float), kind, st));
+        if (m.normals) CU(cudaMemcpyAsync(s->nrm.p + 3 * (size_t) vbase, m.normals, 3 * nv * sizeof(float), kind, st));
+        else CU(cudaMemsetAsync(s->nrm.p + 3 * (size_t) vbase, 0, 3 * nv * sizeof(float), st));
+        if (m.texcoords) CU(cudaMemcpyAsync(s->uv.p + 2 * (size_t) vbase, m.texcoords, 2 * nv * sizeof(float), kind, st));
+        else CU(cudaMemsetAsync(s->uv.p + 2 * (size_t) vbase, 0, 2 * nv * sizeof(float), st));
+        // host copy of the indices (validated here; the device copy is expanded from the same values)
+        s->mesh_faces.emplace_back(3 * nf);
+        std::vector<uint32_t> &hf = s->mesh_faces.back();
+        if (m.mem == MTSB_MEM_DEVICE) { CU(cudaMemcpyAsync(hf.data(), m.faces, 3 * nf * sizeof(uint32_t), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+        else if (nf) memcpy(hf.data(), m.faces, 3 * nf * sizeof(uint32_t));
+        for (size_t k = 0; k < 3 * nf; ++k) if (hf[k] >= m.vertex_count) return fail(MTSB_E_INVALID, "face index out of range");
+        if (nf) {
+            const uint32_t *src = m.faces;
+            if (m.mem == MTSB_MEM_HOST) { CU(raw_faces.alloc(3 * nf)); CU(cudaMemcpyAsync(raw_faces.p, hf.data(), 3 * nf * sizeof(uint32_t), cudaMemcpyHostToDevice, st)); src = raw_faces.p; }
+            k_faces_expand<<<grid_for(nf), kBlock, 0, st>>>(src, (uint32_t) nf, vbase, i, s->faces.p + fbase);
+            if (m.mem == MTSB_MEM_HOST) CU(cudaStreamSynchronize(st));       // raw_faces is reused by the next mesh
         }
+        if (m.emitter_id >= 0) {
+            std::vector<float> &hp = s->emitter_pos[(int) i]; hp.resize(3 * nv);
+            if (m.mem == MTSB_MEM_DEVICE) { CU(cudaMemcpyAsync(hp.data(), m.positions, 3 * nv * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+            else memcpy(hp.data(), m.positions, 3 * nv * sizeof(float));
+        }
+        s->computed_normals.push_back(false);
         vbase += m.vertex_count; fbase += m.face_count;
     }
-    CU(s->pos.upload(s->h_pos.data(), s->h_pos.size(), st));
-    CU(s->nrm.upload(s->h_nrm.data(), s->h_nrm.size(), st));
-    CU(s->uv.upload(h_uv.data(), h_uv.size(), st));
-    CU(s->faces.upload(h_faces.data(), h_faces.size(), st));
     CU(cudaStreamSynchronize(st));
     // ---- colour mode
     CHECK_ARG(d->mode == MTSB_MODE_RGB || d->mode == MTSB_MODE_SPECTRAL);
@@ -397,6 +414,14 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             } else CU(s->tables[ti]->upload(t.data, (size_t) t.width, st));
             CU(cudaStreamSynchronize(st));
             td.data = s->tables[ti]->p;
+        } else if (t.type == MTSB_TEX_MESH_ATTRIBUTE) {
+            CHECK_ARG(t.data && t.width >= 1 && (t.channels == 1 || t.channels == 3) && t.height <= 1);
+            td.w = t.width; td.h = t.height; td.ch = t.channels;
+            s->tables.emplace_back(new DevBuf<float>()); ti = (int) s->tables.size() - 1;
+            CU(s->tables[ti]->upload(t.data, (size_t) t.width * t.channels, st));
+            CU(cudaStreamSynchronize(st));
+            td.data = s->tables[ti]->p;
+            s->ext = true;                   // evaluated by the RgbX / SpectralX shade instances only
         } else if (t.type == MTSB_TEX_UNIFORM) {
             if (!s->spectral) return fail(MTSB_E_INVALID, "uniform spectra need MTSB_MODE_SPECTRAL");
         } else CHECK_ARG(t.type == MTSB_TEX_CONSTANT);
@@ -439,6 +464,14 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         }
         else return fail(MTSB_E_INVALID, "unknown BSDF type");
         s->bsdfs.push_back(bd);
+    }
+    // a mesh_attribute buffer must cover every mesh whose BSDF looks it up (Mesh::eval_attribute indexes by face / vertex)
+    for (const MeshDev &m : s->meshes) {
+        const BsdfDev &b = s->bsdfs[m.bsdf];
+        const int ids[6] = { b.refl, b.eta, b.k, b.spec_r, b.spec_t, b.opacity };
+        for (int id : ids)
+            if (id >= 0 && s->tex[id].type == MTSB_TEX_MESH_ATTRIBUTE && s->tex[id].w != (s->tex[id].h == 1 ? m.face_count : m.vert_count))
+                return fail(MTSB_E_INVALID, "mesh_attribute texture: element count does not match the mesh that uses it");
     }
     // ---- BVH (also yields the scene bbox)
     int rc = build_bvh(s.get());
@@ -602,6 +635,7 @@ static uint32_t pool_limit() {
 }
 static int ensure_pool(mtsb_scene *s, uint32_t n) {
     if (n <= s->pool) return MTSB_OK;
+    s->pool = 0;                 // a failed allocation below must not leave a stale size next to released buffers
     for (int k = 0; k < 2; ++k) {
         CU(s->q_o[k].alloc(n)); CU(s->q_d[k].alloc(n)); CU(s->q_hit[k].alloc(n)); CU(s->q_te[k].alloc(n));
         CU(s->q_misc[k].alloc(n)); CU(s->q_rng[k].alloc(n));
@@ -822,12 +856,12 @@ extern "C" int mtsb_scene_update_vertices(mtsb_scene *s, uint32_t mesh_id, const
     cudaStream_t st = s->ctx->stream;
     const MeshDev &m = s->meshes[mesh_id];
     const size_t nf = 3 * (size_t) m.vert_count;
-    float *dp = s->pos.p + 3 * (size_t) m.vert_begin, *hp = s->h_pos.data() + 3 * (size_t) m.vert_begin;
+    float *dp = s->pos.p + 3 * (size_t) m.vert_begin, *hp = m.emitter >= 0 ? s->emitter_pos[(int) mesh_id].data() : nullptr;
     // positions go straight to the device array (device callers: one D2D copy, no host round trip); the host copy is only
     // refreshed for emitter meshes, whose area CDF is rebuilt on the host in double like the reference (distr_1d.h:49-88)
     CU(cudaMemcpyAsync(dp, positions, nf * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-    if (mem == MTSB_MEM_HOST) memcpy(hp, positions, nf * sizeof(float));
-    else if (m.emitter >= 0) { CU(cudaMemcpyAsync(hp, positions, nf * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+    if (hp && mem == MTSB_MEM_HOST) memcpy(hp, positions, nf * sizeof(float));
+    else if (hp) { CU(cudaMemcpyAsync(hp, positions, nf * sizeof(float), cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
     if (m.has_normals) {      // Mesh::parameters_changed -> recompute_vertex_normals (mesh.cpp:794-804, 199-276), on the device
         float *dn = s->nrm.p + 3 * (size_t) m.vert_begin;
         CU(cudaMemsetAsync(dn, 0, nf * sizeof(float), st));
@@ -851,6 +885,9 @@ extern "C" int mtsb_scene_update_texture(mtsb_scene *s, uint32_t tex_id, const f
         return upload_struct_arrays(s);
     }
     size_t n = (size_t) t.w * t.h * t.ch;
+    if (t.type == MTSB_TEX_MESH_ATTRIBUTE) n = (size_t) t.w * t.ch;
+    else if (t.type != MTSB_TEX_BITMAP)      // tabulated / uniform spectra carry derived host-side tables (bucket index): recreate the scene instead
+        return fail(MTSB_E_INVALID, "mtsb_scene_update_texture: only constant, bitmap and mesh_attribute textures can be updated in place");
     CU(cudaMemcpyAsync((float *) t.data, data, n * sizeof(float), mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ctx->stream));
     CU(cudaStreamSynchronize(s->ctx->stream));
     return MTSB_OK;

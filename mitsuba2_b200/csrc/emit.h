@@ -29,7 +29,7 @@ HD float3 env_lookup(const EmitterDev &e, float u, float v) {
     uint32_t px = min((uint32_t) u, e.w - 2), py = min((uint32_t) v, e.h - 2);
     float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
     uint32_t idx = px + py * e.w;
-    float4 v00 = ldgf4(e.rgba + idx), v10 = ldgf4(e.rgba + idx + 1), v01 = ldgf4(e.rgba + idx + e.w), v11 = ldgf4(e.rgba + idx + e.w + 1);
+    float4 v00 = e.rgba[idx], v10 = e.rgba[idx + 1], v01 = e.rgba[idx + e.w], v11 = e.rgba[idx + e.w + 1];
     float3 a = mk3(fmaf(w0x, v00.x, w1x * v10.x), fmaf(w0x, v00.y, w1x * v10.y), fmaf(w0x, v00.z, w1x * v10.z));
     float3 b = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
     return mk3(fmaf(w0y, a.x, w1y * b.x), fmaf(w0y, a.y, w1y * b.y), fmaf(w0y, a.z, w1y * b.z)) * e.scale;
@@ -40,7 +40,7 @@ HD float4 env_lookup_spectral(const SceneDev &sc, const EmitterDev &e, float u, 
     uint32_t px = min((uint32_t) u, e.w - 2), py = min((uint32_t) v, e.h - 2);
     float w1x = u - (float) px, w1y = v - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
     uint32_t idx = px + py * e.w;
-    float4 v00 = ldgf4(e.rgba + idx), v10 = ldgf4(e.rgba + idx + 1), v01 = ldgf4(e.rgba + idx + e.w), v11 = ldgf4(e.rgba + idx + e.w + 1);
+    float4 v00 = e.rgba[idx], v10 = e.rgba[idx + 1], v01 = e.rgba[idx + e.w], v11 = e.rgba[idx + e.w + 1];
     auto bx = [&](float a, float b) { return fmaf(w0x, a, w1x * b); };
     auto by = [&](float a, float b) { return fmaf(w0y, a, w1y * b); };
     float4 s0 = map_spec(srgb_model_eval(xyz(v00), wav), srgb_model_eval(xyz(v10), wav), bx),
@@ -76,9 +76,7 @@ HD void h2d_sample(const EmitterDev &e, float sx, float sy, float &u, float &v, 
         const float *d = e.level_data[l];
         ox <<= 1; oy <<= 1;
         uint32_t i = h2d_index(ox, oy, e.level_width[l]);
-        // the 2x2 block of a MIP level is contiguous and 16-byte aligned (even ox, oy and level width): one 128-bit load
-        float4 blk = ldgf4((const float4 *) (d + i));
-        float v00 = blk.x, v10 = blk.y, v01 = blk.z, v11 = blk.w;
+        float v00 = d[i], v10 = d[i + 1], v01 = d[i + 2], v11 = d[i + 3];
         sx = fminf(fmaxf(sx, 0.f), 1.f); sy = fminf(fmaxf(sy, 0.f), 1.f);
         float r0 = v00 + v10, r1 = v01 + v11;
         sy *= r0 + r1;
@@ -94,7 +92,7 @@ HD void h2d_sample(const EmitterDev &e, float sx, float sy, float &u, float &v, 
     }
     const float *d0 = e.level_data[0]; uint32_t w0 = e.level_width[0];
     uint32_t i = ox + oy * w0;
-    float v00 = ldgf(d0 + i), v10 = ldgf(d0 + i + 1), v01 = ldgf(d0 + i + w0), v11 = ldgf(d0 + i + w0 + 1);
+    float v00 = d0[i], v10 = d0[i + 1], v01 = d0[i + w0], v11 = d0[i + w0 + 1];
     // warp::square_to_bilinear (include/mitsuba/core/warp.h:398-414)
     float r0 = v00 + v10, r1 = v01 + v11;
     sy = interval_to_linear(r0, r1, sy);
@@ -110,7 +108,7 @@ HD float h2d_eval(const EmitterDev &e, float u, float v) {
     u -= (float) (int) ox; v -= (float) (int) oy;
     const float *d0 = e.level_data[0]; uint32_t w0 = e.level_width[0];
     uint32_t i = ox + oy * w0;
-    float v00 = ldgf(d0 + i), v10 = ldgf(d0 + i + 1), v01 = ldgf(d0 + i + w0), v11 = ldgf(d0 + i + w0 + 1);
+    float v00 = d0[i], v10 = d0[i + 1], v01 = d0[i + w0], v11 = d0[i + w0 + 1];
     return lerpf(lerpf(v00, v10, u), lerpf(v01, v11, u), v);
 }
 HD float env_pdf_direction(const EmitterDev &e, float3 dworld) {
@@ -142,12 +140,12 @@ HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, 
     const MeshDev m = sc.meshes[e.mesh];
     float value = sy * e.cdf_sum;
     const float *cdf = e.cdf;
-    uint32_t idx = binary_search(e.valid_lo, e.valid_hi, [&](uint32_t i) { return ldgf(cdf + i) < value; });
+    uint32_t idx = binary_search(e.valid_lo, e.valid_hi, [&](uint32_t i) { return cdf[i] < value; });
     uint4 f = sc.faces[m.face_begin + idx];
     float3 p0 = ld3(sc.pos, f.x), p1 = ld3(sc.pos, f.y), p2 = ld3(sc.pos, f.z);
     float3 e0 = p1 - p0, e1 = p2 - p0;
     float pmf = 0.5f * norm(cross(e0, e1)) * e.normalization;
-    float cdf_prev = idx > 0 ? ldgf(cdf + idx - 1) * e.normalization : 0.f;
+    float cdf_prev = idx > 0 ? cdf[idx - 1] * e.normalization : 0.f;
     sy = (sy - cdf_prev) / pmf;
     float t = safe_sqrt(1.f - sx), bx = 1.f - t, by = t * sy;
     ds.p = p0 + e0 * bx + e1 * by;

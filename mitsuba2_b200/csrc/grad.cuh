@@ -59,6 +59,27 @@ static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint4 **edges, uint3
     return MTSB_OK;
 }
 
+// unique edges of ALL meshes (key -1 of the cache).  The boundary term seen from x1 needs them: with x2 parameterised on its
+// own triangle, a STATIC occluder's silhouette also sweeps over the material behind it when x1 or x2 sit on the moving mesh
+// (the shadow a fixed box casts onto the moving object; the part of the moving object seen past a fixed edge).
+static int all_edge_list(mtsb_scene *s, const uint4 **edges, uint32_t *n_edges) {
+    auto it = s->mesh_edges.find(-1);
+    if (it == s->mesh_edges.end()) {
+        std::vector<uint4> all, e;
+        for (size_t k = 0; k < s->meshes.size(); ++k) {
+            const MeshDev &m = s->meshes[k];
+            build_edge_list(s->mesh_faces[k].data(), m.face_count, m.vert_begin, m.face_begin, e);
+            all.insert(all.end(), e.begin(), e.end());
+        }
+        std::unique_ptr<DevBuf<uint4>> buf(new DevBuf<uint4>());
+        CU(buf->upload(all.data(), all.size(), s->ctx->stream));
+        CU(cudaStreamSynchronize(s->ctx->stream));
+        it = s->mesh_edges.emplace(-1, std::move(buf)).first;
+    }
+    *edges = it->second->p; *n_edges = (uint32_t) it->second->n;
+    return MTSB_OK;
+}
+
 /* boundary: 0 = interior term only, 1 = + primary-visibility edge sampling, 2 = + edge sampling seen from the first path
  * vertex (shadow / occlusion boundaries); edge_fraction = edge samples per path sample */
 extern "C" int mtsb_grad_config(mtsb_scene *s, int boundary, float edge_fraction) {
@@ -173,12 +194,15 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
             // ---- boundary term seen from the first path vertex (moving shadow / occlusion boundaries)
             if (s->grad_boundary >= 2) {
                 Edge2Launch l2; Edge2Ctx &e2 = l2.e;
-                e2.edges = e.edges; e2.n_edges = e.n_edges; e2.candidates = 16; e2.eps = 1e-3f; e2.total_len = 0.f;
-                DevBuf<float> len3, cdf3;
-                CU(len3.alloc(e.n_edges)); CU(cdf3.alloc(e.n_edges));
-                k_edge_len3<<<grid_for(e.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;
-                CU(cub::DeviceScan::InclusiveSum(tmp.p, tmp_bytes, len3.p, cdf3.p, (int) e.n_edges, st)); launches++;
-                e2.cdf = cdf3.p; l2.total_len = cdf3.p + (e.n_edges - 1);
+                RC(all_edge_list(s, &e2.edges, &e2.n_edges));
+                e2.candidates = 16; e2.eps = 1e-3f; e2.total_len = 0.f;
+                DevBuf<float> len3, cdf3; DevBuf<unsigned char> tmp2;
+                CU(len3.alloc(e2.n_edges)); CU(cdf3.alloc(e2.n_edges));
+                k_edge_len3<<<grid_for(e2.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;
+                size_t tmp2_bytes = 0;
+                CU(cub::DeviceScan::InclusiveSum(nullptr, tmp2_bytes, len3.p, cdf3.p, (int) e2.n_edges, st)); CU(tmp2.alloc(tmp2_bytes));
+                CU(cub::DeviceScan::InclusiveSum(tmp2.p, tmp2_bytes, len3.p, cdf3.p, (int) e2.n_edges, st)); launches++;
+                e2.cdf = cdf3.p; l2.total_len = cdf3.p + (e2.n_edges - 1);
                 CU(s->edge_aux.alloc(4 * (size_t) s->pool)); e2.aux = s->edge_aux.p;
                 // sample counts per pixel follow the path samples: the same (begin, count, total) split, scaled
                 uint32_t s2_total = (uint32_t) ceil((double) spp_total * frac); if (s2_total < 1) s2_total = 1;

@@ -89,6 +89,12 @@ __global__ void k_rough_tables(int distr_type, float alpha, float eta, const flo
     out[i] = rough_boundary_integral(distr_type, alpha, e, rough_table_mu((int) (i % kRoughTransRes)), res == 32 ? n32 : n128, res == 32 ? w32 : w128, res, transmit);
 }
 
+// faces of one mesh (3 x uint32, indices local to the mesh) -> (i0, i1, i2, mesh) with global vertex indices
+__global__ void k_faces_expand(const uint32_t *__restrict__ raw, uint32_t n, uint32_t vbase, uint32_t mesh, uint4 *out) {
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < n) out[f] = make_uint4(raw[3 * f] + vbase, raw[3 * f + 1] + vbase, raw[3 * f + 2] + vbase, mesh);
+}
+
 // ---------------- Mesh::recompute_vertex_normals on the device (src/librender/mesh.cpp:199-276) ------------------------
 // Angle-weighted face normals (Thuermer & Wuethrich 1998) scattered to the three corners with float atomics -- the
 // reference's own vectorised branch does the same with scatter_add (:258-275); its scalar branch accumulates in float in

@@ -222,7 +222,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     // spectral mode: one texture lookup shared by eval and sample (spectrum evaluations are expensive); the rgb kernel
     // re-reads the few floats at each use instead of keeping them live (it is compiled for 48 registers)
     BsdfTexT<M> btex;
-    if (M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
+    if (M::spectral) btex = bsdf_textures<M>(sc, bsdf, si, wav);
     // ---- emitter sampling (path.cpp:155-172, scene.cpp:141-189)
     if (bsdf_is_smooth(bsdf)) {
         float sx = rng.next_f32(), sy = rng.next_f32();
@@ -231,7 +231,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
             if (ds.pdf != 0.f) {
                 float3 wo = si.sh.to_local(ds.d);
                 Spec bval; float bpdf;
-                if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
+                if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si, wav);
                 bsdf_eval_pdf<M>(sc, bsdf, si, wo, bval, bpdf, btex);
                 float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);          // path.cpp:169
                 Spec c = thr * bval * ds.value * mis;
@@ -247,7 +247,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     }
     // ---- BSDF sampling (path.cpp:177-190)
     float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
-    if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si.u, si.v, wav);
+    if (!M::spectral) btex = bsdf_textures<M>(sc, bsdf, si, wav);
     BsdfSampleT<M> bs = bsdf_sample<M>(sc, bsdf, si, s1, s2x, s2y, btex);
     thr *= bs.weight;
     if (is_black(thr)) return out;

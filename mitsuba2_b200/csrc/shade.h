@@ -6,6 +6,7 @@ namespace mtsb {
 
 struct SI {
     float3 p, n; Frame sh; float u, v; float3 wi; float t; uint32_t prim; int mesh; bool valid;
+    float b1, b2;      // barycentrics of the hit (mesh_attribute textures interpolate with them)
 };
 
 HD float3 ld3(const float *a, uint32_t i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
@@ -16,6 +17,7 @@ constexpr uint32_t kPrimMask = 0x3fffffffu;     // primitive ids use 30 bits; th
 HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     SI si;
     si.t = hit.x; si.prim = f2u(hit.w) & kPrimMask; si.valid = hit.x != INFINITY;
+    si.b1 = hit.y; si.b2 = hit.z;
     if (!si.valid) { si.wi = -d; si.mesh = -1; si.p = o; si.n = mk3(0.f); si.u = si.v = 0.f; si.sh.s = si.sh.t = si.sh.n = mk3(0.f); return si; }
     uint4 f = sc.faces[si.prim];
     si.mesh = (int) f.w;
@@ -64,11 +66,11 @@ HD float3 tex_eval_rgb(const SceneDev &sc, int id, float u, float v) {
     float w1x = tu - (float) px, w1y = tv - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
     uint32_t idx = px + py * t.w;
     if (t.ch == 1) {
-        float v00 = ldgf(t.data + idx), v10 = ldgf(t.data + idx + 1), v01 = ldgf(t.data + idx + t.w), v11 = ldgf(t.data + idx + t.w + 1);
+        float v00 = t.data[idx], v10 = t.data[idx + 1], v01 = t.data[idx + t.w], v11 = t.data[idx + t.w + 1];
         float v0 = fmaf(w0x, v00, w1x * v10), v1 = fmaf(w0x, v01, w1x * v11);
         return mk3(fmaf(w0y, v0, w1y * v1));
     }
-    float3 v00 = ldg3(t.data, idx), v10 = ldg3(t.data, idx + 1), v01 = ldg3(t.data, idx + t.w), v11 = ldg3(t.data, idx + t.w + 1);
+    float3 v00 = ld3(t.data, idx), v10 = ld3(t.data, idx + 1), v01 = ld3(t.data, idx + t.w), v11 = ld3(t.data, idx + t.w + 1);
     float3 v0 = mk3(fmaf(w0x, v00.x, w1x * v10.x), fmaf(w0x, v00.y, w1x * v10.y), fmaf(w0x, v00.z, w1x * v10.z));
     float3 v1 = mk3(fmaf(w0x, v01.x, w1x * v11.x), fmaf(w0x, v01.y, w1x * v11.y), fmaf(w0x, v01.z, w1x * v11.z));
     return mk3(fmaf(w0y, v0.x, w1y * v1.x), fmaf(w0y, v0.y, w1y * v1.y), fmaf(w0y, v0.z, w1y * v1.z));
@@ -98,11 +100,11 @@ float4 tex_eval_spectral(const SceneDev &sc, int id, float u, float v, float4 wa
         uint32_t idx = px + py * t.w;
         auto blend = [&](float a, float b) { return fmaf(w0x, a, w1x * b); };
         if (t.ch == 1) {
-            float v0 = blend(ldgf(t.data + idx), ldgf(t.data + idx + 1)), v1 = blend(ldgf(t.data + idx + t.w), ldgf(t.data + idx + t.w + 1));
+            float v0 = blend(t.data[idx], t.data[idx + 1]), v1 = blend(t.data[idx + t.w], t.data[idx + t.w + 1]);
             r = mk4(fmaf(w0y, v0, w1y * v1));
         } else {
-            float4 c00 = srgb_model_eval(ldg3(t.data, idx), wav), c10 = srgb_model_eval(ldg3(t.data, idx + 1), wav),
-                   c01 = srgb_model_eval(ldg3(t.data, idx + t.w), wav), c11 = srgb_model_eval(ldg3(t.data, idx + t.w + 1), wav);
+            float4 c00 = srgb_model_eval(ld3(t.data, idx), wav), c10 = srgb_model_eval(ld3(t.data, idx + 1), wav),
+                   c01 = srgb_model_eval(ld3(t.data, idx + t.w), wav), c11 = srgb_model_eval(ld3(t.data, idx + t.w + 1), wav);
             float4 c0 = map_spec(c00, c10, blend), c1 = map_spec(c01, c11, blend);
             r = map_spec(c0, c1, [&](float a, float b) { return fmaf(w0y, a, w1y * b); });
         }
@@ -114,6 +116,34 @@ template <typename M> HD typename M::Spec tex_eval_m(const SceneDev &sc, int id,
     if constexpr (M::spectral) return tex_eval_spectral(sc, id, u, v, wav); else return tex_eval_rgb(sc, id, u, v);
 }
 HD float3 tex_eval(const SceneDev &sc, int id, float u, float v) { return tex_eval_rgb(sc, id, u, v); }
+// `mesh_attribute` texture (src/textures/mesh_attribute.cpp -> Mesh::eval_attribute, include/mitsuba/render/mesh.h:278-318):
+// a per-vertex (barycentric interpolation, fmadd(v0, b0, fmadd(v1, b1, v2 b2))) or per-face attribute of the mesh that was
+// hit, 1 or 3 floats, times `scale`.  TexDev: type 5, data = the attribute buffer of that mesh, h = 1 per face / 0 per
+// vertex, ch = 1 | 3, value.x = scale.  Spectral mode: 3-float attributes are sRGB-model coefficients (mesh.h:297-306).
+template <typename M>
+HD typename M::Spec mesh_attribute_eval(const SceneDev &sc, const TexDev &t, const SI &si, float4 wav) {
+    typedef typename M::Spec Spec;
+    if (!si.valid) return M::splat(0.f);
+    const MeshDev m = sc.meshes[si.mesh];
+    auto fetch = [&](uint32_t i) -> Spec {
+        if (t.ch == 1) return M::splat(t.data[i]);
+        float3 c = ld3(t.data, i);
+        if constexpr (M::spectral) return srgb_model_eval(c, wav); else return c;
+    };
+    Spec r;
+    if (t.h == 1) r = fetch(si.prim - m.face_begin);
+    else {
+        uint4 f = sc.faces[si.prim];
+        float b0 = 1.f - si.b1 - si.b2;
+        Spec v0 = fetch(f.x - m.vert_begin), v1 = fetch(f.y - m.vert_begin), v2 = fetch(f.z - m.vert_begin);
+        r = v0 * b0 + (v1 * si.b1 + v2 * si.b2);
+    }
+    return r * t.value.x;
+}
+template <typename M> HD typename M::Spec tex_fetch(const SceneDev &sc, int id, const SI &si, float4 wav) {
+    if constexpr (M::ext) { const TexDev &t = sc.tex[id]; if (t.type == 5) return mesh_attribute_eval<M>(sc, t, si, wav); }
+    return tex_eval_m<M>(sc, id, si.u, si.v, wav);
+}
 // texel footprint of a bitmap lookup (for the adjoint scatter): indices of the 4 texels + weights
 HD bool tex_footprint(const TexDev &t, float u, float v, uint32_t idx[4], float w[4]) {
     if (t.type != 1) return false;
@@ -333,17 +363,17 @@ HD float3 plastic_div(float3 d, float f, bool nl) { return mk3(d.x / (1.f - (nl 
 HD float4 plastic_div(float4 d, float f, bool nl) { return make_float4(d.x / (1.f - (nl ? d.x * f : f)), d.y / (1.f - (nl ? d.y * f : f)), d.z / (1.f - (nl ? d.z * f : f)), d.w / (1.f - (nl ? d.w * f : f))); }
 template <typename M> HD typename M::Spec plastic_diffuse(const BsdfDev &b, typename M::Spec d) { return plastic_div(d, fresnel_diffuse_reflectance(1.f / b.eta_f), b.nonlinear != 0); }
 template <typename M>
-HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, float u, float v, float4 wav) {
+HD BsdfTexT<M> bsdf_textures(const SceneDev &sc, const BsdfDev &b, const SI &si, float4 wav) {
     BsdfTexT<M> t; t.a = t.b = t.c = M::splat(1.f); t.opacity = 1.f;
-    if (M::ext && b.opacity >= 0) t.opacity = fminf(fmaxf(tex_eval_m<M>(sc, b.opacity, u, v, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
-    if (b.type == 0) t.a = tex_eval_m<M>(sc, b.refl, u, v, wav);
-    else if (M::ext && (b.type == 4 || b.type == 6)) { t.a = tex_eval_m<M>(sc, b.refl, u, v, wav); if (b.spec_r >= 0) t.b = tex_eval_m<M>(sc, b.spec_r, u, v, wav); }
+    if (M::ext && b.opacity >= 0) t.opacity = fminf(fmaxf(tex_fetch<M>(sc, b.opacity, si, wav).x, 0.f), 1.f);      // mask.cpp: eval_opacity
+    if (b.type == 0) t.a = tex_fetch<M>(sc, b.refl, si, wav);
+    else if (M::ext && (b.type == 4 || b.type == 6)) { t.a = tex_fetch<M>(sc, b.refl, si, wav); if (b.spec_r >= 0) t.b = tex_fetch<M>(sc, b.spec_r, si, wav); }
     else if (b.type == 1 || (M::ext && b.type == 3)) {
-        t.a = tex_eval_m<M>(sc, b.eta, u, v, wav); t.b = tex_eval_m<M>(sc, b.k, u, v, wav);
-        if (b.spec_r >= 0) t.c = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
+        t.a = tex_fetch<M>(sc, b.eta, si, wav); t.b = tex_fetch<M>(sc, b.k, si, wav);
+        if (b.spec_r >= 0) t.c = tex_fetch<M>(sc, b.spec_r, si, wav);
     } else {                      // dielectric, rough dielectric
-        if (b.spec_r >= 0) t.a = tex_eval_m<M>(sc, b.spec_r, u, v, wav);
-        if (b.spec_t >= 0) t.b = tex_eval_m<M>(sc, b.spec_t, u, v, wav);
+        if (b.spec_r >= 0) t.a = tex_fetch<M>(sc, b.spec_r, si, wav);
+        if (b.spec_t >= 0) t.b = tex_fetch<M>(sc, b.spec_t, si, wav);
     }
     return t;
 }
@@ -568,11 +598,11 @@ HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3
 // stand-alone forms (parity hooks, adjoint): look the textures up themselves
 template <typename M = RgbX>
 HD BsdfSampleT<M> bsdf_sample(const SceneDev &sc, const BsdfDev &b, const SI &si, float s1, float sx, float sy, float4 wav = float4()) {
-    return bsdf_sample<M>(sc, b, si, s1, sx, sy, bsdf_textures<M>(sc, b, si.u, si.v, wav));
+    return bsdf_sample<M>(sc, b, si, s1, sx, sy, bsdf_textures<M>(sc, b, si, wav));
 }
 template <typename M = RgbX>
 HD void bsdf_eval_pdf(const SceneDev &sc, const BsdfDev &b, const SI &si, float3 wo, typename M::Spec &val, float &pdf, float4 wav = float4()) {
-    bsdf_eval_pdf<M>(sc, b, si, wo, val, pdf, bsdf_textures<M>(sc, b, si.u, si.v, wav));
+    bsdf_eval_pdf<M>(sc, b, si, wo, val, pdf, bsdf_textures<M>(sc, b, si, wav));
 }
 HD bool bsdf_is_smooth(const BsdfDev &b) { return b.type != 2 && b.type != 3; }      // dielectric and smooth conductor are all-delta
 

@@ -129,24 +129,4 @@ HD Pcg32 sampler_seed(uint64_t seed, uint32_t idx) {
     return r;
 }
 
-
-// Loads through pointers that were themselves loaded from memory (texture / table pointers inside TexDev / EmitterDev):
-// the compiler cannot prove the address space and emits generic LD; these tables are read-only for the whole launch,
-// so go through the non-coherent global path explicitly.
-HD float ldgf(const float *p) {
-#ifdef __CUDA_ARCH__
-    return __ldg(p);
-#else
-    return *p;
-#endif
-}
-HD float4 ldgf4(const float4 *p) {
-#ifdef __CUDA_ARCH__
-    return __ldg(p);
-#else
-    return *p;
-#endif
-}
-HD float3 ldg3(const float *a, uint32_t i) { return mk3(ldgf(a + 3 * i), ldgf(a + 3 * i + 1), ldgf(a + 3 * i + 2)); }
-
 } // namespace mtsb

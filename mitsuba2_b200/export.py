@@ -58,6 +58,9 @@ class _Writer:
                 m[:2, :2], m[:2, 3] = uv[:2, :2], uv[:2, 2]
                 self.w(f'    <transform name="to_uv"><matrix value="{_matrix(m)}"/></transform>')
             self.w("</texture>")
+        elif t["type"] == A.TEX_MESH_ATTRIBUTE:
+            self.w(f'<texture type="mesh_attribute" name="{name}"><string name="name" value="{t["name"]}"/>'
+                   f'<float name="scale" value="{t["scale"]!r}"/></texture>')
         else:
             raise ValueError("tabulated spectra are not exported")
 

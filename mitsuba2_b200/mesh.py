@@ -149,17 +149,20 @@ def load_ply(path, to_world=None, face_normals=False, flip_normals=False):
                 arr = np.frombuffer(fh.read(dt.itemsize * el["count"]), dtype=dt)
                 data[el["name"]] = {p[1]: arr[p[1]] for p in el["props"]}
             else:
-                assert len(el["props"]) == 1, "PLY: only a single list property per face element is supported"
+                assert el["props"][0][0] == "list" and all(p[0] != "list" for p in el["props"][1:]), "PLY: one index list, then scalar properties"
                 _, cty, ity, _ = el["props"][0]
+                extra = el["props"][1:]
                 cdt, idt = np.dtype(endian + _PLY_TYPES[cty]), np.dtype(endian + _PLY_TYPES[ity])
                 raw = fh.read()
-                # fast path: all triangles
-                rec = np.dtype([("c", cdt), ("i", idt, (3,))])
+                # fast path: all triangles (per-face attributes follow the index list, src/shapes/ply.cpp:262-291)
+                rec = np.dtype([("c", cdt), ("i", idt, (3,))] + [(p[1], endian + _PLY_TYPES[p[0]]) for p in extra])
                 if len(raw) >= rec.itemsize * el["count"]:
                     arr = np.frombuffer(raw[:rec.itemsize * el["count"]], dtype=rec)
                     if np.all(arr["c"] == 3):
                         data[el["name"]] = arr["i"].astype(np.uint32)
+                        data[el["name"] + "_props"] = {p[1]: arr[p[1]] for p in extra}
                         continue
+                assert not extra, "PLY: per-face attributes are supported for triangle meshes only"
                 out, off = [], 0
                 for _ in range(el["count"]):
                     c = int(np.frombuffer(raw, cdt, 1, off)[0]); off += cdt.itemsize
@@ -187,7 +190,34 @@ def load_ply(path, to_world=None, face_normals=False, flip_normals=False):
     for a, b in (("u", "v"), ("s", "t"), ("texture_u", "texture_v")):
         if a in v:
             tex = np.stack([v[a], v[b]], axis=1).astype(np.float32)
-    return Mesh(pos, faces, nrm, tex, name=str(path))
+    m = Mesh(pos, faces, nrm, tex, name=str(path))
+    m.attributes.update(_ply_attributes("vertex_", v, {"x", "y", "z", "nx", "ny", "nz", "u", "v", "s", "t", "texture_u", "texture_v"}))
+    m.attributes.update(_ply_attributes("face_", data.get("face_props", {}), set()))
+    return m
+
+
+def _ply_attributes(kind, props, reserved):
+    """``PLYMesh::find_other_fields`` (src/shapes/ply.cpp:594-690): r/g/b(/a) or red/green/blue -> "<kind>color"; other fields
+    group by a common prefix with postfixes from one of [x y z w], [r g b a], [0 1 2 3], [1 2 3 4] -> "<kind><prefix>"."""
+    out, names = {}, list(props)
+    ren = {"red": "r", "green": "g", "blue": "b", "alpha": "a"}
+    if all(k in props for k in ("red", "green", "blue")) and not all(k in props for k in "rgb"):
+        props = {ren.get(k, k): val for k, val in props.items()}
+        names = list(props)
+    if all(k in props for k in "rgb"):
+        cols = [props[k] for k in ("r", "g", "b")] + ([props["a"]] if "a" in props else [])
+        out[kind + "color"] = np.stack(cols, axis=1).astype(np.float32)
+    reserved = set(reserved) | {"r", "g", "b", "a"}
+    groups = {}
+    for nme in names:
+        if nme in reserved or "_" not in nme:
+            continue
+        prefix, post = nme.rsplit("_", 1)
+        if len(post) == 1 and post in "xyzwrgba01234":
+            groups.setdefault(prefix, []).append(nme)
+    for prefix, members in groups.items():
+        out[kind + prefix] = np.stack([props[k] for k in members], axis=1).astype(np.float32)
+    return out
 
 
 def load_serialized(path, to_world=None, shape_index=0, face_normals=False, flip_normals=False):
@@ -251,15 +281,28 @@ def write_ply(path, mesh):
     p, f = mesh.positions, mesh.faces
     props = ["x", "y", "z"] + (["nx", "ny", "nz"] if mesh.normals is not None else []) + (["u", "v"] if mesh.texcoords is not None else [])
     cols = [p] + ([mesh.normals] if mesh.normals is not None else []) + ([mesh.texcoords] if mesh.texcoords is not None else [])
+    fprops, fcols = [], []
+    for name, a in getattr(mesh, "attributes", {}).items():       # "<kind><prefix>" -> fields prefix_0 .. prefix_{n-1}
+        kind, prefix = name.split("_", 1)
+        fields = ["%s_%d" % (prefix, k) for k in range(a.shape[1])]
+        if kind == "vertex":
+            props += fields; cols.append(a)
+        else:
+            fprops += fields; fcols.append(a)
     vert = np.concatenate(cols, axis=1).astype("<f4")
     with open(path, "wb") as fh:
         hdr = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % p.shape[0]
         hdr += "".join("property float %s\n" % q for q in props)
-        hdr += "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % f.shape[0]
+        hdr += "element face %d\nproperty list uchar int vertex_indices\n" % f.shape[0]
+        hdr += "".join("property float %s\n" % q for q in fprops) + "end_header\n"
         fh.write(hdr.encode())
         fh.write(vert.tobytes())
-        rec = np.empty(f.shape[0], dtype=[("c", "u1"), ("i", "<i4", (3,))])
+        rec = np.empty(f.shape[0], dtype=[("c", "u1"), ("i", "<i4", (3,))] + [(q, "<f4") for q in fprops])
         rec["c"], rec["i"] = 3, f
+        if fcols:
+            fa = np.concatenate(fcols, axis=1)
+            for k, q in enumerate(fprops):
+                rec[q] = fa[:, k]
         fh.write(rec.tobytes())
 
 

@@ -78,11 +78,21 @@ def look_at(origin, target, up):
 
 class Mesh:
     def __init__(self, positions, faces, normals=None, texcoords=None, bsdf=0, emitter=-1, name="mesh"):
+        self.device = hasattr(positions, "is_cuda") and positions.is_cuda
+        if self.device:       # CUDA torch tensors: handed to the library as device pointers (mtsb_mesh_desc.mem = MTSB_MEM_DEVICE)
+            import torch
+            self.positions = positions.to(torch.float32).reshape(-1, 3).contiguous()
+            self.faces = faces.to(device=positions.device, dtype=torch.int32).reshape(-1, 3).contiguous()
+            self.normals = normals.to(torch.float32).reshape(-1, 3).contiguous() if normals is not None else None
+            self.texcoords = texcoords.to(torch.float32).reshape(-1, 2).contiguous() if texcoords is not None else None
+            self.bsdf, self.emitter, self.name, self.attributes = int(bsdf), int(emitter), name, {}
+            return
         self.positions = _f32(positions).reshape(-1, 3)
         self.faces = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
         self.normals = _f32(normals).reshape(-1, 3) if normals is not None else None
         self.texcoords = _f32(texcoords).reshape(-1, 2) if texcoords is not None else None
         self.bsdf, self.emitter, self.name = int(bsdf), int(emitter), name
+        self.attributes = {}       # "vertex_<name>" / "face_<name>" -> (n, size) float32 (Mesh::m_mesh_attributes, mesh.h)
 
 
 class SceneData:
@@ -141,6 +151,39 @@ class SceneData:
         assert data.ndim == 3 and data.shape[2] in (1, 3)
         self.textures.append({"type": A.TEX_BITMAP, "data": np.ascontiguousarray(data),
                               "to_uv": _f32(np.eye(3) if to_uv is None else to_uv).reshape(9)})
+        return len(self.textures) - 1
+
+    def bind_mesh_attributes(self, mesh):
+        """A ``mesh_attribute`` texture declared by name only is bound to the attribute buffer of the mesh whose BSDF uses it
+        (``Mesh::eval_attribute`` looks the name up in the shape that was hit): returns the BSDF id to use for `mesh` -- a
+        copy with per-mesh textures when any of its textures is an unbound attribute, else ``mesh.bsdf``."""
+        b = self.bsdfs[mesh.bsdf]
+        keys = [k for k, v in b.items() if (k.endswith("_tex")) and isinstance(v, int) and v >= 0
+                and self.textures[v]["type"] == A.TEX_MESH_ATTRIBUTE and self.textures[v].get("data") is None]
+        if not keys:
+            return mesh.bsdf
+        nb = dict(b)
+        for k in keys:
+            t = self.textures[b[k]]
+            attrs = getattr(mesh, "attributes", {})
+            if t["name"] not in attrs:
+                raise RuntimeError(f"Invalid attribute requested {t['name']}.")      # mesh.cpp:530-531
+            nb[k] = self.add_texture_mesh_attribute(attrs[t["name"]], t["per_face"], t["scale"], t["name"])
+        self.bsdfs.append(nb)
+        return len(self.bsdfs) - 1
+
+    def add_texture_mesh_attribute(self, data, per_face=False, scale=1.0, name=None):
+        """``mesh_attribute`` texture (src/textures/mesh_attribute.cpp): `data` (n, 1|3) = one element per vertex (barycentric
+        interpolation) or per face of the mesh whose BSDF uses it.  Spectral mode: 3-float elements are taken as rgb and
+        converted to sRGB-model coefficients here (the reference expects the caller to have done that, mesh_attribute.cpp:54-58)."""
+        if data is None:          # declared by name (XML): bound per mesh by bind_mesh_attributes
+            self.textures.append({"type": A.TEX_MESH_ATTRIBUTE, "data": None, "per_face": bool(per_face), "scale": float(scale), "name": name})
+            return len(self.textures) - 1
+        d = _f32(data)
+        d = d.reshape(-1, 1) if d.ndim == 1 else d.reshape(d.shape[0], -1)
+        if d.shape[1] not in (1, 3):
+            raise RuntimeError(f'eval_attribute(): Attribute "{name}" requested but had size {d.shape[1]}.')      # mesh.cpp:543
+        self.textures.append({"type": A.TEX_MESH_ATTRIBUTE, "data": np.ascontiguousarray(d), "per_face": bool(per_face), "scale": float(scale), "name": name})
         return len(self.textures) - 1
 
     def add_diffuse(self, reflectance=0.5):
@@ -314,10 +357,18 @@ class SceneData:
         md = (A.MeshDesc * max(1, len(self.meshes)))()
         for i, m in enumerate(self.meshes):
             keep.append(m)
-            md[i].faces = _ptr(m.faces, A.c_u32_p)
-            md[i].positions = _ptr(m.positions, A.c_float_p)
-            md[i].normals = _ptr(m.normals, A.c_float_p)
-            md[i].texcoords = _ptr(m.texcoords, A.c_float_p)
+            if getattr(m, "device", False):
+                import torch
+                torch.cuda.current_stream(m.positions.device).synchronize()
+                cast = lambda t, ty: C.cast(C.c_void_p(t.data_ptr() if t is not None else None), ty)      # noqa: E731
+                md[i].faces, md[i].positions = cast(m.faces, A.c_u32_p), cast(m.positions, A.c_float_p)
+                md[i].normals, md[i].texcoords = cast(m.normals, A.c_float_p), cast(m.texcoords, A.c_float_p)
+                md[i].mem = A.MEM_DEVICE
+            else:
+                md[i].faces = _ptr(m.faces, A.c_u32_p)
+                md[i].positions = _ptr(m.positions, A.c_float_p)
+                md[i].normals = _ptr(m.normals, A.c_float_p)
+                md[i].texcoords = _ptr(m.texcoords, A.c_float_p)
             md[i].face_count, md[i].vertex_count = m.faces.shape[0], m.positions.shape[0]
             md[i].bsdf_id, md[i].emitter_id = m.bsdf, m.emitter
         bd = (A.BsdfDesc * max(1, len(self.bsdfs)))()
@@ -340,7 +391,8 @@ class SceneData:
 
             def fetch(rgb):
                 return rgb2spec.fetch(rgb, model=self.rgb2spec_model)
-        texs = [dict(t) for t in self.textures]
+        texs = [dict(t) if not (t["type"] == A.TEX_MESH_ATTRIBUTE and t.get("data") is None) else {"type": A.TEX_CONSTANT, "value": [0.0, 0.0, 0.0]}
+                for t in self.textures]      # a mesh_attribute declared by name that no shape bound: placeholder, never referenced
         emit_tex = {}
         if spectral:
             # what the texture plugins do when they are instantiated in a spectral variant
@@ -353,6 +405,8 @@ class SceneData:
                     if np.any(c < 0) or np.any(c > 1):
                         raise ValueError(f"Invalid RGB reflectance value {c}, must be in the range [0, 1]!")
                     t["value"] = [float(x) for x in fetch(c)]
+                elif t["type"] == A.TEX_MESH_ATTRIBUTE and t["data"].shape[1] == 3:
+                    t["data"] = np.ascontiguousarray(fetch(np.clip(t["data"], 0.0, 1.0)).astype(np.float32))
                 elif t["type"] == A.TEX_BITMAP and t["data"].shape[2] == 3:  # bitmap.cpp:120-135 (texels -> coefficients)
                     t["data"] = np.ascontiguousarray(fetch(np.clip(t["data"], 0.0, 1.0)))
             for i, e in enumerate(self.emitters):                            # srgb_d65.cpp:36-52
@@ -366,7 +420,7 @@ class SceneData:
         else:
             used = {v for b in self.bsdfs for k, v in b.items() if k.endswith("_tex") and isinstance(v, int) and v >= 0}
             for i, t in enumerate(texs):
-                if t["type"] not in (A.TEX_CONSTANT, A.TEX_BITMAP) or t.get("coeff"):
+                if t["type"] not in (A.TEX_CONSTANT, A.TEX_BITMAP, A.TEX_MESH_ATTRIBUTE) or t.get("coeff"):
                     if i in used:
                         raise ValueError("spectrum textures need mode='spectral' (rgb variants take pre-integrated colours)")
                     texs[i] = {"type": A.TEX_CONSTANT, "value": [0.0, 0.0, 0.0]}     # an emitter's spectrum: rgb mode uses its colour
@@ -376,6 +430,13 @@ class SceneData:
             td[i].d65_scale = t.get("d65_scale", 0.0)
             if t["type"] in (A.TEX_CONSTANT, A.TEX_UNIFORM):
                 td[i].value = (C.c_float * 3)(*t["value"])
+            elif t["type"] == A.TEX_MESH_ATTRIBUTE:
+                d = t["data"]
+                keep.append(d)
+                td[i].width, td[i].channels = d.shape
+                td[i].height = 1 if t["per_face"] else 0
+                td[i].data = _ptr(d, A.c_float_p)
+                td[i].value = (C.c_float * 3)(t["scale"], 0.0, 0.0)
             elif t["type"] == A.TEX_BITMAP:
                 d = t["data"]
                 keep.append(d)

@@ -212,6 +212,12 @@ class _Loader:
             return idx
         el = v
         ty = self.attr(el, "type")
+        if ty == "mesh_attribute":       # src/textures/mesh_attribute.cpp:57-66: bound to the mesh's buffer when a shape uses the BSDF
+            p = self.props(el)
+            nm = p["name"]
+            if "vertex_" not in nm and "face_" not in nm:
+                raise RuntimeError(f'Invalid mesh attribute name: must be start with either "vertex_" or "face_" but was "{nm}".')
+            return self.sd.add_texture_mesh_attribute(None, per_face=nm.startswith("face_"), scale=p.get("scale", 1.0), name=nm)
         if ty != "bitmap":
             raise NotImplementedError(f"texture plugin '{ty}' is outside the hot-path scope")
         p = self.props(el)
@@ -337,6 +343,7 @@ class _Loader:
                     raise NotImplementedError("textured area-light radiance")
                 radiance = rad[1]
         m.bsdf = bsdf if bsdf is not None else self.sd.add_diffuse(0.5)     # shape.cpp:75-76
+        m.bsdf = self.sd.bind_mesh_attributes(m)
         self.sd.add_mesh(m, radiance)
 
     def emitter(self, el):

@@ -525,6 +525,8 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
         ot->lambda_min = t->lambda_min; ot->lambda_max = t->lambda_max; ot->d65_scale = t->d65_scale; ot->w = t->width;
         if (t->type == MTSB_TEX_REGULAR || t->type == MTSB_TEX_IRREGULAR) { size_t n = (size_t) t->width * (t->type == MTSB_TEX_IRREGULAR ? 2 : 1);
             ot->data = malloc(sizeof(float) * n); memcpy(ot->data, t->data, sizeof(float) * n); }
+        if (t->type == MTSB_TEX_MESH_ATTRIBUTE) { ot->h = t->height; ot->ch = t->channels; size_t n = (size_t) t->width * t->channels;
+            ot->data = malloc(sizeof(float) * n); memcpy(ot->data, t->data, sizeof(float) * n); }
         if (t->type == MTSB_TEX_BITMAP) { ot->w = t->width; ot->h = t->height; ot->ch = t->channels; memcpy(ot->to_uv, t->to_uv, sizeof(ot->to_uv));
             size_t n = (size_t) t->width * t->height * t->channels; ot->data = malloc(sizeof(float) * n); memcpy(ot->data, t->data, sizeof(float) * n); }
     }
@@ -571,7 +573,7 @@ void orc_scene_update_texture(orc_scene *s, uint32_t id, const float *data) {
 /* =============================================================================================== */
 /* Surface interaction, textures, BSDFs, emitters                                                   */
 /* =============================================================================================== */
-typedef struct { v3 p, n, sh_s, sh_t, sh_n, wi; float u, v, t; uint32_t prim; int mesh, valid; } osi;
+typedef struct { v3 p, n, sh_s, sh_t, sh_n, wi; float u, v, t; uint32_t prim; int mesh, valid; float b1, b2; } osi;
 static v3 to_local(const osi *si, v3 w) { return V(vdot(w, si->sh_s), vdot(w, si->sh_t), vdot(w, si->sh_n)); }
 static v3 to_world(const osi *si, v3 w) { return vadd(vadd(vscale(si->sh_s, w.x), vscale(si->sh_t, w.y)), vscale(si->sh_n, w.z)); }
 
@@ -582,7 +584,7 @@ static void make_si(const orc_scene *s, v3 o, v3 d, const ohit *h, osi *si) {
     if (!si->valid) { si->wi = vneg(d); si->p = o; return; }
     uint32_t f = h->prim; const omesh *m = &s->meshes[s->face_mesh[f]]; si->mesh = (int) s->face_mesh[f];
     uint32_t i0 = s->faces[3 * f], i1 = s->faces[3 * f + 1], i2 = s->faces[3 * f + 2];
-    float b1 = h->u, b2 = h->v, b0 = 1.f - b1 - b2;
+    float b1 = h->u, b2 = h->v, b0 = 1.f - b1 - b2; si->b1 = b1; si->b2 = b2;
     v3 p0 = ld3(s->pos, i0), p1 = ld3(s->pos, i1), p2 = ld3(s->pos, i2);
     v3 dp0 = vsub(p1, p0), dp1 = vsub(p2, p0);
     si->p = vadd(vadd(vscale(p0, b0), vscale(p1, b1)), vscale(p2, b2));
@@ -715,6 +717,24 @@ static col tex_eval(const orc_scene *s, int id, float u, float v, const float *w
     if (s->spectral && t->d65_scale != 0.f) for (int i = 0; i < 4; ++i) r.c[i] = d65_eval(wav[i]) * t->d65_scale * r.c[i];
     return r;
 }
+/* `mesh_attribute` (src/textures/mesh_attribute.cpp -> Mesh::eval_attribute / interpolate_attribute, mesh.h:278-318) */
+static col tex_eval_si(const orc_scene *s, int id, const osi *si, const float *wav) {
+    const otex *t = &s->tex[id];
+    if (t->type != MTSB_TEX_MESH_ATTRIBUTE) return tex_eval(s, id, si->u, si->v, wav);
+    col r = C1(0.f);
+    if (!si->valid) return r;
+    const omesh *m = &s->meshes[si->mesh];
+    col v[3]; int nv = t->h == 1 ? 1 : 3;
+    for (int k = 0; k < nv; ++k) {
+        uint32_t i = t->h == 1 ? si->prim - m->face_begin : s->faces[3 * si->prim + k] - m->vert_begin;
+        if (t->ch == 1) v[k] = C1(t->data[i]);
+        else if (s->spectral) { for (int c = 0; c < 4; ++c) v[k].c[c] = srgb_model_eval(t->data + 3 * (size_t) i, wav[c]); }
+        else v[k] = C3(V(t->data[3 * (size_t) i], t->data[3 * (size_t) i + 1], t->data[3 * (size_t) i + 2]));
+    }
+    if (nv == 1) r = v[0];
+    else { float b0 = 1.f - si->b1 - si->b2; for (int c = 0; c < 4; ++c) r.c[c] = v[0].c[c] * b0 + (v[1].c[c] * si->b1 + v[2].c[c] * si->b2); }
+    return cscale(r, t->value.x);
+}
 typedef struct { v3 wo; col weight; float pdf, eta; int delta; } obs;
 /* fresnel_diffuse_reflectance (include/mitsuba/render/fresnel.h:324-358) */
 static float fresnel_diffuse_reflectance(float eta) {
@@ -730,7 +750,7 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:78-103 */
         if (!(cos_theta_i > 0.f)) return bs;
         bs.wo = cosine_hemisphere(sx, sy); bs.pdf = INV_PI_F * bs.wo.z;
-        if (bs.pdf > 0.f) bs.weight = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+        if (bs.pdf > 0.f) bs.weight = tex_eval_si(s, b->reflectance_tex, si, wav);
         return bs;
     }
     if (b->type == MTSB_BSDF_ROUGHCONDUCTOR) {         /* roughconductor.cpp:196-276 */
@@ -742,18 +762,18 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         float weight = b->sample_visible ? mf_g1(&distr, bs.wo, m)
                                          : mf_g1(&distr, si->wi, m) * mf_g1(&distr, bs.wo, m) * vdot(si->wi, m) / (cos_theta_i * m.z);
         bs.pdf /= 4.f * vdot(bs.wo, m);
-        col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+        col eta = tex_eval_si(s, b->eta_tex, si, wav), k = tex_eval_si(s, b->k_tex, si, wav);
         col F = fresnel_conductor_col(vdot(si->wi, m), eta, k);
-        if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+        if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
         bs.weight = active ? cscale(F, weight) : C1(0.f);
         return bs;
     }
     if (b->type == MTSB_BSDF_CONDUCTOR) {              /* conductor.cpp: sample (delta reflection, weight = R * F(cos_i)) */
         if (!(cos_theta_i > 0.f)) return bs;
         bs.wo = V(-si->wi.x, -si->wi.y, si->wi.z); bs.pdf = 1.f; bs.delta = 1;
-        col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+        col eta = tex_eval_si(s, b->eta_tex, si, wav), k = tex_eval_si(s, b->k_tex, si, wav);
         col F = fresnel_conductor_col(cos_theta_i, eta, k);
-        if (b->specular_reflectance_tex >= 0) F = cmul(tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav), F);
+        if (b->specular_reflectance_tex >= 0) F = cmul(tex_eval_si(s, b->specular_reflectance_tex, si, wav), F);
         bs.weight = F; return bs;
     }
     if (b->type == MTSB_BSDF_PLASTIC) {                /* plastic.cpp:178-245 */
@@ -765,13 +785,13 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         if (s1 < prob_specular) {
             bs.wo = V(-si->wi.x, -si->wi.y, si->wi.z); bs.pdf = prob_specular; bs.delta = 1;
             col value = C1(f_i / bs.pdf);
-            if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
             bs.weight = value;
         } else {
             bs.wo = cosine_hemisphere(sx, sy); bs.pdf = prob_diffuse * (INV_PI_F * bs.wo.z);
             float f_o; fresnel(bs.wo.z, b->eta, &f_o, &ct, &e1, &e2);
             float fdr_int = fresnel_diffuse_reflectance(1.f / b->eta), inv_eta_2 = 1.f / (b->eta * b->eta);
-            col value = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+            col value = tex_eval_si(s, b->reflectance_tex, si, wav);
             for (int i = 0; i < 4; ++i) value.c[i] /= 1.f - (b->nonlinear ? value.c[i] * fdr_int : fdr_int);
             bs.weight = cscale(value, inv_eta_2 * (1.f - f_i) * (1.f - f_o) / prob_diffuse);
         }
@@ -810,12 +830,12 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
         float dwh_dwo;
         if (selected_r) {
             bs.wo = vsub(vscale(m, 2.f * wim), si->wi);
-            if (b->specular_reflectance_tex >= 0) weight = cmul(weight, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            if (b->specular_reflectance_tex >= 0) weight = cmul(weight, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
             dwh_dwo = 1.f / (4.f * vdot(bs.wo, m));
         } else {
             bs.wo = vsub(vscale(m, fmaf(wim, eta_ti, cos_theta_t)), vscale(si->wi, eta_ti));
             col factor = C1(sqrf(eta_ti));
-            if (b->specular_transmittance_tex >= 0) factor = cmul(factor, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav));
+            if (b->specular_transmittance_tex >= 0) factor = cmul(factor, tex_eval_si(s, b->specular_transmittance_tex, si, wav));
             weight = cmul(weight, factor);
             dwh_dwo = (sqrf(bs.eta) * vdot(bs.wo, m)) / sqrf(wim + bs.eta * vdot(bs.wo, m));
         }
@@ -831,15 +851,15 @@ static obs bsdf_sample_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const
     bs.wo = selected_r ? V(-si->wi.x, -si->wi.y, si->wi.z) : V(-eta_ti * si->wi.x, -eta_ti * si->wi.y, cos_theta_t);
     bs.eta = selected_r ? 1.f : eta_it;
     col w = C1(1.f);
-    if (selected_r) { if (b->specular_reflectance_tex >= 0) w = cmul(w, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav)); }
-    else { if (b->specular_transmittance_tex >= 0) w = cmul(w, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav)); w = cscale(w, sqrf(eta_ti)); }
+    if (selected_r) { if (b->specular_reflectance_tex >= 0) w = cmul(w, tex_eval_si(s, b->specular_reflectance_tex, si, wav)); }
+    else { if (b->specular_transmittance_tex >= 0) w = cmul(w, tex_eval_si(s, b->specular_transmittance_tex, si, wav)); w = cscale(w, sqrf(eta_ti)); }
     bs.weight = w; return bs;
 }
 static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, v3 wo, col *val, float *pdf, const float *wav) {
     *val = C1(0.f); *pdf = 0.f;
     float cos_theta_i = si->wi.z, cos_theta_o = wo.z;
     if (b->type == MTSB_BSDF_DIFFUSE) {                /* diffuse.cpp:105-135 */
-        if (cos_theta_i > 0.f && cos_theta_o > 0.f) { *val = cscale(cscale(tex_eval(s, b->reflectance_tex, si->u, si->v, wav), INV_PI_F), cos_theta_o); *pdf = INV_PI_F * cos_theta_o; }
+        if (cos_theta_i > 0.f && cos_theta_o > 0.f) { *val = cscale(cscale(tex_eval_si(s, b->reflectance_tex, si, wav), INV_PI_F), cos_theta_o); *pdf = INV_PI_F * cos_theta_o; }
         return;
     }
     if (b->type == MTSB_BSDF_ROUGHCONDUCTOR) {         /* roughconductor.cpp:278-394 */
@@ -849,9 +869,9 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         float D = mf_eval(&distr, H);
         if (D != 0.f) {
             float G = mf_g1(&distr, si->wi, H) * mf_g1(&distr, wo, H), result = D * G / (4.f * cos_theta_i);
-            col eta = tex_eval(s, b->eta_tex, si->u, si->v, wav), k = tex_eval(s, b->k_tex, si->u, si->v, wav);
+            col eta = tex_eval_si(s, b->eta_tex, si, wav), k = tex_eval_si(s, b->k_tex, si, wav);
             col F = fresnel_conductor_col(vdot(si->wi, H), eta, k);
-            if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            if (b->specular_reflectance_tex >= 0) F = cmul(F, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
             *val = cscale(F, result);
         }
         if (vdot(si->wi, H) > 0.f && vdot(wo, H) > 0.f)
@@ -870,10 +890,10 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         float G = mf_g1(&distr, si->wi, m) * mf_g1(&distr, wo, m);
         if (reflect) {
             *val = C1(F * D * G / (4.f * fabsf(cos_theta_i)));
-            if (b->specular_reflectance_tex >= 0) *val = cmul(*val, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+            if (b->specular_reflectance_tex >= 0) *val = cmul(*val, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
         } else {
             *val = C1(fabsf((sqrf(inv_eta) * (1.f - F) * D * G * eta * eta * wim * wom) / (cos_theta_i * sqrf(wim + eta * wom))));
-            if (b->specular_transmittance_tex >= 0) *val = cmul(*val, tex_eval(s, b->specular_transmittance_tex, si->u, si->v, wav));
+            if (b->specular_transmittance_tex >= 0) *val = cmul(*val, tex_eval_si(s, b->specular_transmittance_tex, si, wav));
         }
         if (!(wim * cos_theta_i > 0.f && wom * cos_theta_o > 0.f)) return;
         float dwh_dwo = reflect ? 1.f / (4.f * wom) : (eta * eta * wom) / sqrf(wim + eta * wom);
@@ -890,9 +910,9 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         v3 H = vnormalize(vadd(wo, si->wi));
         float D = mf_eval(&distr, H), F, ct, e1, e2; fresnel(vdot(si->wi, H), b->eta, &F, &ct, &e1, &e2);
         col value = C1(F * D * (mf_g1(&distr, si->wi, H) * mf_g1(&distr, wo, H)) / (4.f * cos_theta_i));
-        if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval(s, b->specular_reflectance_tex, si->u, si->v, wav));
+        if (b->specular_reflectance_tex >= 0) value = cmul(value, tex_eval_si(s, b->specular_reflectance_tex, si, wav));
         float t_i = rough_lerp(tab, cos_theta_i), t_o = rough_lerp(tab, cos_theta_o);
-        col diff = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+        col diff = tex_eval_si(s, b->reflectance_tex, si, wav);
         for (int i = 0; i < 4; ++i) diff.c[i] /= 1.f - (b->nonlinear ? diff.c[i] * tab[64] : tab[64]);
         diff = cscale(diff, INV_PI_F * (1.f / (b->eta * b->eta)) * cos_theta_o * t_i * t_o);
         for (int i = 0; i < 4; ++i) val->c[i] = value.c[i] + diff.c[i];
@@ -906,7 +926,7 @@ static void bsdf_eval_pdf_nested(const orc_scene *s, const mtsb_bsdf_desc *b, co
         if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return;
         float f_i, f_o, ct, e1, e2; fresnel(cos_theta_i, b->eta, &f_i, &ct, &e1, &e2); fresnel(cos_theta_o, b->eta, &f_o, &ct, &e1, &e2);
         float fdr_int = fresnel_diffuse_reflectance(1.f / b->eta), inv_eta_2 = 1.f / (b->eta * b->eta);
-        col diff = tex_eval(s, b->reflectance_tex, si->u, si->v, wav);
+        col diff = tex_eval_si(s, b->reflectance_tex, si, wav);
         for (int i = 0; i < 4; ++i) diff.c[i] /= 1.f - (b->nonlinear ? diff.c[i] * fdr_int : fdr_int);
         *val = cscale(diff, (INV_PI_F * cos_theta_o) * inv_eta_2 * (1.f - f_i) * (1.f - f_o));
         float ssw = b->specular_sampling_weight, prob_specular = f_i * ssw, prob_diffuse = (1.f - f_i) * (1.f - ssw);
@@ -963,7 +983,7 @@ static float rough_lerp(const float *data, float x) {
 }
 /* MaskBSDF::eval_opacity (mask.cpp): clamp(opacity->eval_1(si), 0, 1); the texture is single-channel */
 static float mask_opacity(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, const float *wav) {
-    return fminf(fmaxf(tex_eval(s, b->opacity_tex_plus1 - 1, si->u, si->v, wav).c[0], 0.f), 1.f);
+    return fminf(fmaxf(tex_eval_si(s, b->opacity_tex_plus1 - 1, si, wav).c[0], 0.f), 1.f);
 }
 static obs bsdf_sample(const orc_scene *s, const mtsb_bsdf_desc *b, const osi *si, float s1, float sx, float sy, const float *wav) {
     if (b->opacity_tex_plus1 > 0) {                          /* mask.cpp:95-128 */

@@ -770,3 +770,28 @@ class RefBuild:
     def sensor_sample_ray(self, pos, sensor=0):
         r = self._query("sensor", _f32(pos), 8, 1, sensor)
         return r[:, :4].copy(), r[:, 4:].copy()
+
+
+def attribute_scene(res=(48, 32), spp=8, per_face=False):
+    """`mesh_attribute` textures (src/textures/mesh_attribute.cpp): a sphere whose diffuse reflectance is a per-vertex
+    colour attribute (or per-face), and a ground quad whose reflectance is a per-face scalar attribute x scale."""
+    sd = SceneData()
+    rng = np.random.default_rng(12)
+    s1 = M.displaced_sphere(20, 40)
+    s1.attributes["vertex_color"] = (0.1 + 0.8 * rng.random((len(s1.positions), 3))).astype(np.float32)
+    s1.attributes["face_color"] = (0.1 + 0.8 * rng.random((len(s1.faces), 3))).astype(np.float32)
+    s1.bsdf = sd.add_diffuse(sd.add_texture_mesh_attribute(None, per_face=per_face, name="face_color" if per_face else "vertex_color"))
+    s1.bsdf = sd.bind_mesh_attributes(s1)
+    sd.add_mesh(s1)
+    ground = M.quad([-10, -1.2, -10], [-10, -1.2, 10], [10, -1.2, 10], [10, -1.2, -10])
+    ground.attributes["face_weight"] = np.array([[0.9], [0.3]], np.float32)
+    ground.bsdf = sd.add_diffuse(sd.add_texture_mesh_attribute(None, per_face=True, scale=0.8, name="face_weight"))
+    ground.bsdf = sd.bind_mesh_attributes(ground)
+    sd.add_mesh(ground)
+    light = M.quad([-0.5, 3, -0.5], [0.5, 3, -0.5], [0.5, 3, 0.5], [-0.5, 3, 0.5])
+    light.bsdf = sd.add_diffuse(0.5)
+    sd.add_mesh(light, area_radiance=(18.4, 15.6, 8.0))
+    sd.add_constant((0.2, 0.25, 0.3))
+    sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 4, 5, spp
+    return sd

@@ -399,8 +399,22 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     }
     if (boundary < 2) return;
     // ---- boundary term seen from the first path vertex (same sequence as mtsb_render_grad)
-    Edge2Ctx e2; e2.edges = edges.data(); e2.n_edges = (uint32_t) edges.size(); e2.candidates = 16; e2.eps = 1e-3f;
-    std::vector<float> cdf3(edges.size()); acc = 0;
+    // edges of ALL meshes, mesh by mesh (all_edge_list() in grad.cuh): static occluders sweep over moving material too
+    std::vector<uint4> all_edges;
+    for (size_t mi = 0; mi < s->meshes.size(); ++mi) {
+        const MeshDev &mm = s->meshes[mi];
+        std::vector<std::pair<uint64_t, uint32_t>> k2;
+        for (uint32_t f = 0; f < mm.face_count; ++f) { uint4 fc = s->faces[mm.face_begin + f]; uint32_t v[3] = { fc.x, fc.y, fc.z };
+            for (int k = 0; k < 3; ++k) { uint32_t a = v[k], c = v[(k + 1) % 3]; if (a > c) std::swap(a, c); k2.emplace_back(((uint64_t) a << 32) | c, mm.face_begin + f); } }
+        std::sort(k2.begin(), k2.end());
+        for (size_t i = 0; i < k2.size();) {
+            size_t j = i + 1; while (j < k2.size() && k2[j].first == k2[i].first) ++j;
+            all_edges.push_back(make_uint4((uint32_t) (k2[i].first >> 32), (uint32_t) k2[i].first, k2[i].second, j - i > 1 ? k2[i + 1].second : 0xffffffffu));
+            i = j;
+        }
+    }
+    Edge2Ctx e2; e2.edges = all_edges.data(); e2.n_edges = (uint32_t) all_edges.size(); e2.candidates = 16; e2.eps = 1e-3f;
+    std::vector<float> cdf3(all_edges.size()); acc = 0;
     for (uint32_t k = 0; k < e2.n_edges; ++k) { acc += edge_len3_body(s->dev, e2, k); cdf3[k] = (float) acc; }
     e2.cdf = cdf3.data(); e2.total_len = (float) acc;
     std::vector<float4> aux(4 * (size_t) pool); e2.aux = aux.data();

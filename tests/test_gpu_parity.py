@@ -489,3 +489,46 @@ def test_moment_integrator_second_moments(mi):
     sx = mi.load_string(xml)
     sx.render(spp=4, seed=1)
     assert np.isfinite(sx.film_moments()).all() and sx.film_moments().max() > 0
+
+
+@pytest.mark.parametrize("per_face,mode", [(False, "rgb"), (True, "rgb"), (False, "spectral")])
+def test_mesh_attribute_textures_match_oracle(mi, per_face, mode):
+    """`mesh_attribute` textures (src/textures/mesh_attribute.cpp -> Mesh::eval_attribute, mesh.h:278-318), per vertex and
+    per face, rgb and spectral (coefficients): same sample streams as the oracle, which is pinned against the reference CLI
+    in tests/test_oracle_vs_reference_build.py."""
+    sd = H.attribute_scene(res=(48, 32), spp=8, per_face=per_face)
+    if mode == "spectral":
+        sd = H.spectral(sd)
+    sc, orc = mi.Scene(sd), H.Oracle(sd)
+    a, b = sc.render(spp=8, seed=4), orc.render(spp=8, seed=4)
+    bad = np.abs(a - b).max(axis=2) > 1e-3 * (1 + np.abs(b).max(axis=2))
+    assert bad.mean() < 0.02, bad.mean()
+    assert np.abs(a - b).sum() / np.abs(b).sum() < 1e-2
+    # a buffer whose size does not match the mesh is rejected
+    from mitsuba2_b200._abi import MtsbError
+    sd2 = H.attribute_scene(res=(8, 8), spp=1, per_face=per_face)
+    t = next(t for t in sd2.textures if t["type"] == mi._abi.TEX_MESH_ATTRIBUTE and t.get("data") is not None)
+    t["data"] = t["data"][:-1].copy()
+    with pytest.raises(MtsbError):
+        mi.Scene(sd2)
+
+
+def test_scene_from_device_buffers_equals_host_buffers(mi):
+    """mtsb_mesh_desc.mem = MTSB_MEM_DEVICE: meshes handed over as CUDA tensors (no host staging) give the same scene."""
+    import torch
+    from mitsuba2_b200.scenedata import Mesh
+    sd_h = H.material_scene((32, 24), 4)
+    sd_d = H.material_scene((32, 24), 4)
+    for i, m in enumerate(sd_d.meshes):
+        t = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).cuda()      # noqa: E731
+        dm = Mesh(t(m.positions), torch.from_numpy(m.faces.astype(np.int32)).cuda(), t(m.normals), t(m.texcoords), m.bsdf, m.emitter, m.name)
+        sd_d.meshes[i] = dm
+    a, b = mi.Scene(sd_h), mi.Scene(sd_d)
+    om, dm_ = H.Oracle(sd_h).sensor_sample_ray(np.random.default_rng(0).random((20000, 2)))
+    assert np.array_equal(a.intersect_closest_raw(om, dm_).view(np.uint32), b.intersect_closest_raw(om, dm_).view(np.uint32))
+    assert np.abs(a.render(spp=4, seed=1) - b.render(spp=4, seed=1)).max() < 1e-4
+    bad = Mesh(torch.zeros((3, 3), device="cuda"), torch.tensor([[0, 1, 7]], dtype=torch.int32, device="cuda"))
+    sd_d.meshes[1] = bad
+    bad.bsdf = 0
+    with pytest.raises(mi._abi.MtsbError):
+        mi.Scene(sd_d)

@@ -144,14 +144,17 @@ def test_vertex_gradient_shadow_boundary_matches_fd():
     sd = H.vgrad_scene("quadshadow", "diffuse", res=16, spp=128)
     wgt = _ramp(16)
     h = HostSim(sd)
-    g2 = h.render_grad_vertices(wgt, 0, seed=3, boundary=2, edge_fraction=1.0).reshape(-1, 3)
+    # both sides are Monte Carlo estimates (a single seed of either scatters by ~8 %): average the adjoint over 4 seeds and the
+    # differences over 2 seeds at 2048 spp.  Measured over 8 / 4 seeds: tx -6.83 +- 0.08 vs -7.14 +- 0.11, tz -1.55 +- 0.05 vs
+    # -1.37 +- 0.09, scale -8.01 +- 0.10 vs -8.03 +- 0.19.
+    g2 = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=2, edge_fraction=1.0).reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
     g1 = h.render_grad_vertices(wgt, 0, seed=3, boundary=1, edge_fraction=1.0).reshape(-1, 3)
     P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
     F = H.displacement_fields(P0)
-    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "tz", "scale")}
+    fds = {n: float(np.mean([H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 2048, s_) for s_ in (3, 4)])) for n in ("tx", "tz", "scale")}
     ref = max(abs(v) for v in fds.values())
     for n, fd in fds.items():
-        assert abs(float((g2 * F[n]).sum()) - fd) < 0.12 * ref, (n, float((g2 * F[n]).sum()), fd)
+        assert abs(float((g2 * F[n]).sum()) - fd) < 0.10 * ref, (n, float((g2 * F[n]).sum()), fd)
     assert abs(float((g1 * F["scale"]).sum()) - fds["scale"]) > 0.5 * ref      # the term matters here
 
 

@@ -132,3 +132,16 @@ def test_material_scene_image_oracle_vs_reference_cli():
     frac = _ztest(mean, ref_img, var, 8 * 128, 1024)
     assert frac >= 0.9975, frac
     assert abs(mean.mean() - ref_img.mean()) < 0.02 * ref_img.mean()
+
+
+@pytest.mark.parametrize("per_face", [False, True])
+def test_mesh_attribute_textures_oracle_vs_reference_cli(per_face):
+    """`mesh_attribute` (src/textures/mesh_attribute.cpp): per-vertex / per-face colours read from the PLY by the reference's
+    own loader (find_other_fields, ply.cpp:594-690) vs the oracle's restatement of Mesh::eval_attribute."""
+    sd = H.attribute_scene(res=(64, 48), spp=64, per_face=per_face)
+    ref_img, _ = H.RefBuild(sd).render(spp=512)
+    orc = H.Oracle(sd)
+    runs = np.stack([orc.render(spp=64, seed=300 + k) for k in range(16)]).astype(np.float64)
+    frac = _ztest(runs.mean(axis=0), ref_img, runs.var(axis=0, ddof=1) * 64, 16 * 64, 512)
+    assert frac >= 0.9975, frac
+    assert abs(runs.mean() - ref_img.mean()) < 0.01 * ref_img.mean()

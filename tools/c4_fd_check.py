@@ -20,12 +20,19 @@ sys.path.insert(0, ROOT)
 
 
 def run(res=512, spp=64, passes=8, fd_spp=4096, n_tex=64, n_vtx=32, eps_list=(0.25, 0.5, 1.0), device=0, seed=11, tex_res=512, log=None,
-        max_depth=None, boundary=2, edge_fraction=0.25, rr_off=False, same_samples=False):
+        max_depth=None, boundary=2, edge_fraction=0.25, rr_off=False, same_samples=False, variant="full"):
     import mitsuba2_b200 as mi
     from mitsuba2_b200 import scenes
     mi.set_variant("cuda_b200_rgb")
     sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=res, spp=spp, tex_res=tex_res)
     mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
+    if variant == "black_sphere":        # only what the sphere does to the rest of the room (its shadow, its silhouette) is left
+        sd.meshes[mid].bsdf = sd.add_diffuse(0.0)
+    elif variant == "black_room":        # only the sphere's own shading (and its silhouette against black) is left
+        blk = sd.add_diffuse(0.0)
+        for i, m in enumerate(sd.meshes):
+            if i != mid and m.emitter < 0:
+                m.bsdf = blk
     if max_depth is not None:
         sd.max_depth = max_depth
     if rr_off:
@@ -45,7 +52,7 @@ def run(res=512, spp=64, passes=8, fd_spp=4096, n_tex=64, n_vtx=32, eps_list=(0.
     sc.update_texture(tex, T0); sc.update_vertices(mid, P0)
     cur = sc.render(spp=max(256, fd_spp // 4), seed=998)
     dl = (2.0 * (cur - target) / cur.size).astype(np.float32)
-    out = {"config": {"max_depth": sd.max_depth, "rr_depth": sd.rr_depth, "boundary": boundary, "edge_fraction": edge_fraction, "same_samples": same_samples, "res": res, "adjoint_spp": spp, "adjoint_passes": passes, "fd_spp": fd_spp, "texels": n_tex, "vertex_coords": n_vtx,
+    out = {"config": {"variant": variant, "max_depth": sd.max_depth, "rr_depth": sd.rr_depth, "boundary": boundary, "edge_fraction": edge_fraction, "same_samples": same_samples, "res": res, "adjoint_spp": spp, "adjoint_passes": passes, "fd_spp": fd_spp, "texels": n_tex, "vertex_coords": n_vtx,
                       "sphere_triangles": int(len(sd.meshes[mid].faces)), "loss": float(np.mean((cur - target) ** 2))}}
     # ---- adjoint
     t0 = time.time()
@@ -70,7 +77,7 @@ def run(res=512, spp=64, passes=8, fd_spp=4096, n_tex=64, n_vtx=32, eps_list=(0.
     # has weight (the floor region the camera and the first bounces see) and uniformly
     B = 8
     gb = gt[: h // B * B, : w // B * B].reshape(h // B, B, w // B, B, -1).sum(axis=(1, 3))        # adjoint of a block = sum over its texels
-    flat = np.abs(gb).reshape(-1)
+    flat = np.abs(gb).reshape(-1) + 1e-300
     pick = np.concatenate([rng.choice(flat.size, n_tex // 2, replace=False, p=flat / flat.sum()), rng.choice(flat.size, n_tex - n_tex // 2, replace=False)])
     fd_t, an_t = [], []
     for k, idx in enumerate(pick):
@@ -130,8 +137,8 @@ if __name__ == "__main__":
     ap.add_argument("--res", type=int, default=512); ap.add_argument("--spp", type=int, default=64); ap.add_argument("--passes", type=int, default=8)
     ap.add_argument("--fd-spp", type=int, default=4096); ap.add_argument("--texels", type=int, default=64); ap.add_argument("--vertex-coords", type=int, default=32)
     ap.add_argument("--quiet", action="store_true"); ap.add_argument("--max-depth", type=int, default=None); ap.add_argument("--boundary", type=int, default=2)
-    ap.add_argument("--edge-fraction", type=float, default=0.25); ap.add_argument("--rr-off", action="store_true"); ap.add_argument("--same-samples", action="store_true")
+    ap.add_argument("--edge-fraction", type=float, default=0.25); ap.add_argument("--rr-off", action="store_true"); ap.add_argument("--same-samples", action="store_true"); ap.add_argument("--variant", default="full")
     a = ap.parse_args()
     r = run(a.res, a.spp, a.passes, a.fd_spp, a.texels, a.vertex_coords, log=None if a.quiet else lambda s: print(s, file=sys.stderr, flush=True),
-            max_depth=a.max_depth, boundary=a.boundary, edge_fraction=a.edge_fraction, rr_off=a.rr_off, same_samples=a.same_samples)
+            max_depth=a.max_depth, boundary=a.boundary, edge_fraction=a.edge_fraction, rr_off=a.rr_off, same_samples=a.same_samples, variant=a.variant)
     print(json.dumps(r))
