@@ -33,6 +33,7 @@ def build_oracle():
 def build_hostsim():
     csrc = os.path.join(ROOT, "mitsuba2_b200", "csrc")
     src = [os.path.join(ROOT, "tests", "hostsim", "hostsim.cu")] + [os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith(".h")]
+    src.append(os.path.join(ROOT, "include", "mtsb200.h"))
     if _newer(src, HOSTSIM_SO):
         subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-diag-suppress", "20013", "-Xcompiler", "-fPIC",
                                "-shared", "-o", HOSTSIM_SO, src[0]])
