@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 6
+#define MTSB_ABI_VERSION 7
 
 enum { MTSB_OK = 0, MTSB_E_INVALID = -1, MTSB_E_CUDA = -2, MTSB_E_NOMEM = -3, MTSB_E_CANCELLED = -4 };
 enum { MTSB_MEM_HOST = 0, MTSB_MEM_DEVICE = 1 };
@@ -120,6 +120,25 @@ typedef struct mtsb_mesh_desc {
                                    staging copy); device buffers make scene creation a set of device-to-device copies (since ABI 6) */
 } mtsb_mesh_desc;
 
+/* Analytic shapes as BVH leaf primitives (since ABI 7): src/shapes/sphere.cpp:276-300, disk.cpp:144-165, cylinder.cpp:248-287,
+ * rectangle.cpp:142-164 (`ray_intersect` / `ray_test`), their `fill_surface_interaction`, `sample_position` /
+ * `sample_direction` / `pdf_direction`.  `to_world` is the plugin's object-to-world transform with `center` / `radius`
+ * (sphere.cpp:104-106) or `p0` / `p1` / `radius` (cylinder.cpp:88-97) already folded in by the host; the library applies
+ * the plugin's update() (sphere, cylinder: decomposition into scale / rotation / translation, no shear; disk, rectangle:
+ * flip_normals = to_world * scale(1, 1, -1)).
+ * Global primitive index: after the faces of all meshes, one primitive per shape in array order (`m_primitive_map`,
+ * kdtree.h:2382-2400, with the meshes listed first).  Closest-hit records of a disk / rectangle carry the object-space
+ * hit position (x, y) in (u, v) (the two floats the plugins cache); sphere / cylinder: 0.
+ * An AREA emitter refers to shape k through mesh_id = n_meshes + k.  Gradient calls reject scenes with shapes. */
+enum { MTSB_SHAPE_SPHERE = 1, MTSB_SHAPE_DISK = 2, MTSB_SHAPE_CYLINDER = 3, MTSB_SHAPE_RECTANGLE = 4 };
+typedef struct mtsb_shape_desc {
+    int32_t  type;              /* MTSB_SHAPE_* */
+    int32_t  flip_normals;
+    float    to_world[16];      /* row-major 4x4 */
+    int32_t  bsdf_id;           /* index into bsdfs[] */
+    int32_t  emitter_id;        /* index into emitters[] or -1 */
+} mtsb_shape_desc;
+
 /* Sensor + film: src/sensors/perspective.cpp:106-222, src/films/hdrfilm.cpp, rfilters. */
 /* src/rfilters/{box,tent,gaussian,mitchell,catmullrom,lanczos}.cpp */
 enum { MTSB_RFILTER_BOX = 0, MTSB_RFILTER_TENT = 1, MTSB_RFILTER_GAUSSIAN = 2, MTSB_RFILTER_MITCHELL = 3, MTSB_RFILTER_CATMULLROM = 4,
@@ -154,6 +173,8 @@ typedef struct mtsb_scene_desc {
     mtsb_integrator_desc integrator;
     int32_t mode;               /* MTSB_MODE_RGB (scalar_rgb semantics) or MTSB_MODE_SPECTRAL (scalar_spectral: 4 wavelengths
                                    per path, include/mitsuba/core/spectrum.h:304-316, film in XYZ via cie1931_xyz :147-217) */
+    uint32_t n_shapes;          /* analytic shapes (since ABI 7) */
+    const mtsb_shape_desc *shapes;
 } mtsb_scene_desc;
 
 /* ---- SoA ray / hit records (128-bit loads) ------------------------------------------ */

@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
 
 MEM_HOST, MEM_DEVICE = 0, 1
+SHAPE_SPHERE, SHAPE_DISK, SHAPE_CYLINDER, SHAPE_RECTANGLE = 1, 2, 3, 4
 TEX_CONSTANT, TEX_BITMAP, TEX_REGULAR, TEX_IRREGULAR, TEX_UNIFORM, TEX_MESH_ATTRIBUTE = 0, 1, 2, 3, 4, 5
 MODE_RGB, MODE_SPECTRAL = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHDIELECTRIC, BSDF_ROUGHPLASTIC = 0, 1, 2, 3, 4, 5, 6
@@ -49,6 +50,11 @@ class MeshDesc(C.Structure):
                 ("emitter_id", C.c_int32), ("mem", C.c_int32)]
 
 
+class ShapeDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("flip_normals", C.c_int32), ("to_world", C.c_float * 16),
+                ("bsdf_id", C.c_int32), ("emitter_id", C.c_int32)]
+
+
 class SensorDesc(C.Structure):
     _fields_ = [("to_world", C.c_float * 16), ("sample_to_camera", C.c_float * 16), ("near_clip", C.c_float),
                 ("far_clip", C.c_float), ("film_width", C.c_uint32), ("film_height", C.c_uint32),
@@ -64,7 +70,8 @@ class SceneDesc(C.Structure):
                 ("n_emitters", C.c_uint32), ("n_sensors", C.c_uint32),
                 ("meshes", C.POINTER(MeshDesc)), ("bsdfs", C.POINTER(BsdfDesc)), ("textures", C.POINTER(TextureDesc)),
                 ("emitters", C.POINTER(EmitterDesc)), ("sensors", C.POINTER(SensorDesc)),
-                ("integrator", IntegratorDesc), ("mode", C.c_int32)]
+                ("integrator", IntegratorDesc), ("mode", C.c_int32),
+                ("n_shapes", C.c_uint32), ("shapes", C.POINTER(ShapeDesc))]
 
 
 class Stats(C.Structure):

@@ -86,6 +86,8 @@ struct mtsb_scene {
     std::map<int, std::vector<float>> emitter_pos;   // host positions of EMITTER meshes only (area CDF is built on the host in double)
     // device
     DevBuf<float> pos, nrm, uv; DevBuf<uint4> faces;
+    std::vector<ShapeDev> shapes; DevBuf<ShapeDev> d_shapes;   // analytic shapes; meshes[n_tri_meshes + k] is shape k
+    uint32_t n_tri_meshes = 0;
     DevBuf<MeshDev> d_meshes; DevBuf<TexDev> d_tex; DevBuf<BsdfDev> d_bsdfs; DevBuf<EmitterDev> d_emitters;
     std::vector<std::unique_ptr<DevBuf<float>>> tables;       // texture data, cdfs, envmap levels
     std::vector<int> tex_table;                               // texture id -> tables index (-1 constant)
@@ -186,7 +188,7 @@ static int build_bvh(mtsb_scene *s) {
     CU(bounds.alloc(6));
     CU(s->nodes.alloc(5 * ((size_t) n + 1))); CU(s->tris.alloc(3 * (size_t) n));
     BvhBuild b;
-    b.pos = s->pos.p; b.faces = s->faces.p; b.n = n;
+    b.pos = s->pos.p; b.faces = s->faces.p; b.shapes = s->d_shapes.p; b.n = n;
     b.tlo = tlo.p; b.thi = thi.p; b.keys = keys.p; b.order = order.p; b.left = left.p; b.right = right.p; b.parent = parent.p;
     b.rfirst = rfirst.p; b.rlast = rlast.p; b.nlo = nlo.p; b.nhi = nhi.p; b.flags = flags.p;
     b.nodes = s->nodes.p; b.tris = s->tris.p; b.wide_bin = wide_bin.p; b.counters = counters.p;
@@ -261,7 +263,7 @@ static int build_bvh(mtsb_scene *s) {
     CU(cudaEventSynchronize(s->ctx->ev1));
     CU(cudaEventElapsedTime(&s->build_stats.ms_build, s->ctx->ev0, s->ctx->ev1));
     s->build_stats.bvh_nodes = end; s->build_stats.bvh_depth = depth;
-    s->dev.bvh.nodes = s->nodes.p; s->dev.bvh.tris = s->tris.p;
+    s->dev.bvh.nodes = s->nodes.p; s->dev.bvh.tris = s->tris.p; s->dev.bvh.shapes = s->shapes.empty() ? nullptr : s->d_shapes.p;
     return MTSB_OK;
 }
 
@@ -282,7 +284,7 @@ static int upload_struct_arrays(mtsb_scene *s) {
         CU(s->prim_class.upload(cls.data(), cls.size(), st));
     }
     CU(cudaStreamSynchronize(st));
-    s->dev.pos = s->pos.p; s->dev.nrm = s->nrm.p; s->dev.uv = s->uv.p; s->dev.faces = s->faces.p;
+    s->dev.pos = s->pos.p; s->dev.nrm = s->nrm.p; s->dev.uv = s->uv.p; s->dev.faces = s->faces.p; s->dev.shapes = s->d_shapes.p;
     s->dev.meshes = s->d_meshes.p; s->dev.tex = s->d_tex.p; s->dev.bsdfs = s->d_bsdfs.p; s->dev.emitters = s->d_emitters.p;
     return MTSB_OK;
 }
@@ -293,6 +295,7 @@ static int build_area_tables(mtsb_scene *s) {
         EmitterDev &em = s->emitters[e];
         if (em.type != MTSB_EMITTER_AREA) continue;
         const MeshDev &m = s->meshes[em.mesh];
+        if (m.shape >= 0) { em.cdf = nullptr; em.normalization = s->shapes[m.shape].inv_area; continue; }      // analytic: sampled in closed form
         AreaTable t;
         try { t = build_area_table(s->emitter_pos.at(em.mesh).data(), s->mesh_faces[em.mesh].data(), m.face_count); }
         catch (const std::exception &ex) { return fail(MTSB_E_INVALID, ex.what()); }
@@ -334,8 +337,9 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
     // Host copies are kept only where the host needs them: face indices (edge lists, area tables) and emitter positions.
     size_t nv_total = 0, nf_total = 0;
     for (uint32_t i = 0; i < d->n_meshes; ++i) { nv_total += d->meshes[i].vertex_count; nf_total += d->meshes[i].face_count; }
-    if (nf_total > (size_t) kPrimMask) return fail(MTSB_E_INVALID, "more than 2^30 - 1 triangles");
-    CU(s->pos.alloc(3 * nv_total)); CU(s->nrm.alloc(3 * nv_total)); CU(s->uv.alloc(2 * nv_total)); CU(s->faces.alloc(nf_total));
+    CHECK_ARG(d->n_shapes == 0 || d->shapes != nullptr);
+    if (nf_total + d->n_shapes > (size_t) kPrimMask) return fail(MTSB_E_INVALID, "more than 2^30 - 1 primitives");
+    CU(s->pos.alloc(3 * nv_total)); CU(s->nrm.alloc(3 * nv_total)); CU(s->uv.alloc(2 * nv_total)); CU(s->faces.alloc(nf_total + d->n_shapes));
     DevBuf<uint32_t> raw_faces;
     uint32_t vbase = 0, fbase = 0;
     for (uint32_t i = 0; i < d->n_meshes; ++i) {
@@ -347,6 +351,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         const cudaMemcpyKind kind = m.mem == MTSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
         MeshDev md; md.face_begin = fbase; md.face_count = m.face_count; md.vert_begin = vbase; md.vert_count = m.vertex_count;
         md.bsdf = m.bsdf_id; md.emitter = m.emitter_id; md.has_normals = m.normals != nullptr; md.has_uv = m.texcoords != nullptr;
+        md.shape = -1;
         s->meshes.push_back(md);
         const size_t nv = m.vertex_count, nf = m.face_count;
         CU(cudaMemcpyAsync(s->pos.p + 3 * (size_t) vbase, m.positions, 3 * nv * sizeof(float), kind, st));
@@ -373,6 +378,26 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         }
         s->computed_normals.push_back(false);
         vbase += m.vertex_count; fbase += m.face_count;
+    }
+    s->n_tri_meshes = d->n_meshes;
+    // ---- analytic shapes: one primitive and one MeshDev entry each, after the triangle meshes
+    if (d->n_shapes) {
+        std::vector<uint4> sf(d->n_shapes);
+        for (uint32_t k = 0; k < d->n_shapes; ++k) {
+            const mtsb_shape_desc &sh = d->shapes[k];
+            CHECK_ARG(sh.bsdf_id >= 0 && (uint32_t) sh.bsdf_id < d->n_bsdfs);
+            CHECK_ARG(sh.emitter_id < (int32_t) d->n_emitters);
+            ShapeDev sd; const char *err = nullptr;
+            if (!make_shape_dev(sh.type, sh.flip_normals, sh.to_world, sd, &err)) return fail(MTSB_E_INVALID, err);
+            s->shapes.push_back(sd);
+            MeshDev md; md.face_begin = fbase + k; md.face_count = 1; md.vert_begin = 0; md.vert_count = 0;
+            md.bsdf = sh.bsdf_id; md.emitter = sh.emitter_id; md.has_normals = 0; md.has_uv = 1; md.shape = (int) k;
+            s->meshes.push_back(md);
+            sf[k] = make_uint4(k, kAnalyticTag, (uint32_t) sh.type, d->n_meshes + k);
+        }
+        CU(s->d_shapes.upload(s->shapes.data(), s->shapes.size(), st));
+        CU(cudaMemcpyAsync(s->faces.p + fbase, sf.data(), sf.size() * sizeof(uint4), cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
     }
     CU(cudaStreamSynchronize(st));
     // ---- colour mode
@@ -470,6 +495,9 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
         const BsdfDev &b = s->bsdfs[m.bsdf];
         const int ids[6] = { b.refl, b.eta, b.k, b.spec_r, b.spec_t, b.opacity };
         for (int id : ids)
+            if (id >= 0 && s->tex[id].type == MTSB_TEX_MESH_ATTRIBUTE && m.shape >= 0)
+                return fail(MTSB_E_INVALID, "mesh_attribute texture on an analytic shape");
+        for (int id : ids)
             if (id >= 0 && s->tex[id].type == MTSB_TEX_MESH_ATTRIBUTE && s->tex[id].w != (s->tex[id].h == 1 ? m.face_count : m.vert_count))
                 return fail(MTSB_E_INVALID, "mesh_attribute texture: element count does not match the mesh that uses it");
     }
@@ -488,7 +516,8 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             ed.radiance_tex = e.radiance_tex;
         }
         if (e.type == MTSB_EMITTER_AREA) {
-            CHECK_ARG(e.mesh_id >= 0 && (uint32_t) e.mesh_id < d->n_meshes && d->meshes[e.mesh_id].emitter_id == (int32_t) i);
+            CHECK_ARG(e.mesh_id >= 0 && (uint32_t) e.mesh_id < d->n_meshes + d->n_shapes);
+            CHECK_ARG(((uint32_t) e.mesh_id < d->n_meshes ? d->meshes[e.mesh_id].emitter_id : d->shapes[e.mesh_id - d->n_meshes].emitter_id) == (int32_t) i);
             ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
         } else if (e.type == MTSB_EMITTER_CONSTANT) {
             if (s->dev.env_emitter >= 0) return fail(MTSB_E_INVALID, "only one environment emitter is allowed");
@@ -851,7 +880,7 @@ extern "C" int mtsb_film_put(mtsb_scene *s, uint32_t sensor_id, uint64_t n, cons
 // Parameter updates (Mesh::parameters_changed, BitmapTexture::parameters_changed)
 // ---------------------------------------------------------------------------------------------------
 extern "C" int mtsb_scene_update_vertices(mtsb_scene *s, uint32_t mesh_id, const float *positions, int mem) {
-    CHECK_ARG(s && mesh_id < s->meshes.size() && positions);
+    CHECK_ARG(s && mesh_id < s->n_tri_meshes && positions);
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     const MeshDev &m = s->meshes[mesh_id];

@@ -6,7 +6,7 @@
 //   -> leaf triangles re-laid out contiguously per node (48 B, watertight test after Woop et al. 2013).
 // All bodies are HD so tests/hostsim can execute them sequentially on the CPU.
 #pragma once
-#include "vec.h"
+#include "shapes.h"
 
 namespace mtsb {
 
@@ -45,12 +45,15 @@ HD int popc32(uint32_t x) {
 }
 
 constexpr int kMaxLeafTris = 3;
+constexpr uint32_t kAnalyticTag = 0xffffffffu;   // faces[prim].y of an analytic shape primitive
 
 struct BvhBuild {
     // inputs
     const float *pos;        // 3*V, all meshes concatenated
     const uint4 *faces;      // (i0,i1,i2,mesh_id) with global vertex indices; index = global prim id
-    uint32_t n;              // triangles
+                             // analytic shape: (shape index, kAnalyticTag, type, mesh_id)
+    const ShapeDev *shapes;  // analytic shape table (may be null when there is none)
+    uint32_t n;              // primitives (triangles + analytic shapes)
     // scratch
     float4 *tlo, *thi;       // per-triangle bounds (input order)
     uint64_t *keys; uint32_t *order;     // morton keys / sorted triangle order
@@ -69,6 +72,11 @@ struct BvhBuild {
 
 HD void tri_bounds_body(const BvhBuild &b, uint32_t i, float3 &lo, float3 &hi) {
     uint4 f = b.faces[i];
+    if (f.y == kAnalyticTag) {
+        shape_bounds(b.shapes[f.x], lo, hi);
+        b.tlo[i] = mk4(lo, 0.f); b.thi[i] = mk4(hi, 0.f);
+        return;
+    }
     float3 p0 = mk3(b.pos[3 * f.x], b.pos[3 * f.x + 1], b.pos[3 * f.x + 2]);
     float3 p1 = mk3(b.pos[3 * f.y], b.pos[3 * f.y + 1], b.pos[3 * f.y + 2]);
     float3 p2 = mk3(b.pos[3 * f.z], b.pos[3 * f.z + 1], b.pos[3 * f.z + 2]);
@@ -341,6 +349,12 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
                 uint32_t prim = b.order[first + q];
                 uint4 f = b.faces[prim];
                 uint32_t o = 3 * (tri_base + tri_off + q);
+                if (f.y == kAnalyticTag) {      // analytic leaf: type tag in a1.w (0 for triangles), shape index in a2.w
+                    b.tris[o + 0] = make_float4(0.f, 0.f, 0.f, u2f(prim));
+                    b.tris[o + 1] = make_float4(0.f, 0.f, 0.f, u2f(f.z));
+                    b.tris[o + 2] = make_float4(0.f, 0.f, 0.f, u2f(f.x));
+                    continue;
+                }
                 b.tris[o + 0] = make_float4(b.pos[3 * f.x], b.pos[3 * f.x + 1], b.pos[3 * f.x + 2], u2f(prim));
                 b.tris[o + 1] = make_float4(b.pos[3 * f.y], b.pos[3 * f.y + 1], b.pos[3 * f.y + 2], 0.f);
                 b.tris[o + 2] = make_float4(b.pos[3 * f.z], b.pos[3 * f.z + 1], b.pos[3 * f.z + 2], 0.f);
@@ -365,6 +379,7 @@ struct Bvh {
     const uint4 *nodes;
     const float4 *tris;
     uint32_t n_tris;
+    const ShapeDev *shapes;   // analytic leaf primitives (null: triangles only)
 };
 
 // Woop et al. 2013 watertight test.  The per-ray axis permutation + shear is folded into three row vectors so the
@@ -558,7 +573,7 @@ static unsigned long long g_trav_nodes = 0, g_trav_tris = 0;
 // ray by one node visit (plus the triangles that visit selected), so a kernel can interleave rays on a lane
 // (persistent threads with dynamic fetch) while the host simulator just loops.
 struct Trav {
-    float3 o, idir; RayWoop rw;
+    float3 o, d, idir; RayWoop rw;
     float mint, tmax;
     uint32_t octinv;
     uint2 G;            // current node group: x = first child index, y = hits<<24 | imask
@@ -568,7 +583,7 @@ struct Trav {
 template <typename Stack>
 HD void trav_init(Trav &tr, Stack &st, float3 o, float3 d, float mint, float maxt) {
     const float big = 1e30f;
-    tr.o = o;
+    tr.o = o; tr.d = d;
     tr.idir = mk3(fabsf(d.x) > 1e-30f ? 1.f / d.x : copysignf(big, d.x),
                   fabsf(d.y) > 1e-30f ? 1.f / d.y : copysignf(big, d.y),
                   fabsf(d.z) > 1e-30f ? 1.f / d.z : copysignf(big, d.z));
@@ -605,7 +620,9 @@ HD bool trav_step(const Bvh &bvh, Trav &tr, Stack &st) {
             float4 a0 = ldg4f(tp), a1 = ldg4f(tp + 1), a2 = ldg4f(tp + 2);
             float t, u, v;
             TRAV_TRI();
-            if (woop_intersect(tr.rw, tr.o, xyz(a0), xyz(a1), xyz(a2), tr.mint, tr.tmax, t, u, v)) {
+            bool ok = f2u(a1.w) != 0u ? shape_intersect(bvh.shapes[f2u(a2.w)], tr.o, tr.d, tr.mint, tr.tmax, t, u, v)
+                                      : woop_intersect(tr.rw, tr.o, xyz(a0), xyz(a1), xyz(a2), tr.mint, tr.tmax, t, u, v);
+            if (ok) {
                 tr.found = true;
                 tr.hit.t = t;
                 if (AnyHit) return true;

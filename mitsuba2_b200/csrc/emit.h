@@ -134,10 +134,84 @@ HD DirSampleT<M> env_sample_direction(const SceneDev &sc, const EmitterDev &e, f
 
 // ---- area light on a mesh (src/emitters/area.cpp:103-125, src/librender/shape.cpp:252-283,
 //      src/librender/mesh.cpp:320-365, include/mitsuba/core/distr_1d.h:144-203) ---------------------
+// warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:262-267)
+HD float3 square_to_uniform_sphere(float sx, float sy) {
+    float z = fmaf(-2.f, sy, 1.f), r = safe_sqrt(fmaf(-z, z, 1.f));
+    float sn, cs; sincospif(2.f * sx, &sn, &cs);
+    return mk3(r * cs, r * sn, z);
+}
+// Shape::sample_direction of an analytic shape: sphere.cpp:182-255 (cone of directions subtended by the sphere, uniform
+// inside), the others Shape::sample_direction (shape.cpp:252-270) over sample_position (disk.cpp:127-141,
+// cylinder.cpp:214-236, rectangle.cpp:114-127).  Fills p, n, d, dist, pdf.
+static __host__ __device__ __noinline__ void shape_sample_direction(const ShapeDev &sh, float3 ref_p, float sx, float sy,
+                                                                   float3 &p, float3 &n, float3 &d, float &dist, float &pdf) {
+    if (sh.type == kShapeSphere) {
+        float3 dc_v = sh.center - ref_p;
+        float dc_2 = dot(dc_v, dc_v);
+        float radius_adj = sh.radius * (sh.flip ? (1.f + kRayEpsilon) : (1.f - kRayEpsilon));
+        float3 dir;
+        if (dc_2 > sqr(radius_adj)) {
+            float inv_dc = 1.f / sqrtf(dc_2), sin_theta_max = sh.radius * inv_dc, sin_theta_max_2 = sqr(sin_theta_max),
+                  inv_sin_theta_max = 1.f / sin_theta_max, cos_theta_max = safe_sqrt(1.f - sin_theta_max_2);
+            float sin_theta_2 = sin_theta_max_2 > 0.00068523f ? 1.f - sqr(fmaf(cos_theta_max - 1.f, sx, 1.f)) : sin_theta_max_2 * sx,
+                  cos_theta = safe_sqrt(1.f - sin_theta_2);
+            float cos_alpha = sin_theta_2 * inv_sin_theta_max + cos_theta * safe_sqrt(fmaf(-sin_theta_2, sqr(inv_sin_theta_max), 1.f)),
+                  sin_alpha = safe_sqrt(fmaf(-cos_alpha, cos_alpha, 1.f));
+            float sin_phi, cos_phi; sincosf(sy * (2.f * kPi), &sin_phi, &cos_phi);
+            Frame fr; fr.n = dc_v * -inv_dc; coordinate_system(fr.n, fr.s, fr.t);
+            dir = fr.to_world(mk3(cos_phi * sin_alpha, sin_phi * sin_alpha, cos_alpha));
+            p = mk3(fmaf(dir.x, sh.radius, sh.center.x), fmaf(dir.y, sh.radius, sh.center.y), fmaf(dir.z, sh.radius, sh.center.z));
+            d = p - ref_p;
+            float dist2 = dot(d, d);
+            dist = sqrtf(dist2); d = d / dist;
+            pdf = kInvTwoPi / (1.f - cos_theta_max);
+            if (dist == 0.f) pdf = 0.f;
+        } else {
+            dir = square_to_uniform_sphere(sx, sy);
+            p = mk3(fmaf(dir.x, sh.radius, sh.center.x), fmaf(dir.y, sh.radius, sh.center.y), fmaf(dir.z, sh.radius, sh.center.z));
+            d = p - ref_p;
+            float dist2 = dot(d, d);
+            dist = sqrtf(dist2); d = d / dist;
+            pdf = sh.inv_area * dist2 / fabsf(dot(d, dir));
+        }
+        n = sh.flip ? -dir : dir;
+        return;
+    }
+    if (sh.type == kShapeDisk) {
+        float px, py; square_to_uniform_disk_concentric(sx, sy, px, py);
+        p = xform_point_affine(sh.to_world, mk3(px, py, 0.f)); n = sh.n;
+    } else if (sh.type == kShapeCylinder) {
+        float st, ct; sincosf(2.f * kPi * sy, &st, &ct);
+        p = xform_point_affine(sh.to_world, mk3(ct * sh.radius, st * sh.radius, sx * sh.length));
+        n = sh.flip ? mk3(-ct, -st, 0.f) : mk3(ct, st, 0.f);      // cylinder.cpp:222-232 returns the object-space normal as is; kept for parity
+    } else {
+        p = xform_point_affine(sh.to_world, mk3(fmaf(sx, 2.f, -1.f), fmaf(sy, 2.f, -1.f), 0.f)); n = sh.n;
+    }
+    d = p - ref_p;
+    float dist2 = dot(d, d);
+    dist = sqrtf(dist2); d = d / dist;
+    float dp = fabsf(dot(d, n));
+    pdf = sh.inv_area * (dp != 0.f ? dist2 / dp : 0.f);
+}
+// Sphere::pdf_direction (sphere.cpp:257-270); the other shapes use Shape::pdf_direction (shape.cpp:272-283)
+static __host__ __device__ __noinline__ float shape_pdf_direction(const ShapeDev &sh, float3 ref_p, float3 d, float3 n, float dist) {
+    float dp = fabsf(dot(d, n));
+    float area_pdf = sh.inv_area * (dp != 0.f ? (dist * dist) / dp : 0.f);
+    if (sh.type != kShapeSphere) return area_pdf;
+    float sin_alpha = sh.radius * (1.f / norm(sh.center - ref_p)), cos_alpha = safe_sqrt(1.f - sin_alpha * sin_alpha);
+    return sin_alpha < 1.f - kEpsilon ? kInvTwoPi / (1.f - cos_alpha) : sh.inv_area * sqr(dist) / dp;
+}
+
 template <typename M>
 HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {
     DirSampleT<M> ds;
     const MeshDev m = sc.meshes[e.mesh];
+    if (m.shape >= 0) {
+        shape_sample_direction(sc.shapes[m.shape], ref_p, sx, sy, ds.p, ds.n, ds.d, ds.dist, ds.pdf);
+        bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
+        ds.value = active ? emitter_radiance<M>(sc, e, wav) / ds.pdf : M::splat(0.f);
+        return ds;
+    }
     float value = sy * e.cdf_sum;
     const float *cdf = e.cdf;
     uint32_t idx = binary_search(e.valid_lo, e.valid_hi, [&](uint32_t i) { return cdf[i] < value; });
@@ -164,19 +238,15 @@ HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, 
     ds.value = active ? emitter_radiance<M>(sc, e, wav) / ds.pdf : M::splat(0.f);
     return ds;
 }
-HD float area_pdf_direction(const EmitterDev &e, float3 d, float3 n, float dist) {
+HD float area_pdf_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float3 d, float3 n, float dist) {
+    int shape = sc.meshes[e.mesh].shape;
+    if (shape >= 0) return dot(d, n) < 0.f ? shape_pdf_direction(sc.shapes[shape], ref_p, d, n, dist) : 0.f;
     float dp = fabsf(dot(d, n));
     float pdf = e.normalization * (dp != 0.f ? (dist * dist) / dp : 0.f);
     return dot(d, n) < 0.f ? pdf : 0.f;
 }
 
 // ---- Scene::sample_emitter_direction (src/librender/scene.cpp:141-176), without the shadow ray ---
-// warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:262-267)
-HD float3 square_to_uniform_sphere(float sx, float sy) {
-    float z = fmaf(-2.f, sy, 1.f), r = safe_sqrt(fmaf(-z, z, 1.f));
-    float sn, cs; sincospif(2.f * sx, &sn, &cs);
-    return mk3(r * cs, r * sn, z);
-}
 // ConstantBackgroundEmitter::sample_direction (src/emitters/constant.cpp:77-103); pdf_direction = 1/(4 pi)
 template <typename M>
 HD DirSampleT<M> constant_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {

@@ -94,6 +94,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     CHECK_ARG(s && sensor_id < s->sensors.size() && spp_count > 0 && spp_begin + spp_count <= spp_total && dL_dimage);
     CHECK_ARG(grad_texture || grad_vertices);
     if (s->spectral) return fail(MTSB_E_INVALID, "mtsb_render_grad: the adjoint pass is implemented for MTSB_MODE_RGB only");
+    if (!s->shapes.empty()) return fail(MTSB_E_INVALID, "mtsb_render_grad: scenes with analytic shapes are not supported (triangle meshes only)");
     size_t ntex = 0, nvert = 0;
     if (grad_texture) {
         CHECK_ARG(tex_id >= 0 && (size_t) tex_id < s->tex.size());
@@ -102,7 +103,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         ntex = (size_t) td.w * td.h * td.ch;
     }
     if (grad_vertices) {
-        CHECK_ARG(mesh_id >= 0 && (size_t) mesh_id < s->meshes.size());
+        CHECK_ARG(mesh_id >= 0 && (size_t) mesh_id < s->n_tri_meshes);
         if (s->meshes[mesh_id].emitter >= 0) return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex gradients of an emitter mesh are not supported");
         nvert = 3 * (size_t) s->meshes[mesh_id].vert_count;
     }

@@ -6,6 +6,8 @@
 #include <cmath>
 #include <cstdint>
 #include <stdexcept>
+#include <cstring>
+#include "shapes.h"
 
 namespace mtsb {
 
@@ -109,6 +111,77 @@ inline bool invert4x4(const float *m, float *inv) {
     double det = a[0]*o[0] + a[1]*o[4] + a[2]*o[8] + a[3]*o[12];
     if (det == 0.0) return false;
     for (int i = 0; i < 16; ++i) inv[i] = (float) (o[i] / det);
+    return true;
+}
+
+// The analytic shape plugins' constructor + update(): sphere.cpp:100-135, cylinder.cpp:84-127, disk.cpp:76-98,
+// rectangle.cpp:78-95.  `tw` = the plugin's object-to-world matrix (row-major 4x4) with center / radius / p0 / p1 already
+// folded in.  Sphere and cylinder decompose it into scale, rotation and translation (enoki transform_decompose: polar
+// decomposition by ten scaled Newton steps Q <- (g Q + Q^-T / g) / 2) and rebuild it without shear.
+inline bool make_shape_dev(int type, int flip_normals, const float *tw, ShapeDev &out, const char **err) {
+    memset(&out, 0, sizeof(out));
+    out.type = type; out.flip = flip_normals ? 1 : 0;
+    double A[3][3], T[3] = { tw[3], tw[7], tw[11] };
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) A[i][j] = tw[4 * i + j];
+    auto inv_t3 = [](const double M[3][3], double R[3][3]) {      // inverse transpose
+        double c00 = M[1][1] * M[2][2] - M[1][2] * M[2][1], c01 = M[1][2] * M[2][0] - M[1][0] * M[2][2], c02 = M[1][0] * M[2][1] - M[1][1] * M[2][0];
+        double det = M[0][0] * c00 + M[0][1] * c01 + M[0][2] * c02;
+        if (det == 0.0) return false;
+        double id = 1.0 / det;
+        R[0][0] = c00 * id; R[0][1] = c01 * id; R[0][2] = c02 * id;
+        R[1][0] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id; R[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id; R[1][2] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
+        R[2][0] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id; R[2][1] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id; R[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+        return true;
+    };
+    float m[16] = { 0 };
+    m[15] = 1.f;
+    if (type == kShapeSphere || type == kShapeCylinder) {
+        double Q[3][3], Qi[3][3];
+        memcpy(Q, A, sizeof(Q));
+        for (int it = 0; it < 10; ++it) {
+            if (!inv_t3(Q, Qi)) { *err = "shape to_world is singular"; return false; }
+            double fq = 0, fi = 0;
+            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { fq += Q[i][j] * Q[i][j]; fi += Qi[i][j] * Qi[i][j]; }
+            double gamma = std::sqrt(std::sqrt(fi) / std::sqrt(fq));
+            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) Q[i][j] = Q[i][j] * (gamma * 0.5) + Qi[i][j] * (0.5 / gamma);
+        }
+        double S[3][3];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { S[i][j] = 0; for (int k = 0; k < 3; ++k) S[i][j] += Q[k][i] * A[k][j]; }
+        double detq = Q[0][0] * (Q[1][1] * Q[2][2] - Q[1][2] * Q[2][1]) - Q[0][1] * (Q[1][0] * Q[2][2] - Q[1][2] * Q[2][0]) + Q[0][2] * (Q[1][0] * Q[2][1] - Q[1][1] * Q[2][0]);
+        if (detq < 0) for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { Q[i][j] = -Q[i][j]; S[i][j] = -S[i][j]; }
+        double radius = S[0][0], length = S[2][2];
+        if (radius <= 0) { radius = std::fabs(radius); out.flip = !out.flip; }
+        out.radius = (float) radius; out.length = (float) length;
+        out.center = make_float3((float) T[0], (float) T[1], (float) T[2]);
+        double sc = type == kShapeSphere ? (double) out.radius : 1.0;
+        for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) m[4 * i + j] = (float) (Q[i][j] * sc); m[4 * i + 3] = (float) T[i]; }
+        out.inv_area = type == kShapeSphere ? 1.f / (4.f * 3.14159265358979323846f * out.radius * out.radius)
+                                            : 1.f / (2.f * 3.14159265358979323846f * out.radius * out.length);
+    } else if (type == kShapeDisk || type == kShapeRectangle) {
+        for (int i = 0; i < 16; ++i) m[i] = tw[i];
+        if (flip_normals) for (int i = 0; i < 4; ++i) m[4 * i + 2] = -m[4 * i + 2];      // to_world * scale(1, 1, -1)
+        out.flip = 0;
+    } else { *err = "unknown shape type"; return false; }
+    memcpy(out.to_world, m, sizeof(m));
+    if (!invert4x4(out.to_world, out.to_object)) { *err = "shape to_world is singular"; return false; }
+    if (type == kShapeDisk || type == kShapeRectangle) {
+        const float *w = out.to_world, *o = out.to_object;
+        float k = type == kShapeRectangle ? 2.f : 1.f;
+        float3 du = make_float3(w[0] * k, w[4] * k, w[8] * k), dv = make_float3(w[1] * k, w[5] * k, w[9] * k);
+        float3 n = make_float3(o[8], o[9], o[10]);               // Transform * Normal = inverse transpose
+        float nl = std::sqrt(n.x * n.x + n.y * n.y + n.z * n.z);
+        out.n = make_float3(n.x / nl, n.y / nl, n.z / nl);
+        out.dp_du = du; out.dp_dv = dv;
+        if (type == kShapeRectangle) {
+            float3 c = make_float3(du.y * dv.z - du.z * dv.y, du.z * dv.x - du.x * dv.z, du.x * dv.y - du.y * dv.x);
+            out.inv_area = 1.f / std::sqrt(c.x * c.x + c.y * c.y + c.z * c.z);
+        } else {
+            float lu = std::sqrt(du.x * du.x + du.y * du.y + du.z * du.z), lv = std::sqrt(dv.x * dv.x + dv.y * dv.y + dv.z * dv.z);
+            float st = (du.x * dv.x + du.y * dv.y + du.z * dv.z) / (lu * lv);      // dot(frame.t, frame.s)
+            float h = std::sqrt(lv * lv - (lv * st) * (lv * st));
+            out.inv_area = 1.f / (3.14159265358979323846f * lu * h);
+        }
+    }
     return true;
 }
 

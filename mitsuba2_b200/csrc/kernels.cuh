@@ -168,6 +168,13 @@ __device__ __forceinline__ uint32_t float_order_bits(float t) {      // monotone
     uint32_t b = __float_as_uint(t);
     return b ^ ((uint32_t) ((int32_t) b >> 31) | 0x80000000u);
 }
+// out of line: keeps the double-precision quadratic solve out of the triangle loop's register budget
+// (results by value: reference parameters of a non-inlined call would force a stack frame on the caller)
+__device__ __noinline__ float4 shape_intersect_slot(const ShapeDev *sh, float3 o, float3 d, float mint, float maxt) {
+    float t, u, v;
+    bool ok = shape_intersect(*sh, o, d, mint, maxt, t, u, v);
+    return make_float4(t, u, v, ok ? 1.f : 0.f);
+}
 template <bool AnyHit, typename Sink>
 __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count, const float4 *__restrict__ o_mint,
                                                  const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill, Sink sink) {
@@ -263,13 +270,22 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
                     bool mine = j < n_items;
                     uint32_t it = mine ? ws.items[j] : 0u, src = it >> 5;
                     uint32_t stb = __shfl_sync(0xffffffffu, tb, src);
+                    // scenes with analytic shapes: the testing lane re-reads the owner's ray (the shared record holds the
+                    // sheared Woop rows, not the direction)
+                    uint32_t sray = bvh.shapes != nullptr ? __shfl_sync(0xffffffffu, ray, src) : 0u;
                     if (mine) {
                         const float4 *tp = bvh.tris + 3 * (size_t) (stb + (it & 31u));
                         float4 a0 = __ldg(tp), a1 = __ldg(tp + 1), a2 = __ldg(tp + 2);
                         float4 r0 = ws.ray[0][src], r1 = ws.ray[1][src], r2 = ws.ray[2][src], r3 = ws.ray[3][src];
                         RayWoop rw; rw.rx = xyz(r1); rw.ry = xyz(r2); rw.rz = xyz(r3);
                         float t, u, v;
-                        if (woop_intersect(rw, xyz(r0), xyz(a0), xyz(a1), xyz(a2), r0.w, r1.w, t, u, v)) {
+                        bool ok;
+                        if (bvh.shapes != nullptr && f2u(a1.w) != 0u) {
+                            float4 r = shape_intersect_slot(bvh.shapes + f2u(a2.w), xyz(r0), xyz(d_maxt[sray]), r0.w, r1.w);
+                            t = r.x; u = r.y; v = r.z; ok = r.w != 0.f;
+                        } else
+                            ok = woop_intersect(rw, xyz(r0), xyz(a0), xyz(a1), xyz(a2), r0.w, r1.w, t, u, v);
+                        if (ok) {
                             ws.hitrec[lane] = make_float4(t, u, v, a0.w);
                             atomicMin(&ws.best[src], ((unsigned long long) float_order_bits(t) << 32) | lane);
                         }
@@ -331,7 +347,9 @@ __global__ void k_trace_naive(Bvh bvh, uint32_t count, const float4 *o_mint, con
     for (uint32_t k = 0; k < bvh.n_tris; ++k) {
         float4 a0 = bvh.tris[3 * k], a1 = bvh.tris[3 * k + 1], a2 = bvh.tris[3 * k + 2];
         float t, u, v;
-        if (woop_intersect(rw, xyz(o), xyz(a0), xyz(a1), xyz(a2), o.w, tmax, t, u, v)) { tmax = t; h.t = t; h.u = u; h.v = v; h.prim = f2u(a0.w); }
+        bool ok = f2u(a1.w) != 0u ? shape_intersect(bvh.shapes[f2u(a2.w)], xyz(o), xyz(d), o.w, tmax, t, u, v)
+                                  : woop_intersect(rw, xyz(o), xyz(a0), xyz(a1), xyz(a2), o.w, tmax, t, u, v);
+        if (ok) { tmax = t; h.t = t; h.u = u; h.v = v; h.prim = f2u(a0.w); }
     }
     hits[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
 }
@@ -560,6 +578,7 @@ k_splat(SensorDev sn, RenderBatch b) {
     bool live = i < b.n_paths;
     float4 xyza = make_float4(0.f, 0.f, 0.f, 0.f); float wgt = 0.f; float fx = -10.f, fy = -10.f;
     if (live) { xyza = result_to_xyza<M>(b.result[i]); wgt = 1.f; path_film_pos(sn, b, i, fx, fy); }
+    if (live && !film_sample_valid(xyza, wgt)) { live = false; xyza = make_float4(0.f, 0.f, 0.f, 0.f); wgt = 0.f; }   // imageblock.cpp:84-108
     if (sn.radius <= 1.f) {
         int lx = (int) ceilf(fx - 1.f), ly = (int) ceilf(fy - 1.f);
         bool ok = live && lx >= 0 && ly >= 0 && lx < (int) sn.width && ly < (int) sn.height;

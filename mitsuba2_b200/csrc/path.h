@@ -185,7 +185,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
             Le = si.wi.z > 0.f ? emitter_radiance<M>(sc, e, wav) : M::splat(0.f);
             if (depth > 1 && !prev_delta) {
                 float3 dd = si.p - o; float dist = norm(dd); dd = dd / dist;
-                emitter_pdf = area_pdf_direction(e, dd, si.sh.n, dist);
+                emitter_pdf = area_pdf_direction(sc, e, o, dd, si.sh.n, dist);
             }
         } else if (e.type == 1) {
             Le = env_eval<M>(sc, e, d, wav);
@@ -282,8 +282,15 @@ HD float rfilter_eval(const SensorDev &sn, float x) {
     return fmaxf(0.f, expf(alpha * x * x) - expf(alpha * sn.radius * sn.radius));
 }
 
+// ImageBlock::put drops a sample with a non-finite or negative (< -1e-5) channel, weight included, instead of
+// accumulating it (src/librender/imageblock.cpp:84-108; warn_negative / warn_invalid are on for the path integrator's blocks)
+HD bool film_sample_valid(float4 xyza, float wgt) {
+    float lo = fminf(fminf(fminf(xyza.x, xyza.y), fminf(xyza.z, xyza.w)), wgt), sum = xyza.x + xyza.y + xyza.z + xyza.w + wgt;
+    return lo >= -1e-5f && fabsf(sum) <= FLT_MAX && xyza.x == xyza.x && xyza.y == xyza.y && xyza.z == xyza.z && xyza.w == xyza.w;
+}
 template <typename AddFn>
 HD void film_put(const SensorDev &sn, float px, float py, float4 xyza, float wgt, AddFn add) {
+    if (!film_sample_valid(xyza, wgt)) return;
     // full-film block: offset 0, border 0 => pos = pos_ - 0.5
     float x = px - 0.5f, y = py - 0.5f;
     if (sn.radius > 1.f) {

@@ -38,6 +38,7 @@ struct EmitterDev {
 struct MeshDev {
     uint32_t face_begin, face_count, vert_begin, vert_count;
     int bsdf, emitter, has_normals, has_uv;
+    int shape;              // >= 0: an analytic shape (one primitive), index into SceneDev::shapes; -1: triangle mesh
 };
 struct SensorDev {
     float to_world[16], sample_to_camera[16];
@@ -52,6 +53,7 @@ struct SceneDev {
     Bvh bvh;
     const float *pos, *nrm, *uv;
     const uint4 *faces;
+    const ShapeDev *shapes;
     const MeshDev *meshes; const TexDev *tex; const BsdfDev *bsdfs; const EmitterDev *emitters;
     int n_emitters, env_emitter;
     int max_depth, rr_depth;

@@ -13,6 +13,47 @@ HD float3 ld3(const float *a, uint32_t i) { return mk3(a[3 * i], a[3 * i + 1], a
 
 // ShapeKDTree::create_surface_interaction (include/mitsuba/render/kdtree.h:2334-2368) +
 // Mesh::fill_surface_interaction (src/librender/mesh.cpp:399-462); miss: scene_native.inl:29-31.
+// Shape::fill_surface_interaction of the analytic shapes (sphere.cpp:329-373, disk.cpp:167-205, cylinder.cpp:330-361,
+// rectangle.cpp:180-205): position, normal, uv and dp_du; (cx, cy) = the floats ray_intersect cached (local x, y).
+// Out of line: triangle scenes never pay for it in registers.
+static __host__ __device__ __noinline__ void shape_fill_si(const ShapeDev &sh, float3 o, float3 d, float t, float cx, float cy,
+                                                           float3 &p, float3 &n, float &u, float &v, float3 &dp_du) {
+    float3 hitp = mk3(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));
+    if (sh.type == kShapeSphere) {
+        n = normalize(hitp - sh.center);
+        p = mk3(fmaf(n.x, sh.radius, sh.center.x), fmaf(n.y, sh.radius, sh.center.y), fmaf(n.z, sh.radius, sh.center.z));
+        float3 l = xform_point_affine(sh.to_object, p);
+        // unit_angle_z (include/mitsuba/core/vector.h)
+        float temp = 2.f * asinf(0.5f * norm(mk3(l.x, l.y, l.z - mulsign(1.f, l.z))));
+        float theta = l.z >= 0.f ? temp : kPi - temp;
+        float phi = atan2f(l.y, l.x);
+        if (phi < 0.f) phi += 2.f * kPi;
+        u = phi * kInvTwoPi; v = theta * kInvPi;
+        dp_du = xform_vec(sh.to_world, mk3(-l.y, l.x, 0.f)) * (2.f * kPi);
+        if (sh.flip) n = -n;
+    } else if (sh.type == kShapeDisk) {
+        float r = sqrtf(cx * cx + cy * cy), inv_r = 1.f / r;
+        float vv = atan2f(cy, cx) * kInvTwoPi;
+        if (vv < 0.f) vv += 1.f;
+        float cp = r != 0.f ? cx * inv_r : 1.f, sp = r != 0.f ? cy * inv_r : 0.f;
+        dp_du = xform_vec(sh.to_world, mk3(cp, sp, 0.f));
+        n = sh.n; u = r; v = vv; p = hitp;
+    } else if (sh.type == kShapeCylinder) {
+        float3 l = xform_point_affine(sh.to_object, hitp);
+        float phi = atan2f(l.y, l.x);
+        if (phi < 0.f) phi += 2.f * kPi;
+        u = phi * kInvTwoPi; v = l.z / sh.length;
+        dp_du = xform_vec(sh.to_world, mk3(-l.y, l.x, 0.f) * (2.f * kPi));
+        float3 dp_dv = xform_vec(sh.to_world, mk3(0.f, 0.f, sh.length));
+        n = normalize(cross(dp_du, dp_dv));
+        p = hitp + n * (sh.radius - sqrtf(l.x * l.x + l.y * l.y));
+        if (sh.flip) n = -n;
+    } else {
+        n = sh.n; dp_du = sh.dp_du; p = hitp;
+        u = fmaf(cx, 0.5f, 0.5f); v = fmaf(cy, 0.5f, 0.5f);
+    }
+}
+
 constexpr uint32_t kPrimMask = 0x3fffffffu;     // primitive ids use 30 bits; the top two carry the shade class in the queues
 HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     SI si;
@@ -22,6 +63,15 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     uint4 f = sc.faces[si.prim];
     si.mesh = (int) f.w;
     const MeshDev m = sc.meshes[f.w];
+    if (f.y == kAnalyticTag) {
+        float3 dp_du;
+        shape_fill_si(sc.shapes[f.x], o, d, hit.x, hit.y, hit.z, si.p, si.n, si.u, si.v, dp_du);
+        si.sh.n = si.n;
+        si.sh.s = normalize(dp_du - si.n * dot(si.n, dp_du));
+        si.sh.t = cross(si.n, si.sh.s);
+        si.wi = si.sh.to_local(-d);
+        return si;
+    }
     float b1 = hit.y, b2 = hit.z, b0 = 1.f - b1 - b2;
     float3 p0 = ld3(sc.pos, f.x), p1 = ld3(sc.pos, f.y), p2 = ld3(sc.pos, f.z);
     float3 dp0 = p1 - p0, dp1 = p2 - p0;

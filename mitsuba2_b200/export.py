@@ -206,6 +206,25 @@ def write_mitsuba_scene(sd, directory, spp=None, sensor=0, file_format="pfm", va
             w.w(f'<emitter type="area"><rgb name="radiance" value="{_vec(e["radiance"])}"/></emitter>')
         w.ind -= 1
         w.w("</shape>")
+    # analytic shapes after the meshes (global primitive index = mesh faces, then one primitive per shape); to_world already
+    # carries center / radius / p0 / p1, so the plugins' own parameters stay at their defaults
+    names = {A.SHAPE_SPHERE: "sphere", A.SHAPE_DISK: "disk", A.SHAPE_CYLINDER: "cylinder", A.SHAPE_RECTANGLE: "rectangle"}
+    for sh in getattr(sd, "shapes", []):
+        if sh["emitter"] >= 0:
+            while pending and pending[0] < sh["emitter"]:
+                k = pending.pop(0)
+                w.emitter(sd.emitters[k], k)
+        w.w(f'<shape type="{names[sh["type"]]}">')
+        w.ind += 1
+        w.w(f'<transform name="to_world"><matrix value="{_matrix(sh["to_world"])}"/></transform>')
+        if sh["flip_normals"]:
+            w.w('<boolean name="flip_normals" value="true"/>')
+        w.bsdf(sd.bsdfs[sh["bsdf"]])
+        if sh["emitter"] >= 0:
+            e = sd.emitters[sh["emitter"]]
+            w.w(f'<emitter type="area"><rgb name="radiance" value="{_vec(e["radiance"])}"/></emitter>')
+        w.ind -= 1
+        w.w("</shape>")
     for k in pending:
         w.emitter(sd.emitters[k], k)
     w.lines.append("</scene>")

@@ -62,7 +62,7 @@ class Scene:
         if getattr(data, "moment", False):      # <integrator type="moment"> around `path` (src/integrators/moment.cpp)
             for i in range(len(data.sensors)):
                 self.enable_moments(True, i)
-        prim_counts = [m.faces.shape[0] for m in data.meshes]
+        prim_counts = [m.faces.shape[0] for m in data.meshes] + [1] * len(getattr(data, "shapes", []))
         self.primitive_map = np.concatenate([[0], np.cumsum(prim_counts)]).astype(np.int64)
 
     def close(self):

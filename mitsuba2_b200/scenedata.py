@@ -100,6 +100,7 @@ class SceneData:
 
     def __init__(self):
         self.meshes, self.bsdfs, self.textures, self.emitters, self.sensors = [], [], [], [], []
+        self.shapes = []                # analytic shapes (sphere / disk / cylinder / rectangle): BVH leaf primitives
         self.max_depth, self.rr_depth = -1, 5
         self.spp = 4
         # "rgb" (scalar_rgb semantics) or "spectral" (scalar_spectral): the same authored scene serves both; to_desc()
@@ -293,6 +294,47 @@ class SceneData:
             mesh.emitter = len(self.emitters) - 1
         return mid
 
+    # ---- analytic shapes (src/shapes/{sphere,disk,cylinder,rectangle}.cpp) ----------------------------------
+    def add_shape(self, kind, to_world=None, bsdf=0, flip_normals=False, area_radiance=None, name=None):
+        """One analytic primitive.  ``to_world`` is the plugin's final object-to-world matrix (see add_sphere /
+        add_cylinder for the parameters the plugins fold into it).  Global primitive index = number of mesh faces +
+        position in ``shapes``; an area emitter on it is addressed as mesh ``len(meshes) + shape id`` in the C ABI."""
+        kinds = {"sphere": A.SHAPE_SPHERE, "disk": A.SHAPE_DISK, "cylinder": A.SHAPE_CYLINDER, "rectangle": A.SHAPE_RECTANGLE}
+        sh = {"type": kinds[kind] if isinstance(kind, str) else int(kind), "to_world": _f32(np.eye(4) if to_world is None else to_world).reshape(4, 4),
+              "flip_normals": bool(flip_normals), "bsdf": int(bsdf), "emitter": -1, "name": name or str(kind)}
+        self.shapes.append(sh)
+        sid = len(self.shapes) - 1
+        if area_radiance is not None:
+            self.emitters.append(dict(self._radiance(area_radiance), type=A.EMITTER_AREA, shape_id=sid))
+            sh["emitter"] = len(self.emitters) - 1
+        return sid
+
+    def add_sphere(self, center=(0.0, 0.0, 0.0), radius=1.0, to_world=None, **kw):
+        """sphere.cpp:100-110: to_world * translate(center) * scale(radius)"""
+        m = np.eye(4) if to_world is None else np.asarray(to_world, np.float64).reshape(4, 4)
+        t = np.eye(4); t[:3, 3] = center
+        return self.add_shape("sphere", m @ t @ np.diag([radius, radius, radius, 1.0]), **kw)
+
+    def add_disk(self, to_world=None, **kw):
+        return self.add_shape("disk", to_world, **kw)
+
+    def add_rectangle(self, to_world=None, **kw):
+        return self.add_shape("rectangle", to_world, **kw)
+
+    def add_cylinder(self, p0=(0.0, 0.0, 0.0), p1=(0.0, 0.0, 1.0), radius=1.0, to_world=None, **kw):
+        """cylinder.cpp:84-97: to_world * translate(p0) * to_frame(Frame(p1 - p0)) * scale(radius, radius, 1); the frame is
+        built from the raw difference vector as the plugin does (Frame3f(v) -> coordinate_system(v), frame.h / vector.h)."""
+        m = np.eye(4) if to_world is None else np.asarray(to_world, np.float64).reshape(4, 4)
+        n = np.asarray(p1, np.float64) - np.asarray(p0, np.float64)
+        sign = np.copysign(1.0, n[2])
+        a = -1.0 / (sign + n[2])
+        b = n[0] * n[1] * a
+        s_ = np.array([np.copysign(1.0, n[2]) * n[0] * n[0] * a + 1.0, np.copysign(1.0, n[2]) * b, -np.copysign(1.0, n[2]) * n[0]])
+        t_ = np.array([b, sign + n[1] * n[1] * a, -n[1]])
+        fr = np.eye(4); fr[:3, 0], fr[:3, 1], fr[:3, 2] = s_, t_, n
+        tr = np.eye(4); tr[:3, 3] = p0
+        return self.add_shape("cylinder", m @ tr @ fr @ np.diag([radius, radius, 1.0, 1.0]), **kw)
+
     def _radiance(self, value):
         """rgb triple / scalar -> {"radiance"}; a spectrum ({"wavelengths", "values"}, spectral mode) -> + {"radiance_tex"}"""
         if isinstance(value, dict):
@@ -455,7 +497,7 @@ class SceneData:
             ed[i].radiance_tex = emit_tex.get(i, -1)
             if e["type"] == A.EMITTER_AREA:
                 ed[i].radiance = (C.c_float * 3)(*e["radiance"])
-                ed[i].mesh_id = e["mesh_id"]
+                ed[i].mesh_id = e["mesh_id"] if "mesh_id" in e else len(self.meshes) + e["shape_id"]
             elif e["type"] == A.EMITTER_CONSTANT:
                 ed[i].radiance = (C.c_float * 3)(*e["radiance"])
                 ed[i].mesh_id = -1
@@ -488,13 +530,21 @@ class SceneData:
         desc.n_emitters, desc.n_sensors = len(self.emitters), len(self.sensors)
         desc.meshes, desc.bsdfs, desc.textures, desc.emitters, desc.sensors = md, bd, td, ed, sd
         desc.integrator.max_depth, desc.integrator.rr_depth = self.max_depth, self.rr_depth
-        keep += [md, bd, td, ed, sd]
+        shd = (A.ShapeDesc * max(1, len(self.shapes)))()
+        for i, sh in enumerate(self.shapes):
+            shd[i].type, shd[i].flip_normals = sh["type"], int(sh["flip_normals"])
+            shd[i].to_world = (C.c_float * 16)(*_f32(sh["to_world"]).reshape(16))
+            shd[i].bsdf_id, shd[i].emitter_id = sh["bsdf"], sh["emitter"]
+        desc.n_shapes, desc.shapes = len(self.shapes), shd
+        keep += [md, bd, td, ed, sd, shd]
         return desc, keep
 
     # ---- (de)serialisation for fixtures -------------------------------------------------------
     def save_npz(self, path):
         import json
-        arrays, meta = {}, {"max_depth": self.max_depth, "rr_depth": self.rr_depth, "spp": self.spp, "meshes": [],
+        arrays, meta = {}, {"max_depth": self.max_depth, "rr_depth": self.rr_depth, "spp": self.spp,
+                            "shapes": [dict(sh, to_world=np.asarray(sh["to_world"], np.float64).reshape(16).tolist()) for sh in self.shapes],
+                            "meshes": [],
                             "bsdfs": self.bsdfs, "textures": [], "emitters": [], "sensors": []}
         for i, m in enumerate(self.meshes):
             arrays[f"m{i}_p"], arrays[f"m{i}_f"] = m.positions, m.faces
@@ -529,6 +579,7 @@ class SceneData:
         sd = SceneData()
         sd.max_depth, sd.rr_depth, sd.spp = meta["max_depth"], meta["rr_depth"], meta["spp"]
         sd.bsdfs = meta["bsdfs"]
+        sd.shapes = [dict(sh, to_world=_f32(sh["to_world"]).reshape(4, 4)) for sh in meta.get("shapes", [])]
         for i, m in enumerate(meta["meshes"]):
             sd.meshes.append(Mesh(z[f"m{i}_p"], z[f"m{i}_f"], z[f"m{i}_n"] if f"m{i}_n" in z else None,
                                   z[f"m{i}_t"] if f"m{i}_t" in z else None, m["bsdf"], m["emitter"], m["name"]))

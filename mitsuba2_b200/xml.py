@@ -84,6 +84,9 @@ def load_image(path):
 class _Loader:
     def __init__(self, params, base_dir):
         self.params = dict(params)
+        # `_triangulate_rectangles=True` (not a scene parameter): load <shape type="rectangle"> as two triangles instead of an
+        # analytic primitive (gradient passes differentiate triangle meshes only)
+        self.analytic_shapes = not self.params.pop("_triangulate_rectangles", False)
         self.base_dir = base_dir
         self.named = {}          # id -> element (bsdf / emitter / texture / shape definitions)
         self.sd = SceneData()
@@ -323,12 +326,14 @@ class _Loader:
         elif ty == "serialized":
             m = M.load_serialized(self.resolve(el, p["filename"]), to_world, p.get("shape_index", 0), p.get("face_normals", False),
                                   p.get("flip_normals", False))
-        elif ty == "rectangle":
+        elif ty == "rectangle" and not self.analytic_shapes:
             q = M.quad([-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0])
             q.positions = M._apply(to_world, q.positions)
             m = q
+        elif ty in ("sphere", "disk", "cylinder", "rectangle"):
+            m = None        # analytic BVH leaf primitive (src/shapes/{sphere,disk,cylinder,rectangle}.cpp)
         else:
-            raise NotImplementedError(f"shape plugin '{ty}' is outside the hot-path scope (triangle meshes)")
+            raise NotImplementedError(f"shape plugin '{ty}' is outside the hot-path scope (triangle meshes, sphere, disk, cylinder, rectangle)")
         bsdf = None
         radiance = None
         for c in el:
@@ -342,6 +347,16 @@ class _Loader:
                 if rad[0] not in ("rgb", "spectrum"):
                     raise NotImplementedError("textured area-light radiance")
                 radiance = rad[1]
+        if m is None:
+            b = bsdf if bsdf is not None else self.sd.add_diffuse(0.5)
+            kw = dict(to_world=to_world, bsdf=b, flip_normals=p.get("flip_normals", False), area_radiance=radiance)
+            if ty == "sphere":
+                self.sd.add_sphere(p.get("center", (0.0, 0.0, 0.0)), p.get("radius", 1.0), **kw)
+            elif ty == "cylinder":
+                self.sd.add_cylinder(p.get("p0", (0.0, 0.0, 0.0)), p.get("p1", (0.0, 0.0, 1.0)), p.get("radius", 1.0), **kw)
+            else:
+                self.sd.add_shape(ty, **kw)
+            return
         m.bsdf = bsdf if bsdf is not None else self.sd.add_diffuse(0.5)     # shape.cpp:75-76
         m.bsdf = self.sd.bind_mesh_attributes(m)
         self.sd.add_mesh(m, radiance)

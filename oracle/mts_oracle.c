@@ -299,7 +299,9 @@ void orc_perspective_sample_to_camera(float fov, float near_, float far_, float 
 /* =============================================================================================== */
 /* Scene                                                                                            */
 /* =============================================================================================== */
-typedef struct { uint32_t face_begin, face_count, vert_begin, vert_count; int bsdf, emitter, has_normals, has_uv; } omesh;
+typedef struct { uint32_t face_begin, face_count, vert_begin, vert_count; int bsdf, emitter, has_normals, has_uv; int shape; } omesh;
+/* analytic shape after the plugin's update(): sphere.cpp:112-135, cylinder.cpp:103-127, disk.cpp:81-98, rectangle.cpp:85-95 */
+typedef struct { int type, flip; float to_world[16], to_object[16]; v3 center; float radius, length; v3 n, dp_du, dp_dv; float inv_area; } oshape;
 typedef struct { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf [left, left+count) in order[] ; else children left,left+1 */ } onode;
 typedef struct { int n_levels; float **levels; uint32_t *widths; } oh2d;
 typedef struct {
@@ -312,6 +314,7 @@ struct orc_scene {
     omesh *meshes; mtsb_bsdf_desc *bsdfs; otex *tex; oemitter *emitters; mtsb_sensor_desc *sensors;
     float *pos, *nrm, *uv; uint32_t *faces /* 3 per face, global vertex ids */; uint32_t *face_mesh;
     onode *nodes; uint32_t n_nodes; uint32_t *order;
+    uint32_t n_shapes; oshape *shapes;   /* primitive n_faces + k, meshes[n_meshes + k] */
     int env_emitter; int max_depth, rr_depth;
     int spectral, nch;        /* MTSB_MODE_SPECTRAL: 4 wavelengths per path */
     v3 bbox_lo, bbox_hi;
@@ -327,6 +330,7 @@ static void tri_bounds(const orc_scene *s, uint32_t f, float *lo, float *hi) {
     for (int k = 0; k < 3; ++k) { const float *p = s->pos + 3 * (size_t) s->faces[3 * f + k];
         for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], p[a]); hi[a] = fmaxf(hi[a], p[a]); } }
 }
+static void shape_bounds(const oshape *sh, float *lo, float *hi);
 static float *g_centroid; static int g_axis;
 static int cmp_centroid(const void *a, const void *b) {
     float ca = g_centroid[3 * (size_t) *(const uint32_t *) a + g_axis], cb = g_centroid[3 * (size_t) *(const uint32_t *) b + g_axis];
@@ -350,6 +354,9 @@ static void build_rec(orc_scene *s, uint32_t node, uint32_t begin, uint32_t end,
 static void build_accel(orc_scene *s) {
     free(s->nodes); free(s->order); s->nodes = NULL; s->order = NULL; s->n_nodes = 0;
     s->bbox_lo = V(INFINITY, INFINITY, INFINITY); s->bbox_hi = V(-INFINITY, -INFINITY, -INFINITY);
+    for (uint32_t k = 0; k < s->n_shapes; ++k) { float lo[3], hi[3]; shape_bounds(&s->shapes[k], lo, hi);
+        s->bbox_lo = V(fminf(s->bbox_lo.x, lo[0]), fminf(s->bbox_lo.y, lo[1]), fminf(s->bbox_lo.z, lo[2]));
+        s->bbox_hi = V(fmaxf(s->bbox_hi.x, hi[0]), fmaxf(s->bbox_hi.y, hi[1]), fmaxf(s->bbox_hi.z, hi[2])); }
     if (s->n_faces == 0) return;
     float *blo = malloc(sizeof(float) * 3 * (size_t) s->n_faces), *bhi = malloc(sizeof(float) * 3 * (size_t) s->n_faces);
     g_centroid = malloc(sizeof(float) * 3 * (size_t) s->n_faces);
@@ -361,10 +368,130 @@ static void build_accel(orc_scene *s) {
     }
     s->nodes = malloc(sizeof(onode) * (2 * (size_t) s->n_faces + 1)); s->n_nodes = 1;
     build_rec(s, 0, 0, s->n_faces, blo, bhi);
-    s->bbox_lo = V(s->nodes[0].lo[0], s->nodes[0].lo[1], s->nodes[0].lo[2]); s->bbox_hi = V(s->nodes[0].hi[0], s->nodes[0].hi[1], s->nodes[0].hi[2]);
+    s->bbox_lo = V(fminf(s->bbox_lo.x, s->nodes[0].lo[0]), fminf(s->bbox_lo.y, s->nodes[0].lo[1]), fminf(s->bbox_lo.z, s->nodes[0].lo[2]));
+    s->bbox_hi = V(fmaxf(s->bbox_hi.x, s->nodes[0].hi[0]), fmaxf(s->bbox_hi.y, s->nodes[0].hi[1]), fmaxf(s->bbox_hi.z, s->nodes[0].hi[2]));
     free(blo); free(bhi); free(g_centroid); g_centroid = NULL;
 }
 
+/* ---- analytic shapes --------------------------------------------------------------------------------------------------- */
+static int invert4(const float *m, float *inv);
+static v3 xf_point(const float *m, v3 p) { return V(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3], m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7], m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]); }
+static v3 xf_dir(const float *m, v3 v) { return V(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z, m[8] * v.x + m[9] * v.y + m[10] * v.z); }
+static void m3_inv_transpose(double a[3][3], double r[3][3]) {
+    double det = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) - a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) + a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) {
+        int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+        r[i][j] = (a[i1][j1] * a[i2][j2] - a[i1][j2] * a[i2][j1]) / det;      /* cofactor / det = (A^-1)^T */
+    }
+}
+/* enoki transform_decompose: polar decomposition A = Q P (scaled Newton, 10 steps), det(Q) > 0 */
+static void polar(double a[3][3], double q[3][3], double p[3][3]) {
+    memcpy(q, a, sizeof(double) * 9);
+    for (int it = 0; it < 10; ++it) {
+        double qi[3][3]; m3_inv_transpose(q, qi);
+        double nq = 0, ni = 0;
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { nq += q[i][j] * q[i][j]; ni += qi[i][j] * qi[i][j]; }
+        double g = sqrt(sqrt(ni) / sqrt(nq));
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) q[i][j] = .5 * g * q[i][j] + .5 / g * qi[i][j];
+    }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { p[i][j] = 0; for (int k = 0; k < 3; ++k) p[i][j] += q[k][i] * a[k][j]; }
+    double det = q[0][0] * (q[1][1] * q[2][2] - q[1][2] * q[2][1]) - q[0][1] * (q[1][0] * q[2][2] - q[1][2] * q[2][0]) + q[0][2] * (q[1][0] * q[2][1] - q[1][1] * q[2][0]);
+    if (det < 0) for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { q[i][j] = -q[i][j]; p[i][j] = -p[i][j]; }
+}
+static int shape_setup(const mtsb_shape_desc *d, oshape *sh) {
+    memset(sh, 0, sizeof(*sh));
+    sh->type = d->type; sh->flip = d->flip_normals != 0;
+    float w[16]; memcpy(w, d->to_world, sizeof(w));
+    if (d->type == MTSB_SHAPE_SPHERE || d->type == MTSB_SHAPE_CYLINDER) {
+        double a[3][3], q[3][3], p[3][3];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i][j] = w[4 * i + j];
+        polar(a, q, p);
+        double radius = p[0][0];
+        if (radius <= 0) { radius = -radius; sh->flip = !sh->flip; }
+        sh->radius = (float) radius; sh->length = (float) p[2][2];
+        sh->center = V(w[3], w[7], w[11]);
+        double k = d->type == MTSB_SHAPE_SPHERE ? (double) sh->radius : 1.0;      /* transform_compose(S, Q, T) */
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) w[4 * i + j] = (float) (q[i][j] * k);
+        w[12] = w[13] = w[14] = 0.f; w[15] = 1.f;
+        sh->inv_area = d->type == MTSB_SHAPE_SPHERE ? 1.f / (4.f * PI_F * sh->radius * sh->radius) : 1.f / (2.f * PI_F * sh->radius * sh->length);
+    } else if (d->type == MTSB_SHAPE_DISK || d->type == MTSB_SHAPE_RECTANGLE) {
+        if (d->flip_normals) for (int i = 0; i < 4; ++i) w[4 * i + 2] = -w[4 * i + 2];
+        sh->flip = 0;
+    } else return 0;
+    memcpy(sh->to_world, w, sizeof(w));
+    if (!invert4(sh->to_world, sh->to_object)) return 0;
+    if (d->type == MTSB_SHAPE_DISK || d->type == MTSB_SHAPE_RECTANGLE) {
+        float k = d->type == MTSB_SHAPE_RECTANGLE ? 2.f : 1.f;
+        sh->dp_du = xf_dir(sh->to_world, V(k, 0.f, 0.f)); sh->dp_dv = xf_dir(sh->to_world, V(0.f, k, 0.f));
+        sh->n = vnormalize(V(sh->to_object[8], sh->to_object[9], sh->to_object[10]));     /* normals transform by the inverse transpose */
+        if (d->type == MTSB_SHAPE_RECTANGLE) sh->inv_area = 1.f / vnorm(vcross(sh->dp_du, sh->dp_dv));
+        else {
+            float du = vnorm(sh->dp_du), dv = vnorm(sh->dp_dv);
+            v3 fs = vscale(sh->dp_du, 1.f / du), ft = vscale(sh->dp_dv, 1.f / dv);
+            float h = sqrtf(sqrf(dv) - sqrf(vdot(vscale(ft, dv), fs)));             /* disk.cpp:112-116 */
+            sh->inv_area = 1.f / (PI_F * du * h);
+        }
+    }
+    return 1;
+}
+static void shape_bounds(const oshape *sh, float *lo, float *hi) {
+    v3 a = V(INFINITY, INFINITY, INFINITY), b = V(-INFINITY, -INFINITY, -INFINITY);
+    if (sh->type == MTSB_SHAPE_SPHERE) { a = vsub(sh->center, V(sh->radius, sh->radius, sh->radius)); b = vadd(sh->center, V(sh->radius, sh->radius, sh->radius)); }
+    else if (sh->type == MTSB_SHAPE_CYLINDER) {
+        v3 x1 = xf_dir(sh->to_world, V(sh->radius, 0, 0)), x2 = xf_dir(sh->to_world, V(0, sh->radius, 0));
+        v3 x = V(sqrtf(x1.x * x1.x + x2.x * x2.x), sqrtf(x1.y * x1.y + x2.y * x2.y), sqrtf(x1.z * x1.z + x2.z * x2.z));
+        v3 p0 = xf_point(sh->to_world, V(0, 0, 0)), p1 = xf_point(sh->to_world, V(0, 0, sh->length));
+        a = V(fminf(p0.x - x.x, p1.x - x.x), fminf(p0.y - x.y, p1.y - x.y), fminf(p0.z - x.z, p1.z - x.z));
+        b = V(fmaxf(p0.x + x.x, p1.x + x.x), fmaxf(p0.y + x.y, p1.y + x.y), fmaxf(p0.z + x.z, p1.z + x.z));
+    } else for (int k = 0; k < 4; ++k) {
+        v3 p = xf_point(sh->to_world, V(k & 1 ? 1.f : -1.f, k & 2 ? 1.f : -1.f, 0.f));
+        a = V(fminf(a.x, p.x), fminf(a.y, p.y), fminf(a.z, p.z)); b = V(fmaxf(b.x, p.x), fmaxf(b.y, p.y), fmaxf(b.z, p.z));
+    }
+    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
+}
+/* math::solve_quadratic, core/math.h:371-413, on doubles */
+static int solve_quadratic(double a, double b, double c, double *x0, double *x1) {
+    int linear = a == 0.0, ok = !linear || b > 0.0;
+    *x0 = *x1 = -c / b;
+    double disc = b * b - 4.0 * a * c;
+    ok = ok && (linear || disc >= 0.0);
+    if (ok && !linear) {
+        double root = sqrt(disc), temp = -0.5 * (b + copysign(root, b));
+        double r0 = temp / a, r1 = c / temp;
+        *x0 = fmin(r0, r1); *x1 = fmax(r0, r1);
+    }
+    return ok;
+}
+/* ray_intersect of the four plugins; (cu, cv) = the cache floats (disk / rectangle: object-space x, y) */
+static int shape_hit(const oshape *sh, v3 o, v3 d, float mint, float maxt, float *t, float *cu, float *cv) {
+    *cu = *cv = 0.f;
+    if (sh->type == MTSB_SHAPE_SPHERE) {                                        /* sphere.cpp:276-300 */
+        double ox = (double) o.x - sh->center.x, oy = (double) o.y - sh->center.y, oz = (double) o.z - sh->center.z, dx = d.x, dy = d.y, dz = d.z;
+        double near_t, far_t;
+        int found = solve_quadratic(dx * dx + dy * dy + dz * dz, 2.0 * (ox * dx + oy * dy + oz * dz), ox * ox + oy * oy + oz * oz - (double) sh->radius * sh->radius, &near_t, &far_t);
+        int out_bounds = !(near_t <= maxt && far_t >= mint), in_bounds = near_t < mint && far_t > maxt;
+        if (!found || out_bounds || in_bounds) return 0;
+        *t = (float) (near_t < mint ? far_t : near_t);
+        return 1;
+    }
+    v3 lo = xf_point(sh->to_object, o), ld = xf_dir(sh->to_object, d);
+    if (sh->type == MTSB_SHAPE_CYLINDER) {                                      /* cylinder.cpp:248-287 */
+        double ox = lo.x, oy = lo.y, oz = lo.z, dx = ld.x, dy = ld.y, dz = ld.z, near_t, far_t, len = sh->length;
+        int found = solve_quadratic(dx * dx + dy * dy, 2.0 * (dx * ox + dy * oy), ox * ox + oy * oy - (double) sh->radius * sh->radius, &near_t, &far_t);
+        int out_bounds = !(near_t <= maxt && far_t >= mint), in_bounds = near_t < mint && far_t > maxt;
+        double zn = oz + dz * near_t, zf = oz + dz * far_t;
+        int use_near = zn >= 0 && zn <= len && near_t >= mint, use_far = zf >= 0 && zf <= len && far_t <= maxt;
+        if (!found || out_bounds || in_bounds || !(use_near || use_far)) return 0;
+        *t = (float) (use_near ? near_t : far_t);
+        return 1;
+    }
+    float tt = -lo.z * (1.f / ld.z);                                            /* disk.cpp:144-165, rectangle.cpp:142-164 */
+    float x = fmaf(ld.x, tt, lo.x), y = fmaf(ld.y, tt, lo.y);
+    int inside = sh->type == MTSB_SHAPE_DISK ? x * x + y * y <= 1.f : (fabsf(x) <= 1.f && fabsf(y) <= 1.f);
+    if (!(tt >= mint && tt <= maxt && inside)) return 0;
+    *t = tt; *cu = x; *cv = y;
+    return 1;
+}
 /* Mesh::ray_intersect_triangle, include/mitsuba/render/mesh.h:195-221 (Moeller-Trumbore) */
 static int mt_intersect(const orc_scene *s, uint32_t f, v3 o, v3 d, float mint, float maxt, float *u, float *v, float *t) {
     v3 p0 = ld3(s->pos, s->faces[3 * f]), p1 = ld3(s->pos, s->faces[3 * f + 1]), p2 = ld3(s->pos, s->faces[3 * f + 2]);
@@ -390,11 +517,23 @@ static int box_hit(const onode *n, v3 o, v3 id, float mint, float maxt) {
     return t0 <= t1 * 1.00001f + 1e-30f;
 }
 typedef struct { float t, u, v; uint32_t prim; } ohit;
+/* analytic shapes are few: tested one by one, outside the triangle BVH (primitive id n_faces + k) */
+static int trace_shapes(const orc_scene *s, v3 o, v3 d, float mint, float maxt, int any, ohit *h) {
+    int found = 0;
+    for (uint32_t k = 0; k < s->n_shapes; ++k) { float t, cu, cv;
+        if (shape_hit(&s->shapes[k], o, d, mint, maxt, &t, &cu, &cv)) {
+            if (any) { h->t = t; return 1; }
+            maxt = t; found = 1; h->t = t; h->u = cu; h->v = cv; h->prim = s->n_faces + k;
+        } }
+    return found;
+}
 static int trace(const orc_scene *s, v3 o, v3 d, float mint, float maxt, int any, ohit *h) {
     h->t = INFINITY; h->u = h->v = 0.f; h->prim = 0xffffffffu;
-    if (s->n_faces == 0) return 0;
+    int found = 0;
+    if (s->n_shapes) { found = trace_shapes(s, o, d, mint, maxt, any, h); if (found) { if (any) return 1; maxt = h->t; } }
+    if (s->n_faces == 0) return found;
     v3 id = V(1.f / d.x, 1.f / d.y, 1.f / d.z);
-    uint32_t stack[128]; int sp = 0; stack[sp++] = 0; int found = 0;
+    uint32_t stack[128]; int sp = 0; stack[sp++] = 0;
     while (sp) {
         const onode *n = &s->nodes[stack[--sp]];
         if (!box_hit(n, o, id, mint, maxt)) continue;
@@ -414,6 +553,7 @@ static int trace_naive(const orc_scene *s, v3 o, v3 d, float mint, float maxt, o
     h->t = INFINITY; h->u = h->v = 0.f; h->prim = 0xffffffffu; int found = 0;
     for (uint32_t f = 0; f < s->n_faces; ++f) { float u, v, t;
         if (mt_intersect(s, f, o, d, mint, maxt, &u, &v, &t)) { maxt = t; found = 1; h->t = t; h->u = u; h->v = v; h->prim = f; } }
+    if (s->n_shapes) found |= trace_shapes(s, o, d, mint, maxt, 0, h);
     return found;
 }
 void orc_intersect_closest(const orc_scene *s, uint64_t n, const float *o, const float *d, float *hits, int threads) {
@@ -430,6 +570,10 @@ void orc_intersect_naive(const orc_scene *s, uint64_t n, const float *o, const f
     for (int64_t i = 0; i < (int64_t) n; ++i) { ohit h; trace_naive(s, V(o[4 * i], o[4 * i + 1], o[4 * i + 2]), V(d[4 * i], d[4 * i + 1], d[4 * i + 2]), o[4 * i + 3], d[4 * i + 3], &h);
         hits[4 * i] = h.t; hits[4 * i + 1] = h.u; hits[4 * i + 2] = h.v; hits[4 * i + 3] = bitsf(h.prim); }
 }
+
+/* closest hit + the surface interaction built from it, 16 floats per ray: t, uv, primitive id bits, p, n, sh_frame.n, wi
+ * (the record oracle/ref_query.cpp writes for Scene::ray_intersect) */
+void orc_surface_interaction(const orc_scene *s, uint64_t n, const float *o, const float *d, float *out16, int threads);
 
 /* ---- tables ------------------------------------------------------------------------------------ */
 static void build_area_cdf(orc_scene *s, oemitter *e) {    /* distr_1d.h:49-88 over mesh.h:108-116 */
@@ -490,7 +634,7 @@ static int invert4(const float *m, float *inv) {
 }
 static void update_bsphere(orc_scene *s) {   /* envmap.cpp:126-130 */
     v3 c = vscale(vadd(s->bbox_lo, s->bbox_hi), .5f);
-    float r = s->n_faces ? vnorm(vsub(s->bbox_hi, c)) : 0.f;
+    float r = (s->n_faces + s->n_shapes) ? vnorm(vsub(s->bbox_hi, c)) : 0.f;
     r = fmaxf(RAY_EPS, r * (1.f + RAY_EPS));
     for (uint32_t i = 0; i < s->n_emitters; ++i) if (s->emitters[i].type == MTSB_EMITTER_ENVMAP || s->emitters[i].type == MTSB_EMITTER_CONSTANT) s->emitters[i].bsphere_radius = r;
 }
@@ -498,7 +642,8 @@ static void update_bsphere(orc_scene *s) {   /* envmap.cpp:126-130 */
 orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
     orc_scene *s = calloc(1, sizeof(orc_scene));
     s->n_meshes = d->n_meshes; s->n_bsdfs = d->n_bsdfs; s->n_tex = d->n_textures; s->n_emitters = d->n_emitters; s->n_sensors = d->n_sensors;
-    s->meshes = calloc(d->n_meshes ? d->n_meshes : 1, sizeof(omesh));
+    s->meshes = calloc(d->n_meshes + d->n_shapes + 1, sizeof(omesh));
+    s->n_shapes = d->n_shapes; s->shapes = calloc(d->n_shapes + 1, sizeof(oshape));
     for (uint32_t i = 0; i < d->n_meshes; ++i) { s->n_faces += d->meshes[i].face_count; s->n_verts += d->meshes[i].vertex_count; }
     s->pos = calloc(3 * (size_t) s->n_verts + 1, sizeof(float)); s->nrm = calloc(3 * (size_t) s->n_verts + 1, sizeof(float)); s->uv = calloc(2 * (size_t) s->n_verts + 1, sizeof(float));
     s->faces = calloc(3 * (size_t) s->n_faces + 1, sizeof(uint32_t)); s->face_mesh = calloc((size_t) s->n_faces + 1, sizeof(uint32_t));
@@ -506,12 +651,17 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
     for (uint32_t i = 0; i < d->n_meshes; ++i) {
         const mtsb_mesh_desc *m = &d->meshes[i]; omesh *om = &s->meshes[i];
         om->face_begin = fb; om->face_count = m->face_count; om->vert_begin = vb; om->vert_count = m->vertex_count;
-        om->bsdf = m->bsdf_id; om->emitter = m->emitter_id; om->has_normals = m->normals != NULL; om->has_uv = m->texcoords != NULL;
+        om->bsdf = m->bsdf_id; om->emitter = m->emitter_id; om->has_normals = m->normals != NULL; om->has_uv = m->texcoords != NULL; om->shape = -1;
         memcpy(s->pos + 3 * (size_t) vb, m->positions, sizeof(float) * 3 * (size_t) m->vertex_count);
         if (m->normals) memcpy(s->nrm + 3 * (size_t) vb, m->normals, sizeof(float) * 3 * (size_t) m->vertex_count);
         if (m->texcoords) memcpy(s->uv + 2 * (size_t) vb, m->texcoords, sizeof(float) * 2 * (size_t) m->vertex_count);
         for (uint32_t f = 0; f < m->face_count; ++f) { for (int k = 0; k < 3; ++k) s->faces[3 * (size_t) (fb + f) + k] = m->faces[3 * (size_t) f + k] + vb; s->face_mesh[fb + f] = i; }
         vb += m->vertex_count; fb += m->face_count;
+    }
+    for (uint32_t k = 0; k < d->n_shapes; ++k) {
+        omesh *om = &s->meshes[d->n_meshes + k];
+        if (!shape_setup(&d->shapes[k], &s->shapes[k])) { fprintf(stderr, "oracle: bad shape %u\n", k); }
+        om->face_begin = fb + k; om->face_count = 1; om->bsdf = d->shapes[k].bsdf_id; om->emitter = d->shapes[k].emitter_id; om->has_uv = 1; om->shape = (int) k;
     }
     s->bsdfs = calloc(d->n_bsdfs ? d->n_bsdfs : 1, sizeof(mtsb_bsdf_desc)); memcpy(s->bsdfs, d->bsdfs, sizeof(mtsb_bsdf_desc) * d->n_bsdfs);
     s->rough_tab = calloc((d->n_bsdfs ? d->n_bsdfs : 1) * 65, sizeof(float));
@@ -535,7 +685,8 @@ orc_scene *orc_scene_create(const mtsb_scene_desc *d) {
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
         const mtsb_emitter_desc *e = &d->emitters[i]; oemitter *oe = &s->emitters[i];
         oe->type = e->type; oe->radiance_tex = e->radiance_tex;
-        if (e->type == MTSB_EMITTER_AREA) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = e->mesh_id; build_area_cdf(s, oe); }
+        if (e->type == MTSB_EMITTER_AREA) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = e->mesh_id;
+            if (s->meshes[e->mesh_id].shape >= 0) oe->normalization = s->shapes[s->meshes[e->mesh_id].shape].inv_area; else build_area_cdf(s, oe); }
         else if (e->type == MTSB_EMITTER_CONSTANT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1; s->env_emitter = (int) i; }  /* constant.cpp:33-49 */
         else if (e->type == MTSB_EMITTER_POINT) { oe->radiance = V(e->radiance[0], e->radiance[1], e->radiance[2]); oe->mesh = -1;
             oe->position = V(e->position[0], e->position[1], e->position[2]); }                                    /* point.cpp:38-58 */
@@ -562,7 +713,7 @@ void orc_scene_destroy(orc_scene *s) {
     for (uint32_t i = 0; i < s->n_emitters; ++i) { oemitter *e = &s->emitters[i]; free(e->cdf); free(e->rgba);
         for (int l = 0; l < e->warp.n_levels; ++l) free(e->warp.levels[l]); free(e->warp.levels); free(e->warp.widths); }
     free(s->rough_tab); free(s->meshes); free(s->bsdfs); free(s->tex); free(s->emitters); free(s->sensors); free(s->pos); free(s->nrm); free(s->uv);
-    free(s->faces); free(s->face_mesh); free(s->nodes); free(s->order); free(s);
+    free(s->faces); free(s->face_mesh); free(s->nodes); free(s->order); free(s->shapes); free(s);
 }
 void orc_scene_update_texture(orc_scene *s, uint32_t id, const float *data) {
     otex *t = &s->tex[id];
@@ -577,11 +728,54 @@ typedef struct { v3 p, n, sh_s, sh_t, sh_n, wi; float u, v, t; uint32_t prim; in
 static v3 to_local(const osi *si, v3 w) { return V(vdot(w, si->sh_s), vdot(w, si->sh_t), vdot(w, si->sh_n)); }
 static v3 to_world(const osi *si, v3 w) { return vadd(vadd(vscale(si->sh_s, w.x), vscale(si->sh_t, w.y)), vscale(si->sh_n, w.z)); }
 
+/* fill_surface_interaction of the analytic shapes (sphere.cpp:329-373, disk.cpp:167-205, cylinder.cpp:330-361,
+ * rectangle.cpp:180-205) followed by the frame completion of kdtree.h:2356-2362 */
+static void shape_si(const orc_scene *s, uint32_t k, v3 o, v3 d, const ohit *h, osi *si) {
+    const oshape *sh = &s->shapes[k];
+    si->mesh = (int) (s->n_meshes + k); si->b1 = h->u; si->b2 = h->v;
+    v3 at = V(fmaf(d.x, h->t, o.x), fmaf(d.y, h->t, o.y), fmaf(d.z, h->t, o.z)), dp_du;
+    if (sh->type == MTSB_SHAPE_SPHERE) {
+        v3 n = vnormalize(vsub(at, sh->center));
+        si->p = V(fmaf(n.x, sh->radius, sh->center.x), fmaf(n.y, sh->radius, sh->center.y), fmaf(n.z, sh->radius, sh->center.z));
+        v3 l = xf_point(sh->to_object, si->p);
+        float half = asinf(.5f * vnorm(V(l.x, l.y, l.z - mulsign(1.f, l.z)))) * 2.f;      /* unit_angle_z */
+        float theta = l.z >= 0.f ? half : PI_F - half, phi = atan2f(l.y, l.x);
+        if (phi < 0.f) phi += 2.f * PI_F;
+        si->u = phi * (.5f / PI_F); si->v = theta * (1.f / PI_F);
+        dp_du = vscale(xf_dir(sh->to_world, V(-l.y, l.x, 0.f)), 2.f * PI_F);
+        si->n = sh->flip ? vneg(n) : n;
+    } else if (sh->type == MTSB_SHAPE_DISK) {
+        float r = sqrtf(h->u * h->u + h->v * h->v), inv_r = 1.f / r, ang = atan2f(h->v, h->u) * (.5f / PI_F);
+        if (ang < 0.f) ang += 1.f;
+        float c = r != 0.f ? h->u * inv_r : 1.f, sn = r != 0.f ? h->v * inv_r : 0.f;
+        dp_du = xf_dir(sh->to_world, V(c, sn, 0.f));
+        si->n = sh->n; si->u = r; si->v = ang; si->p = at;
+    } else if (sh->type == MTSB_SHAPE_CYLINDER) {
+        v3 l = xf_point(sh->to_object, at);
+        float phi = atan2f(l.y, l.x);
+        if (phi < 0.f) phi += 2.f * PI_F;
+        si->u = phi * (.5f / PI_F); si->v = l.z / sh->length;
+        dp_du = xf_dir(sh->to_world, vscale(V(-l.y, l.x, 0.f), 2.f * PI_F));
+        v3 dp_dv = xf_dir(sh->to_world, V(0.f, 0.f, sh->length));
+        v3 n = vnormalize(vcross(dp_du, dp_dv));
+        si->p = vadd(at, vscale(n, sh->radius - sqrtf(l.x * l.x + l.y * l.y)));
+        si->n = sh->flip ? vneg(n) : n;
+    } else {
+        si->n = sh->n; dp_du = sh->dp_du; si->p = at;
+        si->u = fmaf(h->u, .5f, .5f); si->v = fmaf(h->v, .5f, .5f);
+    }
+    si->sh_n = si->n;
+    si->sh_s = vnormalize(vsub(dp_du, vscale(si->n, vdot(si->n, dp_du))));
+    si->sh_t = vcross(si->n, si->sh_s);
+    si->wi = to_local(si, vneg(d));
+}
+
 /* kdtree.h:2334-2368 + mesh.cpp:399-462; miss: scene_native.inl:29-31 */
 static void make_si(const orc_scene *s, v3 o, v3 d, const ohit *h, osi *si) {
     memset(si, 0, sizeof(*si));
     si->t = h->t; si->prim = h->prim; si->valid = h->t != INFINITY; si->mesh = -1;
     if (!si->valid) { si->wi = vneg(d); si->p = o; return; }
+    if (h->prim >= s->n_faces) { shape_si(s, h->prim - s->n_faces, o, d, h, si); return; }
     uint32_t f = h->prim; const omesh *m = &s->meshes[s->face_mesh[f]]; si->mesh = (int) s->face_mesh[f];
     uint32_t i0 = s->faces[3 * f], i1 = s->faces[3 * f + 1], i2 = s->faces[3 * f + 2];
     float b1 = h->u, b2 = h->v, b0 = 1.f - b1 - b2; si->b1 = b1; si->b2 = b2;
@@ -606,6 +800,21 @@ static void make_si(const orc_scene *s, v3 o, v3 d, const ohit *h, osi *si) {
     si->sh_s = vnormalize(vsub(dp_du, vscale(ns, vdot(ns, dp_du))));
     si->sh_t = vcross(ns, si->sh_s);
     si->wi = to_local(si, vneg(d));
+}
+void orc_surface_interaction(const orc_scene *s, uint64_t n, const float *o, const float *d, float *out, int threads) {
+    #pragma omp parallel for schedule(dynamic, 1024) num_threads(threads > 0 ? threads : 1)
+    for (int64_t i = 0; i < (int64_t) n; ++i) {
+        v3 ro = V(o[4 * i], o[4 * i + 1], o[4 * i + 2]), rd = V(d[4 * i], d[4 * i + 1], d[4 * i + 2]);
+        ohit h; trace(s, ro, rd, o[4 * i + 3], d[4 * i + 3], 0, &h);
+        osi si; make_si(s, ro, rd, &h, &si);
+        float *q = out + 16 * i;
+        memset(q, 0, 16 * sizeof(float));
+        q[0] = h.t; q[3] = bitsf(h.prim);
+        if (!si.valid) continue;
+        q[1] = si.u; q[2] = si.v;
+        q[4] = si.p.x; q[5] = si.p.y; q[6] = si.p.z; q[7] = si.n.x; q[8] = si.n.y; q[9] = si.n.z;
+        q[10] = si.sh_n.x; q[11] = si.sh_n.y; q[12] = si.sh_n.z; q[13] = si.wi.x; q[14] = si.wi.y; q[15] = si.wi.z;
+    }
 }
 /* src/textures/bitmap.cpp:250-293, src/spectra/srgb.cpp */
 /* ---- spectral mode arithmetic -------------------------------------------------------------------------------- */
@@ -1109,9 +1318,68 @@ static uint32_t ek_binary_search(uint32_t start, uint32_t end, const float *cdf,
     }
     return start;
 }
+static v3 square_to_uniform_sphere(float sx, float sy) {    /* warp.h:262-267 */
+    float z = 1.f - 2.f * sy, r = safe_sqrtf(1.f - z * z), phi = 2.f * PI_F * sx;
+    return V(r * cosf(phi), r * sinf(phi), z);
+}
+/* Shape::sample_direction of an analytic shape -> (p, n, d, dist, pdf).  Sphere: sphere.cpp:182-255; the others go through
+ * Shape::sample_direction (shape.cpp:252-270) over their sample_position (disk.cpp:127-141, cylinder.cpp:214-236,
+ * rectangle.cpp:114-127). */
+static void shape_sample_direction(const oshape *sh, v3 ref_p, float sx, float sy, ods *ds) {
+    if (sh->type == MTSB_SHAPE_SPHERE) {
+        v3 dc = vsub(sh->center, ref_p), dir;
+        float dc2 = vdot(dc, dc), radius_adj = sh->radius * (sh->flip ? 1.f + RAY_EPS : 1.f - RAY_EPS);
+        if (dc2 > sqrf(radius_adj)) {            /* reference point outside: uniform over the cone of directions that see the sphere */
+            float inv_dc = 1.f / sqrtf(dc2), smax = sh->radius * inv_dc, smax2 = sqrf(smax), inv_smax = 1.f / smax, cmax = safe_sqrtf(1.f - smax2);
+            float st2 = smax2 > 0.00068523f ? 1.f - sqrf(fmaf(cmax - 1.f, sx, 1.f)) : smax2 * sx, ct = safe_sqrtf(1.f - st2);
+            float cos_alpha = st2 * inv_smax + ct * safe_sqrtf(fmaf(-st2, sqrf(inv_smax), 1.f)), sin_alpha = safe_sqrtf(fmaf(-cos_alpha, cos_alpha, 1.f));
+            float sphi = sinf(sy * (2.f * PI_F)), cphi = cosf(sy * (2.f * PI_F));
+            v3 fn = vscale(dc, -inv_dc), fs, ft; coordinate_system(fn, &fs, &ft);
+            v3 l = V(cphi * sin_alpha, sphi * sin_alpha, cos_alpha);
+            dir = vadd(vadd(vscale(fs, l.x), vscale(ft, l.y)), vscale(fn, l.z));
+            ds->p = V(fmaf(dir.x, sh->radius, sh->center.x), fmaf(dir.y, sh->radius, sh->center.y), fmaf(dir.z, sh->radius, sh->center.z));
+            ds->d = vsub(ds->p, ref_p);
+            float dist2 = vdot(ds->d, ds->d); ds->dist = sqrtf(dist2); ds->d = vscale(ds->d, 1.f / ds->dist);
+            ds->pdf = ds->dist == 0.f ? 0.f : (.5f / PI_F) / (1.f - cmax);
+        } else {                                  /* inside: uniform over the surface */
+            dir = square_to_uniform_sphere(sx, sy);
+            ds->p = V(fmaf(dir.x, sh->radius, sh->center.x), fmaf(dir.y, sh->radius, sh->center.y), fmaf(dir.z, sh->radius, sh->center.z));
+            ds->d = vsub(ds->p, ref_p);
+            float dist2 = vdot(ds->d, ds->d); ds->dist = sqrtf(dist2); ds->d = vscale(ds->d, 1.f / ds->dist);
+            ds->pdf = sh->inv_area * dist2 / fabsf(vdot(ds->d, dir));
+        }
+        ds->n = sh->flip ? vneg(dir) : dir;
+        return;
+    }
+    if (sh->type == MTSB_SHAPE_DISK) { float x, y; disk_concentric(sx, sy, &x, &y); ds->p = xf_point(sh->to_world, V(x, y, 0.f)); ds->n = sh->n; }
+    else if (sh->type == MTSB_SHAPE_CYLINDER) {
+        float st = sinf(2.f * PI_F * sy), ct = cosf(2.f * PI_F * sy);
+        ds->p = xf_point(sh->to_world, V(ct * sh->radius, st * sh->radius, sx * sh->length));
+        v3 n = V(ct, st, 0.f); if (sh->flip) n = vneg(n);
+        ds->n = n;      /* cylinder.cpp:222-232 returns the OBJECT-space normal (only the position goes through to_world); kept as is */
+    } else { ds->p = xf_point(sh->to_world, V(fmaf(sx, 2.f, -1.f), fmaf(sy, 2.f, -1.f), 0.f)); ds->n = sh->n; }
+    ds->d = vsub(ds->p, ref_p);
+    float dist2 = vdot(ds->d, ds->d); ds->dist = sqrtf(dist2); ds->d = vscale(ds->d, 1.f / ds->dist);
+    float dp = fabsf(vdot(ds->d, ds->n));
+    ds->pdf = sh->inv_area * (dp != 0.f ? dist2 / dp : 0.f);
+}
+/* Sphere::pdf_direction (sphere.cpp:257-270); others: Shape::pdf_direction (shape.cpp:272-283) */
+static float shape_pdf_direction(const oshape *sh, v3 ref_p, v3 d, v3 n, float dist) {
+    float dp = fabsf(vdot(d, n));
+    if (sh->type != MTSB_SHAPE_SPHERE) return sh->inv_area * (dp != 0.f ? (dist * dist) / dp : 0.f);
+    float sin_alpha = sh->radius * (1.f / vnorm(vsub(sh->center, ref_p))), cos_alpha = safe_sqrtf(1.f - sin_alpha * sin_alpha);
+    return sin_alpha < 1.f - EPS_F ? (.5f / PI_F) / (1.f - cos_alpha) : sh->inv_area * sqrf(dist) / dp;
+}
 static ods area_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy, const float *wav) {
     /* area.cpp:103-117 -> shape.cpp:252-270 -> mesh.cpp:320-365 -> distr_1d.h:144-203 */
     ods ds; const omesh *m = &s->meshes[e->mesh];
+    if (m->shape >= 0) {
+        memset(&ds, 0, sizeof(ds));
+        shape_sample_direction(&s->shapes[m->shape], ref_p, sx, sy, &ds);
+        int on = vdot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
+        ds.value = on ? cscale(emitter_radiance(s, e, wav), 1.f / ds.pdf) : C1(0.f);
+        return ds;
+    }
     uint32_t idx = ek_binary_search(e->valid_lo, e->valid_hi, e->cdf, sy * e->cdf_sum);
     uint32_t f = m->face_begin + idx, i0 = s->faces[3 * f], i1 = s->faces[3 * f + 1], i2 = s->faces[3 * f + 2];
     v3 p0 = ld3(s->pos, i0), p1 = ld3(s->pos, i1), p2 = ld3(s->pos, i2), e0 = vsub(p1, p0), e1 = vsub(p2, p0);
@@ -1129,13 +1397,11 @@ static ods area_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p
     ds.value = active ? cscale(emitter_radiance(s, e, wav), 1.f / ds.pdf) : C1(0.f);
     return ds;
 }
-static float area_pdf_direction(const oemitter *e, v3 d, v3 n, float dist) {   /* area.cpp:119-125, shape.cpp:272-283 */
+static float area_pdf_direction(const orc_scene *s, const oemitter *e, v3 ref_p, v3 d, v3 n, float dist) {   /* area.cpp:119-125, shape.cpp:272-283 */
+    int shape = s->meshes[e->mesh].shape;
+    if (shape >= 0) return vdot(d, n) < 0.f ? shape_pdf_direction(&s->shapes[shape], ref_p, d, n, dist) : 0.f;
     float dp = fabsf(vdot(d, n)), pdf = e->normalization * (dp != 0.f ? (dist * dist) / dp : 0.f);
     return vdot(d, n) < 0.f ? pdf : 0.f;
-}
-static v3 square_to_uniform_sphere(float sx, float sy) {    /* warp.h:262-267 */
-    float z = 1.f - 2.f * sy, r = safe_sqrtf(1.f - z * z), phi = 2.f * PI_F * sx;
-    return V(r * cosf(phi), r * sinf(phi), z);
 }
 static ods constant_sample_direction(const orc_scene *s, const oemitter *e, v3 ref_p, float sx, float sy, const float *wav) {   /* constant.cpp:77-103 */
     ods ds; memset(&ds, 0, sizeof(ds));
@@ -1250,7 +1516,7 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
             if (!bs.delta) {
                 if (e->type == MTSB_EMITTER_AREA) {
                     v3 dd = vsub(si_bsdf.p, si.p); float dist = vnorm(dd); dd = vscale(dd, 1.f / dist);
-                    emitter_pdf = area_pdf_direction(e, dd, si_bsdf.sh_n, dist);
+                    emitter_pdf = area_pdf_direction(s, e, si.p, dd, si_bsdf.sh_n, dist);
                 } else if (e->type == MTSB_EMITTER_ENVMAP) emitter_pdf = env_pdf_direction(e, nd);   /* ds.d = -si_bsdf.wi = ray.d on a miss (records.h:173) */
                 else emitter_pdf = .25f * INV_PI_F;                                                  /* constant.cpp:98-103 */
                 if (s->n_emitters > 1) emitter_pdf *= 1.f / (float) s->n_emitters;
@@ -1267,6 +1533,7 @@ static void path_sample(const orc_scene *s, pcg32 *rng, v3 o, v3 d, float mint, 
 static void film_put(const mtsb_sensor_desc *sn, float px, float py, const float *value5, float *xyzaw) {
     float radius = sn->rfilter == MTSB_RFILTER_BOX ? sn->rfilter_radius + RAY_EPS : sn->rfilter_radius;
     float x = px - .5f, y = py - .5f; int W = (int) sn->film_width, H = (int) sn->film_height;
+    for (int k = 0; k < 5; ++k) if (!(value5[k] >= -1e-5f) || !isfinite(value5[k])) return;     /* imageblock.cpp:84-108: invalid samples are dropped */
     if (radius > 1.f) {
         int lox = (int) ceilf(x - radius), loy = (int) ceilf(y - radius); if (lox < 0) lox = 0; if (loy < 0) loy = 0;
         int hix = (int) floorf(x + radius), hiy = (int) floorf(y + radius); if (hix > W - 1) hix = W - 1; if (hiy > H - 1) hiy = H - 1;

@@ -60,6 +60,7 @@ void orc_scene_update_texture(orc_scene *s, uint32_t tex_id, const float *data);
 /* Scene::ray_intersect / ray_test / ray_intersect_naive with the reference's Moeller-Trumbore test */
 void orc_intersect_closest(const orc_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, float *hits, int threads);
 void orc_intersect_any(const orc_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, uint32_t *occluded, int threads);
+void orc_surface_interaction(const orc_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, float *out16 /* t, uv, prim bits, p, n, sh_n, wi */, int threads);
 void orc_intersect_naive(const orc_scene *s, uint64_t n, const float *o_mint, const float *d_maxt, float *hits, int threads);
 
 /* stage hooks (same signatures as the mtsb_* parity hooks) */

@@ -87,6 +87,7 @@ class Oracle:
             l.orc_intersect_closest.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
             l.orc_intersect_any.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
             l.orc_intersect_naive.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
+            l.orc_surface_interaction.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int]
             l.orc_sensor_sample_ray.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp]
             l.orc_bsdf_sample.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
             l.orc_bsdf_eval_pdf.argtypes = [vp, C.c_uint32, C.c_uint64, vp, vp, vp, vp, vp]
@@ -119,6 +120,13 @@ class Oracle:
         fn = self.lib().orc_intersect_naive if naive else self.lib().orc_intersect_closest
         fn(self.h, om.shape[0], _p(om), _p(dm), _p(hits), self.threads)
         return hits
+
+    def surface_interaction(self, om, dm):
+        """-> (n,16): t, uv, prim bits, p, n, sh_n, wi (the layout of RefBuild.intersect)"""
+        om, dm = _f32(om), _f32(dm)
+        out = np.empty((om.shape[0], 16), np.float32)
+        self.lib().orc_surface_interaction(self.h, om.shape[0], _p(om), _p(dm), _p(out), self.threads)
+        return out
 
     def intersect_any(self, om, dm):
         om, dm = _f32(om), _f32(dm)
@@ -795,4 +803,52 @@ def attribute_scene(res=(48, 32), spp=8, per_face=False):
     sd.add_constant((0.2, 0.25, 0.3))
     sd.add_perspective(look_at([0, 0, -3.2], [0, 0, 0], [0, 1, 0]), 45.0, 0.01, 100.0, res[0], res[1], "box")
     sd.max_depth, sd.rr_depth, sd.spp = 4, 5, spp
+    return sd
+
+
+def _trs(translate=(0, 0, 0), rotate_axis=(0, 0, 1), rotate_deg=0.0, scale=(1, 1, 1)):
+    """4x4 translate * rotate(axis, angle) * scale"""
+    a = np.asarray(rotate_axis, np.float64)
+    a = a / np.linalg.norm(a)
+    th = np.deg2rad(rotate_deg)
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    R = np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * (K @ K)
+    m = np.eye(4)
+    m[:3, :3] = R @ np.diag(np.broadcast_to(np.asarray(scale, np.float64), 3))
+    m[:3, 3] = translate
+    return m
+
+
+def shapes_scene(res=(48, 32), spp=8, emitters="disk", tri_floor=True, named_conductor=False):
+    """Analytic shapes as leaf primitives next to triangles (src/shapes/{sphere,disk,cylinder,rectangle}.cpp): a diffuse
+    sphere, a rough-conductor sphere with flipped normals seen through an open cylinder, a bitmap-textured rectangle wall,
+    a textured disk, a triangle floor, and an area light on a disk / sphere / cylinder / rectangle (`emitters`, a
+    space-separated list)."""
+    sd = SceneData()
+    rng = np.random.default_rng(5)
+    tex = sd.add_texture_bitmap((0.15 + 0.8 * rng.random((6, 8, 3))).astype(np.float32))
+    if tri_floor:
+        floor = M.quad([-6, -1, -6], [-6, -1, 6], [6, -1, 6], [6, -1, -6])
+        floor.bsdf = sd.add_diffuse((0.5, 0.45, 0.4))
+        sd.add_mesh(floor)
+    else:
+        sd.add_rectangle(_trs((0, -1, 0), (1, 0, 0), -90.0, (6, 6, 1)), bsdf=sd.add_diffuse((0.5, 0.45, 0.4)))
+    sd.add_sphere((-1.2, -0.3, 0.4), 0.7, bsdf=sd.add_diffuse(tex))
+    sd.add_sphere((1.3, -0.45, 0.2), 0.55, to_world=_trs((0, 0, 0), (0, 1, 0), 30.0), bsdf=sd.add_roughconductor(material="Cu", alpha=0.15) if named_conductor else sd.add_roughconductor((0.2, 0.92, 1.1), (3.9, 2.45, 2.14), 0.15))
+    sd.add_cylinder((-0.3, -1.0, 1.6), (0.4, 0.3, 1.9), 0.35, bsdf=sd.make_two_sided(sd.add_diffuse((0.2, 0.5, 0.7))))
+    sd.add_rectangle(_trs((0, 0.5, 3.0), (0, 1, 0), 180.0, (3.0, 1.5, 1)), bsdf=sd.add_diffuse(tex))
+    sd.add_disk(_trs((0.2, -0.99, -0.8), (1, 0, 0), -90.0, (0.8, 0.5, 1)), bsdf=sd.add_diffuse(tex))
+    em = emitters.split()
+    lb = sd.add_diffuse(0.0)
+    if "disk" in em:
+        sd.add_disk(_trs((0, 2.5, 0.5), (1, 0, 0), 90.0, (0.6, 0.6, 1)), bsdf=lb, area_radiance=(14.0, 12.0, 9.0))
+    if "sphere" in em:
+        sd.add_sphere((2.2, 1.2, 1.0), 0.25, bsdf=lb, area_radiance=(20.0, 10.0, 10.0))
+    if "cylinder" in em:
+        sd.add_cylinder((-2.5, 0.2, 1.0), (-2.5, 1.2, 1.0), 0.12, bsdf=lb, area_radiance=(6.0, 12.0, 18.0))
+    if "rectangle" in em:
+        sd.add_rectangle(_trs((0, 2.2, -1.0), (1, 0, 0), 90.0, (0.5, 0.3, 1)), bsdf=lb, flip_normals=False, area_radiance=(12.0, 12.0, 12.0))
+    sd.add_constant((0.08, 0.1, 0.12))
+    sd.add_perspective(look_at([0, 0.6, -4.2], [0, -0.1, 0], [0, 1, 0]), 50.0, 0.01, 100.0, res[0], res[1], "box")
+    sd.max_depth, sd.rr_depth, sd.spp = 5, 5, spp
     return sd

@@ -18,7 +18,7 @@ using namespace mtsb;
 struct hs_scene {
     std::vector<MeshDev> meshes; std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
     std::vector<SensorDev> sensors;
-    std::vector<float> pos, nrm, uv; std::vector<uint4> faces;
+    std::vector<float> pos, nrm, uv; std::vector<uint4> faces; std::vector<ShapeDev> shapes;
     std::vector<std::vector<float>> tables; std::vector<float4> env_rgba; std::vector<float> cie; bool spectral = false, ext = false;
     std::vector<uint4> nodes; std::vector<float4> tris;
     std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
@@ -78,7 +78,7 @@ static void hs_build_bvh(hs_scene *s) {
     std::vector<int> left(n), right(n), parent(2 * (size_t) n), wide_bin(n + 1);
     s->nodes.assign(5 * ((size_t) n + 1), make_uint4(0, 0, 0, 0)); s->tris.assign(3 * (size_t) n, make_float4(0, 0, 0, 0));
     BvhBuild b;
-    b.pos = s->pos.data(); b.faces = s->faces.data(); b.n = n;
+    b.pos = s->pos.data(); b.faces = s->faces.data(); b.shapes = s->shapes.data(); b.n = n;
     b.tlo = tlo.data(); b.thi = thi.data(); b.keys = keys.data(); b.order = order.data(); b.left = left.data(); b.right = right.data();
     b.parent = parent.data(); b.rfirst = rfirst.data(); b.rlast = rlast.data(); b.nlo = nlo.data(); b.nhi = nhi.data(); b.flags = flags.data();
     b.nodes = s->nodes.data(); b.tris = s->tris.data(); b.wide_bin = wide_bin.data(); b.counters = counters.data();
@@ -120,7 +120,7 @@ static void hs_build_bvh(hs_scene *s) {
     uint32_t begin = 0, end = 1, depth = 0;
     while (begin < end) { for (uint32_t w = begin; w < end; ++w) collapse_body(b, w); begin = end; end = counters[0]; depth++; }
     s->bvh_nodes = end; s->bvh_depth = depth;
-    s->dev.bvh.nodes = s->nodes.data(); s->dev.bvh.tris = s->tris.data();
+    s->dev.bvh.nodes = s->nodes.data(); s->dev.bvh.tris = s->tris.data(); s->dev.bvh.shapes = s->shapes.empty() ? nullptr : s->shapes.data();
 }
 
 extern "C" void hs_scene_destroy(hs_scene *s) { delete s; }
@@ -134,6 +134,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         const mtsb_mesh_desc &m = d->meshes[i];
         MeshDev md; md.face_begin = fbase; md.face_count = m.face_count; md.vert_begin = vbase; md.vert_count = m.vertex_count;
         md.bsdf = m.bsdf_id; md.emitter = m.emitter_id; md.has_normals = m.normals != nullptr; md.has_uv = m.texcoords != nullptr;
+        md.shape = -1;
         s->meshes.push_back(md);
         s->pos.insert(s->pos.end(), m.positions, m.positions + 3 * (size_t) m.vertex_count);
         if (m.normals) s->nrm.insert(s->nrm.end(), m.normals, m.normals + 3 * (size_t) m.vertex_count); else s->nrm.insert(s->nrm.end(), 3 * (size_t) m.vertex_count, 0.f);
@@ -141,6 +142,16 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         mesh_faces.emplace_back(m.faces, m.faces + 3 * (size_t) m.face_count);
         for (uint32_t f = 0; f < m.face_count; ++f) s->faces.push_back(make_uint4(m.faces[3 * f] + vbase, m.faces[3 * f + 1] + vbase, m.faces[3 * f + 2] + vbase, i));
         vbase += m.vertex_count; fbase += m.face_count;
+    }
+    for (uint32_t k = 0; k < d->n_shapes; ++k) {       // analytic shapes: same layout as mtsb_scene_create
+        const mtsb_shape_desc &sh = d->shapes[k];
+        ShapeDev sd; const char *err = nullptr;
+        if (!make_shape_dev(sh.type, sh.flip_normals, sh.to_world, sd, &err)) { delete s; return nullptr; }
+        s->shapes.push_back(sd);
+        MeshDev md; md.face_begin = fbase + k; md.face_count = 1; md.vert_begin = 0; md.vert_count = 0;
+        md.bsdf = sh.bsdf_id; md.emitter = sh.emitter_id; md.has_normals = 0; md.has_uv = 1; md.shape = (int) k;
+        s->meshes.push_back(md);
+        s->faces.push_back(make_uint4(k, kAnalyticTag, (uint32_t) sh.type, d->n_meshes + k));
     }
     s->tables.reserve(64 + d->n_textures + d->n_emitters);
     s->spectral = d->mode == MTSB_MODE_SPECTRAL;
@@ -186,6 +197,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         if (e.type == MTSB_EMITTER_AREA) {
             ed.radiance = mk3(e.radiance[0], e.radiance[1], e.radiance[2]); ed.mesh = e.mesh_id;
             const MeshDev &m = s->meshes[e.mesh_id];
+            if (m.shape >= 0) { ed.normalization = s->shapes[m.shape].inv_area; s->emitters.push_back(ed); continue; }
             AreaTable t = build_area_table(s->pos.data() + 3 * (size_t) m.vert_begin, mesh_faces[e.mesh_id].data(), m.face_count);
             s->tables.push_back(t.cdf); ed.cdf = s->tables.back().data(); ed.cdf_sum = t.sum; ed.normalization = t.normalization; ed.valid_lo = t.valid_lo; ed.valid_hi = t.valid_hi;
         } else if (e.type == MTSB_EMITTER_CONSTANT || e.type == MTSB_EMITTER_POINT) {
@@ -223,7 +235,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     }
     for (size_t i = 0; i < s->sensors.size(); ++i) { s->sensors[i].film_xyza = s->film_xyza[i].data(); s->sensors[i].film_w = s->film_w[i].data(); }
     s->dev.max_depth = d->integrator.max_depth < 0 ? (1 << 30) : d->integrator.max_depth; s->dev.rr_depth = d->integrator.rr_depth;
-    s->dev.pos = s->pos.data(); s->dev.nrm = s->nrm.data(); s->dev.uv = s->uv.data(); s->dev.faces = s->faces.data();
+    s->dev.pos = s->pos.data(); s->dev.nrm = s->nrm.data(); s->dev.uv = s->uv.data(); s->dev.faces = s->faces.data(); s->dev.shapes = s->shapes.data();
     s->dev.meshes = s->meshes.data(); s->dev.tex = s->tex.data(); s->dev.bsdfs = s->bsdfs.data(); s->dev.emitters = s->emitters.data();
     return s;
 }

@@ -324,10 +324,13 @@ def test_vertex_gradient_shadow_boundary_matches_host_replay_and_fd(mi):
     np.testing.assert_allclose(g, gh, rtol=2e-2, atol=1e-2 * np.abs(gh).max())
     P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
     F = H.displacement_fields(P0)
-    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "tz", "scale")}
+    # both sides are Monte Carlo estimates (one seed of either scatters by ~8 %, tests/test_grad_cpu.py:147-149): average the
+    # adjoint over 8 seeds and the oracle's differences over 2 seeds at 2048 spp
+    g8 = np.mean([sc.render_grad(wgt, spp=128, seed=s_, mesh_id=0)[1].reshape(-1, 3) for s_ in range(3, 11)], axis=0)
+    fds = {n: float(np.mean([H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 2048, s_) for s_ in (3, 4)])) for n in ("tx", "tz", "scale")}
     ref = max(abs(v) for v in fds.values())
     for n, fd in fds.items():
-        assert abs(float((g * F[n]).sum()) - fd) < 0.12 * ref, (n, fd)
+        assert abs(float((g8 * F[n]).sum()) - fd) < 0.10 * ref, (n, float((g8 * F[n]).sum()), fd)
 
 
 def test_vertex_gradient_rejects_unsupported(mi):
@@ -532,3 +535,66 @@ def test_scene_from_device_buffers_equals_host_buffers(mi):
     bad.bsdf = 0
     with pytest.raises(mi._abi.MtsbError):
         mi.Scene(sd_d)
+
+
+# ---- analytic shapes as BVH leaf primitives (src/shapes/{sphere,disk,cylinder,rectangle}.cpp) -----------
+@pytest.mark.parametrize("tri_floor", [True, False])
+def test_analytic_shapes_hit_ids_and_film_match_oracle(mi, tri_floor):
+    """Spheres, a cylinder, disks and rectangles as leaves of the BVH8 (mixed with triangles, and alone): closest-hit ids
+    bit-exact vs the oracle (itself pinned against the reference plugins), t / cached (x, y), any-hit, the brute-force
+    kernel, and the film with the same sample streams incl. area lights on all four shapes."""
+    sd = H.shapes_scene(res=(96, 64), spp=16, emitters="disk sphere cylinder rectangle", tri_floor=tri_floor)
+    sc, orc = mi.Scene(sd), H.Oracle(sd)
+    rng = np.random.default_rng(0)
+    om_c, dm_c = orc.sensor_sample_ray(rng.random((100000, 2)))
+    om_i, dm_i = H.random_rays(100000, 3, radius=4.0)
+    om, dm = np.concatenate([om_c, om_i]), np.concatenate([dm_c, dm_i])
+    h_g, h_c = sc.intersect_closest_raw(om, dm), orc.intersect_closest(om, dm)
+    pg, pc = h_g.view(np.uint32)[:, 3], h_c.view(np.uint32)[:, 3]
+    n_tri = 2 if tri_floor else 0
+    analytic = (pg >= n_tri) & (pc >= n_tri)
+    assert np.array_equal(pg[analytic], pc[analytic])
+    assert np.mean(pg != pc) < 1e-3                                   # floor triangles: watertight vs Moeller-Trumbore edge rays
+    assert set(np.unique(pg)) >= set(range(len(sd.shapes) + n_tri))
+    same = (pg == pc) & np.isfinite(h_c[:, 0])
+    assert np.allclose(h_g[same, :3], h_c[same, :3], rtol=2e-5, atol=2e-5)
+    dm2 = dm.copy()
+    dm2[:, 3] = rng.random(len(dm2)).astype(np.float32) * 6
+    assert np.mean(sc.intersect_any_raw(om, dm2).astype(bool) != orc.intersect_any(om, dm2).astype(bool)) < 1e-4
+    h_n = sc.intersect_closest_raw(om[:20000], dm[:20000], naive=True)
+    assert np.array_equal(h_n.view(np.uint32)[:, 3], pg[:20000])
+    sc.film_clear()
+    sc.render_accumulate(spp=16, seed=7)
+    f_g, f_c = sc.film_xyzaw(), orc.render_xyzaw(spp=16, seed=7)
+    assert np.isfinite(f_g).all()
+    assert np.allclose(f_g[..., 4], f_c[..., 4], rtol=1e-4, atol=1e-4)
+    assert np.abs(f_g[..., :3] - f_c[..., :3]).sum() / np.abs(f_c[..., :3]).sum() < 2e-2
+    d = np.abs(f_g[..., :3] - f_c[..., :3]).max(axis=2) / (np.abs(f_c[..., :3]).max(axis=2) + 1e-2)
+    assert (d > 1e-2).mean() < 0.02
+
+
+def test_analytic_shapes_spectral_and_gradient_rejection(mi):
+    """Spectral mode renders the same shapes (vs the oracle); gradient passes refuse scenes with analytic shapes."""
+    sd = H.spectral(H.shapes_scene(res=(48, 32), spp=8, emitters="disk sphere", named_conductor=True))
+    sc, orc = mi.Scene(sd), H.Oracle(sd)
+    a, b = sc.render(spp=8, seed=3), orc.render(spp=8, seed=3)
+    assert np.abs(a - b).sum() / np.abs(b).sum() < 2e-2
+    sd = H.shapes_scene(res=(16, 16), spp=2, emitters="disk")
+    sc = mi.Scene(sd)
+    with pytest.raises(Exception, match="analytic shapes"):
+        sc.render_grad(np.ones((16, 16, 3), np.float32), spp=2, seed=1, tex_id=0)
+    with pytest.raises(Exception):
+        sc.update_vertices(1, np.zeros((4, 3), np.float32))          # mesh 1 is a shape: not a triangle mesh
+
+
+def test_film_drops_invalid_samples(mi):
+    """ImageBlock::put rejects samples with a NaN / Inf / negative channel, weight included (imageblock.cpp:84-108)."""
+    for rf in ("box", "gaussian"):
+        sd = H.cbox_scene(8, 1, rf)
+        sc, orc = mi.Scene(sd), H.Oracle(sd)
+        pos = np.array([[3.5, 3.5]] * 4, np.float32)
+        val = np.array([[1, 1, 1, 1, 1], [np.nan, 1, 1, 1, 1], [1, np.inf, 1, 1, 1], [1, 1, -0.5, 1, 1]], np.float32)
+        sc.film_clear(); sc.film_put(pos, val)
+        f = sc.film_xyzaw()
+        assert np.isfinite(f).all() and np.allclose(f, orc.film_put(pos, val), rtol=1e-5, atol=1e-6), rf
+        assert np.allclose(f, orc.film_put(pos[:1], val[:1]), rtol=1e-5, atol=1e-6)

@@ -156,14 +156,20 @@ def test_xml_subset_loader():
       </sensor>
       <bsdf type="diffuse" id="red"><rgb name="reflectance" value="0.8,0.1,0.1"/></bsdf>
       <shape type="rectangle"><ref id="red"/></shape>
-      <shape type="rectangle"><transform name="to_world"><translate y="2"/><rotate x="1" angle="90"/></transform>
+      <shape type="rectangle"><transform name="to_world"><rotate x="1" angle="90"/><translate y="2" z="1"/></transform>
         <emitter type="area"><rgb name="radiance" value="5"/></emitter></shape>
     </scene>"""
     sd = X.load_string(xml)
     assert sd.spp == 4 and sd.max_depth == 5
     assert sd.sensors[0]["width"] == 20 and sd.sensors[0]["height"] == 10
-    assert len(sd.meshes) == 2 and len(sd.emitters) == 1
+    assert len(sd.shapes) == 2 and len(sd.meshes) == 0 and len(sd.emitters) == 1       # rectangles are analytic primitives
     assert Oracle(sd).render_xyzaw(seed=0).shape == (10, 20, 5)
+    sd_t = X.load_string(xml, _triangulate_rectangles=True)
+    assert len(sd_t.meshes) == 2 and len(sd_t.shapes) == 0
+    a, b = Oracle(sd).render_xyzaw(seed=0), Oracle(sd_t).render_xyzaw(seed=0)
+    # same picture either way; the light samples differ (Mesh::sample_position picks a triangle first), so only coverage is
+    # exact at 4 spp
+    assert np.array_equal(a[..., 3:], b[..., 3:]) and abs(a[..., :3].mean() - b[..., :3].mean()) < 0.1 * b[..., :3].mean()
     with pytest.raises(Exception):
         X.load_string("<scene version='2.0.0'><shape type='nosuchshape'/></scene>")
 
@@ -376,3 +382,78 @@ def test_sample_stream_index_beyond_32_bits():
     assert np.abs(a - b).max() < 2e-3 * max(1.0, np.abs(a).max())
     # pixel 8 of this job (index 2^32 + 2^29 - 2, seed + 1) must not reuse the streams of pixel 0 (index 2^29 - 2, seed)
     assert not np.allclose(a.reshape(-1, 5)[8, :3], a.reshape(-1, 5)[0, :3])
+
+
+# ---- analytic shapes as BVH leaf primitives (N4) -------------------------------------------------------------------
+def test_hostsim_analytic_shapes_match_oracle():
+    """sphere / disk / cylinder / rectangle leaves in the product's BVH8 (csrc/shapes.h, bvh.h) vs the oracle's restatement
+    (pinned against the reference plugins in test_oracle_vs_reference_build.py): hit ids exact, any-hit, film, NEE."""
+    sd = H.shapes_scene(emitters="disk sphere cylinder rectangle")
+    o, h = Oracle(sd), HostSim(sd)
+    om, dm = H.random_rays(20000, 3, radius=4.0)
+    a, b = o.intersect_closest(om, dm), h.intersect_closest(om, dm)
+    pa, pb = a.view(np.uint32)[:, 3], b.view(np.uint32)[:, 3]
+    assert set(np.unique(pa)) >= set(range(11))
+    tri = (pa < 2) | (pb < 2)                                  # the floor's two triangles: watertight vs Moeller-Trumbore edge rays
+    assert np.array_equal(pa[~tri], pb[~tri]) and np.mean(pa != pb) < 1e-3
+    same = (pa == pb) & (pa != 0xffffffff)
+    np.testing.assert_allclose(a[same, :3], b[same, :3], rtol=1e-5, atol=1e-5)       # t and the cached object-space (x, y)
+    dm2 = dm.copy()
+    dm2[:, 3] = np.random.default_rng(2).random(len(dm2)).astype(np.float32) * 6
+    assert np.mean(o.intersect_any(om, dm2) != h.intersect_any(om, dm2)) < 1e-3
+    ra, rb = o.render_xyzaw(spp=8, seed=1), h.render_xyzaw(spp=8, seed=1)
+    assert np.abs(ra - rb).sum() / np.abs(ra).sum() < 1e-5
+    rng = np.random.default_rng(1)
+    p, s2 = rng.uniform(-2, 2, (4000, 3)).astype(np.float32), rng.random((4000, 2)).astype(np.float32)
+    ea, eb = o.sample_emitter_direction(p, s2), h.sample_emitter_direction(p, s2)
+    assert np.allclose(ea, eb, rtol=2e-3, atol=1e-5, equal_nan=True)
+
+
+def test_all_analytic_scene_and_npz_roundtrip(tmp_path):
+    """No triangle at all; SceneData with shapes survives save_npz / load_npz."""
+    sd = H.shapes_scene(emitters="sphere", tri_floor=False)
+    assert len(sd.meshes) == 0 and len(sd.shapes) == 7
+    sd.save_npz(str(tmp_path / "s.npz"))
+    from mitsuba2_b200.scenedata import SceneData
+    sd2 = SceneData.load_npz(str(tmp_path / "s.npz"))
+    a, b = HostSim(sd).render_xyzaw(spp=4, seed=2), HostSim(sd2).render_xyzaw(spp=4, seed=2)
+    assert np.array_equal(a, b)
+    o = Oracle(sd).render_xyzaw(spp=4, seed=2)
+    assert np.abs(a - o).sum() / np.abs(o).sum() < 1e-5
+
+
+def test_xml_loader_analytic_shapes():
+    """<shape type="sphere|disk|cylinder|rectangle"> load as analytic primitives with the plugins' parameters folded into
+    to_world (sphere.cpp:100-110, cylinder.cpp:84-97); `_triangulate_rectangles` keeps the two-triangle rectangle."""
+    from mitsuba2_b200 import xml
+    src = '''<scene version="2.0.0">
+      <shape type="sphere"><point name="center" x="1" y="2" z="3"/><float name="radius" value="0.5"/>
+        <emitter type="area"><rgb name="radiance" value="2"/></emitter></shape>
+      <shape type="cylinder"><point name="p0" x="0" y="0" z="0"/><point name="p1" x="0" y="1" z="0"/><float name="radius" value="0.25"/></shape>
+      <shape type="disk"><boolean name="flip_normals" value="true"/></shape>
+      <shape type="rectangle"><transform name="to_world"><translate x="0" y="0" z="5"/></transform></shape>
+      <sensor type="perspective"><film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film></sensor>
+    </scene>'''
+    sd = xml.load_string(src)
+    assert [s["type"] for s in sd.shapes] == [1, 3, 2, 4] and len(sd.meshes) == 0
+    assert np.allclose(sd.shapes[0]["to_world"], [[0.5, 0, 0, 1], [0, 0.5, 0, 2], [0, 0, 0.5, 3], [0, 0, 0, 1]])
+    assert sd.shapes[0]["emitter"] == 0 and sd.emitters[0]["shape_id"] == 0
+    cyl = sd.shapes[1]["to_world"]
+    assert np.allclose(cyl[:3, 2], [0, 1, 0]) and np.allclose(np.linalg.norm(cyl[:3, :2], axis=0), 0.25)
+    assert sd.shapes[2]["flip_normals"] and np.allclose(sd.shapes[3]["to_world"][:3, 3], [0, 0, 5])
+    om = np.array([[1, 2, 0, 0], [0, 0.5, -3, 0], [0.6, -0.5, -3, 0], [0.3, 0.3, 2, 0]], np.float32)
+    dm = np.array([[0, 0, 1, np.inf]] * 4, np.float32)
+    hits = HostSim(sd).intersect_closest(om, dm)
+    assert np.array_equal(hits.view(np.uint32)[:, 3], [0, 1, 2, 3]) and np.allclose(hits[:, 0], [2.5, 2.75, 3.0, 3.0], atol=1e-5)
+    sd_t = xml.load_string(src, _triangulate_rectangles=True)
+    assert len(sd_t.meshes) == 1 and len(sd_t.shapes) == 3
+
+
+def test_film_drops_invalid_samples():
+    """ImageBlock::put rejects samples with a NaN / Inf / negative channel, weight included (imageblock.cpp:84-108)."""
+    sd = H.cbox_scene(8, 1, "gaussian")
+    pos = np.array([[3.5, 3.5]] * 4, np.float32)
+    val = np.array([[1, 1, 1, 1, 1], [np.nan, 1, 1, 1, 1], [1, np.inf, 1, 1, 1], [1, 1, -0.5, 1, 1]], np.float32)
+    f = Oracle(sd).film_put(pos, val)
+    g = Oracle(sd).film_put(pos[:1], val[:1])
+    assert np.isfinite(f).all() and np.array_equal(f, g)
