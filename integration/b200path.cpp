@@ -115,7 +115,12 @@ private:
     struct Flat {
         std::vector<mtsb_mesh_desc> meshes; std::vector<mtsb_bsdf_desc> bsdfs; std::vector<mtsb_texture_desc> textures;
         std::vector<mtsb_emitter_desc> emitters; std::map<const Object *, int> tex_id, bsdf_id;
+        std::vector<mtsb_shape_desc> shapes;
         std::vector<std::vector<float>> keep;
+    };
+    // Shape::m_to_world is protected (render/shape.h:419); a never-instantiated subclass reads it
+    struct ShapeAccess : Shape {
+        static const Transform<Point<float, 4>> &to_world(const Shape *s) { return static_cast<const ShapeAccess *>(s)->m_to_world; }
     };
     static void identity9(float *m) { for (int i = 0; i < 9; ++i) m[i] = (i % 4 == 0) ? 1.f : 0.f; }
 
@@ -201,9 +206,40 @@ private:
         for (size_t i = 0; i < scene->emitters().size(); ++i) emitter_index[scene->emitters()[i].get()] = (int) i;
         f.emitters.resize(scene->emitters().size());
         // shapes in Scene::shapes() order: the global primitive index is the prefix sum over them (kdtree.h:2382-2400)
+        std::vector<std::pair<int, int>> shape_emitters;      // (emitter index, analytic shape index): mesh_id is fixed up below
         for (auto &sh : scene->shapes()) {
             Mesh *mesh = dynamic_cast<Mesh *>(sh.get());
-            if (!mesh) Throw("b200path: shape %s is not a triangle mesh", sh->class_()->name());
+            if (!mesh) {
+                // analytic shapes (src/shapes/{sphere,disk,cylinder,rectangle}.cpp) become BVH leaf primitives of the backend.
+                // The backend lists them after the meshes; only the order of primitive ids differs, not the image.
+                std::string cls = sh->class_()->name();
+                mtsb_shape_desc d; memset(&d, 0, sizeof(d));
+                d.type = cls == "Sphere" ? MTSB_SHAPE_SPHERE : cls == "Disk" ? MTSB_SHAPE_DISK : cls == "Cylinder" ? MTSB_SHAPE_CYLINDER
+                       : cls == "Rectangle" ? MTSB_SHAPE_RECTANGLE : 0;
+                if (!d.type) Throw("b200path: shape plugin %s is not supported by the backend", cls);
+                matrix16(ShapeAccess::to_world(sh.get()).matrix, d.to_world);       // the plugin's state after update()
+                // flip_normals is private to Sphere / Cylinder: read it off a sampled position (disk / rectangle fold it into to_world)
+                if (d.type == MTSB_SHAPE_SPHERE) {
+                    auto ps = sh->sample_position(0.f, Point<float, 2>(0.3f, 0.3f));
+                    d.flip_normals = dot(ps.n, ps.p - sh->bbox().center()) < 0.f;
+                } else if (d.type == MTSB_SHAPE_CYLINDER)
+                    d.flip_normals = sh->sample_position(0.f, Point<float, 2>(0.5f, 0.f)).n.x() < 0.f;     // cylinder.cpp:222-227: object-space normal
+                d.bsdf_id = bsdf(f, const_cast<BSDF *>(sh->bsdf()));
+                d.emitter_id = -1;
+                if (sh->is_emitter()) {
+                    Emitter *em = const_cast<Emitter *>(sh->emitter());
+                    int ei = emitter_index.at(em);
+                    mtsb_emitter_desc e; memset(&e, 0, sizeof(e));
+                    e.type = MTSB_EMITTER_AREA; e.radiance_tex = -1;
+                    int t = texture(f, b200::Params(em).object("radiance"));
+                    if (t < 0 || f.textures[t].type != MTSB_TEX_CONSTANT) Throw("b200path: textured area lights are not supported");
+                    memcpy(e.radiance, f.textures[t].value, sizeof(e.radiance));
+                    f.emitters[ei] = e; d.emitter_id = ei;
+                    shape_emitters.emplace_back(ei, (int) f.shapes.size());
+                }
+                f.shapes.push_back(d);
+                continue;
+            }
             mtsb_mesh_desc m; memset(&m, 0, sizeof(m));
             m.faces = (const uint32_t *) mesh->faces_buffer().data();        // mesh.h:63-65
             m.positions = mesh->vertex_positions_buffer().data();            // mesh.h:48-50 (world space: loaders bake to_world)
@@ -224,6 +260,7 @@ private:
             }
             f.meshes.push_back(m);
         }
+        for (auto &se : shape_emitters) f.emitters[se.first].mesh_id = (int) f.meshes.size() + se.second;     // mtsb200.h: n_meshes + shape index
         // the remaining emitters, in Scene::emitters() order (scene.cpp:23-48; decides `index` in sample_emitter_direction)
         for (size_t i = 0; i < scene->emitters().size(); ++i) {
             Emitter *em = scene->emitters()[i].get();
@@ -251,6 +288,7 @@ private:
         d.n_meshes = (uint32_t) f.meshes.size(); d.n_bsdfs = (uint32_t) f.bsdfs.size(); d.n_textures = (uint32_t) f.textures.size();
         d.n_emitters = (uint32_t) f.emitters.size(); d.n_sensors = 1;
         d.meshes = f.meshes.data(); d.bsdfs = f.bsdfs.data(); d.textures = f.textures.data(); d.emitters = f.emitters.data(); d.sensors = &sd;
+        d.n_shapes = (uint32_t) f.shapes.size(); d.shapes = f.shapes.data();
         d.integrator.max_depth = m_max_depth; d.integrator.rr_depth = m_rr_depth; d.mode = MTSB_MODE_RGB;
         if (mtsb_scene_create(m_ctx, &d, &m_scene)) Throw("b200path: %s", mtsb_last_error());
         mtsb_stats st; mtsb_scene_stats(m_scene, &st); m_bvh_nodes = st.bvh_nodes;

@@ -135,7 +135,7 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
         int sms = 148, per_sm = 8, occ = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<false>, kBlock, 0) == cudaSuccess && occ > 0) per_sm = occ;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow, kBlock, 0) == cudaSuccess && occ > 0 && occ < per_sm) per_sm = occ;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<false>, kBlock, 0) == cudaSuccess && occ > 0 && occ < per_sm) per_sm = occ;
         if (const char *e = getenv("MTSB_TRACE_BLOCKS_PER_SM")) { int v = atoi(e); if (v > 0 && v <= 32) per_sm = v; }
         if (const char *e = getenv("MTSB_REFILL")) { int v = atoi(e); if (v >= 0 && v <= 32) c->refill = (unsigned) v; }
         c->trace_grid = (unsigned) (sms * per_sm);
@@ -395,6 +395,7 @@ extern "C" int mtsb_scene_create(mtsb_ctx *ctx, const mtsb_scene_desc *d, mtsb_s
             s->meshes.push_back(md);
             sf[k] = make_uint4(k, kAnalyticTag, (uint32_t) sh.type, d->n_meshes + k);
         }
+        s->ext = true;                   // analytic surface interactions / light sampling live in the RgbX / SpectralX shade instances
         CU(s->d_shapes.upload(s->shapes.data(), s->shapes.size(), st));
         CU(cudaMemcpyAsync(s->faces.p + fbase, sf.data(), sf.size() * sizeof(uint4), cudaMemcpyHostToDevice, st));
         CU(cudaStreamSynchronize(st));
@@ -628,8 +629,11 @@ static int intersect_common(mtsb_scene *s, uint64_t n, const float *o_mint, cons
     uint32_t *work = s->counters.p + kWorkClosest;
     if (mode != 2) CU(cudaMemsetAsync(work, 0, sizeof(uint32_t), st));
     unsigned tg = trace_grid_for(s->ctx, n);
-    if (mode == 0) k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill, nullptr);
-    else if (mode == 1) k_trace<true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill, nullptr);
+    const bool shp = !s->shapes.empty();      // scenes with analytic leaf primitives run the <.., true> instances
+    if (mode == 0 && !shp) k_trace<false, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill, nullptr);
+    else if (mode == 0) k_trace<false, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h, nullptr, work, s->ctx->refill, nullptr);
+    else if (mode == 1 && !shp) k_trace<true, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill, nullptr);
+    else if (mode == 1) k_trace<true, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, nullptr, d_occ, work, s->ctx->refill, nullptr);
     else k_trace_naive<<<grid_for(n), kBlock, 0, st>>>(s->dev.bvh, (uint32_t) n, (const float4 *) d_o, (const float4 *) d_d, (float4 *) d_h);
     CU(cudaEventRecord(s->ctx->ev1, st));
     CU(cudaGetLastError());
@@ -706,13 +710,15 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     int depth0 = 1;
     if (edge2) {      // primary hits, then one far ray per sample as the depth-2 entry of the other queue
         PathQueue q0 = make_queue(s, 0), q1 = make_queue(s, 1);
-        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p); }
+        { StageTimer t(s->ctx, ST_CLOSEST); if (s->shapes.empty()) k_trace<false, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p);
+          else k_trace<false, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE); k_edge2_raygen<<<grid_for(n), kBlock, 0, st>>>(s->dev, edge2->e, edge2->total_len, b, q0, q1, s->counters.p); }
         launches += 2; cur = 1; depth0 = 2;
     }
     for (int depth = depth0; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
-        { StageTimer t(s->ctx, ST_CLOSEST); k_trace<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
+        { StageTimer t(s->ctx, ST_CLOSEST); if (s->shapes.empty()) k_trace<false, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p);
+          else k_trace<false, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
         { StageTimer t(s->ctx, ST_SHADE);
           if (grad && grad->grad_pos) { if (s->ext) k_shade_grad<true, RgbX><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
                                         else k_shade_grad<true, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }
@@ -731,7 +737,8 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
           } }
         launches += 2;
         if (depth < s->dev.max_depth) {
-            { StageTimer t(s->ctx, ST_ANY); k_shadow<<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
+            { StageTimer t(s->ctx, ST_ANY); if (s->shapes.empty()) k_shadow<false><<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill);
+              else k_shadow<true><<<tg, kBlock, 0, st>>>(s->dev.bvh, sq, s->counters.p, s->dstats.p, (uint32_t) depth, n, s->result.p, s->counters.p + kWorkShadow + depth, s->ctx->refill); }
             launches++;
             if (vgrad) { StageTimer t(s->ctx, ST_SHADE); k_nee_grad<<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, sq, s->counters.p, (uint32_t) depth, n, *grad); launches++; }
         }
@@ -1049,7 +1056,8 @@ extern "C" int mtsb_intersect_closest_noalloc(mtsb_scene *s, uint64_t n, const f
     }
     CU(cudaMemsetAsync(work, 0, kNoAllocHeader, st));          // the fetch cursor must start at zero; the previous call left it at >= its n
     CU(cudaEventRecord(s->ctx->ev0, st));
-    k_trace<false><<<trace_grid_for(s->ctx, n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, d_o, d_d, d_h, nullptr, work, s->ctx->refill, nullptr);
+    if (s->shapes.empty()) k_trace<false, false><<<trace_grid_for(s->ctx, n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, d_o, d_d, d_h, nullptr, work, s->ctx->refill, nullptr);
+    else k_trace<false, true><<<trace_grid_for(s->ctx, n), kBlock, 0, st>>>(s->dev.bvh, nullptr, (uint32_t) n, d_o, d_d, d_h, nullptr, work, s->ctx->refill, nullptr);
     CU(cudaEventRecord(s->ctx->ev1, st));
     CU(cudaGetLastError());
     if (mem == MTSB_MEM_HOST) CU(cudaMemcpyAsync(hits, d_h, n * sizeof(float4), cudaMemcpyDeviceToHost, st));

@@ -206,7 +206,7 @@ template <typename M>
 HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float sx, float sy, float4 wav) {
     DirSampleT<M> ds;
     const MeshDev m = sc.meshes[e.mesh];
-    if (m.shape >= 0) {
+    if (M::ext && m.shape >= 0) {
         shape_sample_direction(sc.shapes[m.shape], ref_p, sx, sy, ds.p, ds.n, ds.d, ds.dist, ds.pdf);
         bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
         ds.value = active ? emitter_radiance<M>(sc, e, wav) / ds.pdf : M::splat(0.f);
@@ -238,9 +238,12 @@ HD DirSampleT<M> area_sample_direction(const SceneDev &sc, const EmitterDev &e, 
     ds.value = active ? emitter_radiance<M>(sc, e, wav) / ds.pdf : M::splat(0.f);
     return ds;
 }
+template <bool Shapes = true>
 HD float area_pdf_direction(const SceneDev &sc, const EmitterDev &e, float3 ref_p, float3 d, float3 n, float dist) {
-    int shape = sc.meshes[e.mesh].shape;
-    if (shape >= 0) return dot(d, n) < 0.f ? shape_pdf_direction(sc.shapes[shape], ref_p, d, n, dist) : 0.f;
+    if (Shapes) {
+        int shape = sc.meshes[e.mesh].shape;
+        if (shape >= 0) return dot(d, n) < 0.f ? shape_pdf_direction(sc.shapes[shape], ref_p, d, n, dist) : 0.f;
+    }
     float dp = fabsf(dot(d, n));
     float pdf = e.normalization * (dp != 0.f ? (dist * dist) / dp : 0.f);
     return dot(d, n) < 0.f ? pdf : 0.f;

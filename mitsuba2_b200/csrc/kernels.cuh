@@ -175,7 +175,9 @@ __device__ __noinline__ float4 shape_intersect_slot(const ShapeDev *sh, float3 o
     bool ok = shape_intersect(*sh, o, d, mint, maxt, t, u, v);
     return make_float4(t, u, v, ok ? 1.f : 0.f);
 }
-template <bool AnyHit, typename Sink>
+// Shapes: the scene has analytic leaf primitives.  A template parameter rather than a run-time test: the mere presence of the
+// out-of-line call in the triangle loop cost the triangle-only instance 4 % (22.3 -> 23.1 ms per C3 step, measured).
+template <bool AnyHit, bool Shapes, typename Sink>
 __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count, const float4 *__restrict__ o_mint,
                                                  const float4 *__restrict__ d_maxt, uint32_t *work, uint32_t refill, Sink sink) {
     __shared__ uint2 s_stack[kStackFast * kBlock];
@@ -272,15 +274,17 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
                     uint32_t stb = __shfl_sync(0xffffffffu, tb, src);
                     // scenes with analytic shapes: the testing lane re-reads the owner's ray (the shared record holds the
                     // sheared Woop rows, not the direction)
-                    uint32_t sray = bvh.shapes != nullptr ? __shfl_sync(0xffffffffu, ray, src) : 0u;
+                    uint32_t sray = 0u;
+                    if constexpr (Shapes) sray = __shfl_sync(0xffffffffu, ray, src);
                     if (mine) {
                         const float4 *tp = bvh.tris + 3 * (size_t) (stb + (it & 31u));
                         float4 a0 = __ldg(tp), a1 = __ldg(tp + 1), a2 = __ldg(tp + 2);
                         float4 r0 = ws.ray[0][src], r1 = ws.ray[1][src], r2 = ws.ray[2][src], r3 = ws.ray[3][src];
                         RayWoop rw; rw.rx = xyz(r1); rw.ry = xyz(r2); rw.rz = xyz(r3);
                         float t, u, v;
-                        bool ok;
-                        if (bvh.shapes != nullptr && f2u(a1.w) != 0u) {
+                        bool ok, analytic = false;
+                        if constexpr (Shapes) analytic = f2u(a1.w) != 0u;
+                        if (analytic) {
                             float4 r = shape_intersect_slot(bvh.shapes + f2u(a2.w), xyz(r0), xyz(d_maxt[sray]), r0.w, r1.w);
                             t = r.x; u = r.y; v = r.z; ok = r.w != 0.f;
                         } else
@@ -318,13 +322,13 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
     }
 }
 
-template <bool AnyHit>
+template <bool AnyHit, bool Shapes = false>
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_trace(Bvh bvh, const uint32_t *count_ptr, uint32_t count_max, const float4 *__restrict__ o_mint,
         const float4 *__restrict__ d_maxt, float4 *__restrict__ hits, uint32_t *__restrict__ occluded,
         uint32_t *work, uint32_t refill, const uint8_t *__restrict__ prim_class) {
     uint32_t count = count_ptr ? min(*count_ptr, count_max) : count_max;
-    trace_persistent<AnyHit>(bvh, count, o_mint, d_maxt, work, refill,
+    trace_persistent<AnyHit, Shapes>(bvh, count, o_mint, d_maxt, work, refill,
         [=](uint32_t i, bool found, const Hit &h) {
             if (AnyHit) occluded[i] = found ? 1u : 0u;
             else {
@@ -537,12 +541,13 @@ __global__ void k_edge_scatter(SceneDev sc, EdgeCtx e, const float *total_len, G
 }
 
 // any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)
+template <bool Shapes = false>
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)
 k_shadow(Bvh bvh, ShadowQueue sq, const uint32_t *counters, unsigned long long *stats, uint32_t depth, uint32_t count_max,
          float4 *result, uint32_t *work, uint32_t refill) {
     uint32_t count = min(counters[1024 + depth], count_max);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[1], (unsigned long long) count);
-    trace_persistent<true>(bvh, count, sq.o_mint, sq.d_maxt, work, refill,
+    trace_persistent<true, Shapes>(bvh, count, sq.o_mint, sq.d_maxt, work, refill,
         [=](uint32_t i, bool found, const Hit &) {
             if (sq.occluded != nullptr) sq.occluded[i] = found ? 1u : 0u;
             if (found) return;
@@ -700,7 +705,7 @@ __global__ void k_bsdf_eval_pdf(SceneDev sc, uint32_t bsdf_id, uint32_t n, const
 __global__ void k_sample_emitter(SceneDev sc, uint32_t n, const float *ref_p, const float *s2, float *out11) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    DirSample ds = sample_emitter_direction(sc, ld3(ref_p, i), s2[2 * i], s2[2 * i + 1]);
+    DirSampleT<RgbX> ds = sample_emitter_direction<RgbX>(sc, ld3(ref_p, i), s2[2 * i], s2[2 * i + 1]);     // RgbX: incl. analytic emitter shapes
     float *o = out11 + 11 * (size_t) i;
     o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.x; o[6] = ds.value.y; o[7] = ds.value.z;
     o[8] = ds.n.x; o[9] = ds.n.y; o[10] = ds.n.z;

@@ -167,7 +167,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     load_throughput(q, i, te, thr, eta, we);
     if (M::spectral) sample_wavelengths(we.x, wav, ray_weight);
     float3 o = xyz(o4), d = xyz(d4);
-    SI si = make_si(sc, o, d, h4);
+    SI si = make_si<M::ext>(sc, o, d, h4);
     bool chain_ok = true;                     // vertex-gradient replay: no delta vertex on the path so far
     if (GradFn::kVertex) {
         float4 p1 = depth > 1 ? q.prev1[i] : make_float4(u2f(0xffffffffu), 0.f, 0.f, u2f(1u));
@@ -185,7 +185,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
             Le = si.wi.z > 0.f ? emitter_radiance<M>(sc, e, wav) : M::splat(0.f);
             if (depth > 1 && !prev_delta) {
                 float3 dd = si.p - o; float dist = norm(dd); dd = dd / dist;
-                emitter_pdf = area_pdf_direction(sc, e, o, dd, si.sh.n, dist);
+                emitter_pdf = area_pdf_direction<M::ext>(sc, e, o, dd, si.sh.n, dist);
             }
         } else if (e.type == 1) {
             Le = env_eval<M>(sc, e, d, wav);

@@ -37,9 +37,10 @@ struct EmitterDev {
 };
 struct MeshDev {
     uint32_t face_begin, face_count, vert_begin, vert_count;
-    int bsdf, emitter, has_normals, has_uv;
+    int bsdf, emitter; int16_t has_normals, has_uv;
     int shape;              // >= 0: an analytic shape (one primitive), index into SceneDev::shapes; -1: triangle mesh
 };
+static_assert(sizeof(MeshDev) == 32, "MeshDev is fetched as two 128-bit loads");
 struct SensorDev {
     float to_world[16], sample_to_camera[16];
     float near_clip, far_clip;

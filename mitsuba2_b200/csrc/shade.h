@@ -55,6 +55,9 @@ static __host__ __device__ __noinline__ void shape_fill_si(const ShapeDev &sh, f
 }
 
 constexpr uint32_t kPrimMask = 0x3fffffffu;     // primitive ids use 30 bits; the top two carry the shade class in the queues
+// Shapes = false: the scene has no analytic primitive (the lean Rgb / Spectral shade instances; scenes with shapes run the
+// RgbX / SpectralX ones)
+template <bool Shapes = true>
 HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     SI si;
     si.t = hit.x; si.prim = f2u(hit.w) & kPrimMask; si.valid = hit.x != INFINITY;
@@ -63,7 +66,7 @@ HD SI make_si(const SceneDev &sc, float3 o, float3 d, float4 hit) {
     uint4 f = sc.faces[si.prim];
     si.mesh = (int) f.w;
     const MeshDev m = sc.meshes[f.w];
-    if (f.y == kAnalyticTag) {
+    if (Shapes && f.y == kAnalyticTag) {
         float3 dp_du;
         shape_fill_si(sc.shapes[f.x], o, d, hit.x, hit.y, hit.z, si.p, si.n, si.u, si.v, dp_du);
         si.sh.n = si.n;

@@ -147,7 +147,7 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
         const mtsb_shape_desc &sh = d->shapes[k];
         ShapeDev sd; const char *err = nullptr;
         if (!make_shape_dev(sh.type, sh.flip_normals, sh.to_world, sd, &err)) { delete s; return nullptr; }
-        s->shapes.push_back(sd);
+        s->shapes.push_back(sd); s->ext = true;
         MeshDev md; md.face_begin = fbase + k; md.face_count = 1; md.vert_begin = 0; md.vert_count = 0;
         md.bsdf = sh.bsdf_id; md.emitter = sh.emitter_id; md.has_normals = 0; md.has_uv = 1; md.shape = (int) k;
         s->meshes.push_back(md);
@@ -452,6 +452,6 @@ extern "C" void hs_bsdf_sample(hs_scene *s, uint32_t id, uint64_t n, const float
     }
 }
 extern "C" void hs_sample_emitter_direction(hs_scene *s, uint64_t n, const float *ref_p, const float *s2, float *out11) {
-    for (uint64_t i = 0; i < n; ++i) { DirSample ds = sample_emitter_direction(s->dev, ld3(ref_p, (uint32_t) i), s2[2 * i], s2[2 * i + 1]); float *o = out11 + 11 * i;
+    for (uint64_t i = 0; i < n; ++i) { DirSampleT<RgbX> ds = sample_emitter_direction<RgbX>(s->dev, ld3(ref_p, (uint32_t) i), s2[2 * i], s2[2 * i + 1]); float *o = out11 + 11 * i;
         o[0] = ds.d.x; o[1] = ds.d.y; o[2] = ds.d.z; o[3] = ds.dist; o[4] = ds.pdf; o[5] = ds.value.x; o[6] = ds.value.y; o[7] = ds.value.z; o[8] = ds.n.x; o[9] = ds.n.y; o[10] = ds.n.z; }
 }

@@ -26,7 +26,9 @@ def _run_cli(sd, tmp, spp, integrator):
 
 
 @pytest.mark.parametrize("scene_fn", [lambda: H.cbox_scene(res=64, spp=64, rfilter="box"), lambda: H.cbox_scene(res=48, spp=64, rfilter="gaussian"),
-                                      lambda: H.material_scene(res=(96, 64), spp=64), lambda: H.n1_scene(res=(48, 32), spp=64)])
+                                      lambda: H.material_scene(res=(96, 64), spp=64), lambda: H.n1_scene(res=(48, 32), spp=64),
+                                      # analytic sphere / disk / cylinder / rectangle plugins of the reference -> BVH leaf primitives
+                                      lambda: H.shapes_scene(res=(72, 48), spp=64, emitters="disk sphere cylinder rectangle")])
 def test_plugin_equals_python_front_end_and_reference_path(scene_fn, tmp_path):
     import mitsuba2_b200 as mi
     mi.set_variant("cuda_b200_rgb")
@@ -49,7 +51,7 @@ def test_plugin_equals_python_front_end_and_reference_path(scene_fn, tmp_path):
 
 def test_plugin_fails_loudly_on_unsupported_plugins(tmp_path):
     xml = tmp_path / "s.xml"
-    xml.write_text('<scene version="2.1.0"><integrator type="b200path"/><shape type="sphere"/>'
+    xml.write_text('<scene version="2.1.0"><integrator type="b200path"/><shape type="sphere"/><emitter type="spot"/>'
                    '<sensor type="perspective"><film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film></sensor></scene>')
     r = subprocess.run([H.RefBuild.CLI, "-m", "scalar_rgb", "-o", str(tmp_path / "o.exr"), str(xml)], env=H.RefBuild._env(), capture_output=True, text=True, timeout=600)
-    assert r.returncode != 0 and "not a triangle mesh" in (r.stdout + r.stderr)
+    assert r.returncode != 0 and "emitter plugin SpotLight is not supported" in (r.stdout + r.stderr)
