@@ -222,8 +222,15 @@ private:
                 if (d.type == MTSB_SHAPE_SPHERE) {
                     auto ps = sh->sample_position(0.f, Point<float, 2>(0.3f, 0.3f));
                     d.flip_normals = dot(ps.n, ps.p - sh->bbox().center()) < 0.f;
-                } else if (d.type == MTSB_SHAPE_CYLINDER)
+                } else if (d.type == MTSB_SHAPE_CYLINDER) {
                     d.flip_normals = sh->sample_position(0.f, Point<float, 2>(0.5f, 0.f)).n.x() < 0.f;     // cylinder.cpp:222-227: object-space normal
+                    // after update() the cylinder's to_world is rigid and radius / length are private (cylinder.cpp:116-123): measure
+                    // them on sampled positions (sample_position: (r cos 2 pi v, r sin 2 pi v, u length)) and fold them back in
+                    auto p00 = sh->sample_position(0.f, Point<float, 2>(0.f, 0.f)).p, p05 = sh->sample_position(0.f, Point<float, 2>(0.f, 0.5f)).p,
+                         p10 = sh->sample_position(0.f, Point<float, 2>(1.f, 0.f)).p;
+                    float radius = 0.5f * norm(p00 - p05), length = norm(p10 - p00);
+                    for (int r = 0; r < 3; ++r) { d.to_world[4 * r] *= radius; d.to_world[4 * r + 1] *= radius; d.to_world[4 * r + 2] *= length; }
+                }
                 d.bsdf_id = bsdf(f, const_cast<BSDF *>(sh->bsdf()));
                 d.emitter_id = -1;
                 if (sh->is_emitter()) {

@@ -13,7 +13,9 @@ import sys
 
 def short(name):
     name = re.sub(r"\(.*", "", name.replace("mtsb::", "").replace("void ", ""))
-    return name.replace("(bool)0", "0").replace("(bool)1", "1")
+    name = name.replace("(bool)0", "0").replace("(bool)1", "1")
+    # triangle-only instances (second template argument Shapes = 0) keep their round-2 names: k_trace<0>, k_trace<1>, k_shadow
+    return name.replace("k_trace<0, 0>", "k_trace<0>").replace("k_trace<1, 0>", "k_trace<1>").replace("k_shadow<0>", "k_shadow")
 
 
 rows = [r for r in csv.reader(l for l in open(sys.argv[1]) if l.startswith('"'))]
