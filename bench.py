@@ -92,6 +92,69 @@ def side_metrics(mi, local):
     return out
 
 
+def multi_gpu_side_metrics(mi, local, rank, world, dist, torch, dev):
+    """The other configurations at N > 1 (every rank runs this; device times are the max over ranks):
+    C3 in the spectral mode, samples sharded like the headline (weak scaling, film all-reduced once);
+    the C4 gradient pass with the samples of one optimisation step sharded over the ranks (strong scaling: 64 spp in total)
+    and the texture + vertex gradients all-reduced -- the data-parallel step of C5 (one view per rank works the same way)."""
+    from mitsuba2_b200 import scenes, distributed
+    A = mi._abi
+    out = {}
+
+    def rmax(v):
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- C3 spectral, weak scaling
+    sd = scenes.c3_scene()
+    sd.mode = "spectral"
+    sc = mi.Scene(sd, device=local)
+    spp, steps, warm = 16, 3, 2
+    npix = sd.sensors[0]["width"] * sd.sensors[0]["height"]
+    film = torch.empty(npix * 5, dtype=torch.float32, device=dev)
+    ms = 0.0
+    for i in range(warm + steps):
+        if i == warm:
+            sc.film_clear()
+            dist.barrier(); torch.cuda.synchronize()
+        st = sc.render_accumulate(spp=spp, seed=1, spp_begin=(i * world + rank) * spp, spp_total=(warm + steps) * world * spp)
+        if i >= warm:
+            ms += st["ms_total"]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    A.check(A.lib().mtsb_film_read(sc._h, 0, film.data_ptr(), A.MEM_DEVICE))
+    dist.all_reduce(film)
+    e1.record(); e1.synchronize()
+    ms = rmax(ms + e0.elapsed_time(e1))
+    out["c3_spectral_msamples_per_s"] = npix * spp * steps * world / (ms * 1e-3) / 1e6
+    out["c3_spectral_scaling"] = "weak (16 spp per GPU per step, film all-reduced once per job)"
+    del sc
+    # ---- C4 gradient pass, 64 spp shared by the ranks, gradients all-reduced
+    sd4, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"))
+    mid = next(i for i, m in enumerate(sd4.meshes) if m.name == "c4_sphere")
+    sc4 = mi.Scene(sd4, device=local)
+    dl = torch.randn(512 * 512 * 3, device=dev)
+    dist.broadcast(dl, 0)
+    lo, cnt = distributed.sample_share(64, rank, world)
+    for name, kw in (("texture", {}), ("texture_and_vertices", {"mesh_id": mid})):
+        t_all = []
+        for i in range(2 + 3):
+            dist.barrier(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            gt, gv = sc4.render_grad(dl, spp=cnt, seed=i, tex_id=tex, spp_begin=lo, spp_total=64, **kw)
+            dist.all_reduce(gt)
+            if gv is not None:
+                dist.all_reduce(gv)
+            e1.record(); e1.synchronize()
+            if i >= 2:
+                t_all.append(rmax(e0.elapsed_time(e1)))
+        out[f"c4_gradient_pass_{name}_ms"] = float(np.median(t_all))
+    out["c4_scaling"] = f"strong (64 spp per step split over {world} GPUs, texture + vertex gradients all-reduced inside the timed region)"
+    return out
+
+
 def spectral_metric(mi, local, spp=16, steps=3, warmup=2):
     """C3 in the spectral mode (`cuda_b200_spectral`: 4 wavelengths per path, same scene authored in RGB + Cu optical
     constants): Msamples/s on one GPU, inputs resident, same timing as the headline."""
@@ -133,6 +196,19 @@ def parity_gates(mi, local):
         g["c3_4M_triangles_crop"] = BP.c3_parity(mi, local, run_spp=32, gpu_runs=32, cpu_runs=8)
     except Exception as e:
         g["bench_size_error"] = repr(e)
+    # C4 at its own size (512^2, 512^2 x 3 texels, 20k-triangle sphere): adjoint vs central finite differences of the CUDA
+    # renderer at identical seeds (tools/c4_fd_check.py; the full protocol -- 64 texel blocks, 32 vertex coordinates, epsilon
+    # sweep, 4096 spp -- is run by hand and tabulated in DESIGN.md section 4b; this is the bounded version)
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import c4_fd_check
+        r = c4_fd_check.run(res=512, spp=64, passes=1, fd_spp=1024, n_tex=16, n_vtx=0, eps_list=(0.5,), device=local, same_samples=True)
+        g["c4_512x512_fd"] = {"texture_rel_l2": r["texture"]["rel_l2"], "texture_cosine": r["texture"]["cosine"],
+                              "vertex_fields_rel_l2": r["vertex_fields_rel_l2"],
+                              "vertex_fields": {k: {"adjoint": v["adjoint"], "fd": v["fd_by_eps"]["0.5"][0]} for k, v in r["vertex_fields"].items()},
+                              "fd_spp": 1024, "same_samples": True}
+    except Exception as e:
+        g["c4_fd_error"] = repr(e)
     sd = H.sphere_scene(n_theta=128, n_phi=256)
     sc, orc = mi.Scene(sd, device=local), H.Oracle(sd)
     om, dm = H.random_rays(200000, 5, radius=1.5)
@@ -513,6 +589,14 @@ def main():
            "d2h_bytes_per_step": int(film_host[0].numel() * 4),
            "note": "per step: pinned texture upload on every rank, render, film all-reduce, rank 0 reads the film back"}
 
+    mg_side = None
+    if world > 1 and not args.no_side_metrics:
+        del scene
+        try:
+            mg_side = multi_gpu_side_metrics(mi, local, rank, world, dist, torch, dev)
+        except Exception as e:
+            mg_side = {"error": repr(e)}
+
     if rank == 0:
         peak, peak_src = peaks()
         prof = ncu_profile()
@@ -550,6 +634,8 @@ def main():
                       "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"]},
                       "scene_setup_s": t_build, "strong_scaling": strong, "multi_gpu_parity": mg_parity},
         }
+        if mg_side is not None:
+            out["extra"]["side_metrics_multi_gpu"] = mg_side
         if world == 1 and not args.no_side_metrics:
             del scene
             try:

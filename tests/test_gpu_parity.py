@@ -134,31 +134,49 @@ def test_sample_sharding_is_exact_union(mi):
     assert np.allclose(full, parts, rtol=1e-5, atol=1e-5)
 
 
-def test_stage_hooks_match_oracle(mi):
-    sd = H.material_scene()
+def _rel_err(g, c, floor):
+    """|g - c| / max(|c|, floor) over the finite entries -> (max, 99.9th percentile)"""
+    g, c = np.asarray(g, np.float64), np.asarray(c, np.float64)
+    e = np.abs(g - c) / np.maximum(np.abs(c), floor)
+    e = e[np.isfinite(e)]
+    return float(e.max()), float(np.quantile(e, 0.999))
+
+
+# per BSDF type (MTSB_BSDF_*): bars at ~5x the error measured on the B200 (tools/hook_errors.py).  `sample`: (99.9th
+# percentile, max) -- the max is the rare sample whose Newton solve in sample_visible_11 / whose lobe choice sits on a
+# float boundary; eval / pdf: max.  Types 0 diffuse, 1 roughconductor, 2 dielectric, 3 conductor, 4 plastic,
+# 5 roughdielectric, 6 roughplastic.
+_SAMPLE_TOL = {0: (3e-5, 1e-4), 1: (5e-5, 1e-3), 2: (1e-6, 2e-6), 3: (2e-6, 2e-6), 4: (5e-5, 1e-4), 5: (1e-4, 1e-2), 6: (1e-4, 1e-2)}
+_EVAL_TOL = {0: 1e-6, 1: 2e-5, 2: 1e-6, 3: 1e-6, 4: 5e-6, 5: 1e-4, 6: 1e-5}
+
+
+@pytest.mark.parametrize("scene_fn", [H.material_scene, H.n4_scene, H.n1_scene])
+def test_stage_hooks_match_oracle(mi, scene_fn):
+    """`sensor.sample_ray`, `bsdf.sample / eval / pdf` of every BSDF of the scene and `scene.sample_emitter_direction` through
+    the C ABI vs the oracle on shared inputs, each function held to its own measured float error."""
+    sd = scene_fn()
     scene, orc = mi.Scene(sd), H.Oracle(sd)
     rng = np.random.default_rng(5)
     n = 4096
     pos = rng.random((n, 2)).astype(np.float32)
-    for a, b in zip(scene.sensor_sample_ray(pos), orc.sensor_sample_ray(pos)):
-        assert np.allclose(a, b, rtol=1e-5, atol=1e-6)
+    (og, dg), (oc, dc) = scene.sensor_sample_ray(pos), orc.sensor_sample_ray(pos)
+    assert np.array_equal(og[:, :3], oc[:, :3]) and np.allclose(og[:, 3], oc[:, 3], rtol=1e-6)      # origin exact, mint = near / d.z
+    assert _rel_err(dg[:, :3], dc[:, :3], 1e-3)[0] < 2e-5 and np.allclose(dg[:, 3], dc[:, 3], rtol=1e-6)
     wi = rng.normal(size=(n, 3)); wi[:, 2] = np.abs(wi[:, 2]) + 0.05; wi /= np.linalg.norm(wi, axis=1, keepdims=True)
     wi[: n // 8, 2] *= -1                      # some back-facing
     wo = rng.normal(size=(n, 3)); wo /= np.linalg.norm(wo, axis=1, keepdims=True)
     uv, s1, s2 = rng.random((n, 2)), rng.random(n), rng.random((n, 2))
     for bid in range(len(sd.bsdfs)):
+        ty = sd.bsdfs[bid]["type"]
         g, c = scene.bsdf_sample(bid, wi, uv, s1, s2), orc.bsdf_sample(bid, wi, uv, s1, s2)
-        # near-normal incidence makes the Newton solve of sample_visible_11 ill-conditioned (tan_i -> 0): a different FMA
-        # contraction moves such a sample by ~1e-3; allow one row in a thousand
-        bad = ~np.isclose(g, c, rtol=2e-3, atol=2e-4).all(axis=1)
-        assert bad.mean() <= 1e-3, (bid, int(bad.sum()))
+        mx, p999 = _rel_err(g, c, 1e-2)
+        assert p999 < _SAMPLE_TOL[ty][0] and mx < _SAMPLE_TOL[ty][1], (bid, ty, mx, p999)
         (eg, pg), (ec, pc) = scene.bsdf_eval_pdf(bid, wi, uv, wo), orc.bsdf_eval_pdf(bid, wi, uv, wo)
-        assert np.allclose(eg, ec, rtol=2e-3, atol=1e-5) and np.allclose(pg, pc, rtol=2e-3, atol=1e-5), bid
+        assert _rel_err(eg, ec, 1e-3)[0] <= _EVAL_TOL[ty] and _rel_err(pg, pc, 1e-3)[0] <= _EVAL_TOL[ty], (bid, ty)
     ref_p = rng.normal(size=(n, 3)).astype(np.float32)
     g, c = scene.sample_emitter_direction(ref_p, s2), orc.sample_emitter_direction(ref_p, s2)
-    assert np.allclose(g[:, :5], c[:, :5], rtol=2e-3, atol=1e-4)
-    fin = np.isfinite(c[:, 5:8]).all(axis=1)
-    assert np.allclose(g[fin, 5:8], c[fin, 5:8], rtol=5e-3, atol=1e-3)
+    assert _rel_err(g[:, :5], c[:, :5], 1e-2)[0] < 2e-4            # direction, distance, pdf (envmap warp: texel-boundary cases)
+    assert _rel_err(g[:, 5:8], c[:, 5:8], 1e-2)[0] < 2e-5          # value
 
 
 def test_film_put_matches_oracle(mi):
