@@ -94,7 +94,7 @@ def c3_scene(n_theta=1000, n_phi=2000, width=1920, height=1080, small=(158, 316)
     return sd
 
 
-def c4_scene(cbox_npz, res=512, spp=64, tex_res=512, sphere=(100, 100), seed=4):
+def c4_scene(cbox_npz, res=512, spp=64, tex_res=512, sphere=(100, 100), seed=4, displace=True, smooth=True):
     """C4 (gradient pass): Cornell-box geometry (fixture `cbox_npz`) whose floor reflectance is a tex_res^2 RGB bitmap
     (values U[0.2,0.8)) and whose small box is replaced by a ~20k-triangle displaced sphere.  Returns (scene, tex id)."""
     sd = SceneData.load_npz(cbox_npz)
@@ -112,7 +112,9 @@ def c4_scene(cbox_npz, res=512, spp=64, tex_res=512, sphere=(100, 100), seed=4):
         if "smallbox" in m.name:
             c = 0.5 * (m.positions.min(axis=0) + m.positions.max(axis=0))
             r = 0.5 * float((m.positions.max(axis=0) - m.positions.min(axis=0)).min())
-            sph = M.displaced_sphere(sphere[0], sphere[1], radius=r, center=tuple(c))
+            sph = M.displaced_sphere(sphere[0], sphere[1], radius=r, center=tuple(c), displace=displace)
+            if not smooth:          # diagnostic variants (tools/c4_fd_check.py): flat shading / undisplaced convex sphere
+                sph.normals = None
             sph.bsdf, sph.name = m.bsdf, "c4_sphere"
             sd.meshes[i] = sph
     sd.spp = spp

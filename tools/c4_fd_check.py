@@ -20,11 +20,11 @@ sys.path.insert(0, ROOT)
 
 
 def run(res=512, spp=64, passes=8, fd_spp=4096, n_tex=64, n_vtx=32, eps_list=(0.25, 0.5, 1.0), device=0, seed=11, tex_res=512, log=None,
-        max_depth=None, boundary=2, edge_fraction=0.25, rr_off=False, same_samples=False, variant="full"):
+        max_depth=None, boundary=2, edge_fraction=0.25, rr_off=False, same_samples=False, variant="full", displace=True, smooth=True, sphere=(100, 100)):
     import mitsuba2_b200 as mi
     from mitsuba2_b200 import scenes
     mi.set_variant("cuda_b200_rgb")
-    sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=res, spp=spp, tex_res=tex_res)
+    sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=res, spp=spp, tex_res=tex_res, displace=displace, smooth=smooth, sphere=sphere)
     mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
     if variant == "black_sphere":        # only what the sphere does to the rest of the room (its shadow, its silhouette) is left
         sd.meshes[mid].bsdf = sd.add_diffuse(0.0)
@@ -138,7 +138,10 @@ if __name__ == "__main__":
     ap.add_argument("--fd-spp", type=int, default=4096); ap.add_argument("--texels", type=int, default=64); ap.add_argument("--vertex-coords", type=int, default=32)
     ap.add_argument("--quiet", action="store_true"); ap.add_argument("--max-depth", type=int, default=None); ap.add_argument("--boundary", type=int, default=2)
     ap.add_argument("--edge-fraction", type=float, default=0.25); ap.add_argument("--rr-off", action="store_true"); ap.add_argument("--same-samples", action="store_true"); ap.add_argument("--variant", default="full")
+    ap.add_argument("--convex", action="store_true", help="undisplaced sphere"); ap.add_argument("--flat", action="store_true", help="no vertex normals")
+    ap.add_argument("--sphere-res", type=int, default=100)
     a = ap.parse_args()
     r = run(a.res, a.spp, a.passes, a.fd_spp, a.texels, a.vertex_coords, log=None if a.quiet else lambda s: print(s, file=sys.stderr, flush=True),
-            max_depth=a.max_depth, boundary=a.boundary, edge_fraction=a.edge_fraction, rr_off=a.rr_off, same_samples=a.same_samples, variant=a.variant)
+            max_depth=a.max_depth, boundary=a.boundary, edge_fraction=a.edge_fraction, rr_off=a.rr_off, same_samples=a.same_samples, variant=a.variant, displace=not a.convex, smooth=not a.flat,
+            sphere=(a.sphere_res, a.sphere_res))
     print(json.dumps(r))
