@@ -202,10 +202,11 @@ def parity_gates(mi, local):
     try:
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import c4_fd_check
-        r = c4_fd_check.run(res=512, spp=64, passes=1, fd_spp=1024, n_tex=16, n_vtx=0, eps_list=(0.5,), device=local, same_samples=True)
+        r = c4_fd_check.run(res=512, spp=64, passes=1, fd_spp=1024, n_tex=16, n_vtx=0, eps_list=(0.25, 0.5), device=local, same_samples=True)
         g["c4_512x512_fd"] = {"texture_rel_l2": r["texture"]["rel_l2"], "texture_cosine": r["texture"]["cosine"],
-                              "vertex_fields_rel_l2": r["vertex_fields_rel_l2"],
-                              "vertex_fields": {k: {"adjoint": v["adjoint"], "fd": v["fd_by_eps"]["0.5"][0]} for k, v in r["vertex_fields"].items()},
+                              "vertex_fields_rel_l2": r.get("vertex_fields_rel_l2_richardson", r["vertex_fields_rel_l2"]),
+                              "vertex_fields": {k: {"adjoint": v["adjoint"], "fd": v.get("fd_richardson", v["fd_by_eps"]["0.5"][0])} for k, v in r["vertex_fields"].items()},
+                              "fd": "central differences at 0.25 and 0.5 mean edge lengths, Richardson-extrapolated",
                               "fd_spp": 1024, "same_samples": True}
     except Exception as e:
         g["c4_fd_error"] = repr(e)

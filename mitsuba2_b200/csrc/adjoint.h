@@ -423,6 +423,13 @@ HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j) {
     if (!(s.len > 0.f)) return s;
     s.t = u2; s.px = ax + u2 * (bx - ax); s.py = ay + u2 * (by - ay);
     s.nx = (ay - by) / s.len; s.ny = (bx - ax) / s.len;            // grad_xy(alpha) / |grad_xy(alpha)|
+    // KNOWN GAP (measured): on a smooth-shaded mesh with a one-sided BSDF the image is black where the
+    // INTERPOLATED normal looks away from the camera (Frame::cos_theta(si.wi) <= 0 in the shading frame), which leaves a dark
+    // rim, thinner than a pixel, between a silhouette edge and the shading-normal terminator inside the front face.  The
+    // terminator is a film-space discontinuity of its own that moves with the mesh and is NOT sampled: the pair below sees
+    // (rim - outside) where the rim exists.  Two fixes were tried and measured worse: sampling the terminator chord as an
+    // extra boundary double-counts wherever the rim is thinner than the pair's spacing (+50 % on the silhouette band of the
+    // C4 sphere); moving the inner sample beyond the rim picks up limb darkening (radiance ~ sqrt(distance from the limb)).
     s.valid = s.px >= 0.f && s.py >= 0.f && s.px < (float) e.width && s.py < (float) e.height;
     return s;
 }
@@ -475,11 +482,12 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
 // from the occluding face, x2 = first hit of the ray just outside the edge (r2 = its distance; infinite for a miss),
 // L_far = full incident radiance along that ray (path-traced by the normal wavefront from depth 2, emitter hits unweighted).
 // Edges are drawn by resampling: `candidates` edges proportional to their 3D length, one of those that are silhouettes from
-// x1 kept uniformly, P = (len / total) * candidates / (silhouette candidates).  Covers moving shadow boundaries and occlusion
+// x1 kept with probability proportional to its angular length / r, P = (len / total) * candidates * w_chosen / sum(w).  Covers moving shadow boundaries and occlusion
 // of indirect light as seen directly by the camera; deeper vertices are not sampled.
 struct Edge2Ctx {
     const uint4 *edges; uint32_t n_edges; const float *cdf; float total_len;   // cdf over 3D edge lengths
     int candidates; float eps;                                                 // eps: angular offset of the far ray
+    int moving_mesh;                                                           // the differentiated mesh (see edge2_raygen_body)
     float4 *aux;                     // 4 x float4 per sample: (edge, t, |dw/dt| / P, valid) | x2 (prim, b1, b2, r2) | d | hit of x1
 };
 HD float edge_len3_body(const SceneDev &sc, const Edge2Ctx &e, uint32_t k) {
@@ -522,18 +530,32 @@ HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBat
     bool ok = si.valid && e.n_edges > 0 && e.total_len > 0.f;
     BsdfDev bsdf;
     if (ok) { bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf]; ok = bsdf.type != 2 && (bsdf.two_sided ? si.wi.z != 0.f : si.wi.z > 0.f); }
-    uint32_t chosen = 0, n_sil = 0;
+    // Resampled importance sampling over the candidates: a silhouette candidate is kept with probability proportional to
+    // w = (angular length of the edge seen from x1) / r -- the factor the integrand grows with for near edges -- and the
+    // estimate is weighted by sum(w) / (candidates * w_chosen).
+    // Edges of the mesh x1 itself lies on are skipped when that mesh is the differentiated one: the self-occlusion of a
+    // bumpy surface seen from a point ON it has edges at every distance down to 0, the integrand grows like len / r^2 and a
+    // length-proportional edge pick has infinite variance there (measured at C4: the standard error of the sphere's own
+    // pixels went from 0.03 to 4 with this term).  Documented bias: the change of a mesh's shadow on ITSELF is not sampled.
+    uint32_t chosen = 0, n_sil = 0; float w_sum = 0.f, w_chosen = 0.f;
+    const bool x1_on_moving = ok && si.mesh == e.moving_mesh;
     for (int c = 0; c < e.candidates; ++c) {          // same number of draws whatever happens: the stream stays aligned
         float u = rng.next_f32(), pick = rng.next_f32();
         if (!ok) continue;
         float value = u * e.total_len; const float *cdf = e.cdf;
         uint32_t k = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
-        if (!edge2_geo(sc, e.edges[k], 0.5f, si.p).silhouette) continue;
-        n_sil++;
-        if (pick * (float) n_sil < 1.f) chosen = k;      // reservoir: keeps each silhouette candidate with equal probability
+        uint4 ek = e.edges[k];
+        if (ek.z == si.prim || ek.w == si.prim) continue;                 // edges of x1's own face lie in its tangent plane
+        if (x1_on_moving && (int) sc.faces[ek.z].w == si.mesh) continue;
+        Edge2Geo gk = edge2_geo(sc, ek, 0.5f, si.p);
+        if (!gk.silhouette) continue;
+        float w = gk.dwdt / gk.r;
+        if (!(w > 0.f) || !(w < 1e30f)) continue;
+        n_sil++; w_sum += w;
+        if (pick * w_sum < w) { chosen = k; w_chosen = w; }      // weighted reservoir
     }
     float t = rng.next_f32();
-    if (ok && n_sil > 0) {
+    if (ok && n_sil > 0 && w_chosen > 0.f) {
         uint4 ed = e.edges[chosen];
         Edge2Geo g = edge2_geo(sc, ed, t, si.p);
         float len = norm(g.b - g.a);
@@ -545,7 +567,7 @@ HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBat
             float3 wf = normalize(g.w + g.n_out * e.eps);
             bool hit2 = bvh_trace<false>(sc.bvh, si.p, wf, mint, INFINITY, st, h);
             if (!hit2 || h.t > g.r * (1.f - 1e-3f)) {     // the ray really passes the edge
-                float inv_p = (e.total_len / len) * ((float) n_sil / (float) e.candidates);
+                float inv_p = (e.total_len / len) * (w_sum / ((float) e.candidates * w_chosen));
                 rec0 = make_float4(u2f(chosen), t, g.dwdt * inv_p, 1.f);
                 if (hit2) rec1 = make_float4(u2f(h.prim), h.u, h.v, h.t);
                 ro = mk4(si.p, mint); rd = mk4(wf, INFINITY);

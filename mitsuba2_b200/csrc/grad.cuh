@@ -196,7 +196,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
             if (s->grad_boundary >= 2) {
                 Edge2Launch l2; Edge2Ctx &e2 = l2.e;
                 RC(all_edge_list(s, &e2.edges, &e2.n_edges));
-                e2.candidates = 16; e2.eps = 1e-3f; e2.total_len = 0.f;
+                e2.candidates = 32; e2.eps = 1e-3f; e2.total_len = 0.f; e2.moving_mesh = mesh_id;
                 DevBuf<float> len3, cdf3; DevBuf<unsigned char> tmp2;
                 CU(len3.alloc(e2.n_edges)); CU(cdf3.alloc(e2.n_edges));
                 k_edge_len3<<<grid_for(e2.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;

@@ -183,3 +183,28 @@ def test_vertex_gradient_texture_sliding_matches_fd():
     assert abs(fds["tx"]) > 0.02 * ref and abs(fds["ty"]) > 0.02 * ref              # the sliding term is not negligible here
     for n, fd in fds.items():
         assert abs(float((g * F[n]).sum()) - fd) < 0.02 * ref, (n, float((g * F[n]).sum()), fd)
+
+
+def test_vertex_gradient_smooth_sphere_silhouette_known_gap():
+    """A coarse smooth-shaded sphere lit from the camera's side on black: interior term + silhouette edge sampling.  The
+    scale derivative is within 5 % of Richardson-extrapolated finite differences of the oracle; the translations are off by
+    < 1 % of that magnitude.  The residual is the one documented in adjoint.h / DESIGN.md 4b: the dark rim between the
+    silhouette and the shading-normal terminator (one-sided BSDF under interpolated normals) is a discontinuity that moves
+    with the mesh and is not sampled.  This test pins the size of that gap."""
+    sd = H.vgrad_scene("smoothsphere", "diffuse", res=32, spp=64)
+    yy, xx = np.mgrid[0:32, 0:32]
+    wgt = np.stack([0.5 + xx / 32, 0.5 + yy / 32, 1.0 + 0 * xx], -1).astype(np.float32)
+    h = HostSim(sd)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    g = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=1, edge_fraction=1.0).reshape(-1, 3) for s_ in range(3, 7)], axis=0)
+    fd = {}
+    for n in ("tx", "ty", "scale"):
+        f1 = H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.005, 1024, 3)
+        f2 = H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.01, 1024, 3)
+        fd[n] = f1 + (f1 - f2) / 3
+    an = {n: float((g * F[n]).sum()) for n in fd}
+    assert abs(an["scale"] - fd["scale"]) < 0.05 * abs(fd["scale"]), (an, fd)
+    assert abs(an["tx"] - fd["tx"]) < 0.012 * abs(fd["scale"]) and abs(an["ty"] - fd["ty"]) < 0.012 * abs(fd["scale"]), (an, fd)
+    g0 = h.render_grad_vertices(wgt, 0, seed=3, boundary=0, edge_fraction=1.0).reshape(-1, 3)
+    assert abs(float((g0 * F["scale"]).sum()) - fd["scale"]) > 0.1 * abs(fd["scale"])      # the silhouette term matters here
