@@ -392,11 +392,70 @@ HD bool edge_project(const EdgeCtx &e, float3 v, float &x, float &y, float &hw) 
     x = hx / hw * (float) e.width; y = hy / hw * (float) e.height;
     return true;
 }
+// ---- shading-normal terminator of a smooth-shaded face --------------------------------------------------------------------
+// A one-sided BSDF is black where the INTERPOLATED normal looks away from the camera (Frame::cos_theta(si.wi) <= 0 in the
+// shading frame, e.g. diffuse.cpp:95-103), which happens on front-facing triangles next to every silhouette and on the flanks
+// of bumps.  The curve  g(b) = n_s(b) . (p(b) - cam) = 0  inside such a triangle is a jump of the image (lit | exactly black)
+// that moves with the mesh: a film-space boundary like a silhouette edge, but not a mesh edge.  Entry k of the edge list with
+// edges[k].y == kTermTag stands for the terminator of face edges[k].x.  Its end points are the roots of g (a quadratic) on
+// two of the triangle's edges -- the same function the silhouette pairs use to decide whether the rim reaches a mesh edge, so
+// the two kinds of samples partition the jumps exactly -- the chord between them is sampled like an edge, the jump is the
+// radiance of the lit side evaluated AT the point (path.h: the face is shaded as if lit; no pair of offset rays, so the
+// chord's distance from the true curve does not matter), and the curve moves with the material (barycentric mix of the
+// three vertex displacements; its slip over the material is along the line of sight and does not show on the film).
+constexpr uint32_t kTermTag = 0xfffffffeu;
+HD bool term_bsdf(const SceneDev &sc, const MeshDev &m) {      // does this mesh have a terminator at all?
+    if (!m.has_normals || m.emitter >= 0) return false;
+    const BsdfDev b = sc.bsdfs[m.bsdf];
+    return !b.two_sided && b.type != 2 && b.type != 5 && b.opacity < 0;
+}
+struct TermSeg { float3 qa, qb, lit; float wa[3], wb[3]; uint4 f; bool valid; };      // lit = a vertex on the lit side
+HD TermSeg term_segment(const SceneDev &sc, float3 cam_o, uint32_t prim) {
+    TermSeg t; t.valid = false; t.qa = t.qb = t.lit = mk3(0.f);
+    for (int i = 0; i < 3; ++i) t.wa[i] = t.wb[i] = 0.f;
+    uint4 f = sc.faces[prim]; t.f = f;
+    const MeshDev m = sc.meshes[f.w];
+    if (!term_bsdf(sc, m)) return t;
+    float3 v[3] = { ld3(sc.pos, f.x), ld3(sc.pos, f.y), ld3(sc.pos, f.z) };
+    float3 n[3] = { ld3(sc.nrm, f.x), ld3(sc.nrm, f.y), ld3(sc.nrm, f.z) };
+    if (!(dot(cross(v[1] - v[0], v[2] - v[0]), v[0] - cam_o) < 0.f)) return t;      // back-facing triangles are not seen
+    float c[3] = { dot(n[0], v[0] - cam_o), dot(n[1], v[1] - cam_o), dot(n[2], v[2] - cam_o) };
+    int found = 0;
+    for (int i = 0; i < 3 && found < 2; ++i) {
+        int j = (i + 1) % 3;
+        if ((c[i] < 0.f) == (c[j] < 0.f)) continue;
+        // g(s) = (n_i + s dn) . (P_i + s dv) on the edge i -> j: root near the linear estimate, two Newton steps
+        float3 dn = n[j] - n[i], dv = v[j] - v[i], Pi = v[i] - cam_o;
+        float A = dot(dn, dv), B = dot(n[i], dv) + dot(dn, Pi), C = c[i];
+        float sroot = C / (C - c[j]);
+        for (int it = 0; it < 2; ++it) { float gs = (A * sroot + B) * sroot + C, dg = 2.f * A * sroot + B; if (dg != 0.f) sroot -= gs / dg; }
+        sroot = fminf(fmaxf(sroot, 0.f), 1.f);
+        float *w = found == 0 ? t.wa : t.wb;
+        w[i] = 1.f - sroot; w[j] = sroot;
+        if (found == 0) t.qa = v[i] + dv * sroot; else t.qb = v[i] + dv * sroot;
+        found++;
+    }
+    t.lit = c[0] < 0.f ? v[0] : (c[1] < 0.f ? v[1] : v[2]);
+    t.valid = found == 2;
+    return t;
+}
+// does the dark rim reach the point a + t (b - a) of a mesh edge?  (same g as above, on that edge)
+HD bool edge_point_dark(const SceneDev &sc, float3 cam_o, uint4 ed, float t) {
+    float3 a = ld3(sc.pos, ed.x), b = ld3(sc.pos, ed.y), na = ld3(sc.nrm, ed.x), nb = ld3(sc.nrm, ed.y);
+    return dot(na + (nb - na) * t, a + (b - a) * t - cam_o) >= 0.f;
+}
+
 // sampling weight of an edge = projected length.  A smooth-shaded mesh (vertex normals) is discontinuous on the film only
 // along its silhouette -- edges whose two faces look opposite ways from the camera, and border edges -- so the others get
 // weight 0; a flat-shaded mesh also jumps across every edge that has a front-facing side.
 HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, float3 cam_o, uint32_t k) {
     uint4 ed = e.edges[k]; float ax, ay, aw, bx, by, bw;
+    if (ed.y == kTermTag) {
+        TermSeg ts = term_segment(sc, cam_o, ed.x);
+        if (!ts.valid || !edge_project(e, ts.qa, ax, ay, aw) || !edge_project(e, ts.qb, bx, by, bw)) return 0.f;
+        float lt = sqrtf(sqr(ax - bx) + sqr(ay - by));
+        return lt < 1e30f ? lt : 0.f;
+    }
     float3 va = ld3(sc.pos, ed.x);
     if (!edge_project(e, va, ax, ay, aw) || !edge_project(e, ld3(sc.pos, ed.y), bx, by, bw)) return 0.f;
     if (ed.w != 0xffffffffu) {
@@ -407,42 +466,49 @@ HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, float3 cam_o, uint3
     float l = sqrtf(sqr(ax - bx) + sqr(ay - by));
     return l < 1e30f ? l : 0.f;
 }
-struct EdgeSample { uint32_t edge; float t, px, py, nx, ny, len; float3 va, vb; bool valid; Pcg32 rng; };
-HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j) {
+struct EdgeSample { uint32_t edge; float t, px, py, nx, ny, len; float3 va, vb; bool valid; Pcg32 rng;
+                    bool term, lit_plus; uint32_t vid[3]; float vw[3]; };      // terminator sample: lit side at +n?, the face's vertices, weights
+HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j, float3 cam_o) {
     EdgeSample s; s.valid = false; s.edge = 0; s.t = 0.f; s.px = s.py = s.nx = s.ny = s.len = 0.f; s.va = s.vb = mk3(0.f);
+    s.term = s.lit_plus = false; for (int i = 0; i < 3; ++i) { s.vid[i] = 0; s.vw[i] = 0.f; }
+    float3 lit = mk3(0.f);
     s.rng = sampler_seed(e.seed ^ 0x9e3779b97f4a7c15ull, (uint32_t) (e.first + j));
     float u1 = s.rng.next_f32(), u2 = s.rng.next_f32(); (void) s.rng.next_f32();
     if (!(e.total_len > 0.f) || e.n_edges == 0) return s;
     float value = u1 * e.total_len; const float *cdf = e.cdf;
     s.edge = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
     uint4 ed = e.edges[s.edge];
-    s.va = ld3(sc.pos, ed.x); s.vb = ld3(sc.pos, ed.y);
+    if (ed.y == kTermTag) {
+        TermSeg ts = term_segment(sc, cam_o, ed.x);
+        if (!ts.valid) return s;
+        s.term = true; s.va = ts.qa; s.vb = ts.qb; lit = ts.lit;
+        s.vid[0] = ts.f.x; s.vid[1] = ts.f.y; s.vid[2] = ts.f.z;
+        for (int i = 0; i < 3; ++i) s.vw[i] = (1.f - u2) * ts.wa[i] + u2 * ts.wb[i];
+    } else { s.va = ld3(sc.pos, ed.x); s.vb = ld3(sc.pos, ed.y); }
     float ax, ay, aw, bx, by, bw;
     if (!edge_project(e, s.va, ax, ay, aw) || !edge_project(e, s.vb, bx, by, bw)) return s;
     s.len = sqrtf(sqr(ax - bx) + sqr(ay - by));
     if (!(s.len > 0.f)) return s;
     s.t = u2; s.px = ax + u2 * (bx - ax); s.py = ay + u2 * (by - ay);
     s.nx = (ay - by) / s.len; s.ny = (bx - ax) / s.len;            // grad_xy(alpha) / |grad_xy(alpha)|
-    // KNOWN GAP (measured): on a smooth-shaded mesh with a one-sided BSDF the image is black where the
-    // INTERPOLATED normal looks away from the camera (Frame::cos_theta(si.wi) <= 0 in the shading frame), which leaves a dark
-    // rim, thinner than a pixel, between a silhouette edge and the shading-normal terminator inside the front face.  The
-    // terminator is a film-space discontinuity of its own that moves with the mesh and is NOT sampled: the pair below sees
-    // (rim - outside) where the rim exists.  Two fixes were tried and measured worse: sampling the terminator chord as an
-    // extra boundary double-counts wherever the rim is thinner than the pair's spacing (+50 % on the silhouette band of the
-    // C4 sphere); moving the inner sample beyond the rim picks up limb darkening (radiance ~ sqrt(distance from the limb)).
+    if (s.term) { float lx, ly, lw; if (!edge_project(e, lit, lx, ly, lw)) return s; s.lit_plus = (lx - ax) * s.nx + (ly - ay) * s.ny > 0.f; }
     s.valid = s.px >= 0.f && s.py >= 0.f && s.px < (float) e.width && s.py < (float) e.height;
     return s;
 }
 // two primary rays per boundary sample: 2j on the alpha > 0 side, 2j+1 on the other, same random-number stream
 HD void edge_raygen_body(const SceneDev &sc, const SensorDev &sn, const EdgeCtx &e, const RenderBatch &b, const PathQueue &q, uint32_t j) {
-    EdgeSample s = edge_sample(sc, e, j);
-    if (!s.valid) { s.px = 0.5f * (float) e.width; s.py = 0.5f * (float) e.height; s.nx = 1.f; s.ny = 0.f; }
+    EdgeSample s = edge_sample(sc, e, j, mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]));
+    if (!s.valid) { s.px = 0.5f * (float) e.width; s.py = 0.5f * (float) e.height; s.nx = 1.f; s.ny = 0.f; s.term = false; }
     for (uint32_t side = 0; side < 2; ++side) {
-        uint32_t i = 2 * j + side; float sg = side == 0 ? e.eps : -e.eps;
+        uint32_t i = 2 * j + side; float sg = s.term ? 0.f : (side == 0 ? e.eps : -e.eps);
         float4 o, d;
         sensor_sample_ray(sn, (s.px + sg * s.nx) / (float) sn.width, (s.py + sg * s.ny) / (float) sn.height, o, d);
+        // terminator sample: ONE path through the point itself, tagged with the face it must see (path.h shades it as lit);
+        // the second slot of the pair is not used (a ray of zero length)
+        uint32_t tag = s.term && side == 0 ? e.edges[s.edge].x + 1u : 0u;
+        if (s.term && side == 1) d.w = 0.f;
         q.o_mint[i] = o; q.d_maxt[i] = d; q.thr_eta[i] = make_float4(1.f, 1.f, 1.f, 1.f);
-        q.misc[i] = make_uint4(i, 1u, f2u(0.f), 0u);
+        q.misc[i] = make_uint4(i, 1u, f2u(0.f), tag);
         rng_store(&q.rng[i], s.rng);
         b.result[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
@@ -450,16 +516,46 @@ HD void edge_raygen_body(const SceneDev &sc, const SensorDev &sn, const EdgeCtx 
 // dPhi = (1/N) sum  dL/dI(pixel) . (L+ - L-) * grad_v(alpha) * total_len / len,  alpha = edge function through a, b
 template <typename Add>
 HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g, const float4 *result, uint32_t j, Add add) {
-    EdgeSample s = edge_sample(sc, e, j);
+    EdgeSample s = edge_sample(sc, e, j, g.cam_o);
     if (!s.valid) return;
     float4 lp = result[2 * j], lm = result[2 * j + 1];
+    uint4 ed = e.edges[s.edge];
+    const float *m = e.w2s;
+    if (s.term) {       // jump = radiance of the lit side (slot 0) against exactly 0
+        if (s.lit_plus) lm = make_float4(0.f, 0.f, 0.f, 0.f); else { lm = lp; lp = make_float4(0.f, 0.f, 0.f, 0.f); }
+    } else if (term_bsdf(sc, sc.meshes[sc.faces[ed.z].w])) {
+        // Smooth-shaded, one-sided: where the dark rim reaches this point of the edge the mesh side of the jump is exactly 0,
+        // whatever the offset ray 0.004 px inside happens to see (it may already be beyond a rim thinner than that, and
+        // that jump belongs to the terminator samples).  Mesh side = the side of the front face's third vertex.
+        if (edge_point_dark(sc, g.cam_o, ed, s.t)) {
+            uint32_t front = ed.z;
+            if (ed.w != 0xffffffffu && !(dot(tri_geo(sc, ed.z).N, s.va - g.cam_o) < 0.f)) front = ed.w;
+            uint4 ff = sc.faces[front];
+            uint32_t third = (ff.x != ed.x && ff.x != ed.y) ? ff.x : ((ff.y != ed.x && ff.y != ed.y) ? ff.y : ff.z);
+            float tx, ty, tw, ax, ay, aw;
+            if (edge_project(e, ld3(sc.pos, third), tx, ty, tw) && edge_project(e, s.va, ax, ay, aw)) {
+                if ((tx - ax) * s.nx + (ty - ay) * s.ny > 0.f) lp = make_float4(0.f, 0.f, 0.f, 0.f); else lm = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    }
     uint32_t pixel = (uint32_t) s.py * e.width + (uint32_t) s.px;
     float3 dI = ld3(g.dL_dimage, pixel);
     float sc_ = (dI.x * (lp.x - lm.x) + dI.y * (lp.y - lm.y) + dI.z * (lp.z - lm.z)) * e.weight * e.total_len;
     if (sc_ == 0.f || !(fabsf(sc_) < 1e30f)) return;
+    if (s.term) {
+        // the sample point p = sum_i w_i v_i moves with the material: displacement along the chord's film normal =
+        // n . J(p) . sum_i w_i dv_i; sc_ carries total_len = (chord length) / (pick probability per unit t)
+        float3 p = s.va + (s.vb - s.va) * s.t; float x, y, hw;
+        if (!edge_project(e, p, x, y, hw)) return;
+        float sx = x / (float) e.width, sy = y / (float) e.height, W = (float) e.width / hw, H = (float) e.height / hw;
+        float gx = -sc_ * s.nx, gy = -sc_ * s.ny;
+        float3 gp = mk3(gx * W * (m[0] - sx * m[12]) + gy * H * (m[4] - sy * m[12]),
+                        gx * W * (m[1] - sx * m[13]) + gy * H * (m[5] - sy * m[13]),
+                        gx * W * (m[2] - sx * m[14]) + gy * H * (m[6] - sy * m[14]));
+        for (int i = 0; i < 3; ++i) add_vertex(g, s.vid[i], gp * s.vw[i], add);
+        return;
+    }
     // grad_a(alpha) = -(1 - t) len n, grad_b(alpha) = -t len n; the 1/len of the edge pick cancels len
-    uint4 ed = e.edges[s.edge];
-    const float *m = e.w2s;
     for (int k = 0; k < 2; ++k) {
         float3 v = k == 0 ? s.va : s.vb; float wgt = -(k == 0 ? 1.f - s.t : s.t) * sc_;
         float gx = wgt * s.nx, gy = wgt * s.ny, x, y, hw;

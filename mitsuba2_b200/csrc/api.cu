@@ -686,9 +686,10 @@ static PathQueue make_queue(mtsb_scene *s, int k) {
 // One batch of the wavefront: raygen -> [closest -> shade -> shadow]* .  `grad` != null selects the adjoint replay
 // (k_shade_grad scatters texel gradients); `splat` adds the finished paths to the film.
 // the shade kernel has four instances: colour mode x (lean | with the N4 plugins: conductor, plastic, rough dielectric, mask)
+// (boundary passes of the gradient, `edge` != null, always take the X instance: it honours the terminator tag of path.h)
 #define LAUNCH_SHADE(grid, ...) do { \
     if (s->spectral) { if (s->ext) k_shade<SpectralX><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); else k_shade<Spectral><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); } \
-    else { if (s->ext) k_shade<RgbX><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); else k_shade<Rgb><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); } } while (0)
+    else { if (s->ext || edge != nullptr) k_shade<RgbX><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); else k_shade<Rgb><<<(grid), kBlock, 0, st>>>(__VA_ARGS__); } } while (0)
 struct EdgeLaunch { EdgeCtx e; const float *total_len; };     // primary rays come from edge samples instead of the film
 struct Edge2Launch { Edge2Ctx e; const float *total_len; };   // depth-2 rays come from edge samples seen from the primary hits
 static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, const GradCtx *grad, bool splat, uint64_t &launches,

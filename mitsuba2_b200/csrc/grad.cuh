@@ -50,6 +50,9 @@ static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint4 **edges, uint3
         const MeshDev &m = s->meshes[mesh_id];
         std::vector<uint4> e;
         build_edge_list(s->mesh_faces[mesh_id].data(), m.face_count, m.vert_begin, m.face_begin, e);
+        // a smooth-shaded mesh also jumps along the shading-normal terminator inside its faces (adjoint.h, kTermTag): one
+        // candidate entry per face, given a length only where the curve exists from the current viewpoint
+        if (m.has_normals) for (uint32_t f = 0; f < m.face_count; ++f) e.push_back(make_uint4(m.face_begin + f, kTermTag, m.face_begin + f, m.face_begin + f));
         std::unique_ptr<DevBuf<uint4>> buf(new DevBuf<uint4>());
         CU(buf->upload(e.data(), e.size(), s->ctx->stream));
         CU(cudaStreamSynchronize(s->ctx->stream));

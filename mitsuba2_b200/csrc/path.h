@@ -12,7 +12,7 @@ struct PathQueue {
     float4 *o_mint, *d_maxt;   // extension ray
     float4 *hit;               // closest-hit result for that ray (t,u,v,prim)
     float4 *thr_eta;           // throughput rgb, eta
-    uint4  *misc;              // path_id, depth | (prev_delta << 31), prev bsdf pdf (bits), unused
+    uint4  *misc;              // path_id, depth | (prev_delta << 31), prev bsdf pdf (bits), depth 1 only: terminator face + 1 (else 0)
     uint4  *rng;               // PCG32 state lo/hi, inc lo/hi
     float2 *wav_eta;           // spectral mode only (+8 B): wavelength sample of the path, eta; thr_eta then holds 4 channels
     float4 *prev1, *prev2;     // vertex-gradient replay only (else null): the two previous path vertices
@@ -168,6 +168,15 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
     if (M::spectral) sample_wavelengths(we.x, wav, ray_weight);
     float3 o = xyz(o4), d = xyz(d4);
     SI si = make_si<M::ext>(sc, o, d, h4);
+    if constexpr (M::ext) {
+        // boundary sample on a shading-normal terminator (adjoint.h, kTermTag): misc.w = face + 1.  The path measures the
+        // radiance of the LIT side of that curve: it counts only if the camera ray really sees the face, and the face is
+        // shaded as if its interpolated normal just looked at the camera (the dark side is exactly 0 for a one-sided BSDF)
+        if (depth == 1 && misc.w != 0u) {
+            if (!si.valid || si.prim + 1u != misc.w) return out;
+            si.wi.z = fmaxf(fabsf(si.wi.z), 1e-4f);
+        }
+    }
     bool chain_ok = true;                     // vertex-gradient replay: no delta vertex on the path so far
     if (GradFn::kVertex) {
         float4 p1 = depth > 1 ? q.prev1[i] : make_float4(u2f(0xffffffffu), 0.f, 0.f, u2f(1u));

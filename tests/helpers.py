@@ -677,8 +677,8 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         P2, F2 = grid_mesh(1, 1, 12.0, [0, 0, 2.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P2, F2, bsdf=bw))
         sd.add_constant([1.0, 1.0, 1.0])
-    if kind == "smoothsphere":    # coarse smooth-shaded sphere lit from the camera's side on black: silhouette + the shading-normal terminator rim
-        ms = M.displaced_sphere(10, 20, radius=0.8, center=(0.05, 0.02, 0.3), displace=False)
+    if kind == "smoothsphere":    # smooth-shaded sphere lit from the camera's side on black: silhouette + the shading-normal terminator rim
+        ms = M.displaced_sphere(20, 40, radius=0.8, center=(0.05, 0.02, 0.3), displace=False)
         ms.bsdf, ms.texcoords = b, None
         sd.add_mesh(ms)
         sd.add_point([0.6, 0.8, -3.0], [40, 40, 40])
