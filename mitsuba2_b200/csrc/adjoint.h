@@ -383,6 +383,7 @@ struct EdgeCtx {
     uint64_t seed; uint64_t first;          // global index of this call's first boundary sample
     float weight;                           // 1 / (boundary samples of the whole job)
     float eps;                              // half distance (pixels) between the two radiance samples
+    int rim_override;                       // 1: silhouette pairs take the mesh side as black where the dark rim reaches the edge (default)
 };
 HD bool edge_project(const EdgeCtx &e, float3 v, float &x, float &y, float &hw) {
     const float *m = e.w2s;
@@ -467,10 +468,12 @@ HD float edge_len_body(const SceneDev &sc, const EdgeCtx &e, float3 cam_o, uint3
     return l < 1e30f ? l : 0.f;
 }
 struct EdgeSample { uint32_t edge; float t, px, py, nx, ny, len; float3 va, vb; bool valid; Pcg32 rng;
-                    bool term, lit_plus; uint32_t vid[3]; float vw[3]; };      // terminator sample: lit side at +n?, the face's vertices, weights
+                    bool term, lit_plus; uint32_t vid[3]; float vw[3];         // terminator sample: lit side at +n?, the face's vertices, weights
+                    int rim_side; uint32_t front; };      // silhouette pair whose edge point lies in the dark rim: +1 / -1 = mesh side at +n / -n, front face
 HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j, float3 cam_o) {
     EdgeSample s; s.valid = false; s.edge = 0; s.t = 0.f; s.px = s.py = s.nx = s.ny = s.len = 0.f; s.va = s.vb = mk3(0.f);
     s.term = s.lit_plus = false; for (int i = 0; i < 3; ++i) { s.vid[i] = 0; s.vw[i] = 0.f; }
+    s.rim_side = 0; s.front = 0;
     float3 lit = mk3(0.f);
     s.rng = sampler_seed(e.seed ^ 0x9e3779b97f4a7c15ull, (uint32_t) (e.first + j));
     float u1 = s.rng.next_f32(), u2 = s.rng.next_f32(); (void) s.rng.next_f32();
@@ -492,6 +495,19 @@ HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j, floa
     s.t = u2; s.px = ax + u2 * (bx - ax); s.py = ay + u2 * (by - ay);
     s.nx = (ay - by) / s.len; s.ny = (bx - ax) / s.len;            // grad_xy(alpha) / |grad_xy(alpha)|
     if (s.term) { float lx, ly, lw; if (!edge_project(e, lit, lx, ly, lw)) return s; s.lit_plus = (lx - ax) * s.nx + (ly - ay) * s.ny > 0.f; }
+    else if (e.rim_override && term_bsdf(sc, sc.meshes[sc.faces[ed.z].w]) && edge_point_dark(sc, cam_o, ed, u2)) {
+        // Smooth-shaded, one-sided: the dark rim reaches this point of the edge, so the mesh side of the jump AT the edge is
+        // exactly 0 -- whatever the offset ray 0.004 px inside sees of the front face (it may already be beyond a rim thinner
+        // than that, and that jump belongs to the terminator samples).  edge_raygen_body tags the ray on the mesh side as
+        // black (path.h) -- and both rays when the edge point is hidden from the camera, so that hidden edges still cancel.
+        // Mesh side = the side of the front face's third vertex.
+        uint32_t front = ed.z;
+        if (ed.w != 0xffffffffu && !(dot(tri_geo(sc, ed.z).N, s.va - cam_o) < 0.f)) front = ed.w;
+        uint4 ff = sc.faces[front];
+        uint32_t third = (ff.x != ed.x && ff.x != ed.y) ? ff.x : ((ff.y != ed.x && ff.y != ed.y) ? ff.y : ff.z);
+        float tx, ty, tw;
+        if (edge_project(e, ld3(sc.pos, third), tx, ty, tw)) { s.rim_side = (tx - ax) * s.nx + (ty - ay) * s.ny > 0.f ? 1 : -1; s.front = front; }
+    }
     s.valid = s.px >= 0.f && s.py >= 0.f && s.px < (float) e.width && s.py < (float) e.height;
     return s;
 }
@@ -499,6 +515,14 @@ HD EdgeSample edge_sample(const SceneDev &sc, const EdgeCtx &e, uint32_t j, floa
 HD void edge_raygen_body(const SceneDev &sc, const SensorDev &sn, const EdgeCtx &e, const RenderBatch &b, const PathQueue &q, uint32_t j) {
     EdgeSample s = edge_sample(sc, e, j, mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]));
     if (!s.valid) { s.px = 0.5f * (float) e.width; s.py = 0.5f * (float) e.height; s.nx = 1.f; s.ny = 0.f; s.term = false; }
+    bool black[2] = { false, false };
+    if (!s.term && s.valid && s.rim_side != 0) {
+        float3 cam = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
+        float3 dir = s.va + (s.vb - s.va) * s.t - cam; float dist = norm(dir); dir = dir / dist;
+        uint2 fast[8]; TravStack<8, 56> st; st.fast = fast; st.stride = 1; Hit h;
+        bool hidden = bvh_trace<true>(sc.bvh, cam, dir, 1e-4f * dist, dist * (1.f - 1e-4f), st, h);
+        black[0] = hidden || s.rim_side > 0; black[1] = hidden || s.rim_side < 0;
+    }
     for (uint32_t side = 0; side < 2; ++side) {
         uint32_t i = 2 * j + side; float sg = s.term ? 0.f : (side == 0 ? e.eps : -e.eps);
         float4 o, d;
@@ -506,6 +530,7 @@ HD void edge_raygen_body(const SceneDev &sc, const SensorDev &sn, const EdgeCtx 
         // terminator sample: ONE path through the point itself, tagged with the face it must see (path.h shades it as lit);
         // the second slot of the pair is not used (a ray of zero length)
         uint32_t tag = s.term && side == 0 ? e.edges[s.edge].x + 1u : 0u;
+        if (black[side]) tag = 0xffffffffu;
         if (s.term && side == 1) d.w = 0.f;
         q.o_mint[i] = o; q.d_maxt[i] = d; q.thr_eta[i] = make_float4(1.f, 1.f, 1.f, 1.f);
         q.misc[i] = make_uint4(i, 1u, f2u(0.f), tag);
@@ -523,20 +548,6 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
     const float *m = e.w2s;
     if (s.term) {       // jump = radiance of the lit side (slot 0) against exactly 0
         if (s.lit_plus) lm = make_float4(0.f, 0.f, 0.f, 0.f); else { lm = lp; lp = make_float4(0.f, 0.f, 0.f, 0.f); }
-    } else if (term_bsdf(sc, sc.meshes[sc.faces[ed.z].w])) {
-        // Smooth-shaded, one-sided: where the dark rim reaches this point of the edge the mesh side of the jump is exactly 0,
-        // whatever the offset ray 0.004 px inside happens to see (it may already be beyond a rim thinner than that, and
-        // that jump belongs to the terminator samples).  Mesh side = the side of the front face's third vertex.
-        if (edge_point_dark(sc, g.cam_o, ed, s.t)) {
-            uint32_t front = ed.z;
-            if (ed.w != 0xffffffffu && !(dot(tri_geo(sc, ed.z).N, s.va - g.cam_o) < 0.f)) front = ed.w;
-            uint4 ff = sc.faces[front];
-            uint32_t third = (ff.x != ed.x && ff.x != ed.y) ? ff.x : ((ff.y != ed.x && ff.y != ed.y) ? ff.y : ff.z);
-            float tx, ty, tw, ax, ay, aw;
-            if (edge_project(e, ld3(sc.pos, third), tx, ty, tw) && edge_project(e, s.va, ax, ay, aw)) {
-                if ((tx - ax) * s.nx + (ty - ay) * s.ny > 0.f) lp = make_float4(0.f, 0.f, 0.f, 0.f); else lm = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
     }
     uint32_t pixel = (uint32_t) s.py * e.width + (uint32_t) s.px;
     float3 dI = ld3(g.dL_dimage, pixel);

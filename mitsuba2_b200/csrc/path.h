@@ -172,8 +172,9 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
         // boundary sample on a shading-normal terminator (adjoint.h, kTermTag): misc.w = face + 1.  The path measures the
         // radiance of the LIT side of that curve: it counts only if the camera ray really sees the face, and the face is
         // shaded as if its interpolated normal just looked at the camera (the dark side is exactly 0 for a one-sided BSDF)
+        // misc.w = ~0: a silhouette pair's ray that counts as black (the mesh side where the dark rim reaches the edge).
         if (depth == 1 && misc.w != 0u) {
-            if (!si.valid || si.prim + 1u != misc.w) return out;
+            if (misc.w == 0xffffffffu || !si.valid || si.prim + 1u != misc.w) return out;
             si.wi.z = fmaxf(fabsf(si.wi.z), 1e-4f);
         }
     }

@@ -391,7 +391,7 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         i = j;
     }
     if (m.has_normals && !getenv("HS_NO_TERM")) for (uint32_t f = 0; f < m.face_count; ++f) edges.push_back(make_uint4(m.face_begin + f, kTermTag, m.face_begin + f, m.face_begin + f));   // mesh_edge_list()
-    EdgeCtx e; e.edges = edges.data(); e.n_edges = (uint32_t) edges.size(); e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f;
+    EdgeCtx e; e.edges = edges.data(); e.n_edges = (uint32_t) edges.size(); e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f; e.rim_override = getenv("HS_NO_TERM") ? 0 : 1;
     double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
     for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
     std::vector<float> cdf(edges.size()); double acc = 0;
