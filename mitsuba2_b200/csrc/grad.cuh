@@ -8,10 +8,6 @@
 // reference's tape (src/python/python/autodiff.py:6-194, ext/enoki/src/autodiff/autodiff.cpp:838-988).
 #pragma once
 
-__global__ void k_axpy(size_t n, const float *__restrict__ x, float *__restrict__ y) {
-    size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
-    if (i < n) y[i] += x[i];
-}
 
 
 // row-major 4x4 inverse (double), for world -> sample space of a sensor
