@@ -595,6 +595,7 @@ struct Edge2Ctx {
     const uint4 *edges; uint32_t n_edges; const float *cdf; float total_len;   // cdf over 3D edge lengths
     int candidates; float eps;                                                 // eps: angular offset of the far ray
     int moving_mesh;                                                           // the differentiated mesh (see edge2_raygen_body)
+    float self_rmin;                                                           // x1 on that mesh: its own edges nearer than this many edge lengths are skipped
     float4 *aux;                     // 4 x float4 per sample: (edge, t, |dw/dt| / P, valid) | x2 (prim, b1, b2, r2) | d | hit of x1
 };
 HD float edge_len3_body(const SceneDev &sc, const Edge2Ctx &e, uint32_t k) {
@@ -653,9 +654,9 @@ HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBat
         uint32_t k = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
         uint4 ek = e.edges[k];
         if (ek.z == si.prim || ek.w == si.prim) continue;                 // edges of x1's own face lie in its tangent plane
-        if (x1_on_moving && (int) sc.faces[ek.z].w == si.mesh) continue;
         Edge2Geo gk = edge2_geo(sc, ek, 0.5f, si.p);
         if (!gk.silhouette) continue;
+        if (x1_on_moving && (int) sc.faces[ek.z].w == si.mesh && gk.r < e.self_rmin * norm(gk.b - gk.a)) continue;
         float w = gk.dwdt / gk.r;
         if (!(w > 0.f) || !(w < 1e30f)) continue;
         n_sil++; w_sum += w;

@@ -48,7 +48,7 @@ static int mesh_edge_list(mtsb_scene *s, int mesh_id, const uint4 **edges, uint3
         build_edge_list(s->mesh_faces[mesh_id].data(), m.face_count, m.vert_begin, m.face_begin, e);
         // a smooth-shaded mesh also jumps along the shading-normal terminator inside its faces (adjoint.h, kTermTag): one
         // candidate entry per face, given a length only where the curve exists from the current viewpoint
-        if (m.has_normals && !getenv("MTSB_NO_TERM")) for (uint32_t f = 0; f < m.face_count; ++f) e.push_back(make_uint4(m.face_begin + f, kTermTag, m.face_begin + f, m.face_begin + f));
+        if (m.has_normals) for (uint32_t f = 0; f < m.face_count; ++f) e.push_back(make_uint4(m.face_begin + f, kTermTag, m.face_begin + f, m.face_begin + f));
         std::unique_ptr<DevBuf<uint4>> buf(new DevBuf<uint4>());
         CU(buf->upload(e.data(), e.size(), s->ctx->stream));
         CU(cudaStreamSynchronize(s->ctx->stream));
@@ -166,7 +166,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         EdgeLaunch el; EdgeCtx &e = el.e;
         RC(mesh_edge_list(s, mesh_id, &e.edges, &e.n_edges));
         if (e.n_edges > 0) {
-            e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f; e.total_len = 0.f; e.rim_override = getenv("MTSB_NO_RIM_OVERRIDE") ? 0 : 1;
+            e.width = sn.width; e.height = sn.height; e.seed = seed; e.eps = 0.004f; e.total_len = 0.f; e.rim_override = 1;
             double c2w_inv[16], s2c_inv[16]; invert4(sn.to_world, c2w_inv); invert4(sn.sample_to_camera, s2c_inv);
             for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double a = 0; for (int k = 0; k < 4; ++k) a += s2c_inv[4 * r + k] * c2w_inv[4 * k + c]; e.w2s[4 * r + c] = (float) a; }
             DevBuf<float> len, cdf; DevBuf<uint8_t> tmp; size_t tmp_bytes = 0;
@@ -195,7 +195,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
             if (s->grad_boundary >= 2) {
                 Edge2Launch l2; Edge2Ctx &e2 = l2.e;
                 RC(all_edge_list(s, &e2.edges, &e2.n_edges));
-                e2.candidates = 32; e2.eps = 1e-3f; e2.total_len = 0.f; e2.moving_mesh = mesh_id;
+                e2.candidates = 32; e2.eps = 1e-3f; e2.total_len = 0.f; e2.moving_mesh = mesh_id; e2.self_rmin = 1e30f;      // all of them (3 and 8 edge lengths were measured: more noise, same bias)
                 DevBuf<float> len3, cdf3; DevBuf<unsigned char> tmp2;
                 CU(len3.alloc(e2.n_edges)); CU(cdf3.alloc(e2.n_edges));
                 k_edge_len3<<<grid_for(e2.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;

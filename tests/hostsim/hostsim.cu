@@ -426,7 +426,7 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
             i = j;
         }
     }
-    Edge2Ctx e2; e2.edges = all_edges.data(); e2.n_edges = (uint32_t) all_edges.size(); e2.candidates = 32; e2.eps = 1e-3f; e2.moving_mesh = mesh_id;
+    Edge2Ctx e2; e2.edges = all_edges.data(); e2.n_edges = (uint32_t) all_edges.size(); e2.candidates = 32; e2.eps = 1e-3f; e2.moving_mesh = mesh_id; e2.self_rmin = 1e30f;
     std::vector<float> cdf3(all_edges.size()); acc = 0;
     for (uint32_t k = 0; k < e2.n_edges; ++k) { acc += edge_len3_body(s->dev, e2, k); cdf3[k] = (float) acc; }
     e2.cdf = cdf3.data(); e2.total_len = (float) acc;
