@@ -329,6 +329,34 @@ def test_vertex_gradient_boundary_matches_host_replay_and_fd(mi):
     np.testing.assert_allclose(p1 + p2, full, rtol=1e-3, atol=1e-4 * np.abs(full).max())
 
 
+def test_vertex_gradient_smooth_sphere_terminator_matches_host_replay_and_fd(mi):
+    """Smooth-shaded sphere on black: silhouette pairs + shading-normal terminator samples (adjoint.h kTermTag, the tagged
+    paths of path.h run in the RgbX shade instance): GPU vs host simulator on the same samples, and the global fields vs
+    Richardson-extrapolated finite differences of the oracle (bars of tests/test_grad_cpu.py)."""
+    sd = H.vgrad_scene("smoothsphere", "diffuse", res=32, spp=64)
+    yy, xx = np.mgrid[0:32, 0:32]
+    wgt = np.stack([0.5 + xx / 32, 0.5 + yy / 32, 1.0 + 0 * xx], -1).astype(np.float32)
+    sc = mi.Scene(sd)
+    sc.grad_config(boundary=1, edge_fraction=1.0)
+    g = sc.render_grad(wgt, spp=64, seed=3, mesh_id=0)[1].reshape(-1, 3)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=1, edge_fraction=1.0).reshape(-1, 3)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    # same samples on both sides: the fields agree closely (single vertices can differ where a float flip moves one edge sample)
+    for n in ("tx", "ty", "scale"):
+        a, b = float((g * F[n]).sum()), float((gh * F[n]).sum())
+        assert abs(a - b) < 2e-3 * max(abs(float((gh * F["scale"]).sum())), 1.0), (n, a, b)
+    g8 = np.mean([sc.render_grad(wgt, spp=64, seed=s_, mesh_id=0)[1].reshape(-1, 3) for s_ in range(3, 11)], axis=0)
+    fd = {}
+    for n in ("tx", "ty", "scale"):
+        f1 = H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.005, 1024, 3)
+        f2 = H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.01, 1024, 3)
+        fd[n] = f1 + (f1 - f2) / 3
+    an = {n: float((g8 * F[n]).sum()) for n in fd}
+    assert abs(an["scale"] - fd["scale"]) < 0.015 * abs(fd["scale"]), (an, fd)
+    assert abs(an["tx"] - fd["tx"]) < 0.012 * abs(fd["scale"]) and abs(an["ty"] - fd["ty"]) < 0.012 * abs(fd["scale"]), (an, fd)
+
+
 def test_vertex_gradient_shadow_boundary_matches_host_replay_and_fd(mi):
     """Boundary term seen from the first path vertex (moving shadow of a quad on a plane): GPU vs host simulator on the
     same samples, and vs finite differences of the oracle (12 % of the largest derivative)."""
