@@ -48,6 +48,11 @@ def render_torch(scene, texture=None, tex_id=-1, spp=None, seed=0, sensor=0, gro
             ctx.share = (begin, count, total)
             if world > 1:
                 img = scene.render_distributed(sensor, total, seed, group)
+            elif dev.type == "cuda" and dev.index == scene.device:
+                # parameters live on the scene's GPU: the developed image stays there too (no host round trip)
+                scene.film_clear(sensor)
+                scene.render_accumulate(sensor, total, seed, 0, total)
+                return scene.film_develop_tensor(sensor)
             else:
                 img = scene.render(sensor, total, seed)
             return torch.from_numpy(np.ascontiguousarray(img)).to(dev)

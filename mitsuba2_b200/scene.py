@@ -242,6 +242,15 @@ class Scene:
         A.check(A.lib().mtsb_film_develop(self._h, sensor, C.c_void_p(out.ctypes.data), A.MEM_HOST))
         return out
 
+    def film_develop_tensor(self, sensor=0):
+        """`film_develop` into a torch CUDA tensor (H,W,3) on this scene's device: no host round trip (autodiff.render_torch)."""
+        import torch
+        h, w = self._film_shape(sensor)
+        out = torch.empty((h, w, 3), dtype=torch.float32, device=torch.device("cuda", self.device))
+        torch.cuda.current_stream(out.device).synchronize()      # the allocation is torch's, the kernel runs on the library's stream
+        A.check(A.lib().mtsb_film_develop(self._h, sensor, C.c_void_p(out.data_ptr()), A.MEM_DEVICE))
+        return out
+
     def film_device_buffer(self, sensor=0):
         """(device pointer, n_floats) of the packed XYZAW film, for NCCL reduction by the caller."""
         p, n = C.c_void_p(), C.c_uint64()

@@ -387,7 +387,8 @@ def test_vertex_gradient_rejects_unsupported(mi):
 
 
 
-def test_inverse_rendering_recovers_texture_with_adam(mi):
+@pytest.mark.parametrize("where", ["cpu", "cuda"])
+def test_inverse_rendering_recovers_texture_with_adam(mi, where):
     """autodiff.render_torch + torch.optim.Adam (reference: autodiff.py:240-482).  Target and iterates share the seed
     (and Russian roulette is off), so the paths are identical and the L2 loss is a deterministic function of the
     texels: it must drop by a large factor and the texels must move towards the target."""
@@ -396,8 +397,9 @@ def test_inverse_rendering_recovers_texture_with_adam(mi):
     sd, tex = H.textured_cbox(res=32, spp=16, tex_res=4, rr_off=True)
     target_tex = sd.textures[tex]["data"].copy()
     sc = mi.Scene(sd)
-    target = torch.from_numpy(sc.render(spp=16, seed=7).copy())
-    param = torch.full(target_tex.shape, 0.5, dtype=torch.float32, requires_grad=True)
+    # "cuda": parameters, image and gradients stay on the GPU (film_develop_tensor, device-pointer update_texture / render_grad)
+    target = torch.from_numpy(sc.render(spp=16, seed=7).copy()).to(where)
+    param = torch.full(target_tex.shape, 0.5, dtype=torch.float32, device=where, requires_grad=True)
     opt = torch.optim.Adam([param], lr=0.03)
     losses = []
     for it in range(60):
@@ -410,7 +412,7 @@ def test_inverse_rendering_recovers_texture_with_adam(mi):
             param.clamp_(0.01, 0.99)
         losses.append(loss.item())
     assert losses[-1] < 0.05 * losses[0], (losses[0], losses[-1])
-    assert np.abs(param.detach().numpy() - target_tex).mean() < 0.5 * np.abs(0.5 - target_tex).mean()
+    assert np.abs(param.detach().cpu().numpy() - target_tex).mean() < 0.5 * np.abs(0.5 - target_tex).mean()
 
 
 def test_cpp_host_renders_through_the_c_abi(mi, tmp_path):
