@@ -195,6 +195,7 @@ def parity_gates(mi, local):
         g["c2_1M_triangles"] = BP.c2_parity(mi, device=local)
         g["c3_4M_triangles_crop"] = BP.c3_parity(mi, local, run_spp=32, gpu_runs=32, cpu_runs=8)
         g["c4_512x512_primal"] = BP.c4_parity(mi, local)
+        g["c3_4M_triangles_crop_spectral"] = BP.c3_spectral_parity(mi, local)
     except Exception as e:
         g["bench_size_error"] = repr(e)
     # C4 at its own size (512^2, 512^2 x 3 texels, 20k-triangle sphere): adjoint vs central finite differences of the CUDA

@@ -100,6 +100,18 @@ def c3_parity(mi, device=0, run_spp=64, gpu_runs=32, cpu_runs=8):
     return out
 
 
+def c3_spectral_parity(mi, device=0):
+    """C3 crop in the spectral mode (scalar_spectral semantics: 4 wavelengths per path, tabulated Cu eta / k, sRGB-model
+    coefficient textures, D65 emitters): same-stream film of the CUDA path vs the oracle.  Both sides use the small 16^3
+    sRGB-to-spectrum table of the unit tests (the 64^3 one only changes the coefficients both are handed)."""
+    sd = H.spectral(c3_crop_scene())
+    sc, orc = mi.Scene(sd, device=device), H.Oracle(sd)
+    a, b = sc.render(spp=1, seed=9), orc.render(spp=1, seed=9)
+    return {"same_stream_1spp_rel_l1": float(np.abs(a - b).sum() / np.abs(b).sum()),
+            "same_stream_1spp_pixels_within_0.01": float(np.mean(np.all(np.abs(a - b) <= 1e-2 * np.maximum(1.0, np.abs(b)), axis=2))),
+            "mean_rel_diff": float(abs(a.mean() - b.mean()) / b.mean())}
+
+
 def c1_parity(mi, device=0, with_reference=True):
     """C1: cbox 256 x 256 x 64 spp, max_depth 6: same-stream film vs the oracle, z-test vs the committed reference-CLI
     render (4096 spp) and vs a live reference render where the binary is present."""
@@ -165,6 +177,12 @@ def test_c3_film_crop_at_bench_size(mi):
     assert g["same_stream_1spp_pixels_within_0.01"] >= 0.98, g
     assert g["z_test_pass_fraction"] >= 0.9975, g
     assert g["mean_rel_diff"] < 0.01, g
+
+
+def test_c3_spectral_film_crop_at_bench_size(mi):
+    g = c3_spectral_parity(mi)
+    print(g)
+    assert g["same_stream_1spp_rel_l1"] <= 2e-2 and g["same_stream_1spp_pixels_within_0.01"] >= 0.98 and g["mean_rel_diff"] < 5e-3, g
 
 
 def test_c1_cbox_at_bench_size(mi):
