@@ -241,6 +241,17 @@ extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
 }
 
 extern "C" void hs_trav_stats(unsigned long long *out, int reset) { out[0] = g_trav_nodes; out[1] = g_trav_tris; if (reset) g_trav_nodes = g_trav_tris = 0; }
+// histogram of the wide nodes: out[0..8] = nodes with k used slots, out[9..33] = nodes with k leaf triangles, out[34] = internal children
+extern "C" void hs_node_stats(hs_scene *s, unsigned long long *out) {
+    for (int i = 0; i < 35; ++i) out[i] = 0;
+    for (uint32_t w = 0; w < s->bvh_nodes; ++w) {
+        uint4 n0 = s->nodes[5 * (size_t) w], n1 = s->nodes[5 * (size_t) w + 1];
+        uint32_t imask = n0.w >> 24, valid = n1.z;
+        int slots = popc32(imask), tris = popc32(valid);
+        for (int k = 0; k < 8; ++k) if ((valid >> (3 * k)) & 7u) slots++;
+        out[slots]++; out[9 + tris]++; out[34] += (unsigned long long) popc32(imask);
+    }
+}
 extern "C" void hs_bvh_info(hs_scene *s, uint32_t *nodes, uint32_t *depth) { *nodes = s->bvh_nodes; *depth = s->bvh_depth; }
 
 extern "C" void hs_intersect(hs_scene *s, uint64_t n, const float *o, const float *d, float *hits, uint32_t *occ, int any) {
