@@ -142,7 +142,7 @@ def _rel_err(g, c, floor):
     return float(e.max()), float(np.quantile(e, 0.999))
 
 
-# per BSDF type (MTSB_BSDF_*): bars at ~5x the error measured on the B200 (tools/hook_errors.py).  `sample`: (99.9th
+# per BSDF type (MTSB_BSDF_*): bars at ~5x the error measured on the B200 (tests/hook_errors.py).  `sample`: (99.9th
 # percentile, max) -- the max is the rare sample whose Newton solve in sample_visible_11 / whose lobe choice sits on a
 # float boundary; eval / pdf: max.  Types 0 diffuse, 1 roughconductor, 2 dielectric, 3 conductor, 4 plastic,
 # 5 roughdielectric, 6 roughplastic.
