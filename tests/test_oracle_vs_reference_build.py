@@ -217,3 +217,67 @@ def test_analytic_shape_emitters_direct_light_image_vs_reference_cli(kind):
     frac = _ztest(runs.mean(axis=0), ref_img, runs.var(axis=0, ddof=1) * 128, 16 * 128, 2048)
     assert frac >= 0.9975, frac
     assert abs(runs.mean() - ref_img.mean()) < 0.005 * ref_img.mean()
+
+
+# ---- gradients: finite differences of the REFERENCE renderer ----------------------------------------------------------
+def _reference_fd(sd, mesh_id, wgt, D, eps, spp):
+    """Central finite difference of sum(wgt * image) along the vertex displacement field D, both images rendered by the
+    unmodified reference CLI (its sampler is seeded per block, so the two renders share their random numbers)."""
+    import copy
+    P0 = np.asarray(sd.meshes[mesh_id].positions, np.float32).reshape(-1, 3).copy()
+    vals = []
+    for sgn in (+1.0, -1.0):
+        s2 = copy.copy(sd)
+        s2.meshes = list(sd.meshes)
+        m = copy.copy(sd.meshes[mesh_id])
+        m.positions = (P0 + sgn * eps * D).astype(np.float32)
+        s2.meshes[mesh_id] = m
+        img, _ = H.RefBuild(s2).render(spp=spp)
+        vals.append(float((img.astype(np.float64) * wgt).sum()))
+    return (vals[0] - vals[1]) / (2 * eps)
+
+
+@pytest.mark.parametrize("kind,fields,boundary", [("plane", ("tz", "tilt"), 0), ("quadenv", ("tx", "scale"), 1), ("quadshadow", ("tz", "scale"), 2)])
+def test_vertex_gradient_vs_finite_differences_of_the_reference(kind, fields, boundary):
+    """The vertex adjoint (the product's stage bodies on the host simulator) against finite differences of the REFERENCE
+    renderer itself: interior term (plane under a point light), film boundary (quad on a background), boundary seen from x1
+    (quad floating above a lit plane).  Tolerance 6 % / 6 % / 12 % of the largest derivative, as for the oracle's differences."""
+    sd = H.vgrad_scene(kind, "diffuse", res=16, spp=128)
+    yy, xx = np.mgrid[0:16, 0:16]
+    wgt = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
+    h = H.HostSim(sd)
+    g = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=boundary, edge_fraction=1.0).reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    fds = {n: _reference_fd(sd, 0, wgt, F[n].astype(np.float32), 0.02, 4096) for n in fields}
+    ref = max(abs(v) for v in fds.values())
+    tol = 0.12 if boundary == 2 else 0.06
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < tol * ref, (kind, n, float((g * F[n]).sum()), fd)
+
+
+def test_texture_gradient_vs_finite_differences_of_the_reference():
+    """The texture adjoint against finite differences of the reference renderer: textured Cornell box, a few texels."""
+    import copy
+    sd, tex = H.textured_cbox(res=16, spp=256, tex_res=4)
+    yy, xx = np.mgrid[0:16, 0:16]
+    wgt = np.stack([0.5 + xx / 16.0, 0.5 + yy / 16.0, 1.5 - xx / 16.0], axis=2).astype(np.float32)
+    h = H.HostSim(sd)
+    g = np.mean([h.render_grad(wgt, tex, seed=s_) for s_ in (5, 6, 7, 8)], axis=0).reshape(sd.textures[tex]["data"].shape)
+    base = sd.textures[tex]["data"].copy()
+
+    def loss(data):
+        s2 = copy.copy(sd)
+        s2.textures = [dict(t) for t in sd.textures]
+        s2.textures[tex]["data"] = data.astype(np.float32)
+        img, _ = H.RefBuild(s2).render(spp=4096)
+        return float((img.astype(np.float64) * wgt).sum())
+
+    fd, an = [], []
+    for y, x, c in ((1, 1, 0), (2, 1, 1), (1, 2, 2), (2, 2, 0)):
+        d = base.copy(); d[y, x, c] += 0.05; lp = loss(d)
+        d[y, x, c] -= 0.10; lm = loss(d)
+        fd.append((lp - lm) / 0.10); an.append(g[y, x, c])
+    fd, an = np.array(fd), np.array(an)
+    print("reference FD", fd, "adjoint", an)
+    assert np.linalg.norm(fd - an) < 0.05 * np.linalg.norm(fd), (fd, an)
