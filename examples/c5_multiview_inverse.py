@@ -1,10 +1,10 @@
 #!/usr/bin/env python
-"""C5: multi-view inverse rendering, one view per rank.
+"""C5: multi-view inverse rendering, the views dealt round-robin to the ranks (8 views, one per rank on 8 GPUs).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 examples/c5_multiview_inverse.py
 
-Every rank holds the whole scene, renders ITS view with all samples, computes the L2 image loss against its target
-view, and back-propagates through `mtsb_render_grad`; the parameter gradients are summed over the ranks with one NCCL
+Every rank holds the whole scene, renders ITS views with all samples, computes the L2 image loss against the target
+of each view, and back-propagates through `mtsb_render_grad`; the parameter gradients are summed over the ranks with one NCCL
 all-reduce and every rank applies the identical Adam update (parameters never need a broadcast).
 
 --param vertices (default, BASELINE config C5): Adam on the vertex positions of the sphere, started from a shrunk and
@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--param", choices=("vertices", "texture"), default="vertices")
     ap.add_argument("--sphere", type=int, default=16, help="latitude bands of the sphere (longitude = 2x)")
     ap.add_argument("--lr", type=float, default=None)
+    ap.add_argument("--views", type=int, default=None, help="number of sensors (default: max(8, ranks)); rank r owns views r, r + ranks, ...")
     ap.add_argument("--smooth", type=int, default=8, help="Jacobi sweeps of gradient smoothing over the mesh (vertices mode)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -44,16 +45,19 @@ def main():
     sd, tex = scenes.c4_scene(os.path.join(ROOT, "tests", "golden", "cbox_scene.npz"), res=args.res, spp=args.spp, tex_res=args.tex,
                               sphere=(args.sphere, 2 * args.sphere))
     mid = next(i for i, m in enumerate(sd.meshes) if m.name == "c4_sphere")
-    # view `rank`: orbit the camera around the box centre
+    # the views orbit the camera around the box centre; this rank's sensors are its share of them
+    n_views = args.views or max(8, world)
+    mine = list(range(rank, n_views, world))
     s0 = sd.sensors[0]
-    ang = (rank - (world - 1) / 2) * 0.12
     c = np.array([278.0, 273.0, 280.0])
-    eye = c + np.array([np.sin(ang) * 1080.0, 0.0, -np.cos(ang) * 1080.0])
     sd.sensors = []
-    sd.add_perspective(look_at(eye, c, [0, 1, 0]), s0["fov_x"], s0["near"], s0["far"], args.res, args.res, "box")
+    for v in mine:
+        ang = (v - (n_views - 1) / 2) * 0.12
+        eye = c + np.array([np.sin(ang) * 1080.0, 0.0, -np.cos(ang) * 1080.0])
+        sd.add_perspective(look_at(eye, c, [0, 1, 0]), s0["fov_x"], s0["near"], s0["far"], args.res, args.res, "box")
     scene = mi.Scene(sd, device=local)
     from mitsuba2_b200 import autodiff
-    target = torch.from_numpy(scene.render(spp=4 * args.spp, seed=12345).copy()).cuda(local)
+    targets = [torch.from_numpy(scene.render(sensor=k, spp=32 * args.spp, seed=12345).copy()).cuda(local) for k in range(len(mine))]
     if args.param == "texture":
         truth = torch.from_numpy(sd.textures[tex]["data"].copy()).cuda(local)
         param = torch.full_like(truth, 0.5, requires_grad=True)
@@ -80,15 +84,33 @@ def main():
             for _ in range(sweeps):
                 gv = (gv + torch.sparse.mm(adj, gv)) / (1.0 + deg)
             return gv
+    def converged_loss():
+        """L2 loss of this rank's views at 32x the samples (the per-iteration loss is dominated by Monte Carlo noise), summed over ranks."""
+        with torch.no_grad():
+            if args.param == "texture":
+                scene.update_texture(tex, param.detach().cpu().numpy())
+            else:
+                scene.update_vertices(mid, param.detach().cpu().numpy())
+            tot = torch.zeros(1, device=param.device)
+            for k, target in enumerate(targets):
+                tot += ((torch.from_numpy(scene.render(sensor=k, spp=32 * args.spp, seed=777).copy()).to(param.device) - target) ** 2).mean()
+            if world > 1:
+                dist.all_reduce(tot)
+        return tot.item() / n_views
+
     opt = torch.optim.Adam([param], lr=lr)
+    loss_start = converged_loss()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
     for it in range(args.iters):
         opt.zero_grad()
-        if args.param == "texture":
-            img = autodiff.render_torch(scene, param, tex, spp=args.spp, seed=it, shard=False)
-        else:
-            img = autodiff.render_torch(scene, spp=args.spp, seed=it, shard=False, vertices=param, mesh_id=mid)
-        loss = ((img - target) ** 2).mean()
-        loss.backward()
+        for k, target in enumerate(targets):           # gradients of this rank's views accumulate in param.grad
+            if args.param == "texture":
+                img = autodiff.render_torch(scene, param, tex, spp=args.spp, seed=it, sensor=k, shard=False)
+            else:
+                img = autodiff.render_torch(scene, spp=args.spp, seed=it, sensor=k, shard=False, vertices=param, mesh_id=mid)
+            loss = ((img - target) ** 2).mean()
+            loss.backward()
         if world > 1:                              # sum the per-view gradients; identical update everywhere
             distributed.allreduce_gradients([param.grad])
         if args.param == "vertices":
@@ -99,7 +121,17 @@ def main():
                 param.clamp_(0.01, 0.99)
         if rank == 0 and (it % 10 == 0 or it == args.iters - 1):
             err = (param.detach() - truth).abs().mean().item()
-            print(f"iter {it:4d}  loss(view 0) {loss.item():.6f}  mean |{args.param} error| {err:.4f}", flush=True)
+            extra = ""
+            if args.param == "vertices":               # vertices may slide along the surface: also the distance to the nearest target vertex
+                seen = (truth - c0)[:, 2] < -0.3 * (truth - c0).norm(dim=1)     # the cameras orbit on the -z side: the back is never observed
+                dist_seen = torch.cdist(param.detach()[seen], truth).min(dim=1).values.mean().item()
+                extra = f"  camera-facing vertices: mean distance to the target's vertices {dist_seen:.4f}"
+            print(f"iter {it:4d}  loss(view {mine[-1]}) {loss.item():.6f}  mean |{args.param} error| {err:.4f}{extra}", flush=True)
+    t1.record(); torch.cuda.synchronize()
+    loss_end = converged_loss()
+    if rank == 0:
+        print(f"mean L2 image loss over the {n_views} views at {32 * args.spp} spp: {loss_start:.3e} -> {loss_end:.3e}", flush=True)
+        print(f"{n_views} views on {world} rank(s): {args.iters} iterations in {t0.elapsed_time(t1) / 1e3:.2f} s ({t0.elapsed_time(t1) / args.iters:.1f} ms / iteration)", flush=True)
     if world > 1:
         dist.destroy_process_group()
 
