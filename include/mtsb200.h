@@ -273,7 +273,9 @@ int mtsb_film_device_ptr(mtsb_scene *scene, uint32_t sensor_id, void **ptr, uint
  * grad_texture (size of texture `tex_id`), grad_vertices (3*vertex_count of mesh `mesh_id`, the parameter the reference
  * exposes as `<mesh>.vertex_positions_buf`, src/librender/mesh.cpp:781-804); either may be NULL.
  * Vertex gradients = interior term (path-space adjoint) + boundary terms (edge sampling on the film and from x1), see
- * mitsuba2_b200/csrc/adjoint.h; the box reconstruction filter and MTSB_MODE_RGB are required. */
+ * mitsuba2_b200/csrc/adjoint.h.  Any reconstruction filter: under a filter wider than a pixel a sample's adjoint weight is the
+ * gather of dL_dimage over its footprint divided by the film's weight channel of all spp_total samples (hdrfilm.cpp develop).
+ * MTSB_MODE_RGB is required. */
 int mtsb_render_grad(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
                      uint32_t spp_total, uint64_t seed, const float *dL_dimage,
                      int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,

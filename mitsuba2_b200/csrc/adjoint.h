@@ -324,8 +324,7 @@ template <typename Add, bool Vtx = true> struct ReplayGrad {
     static constexpr bool kVertex = Vtx;
     GradCtx g; Add add;
     HD float3 weight(const RenderBatch &b, uint32_t path_id, float3 radiance) const {
-        uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
-        return ld3(g.dL_dimage, pixel) * radiance * g.scale;
+        return image_adjoint(g, b, path_id) * radiance;
     }
     // factor S_{k-1} = f_s(x_{k-2}, x_{k-1}, x_k) G~(x_{k-1}, x_k), complete now that x_k (or a miss) is known
     HD void on_vertex(const SceneDev &sc, const PathQueue &q, const RenderBatch &b, uint32_t i, uint32_t path_id, uint32_t depth,
@@ -367,8 +366,7 @@ HD void nee_adjoint(const SceneDev &sc, const GradCtx &g, const PathQueue &q, co
     // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point
     int kind = ds.etype == 0 ? kEndFixedArea : (ds.etype == 3 ? kEndFixedPoint : kEndDirection);
     float3 xC = kind == kEndDirection ? ds.d : ds.p;
-    uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
-    float3 w = ld3(g.dL_dimage, pixel) * xyz(contrib) * g.scale;
+    float3 w = image_adjoint(g, b, path_id) * xyz(contrib);
     vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recB, ds.n, w, add);
 }
 
@@ -549,8 +547,9 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
     if (s.term) {       // jump = radiance of the lit side (slot 0) against exactly 0
         if (s.lit_plus) lm = make_float4(0.f, 0.f, 0.f, 0.f); else { lm = lp; lp = make_float4(0.f, 0.f, 0.f, 0.f); }
     }
-    uint32_t pixel = (uint32_t) s.py * e.width + (uint32_t) s.px;
-    float3 dI = ld3(g.dL_dimage, pixel);
+    float3 dI;
+    if (g.inv_w != nullptr) dI = film_gather(g.filt, g.dL_dimage, g.inv_w, s.px, s.py);       // wide reconstruction filter
+    else dI = ld3(g.dL_dimage, (uint32_t) s.py * e.width + (uint32_t) s.px);
     float sc_ = (dI.x * (lp.x - lm.x) + dI.y * (lp.y - lm.y) + dI.z * (lp.z - lm.z)) * e.weight * e.total_len;
     if (sc_ == 0.f || !(fabsf(sc_) < 1e30f)) return;
     if (s.term) {
@@ -700,9 +699,8 @@ HD void edge2_scatter_body(const SceneDev &sc, const Edge2Ctx &e, const GradCtx 
     float3 val; float pdf;
     bsdf_eval_pdf(sc, bsdf, si, si.sh.to_local(eg.w), val, pdf);
     float4 L = b.result[j];
-    uint32_t pixel = (uint32_t) ((b.offset + j) / b.spp_batch);
-    float3 dI = ld3(g.dL_dimage, pixel);
-    float c = -(dI.x * val.x * L.x + dI.y * val.y * L.y + dI.z * val.z * L.z) * g.scale * rec0.z;
+    float3 dI = image_adjoint(g, b, j);
+    float c = -(dI.x * val.x * L.x + dI.y * val.y * L.y + dI.z * val.z * L.z) * rec0.z;
     if (c == 0.f || !(fabsf(c) < 1e30f)) return;
     float inv_r = 1.f / eg.r, inv_r2 = rec1.w < INFINITY ? 1.f / rec1.w : 0.f;
     float3 gp = eg.n_out * (c * inv_r);

@@ -102,7 +102,7 @@ struct mtsb_scene {
     std::vector<std::unique_ptr<SensorHost>> sensors;
     // wavefront pool
     uint32_t pool = 0;
-    DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result, final_radiance;
+    DevBuf<float4> q_o[2], q_d[2], q_hit[2], q_te[2], s_o, s_d, s_c, result, final_radiance, path_dl;
     DevBuf<uint8_t> prim_class;              // per primitive: 1 + BSDF type (shade class), see k_classify
     DevBuf<uint32_t> class_lists;            // material bins of the shade stage: kShadeClasses x pool queue indices
     DevBuf<uint4> q_misc[2], q_rng[2];

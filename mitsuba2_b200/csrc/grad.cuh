@@ -109,8 +109,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     CU(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     SensorDev sn = s->sensors[sensor_id]->dev;
-    if (sn.rfilter != 0 || sn.radius > 1.f)      // single-pixel splat of weight 1 (imageblock.cpp:162-169)
-        return fail(MTSB_E_INVALID, "mtsb_render_grad: only the box reconstruction filter is supported");
+    const bool wide = sn.radius > 1.f;           // else: single-pixel splat of weight 1 (imageblock.cpp:162-169)
     uint64_t npix = (uint64_t) sn.width * sn.height, total = npix * spp_count;
     uint32_t pool = (uint32_t) (total < pool_limit() ? total : pool_limit());
     if (grad_vertices && pool < 2) pool = 2;
@@ -141,6 +140,22 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     }
     if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
     g.cam_o = mk3(sn.to_world[3], sn.to_world[7], sn.to_world[11]);
+    DevBuf<float> inv_w;
+    if (wide) {
+        // the developed image divides by the film's weight channel: accumulate it over ALL spp_total samples of the job
+        // (every rank of a sharded job derives the same positions from the sampler streams), invert, gather per path
+        CU(inv_w.alloc(npix)); CU(cudaMemsetAsync(inv_w.p, 0, npix * sizeof(float), st));
+        uint64_t all = npix * spp_total;
+        for (uint64_t off = 0; off < all; off += 1u << 30) {
+            RenderBatch b; b.n_paths = (uint32_t) ((all - off) < (1u << 30) ? (all - off) : (1u << 30)); b.offset = off;
+            b.spp_begin = 0; b.spp_batch = spp_total; b.spp_total = spp_total; b.seed = seed; b.result = nullptr;
+            k_film_weights<<<grid_for(b.n_paths), kBlock, 0, st>>>(sn, b, inv_w.p);
+        }
+        k_film_weights_invert<<<grid_for(npix), kBlock, 0, st>>>(inv_w.p, (uint32_t) npix, (float) spp_total);
+        CU(s->path_dl.alloc(s->pool));
+        g.inv_w = inv_w.p; g.path_dl = s->path_dl.p;
+        g.filt = FilmFilter{ sn.rfilter, sn.radius, sn.stddev, sn.filter_c, sn.width, sn.height };
+    }
     CU(cudaMemsetAsync(s->dstats.p, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaEventRecord(s->ctx->ev0, st));
     uint64_t launches = 0;
@@ -152,6 +167,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
         b.seed = seed; b.result = s->result.p;
         RC(run_batch(s, sn, b, nullptr, false, launches));
         CU(cudaMemcpyAsync(s->final_radiance.p, s->result.p, (size_t) n * sizeof(float4), cudaMemcpyDeviceToDevice, st));
+        if (wide) { k_path_adjoint<<<grid_for(n), kBlock, 0, st>>>(sn, b, g, s->path_dl.p); launches++; }
         RC(run_batch(s, sn, b, &g, false, launches));
     }
     if (g.grad_vnrm != nullptr) {        // vertex normals -> positions (Mesh::recompute_vertex_normals), once per call
@@ -214,6 +230,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
                     RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
                     b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = s->result.p;
                     RC(run_batch(s, sn, b, nullptr, false, launches, nullptr, &l2));
+                    if (wide) { k_path_adjoint<<<grid_for(n2), kBlock, 0, st>>>(sn, b, g2, s->path_dl.p); launches++; }
                     k_edge2_scatter<<<grid_for(n2), kBlock, 0, st>>>(s->dev, e2, g2, b); launches++;
                     edge_samples += n2 / 2;
                 }

@@ -540,6 +540,26 @@ __global__ void k_edge_scatter(SceneDev sc, EdgeCtx e, const float *total_len, G
     if (j < n_samples) edge_scatter_body(sc, e, g, result, j, DevAdd());
 }
 
+// ---- gradient pass under a reconstruction filter wider than a pixel (path.h film_gather) ----------------------------
+// weight channel of the film over the samples of `b` (positions only: the first two draws of every path's stream)
+__global__ void k_film_weights(SensorDev sn, RenderBatch b, float *w_sum) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= b.n_paths) return;
+    float fx, fy; path_film_pos(sn, b, i, fx, fy);
+    film_put(sn, fx, fy, make_float4(0.f, 0.f, 0.f, 0.f), 1.f, [&](uint32_t pix, float4, float w) { atomicAdd(&w_sum[pix], w); });
+}
+__global__ void k_film_weights_invert(float *w_sum, uint32_t n, float spp_total) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { float w = w_sum[i]; w_sum[i] = w != 0.f ? spp_total / w : 0.f; }
+}
+// per path of `b`: dL/d(sample radiance) gathered over the sample's footprint
+__global__ void k_path_adjoint(SensorDev sn, RenderBatch b, GradCtx g, float4 *path_dl) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= b.n_paths) return;
+    float fx, fy; path_film_pos(sn, b, i, fx, fy);
+    path_dl[i] = mk4(film_gather(g.filt, g.dL_dimage, g.inv_w, fx, fy) * g.scale, 0.f);
+}
+
 // any-hit traversal of the shadow queue fused with the MIS contribution accumulate (path.cpp:170-171)
 template <bool Shapes = false>
 __global__ void __launch_bounds__(kBlock, kTraceBlocksPerSM)

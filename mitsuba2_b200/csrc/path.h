@@ -114,6 +114,11 @@ struct GradCtx {
     float *grad_tex;                // texture-sized accumulator
     int tex_id;
     float scale;                    // d(developed pixel)/d(sample radiance) = 1/spp_total (box filter)
+    // reconstruction filters wider than a pixel: the developed image is sum_s w_s(p) L_s / W[p], so a sample's adjoint weight
+    // is a gather over its footprint (film_gather below), done once per path and batch by k_path_adjoint; null = box filter
+    const float4 *path_dl = nullptr;
+    const float *inv_w = nullptr;   // per pixel: spp_total / W[p], W = the film's weight channel over ALL spp_total samples (0 where W = 0)
+    FilmFilter filt = { 0, 0.f, 0.f, 0.f, 0u, 0u };
     // vertex-position adjoint (adjoint.h); grad_pos == nullptr: texture gradient only
     float *grad_pos;                // 3 floats per vertex of mesh `mesh_id`
     float *grad_vnrm;               // same indexing: adjoint of the mesh's VERTEX NORMALS (smooth-shaded mesh), turned into
@@ -121,6 +126,12 @@ struct GradCtx {
     int mesh_id; uint32_t vert_begin, vert_count;
     float3 cam_o;                   // sensor origin (x0 of every path)
 };
+// dL/d(radiance of path `path_id`), per channel: box filter = the path's pixel / spp_total; wider filters = the gathered value
+HD float3 image_adjoint(const GradCtx &g, const RenderBatch &b, uint32_t path_id) {
+    if (g.path_dl != nullptr) return xyz(g.path_dl[path_id]);
+    uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
+    return ld3(g.dL_dimage, pixel) * g.scale;
+}
 // Hooks the adjoint replays plug into shade_body (all empty for the primal render):
 //   on_vertex: a path vertex was reconstructed (before its emission is added to the result);
 //   on_bsdf:   the vertex's BSDF is going to be used (after emission, Russian roulette and the depth cut).
@@ -142,8 +153,7 @@ HD void texture_adjoint(const SceneDev &sc, const RenderBatch &b, const GradCtx 
     if (!tex_footprint(t, si.u, si.v, idx, w)) return;
     float3 a = tex_eval(sc, tid, si.u, si.v);
     float4 fin = g.final_radiance[path_id], run = b.result[path_id];
-    uint32_t pixel = (uint32_t) ((b.offset + path_id) / b.spp_batch);
-    float3 dI = ld3(g.dL_dimage, pixel) * g.scale;
+    float3 dI = image_adjoint(g, b, path_id);
     const float tiny = 1e-8f;
     float3 ga = mk3(a.x > tiny ? dI.x * (fin.x - run.x) / a.x : 0.f, a.y > tiny ? dI.y * (fin.y - run.y) / a.y : 0.f,
                     a.z > tiny ? dI.z * (fin.z - run.z) / a.z : 0.f);
@@ -274,7 +284,7 @@ HD ShadeOut shade_body(const SceneDev &sc, const PathQueue &q, const RenderBatch
 }
 
 // ---- film: ImageBlock::put (src/librender/imageblock.cpp:79-172) on a border-less full-film block ----------
-HD float rfilter_eval(const SensorDev &sn, float x) {
+template <typename S> HD float rfilter_eval(const S &sn, float x) {
     if (sn.rfilter == 0) return fabsf(x) <= sn.radius ? 1.f : 0.f;                 // src/rfilters/box.cpp:34-36
     if (sn.rfilter == 1) return fmaxf(0.f, 1.f - fabsf(x / sn.radius));            // src/rfilters/tent.cpp:33-35
     if (sn.rfilter == 3 || sn.rfilter == 4) {                                      // mitchell.cpp:40-53, catmullrom.cpp:29-43
@@ -321,6 +331,27 @@ HD void film_put(const SensorDev &sn, float px, float py, float4 xyza, float wgt
         if (lx >= 0 && ly >= 0 && lx < (int) sn.width && ly < (int) sn.height)
             add((uint32_t) (ly * (int) sn.width + lx), xyza, wgt);
     }
+}
+
+// Adjoint of film_put followed by the film's division by its weight channel (hdrfilm.cpp develop): a sample at (px, py)
+// contributes w(p - x) L / W[p] to every pixel p of its footprint, so dL/dL_sample = sum_p dL/dI[p] w(p - x) inv_w[p] / spp_total
+// (inv_w = spp_total / W; the caller applies 1 / spp_total).  Same footprint arithmetic as film_put.
+HD float3 film_gather(const FilmFilter &sn, const float *dl, const float *inv_w, float px, float py) {
+    float x = px - 0.5f, y = py - 0.5f;
+    float3 acc = mk3(0.f);
+    int lox = max((int) ceilf(x - sn.radius), 0), loy = max((int) ceilf(y - sn.radius), 0);
+    int hix = min((int) floorf(x + sn.radius), (int) sn.width - 1), hiy = min((int) floorf(y + sn.radius), (int) sn.height - 1);
+    int n = (int) ceilf((sn.radius - 2.f * kRayEpsilon) * 2.f);
+    for (int yr = 0; yr < n; ++yr) {
+        int yy = loy + yr; if (yy > hiy) break;
+        float wy = rfilter_eval(sn, (float) loy - y + (float) yr);
+        for (int xr = 0; xr < n; ++xr) {
+            int xx = lox + xr; if (xx > hix) break;
+            uint32_t pix = (uint32_t) (yy * (int) sn.width + xx);
+            acc = acc + ld3(dl, pix) * (wy * rfilter_eval(sn, (float) lox - x + (float) xr) * inv_w[pix]);
+        }
+    }
+    return acc;
 }
 
 // src/librender/integrator.cpp:254-270: rgb -> XYZ (core/spectrum.h:220-227), aovs = {X,Y,Z,alpha,1}

@@ -41,6 +41,8 @@ struct MeshDev {
     int shape;              // >= 0: an analytic shape (one primitive), index into SceneDev::shapes; -1: triangle mesh
 };
 static_assert(sizeof(MeshDev) == 32, "MeshDev is fetched as two 128-bit loads");
+// reconstruction filter + film size, the part of SensorDev the gradient pass's film gather needs (path.h film_gather)
+struct FilmFilter { int rfilter; float radius, stddev, filter_c; uint32_t width, height; };
 struct SensorDev {
     float to_world[16], sample_to_camera[16];
     float near_clip, far_clip;

@@ -857,3 +857,19 @@ def shapes_scene(res=(48, 32), spp=8, emitters="disk", tri_floor=True, named_con
     sd.add_perspective(look_at([0, 0.6, -4.2], [0, -0.1, 0], [0, 1, 0]), 50.0, 0.01, 100.0, res[0], res[1], "box")
     sd.max_depth, sd.rr_depth, sd.spp = 5, 5, spp
     return sd
+
+
+def set_rfilter(sd, kind, sensor=0):
+    """Replace the reconstruction filter of a sensor (defaults of the reference's plugins: gaussian stddev 0.5 / radius 2,
+    mitchell B = C = 1/3 / radius 2, src/rfilters/{gaussian,mitchell}.cpp)."""
+    from mitsuba2_b200 import _abi as A
+    s = sd.sensors[sensor]
+    if kind == "gaussian":
+        s.update(rfilter=A.RFILTER_GAUSSIAN, radius=2.0, stddev=0.5)
+    elif kind == "mitchell":
+        s.update(rfilter=A.RFILTER_MITCHELL, radius=2.0, stddev=1.0 / 3.0, filter_c=1.0 / 3.0)
+    elif kind == "box":
+        s.update(rfilter=A.RFILTER_BOX, radius=0.5)
+    else:
+        raise ValueError(kind)
+    return sd

@@ -374,11 +374,26 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     if (grad_vertices) { g.vert_begin = s->meshes[mesh_id].vert_begin; g.vert_count = s->meshes[mesh_id].vert_count; }
     std::vector<float> vnrm_adj, vnrm_acc;
     if (grad_vertices && s->meshes[mesh_id].has_normals) { vnrm_adj.assign(3 * (size_t) g.vert_count, 0.f); vnrm_acc.assign(3 * (size_t) g.vert_count, 0.f); g.grad_vnrm = vnrm_adj.data(); }
+    // reconstruction filter wider than a pixel: k_film_weights, k_film_weights_invert, k_path_adjoint of kernels.cuh
+    std::vector<float> inv_w; std::vector<float4> path_dl;
+    const bool wide = sn.radius > 1.f;
+    auto fill_path_dl = [&](const RenderBatch &b, const GradCtx &gc) {
+        for (uint32_t i = 0; i < b.n_paths; ++i) { float fx, fy; path_film_pos(sn, b, i, fx, fy); path_dl[i] = mk4(film_gather(gc.filt, gc.dL_dimage, gc.inv_w, fx, fy) * gc.scale, 0.f); }
+    };
+    if (wide) {
+        inv_w.assign(npix, 0.f); path_dl.resize(pool);
+        RenderBatch wb; wb.n_paths = (uint32_t) (npix * spp_total); wb.offset = 0; wb.spp_begin = 0; wb.spp_batch = spp_total; wb.spp_total = spp_total; wb.seed = seed; wb.result = nullptr;
+        for (uint32_t i = 0; i < wb.n_paths; ++i) { float fx, fy; path_film_pos(sn, wb, i, fx, fy);
+            film_put(sn, fx, fy, make_float4(0.f, 0.f, 0.f, 0.f), 1.f, [&](uint32_t pix, float4, float w) { inv_w[pix] += w; }); }
+        for (float &w : inv_w) w = w != 0.f ? (float) spp_total / w : 0.f;
+        g.inv_w = inv_w.data(); g.path_dl = path_dl.data(); g.filt = FilmFilter{ sn.rfilter, sn.radius, sn.stddev, sn.filter_c, sn.width, sn.height };
+    }
     for (uint64_t off = 0; off < total; off += pool) {
         uint32_t n = (uint32_t) std::min<uint64_t>(pool, total - off);
         RenderBatch b; b.n_paths = n; b.offset = off; b.spp_begin = spp_begin; b.spp_batch = spp_count; b.spp_total = spp_total; b.seed = seed; b.result = P.result.data();
         hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad());
         std::copy(P.result.begin(), P.result.begin() + n, fin.begin());
+        if (wide) fill_path_dl(b, g);
         ReplayGrad<HostAdd> rg; rg.g = g;
         hs_run_batch<RgbX>(s, sn, b, P, cnt, rg);
     }
@@ -451,6 +466,7 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
         RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
         b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = P.result.data();
         hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad(), true, &e2);
+        if (wide) fill_path_dl(b, g2);
         for (uint32_t j = 0; j < n2; ++j) edge2_scatter_body(s->dev, e2, g2, b, j, HostAdd());
     }
 }

@@ -379,6 +379,61 @@ def test_vertex_gradient_shadow_boundary_matches_host_replay_and_fd(mi):
         assert abs(float((g8 * F[n]).sum()) - fd) < 0.10 * ref, (n, float((g8 * F[n]).sum()), fd)
 
 
+@pytest.mark.parametrize("rfilter", ["gaussian", "mitchell"])
+def test_gradients_under_wide_reconstruction_filters(mi, rfilter):
+    """The adjoint with a filter wider than a pixel (the film's default is gaussian, film.cpp:46-50): a sample's weight is gathered over
+    its footprint and divided by the film's weight channel (path.h film_gather).  Texture and interior vertex term vs finite
+    differences of the oracle at identical seeds (the film positions do not move: exact up to rounding), the film-boundary
+    term vs 1024-spp differences, and two sample ranges add up to the whole."""
+    sd, tex = H.textured_cbox(res=16, spp=32, tex_res=6)
+    H.set_rfilter(sd, rfilter)
+    wgt = np.random.default_rng(0).normal(size=(16, 16, 3)).astype(np.float32)
+    sc = mi.Scene(sd)
+    g, _ = sc.render_grad(wgt, spp=32, seed=5, tex_id=tex)
+    g = g.reshape(sd.textures[tex]["data"].shape)
+    scale = np.abs(g).max()
+    o = H.Oracle(sd)
+    base = sd.textures[tex]["data"].copy()
+
+    def loss(data):
+        o.update_texture(tex, data)
+        return float(np.sum(np.float64(wgt) * o.develop(o.render_xyzaw(seed=5))))
+
+    for y, x, c in ((1, 2, 0), (3, 3, 1), (4, 0, 2), (2, 5, 1)):
+        d = base.copy(); d[y, x, c] += 0.02
+        lp = loss(d)
+        d[y, x, c] -= 0.04
+        fd = (lp - loss(d)) / 0.04
+        assert abs(g[y, x, c] - fd) <= 3e-2 * scale, (g[y, x, c], fd, scale)
+    g1, _ = sc.render_grad(wgt, spp=12, seed=5, tex_id=tex, spp_begin=0, spp_total=32)
+    g2, _ = sc.render_grad(wgt, spp=20, seed=5, tex_id=tex, spp_begin=12, spp_total=32)
+    np.testing.assert_allclose((g1 + g2).reshape(g.shape), g, rtol=1e-3, atol=1e-4 * scale)
+    # interior vertex term
+    sd = H.set_rfilter(H.vgrad_scene("plane", "beckmann", res=16, spp=32), rfilter)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    sc = mi.Scene(sd)
+    sc.grad_config(boundary=False)
+    _, gv = sc.render_grad(wgt, spp=32, seed=3, mesh_id=0)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    F = H.displacement_fields(P0)
+    for name in ("tz", "tilt"):
+        a = float((gv.reshape(-1, 3) * F[name]).sum())
+        fd = H.oracle_fd_vertices(sd, 0, wgt, F[name].astype(np.float32), 2e-3, 32, 3)
+        assert abs(a - fd) <= 5e-3 * abs(fd) + 1e-3, (name, a, fd)
+    # film-boundary term
+    sd = H.set_rfilter(H.vgrad_scene("quadenv", "diffuse", res=16, spp=128), rfilter)
+    yy, xx = np.mgrid[0:16, 0:16]
+    wgt = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
+    sc = mi.Scene(sd)
+    sc.grad_config(boundary=1, edge_fraction=1.0)
+    gv = np.mean([sc.render_grad(wgt, spp=128, seed=s_, mesh_id=0)[1].reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
+    F = H.displacement_fields(np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3))
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((gv * F[n]).sum()) - fd) < 0.06 * ref, (n, float((gv * F[n]).sum()), fd)
+
+
 def test_vertex_gradient_rejects_unsupported(mi):
     sd = H.vgrad_scene("corner", "diffuse", res=8, spp=2)
     sc = mi.Scene(sd)

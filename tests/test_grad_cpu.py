@@ -209,3 +209,45 @@ def test_vertex_gradient_smooth_sphere_silhouette_and_terminator():
     assert abs(an["tx"] - fd["tx"]) < 0.012 * abs(fd["scale"]) and abs(an["ty"] - fd["ty"]) < 0.012 * abs(fd["scale"]), (an, fd)
     g0 = h.render_grad_vertices(wgt, 0, seed=3, boundary=0, edge_fraction=1.0).reshape(-1, 3)
     assert abs(float((g0 * F["scale"]).sum()) - fd["scale"]) > 0.1 * abs(fd["scale"])      # the boundary terms matter here
+
+
+@pytest.mark.parametrize("rfilter", ["gaussian", "mitchell"])
+def test_gradients_under_wide_reconstruction_filters(rfilter):
+    """Filters wider than a pixel (the film's default is gaussian, film.cpp:46-50): a sample's adjoint weight is the gather of
+    dL/dI over its footprint divided by the film's weight channel (path.h film_gather).  The film positions do not depend on the
+    parameters, so the texture and the interior vertex term equal finite differences of the oracle at identical seeds up to
+    rounding; the film-boundary term is held to 1024-spp differences."""
+    sd, tex = H.textured_cbox(res=16, spp=32, tex_res=6)
+    H.set_rfilter(sd, rfilter)
+    wgt = np.random.default_rng(0).normal(size=(16, 16, 3)).astype(np.float32)
+    g = HostSim(sd).render_grad(wgt, tex, seed=5).reshape(sd.textures[tex]["data"].shape)
+    scale = np.abs(g).max()
+    o = H.Oracle(sd)
+    base = sd.textures[tex]["data"].copy()
+
+    def loss(data):
+        o.update_texture(tex, data)
+        return float(np.sum(np.float64(wgt) * o.develop(o.render_xyzaw(seed=5))))
+
+    for y, x, c in ((1, 2, 0), (3, 3, 1), (4, 0, 2), (2, 5, 1)):
+        d = base.copy(); d[y, x, c] += 0.02
+        lp = loss(d)
+        d[y, x, c] -= 0.04
+        assert abs(g[y, x, c] - (lp - loss(d)) / 0.04) <= 1e-2 * scale
+    sd = H.set_rfilter(H.vgrad_scene("plane", "beckmann", res=16, spp=32), rfilter)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    gv = HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=False).reshape(-1, 3)
+    F = H.displacement_fields(np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3))
+    for name in ("tz", "tilt"):
+        a, fd = float((gv * F[name]).sum()), H.oracle_fd_vertices(sd, 0, wgt, F[name].astype(np.float32), 2e-3, 32, 3)
+        assert abs(a - fd) <= 3e-3 * abs(fd) + 1e-3, (name, a, fd)
+    sd = H.set_rfilter(H.vgrad_scene("quadenv", "diffuse", res=16, spp=128), rfilter)
+    yy, xx = np.mgrid[0:16, 0:16]
+    wgt = np.stack([xx / 16, yy / 16, 0.5 + 0 * xx], -1).astype(np.float32)
+    h = HostSim(sd)
+    gv = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=1, edge_fraction=1.0).reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
+    F = H.displacement_fields(np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3))
+    fds = {n: H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.02, 1024, 3) for n in ("tx", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((gv * F[n]).sum()) - fd) < 0.04 * ref, (n, float((gv * F[n]).sum()), fd)
