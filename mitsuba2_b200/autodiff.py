@@ -35,13 +35,22 @@ def render_torch(scene, texture=None, tex_id=-1, spp=None, seed=0, sensor=0, gro
     def _host(t):
         return t if t.is_cuda else t.cpu().numpy()
 
+    def _stamp(t):
+        # storage, in-place version counter and a checksum (writes through `.data` do not bump the counter)
+        return (t.data_ptr(), t._version, tuple(t.shape), float(t.detach().double().sum()))
+
     class _Render(torch.autograd.Function):
         @staticmethod
         def forward(ctx, tex, vtx):
-            if use_tex:
-                scene.update_texture(tex_id, _host(tex.detach().contiguous().float()))
-            if use_vtx:
-                scene.update_vertices(mesh_id, _host(vtx.detach().contiguous().float()))
+            # several views of one iteration pass the same tensors: the scene is updated (texture upload; vertex normals +
+            # BVH rebuild) only when a parameter changed since the update it last made from it
+            for use, key, t, update in ((use_tex, ("texture", tex_id), tex, scene.update_texture), (use_vtx, ("vertices", mesh_id), vtx, scene.update_vertices)):
+                if not use:
+                    continue
+                stamp = _stamp(t)
+                if scene._param_stamps.get(key) != stamp:
+                    update(key[1], _host(t.detach().contiguous().float()))
+                    scene._param_stamps[key] = stamp
             rank, world = D.world_info(group) if shard else (0, 1)
             total = int(scene.data.spp if spp is None else spp)
             begin, count = D.sample_share(total, rank, world)

@@ -53,6 +53,7 @@ class Scene:
     def __init__(self, data: SceneData, device=0):
         self.data = data
         self.device = device
+        self._param_stamps = {}     # autodiff.render_torch: (kind, id) -> stamp of the tensor the scene was last updated from
         self._ctx = _context(device)
         self._h = C.c_void_p()
         desc, keep = data.to_desc()
@@ -289,12 +290,14 @@ class Scene:
 
     # ---- parameter updates (traverse()/parameters_changed) ------------------------------------------
     def update_vertices(self, mesh_id, positions):
+        self._param_stamps.pop(("vertices", mesh_id), None)
         p, mem, keep = _arg(positions, np.float32, device=self.device)
         A.check(A.lib().mtsb_scene_update_vertices(self._h, mesh_id, p, mem))
         if mem == A.MEM_HOST:
             self.data.meshes[mesh_id].positions = keep.reshape(-1, 3).copy()
 
     def update_texture(self, tex_id, data):
+        self._param_stamps.pop(("texture", tex_id), None)
         p, mem, keep = _arg(data, np.float32, device=self.device)
         A.check(A.lib().mtsb_scene_update_texture(self._h, tex_id, p, mem))
 
