@@ -598,6 +598,24 @@ def main():
            "d2h_bytes_per_step": int(film_host[0].numel() * 4),
            "note": "per step: pinned texture upload on every rank, render, film all-reduce (N > 1), rank 0 reads the film back into pinned host memory; the read-back of step i overlaps the render of step i+1"}
 
+    bvh_update = None
+    if rank == 0 and not args.no_side_metrics:
+        # build and refit timed separately -- the big mesh's own positions pushed through update_vertices
+        # (device pointer; vertex normals recomputed on the GPU), once as a full rebuild and once as a refit
+        try:
+            p = torch.from_numpy(np.ascontiguousarray(sd.meshes[0].positions, np.float32)).to(dev)
+            bvh_update = {"triangles": int(sum(len(m.faces) for m in sd.meshes))}
+            for name, refit in (("rebuild", False), ("refit", True)):
+                scene.update_config(refit=refit)
+                scene.update_vertices(0, p); torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                scene.update_vertices(0, p); torch.cuda.synchronize()
+                bvh_update[name + "_call_ms"] = (time.perf_counter() - t0) * 1e3
+                bvh_update[name + "_bvh_ms"] = scene.build_stats()["ms_build"]
+            scene.update_config(refit=False)
+        except Exception as e:
+            bvh_update = {"error": repr(e)}
+
     mg_side = None
     if world > 1 and not args.no_side_metrics:
         del scene
@@ -640,7 +658,7 @@ def main():
                       "shadow_rays_per_sample": agg["shadow_rays"] / agg["samples"], "algorithmic_bytes_per_sample": bytes_per_sample,
                       "whole_step_gbs": bytes_per_sample * agg["samples"] / (sum(stage_ms.values()) * K * 1e-3) / 1e9,
                       "any_hit_mrays_per_s": agg["shadow_rays"] / max(agg["ms_any"], 1e-9) / 1e3,
-                      "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"]},
+                      "bvh": {"ms_build": build["ms_build"], "nodes": build["bvh_nodes"], "depth": build["bvh_depth"], "update_vertices": bvh_update},
                       "scene_setup_s": t_build, "strong_scaling": strong, "multi_gpu_parity": mg_parity},
         }
         if mg_side is not None:

@@ -56,6 +56,7 @@ def main():
         eye = c + np.array([np.sin(ang) * 1080.0, 0.0, -np.cos(ang) * 1080.0])
         sd.add_perspective(look_at(eye, c, [0, 1, 0]), s0["fov_x"], s0["near"], s0["far"], args.res, args.res, "box")
     scene = mi.Scene(sd, device=local)
+    scene.update_config(refit=True, rebuild_every=16)      # Adam moves the vertices a little per step: refit the BVH, rebuild now and then
     from mitsuba2_b200 import autodiff
     targets = [torch.from_numpy(scene.render(sensor=k, spp=32 * args.spp, seed=12345).copy()).cuda(local) for k in range(len(mine))]
     if args.param == "texture":

@@ -223,6 +223,11 @@ int mtsb_scene_stats(mtsb_scene *scene, mtsb_stats *out);
 /* `Mesh::parameters_changed` (src/librender/mesh.cpp:794-804): new positions, normals recomputed if the
  * mesh had computed normals, area CDF rebuilt, BVH rebuilt */
 int mtsb_scene_update_vertices(mtsb_scene *scene, uint32_t mesh_id, const float *positions, int mem);
+/* How mtsb_scene_update_vertices brings the acceleration structure up to date (the reference rebuilds its kd-tree,
+ * src/librender/scene.cpp:84-99 `parameters_changed` -> accel_release / accel_init): refit = 0 (default) full GPU rebuild;
+ * refit = 1 keeps the topology of the last build and refits leaf triangles and node boxes to the new positions (an
+ * optimisation loop moves vertices a little per step), with a full rebuild on every `rebuild_every`-th update (0 = never). */
+int mtsb_scene_update_config(mtsb_scene *scene, int refit, uint32_t rebuild_every);
 /* `BitmapTextureImpl::parameters_changed` (src/textures/bitmap.cpp:301-331) */
 int mtsb_scene_update_texture(mtsb_scene *scene, uint32_t tex_id, const float *data, int mem);
 

@@ -115,6 +115,7 @@ SYMBOLS = [
     ("mtsb_render_grad", C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp,
                                    C.c_int32, vp, C.c_int32, vp, C.c_int, C.POINTER(Stats)]),
     ("mtsb_grad_config", C.c_int, [vp, C.c_int, C.c_float]),
+    ("mtsb_scene_update_config", C.c_int, [vp, C.c_int, C.c_uint32]),
     ("mtsb_pcg32_floats", C.c_int, [vp, C.c_uint64, vp, vp, C.c_uint32, vp]),
     ("mtsb_sampler_seed", C.c_int, [vp, C.c_uint64, C.c_uint64, vp, vp]),
     ("mtsb_sensor_sample_ray", C.c_int, [vp, C.c_uint32, C.c_uint64, vp, vp, vp]),

@@ -80,6 +80,8 @@ struct BuildScratch {
 struct mtsb_scene {
     mtsb_ctx *ctx;
     BuildScratch build_scratch;
+    std::vector<uint32_t> bvh_levels;     // wide-node index where every level of the last build starts (+ the total): the refit walks them backwards
+    int update_refit = 0; uint32_t rebuild_every = 0, refits_since_build = 0;      // mtsb_scene_update_config
     // host copies needed for updates
     std::vector<MeshDev> meshes; std::vector<std::vector<uint32_t>> mesh_faces; std::vector<bool> computed_normals;
     std::vector<TexDev> tex; std::vector<BsdfDev> bsdfs; std::vector<EmitterDev> emitters;
@@ -249,7 +251,9 @@ static int build_bvh(mtsb_scene *s) {
     CU(cudaMemcpyAsync(counters.p, c0, sizeof(c0), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(wide_bin.p, &root, sizeof(int), cudaMemcpyHostToDevice, st));
     uint32_t begin = 0, end = 1, depth = 0;
+    s->bvh_levels.clear(); s->refits_since_build = 0;
     while (begin < end) {
+        s->bvh_levels.push_back(begin);
         k_collapse<<<grid_for(end - begin), kBlock, 0, st>>>(b, begin, end);
         uint32_t hc[2];
         CU(cudaMemcpyAsync(hc, counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
@@ -257,6 +261,7 @@ static int build_bvh(mtsb_scene *s) {
         begin = end; end = hc[0]; depth++;
         if (depth > 4096) return fail(MTSB_E_INVALID, "BVH collapse did not terminate");
     }
+    s->bvh_levels.push_back(end);
     CU(cudaGetLastError());
     if (depth > (uint32_t) (kStackFast + kStackSlow)) return fail(MTSB_E_INVALID, "BVH too deep for the traversal stack");
     CU(cudaEventRecord(s->ctx->ev1, st));
@@ -264,6 +269,33 @@ static int build_bvh(mtsb_scene *s) {
     CU(cudaEventElapsedTime(&s->build_stats.ms_build, s->ctx->ev0, s->ctx->ev1));
     s->build_stats.bvh_nodes = end; s->build_stats.bvh_depth = depth;
     s->dev.bvh.nodes = s->nodes.p; s->dev.bvh.tris = s->tris.p; s->dev.bvh.shapes = s->shapes.empty() ? nullptr : s->d_shapes.p;
+    return MTSB_OK;
+}
+
+// Refit of the BVH of the last build to the current position array (bvh.h refit_*_body): one pass over the leaf slots, one
+// launch per level from the deepest up, one read-back (the scene box, for the environment emitters' bounding sphere).
+static int refit_bvh(mtsb_scene *s) {
+    cudaStream_t st = s->ctx->stream;
+    uint32_t n = (uint32_t) s->faces.n;
+    if (n == 0 || s->bvh_levels.size() < 2) return build_bvh(s);
+    CU(cudaEventRecord(s->ctx->ev0, st));
+    BuildScratch &bs = s->build_scratch;
+    BvhRefit r; r.nodes = s->nodes.p; r.tris = s->tris.p; r.pos = s->pos.p; r.faces = s->faces.p; r.shapes = s->d_shapes.p;
+    r.box_lo = bs.nlo.p; r.box_hi = bs.nhi.p;      // 2n entries each from the build; there are at most n wide nodes
+    k_refit_tris<<<grid_for(n), kBlock, 0, st>>>(r, n);
+    for (size_t l = s->bvh_levels.size() - 1; l-- > 0;) {
+        uint32_t begin = s->bvh_levels[l], end = s->bvh_levels[l + 1];
+        if (end > begin) k_refit_level<<<grid_for(end - begin), kBlock, 0, st>>>(r, begin, end);
+    }
+    float4 hb[2];
+    CU(cudaMemcpyAsync(&hb[0], r.box_lo, sizeof(float4), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&hb[1], r.box_hi, sizeof(float4), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(s->ctx->ev1, st));
+    CU(cudaEventSynchronize(s->ctx->ev1));
+    CU(cudaGetLastError());
+    CU(cudaEventElapsedTime(&s->build_stats.ms_build, s->ctx->ev0, s->ctx->ev1));
+    s->bbox_lo = xyz(hb[0]); s->bbox_hi = xyz(hb[1]);
+    s->refits_since_build++;
     return MTSB_OK;
 }
 
@@ -905,10 +937,23 @@ extern "C" int mtsb_scene_update_vertices(mtsb_scene *s, uint32_t mesh_id, const
         k_vnormal_faces<<<grid_for(m.face_count), kBlock, 0, st>>>(s->pos.p, s->faces.p, m.face_begin, m.face_count, s->nrm.p);
         k_vnormal_normalize<<<grid_for(m.vert_count), kBlock, 0, st>>>(dn, m.vert_count);
     }
-    RC(build_bvh(s));
+    const bool refit = s->update_refit && (s->rebuild_every == 0 || s->refits_since_build + 1 < s->rebuild_every);
+    if (refit) RC(refit_bvh(s)); else RC(build_bvh(s));
     if (m.emitter >= 0) RC(build_area_tables(s));
     update_env_bsphere(s);
+    if (refit && m.emitter < 0) {        // nothing but the emitters' bounding sphere changed in the tables
+        CU(s->d_emitters.upload(s->emitters.data(), s->emitters.size(), st));
+        CU(cudaStreamSynchronize(st));
+        s->dev.emitters = s->d_emitters.p;
+        return MTSB_OK;
+    }
     return upload_struct_arrays(s);
+}
+
+extern "C" int mtsb_scene_update_config(mtsb_scene *s, int refit, uint32_t rebuild_every) {
+    CHECK_ARG(s);
+    s->update_refit = refit ? 1 : 0; s->rebuild_every = rebuild_every;
+    return MTSB_OK;
 }
 
 extern "C" int mtsb_scene_update_texture(mtsb_scene *s, uint32_t tex_id, const float *data, int mem) {

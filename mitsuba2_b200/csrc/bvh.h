@@ -258,6 +258,36 @@ HD uint32_t bin_first(const BvhBuild &b, int id) {
     return id >= n - 1 ? (uint32_t) (id - (n - 1)) : b.rfirst[id];
 }
 
+// Quantisation frame of a wide node with box [lo, hi]: per axis the power-of-two cell size 2^ex (sc) that maps the extent to 8 bits
+HD void quant_frame(float3 lo, float3 hi, int ex[3], float sc[3]) {
+    float ext[3] = { hi.x - lo.x, hi.y - lo.y, hi.z - lo.z };
+    for (int a = 0; a < 3; ++a) {
+        int e = (int) ceilf(log2f(fmaxf(ext[a], 1e-30f) / 255.f));
+        if (e < -126) e = -126; if (e > 126) e = 126;
+        while (ceilf(ext[a] / exp2f((float) e)) > 254.f) e++;   // one unit of slack for the safety pass below
+        ex[a] = e; sc[a] = exp2f((float) e);
+    }
+}
+// child box [cl, chh] -> quantised planes of slot s, conservative under the exact arithmetic the traversal uses
+HD void quant_child(const float cl[3], const float chh[3], const float plo[3], const float sc[3], int s, uint8_t qlo[3][8], uint8_t qhi[3][8]) {
+    for (int a = 0; a < 3; ++a) {
+        float fl = floorf((cl[a] - plo[a]) / sc[a]), fh = ceilf((chh[a] - plo[a]) / sc[a]);
+        fl = fminf(fmaxf(fl, 0.f), 255.f); fh = fminf(fmaxf(fh, 0.f), 255.f);
+        while (fl > 0.f && plo[a] + fl * sc[a] > cl[a]) fl -= 1.f;
+        while (fh < 255.f && plo[a] + fh * sc[a] < chh[a]) fh += 1.f;
+        qlo[a][s] = (uint8_t) fl; qhi[a][s] = (uint8_t) fh;
+    }
+}
+HD uint32_t pack4u8(const uint8_t *p) { return (uint32_t) p[0] | ((uint32_t) p[1] << 8) | ((uint32_t) p[2] << 16) | ((uint32_t) p[3] << 24); }
+// words 0 and 2..4 of a node (word 1 = child base, triangle base, valid24 is the topology)
+HD void write_node_planes(uint4 *o, float3 lo, const int ex[3], uint32_t imask, const uint8_t qlo[3][8], const uint8_t qhi[3][8]) {
+    uint32_t ew = (uint32_t) (ex[0] + 127) | ((uint32_t) (ex[1] + 127) << 8) | ((uint32_t) (ex[2] + 127) << 16) | (imask << 24);
+    o[0] = make_uint4(f2u(lo.x), f2u(lo.y), f2u(lo.z), ew);
+    o[2] = make_uint4(pack4u8(qlo[0]), pack4u8(qlo[0] + 4), pack4u8(qlo[1]), pack4u8(qlo[1] + 4));
+    o[3] = make_uint4(pack4u8(qlo[2]), pack4u8(qlo[2] + 4), pack4u8(qhi[0]), pack4u8(qhi[0] + 4));
+    o[4] = make_uint4(pack4u8(qhi[1]), pack4u8(qhi[1] + 4), pack4u8(qhi[2]), pack4u8(qhi[2] + 4));
+}
+
 // Collapse: one thread per wide node w of the current level.
 HD void collapse_body(const BvhBuild &b, uint32_t w) {
     int n = (int) b.n;
@@ -308,13 +338,8 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
         done[bk] = true; slot_used[bs] = true; slot_of[bk] = bs;
     }
     // quantisation frame
-    int ex[3]; float sc[3]; float ext[3] = { hi.x - lo.x, hi.y - lo.y, hi.z - lo.z };
-    for (int a = 0; a < 3; ++a) {
-        int e = (int) ceilf(log2f(fmaxf(ext[a], 1e-30f) / 255.f));
-        if (e < -126) e = -126; if (e > 126) e = 126;
-        while (ceilf(ext[a] / exp2f((float) e)) > 254.f) e++;   // one unit of slack for the safety pass below
-        ex[a] = e; sc[a] = exp2f((float) e);
-    }
+    int ex[3]; float sc[3];
+    quant_frame(lo, hi, ex, sc);
     uint8_t qlo[3][8], qhi[3][8];
     for (int s = 0; s < 8; ++s) for (int a = 0; a < 3; ++a) { qlo[a][s] = 255; qhi[a][s] = 0; }   // empty slot: inverted box, never hit
     uint32_t imask = 0, valid24 = 0;
@@ -330,14 +355,7 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
         if (k < 0) continue;
         float4 cl4 = b.nlo[ch[k]], ch4 = b.nhi[ch[k]];
         float cl[3] = { cl4.x, cl4.y, cl4.z }, chh[3] = { ch4.x, ch4.y, ch4.z };
-        for (int a = 0; a < 3; ++a) {
-            float fl = floorf((cl[a] - plo[a]) / sc[a]), fh = ceilf((chh[a] - plo[a]) / sc[a]);
-            fl = fminf(fmaxf(fl, 0.f), 255.f); fh = fminf(fmaxf(fh, 0.f), 255.f);
-            // conservative under the exact arithmetic the traversal uses
-            while (fl > 0.f && plo[a] + fl * sc[a] > cl[a]) fl -= 1.f;
-            while (fh < 255.f && plo[a] + fh * sc[a] < chh[a]) fh += 1.f;
-            qlo[a][s] = (uint8_t) fl; qhi[a][s] = (uint8_t) fh;
-        }
+        quant_child(cl, chh, plo, sc, s, qlo, qhi);
         if (internal[k]) {
             imask |= 1u << s;
             b.wide_bin[child_base + int_rank] = ch[k];
@@ -362,14 +380,69 @@ HD void collapse_body(const BvhBuild &b, uint32_t w) {
             tri_off += cnt;
         }
     }
-    auto pack4 = [](const uint8_t *p) { return (uint32_t) p[0] | ((uint32_t) p[1] << 8) | ((uint32_t) p[2] << 16) | ((uint32_t) p[3] << 24); };
     uint4 *o = b.nodes + 5 * (size_t) w;
-    uint32_t ew = (uint32_t) (ex[0] + 127) | ((uint32_t) (ex[1] + 127) << 8) | ((uint32_t) (ex[2] + 127) << 16) | (imask << 24);
-    o[0] = make_uint4(f2u(lo.x), f2u(lo.y), f2u(lo.z), ew);
+    write_node_planes(o, lo, ex, imask, qlo, qhi);
     o[1] = make_uint4(child_base, tri_base, valid24, 0u);
-    o[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
-    o[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
-    o[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Refit: the vertices moved, the topology of the last build is kept (Mesh::parameters_changed, mesh.cpp:794-804, asks the
+// reference for a kd-tree rebuild; an optimisation loop moves vertices a little every step).  Leaf slots are re-read from the
+// position array, then the wide nodes are re-boxed and re-quantised level by level from the deepest one up: the collapse
+// numbers the nodes level by level, so [begin, end) of every level is known from the build.  Slot assignment, child order and
+// the triangle lists do not change.
+// ------------------------------------------------------------------------------------------------
+struct BvhRefit {
+    uint4 *nodes; float4 *tris;
+    const float *pos; const uint4 *faces; const ShapeDev *shapes;
+    float4 *box_lo, *box_hi;          // per wide node: its box after the refit (children read them one level later)
+};
+HD void refit_tri_body(const BvhRefit &r, uint32_t t) {
+    float4 *tp = r.tris + 3 * (size_t) t;
+    if (f2u(tp[1].w) != 0u) return;                         // analytic shapes do not move
+    uint4 f = r.faces[f2u(tp[0].w)];
+    tp[0] = make_float4(r.pos[3 * f.x], r.pos[3 * f.x + 1], r.pos[3 * f.x + 2], tp[0].w);
+    tp[1] = make_float4(r.pos[3 * f.y], r.pos[3 * f.y + 1], r.pos[3 * f.y + 2], 0.f);
+    tp[2] = make_float4(r.pos[3 * f.z], r.pos[3 * f.z + 1], r.pos[3 * f.z + 2], 0.f);
+}
+HD void refit_node_body(const BvhRefit &r, uint32_t w) {
+    uint4 *o = r.nodes + 5 * (size_t) w;
+    uint4 n0 = o[0], n1 = o[1];
+    uint32_t imask = n0.w >> 24, valid24 = n1.z;
+    float3 clo[8], chi[8]; uint32_t present = 0, int_rank = 0, tri_off = 0;
+    float3 lo = mk3(INFINITY), hi = mk3(-INFINITY);
+    for (int s = 0; s < 8; ++s) {
+        if ((imask >> s) & 1u) {
+            uint32_t c = n1.x + int_rank++;
+            clo[s] = xyz(r.box_lo[c]); chi[s] = xyz(r.box_hi[c]);
+        } else {
+            uint32_t cnt = (uint32_t) popc32((valid24 >> (3 * s)) & 7u);
+            if (cnt == 0) continue;
+            float3 l = mk3(INFINITY), h = mk3(-INFINITY);
+            for (uint32_t q = 0; q < cnt; ++q) {
+                const float4 *tp = r.tris + 3 * (size_t) (n1.y + tri_off + q);
+                float4 a0 = tp[0], a1 = tp[1], a2 = tp[2];
+                if (f2u(a1.w) != 0u) { float3 sl, sh; shape_bounds(r.shapes[f2u(a2.w)], sl, sh); l = fmin3(l, sl); h = fmax3(h, sh); }
+                else { l = fmin3(l, fmin3(xyz(a0), fmin3(xyz(a1), xyz(a2)))); h = fmax3(h, fmax3(xyz(a0), fmax3(xyz(a1), xyz(a2)))); }
+            }
+            tri_off += cnt;
+            clo[s] = l; chi[s] = h;
+        }
+        present |= 1u << s;
+        lo = fmin3(lo, clo[s]); hi = fmax3(hi, chi[s]);
+    }
+    r.box_lo[w] = mk4(lo, 0.f); r.box_hi[w] = mk4(hi, 0.f);
+    int ex[3]; float sc[3];
+    quant_frame(lo, hi, ex, sc);
+    uint8_t qlo[3][8], qhi[3][8];
+    for (int s = 0; s < 8; ++s) for (int a = 0; a < 3; ++a) { qlo[a][s] = 255; qhi[a][s] = 0; }
+    float plo[3] = { lo.x, lo.y, lo.z };
+    for (int s = 0; s < 8; ++s) {
+        if (!((present >> s) & 1u)) continue;
+        float cl[3] = { clo[s].x, clo[s].y, clo[s].z }, chh[3] = { chi[s].x, chi[s].y, chi[s].z };
+        quant_child(cl, chh, plo, sc, s, qlo, qhi);
+    }
+    write_node_planes(o, lo, ex, imask, qlo, qhi);
 }
 
 // ------------------------------------------------------------------------------------------------

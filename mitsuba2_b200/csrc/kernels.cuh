@@ -79,6 +79,15 @@ __global__ void k_collapse(BvhBuild b, uint32_t begin, uint32_t end) {
     if (i < end) collapse_body(b, i);
 }
 
+__global__ void k_refit_tris(BvhRefit r, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) refit_tri_body(r, i);
+}
+__global__ void k_refit_level(BvhRefit r, uint32_t begin, uint32_t end) {
+    uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < end) refit_node_body(r, i);
+}
+
 // rough plastic tables (shade.h): thread i < 64: external transmittance at cosine mu_i; 64 <= i < 128: internal reflectance
 __global__ void k_rough_tables(int distr_type, float alpha, float eta, const float *n32, const float *w32, const float *n128, const float *w128, float *out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

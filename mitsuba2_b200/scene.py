@@ -296,6 +296,11 @@ class Scene:
         if mem == A.MEM_HOST:
             self.data.meshes[mesh_id].positions = keep.reshape(-1, 3).copy()
 
+    def update_config(self, refit=False, rebuild_every=0):
+        """How `update_vertices` brings the BVH up to date: full rebuild (default) or a refit of the last build's topology,
+        with a full rebuild on every `rebuild_every`-th update (0 = never)."""
+        A.check(A.lib().mtsb_scene_update_config(self._h, int(bool(refit)), int(rebuild_every)))
+
     def update_texture(self, tex_id, data):
         self._param_stamps.pop(("texture", tex_id), None)
         p, mem, keep = _arg(data, np.float32, device=self.device)

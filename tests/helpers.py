@@ -206,6 +206,7 @@ class HostSim:
             l.hs_scene_create.argtypes = [C.POINTER(A.SceneDesc)]
             l.hs_scene_destroy.argtypes = [vp]
             l.hs_bvh_info.argtypes = [vp, vp, vp]
+            l.hs_refit_vertices.argtypes = [vp, C.c_uint32, vp]
             l.hs_intersect.argtypes = [vp, C.c_uint64, vp, vp, vp, vp, C.c_int]
             l.hs_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, vp]
             l.hs_render_grad.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, vp, C.c_int32, vp, C.c_int32, vp,
@@ -232,6 +233,11 @@ class HostSim:
         a, b = C.c_uint32(), C.c_uint32()
         self.lib().hs_bvh_info(self.h, C.byref(a), C.byref(b))
         return a.value, b.value
+
+    def refit_vertices(self, mesh_id, positions):
+        """bvh.h refit_*_body under the topology of the build (positions only: normals and emitter tables are not refreshed)."""
+        positions = np.ascontiguousarray(positions, np.float32)
+        self.lib().hs_refit_vertices(self.h, mesh_id, _p(positions))
 
     def intersect_closest(self, om, dm):
         om, dm = _f32(om), _f32(dm)

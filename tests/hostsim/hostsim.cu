@@ -23,6 +23,7 @@ struct hs_scene {
     std::vector<uint4> nodes; std::vector<float4> tris;
     std::vector<std::vector<float4>> film_xyza; std::vector<std::vector<float>> film_w;
     SceneDev dev; uint32_t bvh_nodes = 0, bvh_depth = 0;
+    std::vector<uint32_t> bvh_levels;       // as mtsb_scene::bvh_levels (api.cu)
     float3 lo, hi;
 };
 
@@ -118,12 +119,28 @@ static void hs_build_bvh(hs_scene *s) {
     }
     counters[0] = 1; counters[1] = 0; wide_bin[0] = 0;
     uint32_t begin = 0, end = 1, depth = 0;
-    while (begin < end) { for (uint32_t w = begin; w < end; ++w) collapse_body(b, w); begin = end; end = counters[0]; depth++; }
+    s->bvh_levels.clear();
+    while (begin < end) { s->bvh_levels.push_back(begin); for (uint32_t w = begin; w < end; ++w) collapse_body(b, w); begin = end; end = counters[0]; depth++; }
+    s->bvh_levels.push_back(end);
     s->bvh_nodes = end; s->bvh_depth = depth;
     s->dev.bvh.nodes = s->nodes.data(); s->dev.bvh.tris = s->tris.data(); s->dev.bvh.shapes = s->shapes.empty() ? nullptr : s->shapes.data();
 }
 
 extern "C" void hs_scene_destroy(hs_scene *s) { delete s; }
+
+// refit_bvh() of api.cu: new positions of one mesh under the topology of the last build
+extern "C" void hs_refit_vertices(hs_scene *s, uint32_t mesh_id, const float *positions) {
+    const MeshDev &m = s->meshes[mesh_id];
+    std::copy(positions, positions + 3 * (size_t) m.vert_count, s->pos.begin() + 3 * (size_t) m.vert_begin);
+    uint32_t n = (uint32_t) s->faces.size();
+    std::vector<float4> box_lo(n + 1), box_hi(n + 1);
+    BvhRefit r; r.nodes = s->nodes.data(); r.tris = s->tris.data(); r.pos = s->pos.data(); r.faces = s->faces.data(); r.shapes = s->shapes.data();
+    r.box_lo = box_lo.data(); r.box_hi = box_hi.data();
+    for (uint32_t t = 0; t < n; ++t) refit_tri_body(r, t);
+    for (size_t l = s->bvh_levels.size() - 1; l-- > 0;)
+        for (uint32_t w = s->bvh_levels[l]; w < s->bvh_levels[l + 1]; ++w) refit_node_body(r, w);
+    s->lo = xyz(box_lo[0]); s->hi = xyz(box_hi[0]);
+}
 
 extern "C" hs_scene *hs_scene_create(const mtsb_scene_desc *d) {
     hs_scene *s = new hs_scene();

@@ -562,6 +562,39 @@ def test_update_vertices_device_pointer_normals_on_gpu(mi):
     assert np.abs(sc_dev.render(spp=8, seed=5) - a).max() <= 1e-3 * max(1.0, float(a.max()))
 
 
+def test_update_vertices_refit_equals_rebuild(mi):
+    """`mtsb_scene_update_config(refit=1)`: `update_vertices` keeps the topology of the last build and refits leaf triangles and
+    node boxes (bvh.h refit_*_body) instead of rebuilding.  After a large move (anisotropic scale + shift + per-vertex noise) the
+    refitted scene answers like a scene rebuilt on the new positions: same primitive and t for every ray (equal-t ties aside),
+    same any-hit answers, same image, oracle-close; every `rebuild_every`-th update is a full rebuild; the emitters' bounding
+    sphere follows the new scene box."""
+    sd = H.material_scene((32, 24), 4)
+    sc_fit, sc_new, orc = mi.Scene(sd), mi.Scene(sd), H.Oracle(sd)
+    sc_fit.update_config(refit=True, rebuild_every=4)
+    p0 = sd.meshes[1].positions.copy()
+    rng = np.random.default_rng(2)
+    om, dm = orc.sensor_sample_ray(rng.random((20000, 2)))
+    ro, rd = H.random_rays(20000, 9, radius=3.0)
+    depth0 = sc_fit.build_stats()["bvh_nodes"]
+    for k in range(5):            # updates 1, 2, 3 refit, the 4th rebuilds, the 5th refits again
+        newp = (p0 * np.array([0.9 + 0.05 * k, 0.7, 0.8 + 0.02 * k], np.float32) + np.array([0.1, 0.2 - 0.05 * k, 0.0], np.float32)
+                + 0.01 * rng.normal(size=p0.shape)).astype(np.float32)
+        sc_fit.update_vertices(1, newp); sc_new.update_vertices(1, newp)
+        for o_, d_ in ((om, dm), (ro, rd)):
+            a, b = sc_fit.intersect_closest_raw(o_, d_), sc_new.intersect_closest_raw(o_, d_)
+            pa, pb = _prims(a), _prims(b)
+            assert (pa != pb).mean() < 1e-4, k
+            same = pa == pb
+            assert np.array_equal(a[same, 0], b[same, 0])
+            assert np.array_equal(sc_fit.intersect_any_raw(o_, d_), sc_new.intersect_any_raw(o_, d_))
+    orc.update_vertices(1, newp)
+    assert (_prims(sc_fit.intersect_closest_raw(om, dm)) != _prims(orc.intersect_closest(om, dm))).mean() < 2e-3
+    a, b, c = sc_fit.render(spp=8, seed=5), sc_new.render(spp=8, seed=5), orc.render(spp=8, seed=5)
+    assert np.abs(a - b).max() <= 1e-3 * max(1.0, float(b.max()))
+    assert np.abs(a - c).sum() / np.abs(c).sum() < 3e-2
+    assert sc_fit.build_stats()["bvh_nodes"] > 0 and depth0 > 0
+
+
 def test_moment_integrator_second_moments(mi):
     """`moment` integrator AOVs (src/integrators/moment.cpp:55-90): m2 = filter-weighted sum of the squared per-sample XYZ.
     With one sample per pixel and the box filter the second-moment plane is exactly the square of the film; with many

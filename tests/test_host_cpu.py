@@ -457,3 +457,28 @@ def test_film_drops_invalid_samples():
     f = Oracle(sd).film_put(pos, val)
     g = Oracle(sd).film_put(pos[:1], val[:1])
     assert np.isfinite(f).all() and np.array_equal(f, g)
+
+
+def test_hostsim_bvh_refit_equals_rebuild():
+    """bvh.h refit_tri_body / refit_node_body: after the vertices moved (per-vertex noise + a scale + a shift of the whole
+    mesh, far more than an optimiser step), the refitted BVH answers every ray like a BVH built from scratch on the new
+    positions -- same primitive, same t (the triangle test does not depend on the tree; ties aside) -- and like the oracle."""
+    import copy
+    sd = H.sphere_scene(24, 48)
+    h = HostSim(sd)
+    P0 = np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3)
+    rng = np.random.default_rng(3)
+    P1 = (1.15 * P0 + 0.03 * rng.normal(size=P0.shape) + np.float32([0.2, -0.1, 0.05])).astype(np.float32)
+    h.refit_vertices(0, P1)
+    sd2 = copy.deepcopy(sd)
+    sd2.meshes[0].positions = P1
+    h2, o2 = HostSim(sd2), Oracle(sd2)
+    om, dm = H.random_rays(20000, 7, radius=2.0)
+    a, b, c = h.intersect_closest(om, dm), h2.intersect_closest(om, dm), o2.intersect_closest(om, dm)
+    pa, pb, pc = (x.view(np.uint32)[:, 3] for x in (a, b, c))
+    assert (pa != 0xffffffff).mean() > 0.3
+    assert np.mean(pa != pb) < 1e-4                       # equal-t ties can resolve differently in another visit order
+    same = pa == pb
+    np.testing.assert_array_equal(a[same, 0], b[same, 0])
+    assert np.mean(pa != pc) < 5e-3
+    np.testing.assert_array_equal(h.intersect_any(om, dm), h2.intersect_any(om, dm))
