@@ -286,7 +286,8 @@ int mtsb_render_grad(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, 
                      int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,
                      int mem, mtsb_stats *stats);
 /* Options of the vertex-gradient pass: boundary = 0 interior term only, 1 = + edge sampling on the film (primary
- * visibility), 2 (default) = + edge sampling seen from the first path vertex (shadow / occlusion boundaries);
+ * visibility), 2 (default) = + edge sampling seen from the first path vertex (shadow / occlusion boundaries), 3 = + the same
+ * term at every later path vertex (a shadow seen through a bounce; each depth takes half the samples of the one before);
  * edge_fraction = edge samples of each kind per path sample (default 0.25). */
 int mtsb_grad_config(mtsb_scene *scene, int boundary, float edge_fraction);
 

@@ -589,13 +589,18 @@ HD void edge_scatter_body(const SceneDev &sc, const EdgeCtx &e, const GradCtx &g
 // L_far = full incident radiance along that ray (path-traced by the normal wavefront from depth 2, emitter hits unweighted).
 // Edges are drawn by resampling: `candidates` edges proportional to their 3D length, one of those that are silhouettes from
 // x1 kept with probability proportional to its angular length / r, P = (len / total) * candidates * w_chosen / sum(w).  Covers moving shadow boundaries and occlusion
-// of indirect light as seen directly by the camera; deeper vertices are not sampled.
+// of indirect light as seen directly by the camera.
+// Deeper vertices (Edge2Ctx::depth = k > 1): the same term with x_k in the place of x1.  The prefix x1 .. x_k is an ordinary
+// sampled path (the primal shade kernel runs for k - 1 bounces), its throughput rides in the queue and multiplies L_far; x_k
+// is a material point (fixed barycentrics, as the interior term parametrises it) instead of a point pinned to a pixel.
 struct Edge2Ctx {
     const uint4 *edges; uint32_t n_edges; const float *cdf; float total_len;   // cdf over 3D edge lengths
     int candidates; float eps;                                                 // eps: angular offset of the far ray
     int moving_mesh;                                                           // the differentiated mesh (see edge2_raygen_body)
     float self_rmin;                                                           // x1 on that mesh: its own edges nearer than this many edge lengths are skipped
-    float4 *aux;                     // 4 x float4 per sample: (edge, t, |dw/dt| / P, valid) | x2 (prim, b1, b2, r2) | d | hit of x1
+    float4 *aux;                     // 5 x float4 per PATH: (edge, t, |dw/dt| / P, valid) | far hit (prim, b1, b2, r2) | d | hit of x_k | o
+    uint32_t mov_begin, mov_end;     // the differentiated mesh's edges in `edges` (candidates: half by length over all edges, half over these)
+    int depth;                       // k: the path vertex the edges are seen from (1 = the camera's hit; deeper: mtsb_grad_config boundary 3)
 };
 HD float edge_len3_body(const SceneDev &sc, const Edge2Ctx &e, uint32_t k) {
     uint4 ed = e.edges[k];
@@ -627,9 +632,10 @@ HD Edge2Geo edge2_geo(const SceneDev &sc, uint4 ed, float t, float3 x) {
     g.dwdt = norm(pe) / g.r;
     return g;
 }
-// stage B: queue entry j holds the camera ray, its hit and the sampler state; writes the far ray as a depth-2 path
+// stage B: queue entry j holds the ray into x_k, its hit and the sampler state; writes the far ray as a depth-(k+1) path
 HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBatch &b, const PathQueue &qin, const PathQueue &qout, uint32_t j) {
     float4 o4 = qin.o_mint[j], d4 = qin.d_maxt[j], h4 = qin.hit[j];
+    const uint32_t pid = qin.misc[j].x;
     Pcg32 rng = rng_load(qin.rng[j]);
     float4 rec0 = make_float4(0.f, 0.f, 0.f, 0.f), rec1 = make_float4(u2f(0xffffffffu), 0.f, 0.f, INFINITY);
     float4 ro = make_float4(0.f, 0.f, 0.f, INFINITY), rd = make_float4(0.f, 0.f, 1.f, 0.f);
@@ -644,22 +650,38 @@ HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBat
     // bumpy surface seen from a point ON it has edges at every distance down to 0, the integrand grows like len / r^2 and a
     // length-proportional edge pick has infinite variance there (measured at C4: the standard error of the sphere's own
     // pixels went from 0.03 to 4 with this term).  Documented bias: the change of a mesh's shadow on ITSELF is not sampled.
+    // Candidates come from a mixture: half of them proportional to length over ALL edges, half over the edges of the differentiated
+    // mesh (static edges only matter where the moving mesh is x_k or lies behind them; in a scene of big static polygons they would
+    // otherwise take nearly every candidate).  q = pdf per unit length relative to the plain one.
     uint32_t chosen = 0, n_sil = 0; float w_sum = 0.f, w_chosen = 0.f;
     const bool x1_on_moving = ok && si.mesh == e.moving_mesh;
+    const float *cdf = e.cdf;
+    float mov_lo = 0.f, mov_total = 0.f;
+    if (ok && e.mov_end > e.mov_begin) { mov_lo = e.mov_begin ? cdf[e.mov_begin - 1] : 0.f; mov_total = cdf[e.mov_end - 1] - mov_lo; }
+    const bool mix = mov_total > 0.f && mov_total < e.total_len;
     for (int c = 0; c < e.candidates; ++c) {          // same number of draws whatever happens: the stream stays aligned
         float u = rng.next_f32(), pick = rng.next_f32();
         if (!ok) continue;
-        float value = u * e.total_len; const float *cdf = e.cdf;
-        uint32_t k = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
+        uint32_t k;
+        if (mix && u >= 0.5f) {
+            float value = fmaf(2.f * u - 1.f, mov_total, mov_lo);
+            k = min(max(binary_search(e.mov_begin, e.mov_end, [&](uint32_t i) { return cdf[i] <= value; }), e.mov_begin), e.mov_end - 1);
+        } else {
+            float value = (mix ? 2.f * u : u) * e.total_len;
+            k = min(binary_search(0u, e.n_edges, [&](uint32_t i) { return cdf[i] <= value; }), e.n_edges - 1);
+        }
+        const float q = mix ? 0.5f + (k >= e.mov_begin && k < e.mov_end ? 0.5f * e.total_len / mov_total : 0.f) : 1.f;
         uint4 ek = e.edges[k];
         if (ek.z == si.prim || ek.w == si.prim) continue;                 // edges of x1's own face lie in its tangent plane
         Edge2Geo gk = edge2_geo(sc, ek, 0.5f, si.p);
         if (!gk.silhouette) continue;
         if (x1_on_moving && (int) sc.faces[ek.z].w == si.mesh && gk.r < e.self_rmin * norm(gk.b - gk.a)) continue;
-        float w = gk.dwdt / gk.r;
+        // resampling target: angular length / r, times a prior of 0.1 for a static edge seen from a static x_k (it only
+        // contributes when the moving mesh happens to lie behind it, which is not known before the far ray is traced)
+        float target = gk.dwdt / gk.r * ((k >= e.mov_begin && k < e.mov_end) || x1_on_moving ? 1.f : 0.1f), w = target / q;
         if (!(w > 0.f) || !(w < 1e30f)) continue;
         n_sil++; w_sum += w;
-        if (pick * w_sum < w) { chosen = k; w_chosen = w; }      // weighted reservoir
+        if (pick * w_sum < w) { chosen = k; w_chosen = target; }      // weighted reservoir
     }
     float t = rng.next_f32();
     if (ok && n_sil > 0 && w_chosen > 0.f) {
@@ -681,18 +703,20 @@ HD void edge2_raygen_body(const SceneDev &sc, const Edge2Ctx &e, const RenderBat
             }
         }
     }
-    e.aux[4 * (size_t) j] = rec0; e.aux[4 * (size_t) j + 1] = rec1; e.aux[4 * (size_t) j + 2] = d4; e.aux[4 * (size_t) j + 3] = h4;
-    qout.o_mint[j] = ro; qout.d_maxt[j] = rd; qout.thr_eta[j] = make_float4(1.f, 1.f, 1.f, 1.f);
-    qout.misc[j] = make_uint4(j, 2u | 0x80000000u, f2u(1.f), 0u);      // depth 2 after a "delta" bounce: emitter hits count fully
+    float4 *aux = e.aux + 5 * (size_t) pid;
+    aux[0] = rec0; aux[1] = rec1; aux[2] = d4; aux[3] = h4; aux[4] = o4;
+    qout.o_mint[j] = ro; qout.d_maxt[j] = rd; qout.thr_eta[j] = qin.thr_eta[j];       // prefix throughput (1 at the camera's hit)
+    qout.misc[j] = make_uint4(pid, (uint32_t) (e.depth + 1) | 0x80000000u, f2u(1.f), 0u);      // next depth after a "delta" bounce: emitter hits count fully
     rng_store(&qout.rng[j], rng);
-    b.result[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    b.result[pid] = make_float4(0.f, 0.f, 0.f, 0.f);      // whatever the prefix gathered is not part of this term
 }
 template <typename Add>
 HD void edge2_scatter_body(const SceneDev &sc, const Edge2Ctx &e, const GradCtx &g, const RenderBatch &b, uint32_t j, Add add) {
-    float4 rec0 = e.aux[4 * (size_t) j];
+    const float4 *aux = e.aux + 5 * (size_t) j;        // j = path id
+    float4 rec0 = aux[0];
     if (rec0.w == 0.f) return;
-    float4 rec1 = e.aux[4 * (size_t) j + 1], d4 = e.aux[4 * (size_t) j + 2], h4 = e.aux[4 * (size_t) j + 3];
-    SI si = make_si(sc, g.cam_o, xyz(d4), h4);
+    float4 rec1 = aux[1], d4 = aux[2], h4 = aux[3];
+    SI si = make_si(sc, xyz(aux[4]), xyz(d4), h4);
     uint4 ed = e.edges[f2u(rec0.x)];
     Edge2Geo eg = edge2_geo(sc, ed, rec0.y, si.p);
     const BsdfDev bsdf = sc.bsdfs[sc.meshes[si.mesh].bsdf];
@@ -706,7 +730,7 @@ HD void edge2_scatter_body(const SceneDev &sc, const Edge2Ctx &e, const GradCtx 
     float3 gp = eg.n_out * (c * inv_r);
     add_vertex(g, ed.x, gp * (1.f - rec0.y), add); add_vertex(g, ed.y, gp * rec0.y, add);
     VtxRec r1; r1.prim = si.prim; r1.b1 = h4.y; r1.b2 = h4.z;
-    scatter_point(g, tri_geo(sc, r1.prim), r1, true, si.p, eg.n_out * (c * (inv_r2 - inv_r)), add);
+    scatter_point(g, tri_geo(sc, r1.prim), r1, e.depth == 1, si.p, eg.n_out * (c * (inv_r2 - inv_r)), add);
     if (inv_r2 > 0.f) {
         VtxRec r2; r2.prim = f2u(rec1.x); r2.b1 = rec1.y; r2.b2 = rec1.z;
         TriGeo t2 = tri_geo(sc, r2.prim);

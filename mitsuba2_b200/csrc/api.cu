@@ -111,6 +111,7 @@ struct mtsb_scene {
     DevBuf<float4> q_p1[2], q_p2[2];         // vertex-gradient replay: previous two path vertices per queue entry
     std::map<int, std::unique_ptr<DevBuf<uint4>>> mesh_edges;   // unique edges per mesh (boundary term), built on first use
     int grad_boundary = 2; float grad_edge_fraction = 0.25f;    // mtsb_grad_config
+    std::vector<uint32_t> edge_offsets;                         // all_edge_list(): where every mesh's edges start
     DevBuf<float4> s_nee; DevBuf<uint32_t> s_occ;     // vertex-gradient replay: ShadowQueue::nee_rec / occluded
     DevBuf<float4> edge_aux;                 // boundary term seen from x1: 4 float4 per sample
     DevBuf<uint32_t> counters; DevBuf<unsigned long long> dstats;
@@ -740,18 +741,16 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
     else
     { StageTimer t(s->ctx, ST_RAYGEN); if (s->spectral) k_raygen<Spectral><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p);
       else k_raygen<Rgb><<<grid_for(n), kBlock, 0, st>>>(sn, b, make_queue(s, cur), s->counters.p); } launches++;
-    int depth0 = 1;
-    if (edge2) {      // primary hits, then one far ray per sample as the depth-2 entry of the other queue
-        PathQueue q0 = make_queue(s, 0), q1 = make_queue(s, 1);
-        { StageTimer t(s->ctx, ST_CLOSEST); if (s->shapes.empty()) k_trace<false, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p);
-          else k_trace<false, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + 1, n, q0.o_mint, q0.d_maxt, q0.hit, nullptr, s->counters.p + kWorkClosest + 1, s->ctx->refill, s->prim_class.p); }
-        { StageTimer t(s->ctx, ST_SHADE); k_edge2_raygen<<<grid_for(n), kBlock, 0, st>>>(s->dev, edge2->e, edge2->total_len, b, q0, q1, s->counters.p); }
-        launches += 2; cur = 1; depth0 = 2;
-    }
+    const int depth0 = 1;
     for (int depth = depth0; depth <= max_iter; ++depth) {
         PathQueue qin = make_queue(s, cur), qout = make_queue(s, cur ^ 1);
         { StageTimer t(s->ctx, ST_CLOSEST); if (s->shapes.empty()) k_trace<false, false><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p);
           else k_trace<false, true><<<tg, kBlock, 0, st>>>(s->dev.bvh, s->counters.p + depth, n, qin.o_mint, qin.d_maxt, qin.hit, nullptr, s->counters.p + kWorkClosest + depth, s->ctx->refill, s->prim_class.p); }
+        if (edge2 && depth == edge2->e.depth) {      // the edges are seen from this vertex: one far ray per live path as the next depth's entry
+            { StageTimer t(s->ctx, ST_SHADE); k_edge2_raygen<<<grid_for(n), kBlock, 0, st>>>(s->dev, edge2->e, edge2->total_len, b, qin, qout, s->counters.p); }
+            launches += 2; cur ^= 1;
+            continue;
+        }
         { StageTimer t(s->ctx, ST_SHADE);
           if (grad && grad->grad_pos) { if (s->ext) k_shade_grad<true, RgbX><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
                                         else k_shade_grad<true, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }

@@ -65,10 +65,12 @@ static int all_edge_list(mtsb_scene *s, const uint4 **edges, uint32_t *n_edges) 
     auto it = s->mesh_edges.find(-1);
     if (it == s->mesh_edges.end()) {
         std::vector<uint4> all, e;
+        s->edge_offsets.assign(1, 0u);
         for (size_t k = 0; k < s->meshes.size(); ++k) {
             const MeshDev &m = s->meshes[k];
             build_edge_list(s->mesh_faces[k].data(), m.face_count, m.vert_begin, m.face_begin, e);
             all.insert(all.end(), e.begin(), e.end());
+            s->edge_offsets.push_back((uint32_t) all.size());      // mesh k's edges = [edge_offsets[k], edge_offsets[k + 1])
         }
         std::unique_ptr<DevBuf<uint4>> buf(new DevBuf<uint4>());
         CU(buf->upload(all.data(), all.size(), s->ctx->stream));
@@ -212,6 +214,7 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
                 Edge2Launch l2; Edge2Ctx &e2 = l2.e;
                 RC(all_edge_list(s, &e2.edges, &e2.n_edges));
                 e2.candidates = 32; e2.eps = 1e-3f; e2.total_len = 0.f; e2.moving_mesh = mesh_id; e2.self_rmin = 1e30f;      // all of them (3 and 8 edge lengths were measured: more noise, same bias)
+                e2.mov_begin = s->edge_offsets[mesh_id]; e2.mov_end = s->edge_offsets[mesh_id + 1]; e2.depth = 1;
                 DevBuf<float> len3, cdf3; DevBuf<unsigned char> tmp2;
                 CU(len3.alloc(e2.n_edges)); CU(cdf3.alloc(e2.n_edges));
                 k_edge_len3<<<grid_for(e2.n_edges), kBlock, 0, st>>>(s->dev, e2, len3.p); launches++;
@@ -219,20 +222,27 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
                 CU(cub::DeviceScan::InclusiveSum(nullptr, tmp2_bytes, len3.p, cdf3.p, (int) e2.n_edges, st)); CU(tmp2.alloc(tmp2_bytes));
                 CU(cub::DeviceScan::InclusiveSum(tmp2.p, tmp2_bytes, len3.p, cdf3.p, (int) e2.n_edges, st)); launches++;
                 e2.cdf = cdf3.p; l2.total_len = cdf3.p + (e2.n_edges - 1);
-                CU(s->edge_aux.alloc(4 * (size_t) s->pool)); e2.aux = s->edge_aux.p;
-                // sample counts per pixel follow the path samples: the same (begin, count, total) split, scaled
-                uint32_t s2_total = (uint32_t) ceil((double) spp_total * frac); if (s2_total < 1) s2_total = 1;
-                uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
-                GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
-                uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
-                for (uint64_t off = 0; off < total2; off += s->pool) {
-                    uint32_t n2 = (uint32_t) ((total2 - off) < s->pool ? (total2 - off) : s->pool);
-                    RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
-                    b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = s->result.p;
-                    RC(run_batch(s, sn, b, nullptr, false, launches, nullptr, &l2));
-                    if (wide) { k_path_adjoint<<<grid_for(n2), kBlock, 0, st>>>(sn, b, g2, s->path_dl.p); launches++; }
-                    k_edge2_scatter<<<grid_for(n2), kBlock, 0, st>>>(s->dev, e2, g2, b); launches++;
-                    edge_samples += n2 / 2;
+                CU(s->edge_aux.alloc(5 * (size_t) s->pool)); e2.aux = s->edge_aux.p;
+                // the vertex the edges are seen from: the camera's hit (boundary 2), or every vertex that can still be followed by
+                // another one (boundary 3), each depth with its own samples -- half as many as the one before
+                const int k_last = s->grad_boundary >= 3 ? (s->dev.max_depth - 1 < 8 ? s->dev.max_depth - 1 : 8) : 1;
+                for (int k = 1; k <= k_last; ++k) {
+                    e2.depth = k;
+                    // sample counts per pixel follow the path samples: the same (begin, count, total) split, scaled
+                    uint32_t s2_total = (uint32_t) ceil((double) spp_total * frac / (double) (1u << (k - 1))); if (s2_total < 1) s2_total = 1;
+                    uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
+                    GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
+                    uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
+                    for (uint64_t off = 0; off < total2; off += s->pool) {
+                        uint32_t n2 = (uint32_t) ((total2 - off) < s->pool ? (total2 - off) : s->pool);
+                        RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
+                        b.seed = (seed ^ 0x51ed270b7f4a7c15ull) + 0x9e3779b97f4a7c15ull * (uint64_t) (k - 1); b.result = s->result.p;
+                        if (k > 1) CU(cudaMemsetAsync(e2.aux, 0, 5 * (size_t) n2 * sizeof(float4), st));      // paths that end before vertex k carry no sample
+                        RC(run_batch(s, sn, b, nullptr, false, launches, nullptr, &l2));
+                        if (wide) { k_path_adjoint<<<grid_for(n2), kBlock, 0, st>>>(sn, b, g2, s->path_dl.p); launches++; }
+                        k_edge2_scatter<<<grid_for(n2), kBlock, 0, st>>>(s->dev, e2, g2, b); launches++;
+                        edge_samples += n2 / 2;
+                    }
                 }
                 CU(cudaStreamSynchronize(st));
             }

@@ -683,11 +683,13 @@ __global__ void k_edge_len3(SceneDev sc, Edge2Ctx e, float *len) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k < e.n_edges) len[k] = edge_len3_body(sc, e, k);
 }
+// every live queue entry of depth e.depth continues 1:1 as the far ray of its edge sample (a zero-length ray where there is none)
 __global__ void k_edge2_raygen(SceneDev sc, Edge2Ctx e, const float *total_len, RenderBatch b, PathQueue qin, PathQueue qout, uint32_t *counters) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j == 0) counters[2] = b.n_paths;
+    const uint32_t count = counters[e.depth];
+    if (j == 0) counters[e.depth + 1] = count;
     e.total_len = *total_len;
-    if (j < b.n_paths) edge2_raygen_body(sc, e, b, qin, qout, j);
+    if (j < count) edge2_raygen_body(sc, e, b, qin, qout, j);
 }
 __global__ void k_edge2_scatter(SceneDev sc, Edge2Ctx e, GradCtx g, RenderBatch b) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;

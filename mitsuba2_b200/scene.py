@@ -309,7 +309,8 @@ class Scene:
     # ---- gradient pass ----------------------------------------------------------------------------
     def grad_config(self, boundary=2, edge_fraction=0.25):
         """Options of the vertex-gradient pass: `boundary` 0 / False = interior term only, 1 = + edge sampling on the film
-        (primary visibility), 2 / True = + edge sampling seen from the first path vertex (shadows, occlusion);
+        (primary visibility), 2 / True = + edge sampling seen from the first path vertex (shadows, occlusion), 3 = + the same
+        term at every later path vertex (a shadow seen through a bounce);
         `edge_fraction` = edge samples of each kind per path sample."""
         boundary = 2 if boundary is True else int(boundary)
         A.check(A.lib().mtsb_grad_config(self._h, boundary, float(edge_fraction)))

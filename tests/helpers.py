@@ -688,12 +688,22 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         ms.bsdf, ms.texcoords = b, None
         sd.add_mesh(ms)
         sd.add_point([0.6, 0.8, -3.0], [40, 40, 40])
+    if kind == "indirectshadow":  # a wall lit by a floor that carries the moving quad's shadow: the upper image rows see the quad and
+        # its shadow only through one diffuse bounce (boundary terms of the SECOND path vertex and of the first)
+        P, F = grid_mesh(2, 2, 1.2, [0.1, -0.3, 0.2], [0, 0, 1], [1, 0, 0])          # horizontal quad, normal +y
+        sd.add_mesh(Mesh(P, F, bsdf=b))
+        P2, F2 = grid_mesh(1, 1, 8.0, [0, 0, 1.0], [1, 0, 0], [0, -1, 0])            # wall facing the camera
+        sd.add_mesh(Mesh(P2, F2, bsdf=bw))
+        P3, F3 = grid_mesh(1, 1, 12.0, [0, -1.0, 0.0], [0, 0, 1], [1, 0, 0])         # floor, normal +y
+        sd.add_mesh(Mesh(P3, F3, bsdf=sd.add_diffuse([0.8, 0.8, 0.8])))
+        P4, F4 = grid_mesh(1, 1, 1.5, [0.0, 2.5, 0.0], [1, 0, 0], [0, 0, 1])         # light panel facing down
+        sd.add_mesh(Mesh(P4, F4, bsdf=bw), area_radiance=[30, 30, 30])
     if kind == "quadenv":
         P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P, F, bsdf=b))
         sd.add_constant([1.0, 1.0, 1.0])
     sd.add_perspective(look_at([0, 0, -3.0], [0, 0, 0], [0, 1, 0]), 40.0, 0.01, 100.0, res, res, "box")
-    sd.max_depth, sd.rr_depth, sd.spp = (2 if kind in ("wavy", "texplane", "smoothsphere") else 4), 100, spp
+    sd.max_depth, sd.rr_depth, sd.spp = (2 if kind in ("wavy", "texplane", "smoothsphere") else (3 if kind == "indirectshadow" else 4)), 100, spp
     return sd
 
 

@@ -304,16 +304,6 @@ static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b,
     std::vector<uint2> fast(8);
     uint32_t n = b.n_paths; int cur = 0, depth0 = 1; uint32_t count = n;
     if (raygen) for (uint32_t i = 0; i < n; ++i) raygen_body<M>(sn, b, P.queue(cur), i);
-    if (edge2) {       // run_batch(edge2) in api.cu: primary hits, then the far rays as depth-2 entries of the other queue
-        PathQueue q0 = P.queue(0), q1 = P.queue(1);
-        for (uint32_t i = 0; i < n; ++i) {
-            TravStack<8, 56> st; st.fast = fast.data(); st.stride = 1; Hit h;
-            bvh_trace<false>(s->dev.bvh, xyz(q0.o_mint[i]), xyz(q0.d_maxt[i]), q0.o_mint[i].w, q0.d_maxt[i].w, st, h);
-            q0.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
-        }
-        for (uint32_t i = 0; i < n; ++i) edge2_raygen_body(s->dev, *edge2, b, q0, q1, i);
-        cur = 1; depth0 = 2;
-    }
     for (int depth = depth0; count > 0 && depth <= s->dev.max_depth; ++depth) {
         PathQueue qin = P.queue(cur), qout = P.queue(cur ^ 1);
         for (uint32_t i = 0; i < count; ++i) {
@@ -322,6 +312,11 @@ static void hs_run_batch(hs_scene *s, const SensorDev &sn, const RenderBatch &b,
             qin.hit[i] = make_float4(h.t, h.u, h.v, u2f(h.prim));
         }
         cnt[0] += count; cnt[2] += count;
+        if (edge2 && depth == edge2->depth) {      // run_batch(edge2) in api.cu: the far rays are the next depth's entries, 1:1
+            for (uint32_t i = 0; i < count; ++i) edge2_raygen_body(s->dev, *edge2, b, qin, qout, i);
+            cur ^= 1;
+            continue;
+        }
         uint32_t next = 0, nshadow = 0;
         for (uint32_t i = 0; i < count; ++i) {
             ShadeOut out = shade_body<M>(s->dev, qin, b, i, grad);
@@ -456,9 +451,10 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
     if (boundary < 2) return;
     // ---- boundary term seen from the first path vertex (same sequence as mtsb_render_grad)
     // edges of ALL meshes, mesh by mesh (all_edge_list() in grad.cuh): static occluders sweep over moving material too
-    std::vector<uint4> all_edges;
+    std::vector<uint4> all_edges; uint32_t mov_begin = 0, mov_end = 0;
     for (size_t mi = 0; mi < s->meshes.size(); ++mi) {
         const MeshDev &mm = s->meshes[mi];
+        if ((int) mi == mesh_id) mov_begin = (uint32_t) all_edges.size();
         std::vector<std::pair<uint64_t, uint32_t>> k2;
         for (uint32_t f = 0; f < mm.face_count; ++f) { uint4 fc = s->faces[mm.face_begin + f]; uint32_t v[3] = { fc.x, fc.y, fc.z };
             for (int k = 0; k < 3; ++k) { uint32_t a = v[k], c = v[(k + 1) % 3]; if (a > c) std::swap(a, c); k2.emplace_back(((uint64_t) a << 32) | c, mm.face_begin + f); } }
@@ -468,23 +464,30 @@ extern "C" void hs_render_grad(hs_scene *s, uint32_t sensor_id, uint32_t spp_beg
             all_edges.push_back(make_uint4((uint32_t) (k2[i].first >> 32), (uint32_t) k2[i].first, k2[i].second, j - i > 1 ? k2[i + 1].second : 0xffffffffu));
             i = j;
         }
+        if ((int) mi == mesh_id) mov_end = (uint32_t) all_edges.size();
     }
     Edge2Ctx e2; e2.edges = all_edges.data(); e2.n_edges = (uint32_t) all_edges.size(); e2.candidates = 32; e2.eps = 1e-3f; e2.moving_mesh = mesh_id; e2.self_rmin = 1e30f;
+    e2.mov_begin = mov_begin; e2.mov_end = mov_end; e2.depth = 1;
     std::vector<float> cdf3(all_edges.size()); acc = 0;
     for (uint32_t k = 0; k < e2.n_edges; ++k) { acc += edge_len3_body(s->dev, e2, k); cdf3[k] = (float) acc; }
     e2.cdf = cdf3.data(); e2.total_len = (float) acc;
-    std::vector<float4> aux(4 * (size_t) pool); e2.aux = aux.data();
-    uint32_t s2_total = (uint32_t) ceil((double) spp_total * edge_fraction); if (s2_total < 1) s2_total = 1;
-    uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
-    GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
-    uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
-    for (uint64_t off = 0; off < total2; off += pool) {
-        uint32_t n2 = (uint32_t) std::min<uint64_t>(pool, total2 - off);
-        RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
-        b.seed = seed ^ 0x51ed270b7f4a7c15ull; b.result = P.result.data();
-        hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad(), true, &e2);
-        if (wide) fill_path_dl(b, g2);
-        for (uint32_t j = 0; j < n2; ++j) edge2_scatter_body(s->dev, e2, g2, b, j, HostAdd());
+    std::vector<float4> aux(5 * (size_t) pool); e2.aux = aux.data();
+    const int k_last = boundary >= 3 ? std::min(s->dev.max_depth - 1, 8) : 1;
+    for (int k = 1; k <= k_last; ++k) {
+        e2.depth = k;
+        uint32_t s2_total = (uint32_t) ceil((double) spp_total * edge_fraction / (double) (1u << (k - 1))); if (s2_total < 1) s2_total = 1;
+        uint32_t s2_begin = (uint32_t) ((uint64_t) spp_begin * s2_total / spp_total), s2_end = (uint32_t) ((uint64_t) (spp_begin + spp_count) * s2_total / spp_total);
+        GradCtx g2 = g; g2.scale = 1.f / (float) s2_total;
+        uint64_t total2 = npix * (uint64_t) (s2_end - s2_begin);
+        for (uint64_t off = 0; off < total2; off += pool) {
+            uint32_t n2 = (uint32_t) std::min<uint64_t>(pool, total2 - off);
+            RenderBatch b; b.n_paths = n2; b.offset = off; b.spp_begin = s2_begin; b.spp_batch = s2_end - s2_begin; b.spp_total = s2_total;
+            b.seed = (seed ^ 0x51ed270b7f4a7c15ull) + 0x9e3779b97f4a7c15ull * (uint64_t) (k - 1); b.result = P.result.data();
+            if (k > 1) std::fill(aux.begin(), aux.begin() + 5 * (size_t) n2, make_float4(0.f, 0.f, 0.f, 0.f));
+            hs_run_batch<RgbX>(s, sn, b, P, cnt, NoGrad(), true, &e2);
+            if (wide) fill_path_dl(b, g2);
+            for (uint32_t j = 0; j < n2; ++j) edge2_scatter_body(s->dev, e2, g2, b, j, HostAdd());
+        }
     }
 }
 

@@ -434,6 +434,33 @@ def test_gradients_under_wide_reconstruction_filters(mi, rfilter):
         assert abs(float((gv * F[n]).sum()) - fd) < 0.06 * ref, (n, float((gv * F[n]).sum()), fd)
 
 
+def test_vertex_gradient_boundary_term_of_deeper_vertices_matches_host_replay(mi):
+    """`grad_config(boundary=3)`: the edge-sampling term at the second and later path vertices (a shadow seen through a diffuse
+    bounce; tests/test_grad_cpu.py holds it to finite differences of the oracle).  GPU vs the host simulator on the same samples,
+    and the sample ranges of two calls add up to the single call."""
+    res = 16
+    sd = H.vgrad_scene("indirectshadow", "diffuse", res=res, spp=64)
+    wgt = np.zeros((res, res, 3), np.float32)
+    wgt[:res // 2 - 1] = 1.0
+    sc = mi.Scene(sd)
+    sc.grad_config(boundary=3, edge_fraction=1.0)
+    g = sc.render_grad(wgt, spp=64, seed=3, mesh_id=0)[1].reshape(-1, 3)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 0, seed=3, boundary=3, edge_fraction=1.0).reshape(-1, 3)
+    F = H.displacement_fields(np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3))
+    ref = max(abs(float((gh * F[n]).sum())) for n in ("ty", "tz", "scale"))
+    for n in ("tx", "ty", "tz", "scale"):
+        a, b = float((g * F[n]).sum()), float((gh * F[n]).sum())
+        assert abs(a - b) < 2e-2 * ref, (n, a, b)
+    sc.grad_config(boundary=2, edge_fraction=1.0)
+    g2 = sc.render_grad(wgt, spp=64, seed=3, mesh_id=0)[1].reshape(-1, 3)
+    assert abs(float(((g - g2) * F["scale"]).sum())) > 0.2 * ref          # the deeper term is a large part of this derivative
+    sc.grad_config(boundary=3, edge_fraction=0.5)
+    full = sc.render_grad(wgt, spp=8, seed=2, mesh_id=0)[1]
+    p1 = sc.render_grad(wgt, spp=3, seed=2, mesh_id=0, spp_begin=0, spp_total=8)[1]
+    p2 = sc.render_grad(wgt, spp=5, seed=2, mesh_id=0, spp_begin=3, spp_total=8)[1]
+    np.testing.assert_allclose(p1 + p2, full, rtol=1e-3, atol=1e-4 * np.abs(full).max())
+
+
 def test_vertex_gradient_rejects_unsupported(mi):
     sd = H.vgrad_scene("corner", "diffuse", res=8, spp=2)
     sc = mi.Scene(sd)

@@ -251,3 +251,26 @@ def test_gradients_under_wide_reconstruction_filters(rfilter):
     ref = max(abs(v) for v in fds.values())
     for n, fd in fds.items():
         assert abs(float((gv * F[n]).sum()) - fd) < 0.04 * ref, (n, float((gv * F[n]).sum()), fd)
+
+
+def test_vertex_gradient_boundary_term_of_the_second_path_vertex():
+    """`boundary=3`: the edge-sampling term of adjoint.h evaluated at the deeper path vertices too.  A wall is lit by a floor that
+    carries the soft shadow of the moving quad; only image rows that see the wall count, so the quad and its shadow act through one
+    diffuse bounce: the quad occludes the floor as seen from the wall (term of x1) and the light as seen from the floor (term of
+    x2).  With the x1 term alone the vertical translation and the scale derivative are far off (7.2 / 7.4 against finite
+    differences of 5.3 / 1.9); with the x2 term they agree within the Monte Carlo noise of the two estimates."""
+    res = 16
+    sd = H.vgrad_scene("indirectshadow", "diffuse", res=res, spp=256)
+    wgt = np.zeros((res, res, 3), np.float32)
+    wgt[:res // 2 - 1] = 1.0
+    h = HostSim(sd)
+    F = H.displacement_fields(np.asarray(sd.meshes[0].positions, np.float32).reshape(-1, 3))
+    fd = {n: float(np.mean([H.oracle_fd_vertices(sd, 0, wgt, F[n].astype(np.float32), 0.03, 4096, s_) for s_ in (3, 4)])) for n in ("ty", "tz", "scale")}
+    g2 = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=2, edge_fraction=1.0).reshape(-1, 3) for s_ in range(3, 7)], axis=0)
+    g3 = np.mean([h.render_grad_vertices(wgt, 0, seed=s_, boundary=3, edge_fraction=1.0).reshape(-1, 3) for s_ in range(3, 11)], axis=0)
+    a2 = {n: float((g2 * F[n]).sum()) for n in fd}
+    a3 = {n: float((g3 * F[n]).sum()) for n in fd}
+    ref = max(abs(v) for v in fd.values())
+    assert abs(a2["scale"] - fd["scale"]) > 0.5 * ref and abs(a2["ty"] - fd["ty"]) > 0.2 * ref, (a2, fd)     # the x2 term matters here
+    for n in fd:                                                                                        # standard errors: 0.4 - 0.5
+        assert abs(a3[n] - fd[n]) < 0.25 * ref, (n, a3, fd)
