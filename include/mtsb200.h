@@ -280,7 +280,8 @@ int mtsb_film_device_ptr(mtsb_scene *scene, uint32_t sensor_id, void **ptr, uint
  * Vertex gradients = interior term (path-space adjoint) + boundary terms (edge sampling on the film and from x1), see
  * mitsuba2_b200/csrc/adjoint.h.  Any reconstruction filter: under a filter wider than a pixel a sample's adjoint weight is the
  * gather of dL_dimage over its footprint divided by the film's weight channel of all spp_total samples (hdrfilm.cpp develop).
- * MTSB_MODE_RGB is required. */
+ * MTSB_MODE_RGB is required; `mesh_id` may carry an area light (its emitter samples move with the mesh) unless it has vertex
+ * normals; analytic shapes are not differentiated. */
 int mtsb_render_grad(mtsb_scene *scene, uint32_t sensor_id, uint32_t spp_begin, uint32_t spp_count,
                      uint32_t spp_total, uint64_t seed, const float *dL_dimage,
                      int32_t tex_id, float *grad_texture, int32_t mesh_id, float *grad_vertices,

@@ -349,6 +349,32 @@ template <typename Add, bool Vtx = true> struct ReplayGrad {
 };
 
 // emitter sample at x_k, differentiated once its shadow ray is known to be free (k_nee_grad after k_shadow): factor
+// The emitter sample of (sx, sy) as a material point: which area light, and when that light's mesh is `mesh_id` (a triangle mesh)
+// the triangle and the barycentrics of Mesh::sample_position (emit.h area_sample_direction, same arithmetic).  False otherwise.
+HD bool nee_sample_on_mesh(const SceneDev &sc, int mesh_id, float sx, float sy, VtxRec &rec) {
+    if (sc.n_emitters == 0) return false;
+    uint32_t index = 0;
+    if (sc.n_emitters > 1) {
+        float ne = (float) sc.n_emitters;
+        index = min((uint32_t) (sx * ne), (uint32_t) sc.n_emitters - 1);
+        sx = (sx - (float) index * (1.f / ne)) * ne;
+    }
+    const EmitterDev &e = sc.emitters[index];
+    if (e.type != 0 || e.mesh != mesh_id || e.cdf == nullptr) return false;
+    const MeshDev m = sc.meshes[e.mesh];
+    float value = sy * e.cdf_sum;
+    const float *cdf = e.cdf;
+    uint32_t idx = binary_search(e.valid_lo, e.valid_hi, [&](uint32_t i) { return cdf[i] < value; });
+    uint4 f = sc.faces[m.face_begin + idx];
+    float3 p0 = ld3(sc.pos, f.x), e0 = ld3(sc.pos, f.y) - p0, e1 = ld3(sc.pos, f.z) - p0;
+    float pmf = 0.5f * norm(cross(e0, e1)) * e.normalization;
+    float cdf_prev = idx > 0 ? cdf[idx - 1] * e.normalization : 0.f;
+    sy = (sy - cdf_prev) / pmf;
+    float t = safe_sqrt(1.f - sx);
+    rec.prim = m.face_begin + idx; rec.b1 = 1.f - t; rec.b2 = t * sy;
+    return true;
+}
+
 // f_s(x_{k-1}, x_k, y) G~(x_k, y), weighted by the sample's own contribution.  `rec` = ShadowQueue::nee_rec (queue index of
 // the vertex, the two sampling numbers, depth; depth 0 = path already passed a delta vertex), `contrib` = the shadow
 // record's contribution and path id.  The queue entry of the vertex is still intact at that point of the batch.
@@ -363,11 +389,16 @@ HD void nee_adjoint(const SceneDev &sc, const GradCtx &g, const PathQueue &q, co
     float3 xA = g.cam_o;
     if (depth > 1) { recA = vtx_rec(q.prev1[i]); xA = tri_point(tri_geo(sc, recA.prim), recA); }
     VtxRec recB; recB.prim = si.prim; recB.b1 = hc.y; recB.b2 = hc.z;
-    // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point
+    // area light: fixed point with a normal; envmap / constant background: fixed direction; point light: fixed point.
+    // An area light on the differentiated mesh: the sample is a material point of that mesh (triangle and barycentrics are what
+    // the sampler fixed; the triangle's probability and the uniform barycentric density are detached like every sampling
+    // decision), so the factor is the attached-surface one: |N . d| / r^3 with the UNNORMALISED normal carries the area Jacobian.
     int kind = ds.etype == 0 ? kEndFixedArea : (ds.etype == 3 ? kEndFixedPoint : kEndDirection);
+    VtxRec recC = recB;
+    if (ds.etype == 0 && nee_sample_on_mesh(sc, g.mesh_id, rec.y, rec.z, recC)) kind = kEndSurface;
     float3 xC = kind == kEndDirection ? ds.d : ds.p;
     float3 w = image_adjoint(g, b, path_id) * xyz(contrib);
-    vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recB, ds.n, w, add);
+    vertex_triple(sc, g, xA, recA, depth == 2, si, recB, depth == 1, kind, xC, recC, ds.n, w, add);
 }
 
 // ---- boundary term: edge sampling on the film plane ---------------------------------------------------------------

@@ -105,7 +105,8 @@ extern "C" int mtsb_render_grad(mtsb_scene *s, uint32_t sensor_id, uint32_t spp_
     }
     if (grad_vertices) {
         CHECK_ARG(mesh_id >= 0 && (size_t) mesh_id < s->n_tri_meshes);
-        if (s->meshes[mesh_id].emitter >= 0) return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex gradients of an emitter mesh are not supported");
+        if (s->meshes[mesh_id].emitter >= 0 && s->meshes[mesh_id].has_normals)      // the sampler's pdf uses the interpolated normal there
+            return fail(MTSB_E_INVALID, "mtsb_render_grad: vertex gradients of an emitter mesh with vertex normals are not supported");
         nvert = 3 * (size_t) s->meshes[mesh_id].vert_count;
     }
     CU(cudaSetDevice(s->ctx->device));

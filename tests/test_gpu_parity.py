@@ -461,11 +461,32 @@ def test_vertex_gradient_boundary_term_of_deeper_vertices_matches_host_replay(mi
     np.testing.assert_allclose(p1 + p2, full, rtol=1e-3, atol=1e-4 * np.abs(full).max())
 
 
+def test_vertex_gradient_of_an_emitter_mesh_matches_host_replay_and_fd(mi):
+    """Vertex positions of the mesh that carries the area light: emitter samples are material points of the moving mesh (the
+    attached-surface factor |N . d| / r^3 with the unnormalised normal carries the area Jacobian; sampling probabilities are
+    detached), hits by BSDF sampling are ordinary path vertices.  GPU vs host simulator on the same samples, and the fields
+    vs finite differences of the oracle (tests/test_grad_cpu.py has the tighter CPU bars)."""
+    sd = H.vgrad_scene("corner", "beckmann", res=16, spp=128)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    sc = mi.Scene(sd)
+    g = np.mean([sc.render_grad(wgt, spp=128, seed=s_, mesh_id=1)[1].reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
+    g3 = sc.render_grad(wgt, spp=128, seed=3, mesh_id=1)[1].reshape(-1, 3)
+    gh = H.HostSim(sd).render_grad_vertices(wgt, 1, seed=3).reshape(-1, 3)
+    np.testing.assert_allclose(g3, gh, rtol=2e-2, atol=5e-3 * np.abs(gh).max())
+    F = H.displacement_fields(np.asarray(sd.meshes[1].positions, np.float32).reshape(-1, 3))
+    fds = {n: float(np.mean([H.oracle_fd_vertices(sd, 1, wgt, F[n].astype(np.float32), 0.02, 1024, s_) for s_ in (3, 4)])) for n in ("ty", "tz", "scale")}
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < 0.03 * abs(fd), (n, float((g * F[n]).sum()), fd)
+
+
 def test_vertex_gradient_rejects_unsupported(mi):
+    from mitsuba2_b200 import mesh as M
     sd = H.vgrad_scene("corner", "diffuse", res=8, spp=2)
+    lm = sd.meshes[1]                                                          # the area light: give it vertex normals
+    lm.normals = M.compute_vertex_normals(lm.positions, lm.faces).astype(np.float32)
     sc = mi.Scene(sd)
     with pytest.raises(Exception):
-        sc.render_grad(np.ones((8, 8, 3), np.float32), spp=2, mesh_id=1)      # mesh 1 carries the area light
+        sc.render_grad(np.ones((8, 8, 3), np.float32), spp=2, mesh_id=1)
 
 
 

@@ -274,3 +274,21 @@ def test_vertex_gradient_boundary_term_of_the_second_path_vertex():
     assert abs(a2["scale"] - fd["scale"]) > 0.5 * ref and abs(a2["ty"] - fd["ty"]) > 0.2 * ref, (a2, fd)     # the x2 term matters here
     for n in fd:                                                                                        # standard errors: 0.4 - 0.5
         assert abs(a3[n] - fd[n]) < 0.25 * ref, (n, a3, fd)
+
+
+@pytest.mark.parametrize("kind,bsdf", [("planearea", "diffuse"), ("corner", "beckmann")])
+def test_vertex_gradient_of_an_emitter_mesh(kind, bsdf):
+    """The differentiated mesh carries the area light (outside the view: the image changes only through the illumination).
+    Emitter samples are material points of the moving mesh -- triangle and barycentrics as the sampler fixed them, the
+    attached-surface factor |N . d| / r^3 of vertex_triple with the unnormalised normal carries the area Jacobian, the
+    sampling probabilities and MIS weights are detached -- and a hit by BSDF sampling is an ordinary path vertex.  Against
+    finite differences of the oracle: translations, scale (changes the light's area) and tilt."""
+    sd = H.vgrad_scene(kind, bsdf, res=16, spp=256)
+    wgt = np.random.default_rng(1).uniform(0.5, 1.5, (16, 16, 3)).astype(np.float32)
+    h = HostSim(sd)
+    g = np.mean([h.render_grad_vertices(wgt, 1, seed=s_).reshape(-1, 3) for s_ in (3, 4, 5, 6)], axis=0)
+    F = H.displacement_fields(np.asarray(sd.meshes[1].positions, np.float32).reshape(-1, 3))
+    fds = {n: float(np.mean([H.oracle_fd_vertices(sd, 1, wgt, F[n].astype(np.float32), 0.02, 2048, s_) for s_ in (3, 4)])) for n in ("tx", "ty", "tz", "scale")}
+    ref = max(abs(v) for v in fds.values())
+    for n, fd in fds.items():
+        assert abs(float((g * F[n]).sum()) - fd) < 0.015 * abs(fd) + 0.004 * ref, (n, float((g * F[n]).sum()), fd)
