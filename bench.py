@@ -453,6 +453,8 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):      # NCCL prints its version line on stdout: keep stdout to the one JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mi.set_variant("cuda_b200_rgb")
     t_build = time.perf_counter()
