@@ -647,7 +647,7 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
     is the differentiated one.  plane*: one big plane filling the view (interior term only); quadenv: a small quad in
     front of a constant background (boundary term only); corner: plane + wall + area light outside the view."""
     sd = SceneData()
-    if bsdf == "diffuse":
+    if bsdf in ("diffuse", "diffuse_sky"):
         b = sd.add_diffuse([0.6, 0.5, 0.4])
     elif bsdf == "beckmann":
         b = sd.add_roughconductor(material="Cu", alpha=0.3)
@@ -696,8 +696,11 @@ def vgrad_scene(kind, bsdf="diffuse", res=24, spp=64):
         sd.add_mesh(Mesh(P2, F2, bsdf=bw))
         P3, F3 = grid_mesh(1, 1, 12.0, [0, -1.0, 0.0], [0, 0, 1], [1, 0, 0])         # floor, normal +y
         sd.add_mesh(Mesh(P3, F3, bsdf=sd.add_diffuse([0.8, 0.8, 0.8])))
-        P4, F4 = grid_mesh(1, 1, 1.5, [0.0, 2.5, 0.0], [1, 0, 0], [0, 0, 1])         # light panel facing down
-        sd.add_mesh(Mesh(P4, F4, bsdf=bw), area_radiance=[30, 30, 30])
+        if bsdf == "diffuse_sky":     # variant with a closed-form answer: uniform sky instead of the light panel
+            sd.add_constant([1.0, 1.0, 1.0])
+        else:
+            P4, F4 = grid_mesh(1, 1, 1.5, [0.0, 2.5, 0.0], [1, 0, 0], [0, 0, 1])         # light panel facing down
+            sd.add_mesh(Mesh(P4, F4, bsdf=bw), area_radiance=[30, 30, 30])
     if kind == "quadenv":
         P, F = grid_mesh(2, 2, 1.0, [0.1, 0.05, 0.0], [1, 0, 0], [0, -1, 0])
         sd.add_mesh(Mesh(P, F, bsdf=b))
