@@ -359,10 +359,11 @@ def test_x1_boundary_term_against_analytic_form_factors():
 def test_deeper_boundary_term_against_a_quadrature_of_the_transport():
     """The boundary term of the second path vertex against a deterministic answer.  `indirectshadow` under a uniform sky with
     max_depth 3: the wall's pixels receive sky light (static), the floor's reflection -- the floor is lit by the sky minus the
-    closed-form form factors of the quad and of the wall, and is hidden from the wall where the quad is in the way -- and the
-    reflection of the quad's own lit top.  Integrating that over the floor and the quad on a grid and differencing it in the quad's
-    motion gives ty / tz / scale = -4.44 / 2.38 / -4.40 (grid 960 x 560; the 360 x 210 grid used here moves them by 0.1).  The
-    adjoint with the x1 term only misses a third of the scale derivative (-2.89); with the deeper term it is within 8 %."""
+    closed-form form factors of the quad and of the wall (plus the part both count), and is hidden from the wall where the quad is
+    in the way -- and the reflection of the quad's own lit top.  Integrating that over the floor and the quad on a grid and
+    differencing it in the quad's motion gives ty / tz / scale = -4.34 / 2.46 / -4.21 (the grid moves them by about 0.1; the floor
+    radiance of the model was checked against renders at four points: 0.1762 / 0.1776, 0.613 / 0.6156, ...).  The adjoint with the x1
+    term only misses a third of the scale derivative (-2.95); with the deeper term it gives -4.15 / 2.30 / -4.10."""
     res = 16
     sd = H.vgrad_scene("indirectshadow", "diffuse_sky", res=res, spp=256)
     o, h = Oracle(sd), HostSim(sd)
@@ -383,6 +384,18 @@ def test_deeper_boundary_term_against_a_quadrature_of_the_transport():
             tot += np.arccos(np.clip((a * b).sum(1), -1, 1)) * (cr @ n) / np.maximum(np.linalg.norm(cr, axis=1), 1e-30)
         return np.abs(tot) / (2 * np.pi)
 
+    def ff_rect(X, x0, x1_, zlo, z1, y):          # rectangle [x0, x1] x [zlo, z1] in the plane y, zlo per point
+        mk = lambda x, z: np.stack([np.full(len(X), x), np.full(len(X), y), np.broadcast_to(z, (len(X),))], 1)  # noqa: E731
+        V = [q - X for q in (mk(x0, zlo), mk(x1_, zlo), mk(x1_, z1), mk(x0, z1))]
+        V = [v / np.linalg.norm(v, axis=1, keepdims=True) for v in V]
+        tot = np.zeros(len(X))
+        for i in range(4):
+            a, b = V[i], V[(i + 1) % 4]
+            cr = np.cross(a, b)
+            ln = np.linalg.norm(cr, axis=1)
+            tot += np.where(ln > 1e-14, np.arccos(np.clip((a * b).sum(1), -1, 1)) * cr[:, 1] / np.maximum(ln, 1e-30), 0.0)
+        return np.abs(tot) / (2 * np.pi)
+
     oo, dd = o.sensor_sample_ray(np.array([[(px + a) / res, (py + b) / res] for py in range(rows) for px in range(res)
                                            for b in (0.25, 0.75) for a in (0.25, 0.75)], np.float32))
     O, D = oo[:, :3].astype(np.float64), dd[:, :3].astype(np.float64)
@@ -396,8 +409,12 @@ def test_deeper_boundary_term_against_a_quadrature_of_the_transport():
     def total(shift, s):
         c = [q + shift + s * (q - qc) for q in (np.array([qlo[0], qlo[1], qlo[2]]), np.array([qhi[0], qlo[1], qlo[2]]),
                                                   np.array([qhi[0], qlo[1], qhi[2]]), np.array([qlo[0], qlo[1], qhi[2]]))]
-        Lf = alb_floor * (1 - ff_poly(X2, up, c) - FW)
         x0, x1_, z0, z1, yq = c[0][0], c[1][0], c[0][2], c[2][2], c[0][1]
+        # seen from a floor point the quad hides part of the wall: the part of the quad with z >= zl (beyond the floor point and below
+        # the line that projects onto the wall's top edge) is counted by both form factors
+        zl = np.minimum(np.maximum(np.maximum(z0, X2[:, 2] + (yq + 1) / 5.0 * (1 - X2[:, 2])), X2[:, 2]), z1)
+        both = np.where(zl < z1 - 1e-12, ff_rect(X2, x0, x1_, zl, z1, yq), 0.0)
+        Lf = alb_floor * (1 - ff_poly(X2, up, c) - FW + both)
         u = (np.arange(NQ) + 0.5) / NQ
         XQ = np.array([c[0] + a * (c[1] - c[0]) + b * (c[3] - c[0]) for b in u for a in u])
         dAq = np.linalg.norm(np.cross(c[1] - c[0], c[3] - c[0])) / (NQ * NQ)
@@ -426,4 +443,4 @@ def test_deeper_boundary_term_against_a_quadrature_of_the_transport():
     print("quadrature", exact, "adjoint x1 term only", {n: float((g2 * F[n]).sum()) for n in exact}, "with the deeper term", {n: float((g3 * F[n]).sum()) for n in exact})
     assert abs(float((g2 * F["scale"]).sum()) - exact["scale"]) > 0.25 * ref
     for n, ex in exact.items():
-        assert abs(float((g3 * F[n]).sum()) - ex) < 0.10 * ref, (n, float((g3 * F[n]).sum()), ex)
+        assert abs(float((g3 * F[n]).sum()) - ex) < 0.07 * ref, (n, float((g3 * F[n]).sum()), ex)
