@@ -22,6 +22,8 @@ for r in r2_rgb r2_spectral r2_grad; do
 done
 python profiles/summarize.py hot $O/r2_rgb.ncu-rep 3 40 > $O/r2_rgb_hot_bounce2.txt 2>&1
 python profiles/summarize.py hot $O/r2_rgb.ncu-rep 1 40 > $O/r2_rgb_hot_shade.txt 2>&1
+python profiles/summarize.py bysource $O/r2_rgb.ncu-rep "k_shade" 30 > $O/r2_rgb_shade_by_source.txt 2>&1
+python profiles/summarize.py bysource $O/r2_rgb.ncu-rep "k_trace" 30 > $O/r2_rgb_trace_by_source.txt 2>&1
 python profiles/summarize.py launches $O/r2_launches.csv > $O/r2_launches_summary.txt 2>&1
 python profiles/make_kernel_profile.py $O/r2_counters.csv $O/r2_plain.json $O/r2_kernel_profile.json > $O/r2_kernel_profile.log 2>&1
 rm -f $O/r2_spectral.ncu-rep $O/r2_grad.ncu-rep

@@ -4,6 +4,8 @@
   summarize.py launches <launch_list.csv>            per-kernel share of the step (gpu__time_duration.sum pass)
   summarize.py raw <report.ncu-rep>                  key metrics of every captured launch (ncu --set full)
   summarize.py hot <report.ncu-rep> <launch#> [n]    top-n stall-sample SASS lines of one captured launch
+  summarize.py bysource <report.ncu-rep> <kernel regex> [n]   warp instructions of the first matching launch per CUDA source file,
+                                                     and its top-n source lines (needs -lineinfo and --import-source on)
 """
 import collections
 import csv
@@ -88,11 +90,56 @@ def hot(rep, which, n=25):
         print(f"{i:5d} {r[iS]:>8s} {100 * int(r[iS]) / ts:5.1f} {r[iE]:>10s} {r[iT]:>4s}  {r[1].strip()[:70]}")
 
 
+def bysource(rep, kernel, n=30):
+    rows = ncu_csv(rep, "source", ["--print-source", "cuda,sass", "--kernel-name", "regex:" + kernel])
+    secs, cur, fn, path = [], None, None, None
+    for r in rows:
+        if not r:
+            continue
+        if r[0] == "File Path":
+            path = r[1]
+        elif r[0] == "Function Name":
+            fn = r[1]
+        elif r[0] == "Line No":
+            cur = {"file": path, "fn": fn, "hdr": r, "rows": []}
+            secs.append(cur)
+        elif cur is not None and r[0] != "" and len(r) > 2 and r[2] == "-":      # a CUDA source line (SASS rows have an address there)
+            cur["rows"].append(r)
+    if not secs:
+        print("no source-level data for", kernel)
+        return
+    first_fn, seen, lines, per_file, tot = secs[0]["fn"], set(), [], collections.Counter(), 0
+    for sec in secs:                       # the report repeats the pages for every captured launch: keep the first one's
+        if sec["fn"] != first_fn or sec["file"] in seen:
+            continue
+        seen.add(sec["file"])
+        h = sec["hdr"]
+        iE, iT = h.index("Instructions Executed"), h.index("Thread Instructions Executed")
+        for r in sec["rows"]:
+            try:
+                e, t = int(r[iE]), int(r[iT])
+            except ValueError:
+                continue
+            f = sec["file"].split("/")[-1]
+            per_file[f] += e
+            tot += e
+            lines.append((e, t, f, r[0], r[1].strip()[:100]))
+    name = short(first_fn.replace("(bool)0", "0").replace("(bool)1", "1"))
+    print(f"{name}: warp instructions per CUDA source file (inlined code is charged to the file it was written in)")
+    for f, c in per_file.most_common():
+        print(f"  {f:28s} {100 * c / max(tot, 1):5.1f} %")
+    print(f"top {n} source lines (share of warp instructions, active threads per instruction)")
+    for e, t, f, ln, src in sorted(lines, reverse=True)[:n]:
+        print(f"  {100 * e / max(tot, 1):5.2f} %  {t / max(e, 1):5.1f}  {f}:{ln}  {src}")
+
+
 if __name__ == "__main__":
     cmd = sys.argv[1]
     if cmd == "launches":
         launches(sys.argv[2])
     elif cmd == "raw":
         raw(sys.argv[2])
+    elif cmd == "bysource":
+        bysource(sys.argv[2], sys.argv[3], int(sys.argv[4]) if len(sys.argv) > 4 else 30)
     elif cmd == "hot":
         hot(sys.argv[2], int(sys.argv[3]), int(sys.argv[4]) if len(sys.argv) > 4 else 25)
