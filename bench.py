@@ -453,7 +453,11 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # NCCL's version banner / warnings go to stdout by default: keep stdout to the one JSON line
+        # NCCL writes its version banner / warnings to stdout; NCCL_DEBUG_FILE is honoured above the VERSION level only.
+        # Keep stdout to the one JSON line: raise VERSION to WARN (which still prints the banner) and send it all to stderr.
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mi.set_variant("cuda_b200_rgb")
     t_build = time.perf_counter()
