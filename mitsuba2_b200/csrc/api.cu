@@ -48,6 +48,8 @@ struct mtsb_ctx {
     float timeout = -1.f;                    // seconds; <= 0: none (mtsb_set_timeout)
     int profiling = 0;                       // per-stage CUDA-event timing (mtsb_set_profiling)
     int bin_materials = 1;                   // sort queue entries by material class before shading (MTSB_BIN=0 disables)
+    int bin_emitters = 1;                    // ... and by the emitter the path is going to sample (MTSB_BIN_EMITTER=0 disables)
+    int bin_depth1 = 1;                      // primary hits too: coherent in material, but not in the emitter pick (MTSB_BIN_DEPTH1=0: identity lists there)
     unsigned trace_grid = 148 * 8, refill = 22; // persistent traversal launch shape (set in mtsb_ctx_create)
     std::vector<cudaEvent_t> pool;           // event pairs, grown on demand
     std::vector<int> pool_stage; size_t pool_used = 0;
@@ -143,6 +145,8 @@ extern "C" int mtsb_ctx_create(int device, mtsb_ctx **out) {
         if (const char *e = getenv("MTSB_REFILL")) { int v = atoi(e); if (v >= 0 && v <= 32) c->refill = (unsigned) v; }
         c->trace_grid = (unsigned) (sms * per_sm);
         if (const char *e = getenv("MTSB_BIN")) c->bin_materials = atoi(e) != 0;
+        if (const char *e = getenv("MTSB_BIN_EMITTER")) c->bin_emitters = atoi(e) != 0;
+        if (const char *e = getenv("MTSB_BIN_DEPTH1")) c->bin_depth1 = atoi(e) != 0;
     }
     *out = holder.release();
     return MTSB_OK;
@@ -163,7 +167,7 @@ static inline unsigned grid_for(size_t n) { return (unsigned) ((n + kBlock - 1) 
 // counters buffer (uint32 words): [0,1024) live paths per depth, [1024,2048) shadow rays per depth,
 // [2048,3072) work-fetch cursor of the closest-hit launch of that depth, [3072,4096) same for the shadow launch
 // [4096, 8192) shade-class counters, 4 per depth
-constexpr uint32_t kCounterWords = 8192, kWorkClosest = 2048, kWorkShadow = 3072, kClassCounts = 4096;
+constexpr uint32_t kCounterWords = 12288, kWorkClosest = 2048, kWorkShadow = 3072, kClassCounts = 4096;      // class counters: 8 per depth
 static inline unsigned trace_grid_for(const mtsb_ctx *c, size_t n) {
     unsigned g = grid_for(n);
     return g < c->trace_grid ? (g ? g : 1u) : c->trace_grid;
@@ -756,14 +760,14 @@ static int run_batch(mtsb_scene *s, const SensorDev &sn, const RenderBatch &b, c
                                         else k_shade_grad<true, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }
           else if (grad) { if (s->ext) k_shade_grad<false, RgbX><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad);
                            else k_shade_grad<false, Rgb><<<grid_for(n), kBlock, 0, st>>>(s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, *grad); }
-          else if ((depth == 1 && !s->spectral) || !s->ctx->bin_materials) {
-              // rgb: primary hits are coherent enough, identity lists (binning them: 10.85 -> 11.0 ms of shade per C3 step);
-              // the heavier spectral bodies gain from uniform warps even there (20.6 -> 18.6 ms)
+          else if ((depth == 1 && !s->spectral && !s->ctx->bin_depth1) || !s->ctx->bin_materials) {
+              // identity lists.  (Round 1: binning the coherent primary hits of the rgb kernel by material alone cost 10.85 -> 11.0 ms of
+              // shade per C3 step; with the emitter pick in the class it pays: 10.45 -> 10.11 ms, so depth 1 is binned by default now.)
               ShadeBins bins; bins.lists = nullptr; bins.counts = s->counters.p + depth; bins.pool = 0;
               LAUNCH_SHADE(grid_for(n), s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
           } else {
-              ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + 4 * depth; bins.pool = s->pool;
-              k_classify<<<grid_for(n), kBlock, 0, st>>>(s->counters.p + depth, qin.hit, bins);
+              ShadeBins bins; bins.lists = s->class_lists.p; bins.counts = s->counters.p + kClassCounts + kShadeClasses * depth; bins.pool = s->pool;
+              k_classify<<<grid_for(n), kBlock, 0, st>>>(s->counters.p + depth, qin.hit, bins, s->ctx->bin_emitters ? qin.rng : nullptr, depth > s->dev.rr_depth ? 1 : 0, s->dev.n_emitters);
               LAUNCH_SHADE(grid_for((size_t) n + 32 * kShadeClasses), s->dev, b, qin, qout, sq, s->counters.p, s->dstats.p, (uint32_t) depth, bins);
               launches++;
           } }

@@ -412,14 +412,14 @@ __device__ __forceinline__ void block_alloc2(uint32_t *counter_a, bool want_a, u
 // would run the diffuse, rough-conductor, dielectric and environment branches one after the other.  k_classify appends
 // every queue index to the list of its class (warp-aggregated atomics); the shade kernel then walks the four lists
 // back to back, each padded to a warp boundary, so that a warp sees one class only.
-constexpr int kShadeClasses = 4;          // 0 = miss (environment), 1 + BSDF type otherwise
+constexpr int kShadeClasses = 8;          // 0 = miss (environment); hits: 1 + 2 * (BSDF class - 1) + emitter pick (see k_classify)
 struct ShadeBins {
     uint32_t *lists;                      // kShadeClasses x pool queue indices
     uint32_t *counts;                     // kShadeClasses counters of the current depth
     uint32_t pool;
 };
 __global__ void __launch_bounds__(kBlock)
-k_classify(const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins bins) {
+k_classify(const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins bins, const uint4 *__restrict__ rng, int rr_draw, int n_emitters) {
     // block-aggregated append: one global atomic per class and block (instead of one per class and warp)
     __shared__ uint32_t s_warp[kBlock / 32][kShadeClasses], s_base[kShadeClasses];
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -430,6 +430,18 @@ k_classify(const uint32_t *count_ptr, const float4 *__restrict__ hit, ShadeBins 
     if (i < count) {
         float4 h = hit[i];
         cls = h.x != INFINITY ? (int) (f2u(h.w) >> 30) : 0;       // class tag written by k_trace
+        if (cls > 0) {
+            // with two emitters every path picks one from its own sample (scene.cpp:141-160): the area light's triangle sample and
+            // the environment map's hierarchical warp would run one after the other in a mixed warp.  The pick is the next draw of
+            // the path's stream (after the Russian-roulette draw where there is one), replayed here.
+            int pick = 0;
+            if (rng != nullptr && n_emitters == 2) {
+                Pcg32 r = rng_load(rng[i]);
+                if (rr_draw) (void) r.next_f32();
+                pick = r.next_f32() * 2.f >= 1.f ? 1 : 0;
+            }
+            cls = 1 + 2 * (cls - 1) + pick;
+        }
     }
     uint32_t rank = 0;
 #pragma unroll
