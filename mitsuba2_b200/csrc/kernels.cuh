@@ -300,16 +300,21 @@ __device__ __forceinline__ void trace_persistent(const Bvh &bvh, uint32_t count,
                             ok = woop_intersect(rw, xyz(r0), xyz(a0), xyz(a1), xyz(a2), r0.w, r1.w, t, u, v);
                         if (ok) {
                             ws.hitrec[lane] = make_float4(t, u, v, a0.w);
-                            atomicMin(&ws.best[src], ((unsigned long long) float_order_bits(t) << 32) | lane);
+                            // key = t | primitive id | testing lane: between candidates at the same t the lowest primitive id wins, whoever tested it
+                            atomicMin(&ws.best[src], ((unsigned long long) float_order_bits(t) << 32) | ((unsigned long long) (f2u(a0.w) & 0x07ffffffu) << 5) | lane);
                         }
                     }
                     __syncwarp();
                     unsigned long long bk = ws.best[lane];
                     if (bk != ~0ull) {      // the closest accepted candidate of my ray was tested by lane (bk & 31)
                         float4 r = ws.hitrec[(uint32_t) bk & 31u];
-                        found = true; tmax = r.x;
-                        hit.t = r.x; hit.u = r.y; hit.v = r.z; hit.prim = f2u(r.w);
-                        ws.ray[1][lane].w = r.x;
+                        // a later candidate at exactly the current t replaces the hit only if its primitive id is lower: the answer
+                        // does not depend on which rays share the warp or in which pass a triangle was tested
+                        if (AnyHit || !found || r.x < tmax || f2u(r.w) < hit.prim) {
+                            found = true; tmax = r.x;
+                            hit.t = r.x; hit.u = r.y; hit.v = r.z; hit.prim = f2u(r.w);
+                            ws.ray[1][lane].w = r.x;
+                        }
                         ws.best[lane] = ~0ull;
                     }
                     __syncwarp();
